@@ -1,0 +1,134 @@
+/*
+ * b200_lowbit.h -- C ABI of libb200lowbit.so: the B200 (sm_100a) replacement for the
+ * low-bit linear entry points ipex-llm binds from its closed `libllama-api.so`.
+ *
+ * Reference paths are relative to /root/reference/python/llm/src/ipex_llm/ :
+ *   LC = ggml/model/llama/llama_cpp.py      LBL = transformers/low_bit_linear.py
+ *
+ * Two families:
+ *  (1) reference-named symbols with the reference's exact signatures.  They take HOST
+ *      pointers (that is what the reference passes), copy to the GPU, run the CUDA
+ *      kernels and copy back.  There is NO CPU implementation behind them: without a
+ *      usable CUDA device they record an error (b200_lowbit_last_error) and write nothing.
+ *  (2) `*_cuda` symbols taking DEVICE pointers and a cudaStream_t (as void*); they only
+ *      enqueue work on that stream and return 0 or a non-zero error code.  The Python
+ *      host (ipex_llm_b200/transformers/low_bit_linear.py) uses these.
+ *
+ * Ownership: the caller allocates every buffer it passes; the library keeps no pointer
+ * after the call returns (LBL:113-148, :506).  Library-owned state is a per-device
+ * staging/workspace cache used only by family (1) and by lowbit_matmul_cuda when the
+ * caller passes workspace == NULL.
+ */
+#ifndef B200_LOWBIT_H
+#define B200_LOWBIT_H
+
+#include <stddef.h>
+#include <stdint.h>
+#include <stdbool.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* qtype values: ggml/quantize.py:28-60.  In scope: */
+enum {
+    B200_QT_SYM_INT4 = 2,   /* "sym_int4"  (q4_0 lineage), 34-byte blocks of 64 */
+    B200_QT_ASYM_INT4 = 3,  /* "asym_int4" (q4_1 lineage), 36-byte blocks of 64 */
+    B200_QT_NF4 = 10,       /* "nf4",      34-byte blocks of 64 */
+    B200_QT_FP8_E4M3 = 15,  /* "fp8_e4m3", 66-byte blocks of 64 */
+    B200_QT_FP8_E5M2 = 19,  /* "fp8_e5m2" / "fp8", 66-byte blocks of 64 */
+    B200_QT_FP6 = 29,       /* "fp6" (e3m2), 50-byte blocks of 64 */
+    B200_QT_WOQ_INT4 = 34   /* alias of sym_int4 (convert.py:1101-1109 on torch >= 2.6 string compare) */
+};
+
+/* element types of activations / outputs for the *_cuda matmul entry points */
+enum { B200_DT_F32 = 0, B200_DT_F16 = 1, B200_DT_BF16 = 2 };
+
+/* ------------------------------------------------------------------ family (1) */
+
+/* replaces LC:1189-1193 llama_init_backend(): selects nothing, allocates nothing. */
+void llama_init_backend(void);
+
+/* replaces LC:1050-1056 ggml_type_size: bytes per block record; 0 for unsupported qtypes */
+size_t ggml_type_size(int qtype);
+/* replaces LC:1059-1065 ggml_qk_size: elements per block; 0 for unsupported qtypes */
+int ggml_qk_size(int qtype);
+
+/* replaces LC:946-967 ggml_quantize_tensor (called at LBL:180).
+ * src: n fp32 values, row length k (k % QK == 0); dst: (n/QK)*type_size bytes in the
+ * canonical block layout; hist: 16 x int64 code histogram for the 4-bit types (may be NULL);
+ * returns bytes written, 0 on error. */
+size_t ggml_quantize_tensor(const float* src, void* dst, int qtype, size_t n, int k,
+                            int64_t* hist, bool scale_search);
+
+/* replaces LC:1068-1080 ggml_dequantize_q4_0 (LBL:256-266): sym_int4 blocks -> k fp32 */
+void ggml_dequantize_q4_0(const void* src, void* dst, size_t k);
+/* replaces LC:1084-1099 ggml_dequantize (LBL:269-279): any in-scope qtype -> k fp32 */
+void ggml_dequantize(const void* src, void* dst, size_t k, int qtype);
+
+/* replace LC:1102-1135 ggml_q_format_convet_cpu2xpu / xpu2cpu (LBL:198-253): same-size
+ * relayout canonical <-> device layout.  The B200 device layout is tiled by 16 rows, so the
+ * row length must be known: these reference-shaped symbols use the row length registered
+ * by b200_lowbit_set_row_length() on the calling thread (error if unset or if n is not a
+ * multiple of it).  New code should call the *_2d forms below. */
+void ggml_q_format_convet_cpu2xpu(const void* src, void* dst, size_t n, int qtype);
+void ggml_q_format_convet_xpu2cpu(const void* src, void* dst, size_t n, int qtype);
+void b200_lowbit_set_row_length(int k);
+int ggml_q_format_convert_cpu2cuda_2d(const void* src, void* dst, int64_t rows, int64_t k, int qtype);
+int ggml_q_format_convert_cuda2cpu_2d(const void* src, void* dst, int64_t rows, int64_t k, int qtype);
+
+/* replaces LC:1154-1185 ggml_compute_forward_mul_mat_q_fp32 (LBL:494-529).
+ * src0_ne = (K, N), src1_ne = (K, M) (LBL:509-516); w = canonical packed [N][K/QK] blocks;
+ * x = fp32 [M][K]; result = fp32 [M][N].  All host pointers. */
+void ggml_compute_forward_mul_mat_q_fp32(const int64_t* src0_ne, const void* w, int qtype,
+                                         const int64_t* src1_ne, const void* x, void* result);
+
+/* error channel for the void / size_t symbols above (the reference ABI has none, LBL checks
+ * preconditions in Python).  0 = ok.  The string is valid until the next call on the thread. */
+int b200_lowbit_last_error(void);
+const char* b200_lowbit_last_error_string(void);
+void b200_lowbit_clear_error(void);
+
+/* ------------------------------------------------------------------ family (2) */
+
+/* device-pointer twin of ggml_quantize_tensor; d_hist may be NULL. */
+int ggml_quantize_tensor_cuda(const float* d_src, void* d_dst, int qtype, size_t n, int k,
+                              int64_t* d_hist, bool scale_search, void* stream);
+/* device-pointer twin of ggml_dequantize over the CANONICAL layout; out_dtype B200_DT_* */
+int ggml_dequantize_cuda(const void* d_src, void* d_dst, size_t k, int qtype, int out_dtype,
+                         void* stream);
+/* dequantize a [rows][k] weight held in the DEVICE (tiled) layout */
+int lowbit_dequantize_device_layout_cuda(const void* d_src, void* d_dst, int64_t rows, int64_t k,
+                                         int qtype, int out_dtype, void* stream);
+/* canonical <-> device layout on device buffers (same byte size, src != dst).
+ * to_device != 0: canonical -> tiled ; 0: tiled -> canonical. */
+int lowbit_relayout_cuda(const void* d_src, void* d_dst, int64_t rows, int64_t k, int qtype,
+                         int to_device, void* stream);
+
+/* bytes of workspace lowbit_matmul_cuda needs for this problem (split-K partials, arrival
+ * counters, fp32-activation split planes).  The workspace must be zero-filled once before
+ * its first use and may then be reused by any number of calls that do not overlap in time. */
+size_t lowbit_matmul_workspace_size(int64_t n_rows, int64_t k, int64_t m, int x_dtype);
+
+/* y[M][N] (+)= x[M][K] . dequant(W[N][K])^T  -- the XPU-side op `xe_linear.forward_new` /
+ * `xe_batch.batch_forward` (LBL:696-708) and the CPU-side ggml_compute_forward_mul_mat_q_fp32.
+ * d_w: weight in the DEVICE (tiled) layout.  d_x: [M][K] of x_dtype, row stride k.
+ * d_y: [M][N] of y_dtype, row stride n_rows.  d_bias: NULL or [N] of y_dtype (added once).
+ * accumulate != 0: y += result (residual add), else y = result.
+ * workspace: NULL (library-owned per-device workspace; serialises callers on one device) or a
+ * zero-initialised buffer of at least lowbit_matmul_workspace_size() bytes.
+ * Any M >= 1: M <= 64 runs the HBM-bound GEMV kernel, larger M the tensor-core GEMM. */
+int lowbit_matmul_cuda(const void* d_w, int qtype, int64_t n_rows, int64_t k,
+                       const void* d_x, int x_dtype, int64_t m,
+                       void* d_y, int y_dtype, const void* d_bias, int accumulate,
+                       void* workspace, size_t workspace_bytes, void* stream);
+
+/* number of kernels the last lowbit_* / ggml_*_cuda call on this thread launched */
+int b200_lowbit_last_launch_count(void);
+/* SM count of the current device (0 if no device) */
+int b200_lowbit_sm_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200_LOWBIT_H */

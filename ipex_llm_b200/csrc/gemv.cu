@@ -1,0 +1,177 @@
+// gemv.cu -- host side of kernel (b): workspace layout, grid sizing, qtype dispatch, plus the
+// scalar generic kernel (nf4 until its mma codec lands; rows beyond the last 16-row tile) and
+// the fp32 -> 3 x bf16 activation split.  The mma kernel itself is in gemv_kernel.cuh.
+#include "lowbit_common.cuh"
+#include "lowbit_internal.h"
+#include "gemv_args.h"
+
+namespace lowbit {
+
+void gemv_launch_sym_int4(int x_dtype, int nt, int grid, const GemvArgs& A, cudaStream_t st);
+void gemv_launch_asym_int4(int x_dtype, int nt, int grid, const GemvArgs& A, cudaStream_t st);
+void gemv_launch_fp8_e4m3(int x_dtype, int nt, int grid, const GemvArgs& A, cudaStream_t st);
+void gemv_launch_fp8_e5m2(int x_dtype, int nt, int grid, const GemvArgs& A, cudaStream_t st);
+void gemv_launch_fp6(int x_dtype, int nt, int grid, const GemvArgs& A, cudaStream_t st);
+
+// ------------------------------------------------------------------ generic (any qtype, tail rows)
+// one warp per output row, scalar decode; used for nf4 until its mma codec lands, and for the
+// rows beyond the last full 16-row tile (kept in canonical records in the tail region).
+template <typename XT>
+__global__ void gemv_generic_kernel(const uint8_t* __restrict__ w, TiledGeom G, int qt, int64_t row_begin,
+                                    int64_t row_end, const XT* __restrict__ x, int M, void* y, int y_dtype,
+                                    const void* bias, int accumulate) {
+    const int lane = threadIdx.x & 31;
+    const int64_t row = row_begin + (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    if (row >= row_end) return;
+    const int hdr = header_bytes(qt);
+    for (int m0 = 0; m0 < M; m0 += 8) {
+        float acc[8];
+#pragma unroll
+        for (int i = 0; i < 8; i++) acc[i] = 0.0f;
+        for (int64_t kb = 0; kb < G.nb; kb++) {
+            float d, mn = 0.0f; uint32_t c0, c1;
+            if (row < G.r16) {
+                const int64_t f = (row / 16) * G.nb + kb;
+                const int r = (int)(row % 16);
+                const uint8_t* tile = w + f * G.tile_code_bytes;
+                c0 = tiled_code(qt, tile, r, lane); c1 = tiled_code(qt, tile, r, lane + 32);
+                d = half_bits_to_float(((const uint16_t*)(w + G.off_s + f * 32))[(r & 7) * 2 + (r >> 3)]);
+                if (G.has_m) mn = half_bits_to_float(((const uint16_t*)(w + G.off_m + f * 32))[(r & 7) * 2 + (r >> 3)]);
+            } else {
+                const uint8_t* rec = w + G.off_tail + ((row - G.r16) * G.nb + kb) * G.blk_bytes;
+                d = half_bits_to_float((uint16_t)rec[0] | ((uint16_t)rec[1] << 8));
+                if (G.has_m) mn = half_bits_to_float((uint16_t)rec[2] | ((uint16_t)rec[3] << 8));
+                c0 = canonical_code(qt, rec + hdr, lane); c1 = canonical_code(qt, rec + hdr, lane + 32);
+            }
+            float w0 = __fmul_rn(code_value(qt, c0), d), w1 = __fmul_rn(code_value(qt, c1), d);
+            if (G.has_m) { w0 = __fadd_rn(w0, mn); w1 = __fadd_rn(w1, mn); }
+#pragma unroll
+            for (int i = 0; i < 8; i++) {
+                if (m0 + i < M) {
+                    const XT* xr = x + (int64_t)(m0 + i) * G.k + kb * 64;
+                    acc[i] = fmaf(w0, to_float<XT>(xr[lane]), acc[i]);
+                    acc[i] = fmaf(w1, to_float<XT>(xr[lane + 32]), acc[i]);
+                }
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+#pragma unroll
+            for (int o = 16; o; o >>= 1) acc[i] += __shfl_xor_sync(0xffffffffu, acc[i], o);
+            if (lane == 0 && m0 + i < M)
+                store_out(y, y_dtype, (int64_t)(m0 + i) * G.rows + row, acc[i], bias, row, accumulate);
+        }
+    }
+}
+
+// fp32 activations -> three bf16 planes (hi, mid, lo) whose sum reproduces x to ~2^-24
+__global__ void split_f32_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ out, int64_t n) {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const float v = x[i];
+        const __nv_bfloat16 hi = __float2bfloat16_rn(v);
+        const float r1 = v - __bfloat162float(hi);
+        const __nv_bfloat16 mid = __float2bfloat16_rn(r1);
+        const float r2 = r1 - __bfloat162float(mid);
+        out[i] = hi; out[n + i] = mid; out[2 * n + i] = __float2bfloat16_rn(r2);
+    }
+}
+
+// ------------------------------------------------------------------ host side
+static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+static int max_total_warps() { return sm_count() * GEMV_CTAS_PER_SM * GEMV_WARPS; }
+
+constexpr size_t kCounterBytes = 256 * 1024;                 // 65536 row tiles = 1M rows
+struct WsLayout { size_t counters, partials, xsplit, total; };
+static WsLayout ws_layout(int64_t n_rows, int64_t k, int64_t m, int x_dtype) {
+    WsLayout L;
+    const int64_t mm = m < 8 * GEMV_MAX_NT ? m : 8 * GEMV_MAX_NT;
+    const int nt = mm <= 8 ? 1 : mm <= 16 ? 2 : 4;
+    // fixed-size counter region: a workspace shared by calls with different n_rows must keep
+    // the counters where no other call's partials can land
+    (void)n_rows;
+    L.counters = 0;
+    L.partials = kCounterBytes;
+    L.xsplit = L.partials + align_up((size_t)max_total_warps() * 2 * nt * 128 * sizeof(float), 256);
+    L.total = L.xsplit + (x_dtype == DT_F32 ? align_up((size_t)3 * mm * k * 2, 256) : 0);
+    return L;
+}
+
+size_t gemv_workspace_size(int64_t n_rows, int64_t k, int64_t m, int x_dtype) {
+    return ws_layout(n_rows, k, m, x_dtype).total;
+}
+
+static bool has_mma_codec(int qt) {
+    return qt == QT_SYM_INT4 || qt == QT_ASYM_INT4 || qt == QT_FP8_E4M3 || qt == QT_FP8_E5M2 || qt == QT_FP6;
+}
+
+template <typename XT>
+static void launch_generic(const void* w, const TiledGeom& G, int qt, int64_t r0, int64_t r1, const void* x, int M,
+                           void* y, int y_dtype, const void* bias, int accumulate, cudaStream_t st) {
+    const int warps = 4;
+    const int grid = (int)((r1 - r0 + warps - 1) / warps);
+    gemv_generic_kernel<XT><<<grid, warps * 32, 0, st>>>((const uint8_t*)w, G, qt, r0, r1, (const XT*)x, M, y, y_dtype,
+                                                        bias, accumulate);
+}
+
+int gemv_launch(const void* w, int qt, int64_t n_rows, int64_t k, const void* x, int x_dtype, int64_t m,
+                void* y, int y_dtype, const void* bias, int accumulate, void* workspace,
+                size_t workspace_bytes, cudaStream_t st) {
+    qt = canon_qtype(qt);
+    if (!supported(qt) || k <= 0 || k % QK || n_rows <= 0 || m <= 0) return LB_ERR_ARG;
+    if (x_dtype < 0 || x_dtype > 2 || y_dtype < 0 || y_dtype > 2) return LB_ERR_ARG;
+    if ((size_t)((n_rows + 15) / 16) * sizeof(unsigned) > kCounterBytes) return LB_ERR_ARG;
+    const TiledGeom G = make_geom(n_rows, k, qt);
+    const int esz_x = x_dtype == DT_F32 ? 4 : 2, esz_y = y_dtype == DT_F32 ? 4 : 2;
+
+    // M beyond one pass: chunks of 32 activation rows (the tensor-core GEMM takes over for large M)
+    for (int64_t mb = 0; mb < m; mb += 8 * GEMV_MAX_NT) {
+        const int64_t mc = (m - mb) < 8 * GEMV_MAX_NT ? (m - mb) : 8 * GEMV_MAX_NT;
+        const char* xc = (const char*)x + (size_t)mb * k * esz_x;
+        char* yc = (char*)y + (size_t)mb * n_rows * esz_y;
+        int64_t mma_rows = has_mma_codec(qt) ? G.r16 : 0;
+        if (mma_rows > 0) {
+            const WsLayout L = ws_layout(n_rows, k, mc, x_dtype);
+            if (!workspace || workspace_bytes < L.total) return LB_ERR_WORKSPACE;
+            GemvArgs A;
+            A.w = (const uint8_t*)w; A.G = G; A.M = (int)mc;
+            A.y = yc; A.y_dtype = y_dtype; A.bias = bias; A.accumulate = accumulate;
+            A.counters = (unsigned*)((char*)workspace + L.counters);
+            A.partials = (float*)((char*)workspace + L.partials);
+            A.plane_stride = mc * k;
+            if (x_dtype == DT_F32) {
+                __nv_bfloat16* planes = (__nv_bfloat16*)((char*)workspace + L.xsplit);
+                const int64_t n = mc * k;
+                int sg = (int)((n + 255) / 256); if (sg > sm_count() * 8) sg = sm_count() * 8;
+                split_f32_kernel<<<sg, 256, 0, st>>>((const float*)xc, planes, n);
+                note_launch();
+                A.x = (const uint16_t*)planes;
+            } else A.x = (const uint16_t*)xc;
+            const int nt = mc <= 8 ? 1 : mc <= 16 ? 2 : 4;
+            int64_t tw = max_total_warps();
+            const int64_t want = (G.ntiles + 1) / 2;          // at least ~2 tiles per warp
+            if (tw > want) tw = want;
+            if (tw < 1) tw = 1;
+            const int grid = (int)((tw + GEMV_WARPS - 1) / GEMV_WARPS);
+            A.total_warps = grid * GEMV_WARPS;
+            switch (qt) {
+                case QT_SYM_INT4:  gemv_launch_sym_int4(x_dtype, nt, grid, A, st); break;
+                case QT_ASYM_INT4: gemv_launch_asym_int4(x_dtype, nt, grid, A, st); break;
+                case QT_FP8_E4M3:  gemv_launch_fp8_e4m3(x_dtype, nt, grid, A, st); break;
+                case QT_FP8_E5M2:  gemv_launch_fp8_e5m2(x_dtype, nt, grid, A, st); break;
+                case QT_FP6:       gemv_launch_fp6(x_dtype, nt, grid, A, st); break;
+                default: return LB_ERR_ARG;
+            }
+            note_launch();
+        }
+        if (mma_rows < n_rows) {
+            if (x_dtype == DT_F32) launch_generic<float>(w, G, qt, mma_rows, n_rows, xc, (int)mc, yc, y_dtype, bias, accumulate, st);
+            else if (x_dtype == DT_F16) launch_generic<__half>(w, G, qt, mma_rows, n_rows, xc, (int)mc, yc, y_dtype, bias, accumulate, st);
+            else launch_generic<__nv_bfloat16>(w, G, qt, mma_rows, n_rows, xc, (int)mc, yc, y_dtype, bias, accumulate, st);
+            note_launch();
+        }
+    }
+    return check_launch();
+}
+
+}  // namespace lowbit

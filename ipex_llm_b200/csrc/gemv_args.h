@@ -1,0 +1,45 @@
+// gemv_args.h -- launch-parameter block and constants shared by gemv.cu (host) and
+// gemv_kernel.cuh (device) of the dequant-GEMV.
+#pragma once
+#include "lowbit_common.cuh"
+
+namespace lowbit {
+
+constexpr int GEMV_WARPS = 4;          // warps per CTA
+constexpr int GEMV_CTAS_PER_SM = 4;    // resident CTAs per SM we size the grid for
+constexpr int GEMV_MAX_NT = 4;         // n-tiles of 8 activation rows -> M <= 32 per pass
+
+struct GemvArgs {
+    const uint8_t* w;
+    TiledGeom G;
+    const uint16_t* x;        // NS planes of [M][K] fp16 or bf16
+    int64_t plane_stride;     // elements between planes
+    int M;
+    void* y; int y_dtype;     // [M][rows]
+    const void* bias;         // NULL or [rows] of y_dtype
+    int accumulate;
+    float* partials;          // [total_warps][2][NT][4][32]
+    unsigned* counters;       // [rows/16], zero between calls
+    int total_warps;
+};
+
+__device__ __forceinline__ void store_out(void* y, int dt, int64_t idx, float v, const void* bias, int64_t row, int acc) {
+    if (dt == DT_F32) {
+        float* p = (float*)y + idx;
+        if (bias) v += ((const float*)bias)[row];
+        if (acc) v += __ldcg(p);
+        *p = v;
+    } else if (dt == DT_F16) {
+        __half* p = (__half*)y + idx;
+        if (bias) v += __half2float(((const __half*)bias)[row]);
+        if (acc) v += __half2float(__ldcg(p));
+        *p = __float2half_rn(v);
+    } else {
+        __nv_bfloat16* p = (__nv_bfloat16*)y + idx;
+        if (bias) v += __bfloat162float(((const __nv_bfloat16*)bias)[row]);
+        if (acc) v += __bfloat162float(__ldcg(p));
+        *p = __float2bfloat16_rn(v);
+    }
+}
+
+}  // namespace lowbit

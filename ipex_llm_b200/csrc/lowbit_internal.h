@@ -1,0 +1,41 @@
+// lowbit_internal.h -- declarations shared between the .cu translation units of
+// libb200lowbit.so (not installed; the public ABI is include/b200_lowbit.h).
+#pragma once
+#include <cuda_runtime.h>
+#include <stddef.h>
+#include <stdint.h>
+
+namespace lowbit {
+
+enum {
+    LB_OK = 0,
+    LB_ERR_ARG = 1,        // bad qtype / shape / pointer combination
+    LB_ERR_CUDA = 2,       // a CUDA runtime call failed (see last_error_string)
+    LB_ERR_NO_DEVICE = 3,  // no usable CUDA device: there is no CPU fallback
+    LB_ERR_WORKSPACE = 4,  // caller workspace too small
+};
+
+// per-thread error / launch bookkeeping (capi.cu)
+void set_error(int code, const char* fmt, ...);
+void note_launch();
+int check_launch();   // cudaGetLastError() -> LB_OK / LB_ERR_CUDA (records the message)
+int sm_count();       // SMs of the current device (cached per device)
+
+// layout.cu
+int relayout_launch(const void* src, void* dst, int64_t rows, int64_t k, int qt, bool to_device,
+                    cudaStream_t st);
+int dequant_canonical_launch(const void* src, void* dst, size_t n, int qt, int out_dtype, cudaStream_t st);
+int dequant_tiled_launch(const void* src, void* dst, int64_t rows, int64_t k, int qt, int out_dtype,
+                         cudaStream_t st);
+
+// quantize.cu
+int quantize_launch(const float* src, void* dst, int qt, size_t n, int k, int64_t* hist, bool scale_search,
+                    cudaStream_t st);
+
+// gemv.cu
+size_t gemv_workspace_size(int64_t n_rows, int64_t k, int64_t m, int x_dtype);
+int gemv_launch(const void* w, int qt, int64_t n_rows, int64_t k, const void* x, int x_dtype, int64_t m,
+                void* y, int y_dtype, const void* bias, int accumulate, void* workspace,
+                size_t workspace_bytes, cudaStream_t st);
+
+}  // namespace lowbit

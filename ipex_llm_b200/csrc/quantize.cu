@@ -1,0 +1,209 @@
+// quantize.cu -- kernel (a): fp32 -> canonical low-bit block records on the GPU.
+//
+// Replaces ggml_quantize_tensor (reference llama_cpp.py:946-967, called from
+// low_bit_linear.py:180).  One warp quantises one 64-element block: lane l owns elements l
+// and l+32, which are exactly the two codes packed into byte l of a 4-bit record
+// (convert.py:421-426).  All arithmetic that decides a code is done with explicit
+// __fmul_rn/__fadd_rn/__fdiv_rn so that nvcc cannot contract it into FMAs: the result must
+// be bit-identical to the sequential CPU statement of the same formulas.
+//   sym_int4 : d = signed-absmax / -8 (first max wins), code = min(15, (int8)(x*(1/d) + 8.5))
+//   asym_int4: d = (max-min)/15, m = min,               code = min(15, (int8)((x-min)*(1/d) + 0.5))
+//   nf4      : d = absmax, code = nearest NormalFloat4 entry (ties to the lower index)
+//   fp8/fp6  : d = absmax / MAX, code = RNE-saturating e4m3 / e5m2 / e3m2 of x*(1/d);
+//              scale_search tries 9 multipliers of d and keeps the least squared error.
+// HBM-bound: 4 bytes read per element, ~0.53-1.03 written.
+#include <cuda_fp8.h>
+#include <cuda_fp6.h>
+#include "lowbit_common.cuh"
+#include "lowbit_internal.h"
+
+namespace lowbit {
+
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+    for (int o = 16; o; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+// (key value, index) reductions that reproduce "first occurrence wins" of a serial scan
+__device__ __forceinline__ void warp_argbest(float& key, int& idx, float& val, bool want_max) {
+#pragma unroll
+    for (int o = 16; o; o >>= 1) {
+        const float ok = __shfl_xor_sync(0xffffffffu, key, o);
+        const int oi = __shfl_xor_sync(0xffffffffu, idx, o);
+        const float ov = __shfl_xor_sync(0xffffffffu, val, o);
+        const bool better = want_max ? (ok > key) : (ok < key);
+        if (better || (ok == key && oi < idx)) { key = ok; idx = oi; val = ov; }
+    }
+}
+
+template <int QT> __device__ __forceinline__ float fmt_max() {
+    return QT == QT_FP8_E4M3 ? 448.0f : QT == QT_FP8_E5M2 ? 57344.0f : 28.0f;
+}
+
+template <int QT> __device__ __forceinline__ uint32_t mini_encode(float v) {
+    if (QT == QT_FP8_E4M3) return __nv_cvt_float_to_fp8(v, __NV_SATFINITE, __NV_E4M3);
+    if (QT == QT_FP8_E5M2) return __nv_cvt_float_to_fp8(v, __NV_SATFINITE, __NV_E5M2);
+    return __nv_cvt_float_to_fp6(v, __NV_E3M2, cudaRoundNearest);
+}
+template <int QT> __device__ __forceinline__ float mini_decode(uint32_t c) {
+    if (QT == QT_FP8_E4M3) return decode_e4m3(c);
+    if (QT == QT_FP8_E5M2) return decode_e5m2(c);
+    return decode_e3m2(c);
+}
+
+__device__ __forceinline__ uint32_t nf4_encode(float v) {
+    uint32_t c = 0;
+#pragma unroll
+    for (int i = 0; i < 15; i++) {
+        const float mid = __fmul_rn(__fadd_rn(kNF4Table[i], kNF4Table[i + 1]), 0.5f);
+        c += (v > mid) ? 1u : 0u;
+    }
+    return c;
+}
+
+static __device__ __constant__ float kSearchFactors[9] = {1.0f, 0.95f, 1.05f, 0.9f, 1.1f, 0.85f, 1.15f, 0.8f, 1.2f};
+
+constexpr int QUANT_WARPS = 8;
+
+template <int QT>
+__global__ void __launch_bounds__(QUANT_WARPS * 32)
+quantize_kernel(const float* __restrict__ src, uint8_t* __restrict__ dst, size_t nblk,
+                unsigned long long* __restrict__ hist, int scale_search) {
+    constexpr int BS = (QT == QT_ASYM_INT4) ? 36 : (QT == QT_FP8_E4M3 || QT == QT_FP8_E5M2) ? 66
+                     : (QT == QT_FP6) ? 50 : 34;
+    constexpr bool IS4 = (QT == QT_SYM_INT4 || QT == QT_ASYM_INT4 || QT == QT_NF4);
+    __shared__ unsigned int s_hist[16];
+    __shared__ float s_err[QUANT_WARPS][9][64];   // scale search only (fp8 / fp6)
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (IS4 && hist) { if (threadIdx.x < 16) s_hist[threadIdx.x] = 0; __syncthreads(); }
+
+    const size_t wstride = (size_t)gridDim.x * QUANT_WARPS;
+    for (size_t b = (size_t)blockIdx.x * QUANT_WARPS + warp; b < nblk; b += wstride) {
+        const float x0 = src[b * 64 + lane], x1 = src[b * 64 + 32 + lane];
+        uint8_t* out = dst + b * BS;
+        uint32_t q0 = 0, q1 = 0;
+        if (QT == QT_SYM_INT4) {
+            float a0 = fabsf(x0), a1 = fabsf(x1);
+            float key = a0, val = x0; int idx = lane;
+            if (a1 > a0) { key = a1; val = x1; idx = lane + 32; }
+            warp_argbest(key, idx, val, true);
+            const float d = (key > 0.0f) ? __fdiv_rn(val, -8.0f) : __fdiv_rn(0.0f, -8.0f);
+            const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
+            int i0 = (int)(signed char)(int)__fadd_rn(__fmul_rn(x0, id), 8.5f);
+            int i1 = (int)(signed char)(int)__fadd_rn(__fmul_rn(x1, id), 8.5f);
+            q0 = min(15, i0); q1 = min(15, i1);
+            if (lane == 0) { const __half_raw h = __float2half_rn(d); out[0] = h.x & 0xff; out[1] = h.x >> 8; }
+            out[2 + lane] = (uint8_t)(q0 | (q1 << 4));
+        } else if (QT == QT_ASYM_INT4) {
+            float kmin = x0, vmin = x0; int imin = lane;
+            if (x1 < x0) { kmin = x1; vmin = x1; imin = lane + 32; }
+            warp_argbest(kmin, imin, vmin, false);
+            float kmax = x0, vmax = x0; int imax = lane;
+            if (x1 > x0) { kmax = x1; vmax = x1; imax = lane + 32; }
+            warp_argbest(kmax, imax, vmax, true);
+            const float mn = vmin, mx = vmax;
+            const float d = __fdiv_rn(__fsub_rn(mx, mn), 15.0f);
+            const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
+            int i0 = (int)(signed char)(int)__fadd_rn(__fmul_rn(__fsub_rn(x0, mn), id), 0.5f);
+            int i1 = (int)(signed char)(int)__fadd_rn(__fmul_rn(__fsub_rn(x1, mn), id), 0.5f);
+            q0 = min(15, i0); q1 = min(15, i1);
+            if (lane == 0) {
+                const __half_raw h = __float2half_rn(d), m = __float2half_rn(mn);
+                out[0] = h.x & 0xff; out[1] = h.x >> 8; out[2] = m.x & 0xff; out[3] = m.x >> 8;
+            }
+            out[4 + lane] = (uint8_t)(q0 | (q1 << 4));
+        } else if (QT == QT_NF4) {
+            const float d = warp_max(fmaxf(fabsf(x0), fabsf(x1)));
+            const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
+            q0 = nf4_encode(__fmul_rn(x0, id)); q1 = nf4_encode(__fmul_rn(x1, id));
+            if (lane == 0) { const __half_raw h = __float2half_rn(d); out[0] = h.x & 0xff; out[1] = h.x >> 8; }
+            out[2 + lane] = (uint8_t)(q0 | (q1 << 4));
+        } else {
+            const float amax = warp_max(fmaxf(fabsf(x0), fabsf(x1)));
+            const float d0 = __fdiv_rn(amax, fmt_max<QT>());
+            float d = d0;
+            if (scale_search && d0 != 0.0f) {
+                // every lane evaluates its two elements for the 9 candidate scales; lanes 0..8
+                // then add up one candidate each in element order (the order of the sequential
+                // statement), and lane 0 keeps the first strictly-smallest error.
+#pragma unroll 1
+                for (int c = 0; c < 9; c++) {
+                    const float dc = __fmul_rn(d0, kSearchFactors[c]);
+                    const float idc = __fdiv_rn(1.0f, dc);
+                    const float d16 = __half2float(__float2half_rn(dc));
+                    const float e0 = __fsub_rn(__fmul_rn(mini_decode<QT>(mini_encode<QT>(__fmul_rn(x0, idc))), d16), x0);
+                    const float e1 = __fsub_rn(__fmul_rn(mini_decode<QT>(mini_encode<QT>(__fmul_rn(x1, idc))), d16), x1);
+                    s_err[warp][c][lane] = __fmul_rn(e0, e0);
+                    s_err[warp][c][lane + 32] = __fmul_rn(e1, e1);
+                }
+                __syncwarp();
+                float err = 0.0f;
+                if (lane < 9) for (int j = 0; j < 64; j++) err = __fadd_rn(err, s_err[warp][lane][j]);
+                float best = __int_as_float(0x7f800000); int bc = 0;
+                for (int c = 0; c < 9; c++) {
+                    const float ec = __shfl_sync(0xffffffffu, err, c);
+                    if (ec < best) { best = ec; bc = c; }
+                }
+                d = __fmul_rn(d0, kSearchFactors[bc]);
+                __syncwarp();
+            }
+            const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
+            q0 = mini_encode<QT>(__fmul_rn(x0, id)); q1 = mini_encode<QT>(__fmul_rn(x1, id));
+            if (lane == 0) { const __half_raw h = __float2half_rn(d); out[0] = h.x & 0xff; out[1] = h.x >> 8; }
+            if (QT == QT_FP6) {
+                // 4 consecutive 6-bit codes -> 3 bytes, little-endian (c0 | c1<<6 | c2<<12 | c3<<18)
+                const int base = lane & ~3;
+                uint32_t w0 = 0, w1 = 0;
+#pragma unroll
+                for (int i = 0; i < 4; i++) {
+                    w0 |= (__shfl_sync(0xffffffffu, q0, base + i) & 0x3f) << (6 * i);
+                    w1 |= (__shfl_sync(0xffffffffu, q1, base + i) & 0x3f) << (6 * i);
+                }
+                const int byte = lane & 3, grp = lane >> 2;
+                if (byte < 3) {
+                    out[2 + 3 * grp + byte] = (uint8_t)(w0 >> (8 * byte));
+                    out[2 + 3 * (grp + 8) + byte] = (uint8_t)(w1 >> (8 * byte));
+                }
+            } else {
+                out[2 + lane] = (uint8_t)q0;
+                out[2 + 32 + lane] = (uint8_t)q1;
+            }
+        }
+        if (IS4 && hist) { atomicAdd(&s_hist[q0], 1u); atomicAdd(&s_hist[q1], 1u); }
+    }
+    if (IS4 && hist) {
+        __syncthreads();
+        if (threadIdx.x < 16 && s_hist[threadIdx.x]) atomicAdd(&hist[threadIdx.x], (unsigned long long)s_hist[threadIdx.x]);
+    }
+}
+
+int quantize_launch(const float* src, void* dst, int qt, size_t n, int k, int64_t* hist, bool scale_search,
+                    cudaStream_t st) {
+    qt = canon_qtype(qt);
+    if (!supported(qt) || k <= 0 || (k % QK) || (n % QK)) return LB_ERR_ARG;
+    const size_t nblk = n / QK;
+    if (nblk == 0) return 0;
+    if (hist) {
+        if (cudaMemsetAsync(hist, 0, 16 * sizeof(int64_t), st) != cudaSuccess) return check_launch();
+    }
+    size_t blocks = (nblk + QUANT_WARPS - 1) / QUANT_WARPS;
+    const size_t cap = (size_t)sm_count() * 8;
+    const int grid = (int)(blocks > cap ? cap : blocks);
+    unsigned long long* h = (unsigned long long*)hist;
+    uint8_t* o = (uint8_t*)dst;
+    const int ss = scale_search ? 1 : 0;
+    switch (qt) {
+        case QT_SYM_INT4:  quantize_kernel<QT_SYM_INT4><<<grid, QUANT_WARPS * 32, 0, st>>>(src, o, nblk, h, ss); break;
+        case QT_ASYM_INT4: quantize_kernel<QT_ASYM_INT4><<<grid, QUANT_WARPS * 32, 0, st>>>(src, o, nblk, h, ss); break;
+        case QT_NF4:       quantize_kernel<QT_NF4><<<grid, QUANT_WARPS * 32, 0, st>>>(src, o, nblk, h, ss); break;
+        case QT_FP8_E4M3:  quantize_kernel<QT_FP8_E4M3><<<grid, QUANT_WARPS * 32, 0, st>>>(src, o, nblk, h, ss); break;
+        case QT_FP8_E5M2:  quantize_kernel<QT_FP8_E5M2><<<grid, QUANT_WARPS * 32, 0, st>>>(src, o, nblk, h, ss); break;
+        case QT_FP6:       quantize_kernel<QT_FP6><<<grid, QUANT_WARPS * 32, 0, st>>>(src, o, nblk, h, ss); break;
+        default: return LB_ERR_ARG;
+    }
+    note_launch();
+    return check_launch();
+}
+
+}  // namespace lowbit

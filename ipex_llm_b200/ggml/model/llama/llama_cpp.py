@@ -1,0 +1,217 @@
+"""ctypes binding of libb200lowbit.so -- the B200 twin of the "GGML API" block of the
+reference's ipex_llm/ggml/model/llama/llama_cpp.py:945-1193 (same Python function names and
+argument order, so low_bit_linear.py reads like the reference's).
+
+Library discovery follows llama_cpp.py:71-109: ``<package>/libs/libb200lowbit.so`` unless the
+``LLAMA_CPP_LIB`` environment variable points elsewhere; a missing or unloadable library is a
+``RuntimeError`` at import (there is no Python or CPU fallback for the kernels).
+"""
+import ctypes
+import os
+import pathlib
+
+from ipex_llm_b200.utils.common import invalidInputError
+
+_PKG_ROOT = pathlib.Path(__file__).resolve().parents[3]
+
+
+def _load_shared_library():
+    lib_path = _PKG_ROOT / "libs" / "libb200lowbit.so"
+    if "LLAMA_CPP_LIB" in os.environ:
+        lib_path = pathlib.Path(os.environ["LLAMA_CPP_LIB"]).resolve()
+    if not lib_path.exists():
+        invalidInputError(False, f"Shared library '{lib_path}' not found.",
+                          "build it with `python -m ipex_llm_b200.build_native` "
+                          "(nvcc, sm_100a); there is no CPU fallback.")
+    try:
+        return ctypes.CDLL(str(lib_path))
+    except Exception as e:  # noqa: BLE001 - mirror llama_cpp.py:97-100
+        invalidInputError(False, f"Failed to load shared library '{lib_path}': {e}.")
+
+
+_lib = _load_shared_library()
+LIB_PATH = _lib._name
+
+
+class LowBitNativeError(RuntimeError):
+    pass
+
+
+def _check(rc=None, what=""):
+    """Raise if the native call reported an error (return code or the per-thread channel)."""
+    code = _lib.b200_lowbit_last_error() if rc is None else rc
+    if code:
+        msg = _lib.b200_lowbit_last_error_string().decode(errors="replace")
+        _lib.b200_lowbit_clear_error()
+        raise LowBitNativeError(f"{what}: native error {code}: {msg}")
+
+
+# ---------------------------------------------------------------- reference-shaped (host pointers)
+def ggml_quantize_tensor(src, dst, qtype, n, k, hist, scale_search):
+    _lib.b200_lowbit_clear_error()
+    r = _lib.ggml_quantize_tensor(src, dst, qtype, n, k, hist, scale_search)
+    _check(what="ggml_quantize_tensor")
+    return r
+
+
+_lib.ggml_quantize_tensor.argtypes = [ctypes.POINTER(ctypes.c_float), ctypes.c_void_p, ctypes.c_int,
+                                      ctypes.c_size_t, ctypes.c_int, ctypes.POINTER(ctypes.c_int64),
+                                      ctypes.c_bool]
+_lib.ggml_quantize_tensor.restype = ctypes.c_size_t
+
+
+def ggml_type_size(qtype):
+    return _lib.ggml_type_size(qtype)
+
+
+_lib.ggml_type_size.argtypes = [ctypes.c_int]
+_lib.ggml_type_size.restype = ctypes.c_size_t
+
+
+def ggml_qk_size(qtype):
+    return _lib.ggml_qk_size(qtype)
+
+
+_lib.ggml_qk_size.argtypes = [ctypes.c_int]
+_lib.ggml_qk_size.restype = ctypes.c_int
+
+
+def ggml_dequantize_q4_0(src, dst, k):
+    _lib.b200_lowbit_clear_error()
+    _lib.ggml_dequantize_q4_0(src, dst, k)
+    _check(what="ggml_dequantize_q4_0")
+
+
+_lib.ggml_dequantize_q4_0.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t]
+_lib.ggml_dequantize_q4_0.restype = None
+
+
+def ggml_dequantize(src, dst, k, qtype):
+    _lib.b200_lowbit_clear_error()
+    _lib.ggml_dequantize(src, dst, k, qtype)
+    _check(what="ggml_dequantize")
+
+
+_lib.ggml_dequantize.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_int]
+_lib.ggml_dequantize.restype = None
+
+
+def ggml_q_format_convet_cpu2xpu(src, dst, n, qtype, k=None):
+    """Reference signature plus the row length ``k`` the tiled B200 layout needs."""
+    _lib.b200_lowbit_clear_error()
+    if k is not None:
+        _lib.b200_lowbit_set_row_length(int(k))
+    _lib.ggml_q_format_convet_cpu2xpu(src, dst, n, qtype)
+    _check(what="ggml_q_format_convet_cpu2xpu")
+
+
+def ggml_q_format_convet_xpu2cpu(src, dst, n, qtype, k=None):
+    _lib.b200_lowbit_clear_error()
+    if k is not None:
+        _lib.b200_lowbit_set_row_length(int(k))
+    _lib.ggml_q_format_convet_xpu2cpu(src, dst, n, qtype)
+    _check(what="ggml_q_format_convet_xpu2cpu")
+
+
+for _n in ("ggml_q_format_convet_cpu2xpu", "ggml_q_format_convet_xpu2cpu"):
+    getattr(_lib, _n).argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_int]
+    getattr(_lib, _n).restype = None
+_lib.b200_lowbit_set_row_length.argtypes = [ctypes.c_int]
+_lib.b200_lowbit_set_row_length.restype = None
+for _n in ("ggml_q_format_convert_cpu2cuda_2d", "ggml_q_format_convert_cuda2cpu_2d"):
+    getattr(_lib, _n).argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_int64,
+                                  ctypes.c_int]
+    getattr(_lib, _n).restype = ctypes.c_int
+
+
+def ggml_compute_forward_mul_mat_q_fp32(src_0_ne, src_0_data, src_0_qtype, src_1_ne, src_1_data, result):
+    _lib.b200_lowbit_clear_error()
+    _lib.ggml_compute_forward_mul_mat_q_fp32(src_0_ne, src_0_data, src_0_qtype, src_1_ne, src_1_data,
+                                             result)
+    _check(what="ggml_compute_forward_mul_mat_q_fp32")
+
+
+_lib.ggml_compute_forward_mul_mat_q_fp32.argtypes = [ctypes.POINTER(ctypes.c_int64), ctypes.c_void_p,
+                                                     ctypes.c_int, ctypes.POINTER(ctypes.c_int64),
+                                                     ctypes.c_void_p, ctypes.c_void_p]
+_lib.ggml_compute_forward_mul_mat_q_fp32.restype = None
+
+_lib.b200_lowbit_last_error.restype = ctypes.c_int
+_lib.b200_lowbit_last_error_string.restype = ctypes.c_char_p
+_lib.b200_lowbit_clear_error.restype = None
+_lib.b200_lowbit_last_launch_count.restype = ctypes.c_int
+_lib.b200_lowbit_sm_count.restype = ctypes.c_int
+
+# ---------------------------------------------------------------- device-pointer entry points
+DT_F32, DT_F16, DT_BF16 = 0, 1, 2
+
+_lib.ggml_quantize_tensor_cuda.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_size_t,
+                                           ctypes.c_int, ctypes.c_void_p, ctypes.c_bool, ctypes.c_void_p]
+_lib.ggml_quantize_tensor_cuda.restype = ctypes.c_int
+_lib.ggml_dequantize_cuda.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_int,
+                                      ctypes.c_int, ctypes.c_void_p]
+_lib.ggml_dequantize_cuda.restype = ctypes.c_int
+_lib.lowbit_dequantize_device_layout_cuda.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64,
+                                                      ctypes.c_int64, ctypes.c_int, ctypes.c_int,
+                                                      ctypes.c_void_p]
+_lib.lowbit_dequantize_device_layout_cuda.restype = ctypes.c_int
+_lib.lowbit_relayout_cuda.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_int64,
+                                      ctypes.c_int, ctypes.c_int, ctypes.c_void_p]
+_lib.lowbit_relayout_cuda.restype = ctypes.c_int
+_lib.lowbit_matmul_workspace_size.argtypes = [ctypes.c_int64, ctypes.c_int64, ctypes.c_int64, ctypes.c_int]
+_lib.lowbit_matmul_workspace_size.restype = ctypes.c_size_t
+_lib.lowbit_matmul_cuda.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_int64,
+                                    ctypes.c_void_p, ctypes.c_int, ctypes.c_int64,
+                                    ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int,
+                                    ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p]
+_lib.lowbit_matmul_cuda.restype = ctypes.c_int
+
+
+def ggml_quantize_tensor_cuda(d_src, d_dst, qtype, n, k, d_hist, scale_search, stream):
+    _check(_lib.ggml_quantize_tensor_cuda(d_src, d_dst, qtype, n, k, d_hist, scale_search, stream),
+           "ggml_quantize_tensor_cuda")
+
+
+def ggml_dequantize_cuda(d_src, d_dst, k, qtype, out_dtype, stream):
+    _check(_lib.ggml_dequantize_cuda(d_src, d_dst, k, qtype, out_dtype, stream), "ggml_dequantize_cuda")
+
+
+def lowbit_dequantize_device_layout_cuda(d_src, d_dst, rows, k, qtype, out_dtype, stream):
+    _check(_lib.lowbit_dequantize_device_layout_cuda(d_src, d_dst, rows, k, qtype, out_dtype, stream),
+           "lowbit_dequantize_device_layout_cuda")
+
+
+def lowbit_relayout_cuda(d_src, d_dst, rows, k, qtype, to_device, stream):
+    _check(_lib.lowbit_relayout_cuda(d_src, d_dst, rows, k, qtype, int(to_device), stream),
+           "lowbit_relayout_cuda")
+
+
+def lowbit_matmul_workspace_size(n_rows, k, m, x_dtype):
+    return _lib.lowbit_matmul_workspace_size(n_rows, k, m, x_dtype)
+
+
+def lowbit_matmul_cuda(d_w, qtype, n_rows, k, d_x, x_dtype, m, d_y, y_dtype, d_bias, accumulate,
+                       workspace, workspace_bytes, stream):
+    _check(_lib.lowbit_matmul_cuda(d_w, qtype, n_rows, k, d_x, x_dtype, m, d_y, y_dtype, d_bias,
+                                   int(accumulate), workspace, workspace_bytes, stream),
+           "lowbit_matmul_cuda")
+
+
+def last_launch_count():
+    return _lib.b200_lowbit_last_launch_count()
+
+
+def sm_count():
+    return _lib.b200_lowbit_sm_count()
+
+
+def llama_init_backend():
+    _lib.llama_init_backend()
+
+
+_lib.llama_init_backend.restype = None
+
+_llama_initialized = False
+if not _llama_initialized:
+    llama_init_backend()
+    _llama_initialized = True

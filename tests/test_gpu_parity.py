@@ -1,0 +1,283 @@
+"""GPU parity tests: the sm_100a kernels behind the C ABI against the CPU oracle.
+
+Bars:
+  * packed bytes (quantise, relayout round trip): bit-exact;
+  * dequantise: bit-exact (same fp32 formula, no contraction);
+  * matmul vs mode-B oracle: |diff| <= 2e-6 * sum_k |x_k w_k| + 1e-30 for every element when the
+    activations are exactly representable (the only difference is fp32 summation order), checked
+    against the float64 oracle with the same bound for the oracle's own serial fp32 sum.
+"""
+import ctypes
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import oracle
+
+pytestmark = pytest.mark.gpu
+
+QTYPES = ["sym_int4", "asym_int4", "nf4", "fp8_e4m3", "fp8_e5m2", "fp6"]
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+
+
+@pytest.fixture(scope="module")
+def lbl(native_lib, cuda_device):
+    from ipex_llm_b200.transformers import low_bit_linear
+    return low_bit_linear
+
+
+def qid(name):
+    from ipex_llm_b200.ggml.quantize import ggml_tensor_qtype
+    return ggml_tensor_qtype[name]
+
+
+def rand_w(rng, rows, k, kind="normal"):
+    if kind == "normal":
+        return (rng.standard_normal((rows, k)) * 0.02).astype(np.float32)
+    if kind == "wide":          # wide dynamic range across blocks, outliers inside blocks
+        w = rng.standard_normal((rows, k)) * np.exp(rng.standard_normal((rows, k // 64, 1)).repeat(64, 2).reshape(rows, k) * 2)
+        w[rng.random((rows, k)) < 0.01] *= 20
+        return w.astype(np.float32)
+    raise ValueError(kind)
+
+
+def as_np_u8(t):
+    return (t.view(torch.uint8) if t.dtype != torch.uint8 else t).cpu().numpy()
+
+
+# ---------------------------------------------------------------- (a) quantise / pack
+@pytest.mark.parametrize("qtype", QTYPES)
+@pytest.mark.parametrize("kind", ["normal", "wide"])
+def test_quantize_bit_exact_host_abi(lbl, qtype, kind):
+    rng = np.random.default_rng(100 + len(qtype))
+    w = rand_w(rng, 96, 512, kind)
+    w[0, :64] = 0.0
+    w[1, 64:128] = -0.0
+    w[2, :64] = 0.017
+    w[3, 5] = 3.0
+    w[4, 70] = -3.0
+    w[5, :64] = np.linspace(-1, 1, 64)          # exact ties at .5 steps for some formats
+    got = as_np_u8(lbl.ggml_convert_qtype(torch.from_numpy(w), qid(qtype), device="cpu"))
+    want = oracle.quantize(w, qtype)
+    np.testing.assert_array_equal(got, want)
+
+
+@pytest.mark.parametrize("qtype", QTYPES)
+def test_quantize_bit_exact_device_abi(lbl, cuda_device, qtype):
+    rng = np.random.default_rng(200 + len(qtype))
+    w = rand_w(rng, 257, 1024, "wide")           # ragged row count
+    got = as_np_u8(lbl.ggml_convert_qtype(torch.from_numpy(w).to(cuda_device), qid(qtype)))
+    np.testing.assert_array_equal(got, oracle.quantize(w, qtype))
+
+
+@pytest.mark.parametrize("qtype", ["fp8_e4m3", "fp8_e5m2", "fp6"])
+def test_quantize_scale_search_bit_exact(lbl, cuda_device, qtype):
+    rng = np.random.default_rng(300)
+    w = rand_w(rng, 64, 512, "wide")
+    got = as_np_u8(lbl.ggml_convert_qtype(torch.from_numpy(w).to(cuda_device), qid(qtype), enable_scale_search=True))
+    np.testing.assert_array_equal(got, oracle.quantize(w, qtype, scale_search=True))
+
+
+def test_quantize_reference_golden_vectors(lbl):
+    """the committed vectors made by running the reference's own Python quantisers"""
+    g = np.load(os.path.join(GOLD, "ref_python_q4.npz"))
+    w = g["w"]
+    got0 = as_np_u8(lbl.ggml_convert_qtype(torch.from_numpy(w), qid("sym_int4"), device="cpu")).reshape(-1, 34)
+    want0 = g["q4_0_bytes"].reshape(-1, 34)
+    nz = w.reshape(-1, 64).any(axis=1)
+    np.testing.assert_array_equal(got0[nz], want0[nz])       # all-zero block: see test_oracle_golden
+    got1 = as_np_u8(lbl.ggml_convert_qtype(torch.from_numpy(w), qid("asym_int4"), device="cpu"))
+    np.testing.assert_array_equal(got1, g["q4_1_bytes"])
+
+
+def test_quantize_histogram(native_lib, cuda_device):
+    rng = np.random.default_rng(5)
+    w = rng.standard_normal((32, 256)).astype(np.float32)
+    dst = np.empty(w.size // 64 * 34, np.uint8)
+    hist = (ctypes.c_int64 * 16)()
+    n = native_lib.ggml_quantize_tensor(ctypes.cast(w.ctypes.data, ctypes.POINTER(ctypes.c_float)),
+                                        ctypes.c_void_p(dst.ctypes.data), 2, w.size, 256, hist, False)
+    assert n == dst.size
+    _, want = oracle.quantize(w, "sym_int4", return_hist=True)
+    np.testing.assert_array_equal(np.array(list(hist)), want)
+
+
+def test_quantize_rejects_bad_shapes(lbl):
+    with pytest.raises(RuntimeError):
+        lbl.ggml_convert_qtype(torch.zeros(4, 96), qid("sym_int4"), device="cpu")
+    with pytest.raises(RuntimeError):
+        lbl.ggml_convert_qtype(torch.zeros(4, 128, dtype=torch.float16), qid("sym_int4"), device="cpu")
+    assert lbl.ggml_convert_qtype(torch.zeros(0, 128), qid("sym_int4"), device="cpu").numel() == 0
+
+
+# ---------------------------------------------------------------- dequantise + relayout
+@pytest.mark.parametrize("qtype", QTYPES)
+def test_dequantize_bit_exact(lbl, cuda_device, qtype):
+    rng = np.random.default_rng(400)
+    w = rand_w(rng, 40, 320, "wide")
+    packed = oracle.quantize(w, qtype)
+    want = oracle.dequantize(packed, w.shape, qtype)
+    got_host = lbl.ggml_convert_fp32(torch.from_numpy(packed), w.shape, w.size, qid(qtype)).numpy()
+    np.testing.assert_array_equal(got_host, want)
+    got_dev = lbl.ggml_convert_fp32(torch.from_numpy(packed).to(cuda_device), w.shape, w.size, qid(qtype)).cpu().numpy()
+    np.testing.assert_array_equal(got_dev, want)
+    if qtype == "sym_int4":
+        np.testing.assert_array_equal(lbl.ggml_int4_convert_fp32(torch.from_numpy(packed), w.shape, w.size).numpy(), want)
+
+
+@pytest.mark.parametrize("qtype", QTYPES)
+@pytest.mark.parametrize("rows", [16, 40, 7, 256])
+def test_relayout_roundtrip_and_device_dequant(lbl, cuda_device, qtype, rows):
+    rng = np.random.default_rng(500 + rows)
+    k = 384
+    w = rand_w(rng, rows, k, "wide")
+    packed = torch.from_numpy(oracle.quantize(w, qtype))
+    if qtype == "nf4":
+        packed = packed.view(torch.bfloat16)
+    n = rows * k
+    # host ABI (reference-shaped symbols) and device ABI give the same tiled bytes
+    tiled_h = lbl.ggml_q_format_convet_cpu2xpu(packed, n, qid(qtype), shape=(rows, k))
+    tiled_d = lbl.ggml_q_format_convet_cpu2xpu(packed.to(cuda_device), n, qid(qtype), shape=(rows, k))
+    assert tiled_h.shape == packed.shape and tiled_h.dtype == packed.dtype
+    np.testing.assert_array_equal(as_np_u8(tiled_h), as_np_u8(tiled_d))
+    back = lbl.ggml_q_format_convet_xpu2cpu(tiled_d, n, qid(qtype), shape=(rows, k))
+    np.testing.assert_array_equal(as_np_u8(back), as_np_u8(packed))
+    back_h = lbl.ggml_q_format_convet_xpu2cpu(tiled_h, n, qid(qtype), shape=(rows, k))
+    np.testing.assert_array_equal(as_np_u8(back_h), as_np_u8(packed))
+    # dequantising the tiled layout gives the oracle's values bit for bit
+    deq = lbl.dequantize_device_layout(tiled_d, (rows, k), qid(qtype)).cpu().numpy()
+    np.testing.assert_array_equal(deq, oracle.dequantize(as_np_u8(packed), (rows, k), qtype))
+
+
+def test_relayout_needs_row_length(native_lib):
+    src = np.zeros(34 * 16, np.uint8); dst = np.zeros_like(src)
+    native_lib._lib.b200_lowbit_set_row_length(0)
+    with pytest.raises(RuntimeError, match="row"):
+        native_lib.ggml_q_format_convet_cpu2xpu(ctypes.c_void_p(src.ctypes.data), ctypes.c_void_p(dst.ctypes.data), 16 * 64, 2)
+
+
+# ---------------------------------------------------------------- (b) matmul
+def matmul_bound(packed, shape, qtype, x):
+    """per-element bound for fp32 summation-order differences: 2e-6 * sum |x w| (+ tiny)"""
+    wd = np.abs(oracle.dequantize(packed, shape, qtype)).astype(np.float64)
+    return 2e-6 * (np.abs(x).astype(np.float64) @ wd.T) + 1e-30
+
+
+def run_matmul(lbl, dev, packed, shape, qtype, x_t, **kw):
+    p = torch.from_numpy(packed)
+    if qtype == "nf4":
+        p = p.view(torch.bfloat16)
+    tiled = lbl.ggml_q_format_convet_cpu2xpu(p.to(dev), shape[0] * shape[1], qid(qtype), shape=shape)
+    return lbl.lowbit_matmul(x_t.to(dev), tiled, shape, qid(qtype), **kw)
+
+
+@pytest.mark.parametrize("qtype", QTYPES)
+@pytest.mark.parametrize("xdt", [torch.float16, torch.bfloat16, torch.float32])
+@pytest.mark.parametrize("M", [1, 3, 8])
+def test_gemv_matches_oracle(lbl, cuda_device, qtype, xdt, M):
+    rng = np.random.default_rng(600 + M)
+    N, K = 208, 1024
+    w = rand_w(rng, N, K)
+    packed = oracle.quantize(w, qtype)
+    x_t = torch.from_numpy(rng.standard_normal((M, K)).astype(np.float32)).to(xdt)
+    x = x_t.float().numpy()                                        # the values the kernel sees
+    y = run_matmul(lbl, cuda_device, packed, (N, K), qtype, x_t, out_dtype=torch.float32).cpu().numpy()
+    y64 = oracle.matmul_f64(packed, (N, K), qtype, x)
+    bound = matmul_bound(packed, (N, K), qtype, x)
+    if qtype == "nf4" and xdt != torch.float32:
+        pass
+    assert (np.abs(y - y64) <= bound).all(), float((np.abs(y - y64) / bound).max())
+    # the oracle's own serial fp32 sum sits inside the same bound
+    assert (np.abs(oracle.matmul(packed, (N, K), qtype, x) - y64) <= bound).all()
+
+
+@pytest.mark.parametrize("qtype", ["sym_int4", "asym_int4", "fp8_e4m3"])
+@pytest.mark.parametrize("shape,M", [((16, 64), 1), ((4096, 4096), 1), ((11008, 4096), 2), ((4096, 11008), 1),
+                                      ((1000, 704), 5), ((8, 4096), 1), ((250, 128), 12), ((512, 2048), 32),
+                                      ((512, 2048), 40)])
+def test_gemv_shapes(lbl, cuda_device, qtype, shape, M):
+    rng = np.random.default_rng(700)
+    N, K = shape
+    w = rand_w(rng, N, K)
+    packed = oracle.quantize(w, qtype)
+    x_t = torch.from_numpy(rng.standard_normal((M, K)).astype(np.float32)).half()
+    x = x_t.float().numpy()
+    y = run_matmul(lbl, cuda_device, packed, shape, qtype, x_t, out_dtype=torch.float32).cpu().numpy()
+    y64 = oracle.matmul_f64(packed, shape, qtype, x)
+    bound = matmul_bound(packed, shape, qtype, x)
+    assert (np.abs(y - y64) <= bound).all(), float((np.abs(y - y64) / bound).max())
+
+
+def test_gemv_deterministic_and_counters_reset(lbl, cuda_device):
+    rng = np.random.default_rng(800)
+    N, K = 4096, 4096
+    packed = oracle.quantize(rand_w(rng, N, K), "sym_int4")
+    x_t = torch.from_numpy(rng.standard_normal((1, K)).astype(np.float32)).half()
+    ys = [run_matmul(lbl, cuda_device, packed, (N, K), "sym_int4", x_t, out_dtype=torch.float32) for _ in range(5)]
+    for y in ys[1:]:
+        assert torch.equal(y, ys[0])
+
+
+def test_gemv_epilogue_bias_accumulate_dtypes(lbl, cuda_device):
+    rng = np.random.default_rng(900)
+    N, K, M = 320, 512, 4
+    packed = oracle.quantize(rand_w(rng, N, K), "sym_int4")
+    x_t = torch.from_numpy(rng.standard_normal((M, K)).astype(np.float32)).half()
+    base = run_matmul(lbl, cuda_device, packed, (N, K), "sym_int4", x_t, out_dtype=torch.float32)
+    bias = torch.from_numpy(rng.standard_normal(N).astype(np.float32)).to(cuda_device)
+    yb = run_matmul(lbl, cuda_device, packed, (N, K), "sym_int4", x_t, out_dtype=torch.float32, bias=bias)
+    torch.testing.assert_close(yb, base + bias, rtol=0, atol=1e-6)
+    res = torch.from_numpy(rng.standard_normal((M, N)).astype(np.float32)).to(cuda_device)
+    out = res.clone()
+    run_matmul(lbl, cuda_device, packed, (N, K), "sym_int4", x_t, out=out, accumulate=True)
+    torch.testing.assert_close(out, res + base, rtol=0, atol=1e-6)
+    for dt in (torch.float16, torch.bfloat16):
+        y = run_matmul(lbl, cuda_device, packed, (N, K), "sym_int4", x_t, out_dtype=dt)
+        assert y.dtype == dt
+        torch.testing.assert_close(y.float(), base.to(dt).float(), rtol=0, atol=0)
+
+
+@pytest.mark.parametrize("qtype", QTYPES)
+def test_reference_host_abi_matmul(lbl, qtype):
+    """ggml_compute_forward_mul_mat_q_fp32 with host pointers, as LowBitLinear's CPU branch calls it"""
+    rng = np.random.default_rng(1000)
+    N, K, M = 96, 256, 3
+    packed = oracle.quantize(rand_w(rng, N, K), qtype)
+    x = rng.standard_normal((M, K)).astype(np.float32)
+    p = torch.from_numpy(packed)
+    y = lbl.ggml_matmul_src1_x_src0_t(p.view(torch.bfloat16) if qtype == "nf4" else p, torch.from_numpy(x), (N, K), qid(qtype)).numpy()
+    y64 = oracle.matmul_f64(packed, (N, K), qtype, x)
+    # fp32 activations go through the 3-way bf16 split: exact to ~2^-24 relative per term
+    bound = matmul_bound(packed, (N, K), qtype, x)
+    assert (np.abs(y - y64) <= bound).all(), float((np.abs(y - y64) / bound).max())
+
+
+# ---------------------------------------------------------------- module level
+@pytest.mark.parametrize("qtype", ["sym_int4", "asym_int4", "nf4", "fp8_e5m2", "fp6"])
+def test_lowbit_linear_module(lbl, cuda_device, qtype):
+    torch.manual_seed(0)
+    lin = torch.nn.Linear(512, 272, bias=True)
+    q = lbl.LowBitLinear(512, 272, qid(qtype), bias=True)
+    q.weight = lbl.FP4Params(lin.weight.data.clone(), qtype=qid(qtype))
+    q.bias = torch.nn.Parameter(lin.bias.data.clone())
+    q = q.to(cuda_device)
+    assert q.weight.quantized and q.weight.data.device.type == "cuda" and tuple(q.weight._shape) == (272, 512)
+    assert q.weight.data.dtype == (torch.bfloat16 if qtype == "nf4" else torch.uint8)
+    packed = oracle.quantize(lin.weight.data.numpy(), qtype)
+    x = torch.randn(2, 3, 512)
+    want = torch.from_numpy(oracle.matmul(packed, (272, 512), qtype, x.half().float().view(-1, 512).numpy())).view(2, 3, 272) + lin.bias.data
+    y = q(x.half().to(cuda_device))
+    assert y.dtype == torch.float16 and y.shape == (2, 3, 272)
+    torch.testing.assert_close(y.float().cpu(), want, rtol=2e-3, atol=2e-3)
+    # dtype casts leave the packed weight alone; .to('cpu') restores the canonical bytes
+    before = q.weight.data.clone()
+    q = q.to(torch.float16)
+    assert torch.equal(q.weight.data.view(torch.uint8), before.view(torch.uint8))
+    qc = q.to("cpu")
+    np.testing.assert_array_equal(as_np_u8(qc.weight.data), packed)
+    # CPU-resident weight: the reference's CPU call path still computes (on the GPU, via the host ABI)
+    if qtype in ("sym_int4", "asym_int4", "fp6"):
+        yc = qc(x)
+        torch.testing.assert_close(yc, torch.from_numpy(oracle.matmul(packed, (272, 512), qtype, x.view(-1, 512).numpy())).view(2, 3, 272) + lin.bias.data.float(), rtol=1e-4, atol=1e-4)
