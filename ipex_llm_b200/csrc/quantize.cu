@@ -19,6 +19,16 @@
 
 namespace lowbit {
 
+// fp32 -> fp16 (RNE) bit pattern, little-endian bytes (records are only byte-aligned)
+__device__ __forceinline__ void store_half_bits(uint8_t* p, float v) {
+    // via a packed half2 in a 32-bit register: ptxas 12.9 mis-fuses cvt.rn.f16.f32 + st.u8 of the
+    // 16-bit result into F2I.U8.F16 (a numeric half->u8 conversion), which zeroes the low byte
+    const __half2 h2 = __floats2half2_rn(v, 0.0f);
+    const unsigned int bits = *reinterpret_cast<const unsigned int*>(&h2);
+    p[0] = (uint8_t)(bits & 0xffu);
+    p[1] = (uint8_t)(bits >> 8);
+}
+
 __device__ __forceinline__ float warp_max(float v) {
 #pragma unroll
     for (int o = 16; o; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
@@ -93,7 +103,7 @@ quantize_kernel(const float* __restrict__ src, uint8_t* __restrict__ dst, size_t
             int i0 = (int)(signed char)(int)__fadd_rn(__fmul_rn(x0, id), 8.5f);
             int i1 = (int)(signed char)(int)__fadd_rn(__fmul_rn(x1, id), 8.5f);
             q0 = min(15, i0); q1 = min(15, i1);
-            if (lane == 0) { const __half_raw h = __float2half_rn(d); out[0] = h.x & 0xff; out[1] = h.x >> 8; }
+            if (lane == 0) store_half_bits(out, d);
             out[2 + lane] = (uint8_t)(q0 | (q1 << 4));
         } else if (QT == QT_ASYM_INT4) {
             float kmin = x0, vmin = x0; int imin = lane;
@@ -109,15 +119,14 @@ quantize_kernel(const float* __restrict__ src, uint8_t* __restrict__ dst, size_t
             int i1 = (int)(signed char)(int)__fadd_rn(__fmul_rn(__fsub_rn(x1, mn), id), 0.5f);
             q0 = min(15, i0); q1 = min(15, i1);
             if (lane == 0) {
-                const __half_raw h = __float2half_rn(d), m = __float2half_rn(mn);
-                out[0] = h.x & 0xff; out[1] = h.x >> 8; out[2] = m.x & 0xff; out[3] = m.x >> 8;
+                store_half_bits(out, d); store_half_bits(out + 2, mn);
             }
             out[4 + lane] = (uint8_t)(q0 | (q1 << 4));
         } else if (QT == QT_NF4) {
             const float d = warp_max(fmaxf(fabsf(x0), fabsf(x1)));
             const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
             q0 = nf4_encode(__fmul_rn(x0, id)); q1 = nf4_encode(__fmul_rn(x1, id));
-            if (lane == 0) { const __half_raw h = __float2half_rn(d); out[0] = h.x & 0xff; out[1] = h.x >> 8; }
+            if (lane == 0) store_half_bits(out, d);
             out[2 + lane] = (uint8_t)(q0 | (q1 << 4));
         } else {
             const float amax = warp_max(fmaxf(fabsf(x0), fabsf(x1)));
@@ -150,7 +159,7 @@ quantize_kernel(const float* __restrict__ src, uint8_t* __restrict__ dst, size_t
             }
             const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
             q0 = mini_encode<QT>(__fmul_rn(x0, id)); q1 = mini_encode<QT>(__fmul_rn(x1, id));
-            if (lane == 0) { const __half_raw h = __float2half_rn(d); out[0] = h.x & 0xff; out[1] = h.x >> 8; }
+            if (lane == 0) store_half_bits(out, d);
             if (QT == QT_FP6) {
                 // 4 consecutive 6-bit codes -> 3 bytes, little-endian (c0 | c1<<6 | c2<<12 | c3<<18)
                 const int base = lane & ~3;
