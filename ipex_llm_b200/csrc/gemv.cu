@@ -1,6 +1,7 @@
 // gemv.cu -- host side of kernel (b): workspace layout, grid sizing, qtype dispatch, plus the
 // scalar generic kernel (nf4 until its mma codec lands; rows beyond the last 16-row tile) and
 // the fp32 -> 3 x bf16 activation split.  The mma kernel itself is in gemv_kernel.cuh.
+#include <cstdlib>
 #include "lowbit_common.cuh"
 #include "lowbit_internal.h"
 #include "gemv_args.h"
@@ -12,6 +13,11 @@ void gemv_launch_asym_int4(int x_dtype, int nt, int grid, const GemvArgs& A, cud
 void gemv_launch_fp8_e4m3(int x_dtype, int nt, int grid, const GemvArgs& A, cudaStream_t st);
 void gemv_launch_fp8_e5m2(int x_dtype, int nt, int grid, const GemvArgs& A, cudaStream_t st);
 void gemv_launch_fp6(int x_dtype, int nt, int grid, const GemvArgs& A, cudaStream_t st);
+int gemv_warps_per_sm_sym_int4();
+int gemv_warps_per_sm_asym_int4();
+int gemv_warps_per_sm_fp8_e4m3();
+int gemv_warps_per_sm_fp8_e5m2();
+int gemv_warps_per_sm_fp6();
 
 // ------------------------------------------------------------------ generic (any qtype, tail rows)
 // one warp per output row, scalar decode; used for nf4 until its mma codec lands, and for the
@@ -79,7 +85,17 @@ __global__ void split_f32_kernel(const float* __restrict__ x, __nv_bfloat16* __r
 // ------------------------------------------------------------------ host side
 static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
-static int max_total_warps() { return sm_count() * GEMV_CTAS_PER_SM * GEMV_WARPS; }
+static int max_total_warps() { return sm_count() * GEMV_MAX_WARPS_PER_SM; }
+static int warps_per_sm(int qt) {
+    switch (qt) {
+        case QT_SYM_INT4: return gemv_warps_per_sm_sym_int4();
+        case QT_ASYM_INT4: return gemv_warps_per_sm_asym_int4();
+        case QT_FP8_E4M3: return gemv_warps_per_sm_fp8_e4m3();
+        case QT_FP8_E5M2: return gemv_warps_per_sm_fp8_e5m2();
+        case QT_FP6: return gemv_warps_per_sm_fp6();
+        default: return GEMV_WARPS;
+    }
+}
 
 constexpr size_t kCounterBytes = 256 * 1024;                 // 65536 row tiles = 1M rows
 struct WsLayout { size_t counters, partials, xsplit, total; };
@@ -148,12 +164,13 @@ int gemv_launch(const void* w, int qt, int64_t n_rows, int64_t k, const void* x,
                 A.x = (const uint16_t*)planes;
             } else A.x = (const uint16_t*)xc;
             const int nt = mc <= 8 ? 1 : mc <= 16 ? 2 : 4;
-            int64_t tw = max_total_warps();
+            int64_t tw = (int64_t)sm_count() * warps_per_sm(qt);
             const int64_t want = (G.ntiles + 1) / 2;          // at least ~2 tiles per warp
             if (tw > want) tw = want;
             if (tw < 1) tw = 1;
             const int grid = (int)((tw + GEMV_WARPS - 1) / GEMV_WARPS);
             A.total_warps = grid * GEMV_WARPS;
+            { const char* e = getenv("LOWBIT_GEMV_DBG"); A.dbg = e ? atoi(e) : 0; }
             switch (qt) {
                 case QT_SYM_INT4:  gemv_launch_sym_int4(x_dtype, nt, grid, A, st); break;
                 case QT_ASYM_INT4: gemv_launch_asym_int4(x_dtype, nt, grid, A, st); break;

@@ -5,9 +5,11 @@
 
 namespace lowbit {
 
-constexpr int GEMV_WARPS = 4;          // warps per CTA
-constexpr int GEMV_CTAS_PER_SM = 4;    // resident CTAs per SM we size the grid for
-constexpr int GEMV_MAX_NT = 4;         // n-tiles of 8 activation rows -> M <= 32 per pass
+constexpr int GEMV_WARPS = 4;              // warps per CTA (each warp is an independent pipeline)
+constexpr int GEMV_TPC = 4;                // tiles per staged chunk (one TMA bulk copy of 2-4 KB)
+constexpr int GEMV_STAGES = 4;             // chunks in flight per warp
+constexpr int GEMV_MAX_WARPS_PER_SM = 32;  // bound used to size the split-K partial buffer
+constexpr int GEMV_MAX_NT = 4;             // n-tiles of 8 activation rows -> M <= 32 per pass
 
 struct GemvArgs {
     const uint8_t* w;
@@ -21,6 +23,7 @@ struct GemvArgs {
     float* partials;          // [total_warps][2][NT][4][32]
     unsigned* counters;       // [rows/16], zero between calls
     int total_warps;
+    int dbg;                  // development switches (LOWBIT_GEMV_DBG): 1 skip flush, 2 skip x loads, 4 skip mma
 };
 
 __device__ __forceinline__ void store_out(void* y, int dt, int64_t idx, float v, const void* bias, int64_t row, int acc) {
