@@ -123,6 +123,11 @@ int lowbit_matmul_cuda(const void* d_w, int qtype, int64_t n_rows, int64_t k,
                        void* d_y, int y_dtype, const void* d_bias, int accumulate,
                        void* workspace, size_t workspace_bytes, void* stream);
 
+/* on != 0: the matmul kernels are launched with programmatic stream serialization (PDL): a
+ * kernel may start streaming its weights while the previous kernel on the stream drains; it
+ * reads activations only after griddepcontrol.wait.  Process-wide switch, default off. */
+void lowbit_set_programmatic_dependent_launch(int on);
+
 /* number of kernels the last lowbit_* / ggml_*_cuda call on this thread launched */
 int b200_lowbit_last_launch_count(void);
 /* SM count of the current device (0 if no device) */

@@ -108,6 +108,7 @@ void b200_lowbit_clear_error(void) { t_err = 0; t_msg[0] = 0; }
 int b200_lowbit_last_launch_count(void) { return t_launches; }
 int b200_lowbit_sm_count(void) { return have_device() ? sm_count() : 0; }
 void b200_lowbit_set_row_length(int k) { t_row_len = k; }
+void lowbit_set_programmatic_dependent_launch(int on) { gemv_set_pdl(on); }
 
 // ------------------------------------------------------------------ family (2)
 int ggml_quantize_tensor_cuda(const float* d_src, void* d_dst, int qtype, size_t n, int k, int64_t* d_hist,

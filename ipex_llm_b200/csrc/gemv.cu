@@ -8,11 +8,11 @@
 
 namespace lowbit {
 
-void gemv_launch_sym_int4(int x_dtype, int nt, int grid, const GemvArgs& A, cudaStream_t st);
-void gemv_launch_asym_int4(int x_dtype, int nt, int grid, const GemvArgs& A, cudaStream_t st);
-void gemv_launch_fp8_e4m3(int x_dtype, int nt, int grid, const GemvArgs& A, cudaStream_t st);
-void gemv_launch_fp8_e5m2(int x_dtype, int nt, int grid, const GemvArgs& A, cudaStream_t st);
-void gemv_launch_fp6(int x_dtype, int nt, int grid, const GemvArgs& A, cudaStream_t st);
+void gemv_launch_sym_int4(int x_dtype, int m, int grid, const GemvArgs& A, cudaStream_t st);
+void gemv_launch_asym_int4(int x_dtype, int m, int grid, const GemvArgs& A, cudaStream_t st);
+void gemv_launch_fp8_e4m3(int x_dtype, int m, int grid, const GemvArgs& A, cudaStream_t st);
+void gemv_launch_fp8_e5m2(int x_dtype, int m, int grid, const GemvArgs& A, cudaStream_t st);
+void gemv_launch_fp6(int x_dtype, int m, int grid, const GemvArgs& A, cudaStream_t st);
 int gemv_warps_per_sm_sym_int4();
 int gemv_warps_per_sm_asym_int4();
 int gemv_warps_per_sm_fp8_e4m3();
@@ -36,15 +36,14 @@ __global__ void gemv_generic_kernel(const uint8_t* __restrict__ w, TiledGeom G, 
         for (int i = 0; i < 8; i++) acc[i] = 0.0f;
         for (int64_t kb = 0; kb < G.nb; kb++) {
             float d, mn = 0.0f; uint32_t c0, c1;
-            if (row < G.r16) {
-                const int64_t f = (row / 16) * G.nb + kb;
+            if (row < G.r64) {
                 const int r = (int)(row % 16);
-                const uint8_t* tile = w + f * G.tile_code_bytes;
+                const uint8_t* tile = w + tile_code_offset(G, row, kb);
                 c0 = tiled_code(qt, tile, r, lane); c1 = tiled_code(qt, tile, r, lane + 32);
-                d = half_bits_to_float(((const uint16_t*)(w + G.off_s + f * 32))[(r & 7) * 2 + (r >> 3)]);
-                if (G.has_m) mn = half_bits_to_float(((const uint16_t*)(w + G.off_m + f * 32))[(r & 7) * 2 + (r >> 3)]);
+                d = half_bits_to_float(*(const uint16_t*)(w + G.off_s + scale_offset(G, row, kb)));
+                if (G.has_m) mn = half_bits_to_float(*(const uint16_t*)(w + G.off_m + scale_offset(G, row, kb)));
             } else {
-                const uint8_t* rec = w + G.off_tail + ((row - G.r16) * G.nb + kb) * G.blk_bytes;
+                const uint8_t* rec = w + G.off_tail + ((row - G.r64) * G.nb + kb) * G.blk_bytes;
                 d = half_bits_to_float((uint16_t)rec[0] | ((uint16_t)rec[1] << 8));
                 if (G.has_m) mn = half_bits_to_float((uint16_t)rec[2] | ((uint16_t)rec[3] << 8));
                 c0 = canonical_code(qt, rec + hdr, lane); c1 = canonical_code(qt, rec + hdr, lane + 32);
@@ -85,6 +84,9 @@ __global__ void split_f32_kernel(const float* __restrict__ x, __nv_bfloat16* __r
 // ------------------------------------------------------------------ host side
 static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
+static int g_pdl = 0;     // programmatic dependent launch for the GEMV kernels (set by the host engine)
+void gemv_set_pdl(int on) { g_pdl = on ? 1 : 0; }
+
 static int max_total_warps() { return sm_count() * GEMV_MAX_WARPS_PER_SM; }
 static int warps_per_sm(int qt) {
     switch (qt) {
@@ -108,7 +110,7 @@ static WsLayout ws_layout(int64_t n_rows, int64_t k, int64_t m, int x_dtype) {
     (void)n_rows;
     L.counters = 0;
     L.partials = kCounterBytes;
-    L.xsplit = L.partials + align_up((size_t)max_total_warps() * 2 * nt * 128 * sizeof(float), 256);
+    L.xsplit = L.partials + align_up((size_t)max_total_warps() * 2 * RG_TILES * nt * 128 * sizeof(float), 256);
     L.total = L.xsplit + (x_dtype == DT_F32 ? align_up((size_t)3 * mm * k * 2, 256) : 0);
     return L;
 }
@@ -136,7 +138,7 @@ int gemv_launch(const void* w, int qt, int64_t n_rows, int64_t k, const void* x,
     qt = canon_qtype(qt);
     if (!supported(qt) || k <= 0 || k % QK || n_rows <= 0 || m <= 0) return LB_ERR_ARG;
     if (x_dtype < 0 || x_dtype > 2 || y_dtype < 0 || y_dtype > 2) return LB_ERR_ARG;
-    if ((size_t)((n_rows + 15) / 16) * sizeof(unsigned) > kCounterBytes) return LB_ERR_ARG;
+    if ((size_t)((n_rows + 63) / 64) * sizeof(unsigned) > kCounterBytes) return LB_ERR_ARG;
     const TiledGeom G = make_geom(n_rows, k, qt);
     const int esz_x = x_dtype == DT_F32 ? 4 : 2, esz_y = y_dtype == DT_F32 ? 4 : 2;
 
@@ -145,7 +147,7 @@ int gemv_launch(const void* w, int qt, int64_t n_rows, int64_t k, const void* x,
         const int64_t mc = (m - mb) < 8 * GEMV_MAX_NT ? (m - mb) : 8 * GEMV_MAX_NT;
         const char* xc = (const char*)x + (size_t)mb * k * esz_x;
         char* yc = (char*)y + (size_t)mb * n_rows * esz_y;
-        int64_t mma_rows = has_mma_codec(qt) ? G.r16 : 0;
+        int64_t mma_rows = has_mma_codec(qt) ? G.r64 : 0;
         if (mma_rows > 0) {
             const WsLayout L = ws_layout(n_rows, k, mc, x_dtype);
             if (!workspace || workspace_bytes < L.total) return LB_ERR_WORKSPACE;
@@ -163,20 +165,19 @@ int gemv_launch(const void* w, int qt, int64_t n_rows, int64_t k, const void* x,
                 note_launch();
                 A.x = (const uint16_t*)planes;
             } else A.x = (const uint16_t*)xc;
-            const int nt = mc <= 8 ? 1 : mc <= 16 ? 2 : 4;
             int64_t tw = (int64_t)sm_count() * warps_per_sm(qt);
-            const int64_t want = (G.ntiles + 1) / 2;          // at least ~2 tiles per warp
+            const int64_t want = G.nsuper;                    // at least one super-tile per warp
             if (tw > want) tw = want;
             if (tw < 1) tw = 1;
             const int grid = (int)((tw + GEMV_WARPS - 1) / GEMV_WARPS);
-            A.total_warps = grid * GEMV_WARPS;
-            { const char* e = getenv("LOWBIT_GEMV_DBG"); A.dbg = e ? atoi(e) : 0; }
+            A.total_warps = (int)tw;
+            A.pdl = g_pdl;
             switch (qt) {
-                case QT_SYM_INT4:  gemv_launch_sym_int4(x_dtype, nt, grid, A, st); break;
-                case QT_ASYM_INT4: gemv_launch_asym_int4(x_dtype, nt, grid, A, st); break;
-                case QT_FP8_E4M3:  gemv_launch_fp8_e4m3(x_dtype, nt, grid, A, st); break;
-                case QT_FP8_E5M2:  gemv_launch_fp8_e5m2(x_dtype, nt, grid, A, st); break;
-                case QT_FP6:       gemv_launch_fp6(x_dtype, nt, grid, A, st); break;
+                case QT_SYM_INT4:  gemv_launch_sym_int4(x_dtype, (int)mc, grid, A, st); break;
+                case QT_ASYM_INT4: gemv_launch_asym_int4(x_dtype, (int)mc, grid, A, st); break;
+                case QT_FP8_E4M3:  gemv_launch_fp8_e4m3(x_dtype, (int)mc, grid, A, st); break;
+                case QT_FP8_E5M2:  gemv_launch_fp8_e5m2(x_dtype, (int)mc, grid, A, st); break;
+                case QT_FP6:       gemv_launch_fp6(x_dtype, (int)mc, grid, A, st); break;
                 default: return LB_ERR_ARG;
             }
             note_launch();

@@ -6,9 +6,7 @@
 namespace lowbit {
 
 constexpr int GEMV_WARPS = 4;              // warps per CTA (each warp is an independent pipeline)
-constexpr int GEMV_TPC = 4;                // tiles per staged chunk (one TMA bulk copy of 2-4 KB)
-constexpr int GEMV_STAGES = 4;             // chunks in flight per warp
-constexpr int GEMV_MAX_WARPS_PER_SM = 32;  // bound used to size the split-K partial buffer
+constexpr int GEMV_MAX_WARPS_PER_SM = 16;  // warps per SM the grid is sized for (shared memory bound)
 constexpr int GEMV_MAX_NT = 4;             // n-tiles of 8 activation rows -> M <= 32 per pass
 
 struct GemvArgs {
@@ -20,10 +18,10 @@ struct GemvArgs {
     void* y; int y_dtype;     // [M][rows]
     const void* bias;         // NULL or [rows] of y_dtype
     int accumulate;
-    float* partials;          // [total_warps][2][NT][4][32]
-    unsigned* counters;       // [rows/16], zero between calls
-    int total_warps;
-    int dbg;                  // development switches (LOWBIT_GEMV_DBG): 1 skip flush, 2 skip x loads, 4 skip mma
+    float* partials;          // [total_warps][2][4 row tiles][NT][ACC][32]
+    unsigned* counters;       // [rows/64], zero between calls
+    int total_warps;          // <= number of super-tiles: every warp below it owns at least one
+    int pdl;                  // launched with programmatic stream serialization
 };
 
 __device__ __forceinline__ void store_out(void* y, int dt, int64_t idx, float v, const void* bias, int64_t row, int acc) {

@@ -16,17 +16,18 @@ __global__ void relayout_to_tiled_kernel(const uint8_t* __restrict__ src, uint8_
                                          TiledGeom G, int qt) {
     const int64_t q_bytes = G.off_s;
     const int64_t sm_halves = (G.off_tail - G.off_s) / 2;
-    const int64_t tail_bytes = (G.rows - G.r16) * G.nb * G.blk_bytes;
+    const int64_t tail_bytes = (G.rows - G.r64) * G.nb * G.blk_bytes;
     const int64_t total = q_bytes + sm_halves + tail_bytes;
     const int hdr = header_bytes(qt);
     for (int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; idx < total;
          idx += (int64_t)gridDim.x * blockDim.x) {
         if (idx < q_bytes) {
-            const int64_t f = idx / G.tile_code_bytes;
-            const int off = (int)(idx % G.tile_code_bytes);
-            const int64_t rt = f / G.nb, kb = f % G.nb;
-            // canonical record of (row, kb): src + (row*nb + kb)*blk
-            auto rec = [&](int r) { return src + ((rt * 16 + r) * G.nb + kb) * G.blk_bytes + hdr; };
+            const int64_t u = idx / G.super_code_bytes;
+            const int rem = (int)(idx % G.super_code_bytes);
+            const int tr = rem / G.tile_code_bytes, off = rem % G.tile_code_bytes;
+            const int64_t rg = u / G.nb, kb = u % G.nb;
+            // canonical record of (row, kb): src + (row*nb + kb)*blk ; r = row inside the 16-row tile
+            auto rec = [&](int r) { return src + ((rg * RG_ROWS + tr * 16 + r) * G.nb + kb) * G.blk_bytes + hdr; };
             uint32_t out = 0;
             if (qt == QT_FP8_E4M3 || qt == QT_FP8_E5M2) {
                 const int h = off >> 9, l = (off & 511) >> 4, e = off & 15;
@@ -58,17 +59,17 @@ __global__ void relayout_to_tiled_kernel(const uint8_t* __restrict__ src, uint8_
             dst[idx] = (uint8_t)out;
         } else if (idx < q_bytes + sm_halves) {
             int64_t hidx = idx - q_bytes;                 // index of the fp16 in S (then M)
-            const int which = hidx >= G.ntiles * 16 ? 1 : 0;   // 0: d, 1: m
-            hidx -= which ? G.ntiles * 16 : 0;
-            const int64_t f = hidx / 16;
-            const int g = (int)(hidx % 16) >> 1, h = (int)hidx & 1;
-            const int64_t rt = f / G.nb, kb = f % G.nb;
-            const uint8_t* r = src + ((rt * 16 + g + 8 * h) * G.nb + kb) * G.blk_bytes + 2 * which;
-            uint8_t* o = dst + G.off_s + (which ? G.ntiles * 32 : 0) + hidx * 2;
+            const int which = hidx >= G.nsuper * 64 ? 1 : 0;   // 0: d, 1: m
+            hidx -= which ? G.nsuper * 64 : 0;
+            const int64_t u = hidx / 64;
+            const int e = (int)(hidx % 64), g = e >> 3, tr = (e & 7) >> 1, h = e & 1;   // [g][r][h]
+            const int64_t rg = u / G.nb, kb = u % G.nb;
+            const uint8_t* r = src + ((rg * RG_ROWS + tr * 16 + g + 8 * h) * G.nb + kb) * G.blk_bytes + 2 * which;
+            uint8_t* o = dst + G.off_s + (which ? G.nsuper * 128 : 0) + hidx * 2;
             o[0] = r[0]; o[1] = r[1];
         } else {
             const int64_t b = idx - q_bytes - sm_halves;
-            dst[G.off_tail + b] = src[G.r16 * G.nb * G.blk_bytes + b];
+            dst[G.off_tail + b] = src[G.r64 * G.nb * G.blk_bytes + b];
         }
     }
 }
@@ -78,7 +79,7 @@ __global__ void relayout_to_tiled_kernel(const uint8_t* __restrict__ src, uint8_
 __global__ void relayout_to_canonical_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst,
                                              TiledGeom G, int qt) {
     const int64_t total = G.rows * G.nb * G.blk_bytes;
-    const int64_t main_bytes = G.r16 * G.nb * G.blk_bytes;
+    const int64_t main_bytes = G.r64 * G.nb * G.blk_bytes;
     const int hdr = header_bytes(qt);
     for (int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; idx < total;
          idx += (int64_t)gridDim.x * blockDim.x) {
@@ -86,14 +87,13 @@ __global__ void relayout_to_canonical_kernel(const uint8_t* __restrict__ src, ui
         const int64_t blk = idx / G.blk_bytes;
         const int b = (int)(idx % G.blk_bytes);
         const int64_t row = blk / G.nb, kb = blk % G.nb;
-        const int64_t f = (row / 16) * G.nb + kb;
-        const int r = (int)(row % 16), g = r & 7, h = r >> 3;
+        const int r = (int)(row % 16);
         if (b < hdr) {
             const int which = b >> 1;
-            dst[idx] = src[G.off_s + (which ? G.ntiles * 32 : 0) + f * 32 + (g * 2 + h) * 2 + (b & 1)];
+            dst[idx] = src[(which ? G.off_m : G.off_s) + scale_offset(G, row, kb) + (b & 1)];
             continue;
         }
-        const uint8_t* tile = src + f * G.tile_code_bytes;
+        const uint8_t* tile = src + tile_code_offset(G, row, kb);
         const int cb = b - hdr;
         uint32_t out;
         if (qt == QT_FP8_E4M3 || qt == QT_FP8_E5M2) out = tiled_code(qt, tile, r, cb);
@@ -120,18 +120,15 @@ __global__ void dequant_kernel(const uint8_t* __restrict__ src, OutT* __restrict
         bool tiled_here = false;
         if (TILED) {
             const int64_t row = blk / G.nb, kb = blk % G.nb;
-            if (row < G.r16) {
+            if (row < G.r64) {
                 tiled_here = true;
-                const int64_t f = (row / 16) * G.nb + kb;
-                const int r = (int)(row % 16);
-                code = tiled_code(qt, src + f * G.tile_code_bytes, r, j);
-                const uint16_t* s = (const uint16_t*)(src + G.off_s + f * 32);
-                dh = s[(r & 7) * 2 + (r >> 3)];
-                if (G.has_m) mh = ((const uint16_t*)(src + G.off_m + f * 32))[(r & 7) * 2 + (r >> 3)];
+                code = tiled_code(qt, src + tile_code_offset(G, row, kb), (int)(row % 16), j);
+                dh = *(const uint16_t*)(src + G.off_s + scale_offset(G, row, kb));
+                if (G.has_m) mh = *(const uint16_t*)(src + G.off_m + scale_offset(G, row, kb));
             }
         }
         if (!tiled_here) {
-            const uint8_t* rec = TILED ? src + G.off_tail + (blk - G.r16 * G.nb) * G.blk_bytes
+            const uint8_t* rec = TILED ? src + G.off_tail + (blk - G.r64 * G.nb) * G.blk_bytes
                                        : src + blk * G.blk_bytes;
             dh = (uint16_t)rec[0] | ((uint16_t)rec[1] << 8);
             if (G.has_m) mh = (uint16_t)rec[2] | ((uint16_t)rec[3] << 8);

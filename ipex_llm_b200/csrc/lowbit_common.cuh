@@ -7,14 +7,19 @@
 // qtype numbers: ggml/quantize.py:28-60.
 //
 // Device ("tiled") layout, same byte size as canonical, for a [rows][k] weight:
-//   R16 = rows & ~15 full 16-row tiles, nb = k/64 blocks per row, tile (rt, kb) = rows
-//   16*rt..16*rt+15 x k-block kb, flat index f = rt*nb + kb.
-//   region Q : f * QB bytes      codes, arranged so that lane l = 4*g + t of a warp owns
-//              rows (16rt+g, 16rt+g+8) x elements kb*64 + 16t .. 16t+15 -- exactly the
-//              mma.m16n8k16 A-fragment rows of that lane -- in 16-byte pieces at 16*l.
-//   region S : R16/16*nb*QB + f*32      fp16 d   as [g][h]  (h=0: row g, h=1: row g+8)
+//   R64 = rows & ~63 rows live in 64-row groups, nb = k/64 blocks per row.  Super-tile
+//   u = rg*nb + kb is the 64 rows of group rg x the 64 elements of k-block kb = four 16-row
+//   tiles r = 0..3 (rows 64rg + 16r + 0..15).
+//   region Q : u * 4*TB + r*TB   codes of tile r (TB = 512 / 1024 / 768 bytes for 4/8/6-bit),
+//              arranged so that lane l = 4*g + t of a warp owns rows (g, g+8) of the tile x
+//              elements 16t..16t+15 -- exactly the mma.m16n8k16 A-fragment rows of that lane
+//              -- in 16-byte pieces at 16*l.
+//   region S : after Q, u*128 bytes + fp16 d as [g][r][h]  (row 64rg + 16r + g + 8h), so lane
+//              (g,*) gets the scales of its 8 rows of the super-tile with one 16-byte load
 //   region M : (asym_int4 only) after S, same shape, fp16 m
-//   tail     : rows R16..rows-1 stay in canonical records after the planes.
+//   tail     : rows R64..rows-1 stay in canonical records after the planes.
+//   A run of super-tiles is ONE contiguous byte range of codes (+ one of scales): a warp streams
+//   its share of the matrix with plain 1-D TMA bulk copies.
 #pragma once
 #include <cuda_runtime.h>
 #include <cuda_fp16.h>
@@ -51,24 +56,40 @@ __host__ __device__ inline int type_size(int qt) {
 __host__ __device__ inline bool supported(int qt) { return code_bytes(qt) != 0; }
 
 // ---- tiled layout geometry -------------------------------------------------------------
+constexpr int RG_TILES = 4;     // 16-row tiles per row group
+constexpr int RG_ROWS = 64;     // rows per row group
+
 struct TiledGeom {
-    int64_t rows, k, nb, r16, ntiles;   // ntiles = (r16/16) * nb
+    int64_t rows, k, nb, r64, nsuper;   // nsuper = (r64/64) * nb super-tiles
     int tile_code_bytes;                // 16 rows * code_bytes
+    int super_code_bytes;               // 4 tiles
     int64_t off_s, off_m, off_tail;     // byte offsets of the regions
     int blk_bytes;
     bool has_m;
 };
 __host__ __device__ inline TiledGeom make_geom(int64_t rows, int64_t k, int qt) {
     TiledGeom g;
-    g.rows = rows; g.k = k; g.nb = k / QK; g.r16 = rows & ~int64_t(15);
-    g.ntiles = (g.r16 / 16) * g.nb;
+    g.rows = rows; g.k = k; g.nb = k / QK; g.r64 = rows & ~int64_t(RG_ROWS - 1);
+    g.nsuper = (g.r64 / RG_ROWS) * g.nb;
     g.tile_code_bytes = 16 * code_bytes(qt);
+    g.super_code_bytes = RG_TILES * g.tile_code_bytes;
     g.has_m = canon_qtype(qt) == QT_ASYM_INT4;
     g.blk_bytes = type_size(qt);
-    g.off_s = g.ntiles * g.tile_code_bytes;
-    g.off_m = g.off_s + g.ntiles * 32;
-    g.off_tail = g.off_m + (g.has_m ? g.ntiles * 32 : 0);
+    g.off_s = g.nsuper * g.super_code_bytes;
+    g.off_m = g.off_s + g.nsuper * 128;
+    g.off_tail = g.off_m + (g.has_m ? g.nsuper * 128 : 0);
     return g;
+}
+// byte offset of the codes of the 16-row tile holding (row, kb), row < r64
+__host__ __device__ inline int64_t tile_code_offset(const TiledGeom& G, int64_t row, int64_t kb) {
+    const int64_t u = (row / RG_ROWS) * G.nb + kb;
+    return u * G.super_code_bytes + ((row % RG_ROWS) / 16) * G.tile_code_bytes;
+}
+// byte offset (from off_s, or from off_m for the minimum) of the fp16 scale of (row, kb)
+__host__ __device__ inline int64_t scale_offset(const TiledGeom& G, int64_t row, int64_t kb) {
+    const int64_t u = (row / RG_ROWS) * G.nb + kb;
+    const int rr = (int)(row % RG_ROWS), r = rr >> 4, g = rr & 7, h = (rr >> 3) & 1;
+    return u * 128 + (g * 8 + r * 2 + h) * 2;
 }
 
 // ---- scalar decode helpers (used by dequant / generic kernels; not the GEMV hot loop) ----

@@ -197,6 +197,14 @@ def lowbit_matmul_cuda(d_w, qtype, n_rows, k, d_x, x_dtype, m, d_y, y_dtype, d_b
            "lowbit_matmul_cuda")
 
 
+_lib.lowbit_set_programmatic_dependent_launch.argtypes = [ctypes.c_int]
+_lib.lowbit_set_programmatic_dependent_launch.restype = None
+
+
+def lowbit_set_programmatic_dependent_launch(on):
+    _lib.lowbit_set_programmatic_dependent_launch(int(bool(on)))
+
+
 def last_launch_count():
     return _lib.b200_lowbit_last_launch_count()
 

@@ -21,9 +21,13 @@ def bench(N,K,M=1,qt=2,xdt=torch.float16,nw=24,tag=""):
     e1.record(); torch.cuda.synchronize()
     msg=e0.elapsed_time(e1)/(5*nw)
     print(f"{tag:12s} N={N:6d} K={K:6d} M={M:2d} qt={qt:2d} bytes={nbytes/1e6:7.2f}MB graph {msg*1e3:7.1f}us {nbytes/msg/1e6:7.0f}GB/s",flush=True)
-for dbg in (0,1,2,4,3,7):
+for dbg in (0,):
     os.environ["LOWBIT_GEMV_DBG"]=str(dbg)
     bench(11008,4096,tag=f"dbg={dbg}")
 os.environ["LOWBIT_GEMV_DBG"]="0"
 for N in (16,64,592,2368,4736,56832):
     bench(N,4096,tag="sizes")
+ggml.lowbit_set_programmatic_dependent_launch(1)
+for N in (16,4096,11008,32000):
+    bench(N,4096,tag="pdl")
+bench(4096,11008,tag="pdl")
