@@ -8,16 +8,11 @@
 
 namespace lowbit {
 
-void gemv_launch_sym_int4(int x_dtype, int m, int grid, const GemvArgs& A, cudaStream_t st);
-void gemv_launch_asym_int4(int x_dtype, int m, int grid, const GemvArgs& A, cudaStream_t st);
-void gemv_launch_fp8_e4m3(int x_dtype, int m, int grid, const GemvArgs& A, cudaStream_t st);
-void gemv_launch_fp8_e5m2(int x_dtype, int m, int grid, const GemvArgs& A, cudaStream_t st);
-void gemv_launch_fp6(int x_dtype, int m, int grid, const GemvArgs& A, cudaStream_t st);
-int gemv_warps_per_sm_sym_int4();
-int gemv_warps_per_sm_asym_int4();
-int gemv_warps_per_sm_fp8_e4m3();
-int gemv_warps_per_sm_fp8_e5m2();
-int gemv_warps_per_sm_fp6();
+void gemv_launch_sym_int4(int x_dtype, int m, int64_t groups, int64_t nb, const GemvArgs& A, cudaStream_t st);
+void gemv_launch_asym_int4(int x_dtype, int m, int64_t groups, int64_t nb, const GemvArgs& A, cudaStream_t st);
+void gemv_launch_fp8_e4m3(int x_dtype, int m, int64_t groups, int64_t nb, const GemvArgs& A, cudaStream_t st);
+void gemv_launch_fp8_e5m2(int x_dtype, int m, int64_t groups, int64_t nb, const GemvArgs& A, cudaStream_t st);
+void gemv_launch_fp6(int x_dtype, int m, int64_t groups, int64_t nb, const GemvArgs& A, cudaStream_t st);
 
 // ------------------------------------------------------------------ generic (any qtype, tail rows)
 // one warp per output row, scalar decode; used for nf4 until its mma codec lands, and for the
@@ -84,39 +79,16 @@ __global__ void split_f32_kernel(const float* __restrict__ x, __nv_bfloat16* __r
 // ------------------------------------------------------------------ host side
 static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
+static unsigned long long* g_ts = nullptr;   // development: phase timestamps
+void gemv_set_debug_timestamps(void* p) { g_ts = (unsigned long long*)p; }
 static int g_pdl = 0;     // programmatic dependent launch for the GEMV kernels (set by the host engine)
 void gemv_set_pdl(int on) { g_pdl = on ? 1 : 0; }
 
-static int max_total_warps() { return sm_count() * GEMV_MAX_WARPS_PER_SM; }
-static int warps_per_sm(int qt) {
-    switch (qt) {
-        case QT_SYM_INT4: return gemv_warps_per_sm_sym_int4();
-        case QT_ASYM_INT4: return gemv_warps_per_sm_asym_int4();
-        case QT_FP8_E4M3: return gemv_warps_per_sm_fp8_e4m3();
-        case QT_FP8_E5M2: return gemv_warps_per_sm_fp8_e5m2();
-        case QT_FP6: return gemv_warps_per_sm_fp6();
-        default: return GEMV_WARPS;
-    }
-}
-
-constexpr size_t kCounterBytes = 256 * 1024;                 // 65536 row tiles = 1M rows
-struct WsLayout { size_t counters, partials, xsplit, total; };
-static WsLayout ws_layout(int64_t n_rows, int64_t k, int64_t m, int x_dtype) {
-    WsLayout L;
-    const int64_t mm = m < 8 * GEMV_MAX_NT ? m : 8 * GEMV_MAX_NT;
-    const int nt = mm <= 8 ? 1 : mm <= 16 ? 2 : 4;
-    // fixed-size counter region: a workspace shared by calls with different n_rows must keep
-    // the counters where no other call's partials can land
-    (void)n_rows;
-    L.counters = 0;
-    L.partials = kCounterBytes;
-    L.xsplit = L.partials + align_up((size_t)max_total_warps() * 2 * RG_TILES * nt * 128 * sizeof(float), 256);
-    L.total = L.xsplit + (x_dtype == DT_F32 ? align_up((size_t)3 * mm * k * 2, 256) : 0);
-    return L;
-}
-
+// The only scratch the matmul needs: three bf16 planes of an fp32 activation chunk.
 size_t gemv_workspace_size(int64_t n_rows, int64_t k, int64_t m, int x_dtype) {
-    return ws_layout(n_rows, k, m, x_dtype).total;
+    (void)n_rows;
+    const int64_t mm = m < 8 * GEMV_MAX_NT ? m : 8 * GEMV_MAX_NT;
+    return x_dtype == DT_F32 ? align_up((size_t)3 * mm * k * 2, 256) : 0;
 }
 
 static bool has_mma_codec(int qt) {
@@ -138,7 +110,7 @@ int gemv_launch(const void* w, int qt, int64_t n_rows, int64_t k, const void* x,
     qt = canon_qtype(qt);
     if (!supported(qt) || k <= 0 || k % QK || n_rows <= 0 || m <= 0) return LB_ERR_ARG;
     if (x_dtype < 0 || x_dtype > 2 || y_dtype < 0 || y_dtype > 2) return LB_ERR_ARG;
-    if ((size_t)((n_rows + 63) / 64) * sizeof(unsigned) > kCounterBytes) return LB_ERR_ARG;
+    if (((uintptr_t)w & 15) || ((uintptr_t)x & 15)) return LB_ERR_ARG;        // TMA bulk / 128-bit loads
     const TiledGeom G = make_geom(n_rows, k, qt);
     const int esz_x = x_dtype == DT_F32 ? 4 : 2, esz_y = y_dtype == DT_F32 ? 4 : 2;
 
@@ -149,35 +121,28 @@ int gemv_launch(const void* w, int qt, int64_t n_rows, int64_t k, const void* x,
         char* yc = (char*)y + (size_t)mb * n_rows * esz_y;
         int64_t mma_rows = has_mma_codec(qt) ? G.r64 : 0;
         if (mma_rows > 0) {
-            const WsLayout L = ws_layout(n_rows, k, mc, x_dtype);
-            if (!workspace || workspace_bytes < L.total) return LB_ERR_WORKSPACE;
             GemvArgs A;
             A.w = (const uint8_t*)w; A.G = G; A.M = (int)mc;
             A.y = yc; A.y_dtype = y_dtype; A.bias = bias; A.accumulate = accumulate;
-            A.counters = (unsigned*)((char*)workspace + L.counters);
-            A.partials = (float*)((char*)workspace + L.partials);
             A.plane_stride = mc * k;
+            A.pdl = g_pdl; A.ts = g_ts;
             if (x_dtype == DT_F32) {
-                __nv_bfloat16* planes = (__nv_bfloat16*)((char*)workspace + L.xsplit);
+                const size_t need = gemv_workspace_size(n_rows, k, mc, x_dtype);
+                if (!workspace || workspace_bytes < need) return LB_ERR_WORKSPACE;
+                __nv_bfloat16* planes = (__nv_bfloat16*)workspace;
                 const int64_t n = mc * k;
                 int sg = (int)((n + 255) / 256); if (sg > sm_count() * 8) sg = sm_count() * 8;
                 split_f32_kernel<<<sg, 256, 0, st>>>((const float*)xc, planes, n);
                 note_launch();
                 A.x = (const uint16_t*)planes;
             } else A.x = (const uint16_t*)xc;
-            int64_t tw = (int64_t)sm_count() * warps_per_sm(qt);
-            const int64_t want = G.nsuper;                    // at least one super-tile per warp
-            if (tw > want) tw = want;
-            if (tw < 1) tw = 1;
-            const int grid = (int)((tw + GEMV_WARPS - 1) / GEMV_WARPS);
-            A.total_warps = (int)tw;
-            A.pdl = g_pdl;
+            const int64_t groups = G.r64 / RG_ROWS;
             switch (qt) {
-                case QT_SYM_INT4:  gemv_launch_sym_int4(x_dtype, (int)mc, grid, A, st); break;
-                case QT_ASYM_INT4: gemv_launch_asym_int4(x_dtype, (int)mc, grid, A, st); break;
-                case QT_FP8_E4M3:  gemv_launch_fp8_e4m3(x_dtype, (int)mc, grid, A, st); break;
-                case QT_FP8_E5M2:  gemv_launch_fp8_e5m2(x_dtype, (int)mc, grid, A, st); break;
-                case QT_FP6:       gemv_launch_fp6(x_dtype, (int)mc, grid, A, st); break;
+                case QT_SYM_INT4:  gemv_launch_sym_int4(x_dtype, (int)mc, groups, G.nb, A, st); break;
+                case QT_ASYM_INT4: gemv_launch_asym_int4(x_dtype, (int)mc, groups, G.nb, A, st); break;
+                case QT_FP8_E4M3:  gemv_launch_fp8_e4m3(x_dtype, (int)mc, groups, G.nb, A, st); break;
+                case QT_FP8_E5M2:  gemv_launch_fp8_e5m2(x_dtype, (int)mc, groups, G.nb, A, st); break;
+                case QT_FP6:       gemv_launch_fp6(x_dtype, (int)mc, groups, G.nb, A, st); break;
                 default: return LB_ERR_ARG;
             }
             note_launch();

@@ -6,7 +6,7 @@
 namespace lowbit {
 
 constexpr int GEMV_WARPS = 4;              // warps per CTA (each warp is an independent pipeline)
-constexpr int GEMV_MAX_WARPS_PER_SM = 16;  // warps per SM the grid is sized for (shared memory bound)
+constexpr int GEMV_MAX_SPLIT = 8;           // CTAs per cluster = K slices of one 64-row group
 constexpr int GEMV_MAX_NT = 4;             // n-tiles of 8 activation rows -> M <= 32 per pass
 
 struct GemvArgs {
@@ -18,10 +18,8 @@ struct GemvArgs {
     void* y; int y_dtype;     // [M][rows]
     const void* bias;         // NULL or [rows] of y_dtype
     int accumulate;
-    float* partials;          // [total_warps][2][4 row tiles][NT][ACC][32]
-    unsigned* counters;       // [rows/64], zero between calls
-    int total_warps;          // <= number of super-tiles: every warp below it owns at least one
     int pdl;                  // launched with programmatic stream serialization
+    unsigned long long* ts;   // development: per-warp phase timestamps (8 per warp) or NULL
 };
 
 __device__ __forceinline__ void store_out(void* y, int dt, int64_t idx, float v, const void* bias, int64_t row, int acc) {

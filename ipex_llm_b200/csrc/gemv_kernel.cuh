@@ -26,11 +26,14 @@
 //    fp32 activations are split into three bf16 planes (hi/mid/lo).  fp8/fp6 use cvt.
 //  * One x fragment, one sum(x) and one 16-byte scale load serve the four row tiles of a
 //    super-tile (64 rows x 64 k).
-//  * Work split ("stream-K"): warp w of W owns the contiguous tile span [w*T/W, (w+1)*T/W):
-//    balanced over 148 SMs whatever N and K are.  A warp that does not cover a whole row tile
-//    writes its fp32 partial fragment to the workspace and bumps that row tile's arrival counter;
-//    the last arriver adds the partials in warp order (deterministic, no float atomics) and
-//    stores.  Counters return to zero.
+//  * Work split: one thread-block CLUSTER per 64-row group; the S CTAs of the cluster split K,
+//    the 4 warps of a CTA split the CTA's K slice, each warp streams one contiguous run of
+//    super-tiles.  Partial sums meet in shared memory (warps of a CTA) and then in the leader
+//    CTA through distributed shared memory (ld.shared::cluster), always in the same order:
+//    deterministic, no atomics, no global scratch, no fences.  (Measured: a global-memory
+//    "last arriver" fix-up cost 3-5 us of serial L2 round trips per launch -- more than the
+//    3.7 us the 24 MB of a gate_proj take at HBM speed.)  S is chosen so that groups x S fills
+//    the ~4 CTA slots of every SM.
 //  * griddepcontrol.wait sits between the first weight copies and the first read of x, so under
 //    programmatic dependent launch the weight stream of call i+1 overlaps the tail of call i.
 #pragma once
@@ -42,6 +45,12 @@
 namespace lowbit {
 
 // ------------------------------------------------------------------ small PTX wrappers
+__device__ __forceinline__ unsigned long long gtime() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+#define TS(i) do { if (A.ts && lane == 0) A.ts[wid * 8 + (i)] = gtime(); } while (0)
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
 __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
@@ -210,104 +219,26 @@ template <int QT, bool BF> struct Staging {
     static constexpr int kStages = 3;
     static constexpr int kMinBytes = (C::kOffset == 2) ? 128 : 0;
     static constexpr int kStageBytes = kChunk * (kSuperCodes + 128 + kMinBytes);
-    static constexpr int kSmemBytes = GEMV_WARPS * (kStages * kStageBytes + kStages * 8);
+    static constexpr int kWarpBytes = kStages * kStageBytes;                      // >= 8 KB: also holds the reduction slot
+    static constexpr int kSmemBytes = GEMV_WARPS * (kWarpBytes + kStages * 8);
 };
+
+__device__ __forceinline__ uint32_t cluster_ctarank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ float ld_dsmem_f32(uint32_t local_addr, uint32_t rank) {
+    uint32_t remote; float v;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local_addr), "r"(rank));
+    asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(remote));
+    return v;
+}
 
 // ------------------------------------------------------------------ the kernel
 // ACC = accumulators per (row tile, n-tile): 4 (c0..c3), or 2 when M == 1 (only column 0 is live:
 // c0 = row g, c2 = row g+8).
-//
-// Row group `rg` is finished for this warp, which covered its k-blocks [kb_a, kb_b).  Rare path
-// (once or twice per warp), kept out of line so the main loop stays small.
-template <int NT, int ACC>
-__device__ __noinline__ void flush_row_group(const GemvArgs& A, const float (&acc)[RG_TILES][NT][ACC], int64_t wid,
-                                             int64_t u0, int rg, int kb_a, int kb_b, int lane) {
-    constexpr int NV = RG_TILES * NT * ACC;            // floats per lane
-    const int64_t T = A.G.nsuper, W = A.total_warps, nb = A.G.nb;
-    const int64_t r_begin = (int64_t)rg * nb, r_end = r_begin + nb;
-    float tot[RG_TILES][NT][ACC];
-    bool do_store = false;
-    if (kb_a == 0 && kb_b == (int)nb) {
-        do_store = true;
-#pragma unroll
-        for (int r = 0; r < RG_TILES; r++)
-#pragma unroll
-            for (int j = 0; j < NT; j++)
-#pragma unroll
-                for (int c = 0; c < ACC; c++) tot[r][j][c] = acc[r][j][c];
-    } else {
-        const int which = (u0 >= r_begin) ? 0 : 1;
-        float* P = A.partials + (wid * 2 + which) * (NV * 32);
-#pragma unroll
-        for (int r = 0; r < RG_TILES; r++)
-#pragma unroll
-            for (int j = 0; j < NT; j++)
-#pragma unroll
-                for (int c = 0; c < ACC; c++) __stcg(P + ((r * NT + j) * ACC + c) * 32 + lane, acc[r][j][c]);
-        __threadfence();
-        // owners of the first and last super-tile of this row group: owner(u) = ((u+1)*W - 1) / T
-        const int64_t w_first = ((r_begin + 1) * W - 1) / T;
-        const int64_t w_last = (r_end * W - 1) / T;
-        const unsigned need = (unsigned)(w_last - w_first + 1);
-        unsigned old = 0;
-        if (lane == 0) old = atomicAdd(A.counters + rg, 1u);
-        old = __shfl_sync(0xffffffffu, old, 0);
-        if (old == need - 1) {
-            __threadfence();
-            do_store = true;
-#pragma unroll
-            for (int r = 0; r < RG_TILES; r++)
-#pragma unroll
-                for (int j = 0; j < NT; j++)
-#pragma unroll
-                    for (int c = 0; c < ACC; c++) tot[r][j][c] = 0.0f;
-            // every contributor but the first starts inside this row group (slot 0); the first one
-            // uses slot 1 iff its span began in an earlier row group
-            const int first_slot = (w_first * T / W >= r_begin) ? 0 : 1;
-            for (int64_t wc = w_first; wc <= w_last; wc++) {
-                const float* Q = A.partials + (wc * 2 + (wc == w_first ? first_slot : 0)) * (NV * 32);
-                float v[NV];
-#pragma unroll
-                for (int i = 0; i < NV; i++) v[i] = __ldcg(Q + i * 32 + lane);
-#pragma unroll
-                for (int r = 0; r < RG_TILES; r++)
-#pragma unroll
-                    for (int j = 0; j < NT; j++)
-#pragma unroll
-                        for (int c = 0; c < ACC; c++) tot[r][j][c] += v[(r * NT + j) * ACC + c];
-            }
-            if (lane == 0) A.counters[rg] = 0u;
-        }
-    }
-    if (do_store) {
-        const int g = lane >> 2, t = lane & 3;
-        const int64_t N = A.G.rows;
-#pragma unroll
-        for (int r = 0; r < RG_TILES; r++) {
-            const int64_t r0 = (int64_t)rg * RG_ROWS + r * 16 + g, r1 = r0 + 8;
-#pragma unroll
-            for (int j = 0; j < NT; j++) {
-                const int m0 = 8 * j + 2 * t;
-                if (ACC == 2) {
-                    if (t == 0) {
-                        store_out(A.y, A.y_dtype, r0, tot[r][j][0], A.bias, r0, A.accumulate);
-                        store_out(A.y, A.y_dtype, r1, tot[r][j][ACC - 1], A.bias, r1, A.accumulate);
-                    }
-                } else {
-                    if (m0 < A.M) {
-                        store_out(A.y, A.y_dtype, (int64_t)m0 * N + r0, tot[r][j][0], A.bias, r0, A.accumulate);
-                        store_out(A.y, A.y_dtype, (int64_t)m0 * N + r1, tot[r][j][2 % ACC], A.bias, r1, A.accumulate);
-                    }
-                    if (m0 + 1 < A.M) {
-                        store_out(A.y, A.y_dtype, (int64_t)(m0 + 1) * N + r0, tot[r][j][1], A.bias, r0, A.accumulate);
-                        store_out(A.y, A.y_dtype, (int64_t)(m0 + 1) * N + r1, tot[r][j][3 % ACC], A.bias, r1, A.accumulate);
-                    }
-                }
-            }
-        }
-    }
-}
-
+// grid = (S, groups): blockIdx.y = 64-row group, blockIdx.x = K slice = rank in the cluster (S,1,1).
 template <int QT, bool BF, int NS, int NT, int ACC>
 __global__ void __launch_bounds__(GEMV_WARPS * 32)
 gemv_kernel(const GemvArgs A) {
@@ -316,21 +247,29 @@ gemv_kernel(const GemvArgs A) {
     using Tile = typename C::Tile;
     constexpr int CH = S::kChunk, STAGES = S::kStages, STAGE_BYTES = S::kStageBytes;
     constexpr int SUPER = S::kSuperCodes;
+    constexpr int NV = RG_TILES * NT * ACC;            // accumulator floats per lane
+    static_assert(NV * 128 <= S::kWarpBytes, "reduction slot must fit in the warp's ring");
     extern __shared__ __align__(128) uint8_t smem[];
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int g = lane >> 2, t = lane & 3;
-    const int64_t wid = (int64_t)blockIdx.x * GEMV_WARPS + warp;
-    if (A.pdl) asm volatile("griddepcontrol.launch_dependents;");
-    if (wid >= A.total_warps) return;                 // warps are independent: no CTA-wide barrier below
-    const int64_t u0 = wid * A.G.nsuper / A.total_warps, u1 = (wid + 1) * A.G.nsuper / A.total_warps;
-    const int n_super = (int)(u1 - u0);               // >= 1 because total_warps <= nsuper
+    const int nsplit = gridDim.x, slice = blockIdx.x, rg = blockIdx.y;
     const int nb = (int)A.G.nb;
-    const int n_chunks = (n_super + CH - 1) / CH;
+    if (A.pdl) asm volatile("griddepcontrol.launch_dependents;");
 
-    // this warp's private ring: [STAGES][codes | scales | mins], then STAGES mbarriers
-    const uint32_t ring = smem_u32(smem) + warp * (STAGES * STAGE_BYTES);
-    const uint32_t bars = smem_u32(smem) + GEMV_WARPS * (STAGES * STAGE_BYTES) + warp * (STAGES * 8);
+    // this CTA's k-blocks [ck0, ck1), this warp's [kb0, kb1)
+    const int ck0 = (int)((int64_t)slice * nb / nsplit), ck1 = (int)((int64_t)(slice + 1) * nb / nsplit);
+    const int kb0 = ck0 + (int)((int64_t)warp * (ck1 - ck0) / GEMV_WARPS);
+    const int kb1 = ck0 + (int)((int64_t)(warp + 1) * (ck1 - ck0) / GEMV_WARPS);
+    const int n_super = kb1 - kb0;
+    const int n_chunks = (n_super + CH - 1) / CH;
+    const int64_t u0 = (int64_t)rg * nb + kb0;         // first super-tile of this warp
+    const int64_t wid = ((int64_t)rg * nsplit + slice) * GEMV_WARPS + warp;   // timestamps only
+    TS(0);
+
+    // this warp's private ring: [STAGES][codes | scales | mins]; the mbarriers sit after all rings
+    const uint32_t ring = smem_u32(smem) + warp * S::kWarpBytes;
+    const uint32_t bars = smem_u32(smem) + GEMV_WARPS * S::kWarpBytes + warp * (STAGES * 8);
     const uint8_t* gq = A.w + u0 * SUPER;
     const uint8_t* gs = A.w + A.G.off_s + u0 * 128;
     const uint8_t* gm = A.w + A.G.off_m + u0 * 128;
@@ -345,16 +284,17 @@ gemv_kernel(const GemvArgs A) {
         if (S::kMinBytes) bulk_g2s(dst + CH * (SUPER + 128), gm + (size_t)c * (CH * 128), ns * 128, bar);
     };
 
-    if (lane == 0) {
+    if (lane == 0 && n_chunks > 0) {
 #pragma unroll
         for (int s = 0; s < STAGES; s++) mbar_init(bars + s * 8, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         // weights do not depend on the previous kernel: start streaming before the PDL wait
         for (int c = 0; c < STAGES && c < n_chunks; c++) issue(c);
     }
     __syncwarp();
+    TS(1);
     if (A.pdl) asm volatile("griddepcontrol.wait;" ::: "memory");
+    TS(2);
 
     float acc[RG_TILES][NT][ACC];
 #pragma unroll
@@ -363,12 +303,9 @@ gemv_kernel(const GemvArgs A) {
         for (int j = 0; j < NT; j++)
 #pragma unroll
             for (int c = 0; c < ACC; c++) acc[r][j][c] = 0.0f;
-    int rg = (int)(u0 / nb);
-    int kb = (int)(u0 - (int64_t)rg * nb);
-    int kb_first = kb;              // first k-block of the current row group handled by this warp
 
     // lane (g,t) reads x[8j+g][kb*64 + 16t .. +15] for n-tile j (plane p); rows >= M read as zero
-    const char* xbase[NT][NS];
+    const char* xptr[NT][NS];
     bool xvalid[NT];
     uint4 xb[NT][NS][2];            // lanes without a valid row keep zeros
 #pragma unroll
@@ -376,33 +313,22 @@ gemv_kernel(const GemvArgs A) {
         xvalid[j] = (8 * j + g) < A.M;
 #pragma unroll
         for (int p = 0; p < NS; p++) {
-            xbase[j][p] = reinterpret_cast<const char*>(A.x + p * A.plane_stride + (int64_t)(8 * j + g) * A.G.k + t * 16);
+            xptr[j][p] = reinterpret_cast<const char*>(A.x + p * A.plane_stride + (int64_t)(8 * j + g) * A.G.k + t * 16) +
+                         (size_t)kb0 * 128;
             xb[j][p][0] = make_uint4(0, 0, 0, 0); xb[j][p][1] = make_uint4(0, 0, 0, 0);
         }
     }
-    unsigned xoff = (unsigned)kb * 128u;   // byte offset of the current k-block inside an x row
+    unsigned xoff = 0;              // byte offset of the current k-block from kb0 inside an x row
 
     uint32_t ones[4];
     ones[0] = ones[1] = ones[2] = ones[3] = BF ? 0x3f803f80u : 0x3c003c00u;
-
-    // hand the accumulators to the out-of-line flush through a by-value copy so that `acc` itself
-    // never has to live in local memory
-    auto flush_acc = [&]() {
-        float tmp[RG_TILES][NT][ACC];
-#pragma unroll
-        for (int r = 0; r < RG_TILES; r++)
-#pragma unroll
-            for (int j = 0; j < NT; j++)
-#pragma unroll
-                for (int c = 0; c < ACC; c++) { tmp[r][j][c] = acc[r][j][c]; acc[r][j][c] = 0.0f; }
-        flush_row_group<NT, ACC>(A, tmp, wid, u0, rg, kb_first, kb, lane);
-    };
 
     for (int c = 0; c < n_chunks; c++) {
         const int st = c % STAGES;
         const uint32_t stage = ring + st * STAGE_BYTES;
         const int ns = min(CH, n_super - c * CH);
         mbar_wait(bars + st * 8, (uint32_t)((c / STAGES) & 1));
+        if (c == 0) TS(3);
 #pragma unroll
         for (int i = 0; i < CH; i++) {
             if (i < ns) {
@@ -412,46 +338,57 @@ gemv_kernel(const GemvArgs A) {
                 for (int j = 0; j < NT; j++)
 #pragma unroll
                     for (int p = 0; p < NS; p++)
-                        if (xvalid[j]) {                        // L1-cached: x is re-read for every row group
-                            xb[j][p][0] = ldg_cached16(xbase[j][p] + xoff);
-                            xb[j][p][1] = ldg_cached16(xbase[j][p] + xoff + 16);
+                        if (xvalid[j]) {                        // L1/L2-cached: x is shared by every row group
+                            xb[j][p][0] = ldg_cached16(xptr[j][p] + xoff);
+                            xb[j][p][1] = ldg_cached16(xptr[j][p] + xoff + 16);
                         }
+                xoff += 128u;
                 float xs[NT][4];                                // sum over the k-block of x (all 16 "rows" equal)
                 if (C::kOffset) {
 #pragma unroll
                     for (int j = 0; j < NT; j++) {
+                        float xs2[4];
                         xs[j][0] = xs[j][1] = xs[j][2] = xs[j][3] = 0.0f;
+                        xs2[0] = xs2[1] = xs2[2] = xs2[3] = 0.0f;
 #pragma unroll
                         for (int p = 0; p < NS; p++) {
                             mma16816<BF>(xs[j], ones, xb[j][p][0].x, xb[j][p][0].y);
-                            mma16816<BF>(xs[j], ones, xb[j][p][0].z, xb[j][p][0].w);
+                            mma16816<BF>(xs2, ones, xb[j][p][0].z, xb[j][p][0].w);
                             mma16816<BF>(xs[j], ones, xb[j][p][1].x, xb[j][p][1].y);
-                            mma16816<BF>(xs[j], ones, xb[j][p][1].z, xb[j][p][1].w);
+                            mma16816<BF>(xs2, ones, xb[j][p][1].z, xb[j][p][1].w);
                         }
+                        xs[j][0] += xs2[0]; xs[j][1] += xs2[1];
                     }
                 }
                 const uint4 dq = lds16(stage + CH * SUPER + i * 128 + g * 16);       // [r][h] fp16 d
                 uint4 mq = make_uint4(0, 0, 0, 0);
                 if (C::kOffset == 2) mq = lds16(stage + CH * (SUPER + 128) + i * 128 + g * 16);
+                // the four row tiles advance in lock step so that four independent HMMA chains are in flight
+                Tile tile[RG_TILES];
+                float cc[RG_TILES][NT][4];
 #pragma unroll
                 for (int r = 0; r < RG_TILES; r++) {
-                    Tile tile;
-                    C::load(tile, codes, r, lane);
-                    float cc[NT][4];
+                    C::load(tile[r], codes, r, lane);
 #pragma unroll
-                    for (int j = 0; j < NT; j++) cc[j][0] = cc[j][1] = cc[j][2] = cc[j][3] = 0.0f;
+                    for (int j = 0; j < NT; j++) cc[r][j][0] = cc[r][j][1] = cc[r][j][2] = cc[r][j][3] = 0.0f;
+                }
 #pragma unroll
-                    for (int s = 0; s < 4; s++) {
+                for (int s = 0; s < 4; s++) {
+#pragma unroll
+                    for (int r = 0; r < RG_TILES; r++) {
                         uint32_t a[4];
-                        C::frag(tile, s, a);
+                        C::frag(tile[r], s, a);
 #pragma unroll
                         for (int j = 0; j < NT; j++)
 #pragma unroll
                             for (int p = 0; p < NS; p++) {
                                 const uint4 v = xb[j][p][s >> 1];
-                                mma16816<BF>(cc[j], a, (s & 1) ? v.z : v.x, (s & 1) ? v.w : v.y);
+                                mma16816<BF>(cc[r][j], a, (s & 1) ? v.z : v.x, (s & 1) ? v.w : v.y);
                             }
                     }
+                }
+#pragma unroll
+                for (int r = 0; r < RG_TILES; r++) {
                     const uint32_t dr = r == 0 ? dq.x : r == 1 ? dq.y : r == 2 ? dq.z : dq.w;
                     const float2 d = __half22float2(u32_as_h2(dr));
                     const float dlo = d.x * C::kLo, dhi = d.y * C::kHi;
@@ -465,16 +402,16 @@ gemv_kernel(const GemvArgs A) {
 #pragma unroll
                     for (int j = 0; j < NT; j++) {
                         if (ACC == 2) {
-                            acc[r][j][0] = fmaf(dlo, cc[j][0], acc[r][j][0]);
-                            acc[r][j][1] = fmaf(dhi, cc[j][2], acc[r][j][1]);
+                            acc[r][j][0] = fmaf(dlo, cc[r][j][0], acc[r][j][0]);
+                            acc[r][j][1] = fmaf(dhi, cc[r][j][2], acc[r][j][1]);
                             if (C::kOffset) {
                                 acc[r][j][0] = fmaf(olo, xs[j][0], acc[r][j][0]);
                                 acc[r][j][1] = fmaf(ohi, xs[j][0], acc[r][j][1]);
                             }
                         } else {
-                            acc[r][j][0] = fmaf(dlo, cc[j][0], acc[r][j][0]); acc[r][j][1] = fmaf(dlo, cc[j][1], acc[r][j][1]);
-                            acc[r][j][2 % ACC] = fmaf(dhi, cc[j][2], acc[r][j][2 % ACC]);
-                            acc[r][j][3 % ACC] = fmaf(dhi, cc[j][3], acc[r][j][3 % ACC]);
+                            acc[r][j][0] = fmaf(dlo, cc[r][j][0], acc[r][j][0]); acc[r][j][1] = fmaf(dlo, cc[r][j][1], acc[r][j][1]);
+                            acc[r][j][2 % ACC] = fmaf(dhi, cc[r][j][2], acc[r][j][2 % ACC]);
+                            acc[r][j][3 % ACC] = fmaf(dhi, cc[r][j][3], acc[r][j][3 % ACC]);
                             if (C::kOffset) {
                                 acc[r][j][0] = fmaf(olo, xs[j][0], acc[r][j][0]); acc[r][j][1] = fmaf(olo, xs[j][1], acc[r][j][1]);
                                 acc[r][j][2 % ACC] = fmaf(ohi, xs[j][0], acc[r][j][2 % ACC]);
@@ -483,24 +420,104 @@ gemv_kernel(const GemvArgs A) {
                         }
                     }
                 }
-                xoff += 128u;
-                if (++kb == nb) {                     // end of the row group: flush and wrap
-                    flush_acc();
-                    rg++; kb = 0; kb_first = 0; xoff = 0u;
-                }
             }
         }
         // every lane has consumed the stage (its data sits in registers already used): refill it
         __syncwarp();
         if (lane == 0 && c + STAGES < n_chunks) issue(c + STAGES);
     }
-    if (kb != kb_first) flush_acc();
+    TS(4);
+
+    // ---- reduction.  Slot layout: value v = (r*NT + j)*ACC + c of lane l at float index v*32 + l.
+    // 1) every warp parks its fragment in its own (now idle) ring
+    float* slot = reinterpret_cast<float*>(smem + warp * S::kWarpBytes);
+#pragma unroll
+    for (int r = 0; r < RG_TILES; r++)
+#pragma unroll
+        for (int j = 0; j < NT; j++)
+#pragma unroll
+            for (int c = 0; c < ACC; c++) slot[((r * NT + j) * ACC + c) * 32 + lane] = acc[r][j][c];
+    __syncthreads();
+    // 2) the CTA's sum lands in warp 0's slot (fixed warp order)
+    float* cta = reinterpret_cast<float*>(smem);
+    for (int i = threadIdx.x; i < NV * 32; i += GEMV_WARPS * 32) {
+        float v = cta[i];
+#pragma unroll
+        for (int w = 1; w < GEMV_WARPS; w++) v += reinterpret_cast<const float*>(smem + w * S::kWarpBytes)[i];
+        cta[i] = v;
+    }
+    // 3) the leader CTA adds the K slices of its peers through distributed shared memory (fixed
+    //    rank order) and stores
+    if (nsplit > 1) cluster_sync_all();
+    if (slice == 0) {
+        const int64_t N = A.G.rows;
+        for (int i = threadIdx.x; i < NV * 32; i += GEMV_WARPS * 32) {
+            float v = cta[i];
+            for (int rk = 1; rk < nsplit; rk++) v += ld_dsmem_f32(smem_u32(cta + i), (uint32_t)rk);
+            const int l = i & 31, val = i >> 5, c = val % ACC, j = (val / ACC) % NT, r = val / (ACC * NT);
+            const int gg = l >> 2, tt = l & 3;
+            const int hi = (ACC == 2) ? c : (c >> 1);                     // row g (0) or g+8 (1)
+            const int col = 8 * j + 2 * tt + ((ACC == 2) ? 0 : (c & 1));
+            const int64_t row = (int64_t)rg * RG_ROWS + r * 16 + gg + 8 * hi;
+            if (col < A.M && (ACC != 2 || tt == 0))
+                store_out(A.y, A.y_dtype, (int64_t)col * N + row, v, A.bias, row, A.accumulate);
+        }
+    }
+    if (nsplit > 1) cluster_sync_all();                                   // peers' smem must outlive the reads
+    TS(5);
+}
+
+// K slices per 64-row group = cluster size: the largest of 8/4/2/1 for which every group's cluster
+// is resident at once (cudaOccupancyMaxActiveClusters: cluster placement strands some SMs, e.g.
+// size 4 leaves 132 of 148 usable) and every warp still gets at least one k-block.
+template <typename K>
+static int pick_split(K kernel, int smem, int64_t groups, int64_t nb, int (&cache)[4]) {
+    static const int sizes[4] = {8, 4, 2, 1};
+    for (int i = 0; i < 4; i++) {
+        const int sz = sizes[i];
+        if (sz > 1 && (int64_t)sz * GEMV_WARPS > nb) continue;
+        if (cache[i] < 0) {
+            cudaLaunchConfig_t cfg = {};
+            cfg.gridDim = dim3(sz, 64, 1); cfg.blockDim = dim3(GEMV_WARPS * 32); cfg.dynamicSmemBytes = smem;
+            cudaLaunchAttribute at[1];
+            at[0].id = cudaLaunchAttributeClusterDimension;
+            at[0].val.clusterDim.x = sz; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+            cfg.attrs = at; cfg.numAttrs = 1;
+            int n = 0;
+            if (cudaOccupancyMaxActiveClusters(&n, kernel, &cfg) != cudaSuccess) { cudaGetLastError(); n = 0; }
+            cache[i] = n;
+        }
+        if (groups <= cache[i] || sz == 1) return sz;
+    }
+    return 1;
+}
+
+template <typename K>
+static void launch_kernel(K kernel, int smem, int64_t groups, int64_t nb, const GemvArgs& A, cudaStream_t st,
+                          int (&cache)[4]) {
+    const int split = pick_split(kernel, smem, groups, nb, cache);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)split, (unsigned)groups, 1);
+    cfg.blockDim = dim3(GEMV_WARPS * 32); cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute at[2];
+    int na = 0;
+    at[na].id = cudaLaunchAttributeClusterDimension;
+    at[na].val.clusterDim.x = split; at[na].val.clusterDim.y = 1; at[na].val.clusterDim.z = 1;
+    na++;
+    if (A.pdl) {
+        at[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[na].val.programmaticStreamSerializationAllowed = 1;
+        na++;
+    }
+    cfg.attrs = at; cfg.numAttrs = na;
+    cudaLaunchKernelEx(&cfg, kernel, A);
 }
 
 template <int QT, bool BF, int NS>
-static void launch_nt(int m, int grid, const GemvArgs& A, cudaStream_t st) {
+static void launch_nt(int m, int64_t groups, int64_t nb, const GemvArgs& A, cudaStream_t st) {
     constexpr int SMEM = Staging<QT, BF>::kSmemBytes;
     static bool configured = false;     // per instantiation: raise the dynamic shared memory limit once
+    static int cache[4][4] = {{-1, -1, -1, -1}, {-1, -1, -1, -1}, {-1, -1, -1, -1}, {-1, -1, -1, -1}};
     if (!configured) {
         cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 1, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
         cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 1, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
@@ -508,37 +525,22 @@ static void launch_nt(int m, int grid, const GemvArgs& A, cudaStream_t st) {
         cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 4, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
         configured = true;
     }
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(GEMV_WARPS * 32); cfg.dynamicSmemBytes = SMEM; cfg.stream = st;
-    cudaLaunchAttribute at[1];
-    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    at[0].val.programmaticStreamSerializationAllowed = 1;
-    cfg.attrs = at; cfg.numAttrs = A.pdl ? 1 : 0;
-    if (m == 1) cudaLaunchKernelEx(&cfg, gemv_kernel<QT, BF, NS, 1, 2>, A);
-    else if (m <= 8) cudaLaunchKernelEx(&cfg, gemv_kernel<QT, BF, NS, 1, 4>, A);
-    else if (m <= 16) cudaLaunchKernelEx(&cfg, gemv_kernel<QT, BF, NS, 2, 4>, A);
-    else cudaLaunchKernelEx(&cfg, gemv_kernel<QT, BF, NS, 4, 4>, A);
+    if (m == 1) launch_kernel(gemv_kernel<QT, BF, NS, 1, 2>, SMEM, groups, nb, A, st, cache[0]);
+    else if (m <= 8) launch_kernel(gemv_kernel<QT, BF, NS, 1, 4>, SMEM, groups, nb, A, st, cache[1]);
+    else if (m <= 16) launch_kernel(gemv_kernel<QT, BF, NS, 2, 4>, SMEM, groups, nb, A, st, cache[2]);
+    else launch_kernel(gemv_kernel<QT, BF, NS, 4, 4>, SMEM, groups, nb, A, st, cache[3]);
 }
 template <int QT>
-static void launch_qt(int x_dtype, int m, int grid, const GemvArgs& A, cudaStream_t st) {
-    if (x_dtype == DT_F16) launch_nt<QT, false, 1>(m, grid, A, st);
-    else if (x_dtype == DT_BF16) launch_nt<QT, true, 1>(m, grid, A, st);
-    else launch_nt<QT, true, 3>(m, grid, A, st);
-}
-
-// resident warps per SM this qtype's kernel is sized for (shared memory bound)
-template <int QT> static int warps_per_sm_qt() {
-    const int per_cta = Staging<QT, false>::kSmemBytes + 1024;      // + driver reservation per CTA
-    int ctas = (227 * 1024) / per_cta;
-    if (ctas * GEMV_WARPS > GEMV_MAX_WARPS_PER_SM) ctas = GEMV_MAX_WARPS_PER_SM / GEMV_WARPS;
-    return ctas * GEMV_WARPS;
+static void launch_qt(int x_dtype, int m, int64_t groups, int64_t nb, const GemvArgs& A, cudaStream_t st) {
+    if (x_dtype == DT_F16) launch_nt<QT, false, 1>(m, groups, nb, A, st);
+    else if (x_dtype == DT_BF16) launch_nt<QT, true, 1>(m, groups, nb, A, st);
+    else launch_nt<QT, true, 3>(m, groups, nb, A, st);
 }
 
 // one translation unit per qtype instantiates this (keeps nvcc times parallel)
-#define LOWBIT_DEFINE_GEMV_QT(NAME, QT)                                                         \
-    void gemv_launch_##NAME(int x_dtype, int m, int grid, const GemvArgs& A, cudaStream_t st) { \
-        launch_qt<QT>(x_dtype, m, grid, A, st);                                                 \
-    }                                                                                           \
-    int gemv_warps_per_sm_##NAME() { return warps_per_sm_qt<QT>(); }
+#define LOWBIT_DEFINE_GEMV_QT(NAME, QT)                                                                         \
+    void gemv_launch_##NAME(int x_dtype, int m, int64_t groups, int64_t nb, const GemvArgs& A, cudaStream_t st) { \
+        launch_qt<QT>(x_dtype, m, groups, nb, A, st);                                                           \
+    }
 
 }  // namespace lowbit
