@@ -284,12 +284,12 @@ gemv_kernel(const GemvArgs A) {
         if (S::kMinBytes) bulk_g2s(dst + CH * (SUPER + 128), gm + (size_t)c * (CH * 128), ns * 128, bar);
     };
 
-    if (lane == 0 && n_chunks > 0) {
-#pragma unroll
-        for (int s = 0; s < STAGES; s++) mbar_init(bars + s * 8, 1);
+    // lane s owns stage s during start-up (the barrier inits and first copies go out in parallel);
+    // weights do not depend on the previous kernel: they start streaming before the PDL wait
+    if (lane < STAGES && lane < n_chunks) {
+        mbar_init(bars + lane * 8, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        // weights do not depend on the previous kernel: start streaming before the PDL wait
-        for (int c = 0; c < STAGES && c < n_chunks; c++) issue(c);
+        issue(lane);
     }
     __syncwarp();
     TS(1);
@@ -452,8 +452,13 @@ gemv_kernel(const GemvArgs A) {
     if (slice == 0) {
         const int64_t N = A.G.rows;
         for (int i = threadIdx.x; i < NV * 32; i += GEMV_WARPS * 32) {
+            float pv[GEMV_MAX_SPLIT - 1];
+#pragma unroll
+            for (int rk = 1; rk < GEMV_MAX_SPLIT; rk++)      // all remote loads in flight before the adds
+                pv[rk - 1] = rk < nsplit ? ld_dsmem_f32(smem_u32(cta + i), (uint32_t)rk) : 0.0f;
             float v = cta[i];
-            for (int rk = 1; rk < nsplit; rk++) v += ld_dsmem_f32(smem_u32(cta + i), (uint32_t)rk);
+#pragma unroll
+            for (int rk = 1; rk < GEMV_MAX_SPLIT; rk++) v += pv[rk - 1];
             const int l = i & 31, val = i >> 5, c = val % ACC, j = (val / ACC) % NT, r = val / (ACC * NT);
             const int gg = l >> 2, tt = l & 3;
             const int hi = (ACC == 2) ? c : (c >> 1);                     // row g (0) or g+8 (1)
