@@ -216,10 +216,11 @@ template <int QT, bool BF> struct Staging {
     using C = Codec<QT, BF>;
     static constexpr int kSuperCodes = RG_TILES * C::kTileBytes;                  // 2048 / 4096 / 3072
     static constexpr int kChunk = kSuperCodes <= 2048 ? 2 : 1;                    // ~4 KB of codes per bulk copy
-    static constexpr int kStages = 3;
+    static constexpr int kStages = 2;
     static constexpr int kMinBytes = (C::kOffset == 2) ? 128 : 0;
     static constexpr int kStageBytes = kChunk * (kSuperCodes + 128 + kMinBytes);
-    static constexpr int kWarpBytes = kStages * kStageBytes;                      // >= 8 KB: also holds the reduction slot
+    static constexpr int kRingBytes = kStages * kStageBytes;
+    static constexpr int kWarpBytes = kRingBytes > 8192 ? kRingBytes : 8192;      // also holds the reduction slot (<= 8 KB)
     static constexpr int kSmemBytes = GEMV_WARPS * (kWarpBytes + kStages * 8);
 };
 
@@ -343,21 +344,31 @@ gemv_kernel(const GemvArgs A) {
                             xb[j][p][1] = ldg_cached16(xptr[j][p] + xoff + 16);
                         }
                 xoff += 128u;
-                float xs[NT][4];                                // sum over the k-block of x (all 16 "rows" equal)
+                // sum over the k-block of x for columns 2t, 2t+1 of n-tile j, on the CUDA cores (the
+                // legacy HMMA pipe is this kernel's scarce resource on sm_100: ~30-45 cycles per
+                // mma.sync per SM sub-partition).  Lane (g,t) holds 16 of the 64 values of row 8j+g;
+                // fp32 adds in a fixed order, then a butterfly over t and a fetch from rows 2t, 2t+1.
+                float xs[NT][2];
                 if (C::kOffset) {
 #pragma unroll
                     for (int j = 0; j < NT; j++) {
-                        float xs2[4];
-                        xs[j][0] = xs[j][1] = xs[j][2] = xs[j][3] = 0.0f;
-                        xs2[0] = xs2[1] = xs2[2] = xs2[3] = 0.0f;
+                        float part = 0.0f;
 #pragma unroll
                         for (int p = 0; p < NS; p++) {
-                            mma16816<BF>(xs[j], ones, xb[j][p][0].x, xb[j][p][0].y);
-                            mma16816<BF>(xs2, ones, xb[j][p][0].z, xb[j][p][0].w);
-                            mma16816<BF>(xs[j], ones, xb[j][p][1].x, xb[j][p][1].y);
-                            mma16816<BF>(xs2, ones, xb[j][p][1].z, xb[j][p][1].w);
+                            const uint32_t w8[8] = {xb[j][p][0].x, xb[j][p][0].y, xb[j][p][0].z, xb[j][p][0].w,
+                                                    xb[j][p][1].x, xb[j][p][1].y, xb[j][p][1].z, xb[j][p][1].w};
+                            float2 a2 = make_float2(0.0f, 0.0f);
+#pragma unroll
+                            for (int q = 0; q < 8; q++) {
+                                const float2 f = BF ? __bfloat1622float2(u32_as_bf2(w8[q])) : __half22float2(u32_as_h2(w8[q]));
+                                a2.x += f.x; a2.y += f.y;
+                            }
+                            part += a2.x + a2.y;
                         }
-                        xs[j][0] += xs2[0]; xs[j][1] += xs2[1];
+                        part += __shfl_xor_sync(0xffffffffu, part, 1);
+                        part += __shfl_xor_sync(0xffffffffu, part, 2);          // every lane of group g: sum of row 8j+g
+                        xs[j][0] = __shfl_sync(0xffffffffu, part, (2 * t) * 4);      // row 2t   -> column 2t
+                        xs[j][1] = __shfl_sync(0xffffffffu, part, (2 * t + 1) * 4);  // row 2t+1 -> column 2t+1
                     }
                 }
                 const uint4 dq = lds16(stage + CH * SUPER + i * 128 + g * 16);       // [r][h] fp16 d
@@ -472,13 +483,13 @@ gemv_kernel(const GemvArgs A) {
     TS(5);
 }
 
-// K slices per 64-row group = cluster size: the largest of 8/4/2/1 for which every group's cluster
+// K slices per 64-row group = cluster size: the largest of 8..1 for which every group's cluster
 // is resident at once (cudaOccupancyMaxActiveClusters: cluster placement strands some SMs, e.g.
 // size 4 leaves 132 of 148 usable) and every warp still gets at least one k-block.
 template <typename K>
-static int pick_split(K kernel, int smem, int64_t groups, int64_t nb, int (&cache)[4]) {
-    static const int sizes[4] = {8, 4, 2, 1};
-    for (int i = 0; i < 4; i++) {
+static int pick_split(K kernel, int smem, int64_t groups, int64_t nb, int (&cache)[8]) {
+    static const int sizes[8] = {8, 7, 6, 5, 4, 3, 2, 1};
+    for (int i = 0; i < 8; i++) {
         const int sz = sizes[i];
         if (sz > 1 && (int64_t)sz * GEMV_WARPS > nb) continue;
         if (cache[i] < 0) {
@@ -499,7 +510,7 @@ static int pick_split(K kernel, int smem, int64_t groups, int64_t nb, int (&cach
 
 template <typename K>
 static void launch_kernel(K kernel, int smem, int64_t groups, int64_t nb, const GemvArgs& A, cudaStream_t st,
-                          int (&cache)[4]) {
+                          int (&cache)[8]) {
     const int split = pick_split(kernel, smem, groups, nb, cache);
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)split, (unsigned)groups, 1);
@@ -522,7 +533,8 @@ template <int QT, bool BF, int NS>
 static void launch_nt(int m, int64_t groups, int64_t nb, const GemvArgs& A, cudaStream_t st) {
     constexpr int SMEM = Staging<QT, BF>::kSmemBytes;
     static bool configured = false;     // per instantiation: raise the dynamic shared memory limit once
-    static int cache[4][4] = {{-1, -1, -1, -1}, {-1, -1, -1, -1}, {-1, -1, -1, -1}, {-1, -1, -1, -1}};
+    static int cache[4][8];
+    if (!configured) for (auto& row : cache) for (int& v : row) v = -1;
     if (!configured) {
         cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 1, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
         cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 1, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
