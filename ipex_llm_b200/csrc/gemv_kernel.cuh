@@ -37,6 +37,7 @@
 //  * griddepcontrol.wait sits between the first weight copies and the first read of x, so under
 //    programmatic dependent launch the weight stream of call i+1 overlaps the tail of call i.
 #pragma once
+#include <cstdlib>
 #include <cuda_fp8.h>
 #include "lowbit_common.cuh"
 #include "lowbit_internal.h"
@@ -221,13 +222,29 @@ template <int QT, bool BF> struct Staging {
     static constexpr int kStageBytes = kChunk * (kSuperCodes + 128 + kMinBytes);
     static constexpr int kRingBytes = kStages * kStageBytes;
     static constexpr int kWarpBytes = kRingBytes > 8192 ? kRingBytes : 8192;      // also holds the reduction slot (<= 8 KB)
-    static constexpr int kSmemBytes = GEMV_WARPS * (kWarpBytes + kStages * 8);
+    static constexpr int kBarBytes = GEMV_WARPS * kStages * 8 + 8;                // + the leader's receive barrier
+    // + the leader CTA's receive buffer for its peers' CTA sums (push reduction, M <= 8 kernels):
+    // (split-1) x NV x 32 floats
+    static constexpr int smem_bytes(int nt, int acc) {
+        return GEMV_WARPS * kWarpBytes + kBarBytes + 8 + (nt == 1 ? (GEMV_MAX_SPLIT - 1) * (RG_TILES * acc) * 128 : 0);
+    }
 };
 
 __device__ __forceinline__ uint32_t cluster_ctarank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
 __device__ __forceinline__ void cluster_sync_all() {
     asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
     asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t map_to_rank(uint32_t local_addr, uint32_t rank) {
+    uint32_t remote;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local_addr), "r"(rank));
+    return remote;
+}
+// asynchronous remote store that counts its 4 bytes on the destination CTA's mbarrier: no fences, and
+// the sending CTA may exit as soon as it has issued its stores
+__device__ __forceinline__ void st_async_f32(uint32_t remote_addr, float v, uint32_t remote_bar) {
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.b32 [%0], %1, [%2];"
+                 ::"r"(remote_addr), "r"(__float_as_uint(v)), "r"(remote_bar) : "memory");
 }
 __device__ __forceinline__ float ld_dsmem_f32(uint32_t local_addr, uint32_t rank) {
     uint32_t remote; float v;
@@ -285,6 +302,16 @@ gemv_kernel(const GemvArgs A) {
         if (S::kMinBytes) bulk_g2s(dst + CH * (SUPER + 128), gm + (size_t)c * (CH * 128), ns * 128, bar);
     };
 
+    constexpr bool PUSH = (NT == 1);                   // peers push their sums into the leader (else the leader pulls)
+    const uint32_t rbar = smem_u32(smem) + GEMV_WARPS * S::kWarpBytes + GEMV_WARPS * STAGES * 8;
+    float* recv = reinterpret_cast<float*>(smem + GEMV_WARPS * S::kWarpBytes + S::kBarBytes + 8);
+    if (PUSH && nsplit > 1) {
+        if (slice == 0 && threadIdx.x == 0) {
+            mbar_init(rbar, 1);
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        }
+        asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");   // matched by the wait before the tail
+    }
     // lane s owns stage s during start-up (the barrier inits and first copies go out in parallel);
     // weights do not depend on the previous kernel: they start streaming before the PDL wait
     if (lane < STAGES && lane < n_chunks) {
@@ -344,31 +371,22 @@ gemv_kernel(const GemvArgs A) {
                             xb[j][p][1] = ldg_cached16(xptr[j][p] + xoff + 16);
                         }
                 xoff += 128u;
-                // sum over the k-block of x for columns 2t, 2t+1 of n-tile j, on the CUDA cores (the
-                // legacy HMMA pipe is this kernel's scarce resource on sm_100: ~30-45 cycles per
-                // mma.sync per SM sub-partition).  Lane (g,t) holds 16 of the 64 values of row 8j+g;
-                // fp32 adds in a fixed order, then a butterfly over t and a fetch from rows 2t, 2t+1.
+                // -8 * sum over the k-block of x (sym) / sum (asym) for columns 2t, 2t+1: a ones-row mma,
+                // two independent chains (the tensor pipe is ~13 % busy in this kernel; issue slots are scarce)
                 float xs[NT][2];
                 if (C::kOffset) {
 #pragma unroll
                     for (int j = 0; j < NT; j++) {
-                        float part = 0.0f;
+                        float s1[4] = {0.0f, 0.0f, 0.0f, 0.0f}, s2[4] = {0.0f, 0.0f, 0.0f, 0.0f};
 #pragma unroll
                         for (int p = 0; p < NS; p++) {
-                            const uint32_t w8[8] = {xb[j][p][0].x, xb[j][p][0].y, xb[j][p][0].z, xb[j][p][0].w,
-                                                    xb[j][p][1].x, xb[j][p][1].y, xb[j][p][1].z, xb[j][p][1].w};
-                            float2 a2 = make_float2(0.0f, 0.0f);
-#pragma unroll
-                            for (int q = 0; q < 8; q++) {
-                                const float2 f = BF ? __bfloat1622float2(u32_as_bf2(w8[q])) : __half22float2(u32_as_h2(w8[q]));
-                                a2.x += f.x; a2.y += f.y;
-                            }
-                            part += a2.x + a2.y;
+                            mma16816<BF>(s1, ones, xb[j][p][0].x, xb[j][p][0].y);
+                            mma16816<BF>(s2, ones, xb[j][p][0].z, xb[j][p][0].w);
+                            mma16816<BF>(s1, ones, xb[j][p][1].x, xb[j][p][1].y);
+                            mma16816<BF>(s2, ones, xb[j][p][1].z, xb[j][p][1].w);
                         }
-                        part += __shfl_xor_sync(0xffffffffu, part, 1);
-                        part += __shfl_xor_sync(0xffffffffu, part, 2);          // every lane of group g: sum of row 8j+g
-                        xs[j][0] = __shfl_sync(0xffffffffu, part, (2 * t) * 4);      // row 2t   -> column 2t
-                        xs[j][1] = __shfl_sync(0xffffffffu, part, (2 * t + 1) * 4);  // row 2t+1 -> column 2t+1
+                        const float k = (C::kOffset == 1) ? -8.0f : 1.0f;
+                        xs[j][0] = k * (s1[0] + s2[0]); xs[j][1] = k * (s1[1] + s2[1]);
                     }
                 }
                 const uint4 dq = lds16(stage + CH * SUPER + i * 128 + g * 16);       // [r][h] fp16 d
@@ -402,32 +420,25 @@ gemv_kernel(const GemvArgs A) {
                 for (int r = 0; r < RG_TILES; r++) {
                     const uint32_t dr = r == 0 ? dq.x : r == 1 ? dq.y : r == 2 ? dq.z : dq.w;
                     const float2 d = __half22float2(u32_as_h2(dr));
-                    const float dlo = d.x * C::kLo, dhi = d.y * C::kHi;
-                    float olo = 0.0f, ohi = 0.0f;
-                    if (C::kOffset == 1) { olo = -8.0f * d.x; ohi = -8.0f * d.y; }
+                    float2 mn = make_float2(0.0f, 0.0f);
                     if (C::kOffset == 2) {
                         const uint32_t mr = r == 0 ? mq.x : r == 1 ? mq.y : r == 2 ? mq.z : mq.w;
-                        const float2 mn = __half22float2(u32_as_h2(mr));
-                        olo = mn.x; ohi = mn.y;
+                        mn = __half22float2(u32_as_h2(mr));
                     }
 #pragma unroll
                     for (int j = 0; j < NT; j++) {
-                        if (ACC == 2) {
-                            acc[r][j][0] = fmaf(dlo, cc[r][j][0], acc[r][j][0]);
-                            acc[r][j][1] = fmaf(dhi, cc[r][j][2], acc[r][j][1]);
-                            if (C::kOffset) {
-                                acc[r][j][0] = fmaf(olo, xs[j][0], acc[r][j][0]);
-                                acc[r][j][1] = fmaf(ohi, xs[j][0], acc[r][j][1]);
-                            }
-                        } else {
-                            acc[r][j][0] = fmaf(dlo, cc[r][j][0], acc[r][j][0]); acc[r][j][1] = fmaf(dlo, cc[r][j][1], acc[r][j][1]);
-                            acc[r][j][2 % ACC] = fmaf(dhi, cc[r][j][2], acc[r][j][2 % ACC]);
-                            acc[r][j][3 % ACC] = fmaf(dhi, cc[r][j][3], acc[r][j][3 % ACC]);
-                            if (C::kOffset) {
-                                acc[r][j][0] = fmaf(olo, xs[j][0], acc[r][j][0]); acc[r][j][1] = fmaf(olo, xs[j][1], acc[r][j][1]);
-                                acc[r][j][2 % ACC] = fmaf(ohi, xs[j][0], acc[r][j][2 % ACC]);
-                                acc[r][j][3 % ACC] = fmaf(ohi, xs[j][1], acc[r][j][3 % ACC]);
-                            }
+#pragma unroll
+                        for (int c = 0; c < ACC; c++) {
+                            const int ci = (ACC == 2) ? 2 * c : c;             // cc register feeding accumulator c
+                            const bool hi = (ACC == 2) ? (c == 1) : (c >= 2);   // row g+8
+                            const float dv = hi ? d.y : d.x;
+                            const float col = xs[j][(ACC == 2) ? 0 : (c & 1)];
+                            if (C::kOffset == 1)        // d * (code_sum * 2^s - 8 * sum(x))
+                                acc[r][j][c] = fmaf(dv, fmaf(cc[r][j][ci], hi ? C::kHi : C::kLo, col), acc[r][j][c]);
+                            else if (C::kOffset == 2)   // d * code_sum * 2^s + m * sum(x)
+                                acc[r][j][c] = fmaf(hi ? mn.y : mn.x, col, fmaf(dv * (hi ? C::kHi : C::kLo), cc[r][j][ci], acc[r][j][c]));
+                            else
+                                acc[r][j][c] = fmaf(dv, cc[r][j][ci], acc[r][j][c]);
                         }
                     }
                 }
@@ -457,35 +468,72 @@ gemv_kernel(const GemvArgs A) {
         for (int w = 1; w < GEMV_WARPS; w++) v += reinterpret_cast<const float*>(smem + w * S::kWarpBytes)[i];
         cta[i] = v;
     }
-    // 3) the leader CTA adds the K slices of its peers through distributed shared memory (fixed
-    //    rank order) and stores
-    if (nsplit > 1) cluster_sync_all();
-    if (slice == 0) {
-        const int64_t N = A.G.rows;
-        for (int i = threadIdx.x; i < NV * 32; i += GEMV_WARPS * 32) {
-            float pv[GEMV_MAX_SPLIT - 1];
-#pragma unroll
-            for (int rk = 1; rk < GEMV_MAX_SPLIT; rk++)      // all remote loads in flight before the adds
-                pv[rk - 1] = rk < nsplit ? ld_dsmem_f32(smem_u32(cta + i), (uint32_t)rk) : 0.0f;
-            float v = cta[i];
-#pragma unroll
-            for (int rk = 1; rk < GEMV_MAX_SPLIT; rk++) v += pv[rk - 1];
-            const int l = i & 31, val = i >> 5, c = val % ACC, j = (val / ACC) % NT, r = val / (ACC * NT);
-            const int gg = l >> 2, tt = l & 3;
-            const int hi = (ACC == 2) ? c : (c >> 1);                     // row g (0) or g+8 (1)
-            const int col = 8 * j + 2 * tt + ((ACC == 2) ? 0 : (c & 1));
-            const int64_t row = (int64_t)rg * RG_ROWS + r * 16 + gg + 8 * hi;
-            if (col < A.M && (ACC != 2 || tt == 0))
-                store_out(A.y, A.y_dtype, (int64_t)col * N + row, v, A.bias, row, A.accumulate);
+    // 3) across the cluster, always in rank order.  M <= 8: every peer pushes its CTA sum into the
+    //    leader's receive buffer with st.async (completion counted on the leader's mbarrier) and exits;
+    //    the leader waits for the bytes, adds and stores.  Larger M: the leader pulls through
+    //    ld.shared::cluster between two cluster barriers.
+    const int64_t N = A.G.rows;
+    auto store_value = [&](int i, float v) {
+        const int l = i & 31, val = i >> 5, c = val % ACC, j = (val / ACC) % NT, r = val / (ACC * NT);
+        const int gg = l >> 2, tt = l & 3;
+        const int hi = (ACC == 2) ? c : (c >> 1);                     // row g (0) or g+8 (1)
+        const int col = 8 * j + 2 * tt + ((ACC == 2) ? 0 : (c & 1));
+        const int64_t row = (int64_t)rg * RG_ROWS + r * 16 + gg + 8 * hi;
+        if (col < A.M && (ACC != 2 || tt == 0))
+            store_out(A.y, A.y_dtype, (int64_t)col * N + row, v, A.bias, row, A.accumulate);
+    };
+    if (nsplit == 1) {
+        for (int i = threadIdx.x; i < NV * 32; i += GEMV_WARPS * 32) store_value(i, cta[i]);
+    } else if (PUSH) {
+        asm volatile("barrier.cluster.wait.aligned;" ::: "memory");   // the leader's barrier init is visible
+        if (slice != 0) {
+            const uint32_t rb = map_to_rank(rbar, 0);
+            for (int i = threadIdx.x; i < NV * 32; i += GEMV_WARPS * 32)
+                st_async_f32(map_to_rank(smem_u32(recv + (slice - 1) * (NV * 32) + i), 0), cta[i], rb);
+        } else {
+            if (threadIdx.x == 0) mbar_expect_tx(rbar, (uint32_t)((nsplit - 1) * NV * 32 * 4));
+            mbar_wait(rbar, 0);
+            for (int i = threadIdx.x; i < NV * 32; i += GEMV_WARPS * 32) {
+                float v = cta[i];
+                for (int rk = 1; rk < nsplit; rk++) v += recv[(rk - 1) * (NV * 32) + i];
+                store_value(i, v);
+            }
         }
+    } else {
+        cluster_sync_all();
+        if (slice == 0) {
+            for (int i = threadIdx.x; i < NV * 32; i += GEMV_WARPS * 32) {
+                float pv[GEMV_MAX_SPLIT - 1];
+#pragma unroll
+                for (int rk = 1; rk < GEMV_MAX_SPLIT; rk++)      // all remote loads in flight before the adds
+                    pv[rk - 1] = rk < nsplit ? ld_dsmem_f32(smem_u32(cta + i), (uint32_t)rk) : 0.0f;
+                float v = cta[i];
+#pragma unroll
+                for (int rk = 1; rk < GEMV_MAX_SPLIT; rk++) v += pv[rk - 1];
+                store_value(i, v);
+            }
+        }
+        cluster_sync_all();                                      // peers' smem must outlive the reads
     }
-    if (nsplit > 1) cluster_sync_all();                                   // peers' smem must outlive the reads
     TS(5);
 }
 
 // K slices per 64-row group = cluster size: the largest of 8..1 for which every group's cluster
 // is resident at once (cudaOccupancyMaxActiveClusters: cluster placement strands some SMs, e.g.
 // size 4 leaves 132 of 148 usable) and every warp still gets at least one k-block.
+// Fraction of the co-resident cluster slots one launch may take.  Below 1 the NEXT launch's CTAs
+// find free slots while this one still runs, so that under programmatic dependent launch they
+// stream their first chunks during this launch's compute and reduction tail.
+static float occupancy_fraction() {
+    static float f = -1.0f;
+    if (f < 0.0f) {
+        const char* e = getenv("LOWBIT_GEMV_OCC");
+        f = e ? (float)atof(e) : 1.0f;
+        if (!(f > 0.05f && f <= 1.0f)) f = 1.0f;
+    }
+    return f;
+}
+
 template <typename K>
 static int pick_split(K kernel, int smem, int64_t groups, int64_t nb, int (&cache)[8]) {
     static const int sizes[8] = {8, 7, 6, 5, 4, 3, 2, 1};
@@ -503,7 +551,7 @@ static int pick_split(K kernel, int smem, int64_t groups, int64_t nb, int (&cach
             if (cudaOccupancyMaxActiveClusters(&n, kernel, &cfg) != cudaSuccess) { cudaGetLastError(); n = 0; }
             cache[i] = n;
         }
-        if (groups <= cache[i] || sz == 1) return sz;
+        if (groups <= (int64_t)(cache[i] * occupancy_fraction()) || sz == 1) return sz;
     }
     return 1;
 }
@@ -531,21 +579,21 @@ static void launch_kernel(K kernel, int smem, int64_t groups, int64_t nb, const 
 
 template <int QT, bool BF, int NS>
 static void launch_nt(int m, int64_t groups, int64_t nb, const GemvArgs& A, cudaStream_t st) {
-    constexpr int SMEM = Staging<QT, BF>::kSmemBytes;
+    using SG = Staging<QT, BF>;
     static bool configured = false;     // per instantiation: raise the dynamic shared memory limit once
     static int cache[4][8];
     if (!configured) for (auto& row : cache) for (int& v : row) v = -1;
     if (!configured) {
-        cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 1, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
-        cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 1, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
-        cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 2, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
-        cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 4, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
+        cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 1, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, SG::smem_bytes(1, 2));
+        cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 1, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, SG::smem_bytes(1, 4));
+        cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 2, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, SG::smem_bytes(2, 4));
+        cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 4, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, SG::smem_bytes(4, 4));
         configured = true;
     }
-    if (m == 1) launch_kernel(gemv_kernel<QT, BF, NS, 1, 2>, SMEM, groups, nb, A, st, cache[0]);
-    else if (m <= 8) launch_kernel(gemv_kernel<QT, BF, NS, 1, 4>, SMEM, groups, nb, A, st, cache[1]);
-    else if (m <= 16) launch_kernel(gemv_kernel<QT, BF, NS, 2, 4>, SMEM, groups, nb, A, st, cache[2]);
-    else launch_kernel(gemv_kernel<QT, BF, NS, 4, 4>, SMEM, groups, nb, A, st, cache[3]);
+    if (m == 1) launch_kernel(gemv_kernel<QT, BF, NS, 1, 2>, SG::smem_bytes(1, 2), groups, nb, A, st, cache[0]);
+    else if (m <= 8) launch_kernel(gemv_kernel<QT, BF, NS, 1, 4>, SG::smem_bytes(1, 4), groups, nb, A, st, cache[1]);
+    else if (m <= 16) launch_kernel(gemv_kernel<QT, BF, NS, 2, 4>, SG::smem_bytes(2, 4), groups, nb, A, st, cache[2]);
+    else launch_kernel(gemv_kernel<QT, BF, NS, 4, 4>, SG::smem_bytes(4, 4), groups, nb, A, st, cache[3]);
 }
 template <int QT>
 static void launch_qt(int x_dtype, int m, int64_t groups, int64_t nb, const GemvArgs& A, cudaStream_t st) {
