@@ -128,6 +128,13 @@ int lowbit_matmul_cuda(const void* d_w, int qtype, int64_t n_rows, int64_t k,
  * reads activations only after griddepcontrol.wait.  Process-wide switch, default off. */
 void lowbit_set_programmatic_dependent_launch(int on);
 
+/* One-shot hint consumed by the next lowbit_matmul_cuda on the calling thread: the device
+ * pointer and size of the weights the FOLLOWING matmul on the same stream will read (in a decoder
+ * the order of the linears is static).  The kernel asks the L2 to prefetch them
+ * (cp.async.bulk.prefetch.L2) while it runs, which keeps HBM busy during launch gaps and
+ * reduction tails.  Purely a performance hint: NULL / 0 or never calling it is always correct. */
+void lowbit_hint_next_weights(const void* d_w, size_t bytes);
+
 /* number of kernels the last lowbit_* / ggml_*_cuda call on this thread launched */
 int b200_lowbit_last_launch_count(void);
 /* SM count of the current device (0 if no device) */

@@ -109,6 +109,7 @@ int b200_lowbit_last_launch_count(void) { return t_launches; }
 int b200_lowbit_sm_count(void) { return have_device() ? sm_count() : 0; }
 void b200_lowbit_set_row_length(int k) { t_row_len = k; }
 void lowbit_set_programmatic_dependent_launch(int on) { gemv_set_pdl(on); }
+void lowbit_hint_next_weights(const void* d_w, size_t bytes) { gemv_set_next_weights(d_w, bytes); }
 /* development aid, not in the public header: per-warp phase timestamps of the GEMV kernel */
 void lowbit_debug_set_timestamps(void* dev_ptr) { gemv_set_debug_timestamps(dev_ptr); }
 

@@ -81,6 +81,9 @@ static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; 
 
 static unsigned long long* g_ts = nullptr;   // development: phase timestamps
 void gemv_set_debug_timestamps(void* p) { g_ts = (unsigned long long*)p; }
+static thread_local const uint8_t* t_next_w = nullptr;     // L2 prefetch hint for the next launch (one-shot)
+static thread_local unsigned long long t_next_bytes = 0;
+void gemv_set_next_weights(const void* w, size_t bytes) { t_next_w = (const uint8_t*)w; t_next_bytes = bytes; }
 static int g_pdl = 0;     // programmatic dependent launch for the GEMV kernels (set by the host engine)
 void gemv_set_pdl(int on) { g_pdl = on ? 1 : 0; }
 
@@ -126,6 +129,8 @@ int gemv_launch(const void* w, int qt, int64_t n_rows, int64_t k, const void* x,
             A.y = yc; A.y_dtype = y_dtype; A.bias = bias; A.accumulate = accumulate;
             A.plane_stride = mc * k;
             A.pdl = g_pdl; A.ts = g_ts;
+            A.next_w = t_next_w; A.next_bytes = t_next_bytes;
+            t_next_w = nullptr; t_next_bytes = 0;            // one-shot hint
             if (x_dtype == DT_F32) {
                 const size_t need = gemv_workspace_size(n_rows, k, mc, x_dtype);
                 if (!workspace || workspace_bytes < need) return LB_ERR_WORKSPACE;

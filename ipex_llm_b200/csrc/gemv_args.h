@@ -19,6 +19,8 @@ struct GemvArgs {
     const void* bias;         // NULL or [rows] of y_dtype
     int accumulate;
     int pdl;                  // launched with programmatic stream serialization
+    const uint8_t* next_w;    // hint: weights of the NEXT matmul on this stream, prefetched into L2 (or NULL)
+    unsigned long long next_bytes;
     unsigned long long* ts;   // development: per-warp phase timestamps (8 per warp) or NULL
 };
 

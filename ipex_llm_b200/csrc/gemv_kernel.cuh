@@ -316,11 +316,27 @@ gemv_kernel(const GemvArgs A) {
     // weights do not depend on the previous kernel: they start streaming before the PDL wait
     if (lane < STAGES && lane < n_chunks) {
         mbar_init(bars + lane * 8, 1);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        // make the init visible to the async proxy (the TMA engine completes bytes on this barrier);
+        // the cluster-scoped fence.mbarrier_init costs ~1 us here (it also invalidates L1)
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         issue(lane);
     }
     __syncwarp();
     TS(1);
+    // HBM is idle during a kernel's start-up, its reduction tail and the launch gap: about a third of a
+    // 24 MB GEMV.  If the host told us which weights the NEXT matmul on this stream reads, every warp asks
+    // the L2 (126 MB) to fetch its share of them now, behind our own demand loads.
+    if (A.next_w && lane == 0) {
+        const unsigned long long nw = (unsigned long long)gridDim.x * gridDim.y * GEMV_WARPS;
+        const unsigned long long me = ((unsigned long long)blockIdx.y * gridDim.x + blockIdx.x) * GEMV_WARPS + warp;
+        unsigned long long share = ((A.next_bytes + nw - 1) / nw + 127ull) & ~127ull;
+        const unsigned long long off = me * share;
+        if (off < A.next_bytes) {
+            if (off + share > A.next_bytes) share = (A.next_bytes - off) & ~15ull;
+            if (share)
+                asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(A.next_w + off), "r"((uint32_t)share) : "memory");
+        }
+    }
     if (A.pdl) asm volatile("griddepcontrol.wait;" ::: "memory");
     TS(2);
 

@@ -205,6 +205,14 @@ def lowbit_set_programmatic_dependent_launch(on):
     _lib.lowbit_set_programmatic_dependent_launch(int(bool(on)))
 
 
+_lib.lowbit_hint_next_weights.argtypes = [ctypes.c_void_p, ctypes.c_size_t]
+_lib.lowbit_hint_next_weights.restype = None
+
+
+def lowbit_hint_next_weights(d_w, nbytes):
+    _lib.lowbit_hint_next_weights(d_w, nbytes)
+
+
 def last_launch_count():
     return _lib.b200_lowbit_last_launch_count()
 

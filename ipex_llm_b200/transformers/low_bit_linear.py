@@ -221,7 +221,7 @@ def _get_workspace(device, need):
 
 
 def lowbit_matmul(x_2d: torch.Tensor, weight: torch.Tensor, weight_shape, qtype: int, out: torch.Tensor = None,
-                  bias: torch.Tensor = None, accumulate: bool = False, out_dtype=None):
+                  bias: torch.Tensor = None, accumulate: bool = False, out_dtype=None, next_weight: torch.Tensor = None):
     """x_2d [M,K] (fp32/fp16/bf16, CUDA) @ dequant(W [N,K], tiled device layout).T -> [M,N].
 
     The B200 twin of ``xe_linear.forward_new(x_2d, w, qtype, out_len)`` (LBL:704-708); ``out`` /
@@ -247,6 +247,8 @@ def lowbit_matmul(x_2d: torch.Tensor, weight: torch.Tensor, weight_shape, qtype:
     dev = x_2d.device
     need = ggml.lowbit_matmul_workspace_size(N, K, M, _TORCH_TO_DT[x_2d.dtype])
     ws = _get_workspace(dev, need)
+    if next_weight is not None:      # L2 prefetch hint: the weights the following matmul on this stream reads
+        ggml.lowbit_hint_next_weights(ctypes.c_void_p(next_weight.data_ptr()), next_weight.numel() * next_weight.element_size())
     with torch.cuda.device(dev):
         ggml.lowbit_matmul_cuda(ctypes.c_void_p(w.data_ptr()), qtype, N, K,
                                 ctypes.c_void_p(x_2d.data_ptr()), _TORCH_TO_DT[x_2d.dtype], M,
@@ -379,6 +381,7 @@ class LowBitLinear(nn.Linear):
         self.is_lm_head = self.in_len * self.out_len >= 32000 * 4096 and self.bias is None
         self.low_memory_mode = self.is_lm_head
         self.act_order = act_order
+        self.next_linear = None     # optional: the LowBitLinear that runs next (L2 prefetch hint, decode only)
         if act_order:
             self.register_buffer("g_idx_map", torch.arange(self.in_len, dtype=torch.int64))
 
@@ -413,8 +416,9 @@ class LowBitLinear(nn.Linear):
             if x_2d.dtype not in _TORCH_TO_DT:
                 x_2d = x_2d.float()
             fuse_bias = self.bias is not None and self.mp_group is None
+            nxt = self.next_linear.weight.data if (self.next_linear is not None and x_2d.shape[0] <= GEMV_MAX_M) else None
             result = lowbit_matmul(x_2d, self.weight.data, self.weight_shape, self.qtype,
-                                   bias=self.bias if fuse_bias else None)
+                                   bias=self.bias if fuse_bias else None, next_weight=nxt)
             result = result.view(new_shape)
             if self.mp_group is not None:
                 result = self._all_reduce(result)
