@@ -123,6 +123,21 @@ int lowbit_matmul_cuda(const void* d_w, int qtype, int64_t n_rows, int64_t k,
                        void* d_y, int y_dtype, const void* d_bias, int accumulate,
                        void* workspace, size_t workspace_bytes, void* stream);
 
+/* No counterpart in the reference.  The fp32-activation matmul of lowbit_matmul_cuda, for hosts that
+ * cannot give the library memory: an inference server whose arena owns all device memory and bans
+ * cudaMalloc after start-up, a process held to a fixed device-memory budget, a thread that must not
+ * hit the allocator's implicit synchronisation.  The scratch the kernel needs (three bf16 planes of
+ * the activations) is a fixed array inside the library: 1.5 MiB on every GPU that loads it, kept
+ * until the process exits.  Limit: m * k <= 262144 activation elements, larger calls return an
+ * error and launch nothing.  x is fp32 [m][k]; the other arguments are those of lowbit_matmul_cuda.
+ * The call allocates nothing.  Its first use on a device also looks up the array's device address
+ * (that device must be current); make that first call outside any stream capture.  All calls share
+ * the one array: two calls whose kernels may overlap on the GPU (different streams) race on it.
+ * Nothing in it needs clearing between calls - each call overwrites what it reads. */
+int lowbit_matmul_f32_noalloc_cuda(const void* d_w, int qtype, int64_t n_rows, int64_t k,
+                                   const float* d_x, int64_t m, void* d_y, int y_dtype,
+                                   const void* d_bias, int accumulate, void* stream);
+
 /* on != 0: the matmul kernels are launched with programmatic stream serialization (PDL): a
  * kernel may start streaming its weights while the previous kernel on the stream drains; it
  * reads activations only after griddepcontrol.wait.  Process-wide switch, default off. */

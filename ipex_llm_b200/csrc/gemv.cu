@@ -2,6 +2,7 @@
 // scalar generic kernel (nf4 until its mma codec lands; rows beyond the last 16-row tile) and
 // the fp32 -> 3 x bf16 activation split.  The mma kernel itself is in gemv_kernel.cuh.
 #include <cstdlib>
+#include <mutex>
 #include "lowbit_common.cuh"
 #include "lowbit_internal.h"
 #include "gemv_args.h"
@@ -163,3 +164,71 @@ int gemv_launch(const void* w, int qt, int64_t n_rows, int64_t k, const void* x,
 }
 
 }  // namespace lowbit
+
+// ------------------------------------------------------------------ allocation-free fp32 matmul
+// lowbit_matmul_cuda with fp32 activations needs scratch for the three bf16 planes it splits the
+// activations into.  Normally the caller allocates that (or lets the library cudaMalloc it).  Some
+// hosts can do neither: a serving runtime that handed every byte of device memory to its own arena
+// at start-up and forbids later cudaMalloc calls, a process running under a fixed device-memory
+// budget, or a latency-critical thread that must not take the allocator's implicit device
+// synchronisation.  For them the scratch lives in the library image itself.
+namespace {
+
+constexpr size_t kNoAllocMaxElems = 262144;   // activation elements (m * k) one call may carry
+// three bf16 planes of kNoAllocMaxElems elements = 1.5 MiB, resident on every GPU that loads the
+// library until the process exits
+static __device__ __align__(256) unsigned char g_noalloc_scratch[3 * kNoAllocMaxElems * 2];
+
+std::mutex g_noalloc_mu;
+void* g_noalloc_ptr[64] = {nullptr};          // device address of the array, per device ordinal
+
+// In host code the symbol above is only a stand-in: the device address has to be asked for, once per
+// device, with that device current.
+int noalloc_scratch(void** out) {
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess || dev < 0 || dev >= 64) {
+        lowbit::set_error(lowbit::LB_ERR_NO_DEVICE, "lowbit_matmul_f32_noalloc_cuda: no current CUDA device (%s)",
+                          e == cudaSuccess ? "ordinal out of range" : cudaGetErrorString(e));
+        cudaGetLastError();
+        return lowbit::LB_ERR_NO_DEVICE;
+    }
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    if (!g_noalloc_ptr[dev]) {
+        void* p = nullptr;
+        e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (e != cudaSuccess || !p) {
+            lowbit::set_error(lowbit::LB_ERR_CUDA, "lowbit_matmul_f32_noalloc_cuda: cudaGetSymbolAddress failed: %s",
+                              cudaGetErrorString(e));
+            cudaGetLastError();
+            return lowbit::LB_ERR_CUDA;
+        }
+        g_noalloc_ptr[dev] = p;
+    }
+    *out = g_noalloc_ptr[dev];
+    return lowbit::LB_OK;
+}
+
+}  // namespace
+
+extern "C" int lowbit_matmul_f32_noalloc_cuda(const void* d_w, int qtype, int64_t n_rows, int64_t k, const float* d_x,
+                                              int64_t m, void* d_y, int y_dtype, const void* d_bias, int accumulate,
+                                              void* stream) {
+    using namespace lowbit;
+    if (m == 0 || n_rows == 0) return LB_OK;
+    if (m < 0 || k <= 0 || (uint64_t)m * (uint64_t)k > kNoAllocMaxElems) {
+        set_error(LB_ERR_ARG, "lowbit_matmul_f32_noalloc_cuda: m * k = %lld x %lld exceeds the built-in scratch (%zu activation "
+                  "elements); use lowbit_matmul_cuda with a caller workspace", (long long)m, (long long)k, kNoAllocMaxElems);
+        return LB_ERR_ARG;
+    }
+    void* scratch = nullptr;
+    int rc = noalloc_scratch(&scratch);          // first call on a device resolves the symbol address
+    if (rc) return rc;
+    // every element of the planes this call reads is written by its own split pass first, so nothing in
+    // the shared array has to start at zero and nothing left by an earlier call is ever read
+    rc = gemv_launch(d_w, qtype, n_rows, k, d_x, DT_F32, m, d_y, y_dtype, d_bias, accumulate, scratch,
+                     sizeof(g_noalloc_scratch), (cudaStream_t)stream);
+    if (rc == LB_ERR_ARG) set_error(rc, "lowbit_matmul_f32_noalloc_cuda: bad argument (qtype %d, N %lld, K %lld, M %lld)", qtype,
+                                    (long long)n_rows, (long long)k, (long long)m);
+    return rc;
+}

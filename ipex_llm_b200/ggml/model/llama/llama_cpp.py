@@ -213,6 +213,19 @@ def lowbit_hint_next_weights(d_w, nbytes):
     _lib.lowbit_hint_next_weights(d_w, nbytes)
 
 
+_lib.lowbit_matmul_f32_noalloc_cuda.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_int64,
+                                                ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p, ctypes.c_int,
+                                                ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p]
+_lib.lowbit_matmul_f32_noalloc_cuda.restype = ctypes.c_int
+
+
+def lowbit_matmul_f32_noalloc_cuda(d_w, qtype, n_rows, k, d_x, m, d_y, y_dtype, d_bias, accumulate, stream):
+    """fp32-activation matmul that allocates nothing (scratch is a fixed array inside the library,
+    m * k <= 262144); for hosts that cannot let the library or themselves call cudaMalloc."""
+    _check(_lib.lowbit_matmul_f32_noalloc_cuda(d_w, qtype, n_rows, k, d_x, m, d_y, y_dtype, d_bias,
+                                               int(accumulate), stream), "lowbit_matmul_f32_noalloc_cuda")
+
+
 def last_launch_count():
     return _lib.b200_lowbit_last_launch_count()
 
