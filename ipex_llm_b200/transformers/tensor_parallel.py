@@ -1,0 +1,95 @@
+"""Tensor-parallel sharding of low-bit linears, the way the reference's DeepSpeed-AutoTP recipe
+does it (example/GPU/Deepspeed-AutoTP/deepspeed_autotp.py:74-106, convert.py:217-228):
+
+* column-parallel (split the output rows N): qkv / gate / up.  In the canonical layout a row is
+  ``K/QK`` consecutive block records, so a row range is one contiguous byte slice (the reference
+  relies on the same fact when it concatenates packed q, k, v: models/common.py:395-410);
+* row-parallel (split K): o_proj / down_proj.  Each rank keeps a block range of every row; its
+  partial output is summed across ranks by ONE all-reduce placed after the matmul and before the
+  bias (low_bit_linear.py:715-725) -- ``LowBitLinear._all_reduce`` with ``mp_group`` set.
+
+Both slicings commute with quantisation: blocks never straddle a shard boundary (K/world must be
+a multiple of QK), so slicing packed bytes is bit-identical to quantising the fp16 shard, which is
+what the reference does (it shards first, then calls optimize_model).  All functions here are
+byte/index manipulation on the CANONICAL layout; nothing is computed.
+"""
+import torch
+
+import ipex_llm_b200.ggml.model.llama.llama_cpp as ggml
+from ipex_llm_b200.utils.common import invalidInputError
+
+
+def _as_bytes(packed):
+    return packed.view(torch.uint8) if packed.dtype != torch.uint8 else packed
+
+
+def shard_bounds(total, world, rank, unit=1):
+    """[begin, end) of an even split of ``total`` (a multiple of ``unit * world``)."""
+    invalidInputError(total % (unit * world) == 0,
+                      f"cannot split {total} into {world} shards of a multiple of {unit}")
+    per = total // world
+    return rank * per, (rank + 1) * per
+
+
+def shard_packed_column(packed: torch.Tensor, shape, qtype: int, rank: int, world: int):
+    """rows [rank*N/world, (rank+1)*N/world) of a canonical packed [N, K] weight -> (packed, shape)"""
+    n, k = shape
+    qk, bs = ggml.ggml_qk_size(qtype), ggml.ggml_type_size(qtype)
+    r0, r1 = shard_bounds(n, world, rank)
+    row_bytes = (k // qk) * bs
+    b = _as_bytes(packed)
+    invalidInputError(b.numel() == n * row_bytes, "packed size does not match shape")
+    out = b[r0 * row_bytes:r1 * row_bytes].clone()
+    return (out.view(packed.dtype) if packed.dtype != torch.uint8 else out), (r1 - r0, k)
+
+
+def shard_packed_row(packed: torch.Tensor, shape, qtype: int, rank: int, world: int):
+    """columns [rank*K/world, (rank+1)*K/world) (whole blocks) of a canonical packed [N, K] weight"""
+    n, k = shape
+    qk, bs = ggml.ggml_qk_size(qtype), ggml.ggml_type_size(qtype)
+    k0, k1 = shard_bounds(k, world, rank, unit=qk)
+    nb = k // qk
+    b = _as_bytes(packed)
+    invalidInputError(b.numel() == n * nb * bs, "packed size does not match shape")
+    out = b.view(n, nb, bs)[:, k0 // qk:k1 // qk, :].contiguous().view(-1)
+    return (out.view(packed.dtype) if packed.dtype != torch.uint8 else out), (n, k1 - k0)
+
+
+def shard_qkv_column(packed: torch.Tensor, shape, qtype: int, rank: int, world: int, q_rows: int, kv_rows: int):
+    """merged qkv_proj ([q | k | v] rows, models/common.py:23-53): every rank takes its slice of the
+    heads of q, of k and of v (AutoTP shards q, k, v separately, before the merge)."""
+    n, k = shape
+    invalidInputError(n == q_rows + 2 * kv_rows, "qkv row counts do not add up")
+    qk, bs = ggml.ggml_qk_size(qtype), ggml.ggml_type_size(qtype)
+    row_bytes = (k // qk) * bs
+    b = _as_bytes(packed)
+    parts, rows = [], 0
+    for base, cnt in ((0, q_rows), (q_rows, kv_rows), (q_rows + kv_rows, kv_rows)):
+        r0, r1 = shard_bounds(cnt, world, rank)
+        parts.append(b[(base + r0) * row_bytes:(base + r1) * row_bytes])
+        rows += r1 - r0
+    out = torch.cat(parts)
+    return (out.view(packed.dtype) if packed.dtype != torch.uint8 else out), (rows, k)
+
+
+def make_parallel_linear(packed, shape, qtype, mode, rank, world, mp_group=None, bias=None, device=None):
+    """Build the rank-local ``LowBitLinear`` of a column- ("column") or row-parallel ("row") linear
+    from the unsharded canonical packed weight.  Row-parallel modules carry ``mp_group`` (their
+    forward all-reduces); the bias of a row-parallel linear is added once, after the all-reduce."""
+    from ipex_llm_b200.transformers.low_bit_linear import LowBitLinear, FP4Params
+    invalidInputError(mode in ("column", "row"), "mode must be 'column' or 'row'")
+    if mode == "column":
+        p, shp = shard_packed_column(packed, shape, qtype, rank, world)
+        b = None if bias is None else bias[shard_bounds(shape[0], world, rank)[0]:shard_bounds(shape[0], world, rank)[1]].clone()
+        group = None
+    else:
+        p, shp = shard_packed_row(packed, shape, qtype, rank, world)
+        b = None if bias is None else bias.clone()
+        group = mp_group
+    lin = LowBitLinear(shp[1], shp[0], qtype, bias=b is not None, mp_group=group)
+    lin.weight = FP4Params(p, quantized=True, _shape=torch.Size(shp), qtype=qtype)
+    if b is not None:
+        lin.bias = torch.nn.Parameter(b, requires_grad=False)
+    if device is not None:
+        lin = lin.to(device)
+    return lin

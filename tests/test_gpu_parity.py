@@ -281,3 +281,27 @@ def test_lowbit_linear_module(lbl, cuda_device, qtype):
     if qtype in ("sym_int4", "asym_int4", "fp6"):
         yc = qc(x)
         torch.testing.assert_close(yc, torch.from_numpy(oracle.matmul(packed, (272, 512), qtype, x.view(-1, 512).numpy())).view(2, 3, 272) + lin.bias.data.float(), rtol=1e-4, atol=1e-4)
+
+
+# ---------------------------------------------------------------- tensor parallel shards (one GPU)
+@pytest.mark.parametrize("qtype", ["sym_int4", "fp8_e5m2"])
+def test_tp_shards_reproduce_full_result(lbl, cuda_device, qtype):
+    """column shards concatenate, row shards sum to the unsharded output (the all-reduce the
+    row-parallel LowBitLinear issues over NCCL is emulated by a local sum of the rank partials)"""
+    from ipex_llm_b200.transformers import tensor_parallel as tp
+    rng = np.random.default_rng(1100)
+    N, K, M, world = 256, 1024, 2, 4
+    w = rand_w(rng, N, K)
+    packed = torch.from_numpy(oracle.quantize(w, qtype))
+    x_t = torch.from_numpy(rng.standard_normal((M, K)).astype(np.float32)).half()
+    full = run_matmul(lbl, cuda_device, oracle.quantize(w, qtype), (N, K), qtype, x_t, out_dtype=torch.float32)
+    cols, rows = [], torch.zeros(M, N, device=cuda_device)
+    for rank in range(world):
+        lin = tp.make_parallel_linear(packed, (N, K), qid(qtype), "column", rank, world, device=cuda_device)
+        cols.append(lin(x_t.to(cuda_device)).float())
+        lin = tp.make_parallel_linear(packed, (N, K), qid(qtype), "row", rank, world, device=cuda_device)
+        k0, k1 = rank * K // world, (rank + 1) * K // world
+        rows += lbl.lowbit_matmul(x_t[:, k0:k1].contiguous().to(cuda_device), lin.weight.data, lin.weight_shape,
+                                  lin.qtype, out_dtype=torch.float32)
+    torch.testing.assert_close(torch.cat(cols, dim=1), full.half().float(), rtol=0, atol=0)
+    torch.testing.assert_close(rows, full, rtol=1e-5, atol=1e-6)
