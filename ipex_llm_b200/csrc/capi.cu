@@ -145,8 +145,24 @@ int lowbit_relayout_cuda(const void* d_src, void* d_dst, int64_t rows, int64_t k
     return rc;
 }
 
+static bool use_gemm(int qtype, int64_t n_rows, int64_t k, int64_t m) {
+    return m > kGemvMaxM && gemm_tc_supported(qtype, n_rows, k);
+}
+
 size_t lowbit_matmul_workspace_size(int64_t n_rows, int64_t k, int64_t m, int x_dtype) {
+    if (use_gemm(B200_QT_SYM_INT4, n_rows, k, m)) return gemm_tc_workspace_size(k, m, x_dtype);
     return gemv_workspace_size(n_rows, k, m, x_dtype);
+}
+
+static int matmul_dispatch(const void* d_w, int qtype, int64_t n_rows, int64_t k, const void* d_x, int x_dtype, int64_t m,
+                           void* d_y, int y_dtype, const void* d_bias, int accumulate, void* workspace, size_t workspace_bytes,
+                           cudaStream_t st) {
+    if (use_gemm(qtype, n_rows, k, m)) {
+        int64_t done = 0;
+        return gemm_tc_launch(d_w, qtype, n_rows, k, d_x, x_dtype, m, d_y, y_dtype, d_bias, accumulate, workspace,
+                              workspace_bytes, st, &done);
+    }
+    return gemv_launch(d_w, qtype, n_rows, k, d_x, x_dtype, m, d_y, y_dtype, d_bias, accumulate, workspace, workspace_bytes, st);
 }
 
 int lowbit_matmul_cuda(const void* d_w, int qtype, int64_t n_rows, int64_t k, const void* d_x, int x_dtype,
@@ -159,7 +175,7 @@ int lowbit_matmul_cuda(const void* d_w, int qtype, int64_t n_rows, int64_t k, co
         lk.lock();
         DevState* S = dev_state();
         if (!S) { set_error(LB_ERR_NO_DEVICE, "lowbit_matmul_cuda: no CUDA device"); return LB_ERR_NO_DEVICE; }
-        const size_t need = gemv_workspace_size(n_rows, k, m, x_dtype);
+        const size_t need = lowbit_matmul_workspace_size(n_rows, k, m, x_dtype);
         if (need > S->ws.cap) {
             // growing frees the old buffer: wait for work that may still use it
             cudaDeviceSynchronize();
@@ -168,8 +184,8 @@ int lowbit_matmul_cuda(const void* d_w, int qtype, int64_t n_rows, int64_t k, co
         }
         workspace = S->ws.p; workspace_bytes = S->ws.cap;
     }
-    int rc = gemv_launch(d_w, qtype, n_rows, k, d_x, x_dtype, m, d_y, y_dtype, d_bias, accumulate, workspace,
-                         workspace_bytes, (cudaStream_t)stream);
+    int rc = matmul_dispatch(d_w, qtype, n_rows, k, d_x, x_dtype, m, d_y, y_dtype, d_bias, accumulate, workspace,
+                             workspace_bytes, (cudaStream_t)stream);
     if (rc == LB_ERR_ARG) set_error(rc, "lowbit_matmul_cuda: bad argument (qtype %d, N %lld, K %lld, M %lld)", qtype, (long long)n_rows, (long long)k, (long long)m);
     if (rc == LB_ERR_WORKSPACE) set_error(rc, "lowbit_matmul_cuda: workspace too small (%zu bytes)", workspace_bytes);
     return rc;
@@ -252,7 +268,7 @@ void ggml_compute_forward_mul_mat_q_fp32(const int64_t* src0_ne, const void* w, 
     }
     if (M == 0) return;
     const size_t w_bytes = (size_t)N * (K / QK) * bs, x_bytes = (size_t)M * K * 4, y_bytes = (size_t)M * N * 4;
-    const size_t ws_bytes = gemv_workspace_size(N, K, M, DT_F32);
+    const size_t ws_bytes = lowbit_matmul_workspace_size(N, K, M, DT_F32);
     // in: [canonical w][x]   out: [tiled w]   aux: y
     const size_t w_al = (w_bytes + 255) / 256 * 256;
     if (S->in.ensure(w_al + x_bytes, false) || S->out.ensure(w_bytes, false) || S->aux.ensure(y_bytes, false)) return;
@@ -260,7 +276,7 @@ void ggml_compute_forward_mul_mat_q_fp32(const int64_t* src0_ne, const void* w, 
     if (!cuda_ok(cudaMemcpy(S->in.p, w, w_bytes, cudaMemcpyHostToDevice), "H2D w")) return;
     if (!cuda_ok(cudaMemcpy((char*)S->in.p + w_al, x, x_bytes, cudaMemcpyHostToDevice), "H2D x")) return;
     if (relayout_launch(S->in.p, S->out.p, N, K, qtype, true, 0)) return;
-    if (gemv_launch(S->out.p, qtype, N, K, (char*)S->in.p + w_al, DT_F32, M, S->aux.p, DT_F32, nullptr, 0, S->ws.p, S->ws.cap, 0)) {
+    if (matmul_dispatch(S->out.p, qtype, N, K, (char*)S->in.p + w_al, DT_F32, M, S->aux.p, DT_F32, nullptr, 0, S->ws.p, S->ws.cap, 0)) {
         if (!t_err) set_error(LB_ERR_CUDA, "ggml_compute_forward_mul_mat_q_fp32: launch failed");
         return;
     }

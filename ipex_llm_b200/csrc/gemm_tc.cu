@@ -1,0 +1,487 @@
+// gemm_tc.cu -- kernel (c): prefill dequant-GEMM on the 5th-generation tensor cores.
+//
+// y[M][N] (+)= x[M][K] . dequant(W[N][K])^T for M > 32 activation rows: what LowBitLinear.forward
+// asks of xe_linear.forward_new during prefill (reference low_bit_linear.py:700-708) and of
+// ggml_compute_forward_mul_mat_q_fp32 / the dequantise + F.linear fallback on CPU (:739-745).
+//
+// One CTA computes a [128*MT tokens] x [128 features] tile (MT = 1 or 2), looping over K in
+// 64-element k-blocks through a 3-stage shared-memory pipeline:
+//   warp 0   producer : TMA 2-D tiled loads (128B swizzle) of the activation tile(s) and 1-D TMA
+//                       bulk copies of the PACKED weights of the tile's two 64-row groups (codes +
+//                       fp16 scales [+ minima]) -- weights cross HBM->SM at 4.25-8.25 bits each;
+//   warps 2-5 dequant : expand the packed codes to fp16/bf16 (magic-number trick / cvt, scale
+//                       applied with one fused multiply-add per pair) straight into the K-major
+//                       128B-swizzled B operand tile in shared memory; later the same warps are
+//                       the epilogue (tcgen05.ld of their 32 TMEM lanes -> bias/accumulate -> store);
+//   warp 1   MMA      : one elected thread issues tcgen05.mma.cta_group::1.kind::f16 (M=128, N=128,
+//                       K=16; 4 per k-block per token sub-tile), accumulators in TMEM (128*MT columns),
+//                       tcgen05.commit releases the stage and finally signals the epilogue.
+// The expanded weights never touch HBM; both token sub-tiles reuse one expanded B tile.
+// Weight rounding: (code - offset) * d is rounded ONCE to fp16 (11 bits) -- or to bf16 when the
+// activations are bf16 -- which is the precision contract of this path (tests: 2e-3 * sum|x w|).
+#include <cuda.h>
+#include <cuda_fp8.h>
+#include <mutex>
+#include "lowbit_common.cuh"
+#include "lowbit_internal.h"
+
+namespace lowbit {
+
+namespace gemmtc {
+
+constexpr int kStages = 3;
+constexpr int kThreads = 192;
+constexpr int kTileN = 128;          // features per CTA (two 64-row groups)
+constexpr int kTileBytesAB = 128 * 128;   // one 128-row x 64-element 2-byte operand tile
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}" ::"r"(bar), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, int c0, int c1, uint32_t bar) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                 ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(bar) : "memory");
+}
+// K-major, 128B-swizzled operand tile whose rows are 128 bytes: LBO = 1 (unused), SBO = 1024 B
+// (eight rows), descriptor version 1 (sm_100), layout type 2 = SWIZZLE_128B
+__device__ __forceinline__ uint64_t make_desc(uint32_t smem_addr) {
+    return (uint64_t)((smem_addr >> 4) & 0x3fff) | ((uint64_t)1 << 16) | ((uint64_t)64 << 32) | ((uint64_t)1 << 46) |
+           ((uint64_t)2 << 61);
+}
+__device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
+    uint32_t r[32];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+          "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+          "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 32; i++) v[i] = __uint_as_float(r[i]);
+}
+
+__device__ __forceinline__ uint32_t h2u(__half2 h) { return *reinterpret_cast<uint32_t*>(&h); }
+__device__ __forceinline__ __half2 u2h(uint32_t u) { return *reinterpret_cast<__half2*>(&u); }
+__device__ __forceinline__ uint32_t h2_to_bf2(uint32_t h) {
+    const float2 f = __half22float2(u2h(h));
+    __nv_bfloat162 b = __floats2bfloat162_rn(f.x, f.y);
+    return *reinterpret_cast<uint32_t*>(&b);
+}
+__device__ __forceinline__ uint32_t and_or(uint32_t a, uint32_t b, uint32_t c) {
+    uint32_t d;
+    asm("lop3.b32 %0, %1, %2, %3, 0xEA;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+
+// Scaled fp16 values of k-step s of one 16x64 tile for lane (g,t): out[0] = row g (4s,4s+1),
+// out[1] = row g+8 (4s,4s+1), out[2] = row g (4s+2,4s+3), out[3] = row g+8 (4s+2,4s+3); the same
+// register order as the mma.sync fragments of the GEMV kernel (the tile layout is shared).
+template <int QT> struct Expand;
+
+template <int OFFSET> struct Expand4 {          // sym_int4 (OFFSET 1) / asym_int4 (OFFSET 2)
+    static constexpr int kTileBytes = 512;
+    static constexpr bool kHasMin = OFFSET == 2;
+    __device__ static __forceinline__ void run(uint32_t codes, int lane, int s, __half2 dlo, __half2 dhi, __half2 mlo,
+                                               __half2 mhi, uint32_t (&out)[4]) {
+        uint32_t w;
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w) : "r"(codes + lane * 16 + s * 4));
+        const uint32_t w2 = w >> 8;
+        const __half2 k1024 = __floats2half2_rn(1024.0f, 1024.0f), k16th = __floats2half2_rn(0.0625f, 0.0625f);
+        const __half2 k64 = __floats2half2_rn(64.0f, 64.0f);
+        // 0x6400 | n = 1024 + n ; 0x6400 | (n << 4) = 1024 + 16 n  (exact in fp16)
+        const __half2 v0 = __hsub2(u2h(and_or(w, 0x000f000fu, 0x64006400u)), k1024);                 // n
+        const __half2 v1 = __hfma2(u2h(and_or(w, 0x00f000f0u, 0x64006400u)), k16th, __hneg2(k64));   // n
+        const __half2 v2 = __hsub2(u2h(and_or(w2, 0x000f000fu, 0x64006400u)), k1024);
+        const __half2 v3 = __hfma2(u2h(and_or(w2, 0x00f000f0u, 0x64006400u)), k16th, __hneg2(k64));
+        if (OFFSET == 1) {
+            // (n - 8) * d: n - 8 is exact, the product is rounded once
+            const __half2 k8 = __floats2half2_rn(8.0f, 8.0f);
+            out[0] = h2u(__hmul2(__hsub2(v0, k8), dlo)); out[1] = h2u(__hmul2(__hsub2(v1, k8), dhi));
+            out[2] = h2u(__hmul2(__hsub2(v2, k8), dlo)); out[3] = h2u(__hmul2(__hsub2(v3, k8), dhi));
+        } else {
+            out[0] = h2u(__hfma2(v0, dlo, mlo)); out[1] = h2u(__hfma2(v1, dhi, mhi));
+            out[2] = h2u(__hfma2(v2, dlo, mlo)); out[3] = h2u(__hfma2(v3, dhi, mhi));
+        }
+    }
+};
+template <> struct Expand<QT_SYM_INT4> : Expand4<1> {};
+template <> struct Expand<QT_ASYM_INT4> : Expand4<2> {};
+
+template <int QT> struct Expand8 {
+    static constexpr int kTileBytes = 1024;
+    static constexpr bool kHasMin = false;
+    __device__ static __forceinline__ uint32_t pair(uint32_t w, int hi) {
+        uint32_t h;
+        if (QT == QT_FP8_E5M2) h = __byte_perm(w, 0u, hi ? 0x3424u : 0x1404u);
+        else {
+            const unsigned short two = (unsigned short)(hi ? (w >> 16) : (w & 0xffffu));
+            asm("cvt.rn.f16x2.e4m3x2 %0, %1;" : "=r"(h) : "h"(two));
+        }
+        return h;
+    }
+    __device__ static __forceinline__ void run(uint32_t codes, int lane, int s, __half2 dlo, __half2 dhi, __half2, __half2,
+                                               uint32_t (&out)[4]) {
+        uint32_t w0, w1;
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w0) : "r"(codes + lane * 16 + s * 4));
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w1) : "r"(codes + 512 + lane * 16 + s * 4));
+        out[0] = h2u(__hmul2(u2h(pair(w0, 0)), dlo)); out[1] = h2u(__hmul2(u2h(pair(w1, 0)), dhi));
+        out[2] = h2u(__hmul2(u2h(pair(w0, 1)), dlo)); out[3] = h2u(__hmul2(u2h(pair(w1, 1)), dhi));
+    }
+};
+template <> struct Expand<QT_FP8_E4M3> : Expand8<QT_FP8_E4M3> {};
+template <> struct Expand<QT_FP8_E5M2> : Expand8<QT_FP8_E5M2> {};
+
+template <> struct Expand<QT_FP6> {
+    static constexpr int kTileBytes = 768;
+    static constexpr bool kHasMin = false;
+    __device__ static __forceinline__ uint32_t cvt2(unsigned short two) {
+        uint32_t h;
+        asm("cvt.rn.f16x2.e3m2x2 %0, %1;" : "=r"(h) : "h"(two));
+        return h;
+    }
+    __device__ static __forceinline__ void run(uint32_t codes, int lane, int s, __half2 dlo, __half2 dhi, __half2, __half2,
+                                               uint32_t (&out)[4]) {
+        const int u = s >> 1;
+        uint32_t l0, l1, h0, h1;
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(l0) : "r"(codes + lane * 16 + u * 4));
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(l1) : "r"(codes + lane * 16 + 8 + u * 4));
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(h0) : "r"(codes + 512 + lane * 8));
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(h1) : "r"(codes + 512 + lane * 8 + 4));
+        const uint32_t sh = (s & 1) ? 4u : 0u;
+        const uint32_t e0 = ((l0 >> sh) & 0x0f0f0f0fu) | (((h0 >> (2 * s)) & 0x03030303u) << 4);
+        const uint32_t e1 = ((l1 >> sh) & 0x0f0f0f0fu) | (((h1 >> (2 * s)) & 0x03030303u) << 4);
+        out[0] = h2u(__hmul2(u2h(cvt2((unsigned short)(e0 & 0xffffu))), dlo));
+        out[1] = h2u(__hmul2(u2h(cvt2((unsigned short)(e1 & 0xffffu))), dhi));
+        out[2] = h2u(__hmul2(u2h(cvt2((unsigned short)(e0 >> 16))), dlo));
+        out[3] = h2u(__hmul2(u2h(cvt2((unsigned short)(e1 >> 16))), dhi));
+    }
+};
+
+struct GemmArgs {
+    const uint8_t* w;
+    TiledGeom G;
+    int M;
+    void* y; int y_dtype;
+    const void* bias;
+    int accumulate;
+};
+
+template <int QT> struct Smem {
+    static constexpr int kSuper = RG_TILES * Expand<QT>::kTileBytes;
+    static constexpr int kPackedGroup = kSuper + 128 + (Expand<QT>::kHasMin ? 128 : 0);
+    static constexpr int kPacked = ((2 * kPackedGroup + 127) / 128) * 128;
+    // every stage starts 1024-byte aligned (the swizzled operand tiles sit at its start)
+    __host__ __device__ static constexpr int stage_bytes(int mt) { return ((mt * kTileBytesAB + kTileBytesAB + kPacked + 1023) / 1024) * 1024; }
+    __host__ __device__ static constexpr int total(int mt) { return 1024 + kStages * stage_bytes(mt) + 256; }
+};
+
+__device__ __forceinline__ void store_vals(const GemmArgs& A, int64_t token, int64_t n0, const float (&v)[32]) {
+    const int64_t N = A.G.rows;
+#pragma unroll
+    for (int i = 0; i < 32; i++) {
+        const int64_t row = n0 + i;
+        float val = v[i];
+        const int64_t idx = token * N + row;
+        if (A.y_dtype == DT_F32) {
+            float* p = (float*)A.y + idx;
+            if (A.bias) val += ((const float*)A.bias)[row];
+            if (A.accumulate) val += *p;
+            *p = val;
+        } else if (A.y_dtype == DT_F16) {
+            __half* p = (__half*)A.y + idx;
+            if (A.bias) val += __half2float(((const __half*)A.bias)[row]);
+            if (A.accumulate) val += __half2float(*p);
+            *p = __float2half_rn(val);
+        } else {
+            __nv_bfloat16* p = (__nv_bfloat16*)A.y + idx;
+            if (A.bias) val += __bfloat162float(((const __nv_bfloat16*)A.bias)[row]);
+            if (A.accumulate) val += __bfloat162float(*p);
+            *p = __float2bfloat16_rn(val);
+        }
+    }
+}
+
+// grid = (N / 128 feature tiles, ceil(M / (128*MT)) token tiles)
+template <int QT, bool BF, int MT>
+__global__ void __launch_bounds__(kThreads, 1)
+gemm_kernel(const __grid_constant__ CUtensorMap xmap, const GemmArgs A) {
+    using E = Expand<QT>;
+    using SM = Smem<QT>;
+    constexpr int STAGE = SM::stage_bytes(MT);
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;       // 128B swizzle wants 1024-byte alignment
+    const uint32_t bars = base + kStages * STAGE;                      // full[s], deq[s], empty[s], tmem_full, tmem slot
+    auto full_bar = [&](int s) { return bars + s * 8; };
+    auto deq_bar = [&](int s) { return bars + (kStages + s) * 8; };
+    auto empty_bar = [&](int s) { return bars + (2 * kStages + s) * 8; };
+    const uint32_t tmem_full = bars + 3 * kStages * 8;
+    const uint32_t tmem_slot = tmem_full + 8;
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int ftile = blockIdx.x;
+    const int m0 = blockIdx.y * (128 * MT);
+    const int nb = (int)A.G.nb;
+    constexpr uint32_t TMEM_COLS = 128 * MT;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kStages; s++) { mbar_init(full_bar(s), 1); mbar_init(deq_bar(s), 128); mbar_init(empty_bar(s), 1); }
+        mbar_init(tmem_full, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(TMEM_COLS) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    uint32_t tmem_base;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+
+    if (warp == 0) {
+        // ================= producer =================
+        if (lane == 0) {
+            const int64_t rg0 = (int64_t)ftile * 2;
+            for (int kb = 0; kb < nb; kb++) {
+                const int s = kb % kStages, round = kb / kStages;
+                mbar_wait(empty_bar(s), (uint32_t)((round & 1) ^ 1));
+                const uint32_t st = base + s * STAGE;
+                mbar_expect_tx(full_bar(s), MT * kTileBytesAB + 2 * SM::kPackedGroup);
+#pragma unroll
+                for (int mt = 0; mt < MT; mt++) tma_load_2d(st + mt * kTileBytesAB, &xmap, kb * 64, m0 + mt * 128, full_bar(s));
+                const uint32_t pk = st + (MT + 1) * kTileBytesAB;
+#pragma unroll
+                for (int gi = 0; gi < 2; gi++) {
+                    const int64_t u = (rg0 + gi) * nb + kb;
+                    const uint32_t dst = pk + gi * SM::kPackedGroup;
+                    bulk_g2s(dst, A.w + u * SM::kSuper, SM::kSuper, full_bar(s));
+                    bulk_g2s(dst + SM::kSuper, A.w + A.G.off_s + u * 128, 128, full_bar(s));
+                    if (E::kHasMin) bulk_g2s(dst + SM::kSuper + 128, A.w + A.G.off_m + u * 128, 128, full_bar(s));
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ================= MMA issuer =================
+        if (lane == 0) {
+            // c_format F32 (1<<4), a/b format (0 f16, 1 bf16), both K-major, N = 128 (>>3 at bit 17), M = 128 (>>4 at bit 24)
+            const uint32_t idesc = (1u << 4) | ((BF ? 1u : 0u) << 7) | ((BF ? 1u : 0u) << 10) | ((128u >> 3) << 17) | ((128u >> 4) << 24);
+            for (int kb = 0; kb < nb; kb++) {
+                const int s = kb % kStages, round = kb / kStages;
+                mbar_wait(full_bar(s), (uint32_t)(round & 1));
+                mbar_wait(deq_bar(s), (uint32_t)(round & 1));
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const uint32_t st = base + s * STAGE;
+                const uint32_t btile = st + MT * kTileBytesAB;
+#pragma unroll
+                for (int mt = 0; mt < MT; mt++) {
+#pragma unroll
+                    for (int k4 = 0; k4 < 4; k4++) {
+                        const uint64_t ad = make_desc(st + mt * kTileBytesAB + k4 * 32);
+                        const uint64_t bd = make_desc(btile + k4 * 32);
+                        umma_f16(tmem_base + mt * 128, ad, bd, idesc, (kb > 0 || k4 > 0) ? 1u : 0u);
+                    }
+                }
+                umma_commit(empty_bar(s));                  // stage reusable once these MMAs have read it
+            }
+            umma_commit(tmem_full);                          // accumulators complete
+        }
+    } else {
+        // ================= dequant warps, then epilogue =================
+        const int dw = warp - 2;                             // 0..3: tile r = dw of both row groups
+        const int g = lane >> 2, t = lane & 3;
+        for (int kb = 0; kb < nb; kb++) {
+            const int s = kb % kStages, round = kb / kStages;
+            mbar_wait(full_bar(s), (uint32_t)(round & 1));
+            const uint32_t st = base + s * STAGE;
+            const uint32_t btile = st + MT * kTileBytesAB;
+            const uint32_t pk = st + (MT + 1) * kTileBytesAB;
+#pragma unroll
+            for (int gi = 0; gi < 2; gi++) {
+                const uint32_t grp = pk + gi * SM::kPackedGroup;
+                const uint32_t codes = grp + dw * E::kTileBytes;
+                uint32_t dq, mq = 0;
+                asm volatile("ld.shared.u32 %0, [%1];" : "=r"(dq) : "r"(grp + SM::kSuper + g * 16 + dw * 4));
+                if (E::kHasMin) asm volatile("ld.shared.u32 %0, [%1];" : "=r"(mq) : "r"(grp + SM::kSuper + 128 + g * 16 + dw * 4));
+                const __half2 d2 = u2h(dq), m2 = u2h(mq);
+                const __half2 dlo = __low2half2(d2), dhi = __high2half2(d2);
+                const __half2 mlo = __low2half2(m2), mhi = __high2half2(m2);
+                // feature rows of this lane inside the 128-row B tile: f = 64*gi + 16*dw + g (+8)
+                const int f_lo = 64 * gi + 16 * dw + g;
+                const uint32_t row_lo = btile + (f_lo >> 3) * 1024 + (f_lo & 7) * 128;
+                const uint32_t row_hi = row_lo + 1024;      // f + 8: next 8-row group, same row inside it
+#pragma unroll
+                for (int q = 0; q < 2; q++) {               // k-steps 2q, 2q+1 -> one 16-byte chunk per row
+                    uint32_t a[4], b[4];
+                    E::run(codes, lane, 2 * q, dlo, dhi, mlo, mhi, a);
+                    E::run(codes, lane, 2 * q + 1, dlo, dhi, mlo, mhi, b);
+                    if (BF) {
+#pragma unroll
+                        for (int i = 0; i < 4; i++) { a[i] = h2_to_bf2(a[i]); b[i] = h2_to_bf2(b[i]); }
+                    }
+                    const uint32_t chunk = (uint32_t)((2 * t + q) ^ g) * 16;      // 128B swizzle: chunk ^ (row & 7)
+                    asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(row_lo + chunk), "r"(a[0]), "r"(a[2]), "r"(b[0]), "r"(b[2]) : "memory");
+                    asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(row_hi + chunk), "r"(a[1]), "r"(a[3]), "r"(b[1]), "r"(b[3]) : "memory");
+                }
+            }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");      // generic-proxy writes -> async-proxy (UMMA) reads
+            mbar_arrive(deq_bar(s));
+        }
+        // ---- epilogue: warp w may touch TMEM lanes 32*(w%4) .. +31
+        mbar_wait(tmem_full, 0);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const int quarter = warp & 3;
+#pragma unroll
+        for (int mt = 0; mt < MT; mt++) {
+            const int64_t token = (int64_t)m0 + mt * 128 + quarter * 32 + lane;
+#pragma unroll 1
+            for (int c = 0; c < 128; c += 32) {
+                float v[32];
+                tmem_ld32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(mt * 128 + c), v);
+                if (token < A.M) store_vals(A, token, (int64_t)ftile * kTileN + c, v);
+            }
+        }
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    }
+    __syncthreads();
+    if (warp == 1) {
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
+    }
+}
+
+// fp32 activations -> bf16 (prefill precision contract) into the workspace
+__global__ void f32_to_bf16_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ out, int64_t n) {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        out[i] = __float2bfloat16_rn(x[i]);
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+            qres == cudaDriverEntryPointSuccess)
+            fn = (EncodeTiledFn)p;
+        else cudaGetLastError();
+    });
+    return fn;
+}
+
+template <int QT, bool BF, int MT>
+static int launch_one(const CUtensorMap& map, const GemmArgs& A, dim3 grid, cudaStream_t st) {
+    constexpr int SMEM = Smem<QT>::total(MT);
+    static bool configured = false;
+    if (!configured) {
+        cudaFuncSetAttribute(gemm_kernel<QT, BF, MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
+        configured = true;
+    }
+    gemm_kernel<QT, BF, MT><<<grid, kThreads, SMEM, st>>>(map, A);
+    return 0;
+}
+template <int QT>
+static int launch_qt(bool bf, int mt, const CUtensorMap& map, const GemmArgs& A, dim3 grid, cudaStream_t st) {
+    if (bf) return mt == 2 ? launch_one<QT, true, 2>(map, A, grid, st) : launch_one<QT, true, 1>(map, A, grid, st);
+    return mt == 2 ? launch_one<QT, false, 2>(map, A, grid, st) : launch_one<QT, false, 1>(map, A, grid, st);
+}
+
+}  // namespace gemmtc
+
+bool gemm_tc_supported(int qt, int64_t n_rows, int64_t k) {
+    qt = canon_qtype(qt);
+    const bool q = qt == QT_SYM_INT4 || qt == QT_ASYM_INT4 || qt == QT_FP8_E4M3 || qt == QT_FP8_E5M2 || qt == QT_FP6;
+    return q && n_rows >= 128 && (n_rows % 128) == 0 && k >= 64 && (k % 64) == 0;
+}
+
+size_t gemm_tc_workspace_size(int64_t k, int64_t m, int x_dtype) {
+    return x_dtype == DT_F32 ? (size_t)((m * k * 2 + 255) / 256 * 256) : 0;
+}
+
+// rows [0, n_main) with n_main = n_rows & ~127 are computed here; the caller handles the rest
+int gemm_tc_launch(const void* w, int qt, int64_t n_rows, int64_t k, const void* x, int x_dtype, int64_t m, void* y,
+                   int y_dtype, const void* bias, int accumulate, void* workspace, size_t workspace_bytes, cudaStream_t st,
+                   int64_t* n_done) {
+    using namespace gemmtc;
+    qt = canon_qtype(qt);
+    *n_done = 0;
+    if (!gemm_tc_supported(qt, n_rows, k)) return LB_ERR_ARG;
+    EncodeTiledFn enc = encode_fn();
+    if (!enc) { set_error(LB_ERR_CUDA, "cuTensorMapEncodeTiled is not available from this driver"); return LB_ERR_CUDA; }
+    const int64_t n_main = n_rows & ~int64_t(127);
+    const void* xa = x;
+    bool bf = (x_dtype == DT_BF16);
+    if (x_dtype == DT_F32) {
+        const size_t need = gemm_tc_workspace_size(k, m, x_dtype);
+        if (!workspace || workspace_bytes < need) return LB_ERR_WORKSPACE;
+        const int64_t n = m * k;
+        int sg = (int)((n + 255) / 256); if (sg > sm_count() * 16) sg = sm_count() * 16;
+        f32_to_bf16_kernel<<<sg, 256, 0, st>>>((const float*)x, (__nv_bfloat16*)workspace, n);
+        note_launch();
+        xa = workspace; bf = true;
+    }
+    if (((uintptr_t)xa & 15) || ((uintptr_t)w & 15)) return LB_ERR_ARG;
+    CUtensorMap map;
+    const cuuint64_t gdim[2] = {(cuuint64_t)k, (cuuint64_t)m};
+    const cuuint64_t gstride[1] = {(cuuint64_t)k * 2};
+    const cuuint32_t box[2] = {64, 128};
+    const cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(&map, bf ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(xa), gdim,
+                     gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                     CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { set_error(LB_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d)", (int)r); return LB_ERR_CUDA; }
+    GemmArgs A;
+    A.w = (const uint8_t*)w; A.G = make_geom(n_rows, k, qt); A.M = (int)m;
+    A.y = y; A.y_dtype = y_dtype; A.bias = bias; A.accumulate = accumulate;
+    const int mt = m > 128 ? 2 : 1;
+    const dim3 grid((unsigned)(n_main / 128), (unsigned)((m + 128 * mt - 1) / (128 * mt)), 1);
+    switch (qt) {
+        case QT_SYM_INT4:  launch_qt<QT_SYM_INT4>(bf, mt, map, A, grid, st); break;
+        case QT_ASYM_INT4: launch_qt<QT_ASYM_INT4>(bf, mt, map, A, grid, st); break;
+        case QT_FP8_E4M3:  launch_qt<QT_FP8_E4M3>(bf, mt, map, A, grid, st); break;
+        case QT_FP8_E5M2:  launch_qt<QT_FP8_E5M2>(bf, mt, map, A, grid, st); break;
+        case QT_FP6:       launch_qt<QT_FP6>(bf, mt, map, A, grid, st); break;
+        default: return LB_ERR_ARG;
+    }
+    note_launch();
+    *n_done = n_main;
+    return check_launch();
+}
+
+}  // namespace lowbit

@@ -41,4 +41,14 @@ int gemv_launch(const void* w, int qt, int64_t n_rows, int64_t k, const void* x,
                 void* y, int y_dtype, const void* bias, int accumulate, void* workspace,
                 size_t workspace_bytes, cudaStream_t st);
 
+// gemm_tc.cu (tcgen05 prefill GEMM)
+bool gemm_tc_supported(int qt, int64_t n_rows, int64_t k);
+size_t gemm_tc_workspace_size(int64_t k, int64_t m, int x_dtype);
+int gemm_tc_launch(const void* w, int qt, int64_t n_rows, int64_t k, const void* x, int x_dtype, int64_t m, void* y,
+                   int y_dtype, const void* bias, int accumulate, void* workspace, size_t workspace_bytes, cudaStream_t st,
+                   int64_t* n_done);
+
+// M above this goes to the tensor-core GEMM when the shape allows, else to chunks of the GEMV
+constexpr int64_t kGemvMaxM = 32;
+
 }  // namespace lowbit

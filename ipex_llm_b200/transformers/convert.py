@@ -1,0 +1,128 @@
+"""Model conversion: swap eligible ``nn.Linear`` modules for ``LowBitLinear`` -- the part of the
+reference's ipex_llm/transformers/convert.py (CV below) that CONSTRUCTS the hot path
+(``is_linear_module`` CV:138-234, ``is_lm_head`` CV:126-130, ``use_scale_search`` CV:459-469,
+``_replace_with_low_bit_linear`` CV:472-752, ``ggml_convert_low_bit`` CV:1092-1193).
+
+Out of scope here: GPTQ/AWQ importers, vLLM/DeepSpeed module detection, embeddings,
+and the per-model forward patches of ``_optimize_pre`` / ``_optimize_post`` (qkv merging, fused MLP,
+attention kernels) -- the stock Hugging Face forwards run unchanged on top of ``LowBitLinear``.
+"""
+import logging
+import os
+import warnings
+
+import torch
+from torch import nn
+
+from ipex_llm_b200.ggml.quantize import ggml_tensor_qtype, B200_SUPPORTED_QTYPE_IDS
+from ipex_llm_b200.utils.common import invalidInputError
+
+logger = logging.getLogger("ipex_llm_b200")
+
+
+def is_linear_module(module):
+    """CV:138-234 reduced to the plain ``nn.Linear`` case: (is_linear, (in, out, mp_group))"""
+    from ipex_llm_b200.transformers.low_bit_linear import LowBitLinear
+    if isinstance(module, nn.Linear) and not isinstance(module, LowBitLinear):
+        return True, (module.in_features, module.out_features, None)
+    return False, None
+
+
+def is_lm_head(name, model_config, out_features):
+    """CV:126-130"""
+    return name == "lm_head" or getattr(model_config, "vocab_size", None) == out_features
+
+
+def use_scale_search(model_config, qtype):
+    """CV:459-469: scale search for fp6 and fp8_e4m3, with the reference's model exceptions"""
+    model_type = getattr(model_config, "model_type", None)
+    if qtype == ggml_tensor_qtype["fp6"] and model_type not in ["qwen2"]:
+        return True
+    if qtype == ggml_tensor_qtype["fp8_e4m3"] and model_type not in ["qwen2", "baichuan"]:
+        if model_type == "llama" and getattr(model_config, "vocab_size", None) == 128256 and \
+                "instruct" in str(getattr(model_config, "_name_or_path", "")).lower():
+            return False
+        return True
+    return False
+
+
+def _replace_with_low_bit_linear(model, qtype, modules_to_not_convert=None, convert_shape_only=False,
+                                 prefix_name="", model_config=None, enable_scale_search=False):
+    """CV:472-752.  Linears whose in_features is not a multiple of 64 stay as they are (CV:615-617);
+    lm_head (by name or vocab-sized output) gets ``optimize_lm_head`` unless IPEX_LLM_LAST_LM_HEAD=0
+    (CV:504-513).  Quantisation happens inside ``FP4Params.to(device)`` of the module's own device."""
+    from ipex_llm_b200.transformers.low_bit_linear import LowBitLinear, FP4Params
+    modules_to_not_convert = modules_to_not_convert or []
+    has_been_replaced = False
+    for name, module in model.named_children():
+        is_linear, linear_args = is_linear_module(module)
+        full_module_name = prefix_name + "." + name if prefix_name != "" else name
+        if any(key in full_module_name for key in modules_to_not_convert):
+            continue
+        if is_linear:
+            in_features, out_features, mp_group = linear_args
+            if in_features % 64 != 0:
+                continue
+            optimize_lm_head = is_lm_head(name, model_config, out_features) and \
+                os.environ.get("IPEX_LLM_LAST_LM_HEAD", None) != "0"
+            with torch.device("meta"):
+                new_linear = LowBitLinear(in_features, out_features, qtype, module.bias is not None,
+                                          mp_group=mp_group, optimize_lm_head=optimize_lm_head,
+                                          enable_scale_search=enable_scale_search)
+            device = module.weight.data.device
+            new_linear._parameters["weight"] = FP4Params(data=module.weight.data, requires_grad=False, quantized=False,
+                                                         _shape=None, convert_shape_only=convert_shape_only,
+                                                         qtype=qtype, in_features=in_features,
+                                                         enable_scale_search=enable_scale_search).to(device)
+            if module.bias is not None:
+                new_linear._parameters["bias"] = nn.Parameter(module.bias.data, requires_grad=False).to(device)
+            if not module.training:
+                new_linear.eval()
+            model._modules[name] = new_linear
+            model._modules[name].requires_grad_(False)
+            has_been_replaced = True
+            module.weight = None
+        if len(list(module.children())) > 0:
+            _, flag = _replace_with_low_bit_linear(module, qtype, modules_to_not_convert, convert_shape_only,
+                                                   prefix_name=full_module_name, model_config=model_config,
+                                                   enable_scale_search=enable_scale_search)
+            has_been_replaced = flag or has_been_replaced
+    return model, has_been_replaced
+
+
+def convert_bigdl_other_module(model, dtype):
+    """CV:1196-1229: every floating-point parameter / buffer outside the low-bit linears -> dtype"""
+    from ipex_llm_b200.transformers.low_bit_linear import LowBitLinear
+    for module in model.modules():
+        if list(module.children()) or isinstance(module, LowBitLinear):
+            continue
+        module.to(dtype)
+
+
+def ggml_convert_low_bit(model, qtype, optimize_model=True, convert_shape_only=False, device="cpu",
+                         modules_to_not_convert=None, torch_dtype="auto", **unused):
+    """CV:1092-1193.  ``woq_int4`` is the same format as ``sym_int4`` (CV:1101-1109)."""
+    if qtype == ggml_tensor_qtype["woq_int4"]:
+        qtype = ggml_tensor_qtype["sym_int4"]
+    invalidInputError(qtype in B200_SUPPORTED_QTYPE_IDS,
+                      f"qtype {qtype} is not implemented by the B200 low-bit kernels")
+    model_config = getattr(model, "config", None)
+    enable_scale_search = use_scale_search(model_config, qtype)
+    model, has_been_replaced = _replace_with_low_bit_linear(model, qtype, modules_to_not_convert or [],
+                                                            convert_shape_only, model_config=model_config,
+                                                            enable_scale_search=enable_scale_search)
+    if not has_been_replaced:
+        warnings.warn("No linear modules were found in your model.")
+    elif device == "cpu" and torch_dtype != "auto":
+        convert_bigdl_other_module(model, torch_dtype)
+    return model
+
+
+def chain_decode_prefetch(model):
+    """Name each LowBitLinear's successor in module order so that the decode GEMV can prefetch the next
+    weights into L2 (``LowBitLinear.next_linear``; a pure performance hint, see low_bit_linear.py)."""
+    from ipex_llm_b200.transformers.low_bit_linear import LowBitLinear
+    lins = [m for m in model.modules() if isinstance(m, LowBitLinear)]
+    for a, b in zip(lins, lins[1:] + lins[:1]):
+        a.next_linear = b
+    return model

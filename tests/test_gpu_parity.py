@@ -305,3 +305,44 @@ def test_tp_shards_reproduce_full_result(lbl, cuda_device, qtype):
                                   lin.qtype, out_dtype=torch.float32)
     torch.testing.assert_close(torch.cat(cols, dim=1), full.half().float(), rtol=0, atol=0)
     torch.testing.assert_close(rows, full, rtol=1e-5, atol=1e-6)
+
+
+# ---------------------------------------------------------------- (c) prefill GEMM on tcgen05
+@pytest.mark.parametrize("qtype", ["sym_int4", "asym_int4", "fp8_e4m3", "fp8_e5m2", "fp6"])
+@pytest.mark.parametrize("xdt,tol", [(torch.float16, 1e-3), (torch.bfloat16, 8e-3), (torch.float32, 8e-3)])
+@pytest.mark.parametrize("shape,M", [((256, 512), 64), ((128, 64), 33), ((384, 1024), 300)])
+def test_gemm_prefill_matches_oracle(lbl, cuda_device, qtype, xdt, tol, shape, M):
+    """M > 32 goes to the tensor-core kernel: dequantised weights are rounded once to fp16 (bf16 for
+    bf16 / fp32 activations, which are themselves taken in bf16): |diff| <= tol * sum|x w|"""
+    rng = np.random.default_rng(1200 + M)
+    N, K = shape
+    w = rand_w(rng, N, K)
+    packed = oracle.quantize(w, qtype)
+    x_t = torch.from_numpy(rng.standard_normal((M, K)).astype(np.float32)).to(xdt)
+    x = x_t.float().numpy()
+    y = run_matmul(lbl, cuda_device, packed, shape, qtype, x_t, out_dtype=torch.float32).cpu().numpy()
+    y64 = oracle.matmul_f64(packed, shape, qtype, x)
+    wd = np.abs(oracle.dequantize(packed, shape, qtype)).astype(np.float64)
+    bound = tol * (np.abs(x).astype(np.float64) @ wd.T) + 1e-30
+    assert np.isfinite(y).all()
+    assert (np.abs(y - y64) <= bound).all(), float((np.abs(y - y64) / bound).max())
+
+
+def test_gemm_prefill_epilogue_and_module(lbl, cuda_device):
+    rng = np.random.default_rng(1300)
+    N, K, M = 256, 512, 96
+    packed = oracle.quantize(rand_w(rng, N, K), "sym_int4")
+    x_t = torch.from_numpy(rng.standard_normal((M, K)).astype(np.float32)).half()
+    base = run_matmul(lbl, cuda_device, packed, (N, K), "sym_int4", x_t, out_dtype=torch.float32)
+    bias = torch.from_numpy(rng.standard_normal(N).astype(np.float32)).to(cuda_device)
+    yb = run_matmul(lbl, cuda_device, packed, (N, K), "sym_int4", x_t, out_dtype=torch.float32, bias=bias)
+    torch.testing.assert_close(yb, base + bias, rtol=0, atol=1e-5)
+    res = torch.from_numpy(rng.standard_normal((M, N)).astype(np.float32)).to(cuda_device)
+    out = res.clone()
+    run_matmul(lbl, cuda_device, packed, (N, K), "sym_int4", x_t, out=out, accumulate=True)
+    torch.testing.assert_close(out, res + base, rtol=0, atol=1e-5)
+    yh = run_matmul(lbl, cuda_device, packed, (N, K), "sym_int4", x_t, out_dtype=torch.float16)
+    torch.testing.assert_close(yh.float(), base.half().float(), rtol=0, atol=0)
+    # the GEMV (M <= 32, exact) and the GEMM (fp16-rounded weights) agree to the GEMM's tolerance
+    small = run_matmul(lbl, cuda_device, packed, (N, K), "sym_int4", x_t[:32], out_dtype=torch.float32)
+    torch.testing.assert_close(base[:32], small, rtol=2e-3, atol=2e-3)
