@@ -59,9 +59,22 @@ def assign_low_bit_state_dict(model, state):
 
 @contextmanager
 def low_memory_init():
-    """OP:107-122: build a model without allocating its weights (torch meta device)"""
-    with torch.device("meta"):
+    """OP:107-122: build a model without keeping its weights.  Like accelerate's ``init_empty_weights``
+    (which the reference uses), PARAMETERS land on the meta device as they are registered while buffers
+    (rotary tables, masks -- often non-persistent, so absent from checkpoints) are computed for real."""
+    old_register = torch.nn.Module.register_parameter
+
+    def register_on_meta(module, name, param):
+        old_register(module, name, param)
+        if param is not None and module._parameters[name].device.type != "meta":
+            p = module._parameters[name]
+            module._parameters[name] = torch.nn.Parameter(p.detach().to("meta"), requires_grad=p.requires_grad)
+
+    torch.nn.Module.register_parameter = register_on_meta
+    try:
         yield
+    finally:
+        torch.nn.Module.register_parameter = old_register
 
 
 def load_low_bit(model, model_path):

@@ -89,7 +89,8 @@ class _BaseAutoModelClass:
                                    "with load_in_4bit or load_in_low_bit to get a low-bit model , and "
                                    " serialize the model using save_low_bit first.")
         invalidInputError(low_bit in ggml_tensor_qtype, f"Unknown bigdl_transformers_low_bit value: {low_bit}")
-        with torch.device("meta"):
+        from ipex_llm_b200.optimize import low_memory_init
+        with low_memory_init():
             model = cls.HF_MODEL.from_config(config)
         model = ggml_convert_low_bit(model, ggml_tensor_qtype[low_bit], kwargs.pop("optimize_model", True),
                                      convert_shape_only=True, device="meta",
