@@ -126,3 +126,61 @@ def chain_decode_prefetch(model):
     for a, b in zip(lins, lins[1:] + lins[:1]):
         a.next_linear = b
     return model
+
+
+def convert_gptq(module, awq=False, llm_awq=False, act_order=False):
+    """GPTQ / AWQ 4-bit linear -> asym_int4 block records, without touching the weights' values
+    (reference CV:382-456: ``qs[j] = w[j] | w[j + QK/2] << 4``, record = ``d, m = -(zero * scale), qs``).
+
+    ``module`` carries ``qweight`` (int32, eight 4-bit codes per word), ``qzeros`` (int32), ``scales``
+    (fp16 [groups, out]), ``bits`` == 4, ``group_size`` (a multiple of 64) and, for GPTQ with
+    ``act_order``, ``g_idx``.  GPTQ packs codes along the input dimension and stores zero - 1; AWQ
+    packs along the output dimension (``wf`` gives its nibble order) and stores the zero itself.
+    Returns (packed uint8 canonical [out, in] asym_int4, g_idx_map or None).
+    """
+    from ipex_llm_b200.transformers.low_bit_linear import get_block_size
+    qk = get_block_size("asym_int4")
+    invalidInputError(module.bits == 4, "only 4-bit GPTQ/AWQ checkpoints map onto asym_int4")
+    invalidInputError(module.group_size % qk == 0, f"group_size must be a multiple of {qk}")
+    shifts = module.wf.reshape(-1).to(torch.int32)                     # bit offset of each of the 8 codes in a word
+    scales = module.scales.to(torch.float16)                           # [groups, out]
+    groups, out_features = scales.shape
+
+    def unpack_last(t):                                                # [..., n] int32 -> [..., n, 8] codes
+        return (t.unsqueeze(-1) >> shifts) & 0xF
+
+    zeros = unpack_last(module.qzeros).reshape(module.qzeros.shape[0], -1)[:, :out_features]
+    if not awq:
+        zeros = zeros + 1
+    if awq:
+        codes = unpack_last(module.qweight).reshape(module.qweight.shape[0], -1)      # [in, out]
+        if llm_awq:
+            codes = codes.t()
+    else:
+        codes = unpack_last(module.qweight.t()).reshape(out_features, -1).t()       # words run along `in`
+    g_idx_map = None
+    if act_order and not awq:
+        invalidInputError(module.g_idx.shape[0] == codes.shape[0], "g_idx and weight shape mismatch")
+        _, g_idx_map = torch.sort(module.g_idx)
+        codes = codes[g_idx_map, :]
+    in_features = codes.shape[0]
+    if llm_awq:
+        real = in_features // module.group_size
+        zeros, scales = zeros[:, :real].t() if zeros.shape[0] != real else zeros[:real], scales[:real]
+    w = codes.t().reshape(out_features, in_features // qk, qk).to(torch.uint8)        # [out, blocks, 64]
+    qs = w[:, :, :qk // 2] | (w[:, :, qk // 2:] << 4)
+    per_block = module.group_size // qk
+    d = scales.t().repeat_interleave(per_block, dim=1).contiguous()                    # [out, blocks]
+    z = zeros.t().to(torch.float16).repeat_interleave(per_block, dim=1)
+    m = -(z * d)
+    rec = torch.cat([d.unsqueeze(-1).view(torch.uint8), m.contiguous().unsqueeze(-1).view(torch.uint8), qs], dim=-1)
+    return rec.reshape(-1), g_idx_map
+
+
+def merge_quantized_qkv(q, k, v):
+    """packed CANONICAL q, k, v (same qtype, same in_features) -> one packed qkv weight: rows are
+    block-contiguous in the canonical layout, so this is a byte concatenation on the CPU side
+    (reference models/common.py:379-413, which also hops through the CPU layout)."""
+    parts = [t.view(torch.uint8) if t.dtype != torch.uint8 else t for t in (q, k, v)]
+    out = torch.cat([p.reshape(-1) for p in parts])
+    return out.view(q.dtype) if q.dtype != torch.uint8 else out

@@ -1,0 +1,71 @@
+"""Host-side conversion logic that needs no GPU: GPTQ -> asym_int4 repacking against the bytes the
+reference's own convert_gptq produced (tests/golden/ref_python_q4.npz, made by make_golden.py), qkv
+merging, scale-search policy, meta-device conversion."""
+import os
+import types
+
+import numpy as np
+import pytest
+import torch
+
+import oracle
+
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+
+
+def test_convert_gptq_matches_reference_bytes(native_lib):
+    from ipex_llm_b200.transformers.convert import convert_gptq
+    g = np.load(os.path.join(GOLD, "ref_python_q4.npz"))
+    ints, zeros, scales = g["gptq_ints"].astype(np.int64), g["gptq_zeros"].astype(np.int64), g["gptq_scales"]
+    in_f, out_f = ints.shape
+    group = in_f // zeros.shape[0]
+    shifts = np.arange(0, 32, 4, dtype=np.int64)
+    qweight = np.zeros((in_f // 8, out_f), dtype=np.int64)
+    for i in range(8):
+        qweight |= ints[i::8, :] << shifts[i]
+    qzeros = np.zeros((zeros.shape[0], out_f // 8), dtype=np.int64)
+    for i in range(8):
+        qzeros |= zeros[:, i::8] << shifts[i]
+    mod = types.SimpleNamespace(scales=torch.from_numpy(scales),
+                                qzeros=torch.from_numpy(qzeros.astype(np.uint32).view(np.int32)),
+                                qweight=torch.from_numpy(qweight.astype(np.uint32).view(np.int32)),
+                                wf=torch.tensor(shifts, dtype=torch.int32).unsqueeze(0), bits=4, group_size=group,
+                                in_features=in_f, g_idx=None)
+    packed, gmap = convert_gptq(mod)
+    assert gmap is None
+    np.testing.assert_array_equal(packed.numpy(), g["gptq_bytes"])
+    # and those records mean GPTQ's weights
+    d = oracle.dequantize(packed.numpy(), (out_f, in_f), "asym_int4")
+    np.testing.assert_allclose(d, g["gptq_weight"], rtol=0, atol=2e-3 * np.abs(g["gptq_weight"]).max())
+
+
+def test_merge_quantized_qkv_is_row_concat(native_lib):
+    from ipex_llm_b200.transformers.convert import merge_quantized_qkv
+    rng = np.random.default_rng(0)
+    q, k, v = [(rng.standard_normal((n, 128)) * 0.02).astype(np.float32) for n in (64, 16, 16)]
+    merged = merge_quantized_qkv(*[torch.from_numpy(oracle.quantize(t, "sym_int4")) for t in (q, k, v)])
+    np.testing.assert_array_equal(merged.numpy(), oracle.quantize(np.concatenate([q, k, v]), "sym_int4"))
+
+
+def test_scale_search_policy_and_meta_conversion(native_lib):
+    from ipex_llm_b200.transformers.convert import use_scale_search, ggml_convert_low_bit
+    from ipex_llm_b200.transformers.low_bit_linear import LowBitLinear
+    cfg = types.SimpleNamespace(model_type="llama", vocab_size=32000, _name_or_path="x")
+    assert use_scale_search(cfg, 29) and use_scale_search(cfg, 15) and not use_scale_search(cfg, 2)
+    assert not use_scale_search(types.SimpleNamespace(model_type="qwen2"), 29)
+    assert not use_scale_search(types.SimpleNamespace(model_type="llama", vocab_size=128256, _name_or_path="Llama-3-Instruct"), 15)
+
+    class Net(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.a = torch.nn.Linear(128, 64)
+            self.odd = torch.nn.Linear(100, 8)          # in_features % 64 != 0: left alone (convert.py:615)
+            self.lm_head = torch.nn.Linear(128, 320, bias=False)
+    with torch.device("meta"):
+        net = Net()
+    net = ggml_convert_low_bit(net, 34, convert_shape_only=True, device="meta", modules_to_not_convert=[])   # woq_int4 alias
+    assert isinstance(net.a, LowBitLinear) and net.a.qtype == 2 and net.a.weight.data.shape == (64 * 2 * 34,)
+    assert isinstance(net.odd, torch.nn.Linear) and not isinstance(net.odd, LowBitLinear)
+    assert net.lm_head.optimize_lm_head and not net.a.optimize_lm_head
+    with pytest.raises(RuntimeError):
+        ggml_convert_low_bit(Net(), 8)                  # sym_int8: not implemented, loud
