@@ -123,6 +123,19 @@ int lowbit_matmul_cuda(const void* d_w, int qtype, int64_t n_rows, int64_t k,
                        void* d_y, int y_dtype, const void* d_bias, int accumulate,
                        void* workspace, size_t workspace_bytes, void* stream);
 
+/* Fused MLP front half: y[M][N] = act(x . Wgate^T) * (x . Wup^T) -- the XPU op
+ * `xe_linear.mlp_forward_xpu(x_2d, gate_w, up_w, M, K, N, act, qtype)` called from fuse_mlp_base
+ * (transformers/models/common.py:146-161; act ids from models/utils.py: SILU 0, GELU 1).
+ * d_w_gate / d_w_up: two [N][K] weights of the SAME qtype in the device layout.  For M <= 8, N a
+ * multiple of 64 and a tensor-core qtype this is ONE kernel launch that streams both matrices once
+ * and never writes the two intermediate vectors; otherwise it runs the two matmuls into fp32
+ * scratch and one elementwise kernel (same result up to fp32 rounding of the intermediates).
+ * workspace: NULL (library-owned) or lowbit_mlp_workspace_size() bytes. */
+size_t lowbit_mlp_workspace_size(int64_t n_rows, int64_t k, int64_t m, int x_dtype);
+int lowbit_mlp_cuda(const void* d_w_gate, const void* d_w_up, int qtype, int64_t n_rows, int64_t k,
+                    const void* d_x, int x_dtype, int64_t m, void* d_y, int y_dtype, int act,
+                    void* workspace, size_t workspace_bytes, void* stream);
+
 /* No counterpart in the reference.  The fp32-activation matmul of lowbit_matmul_cuda, for hosts that
  * cannot give the library memory: an inference server whose arena owns all device memory and bans
  * cudaMalloc after start-up, a process held to a fixed device-memory budget, a thread that must not

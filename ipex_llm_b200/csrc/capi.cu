@@ -191,6 +191,53 @@ int lowbit_matmul_cuda(const void* d_w, int qtype, int64_t n_rows, int64_t k, co
     return rc;
 }
 
+size_t lowbit_mlp_workspace_size(int64_t n_rows, int64_t k, int64_t m, int x_dtype) {
+    const size_t base = (lowbit_matmul_workspace_size(n_rows, k, m, x_dtype) + 255) / 256 * 256;
+    return base + 2 * (size_t)m * n_rows * sizeof(float);
+}
+
+int lowbit_mlp_cuda(const void* d_w_gate, const void* d_w_up, int qtype, int64_t n_rows, int64_t k, const void* d_x,
+                    int x_dtype, int64_t m, void* d_y, int y_dtype, int act, void* workspace, size_t workspace_bytes,
+                    void* stream) {
+    t_launches = 0;
+    if (m == 0 || n_rows == 0) return LB_OK;
+    if (act != 0 && act != 1) { set_error(LB_ERR_ARG, "lowbit_mlp_cuda: act must be 0 (SILU) or 1 (GELU), got %d", act); return LB_ERR_ARG; }
+    if (!d_w_gate || !d_w_up || !d_x || !d_y || m < 0 || n_rows < 0) { set_error(LB_ERR_ARG, "lowbit_mlp_cuda: null pointer or negative size"); return LB_ERR_ARG; }
+    const bool fused = gemv_mlp_fused_supported(qtype, n_rows, k, m);
+    const size_t base = (lowbit_matmul_workspace_size(n_rows, k, m, x_dtype) + 255) / 256 * 256;
+    const size_t need = base + (fused ? 0 : 2 * (size_t)m * n_rows * sizeof(float));
+    std::unique_lock<std::mutex> lk(g_mu, std::defer_lock);
+    if (!workspace) {
+        lk.lock();
+        DevState* S = dev_state();
+        if (!S) { set_error(LB_ERR_NO_DEVICE, "lowbit_mlp_cuda: no CUDA device"); return LB_ERR_NO_DEVICE; }
+        if (need > S->ws.cap) {
+            cudaDeviceSynchronize();
+            int rc = S->ws.ensure(need, true);
+            if (rc) return rc;
+        }
+        workspace = S->ws.p; workspace_bytes = S->ws.cap;
+    } else if (workspace_bytes < need) {
+        set_error(LB_ERR_WORKSPACE, "lowbit_mlp_cuda: workspace too small (%zu < %zu bytes)", workspace_bytes, need);
+        return LB_ERR_WORKSPACE;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    int rc;
+    if (fused) {
+        rc = gemv_launch_ex(d_w_gate, d_w_up, act + 1, qtype, n_rows, k, d_x, x_dtype, m, d_y, y_dtype, nullptr, 0, workspace,
+                            workspace_bytes, st);
+    } else {
+        float* tg = (float*)((char*)workspace + base);
+        float* tu = tg + (size_t)m * n_rows;
+        rc = matmul_dispatch(d_w_gate, qtype, n_rows, k, d_x, x_dtype, m, tg, DT_F32, nullptr, 0, workspace, base, st);
+        if (!rc) rc = matmul_dispatch(d_w_up, qtype, n_rows, k, d_x, x_dtype, m, tu, DT_F32, nullptr, 0, workspace, base, st);
+        if (!rc) rc = act_mul_launch(tg, tu, d_y, y_dtype, m * n_rows, act + 1, st);
+    }
+    if (rc == LB_ERR_ARG) set_error(rc, "lowbit_mlp_cuda: bad argument (qtype %d, N %lld, K %lld, M %lld)", qtype, (long long)n_rows, (long long)k, (long long)m);
+    if (rc == LB_ERR_WORKSPACE) set_error(rc, "lowbit_mlp_cuda: workspace too small (%zu bytes)", workspace_bytes);
+    return rc;
+}
+
 // ------------------------------------------------------------------ family (1)
 size_t ggml_quantize_tensor(const float* src, void* dst, int qtype, size_t n, int k, int64_t* hist,
                             bool scale_search) {

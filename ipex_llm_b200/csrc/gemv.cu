@@ -108,10 +108,37 @@ static void launch_generic(const void* w, const TiledGeom& G, int qt, int64_t r0
                                                         bias, accumulate);
 }
 
+// y = act(g) * u elementwise (the unfused tail of the MLP when the fused GEMV does not apply)
+__global__ void act_mul_kernel(const float* __restrict__ gate, const float* __restrict__ up, void* y, int y_dtype, int64_t n,
+                               int act) {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        store_out(y, y_dtype, i, apply_act(gate[i], act) * up[i], nullptr, 0, 0);
+}
+
+int act_mul_launch(const float* gate, const float* up, void* y, int y_dtype, int64_t n, int act, cudaStream_t st) {
+    int g = (int)((n + 255) / 256); if (g > sm_count() * 8) g = sm_count() * 8;
+    act_mul_kernel<<<g, 256, 0, st>>>(gate, up, y, y_dtype, n, act);
+    note_launch();
+    return check_launch();
+}
+
+bool gemv_mlp_fused_supported(int qt, int64_t n_rows, int64_t k, int64_t m) {
+    qt = canon_qtype(qt);
+    return supported(qt) && has_mma_codec(qt) && n_rows > 0 && n_rows % RG_ROWS == 0 && k > 0 && k % QK == 0 && m >= 1 && m <= 8;
+}
+
 int gemv_launch(const void* w, int qt, int64_t n_rows, int64_t k, const void* x, int x_dtype, int64_t m,
                 void* y, int y_dtype, const void* bias, int accumulate, void* workspace,
                 size_t workspace_bytes, cudaStream_t st) {
+    return gemv_launch_ex(w, nullptr, 0, qt, n_rows, k, x, x_dtype, m, y, y_dtype, bias, accumulate, workspace, workspace_bytes, st);
+}
+
+// w2 != NULL: y = act(x . w^T) * (x . w2^T) in one launch (caller checked gemv_mlp_fused_supported)
+int gemv_launch_ex(const void* w, const void* w2, int act, int qt, int64_t n_rows, int64_t k, const void* x, int x_dtype,
+                   int64_t m, void* y, int y_dtype, const void* bias, int accumulate, void* workspace,
+                   size_t workspace_bytes, cudaStream_t st) {
     qt = canon_qtype(qt);
+    if (w2 && (!gemv_mlp_fused_supported(qt, n_rows, k, m) || ((uintptr_t)w2 & 15) || bias || accumulate)) return LB_ERR_ARG;
     if (!supported(qt) || k <= 0 || k % QK || n_rows <= 0 || m <= 0) return LB_ERR_ARG;
     if (x_dtype < 0 || x_dtype > 2 || y_dtype < 0 || y_dtype > 2) return LB_ERR_ARG;
     if (((uintptr_t)w & 15) || ((uintptr_t)x & 15)) return LB_ERR_ARG;        // TMA bulk / 128-bit loads
@@ -126,7 +153,7 @@ int gemv_launch(const void* w, int qt, int64_t n_rows, int64_t k, const void* x,
         int64_t mma_rows = has_mma_codec(qt) ? G.r64 : 0;
         if (mma_rows > 0) {
             GemvArgs A;
-            A.w = (const uint8_t*)w; A.G = G; A.M = (int)mc;
+            A.w = (const uint8_t*)w; A.w2 = (const uint8_t*)w2; A.act = act; A.G = G; A.M = (int)mc;
             A.y = yc; A.y_dtype = y_dtype; A.bias = bias; A.accumulate = accumulate;
             A.plane_stride = mc * k;
             A.pdl = g_pdl; A.ts = g_ts;

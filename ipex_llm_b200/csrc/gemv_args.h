@@ -9,8 +9,19 @@ constexpr int GEMV_WARPS = 4;              // warps per CTA (each warp is an ind
 constexpr int GEMV_MAX_SPLIT = 8;           // CTAs per cluster = K slices of one 64-row group
 constexpr int GEMV_MAX_NT = 4;             // n-tiles of 8 activation rows -> M <= 32 per pass
 
+// activation of the fused MLP (reference xe_linear.mlp_forward_xpu act ids: SILU 0 / GELU 1 are
+// mapped by the host to 1 / 2 here; 0 = identity).  expf, not __expf: the result must not depend
+// on fast-math flags.
+__device__ __forceinline__ float apply_act(float v, int act) {
+    if (act == 1) return v / (1.0f + expf(-v));                                    // SiLU
+    if (act == 2) return 0.5f * v * (1.0f + erff(v * 0.70710678118654752f));       // GELU (erf)
+    return v;
+}
+
 struct GemvArgs {
     const uint8_t* w;
+    const uint8_t* w2;        // second matrix of the fused MLP (same shape / qtype) or NULL
+    int act;                  // fused MLP activation on w's output: 1 SiLU, 2 GELU(erf)
     TiledGeom G;
     const uint16_t* x;        // NS planes of [M][K] fp16 or bf16
     int64_t plane_stride;     // elements between planes

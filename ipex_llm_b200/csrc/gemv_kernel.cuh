@@ -225,8 +225,8 @@ template <int QT, bool BF> struct Staging {
     static constexpr int kBarBytes = GEMV_WARPS * kStages * 8 + 8;                // + the leader's receive barrier
     // + the leader CTA's receive buffer for its peers' CTA sums (push reduction, M <= 8 kernels):
     // (split-1) x NV x 32 floats
-    static constexpr int smem_bytes(int nt, int acc) {
-        return GEMV_WARPS * kWarpBytes + kBarBytes + 8 + (nt == 1 ? (GEMV_MAX_SPLIT - 1) * (RG_TILES * acc) * 128 : 0);
+    static constexpr int smem_bytes(int nt, int acc, int nm) {
+        return GEMV_WARPS * kWarpBytes + kBarBytes + 8 + (nt == 1 ? (GEMV_MAX_SPLIT - 1) * (nm * RG_TILES * acc) * 128 : 0);
     }
 };
 
@@ -257,7 +257,10 @@ __device__ __forceinline__ float ld_dsmem_f32(uint32_t local_addr, uint32_t rank
 // ACC = accumulators per (row tile, n-tile): 4 (c0..c3), or 2 when M == 1 (only column 0 is live:
 // c0 = row g, c2 = row g+8).
 // grid = (S, groups): blockIdx.y = 64-row group, blockIdx.x = K slice = rank in the cluster (S,1,1).
-template <int QT, bool BF, int NS, int NT, int ACC>
+// NM = 2 is the fused MLP (reference fuse_mlp_base, models/common.py:146-161: xe_linear.mlp_forward_xpu):
+// the same rows of a second matrix (A.w2, "up") are streamed after the first ("gate") and the epilogue
+// stores act(gate . x) * (up . x).
+template <int QT, bool BF, int NS, int NT, int ACC, int NM>
 __global__ void __launch_bounds__(GEMV_WARPS * 32)
 gemv_kernel(const GemvArgs A) {
     using C = Codec<QT, BF>;
@@ -265,8 +268,9 @@ gemv_kernel(const GemvArgs A) {
     using Tile = typename C::Tile;
     constexpr int CH = S::kChunk, STAGES = S::kStages, STAGE_BYTES = S::kStageBytes;
     constexpr int SUPER = S::kSuperCodes;
-    constexpr int NV = RG_TILES * NT * ACC;            // accumulator floats per lane
-    static_assert(NV * 128 <= S::kWarpBytes, "reduction slot must fit in the warp's ring");
+    constexpr int NV = RG_TILES * NT * ACC;            // accumulator floats per lane and matrix
+    constexpr int NVT = NM * NV;
+    static_assert(NVT * 128 <= S::kWarpBytes, "reduction slot must fit in the warp's ring");
     extern __shared__ __align__(128) uint8_t smem[];
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -288,18 +292,19 @@ gemv_kernel(const GemvArgs A) {
     // this warp's private ring: [STAGES][codes | scales | mins]; the mbarriers sit after all rings
     const uint32_t ring = smem_u32(smem) + warp * S::kWarpBytes;
     const uint32_t bars = smem_u32(smem) + GEMV_WARPS * S::kWarpBytes + warp * (STAGES * 8);
-    const uint8_t* gq = A.w + u0 * SUPER;
-    const uint8_t* gs = A.w + A.G.off_s + u0 * 128;
-    const uint8_t* gm = A.w + A.G.off_m + u0 * 128;
+    const int total_chunks = NM * n_chunks;            // the ring runs through matrix 0, then matrix 1
 
-    auto issue = [&](int c) {                         // lane 0: copy chunk c into stage c % STAGES
+    auto issue = [&](int c) {                         // one lane: copy global chunk c into stage c % STAGES
         const int st = c % STAGES;
-        const int ns = min(CH, n_super - c * CH);
+        const int mat = (NM == 2 && c >= n_chunks) ? 1 : 0;
+        const int lc = c - mat * n_chunks;
+        const uint8_t* wb = mat ? A.w2 : A.w;
+        const int ns = min(CH, n_super - lc * CH);
         const uint32_t dst = ring + st * STAGE_BYTES, bar = bars + st * 8;
         mbar_expect_tx(bar, ns * (SUPER + 128 + S::kMinBytes));
-        bulk_g2s(dst, gq + (size_t)c * (CH * SUPER), ns * SUPER, bar);
-        bulk_g2s(dst + CH * SUPER, gs + (size_t)c * (CH * 128), ns * 128, bar);
-        if (S::kMinBytes) bulk_g2s(dst + CH * (SUPER + 128), gm + (size_t)c * (CH * 128), ns * 128, bar);
+        bulk_g2s(dst, wb + (u0 + (int64_t)lc * CH) * SUPER, ns * SUPER, bar);
+        bulk_g2s(dst + CH * SUPER, wb + A.G.off_s + (u0 + (int64_t)lc * CH) * 128, ns * 128, bar);
+        if (S::kMinBytes) bulk_g2s(dst + CH * (SUPER + 128), wb + A.G.off_m + (u0 + (int64_t)lc * CH) * 128, ns * 128, bar);
     };
 
     constexpr bool PUSH = (NT == 1);                   // peers push their sums into the leader (else the leader pulls)
@@ -314,7 +319,7 @@ gemv_kernel(const GemvArgs A) {
     }
     // lane s owns stage s during start-up (the barrier inits and first copies go out in parallel);
     // weights do not depend on the previous kernel: they start streaming before the PDL wait
-    if (lane < STAGES && lane < n_chunks) {
+    if (lane < STAGES && lane < total_chunks) {
         mbar_init(bars + lane * 8, 1);
         // make the init visible to the async proxy (the TMA engine completes bytes on this barrier);
         // the cluster-scoped fence.mbarrier_init costs ~1 us here (it also invalidates L1)
@@ -340,13 +345,15 @@ gemv_kernel(const GemvArgs A) {
     if (A.pdl) asm volatile("griddepcontrol.wait;" ::: "memory");
     TS(2);
 
-    float acc[RG_TILES][NT][ACC];
+    float accm[NM][RG_TILES][NT][ACC];
 #pragma unroll
-    for (int r = 0; r < RG_TILES; r++)
+    for (int mt = 0; mt < NM; mt++)
 #pragma unroll
-        for (int j = 0; j < NT; j++)
+        for (int r = 0; r < RG_TILES; r++)
 #pragma unroll
-            for (int c = 0; c < ACC; c++) acc[r][j][c] = 0.0f;
+            for (int j = 0; j < NT; j++)
+#pragma unroll
+                for (int c = 0; c < ACC; c++) accm[mt][r][j][c] = 0.0f;
 
     // lane (g,t) reads x[8j+g][kb*64 + 16t .. +15] for n-tile j (plane p); rows >= M read as zero
     const char* xptr[NT][NS];
@@ -367,10 +374,15 @@ gemv_kernel(const GemvArgs A) {
     uint32_t ones[4];
     ones[0] = ones[1] = ones[2] = ones[3] = BF ? 0x3f803f80u : 0x3c003c00u;
 
-    for (int c = 0; c < n_chunks; c++) {
+#pragma unroll
+    for (int mt = 0; mt < NM; mt++) {
+    float (&acc)[RG_TILES][NT][ACC] = accm[mt];
+    xoff = 0;
+    for (int lc = 0; lc < n_chunks; lc++) {
+        const int c = mt * n_chunks + lc;
         const int st = c % STAGES;
         const uint32_t stage = ring + st * STAGE_BYTES;
-        const int ns = min(CH, n_super - c * CH);
+        const int ns = min(CH, n_super - lc * CH);
         mbar_wait(bars + st * 8, (uint32_t)((c / STAGES) & 1));
         if (c == 0) TS(3);
 #pragma unroll
@@ -462,7 +474,8 @@ gemv_kernel(const GemvArgs A) {
         }
         // every lane has consumed the stage (its data sits in registers already used): refill it
         __syncwarp();
-        if (lane == 0 && c + STAGES < n_chunks) issue(c + STAGES);
+        if (lane == 0 && c + STAGES < total_chunks) issue(c + STAGES);
+    }
     }
     TS(4);
 
@@ -470,15 +483,17 @@ gemv_kernel(const GemvArgs A) {
     // 1) every warp parks its fragment in its own (now idle) ring
     float* slot = reinterpret_cast<float*>(smem + warp * S::kWarpBytes);
 #pragma unroll
-    for (int r = 0; r < RG_TILES; r++)
+    for (int mt = 0; mt < NM; mt++)
 #pragma unroll
-        for (int j = 0; j < NT; j++)
+        for (int r = 0; r < RG_TILES; r++)
 #pragma unroll
-            for (int c = 0; c < ACC; c++) slot[((r * NT + j) * ACC + c) * 32 + lane] = acc[r][j][c];
+            for (int j = 0; j < NT; j++)
+#pragma unroll
+                for (int c = 0; c < ACC; c++) slot[(mt * NV + (r * NT + j) * ACC + c) * 32 + lane] = accm[mt][r][j][c];
     __syncthreads();
     // 2) the CTA's sum lands in warp 0's slot (fixed warp order)
     float* cta = reinterpret_cast<float*>(smem);
-    for (int i = threadIdx.x; i < NV * 32; i += GEMV_WARPS * 32) {
+    for (int i = threadIdx.x; i < NVT * 32; i += GEMV_WARPS * 32) {
         float v = cta[i];
 #pragma unroll
         for (int w = 1; w < GEMV_WARPS; w++) v += reinterpret_cast<const float*>(smem + w * S::kWarpBytes)[i];
@@ -498,35 +513,55 @@ gemv_kernel(const GemvArgs A) {
         if (col < A.M && (ACC != 2 || tt == 0))
             store_out(A.y, A.y_dtype, (int64_t)col * N + row, v, A.bias, row, A.accumulate);
     };
+    // value i of matrix mt lives at float index mt*NV*32 + i; NV*32 is a multiple of the block size, so the
+    // thread that owns i owns it for both matrices and can apply act(gate) * up itself
+    auto finish = [&](int i, const float (&vm)[NM]) {
+        store_value(i, NM == 2 ? apply_act(vm[0], A.act) * vm[NM - 1] : vm[0]);
+    };
     if (nsplit == 1) {
-        for (int i = threadIdx.x; i < NV * 32; i += GEMV_WARPS * 32) store_value(i, cta[i]);
+        for (int i = threadIdx.x; i < NV * 32; i += GEMV_WARPS * 32) {
+            float vm[NM];
+#pragma unroll
+            for (int mt = 0; mt < NM; mt++) vm[mt] = cta[mt * NV * 32 + i];
+            finish(i, vm);
+        }
     } else if (PUSH) {
         asm volatile("barrier.cluster.wait.aligned;" ::: "memory");   // the leader's barrier init is visible
         if (slice != 0) {
             const uint32_t rb = map_to_rank(rbar, 0);
-            for (int i = threadIdx.x; i < NV * 32; i += GEMV_WARPS * 32)
-                st_async_f32(map_to_rank(smem_u32(recv + (slice - 1) * (NV * 32) + i), 0), cta[i], rb);
+            for (int i = threadIdx.x; i < NVT * 32; i += GEMV_WARPS * 32)
+                st_async_f32(map_to_rank(smem_u32(recv + (slice - 1) * (NVT * 32) + i), 0), cta[i], rb);
         } else {
-            if (threadIdx.x == 0) mbar_expect_tx(rbar, (uint32_t)((nsplit - 1) * NV * 32 * 4));
+            if (threadIdx.x == 0) mbar_expect_tx(rbar, (uint32_t)((nsplit - 1) * NVT * 32 * 4));
             mbar_wait(rbar, 0);
             for (int i = threadIdx.x; i < NV * 32; i += GEMV_WARPS * 32) {
-                float v = cta[i];
-                for (int rk = 1; rk < nsplit; rk++) v += recv[(rk - 1) * (NV * 32) + i];
-                store_value(i, v);
+                float vm[NM];
+#pragma unroll
+                for (int mt = 0; mt < NM; mt++) {
+                    float v = cta[mt * NV * 32 + i];
+                    for (int rk = 1; rk < nsplit; rk++) v += recv[(rk - 1) * (NVT * 32) + mt * NV * 32 + i];
+                    vm[mt] = v;
+                }
+                finish(i, vm);
             }
         }
     } else {
         cluster_sync_all();
         if (slice == 0) {
             for (int i = threadIdx.x; i < NV * 32; i += GEMV_WARPS * 32) {
-                float pv[GEMV_MAX_SPLIT - 1];
+                float vm[NM];
 #pragma unroll
-                for (int rk = 1; rk < GEMV_MAX_SPLIT; rk++)      // all remote loads in flight before the adds
-                    pv[rk - 1] = rk < nsplit ? ld_dsmem_f32(smem_u32(cta + i), (uint32_t)rk) : 0.0f;
-                float v = cta[i];
+                for (int mt = 0; mt < NM; mt++) {
+                    float pv[GEMV_MAX_SPLIT - 1];
 #pragma unroll
-                for (int rk = 1; rk < GEMV_MAX_SPLIT; rk++) v += pv[rk - 1];
-                store_value(i, v);
+                    for (int rk = 1; rk < GEMV_MAX_SPLIT; rk++)      // all remote loads in flight before the adds
+                        pv[rk - 1] = rk < nsplit ? ld_dsmem_f32(smem_u32(cta + mt * NV * 32 + i), (uint32_t)rk) : 0.0f;
+                    float v = cta[mt * NV * 32 + i];
+#pragma unroll
+                    for (int rk = 1; rk < GEMV_MAX_SPLIT; rk++) v += pv[rk - 1];
+                    vm[mt] = v;
+                }
+                finish(i, vm);
             }
         }
         cluster_sync_all();                                      // peers' smem must outlive the reads
@@ -597,19 +632,26 @@ template <int QT, bool BF, int NS>
 static void launch_nt(int m, int64_t groups, int64_t nb, const GemvArgs& A, cudaStream_t st) {
     using SG = Staging<QT, BF>;
     static bool configured = false;     // per instantiation: raise the dynamic shared memory limit once
-    static int cache[4][8];
-    if (!configured) for (auto& row : cache) for (int& v : row) v = -1;
+    static int cache[6][8];
     if (!configured) {
-        cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 1, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, SG::smem_bytes(1, 2));
-        cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 1, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, SG::smem_bytes(1, 4));
-        cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 2, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, SG::smem_bytes(2, 4));
-        cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 4, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, SG::smem_bytes(4, 4));
+        for (auto& row : cache) for (int& v : row) v = -1;
+        cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 1, 2, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, SG::smem_bytes(1, 2, 1));
+        cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 1, 4, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, SG::smem_bytes(1, 4, 1));
+        cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 2, 4, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, SG::smem_bytes(2, 4, 1));
+        cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 4, 4, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, SG::smem_bytes(4, 4, 1));
+        cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 1, 2, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, SG::smem_bytes(1, 2, 2));
+        cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 1, 4, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, SG::smem_bytes(1, 4, 2));
         configured = true;
     }
-    if (m == 1) launch_kernel(gemv_kernel<QT, BF, NS, 1, 2>, SG::smem_bytes(1, 2), groups, nb, A, st, cache[0]);
-    else if (m <= 8) launch_kernel(gemv_kernel<QT, BF, NS, 1, 4>, SG::smem_bytes(1, 4), groups, nb, A, st, cache[1]);
-    else if (m <= 16) launch_kernel(gemv_kernel<QT, BF, NS, 2, 4>, SG::smem_bytes(2, 4), groups, nb, A, st, cache[2]);
-    else launch_kernel(gemv_kernel<QT, BF, NS, 4, 4>, SG::smem_bytes(4, 4), groups, nb, A, st, cache[3]);
+    if (A.w2) {                          // fused MLP: M <= 8 only (the host falls back otherwise)
+        if (m == 1) launch_kernel(gemv_kernel<QT, BF, NS, 1, 2, 2>, SG::smem_bytes(1, 2, 2), groups, nb, A, st, cache[4]);
+        else launch_kernel(gemv_kernel<QT, BF, NS, 1, 4, 2>, SG::smem_bytes(1, 4, 2), groups, nb, A, st, cache[5]);
+        return;
+    }
+    if (m == 1) launch_kernel(gemv_kernel<QT, BF, NS, 1, 2, 1>, SG::smem_bytes(1, 2, 1), groups, nb, A, st, cache[0]);
+    else if (m <= 8) launch_kernel(gemv_kernel<QT, BF, NS, 1, 4, 1>, SG::smem_bytes(1, 4, 1), groups, nb, A, st, cache[1]);
+    else if (m <= 16) launch_kernel(gemv_kernel<QT, BF, NS, 2, 4, 1>, SG::smem_bytes(2, 4, 1), groups, nb, A, st, cache[2]);
+    else launch_kernel(gemv_kernel<QT, BF, NS, 4, 4, 1>, SG::smem_bytes(4, 4, 1), groups, nb, A, st, cache[3]);
 }
 template <int QT>
 static void launch_qt(int x_dtype, int m, int64_t groups, int64_t nb, const GemvArgs& A, cudaStream_t st) {

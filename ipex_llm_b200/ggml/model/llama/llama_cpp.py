@@ -197,6 +197,24 @@ def lowbit_matmul_cuda(d_w, qtype, n_rows, k, d_x, x_dtype, m, d_y, y_dtype, d_b
            "lowbit_matmul_cuda")
 
 
+_lib.lowbit_mlp_workspace_size.argtypes = [ctypes.c_int64, ctypes.c_int64, ctypes.c_int64, ctypes.c_int]
+_lib.lowbit_mlp_workspace_size.restype = ctypes.c_size_t
+_lib.lowbit_mlp_cuda.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_int64,
+                                 ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_void_p, ctypes.c_int,
+                                 ctypes.c_int, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p]
+_lib.lowbit_mlp_cuda.restype = ctypes.c_int
+
+
+def lowbit_mlp_workspace_size(n_rows, k, m, x_dtype):
+    return _lib.lowbit_mlp_workspace_size(n_rows, k, m, x_dtype)
+
+
+def lowbit_mlp_cuda(d_w_gate, d_w_up, qtype, n_rows, k, d_x, x_dtype, m, d_y, y_dtype, act, workspace,
+                    workspace_bytes, stream):
+    _check(_lib.lowbit_mlp_cuda(d_w_gate, d_w_up, qtype, n_rows, k, d_x, x_dtype, m, d_y, y_dtype, act,
+                                workspace, workspace_bytes, stream), "lowbit_mlp_cuda")
+
+
 _lib.lowbit_set_programmatic_dependent_launch.argtypes = [ctypes.c_int]
 _lib.lowbit_set_programmatic_dependent_launch.restype = None
 

@@ -258,6 +258,37 @@ def lowbit_matmul(x_2d: torch.Tensor, weight: torch.Tensor, weight_shape, qtype:
     return out
 
 
+SILU = 0     # activation ids of the reference (transformers/models/utils.py: SILU / GELU)
+GELU = 1
+
+
+def mlp_forward(x_2d: torch.Tensor, gate_weight: torch.Tensor, up_weight: torch.Tensor, M: int, K: int, N: int,
+                act: int, qtype: int, out: torch.Tensor = None):
+    """``xe_linear.mlp_forward_xpu(x_2d, gate_w, up_w, M, K, N, act, qtype)`` (models/common.py:146-161):
+    act(x . Wgate^T) * (x . Wup^T) -> [M, N] in the activation dtype.  Both weights are [N, K]
+    in the tiled device layout; at decode sizes (M <= 8) one kernel streams both matrices."""
+    invalidInputError(x_2d.dtype in _TORCH_TO_DT, f"unsupported activation dtype {x_2d.dtype}")
+    invalidInputError(tuple(x_2d.shape) == (M, K), f"activation shape {tuple(x_2d.shape)} != ({M}, {K})")
+    invalidInputError(act in (SILU, GELU), f"unknown activation id {act}")
+    invalidInputError(gate_weight.numel() * gate_weight.element_size() == up_weight.numel() * up_weight.element_size(),
+                      "gate and up weights must have the same packed size")
+    x_2d = x_2d.contiguous()
+    if out is None:
+        out = torch.empty((M, N), dtype=x_2d.dtype, device=x_2d.device)
+    if M == 0:
+        return out
+    dev = x_2d.device
+    dt = _TORCH_TO_DT[x_2d.dtype]
+    ws = _get_workspace(dev, ggml.lowbit_mlp_workspace_size(N, K, M, dt))
+    g = gate_weight.view(torch.uint8) if gate_weight.dtype != torch.uint8 else gate_weight
+    u = up_weight.view(torch.uint8) if up_weight.dtype != torch.uint8 else up_weight
+    with torch.cuda.device(dev):
+        ggml.lowbit_mlp_cuda(ctypes.c_void_p(g.data_ptr()), ctypes.c_void_p(u.data_ptr()), qtype, N, K,
+                             ctypes.c_void_p(x_2d.data_ptr()), dt, M, ctypes.c_void_p(out.data_ptr()),
+                             _TORCH_TO_DT[out.dtype], act, ctypes.c_void_p(ws.data_ptr()), ws.numel(), _stream_ptr(dev))
+    return out
+
+
 def ggml_matmul_src1_x_src0_t(src0: torch.Tensor, src1: torch.Tensor, src0_shape: torch.Size, src0_qtype: int):
     """LBL:494-529: result[M,N] = src1[M,K] . W[N,K]^T with W = canonical packed blocks on the
     CPU; fp32 in, fp32 out, one call across the reference C ABI (which runs on the GPU here)."""
