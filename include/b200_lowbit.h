@@ -136,6 +136,27 @@ int lowbit_mlp_cuda(const void* d_w_gate, const void* d_w_up, int qtype, int64_t
                     const void* d_x, int x_dtype, int64_t m, void* d_y, int y_dtype, int act,
                     void* workspace, size_t workspace_bytes, void* stream);
 
+/* One-token mixture-of-experts MLP -- the XPU op `xe_linear.moe_forward_vec(x, topk_ids, topk_weight,
+ * gates, ups, downs, hidden, intermediate, qtype)` (transformers/models/qwen3_moe.py:88-105,
+ * deepseek.py:296-312):  y[hidden] (+)= sum_z weight[z] * Wdown[e_z] . (act(Wgate[e_z] . x) * (Wup[e_z] . x)),
+ * e_z = topk_ids[z].  d_gates / d_ups / d_downs: DEVICE arrays of n_experts 64-bit device addresses
+ * (what the reference builds from `expert.*_proj.weight.data_ptr()`), each pointing at a weight of
+ * `qtype` in the device layout ([inter][hidden] for gate/up, [hidden][inter] for down).  topk ids are
+ * read on the device (ids_dtype 0 = int32, 1 = int64), so the call needs no host synchronisation and
+ * can be recorded in a CUDA graph; an id outside [0, n_experts) contributes zero.  Two launches:
+ * all routed gate/up pairs, then ONE GEMV over the routed down projections concatenated along K
+ * (deterministic: no atomics).  Requires a tensor-core qtype and hidden, inter multiples of 64
+ * (lowbit_moe_supported() says so); act as in lowbit_mlp_cuda.
+ * workspace: NULL (library-owned) or lowbit_moe_workspace_size() bytes, 256-byte aligned. */
+int lowbit_moe_supported(int qtype, int64_t hidden, int64_t inter, int top_k);
+size_t lowbit_moe_workspace_size(int64_t hidden, int64_t inter, int top_k, int x_dtype);
+int lowbit_moe_cuda(const void* d_x, int x_dtype, const void* d_topk_ids, int ids_dtype,
+                    const void* d_topk_weight, int weight_dtype, int top_k,
+                    const uint64_t* d_gates, const uint64_t* d_ups, const uint64_t* d_downs, int n_experts,
+                    int64_t hidden, int64_t inter, int qtype, int act,
+                    void* d_y, int y_dtype, int accumulate,
+                    void* workspace, size_t workspace_bytes, void* stream);
+
 /* No counterpart in the reference.  The fp32-activation matmul of lowbit_matmul_cuda, for hosts that
  * cannot give the library memory: an inference server whose arena owns all device memory and bans
  * cudaMalloc after start-up, a process held to a fixed device-memory budget, a thread that must not

@@ -238,6 +238,54 @@ int lowbit_mlp_cuda(const void* d_w_gate, const void* d_w_up, int qtype, int64_t
     return rc;
 }
 
+int lowbit_moe_supported(int qtype, int64_t hidden, int64_t inter, int top_k) {
+    return moe_supported(qtype, hidden, inter, top_k) ? 1 : 0;
+}
+
+size_t lowbit_moe_workspace_size(int64_t hidden, int64_t inter, int top_k, int x_dtype) {
+    return moe_workspace_size(hidden, inter, top_k, x_dtype);
+}
+
+int lowbit_moe_cuda(const void* d_x, int x_dtype, const void* d_topk_ids, int ids_dtype, const void* d_topk_weight,
+                    int weight_dtype, int top_k, const uint64_t* d_gates, const uint64_t* d_ups, const uint64_t* d_downs,
+                    int n_experts, int64_t hidden, int64_t inter, int qtype, int act, void* d_y, int y_dtype, int accumulate,
+                    void* workspace, size_t workspace_bytes, void* stream) {
+    t_launches = 0;
+    if (!d_x || !d_topk_ids || !d_topk_weight || !d_gates || !d_ups || !d_downs || !d_y || n_experts <= 0 ||
+        (ids_dtype != 0 && ids_dtype != 1) || (act != 0 && act != 1)) {
+        set_error(LB_ERR_ARG, "lowbit_moe_cuda: null pointer, bad ids_dtype / act or n_experts <= 0");
+        return LB_ERR_ARG;
+    }
+    if (!moe_supported(qtype, hidden, inter, top_k)) {
+        set_error(LB_ERR_ARG, "lowbit_moe_cuda: unsupported problem (qtype %d, hidden %lld, inter %lld, top_k %d)", qtype,
+                  (long long)hidden, (long long)inter, top_k);
+        return LB_ERR_ARG;
+    }
+    const size_t need = moe_workspace_size(hidden, inter, top_k, x_dtype);
+    std::unique_lock<std::mutex> lk(g_mu, std::defer_lock);
+    if (!workspace) {
+        lk.lock();
+        DevState* S = dev_state();
+        if (!S) { set_error(LB_ERR_NO_DEVICE, "lowbit_moe_cuda: no CUDA device"); return LB_ERR_NO_DEVICE; }
+        if (need > S->ws.cap) {
+            cudaDeviceSynchronize();
+            int rc = S->ws.ensure(need, true);
+            if (rc) return rc;
+        }
+        workspace = S->ws.p; workspace_bytes = S->ws.cap;
+    }
+    MoeParams P;
+    P.x = d_x; P.x_dtype = x_dtype; P.ids = d_topk_ids; P.ids_i64 = ids_dtype; P.weights = d_topk_weight; P.w_dtype = weight_dtype;
+    P.top_k = top_k; P.gates = (const unsigned long long*)d_gates; P.ups = (const unsigned long long*)d_ups;
+    P.downs = (const unsigned long long*)d_downs; P.n_experts = n_experts; P.hidden = hidden; P.inter = inter;
+    P.qtype = qtype; P.act = act + 1; P.y = d_y; P.y_dtype = y_dtype; P.accumulate = accumulate;
+    P.workspace = workspace; P.workspace_bytes = workspace_bytes;
+    int rc = moe_launch(P, (cudaStream_t)stream);
+    if (rc == LB_ERR_ARG) set_error(rc, "lowbit_moe_cuda: bad argument (dtype codes or alignment)");
+    if (rc == LB_ERR_WORKSPACE) set_error(rc, "lowbit_moe_cuda: workspace too small (%zu < %zu bytes)", workspace_bytes, need);
+    return rc;
+}
+
 // ------------------------------------------------------------------ family (1)
 size_t ggml_quantize_tensor(const float* src, void* dst, int qtype, size_t n, int k, int64_t* hist,
                             bool scale_search) {

@@ -152,7 +152,7 @@ int gemv_launch_ex(const void* w, const void* w2, int act, int qt, int64_t n_row
         char* yc = (char*)y + (size_t)mb * n_rows * esz_y;
         int64_t mma_rows = has_mma_codec(qt) ? G.r64 : 0;
         if (mma_rows > 0) {
-            GemvArgs A;
+            GemvArgs A = {};
             A.w = (const uint8_t*)w; A.w2 = (const uint8_t*)w2; A.act = act; A.G = G; A.M = (int)mc;
             A.y = yc; A.y_dtype = y_dtype; A.bias = bias; A.accumulate = accumulate;
             A.plane_stride = mc * k;
@@ -187,6 +187,80 @@ int gemv_launch_ex(const void* w, const void* w2, int act, int qt, int64_t n_row
             note_launch();
         }
     }
+    return check_launch();
+}
+
+// ------------------------------------------------------------------ mixture-of-experts decode (one token)
+static int launch_by_qt(int qt, int x_dtype, int m, int64_t groups, int64_t nb, const GemvArgs& A, cudaStream_t st) {
+    switch (qt) {
+        case QT_SYM_INT4:  gemv_launch_sym_int4(x_dtype, m, groups, nb, A, st); break;
+        case QT_ASYM_INT4: gemv_launch_asym_int4(x_dtype, m, groups, nb, A, st); break;
+        case QT_FP8_E4M3:  gemv_launch_fp8_e4m3(x_dtype, m, groups, nb, A, st); break;
+        case QT_FP8_E5M2:  gemv_launch_fp8_e5m2(x_dtype, m, groups, nb, A, st); break;
+        case QT_FP6:       gemv_launch_fp6(x_dtype, m, groups, nb, A, st); break;
+        default: return LB_ERR_ARG;
+    }
+    note_launch();
+    return LB_OK;
+}
+
+bool moe_supported(int qt, int64_t hidden, int64_t inter, int top_k) {
+    qt = canon_qtype(qt);
+    return supported(qt) && has_mma_codec(qt) && hidden > 0 && inter > 0 && hidden % RG_ROWS == 0 && inter % RG_ROWS == 0 &&
+           top_k >= 1 && top_k <= 1024;
+}
+
+// [planes of x | routed intermediates | planes of the intermediates]; the planes only for fp32 activations
+size_t moe_workspace_size(int64_t hidden, int64_t inter, int top_k, int x_dtype) {
+    const size_t esz = x_dtype == DT_F32 ? 4 : 2;
+    size_t n = align_up((size_t)top_k * inter * esz, 256);
+    if (x_dtype == DT_F32) n += align_up((size_t)3 * hidden * 2, 256) + align_up((size_t)3 * top_k * inter * 2, 256);
+    return n;
+}
+
+static void split_planes(const float* x, __nv_bfloat16* planes, int64_t n, cudaStream_t st) {
+    int sg = (int)((n + 255) / 256); if (sg > sm_count() * 8) sg = sm_count() * 8;
+    split_f32_kernel<<<sg, 256, 0, st>>>(x, planes, n);
+    note_launch();
+}
+
+int moe_launch(const MoeParams& P, cudaStream_t st) {
+    const int qt = canon_qtype(P.qtype);
+    if (!moe_supported(qt, P.hidden, P.inter, P.top_k)) return LB_ERR_ARG;
+    if (P.x_dtype < 0 || P.x_dtype > 2 || P.y_dtype < 0 || P.y_dtype > 2 || P.w_dtype < 0 || P.w_dtype > 2) return LB_ERR_ARG;
+    if (((uintptr_t)P.x & 15) || ((uintptr_t)P.workspace & 255)) return LB_ERR_ARG;
+    if (!P.workspace || P.workspace_bytes < moe_workspace_size(P.hidden, P.inter, P.top_k, P.x_dtype)) return LB_ERR_WORKSPACE;
+    const bool f32 = P.x_dtype == DT_F32;
+    const size_t esz = f32 ? 4 : 2;
+    char* ws = (char*)P.workspace;
+    char* inter_buf = ws;
+    char* planes1 = ws + align_up((size_t)P.top_k * P.inter * esz, 256);
+    char* planes2 = planes1 + align_up((size_t)3 * P.hidden * 2, 256);
+
+    // launch 1: h[z] = act(x . Wgate[e_z]^T) * (x . Wup[e_z]^T) for every routed slot z
+    GemvArgs A = {};
+    A.mode = 1; A.M = 1; A.act = P.act;
+    A.G = make_geom(P.inter, P.hidden, qt);
+    A.tab_w = P.gates; A.tab_w2 = P.ups; A.sel = P.ids; A.sel_i64 = P.ids_i64; A.n_experts = P.n_experts; A.n_seg = P.top_k;
+    A.y = inter_buf; A.y_dtype = P.x_dtype;
+    A.plane_stride = P.hidden; A.pdl = g_pdl; A.ts = nullptr;
+    if (f32) { split_planes((const float*)P.x, (__nv_bfloat16*)planes1, P.hidden, st); A.x = (const uint16_t*)planes1; }
+    else A.x = (const uint16_t*)P.x;
+    int rc = launch_by_qt(qt, P.x_dtype, 1, A.G.r64 / RG_ROWS, A.G.nb, A, st);
+    if (rc) return rc;
+
+    // launch 2: y (+)= sum_z weight[z] * (h[z] . Wdown[e_z]^T): one GEMV over the concatenated K axis
+    GemvArgs B = {};
+    B.mode = 2; B.M = 1;
+    B.G = make_geom(P.hidden, P.inter, qt);
+    B.tab_w = P.downs; B.sel = P.ids; B.sel_i64 = P.ids_i64; B.n_experts = P.n_experts; B.n_seg = P.top_k;
+    B.seg_scale = P.weights; B.seg_scale_dtype = P.w_dtype;
+    B.y = P.y; B.y_dtype = P.y_dtype; B.accumulate = P.accumulate;
+    B.plane_stride = (int64_t)P.top_k * P.inter; B.pdl = g_pdl;
+    if (f32) { split_planes((const float*)inter_buf, (__nv_bfloat16*)planes2, (int64_t)P.top_k * P.inter, st); B.x = (const uint16_t*)planes2; }
+    else B.x = (const uint16_t*)inter_buf;
+    rc = launch_by_qt(qt, P.x_dtype, 1, B.G.r64 / RG_ROWS, B.G.nb, B, st);
+    if (rc) return rc;
     return check_launch();
 }
 

@@ -33,6 +33,17 @@ struct GemvArgs {
     const uint8_t* next_w;    // hint: weights of the NEXT matmul on this stream, prefetched into L2 (or NULL)
     unsigned long long next_bytes;
     unsigned long long* ts;   // development: per-warp phase timestamps (8 per warp) or NULL
+    // mixture-of-experts decode (reference xe_linear.moe_forward_vec), M == 1:
+    //   mode 1: blockIdx.z = routed slot z; w / w2 = tab_w[sel[z]] / tab_w2[sel[z]]; y row z
+    //   mode 2: the K axis is the concatenation of n_seg matrices tab_w[sel[z]] ([rows][k] each) and
+    //           x is [n_seg][k]; slot z's partial sums are multiplied by seg_scale[z]
+    int mode;
+    const unsigned long long* tab_w;
+    const unsigned long long* tab_w2;
+    const void* sel; int sel_i64;          // routed expert ids, int32 or int64
+    int n_experts;                         // ids outside [0, n_experts) contribute zero
+    int n_seg;
+    const void* seg_scale; int seg_scale_dtype;
 };
 
 __device__ __forceinline__ void store_out(void* y, int dt, int64_t idx, float v, const void* bias, int64_t row, int acc) {

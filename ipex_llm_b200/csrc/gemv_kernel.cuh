@@ -260,7 +260,10 @@ __device__ __forceinline__ float ld_dsmem_f32(uint32_t local_addr, uint32_t rank
 // NM = 2 is the fused MLP (reference fuse_mlp_base, models/common.py:146-161: xe_linear.mlp_forward_xpu):
 // the same rows of a second matrix (A.w2, "up") are streamed after the first ("gate") and the epilogue
 // stores act(gate . x) * (up . x).
-template <int QT, bool BF, int NS, int NT, int ACC, int NM>
+// MODE 1 / 2 are the two launches of the mixture-of-experts decode (see GemvArgs): 1 = one routed
+// expert per blockIdx.z (used with NM = 2 for gate/up), 2 = the routed experts' down projections
+// concatenated along K, each slot's sums weighted by its routing weight.
+template <int QT, bool BF, int NS, int NT, int ACC, int NM, int MODE>
 __global__ void __launch_bounds__(GEMV_WARPS * 32)
 gemv_kernel(const GemvArgs A) {
     using C = Codec<QT, BF>;
@@ -277,34 +280,76 @@ gemv_kernel(const GemvArgs A) {
     const int g = lane >> 2, t = lane & 3;
     const int nsplit = gridDim.x, slice = blockIdx.x, rg = blockIdx.y;
     const int nb = (int)A.G.nb;
+    const int nbt = (MODE == 2) ? nb * A.n_seg : nb;   // k-blocks along the (concatenated) K axis
     if (A.pdl) asm volatile("griddepcontrol.launch_dependents;");
+    // the routed expert ids come from the previous kernel: nothing can be fetched before it is done
+    if (MODE != 0 && A.pdl) asm volatile("griddepcontrol.wait;" ::: "memory");
+
+    auto expert_of = [&](int z, bool& ok) -> int {
+        const long long e = A.sel_i64 ? reinterpret_cast<const long long*>(A.sel)[z]
+                                      : (long long)reinterpret_cast<const int*>(A.sel)[z];
+        ok = e >= 0 && e < A.n_experts;
+        return ok ? (int)e : 0;
+    };
+    const uint8_t* wb0 = A.w;
+    const uint8_t* wb1 = A.w2;
+    float out_scale = 1.0f;
+    if (MODE == 1) {
+        bool ok;
+        const int e = expert_of(blockIdx.z, ok);
+        wb0 = reinterpret_cast<const uint8_t*>(A.tab_w[e]);
+        wb1 = reinterpret_cast<const uint8_t*>(A.tab_w2[e]);
+        out_scale = ok ? 1.0f : 0.0f;
+    }
 
     // this CTA's k-blocks [ck0, ck1), this warp's [kb0, kb1)
-    const int ck0 = (int)((int64_t)slice * nb / nsplit), ck1 = (int)((int64_t)(slice + 1) * nb / nsplit);
+    const int ck0 = (int)((int64_t)slice * nbt / nsplit), ck1 = (int)((int64_t)(slice + 1) * nbt / nsplit);
     const int kb0 = ck0 + (int)((int64_t)warp * (ck1 - ck0) / GEMV_WARPS);
     const int kb1 = ck0 + (int)((int64_t)(warp + 1) * (ck1 - ck0) / GEMV_WARPS);
     const int n_super = kb1 - kb0;
-    const int n_chunks = (n_super + CH - 1) / CH;
-    const int64_t u0 = (int64_t)rg * nb + kb0;         // first super-tile of this warp
+    // the warp's work is a list of segments: one per matrix (NM) and, in MODE 2, per routed slot its
+    // range touches; a segment is `n` consecutive super-tiles starting at k-block `a` of matrix `base`
+    const int z_first = (MODE == 2) ? kb0 / nb : 0;
+    const int z_last = (MODE == 2) ? (n_super > 0 ? (kb1 - 1) / nb : z_first - 1) : 0;
+    auto seg_load = [&](int mt, int z, int& a, int& n, const uint8_t*& base) {
+        if (MODE == 2) {
+            const int lo = max(kb0, z * nb), hi = min(kb1, (z + 1) * nb);
+            bool ok;
+            a = lo - z * nb; n = hi - lo;
+            base = reinterpret_cast<const uint8_t*>(A.tab_w[expert_of(z, ok)]);
+        } else {
+            a = kb0; n = n_super; base = mt ? wb1 : wb0;
+        }
+    };
     const int64_t wid = ((int64_t)rg * nsplit + slice) * GEMV_WARPS + warp;   // timestamps only
     TS(0);
 
     // this warp's private ring: [STAGES][codes | scales | mins]; the mbarriers sit after all rings
     const uint32_t ring = smem_u32(smem) + warp * S::kWarpBytes;
     const uint32_t bars = smem_u32(smem) + GEMV_WARPS * S::kWarpBytes + warp * (STAGES * 8);
-    const int total_chunks = NM * n_chunks;            // the ring runs through matrix 0, then matrix 1
-
-    auto issue = [&](int c) {                         // one lane: copy global chunk c into stage c % STAGES
-        const int st = c % STAGES;
-        const int mat = (NM == 2 && c >= n_chunks) ? 1 : 0;
-        const int lc = c - mat * n_chunks;
-        const uint8_t* wb = mat ? A.w2 : A.w;
-        const int ns = min(CH, n_super - lc * CH);
-        const uint32_t dst = ring + st * STAGE_BYTES, bar = bars + st * 8;
-        mbar_expect_tx(bar, ns * (SUPER + 128 + S::kMinBytes));
-        bulk_g2s(dst, wb + (u0 + (int64_t)lc * CH) * SUPER, ns * SUPER, bar);
-        bulk_g2s(dst + CH * SUPER, wb + A.G.off_s + (u0 + (int64_t)lc * CH) * 128, ns * 128, bar);
-        if (S::kMinBytes) bulk_g2s(dst + CH * (SUPER + 128), wb + A.G.off_m + (u0 + (int64_t)lc * CH) * 128, ns * 128, bar);
+    // issue cursor: walks the segment list one chunk at a time (same state in every lane)
+    int i_mt = 0, i_z = z_first, i_lc = 0, i_c = 0, i_a = 0, i_n = 0;
+    const uint8_t* i_base = nullptr;
+    bool i_live = n_super > 0;
+    if (i_live) seg_load(0, z_first, i_a, i_n, i_base);
+    auto issue_next = [&](bool doit) {                 // copy the cursor's chunk into stage i_c % STAGES, advance
+        if (!i_live) return;
+        if (doit) {
+            const int st = i_c % STAGES;
+            const int ns = min(CH, i_n - i_lc * CH);
+            const int64_t u = (int64_t)rg * nb + i_a + i_lc * CH;
+            const uint32_t dst = ring + st * STAGE_BYTES, bar = bars + st * 8;
+            mbar_expect_tx(bar, ns * (SUPER + 128 + S::kMinBytes));
+            bulk_g2s(dst, i_base + u * SUPER, ns * SUPER, bar);
+            bulk_g2s(dst + CH * SUPER, i_base + A.G.off_s + u * 128, ns * 128, bar);
+            if (S::kMinBytes) bulk_g2s(dst + CH * (SUPER + 128), i_base + A.G.off_m + u * 128, ns * 128, bar);
+        }
+        i_c++; i_lc++;
+        if (i_lc * CH >= i_n) {
+            i_lc = 0;
+            if (i_z < z_last) i_z++; else { i_z = z_first; i_mt++; }
+            if (i_mt == NM) i_live = false; else seg_load(i_mt, i_z, i_a, i_n, i_base);
+        }
     };
 
     constexpr bool PUSH = (NT == 1);                   // peers push their sums into the leader (else the leader pulls)
@@ -319,13 +364,14 @@ gemv_kernel(const GemvArgs A) {
     }
     // lane s owns stage s during start-up (the barrier inits and first copies go out in parallel);
     // weights do not depend on the previous kernel: they start streaming before the PDL wait
-    if (lane < STAGES && lane < total_chunks) {
+    if (lane < STAGES) {
         mbar_init(bars + lane * 8, 1);
         // make the init visible to the async proxy (the TMA engine completes bytes on this barrier);
         // the cluster-scoped fence.mbarrier_init costs ~1 us here (it also invalidates L1)
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-        issue(lane);
     }
+#pragma unroll
+    for (int s = 0; s < STAGES; s++) issue_next(lane == s);
     __syncwarp();
     TS(1);
     // HBM is idle during a kernel's start-up, its reduction tail and the launch gap: about a third of a
@@ -342,7 +388,7 @@ gemv_kernel(const GemvArgs A) {
                 asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(A.next_w + off), "r"((uint32_t)share) : "memory");
         }
     }
-    if (A.pdl) asm volatile("griddepcontrol.wait;" ::: "memory");
+    if (MODE == 0 && A.pdl) asm volatile("griddepcontrol.wait;" ::: "memory");
     TS(2);
 
     float accm[NM][RG_TILES][NT][ACC];
@@ -374,15 +420,28 @@ gemv_kernel(const GemvArgs A) {
     uint32_t ones[4];
     ones[0] = ones[1] = ones[2] = ones[3] = BF ? 0x3f803f80u : 0x3c003c00u;
 
+    float tot[MODE == 2 ? RG_TILES : 1][NT][ACC];      // MODE 2: sum over finished slots of scale * acc
+#pragma unroll
+    for (int r = 0; r < (MODE == 2 ? RG_TILES : 1); r++)
+#pragma unroll
+        for (int j = 0; j < NT; j++)
+#pragma unroll
+            for (int q = 0; q < ACC; q++) tot[r][j][q] = 0.0f;
+
+    int c = 0;                                         // chunks consumed so far (stage and phase follow from it)
 #pragma unroll
     for (int mt = 0; mt < NM; mt++) {
     float (&acc)[RG_TILES][NT][ACC] = accm[mt];
     xoff = 0;
-    for (int lc = 0; lc < n_chunks; lc++) {
-        const int c = mt * n_chunks + lc;
+    for (int z = z_first; z <= z_last; z++) {
+    int s_a, s_n;
+    const uint8_t* s_base;
+    seg_load(mt, z, s_a, s_n, s_base);
+    const int n_chunks = (s_n + CH - 1) / CH;
+    for (int lc = 0; lc < n_chunks; lc++, c++) {
         const int st = c % STAGES;
         const uint32_t stage = ring + st * STAGE_BYTES;
-        const int ns = min(CH, n_super - lc * CH);
+        const int ns = min(CH, s_n - lc * CH);
         mbar_wait(bars + st * 8, (uint32_t)((c / STAGES) & 1));
         if (c == 0) TS(3);
 #pragma unroll
@@ -474,8 +533,33 @@ gemv_kernel(const GemvArgs A) {
         }
         // every lane has consumed the stage (its data sits in registers already used): refill it
         __syncwarp();
-        if (lane == 0 && c + STAGES < total_chunks) issue(c + STAGES);
+        if (lane == 0) issue_next(true);
     }
+    if (MODE == 2) {                                   // slot z is done: fold it in with its routing weight
+        bool ok;
+        expert_of(z, ok);
+        float sc = 0.0f;
+        if (ok) {
+            if (A.seg_scale_dtype == DT_F32) sc = reinterpret_cast<const float*>(A.seg_scale)[z];
+            else if (A.seg_scale_dtype == DT_F16) sc = __half2float(reinterpret_cast<const __half*>(A.seg_scale)[z]);
+            else sc = __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(A.seg_scale)[z]);
+        }
+#pragma unroll
+        for (int r = 0; r < (MODE == 2 ? RG_TILES : 0); r++)
+#pragma unroll
+            for (int j = 0; j < NT; j++)
+#pragma unroll
+                for (int q = 0; q < ACC; q++) { tot[r][j][q] = fmaf(sc, acc[r][j][q], tot[r][j][q]); acc[r][j][q] = 0.0f; }
+    }
+    }
+    }
+    if (MODE == 2) {
+#pragma unroll
+        for (int r = 0; r < (MODE == 2 ? RG_TILES : 0); r++)
+#pragma unroll
+            for (int j = 0; j < NT; j++)
+#pragma unroll
+                for (int q = 0; q < ACC; q++) accm[0][r][j][q] = tot[r][j][q];
     }
     TS(4);
 
@@ -511,12 +595,13 @@ gemv_kernel(const GemvArgs A) {
         const int col = 8 * j + 2 * tt + ((ACC == 2) ? 0 : (c & 1));
         const int64_t row = (int64_t)rg * RG_ROWS + r * 16 + gg + 8 * hi;
         if (col < A.M && (ACC != 2 || tt == 0))
-            store_out(A.y, A.y_dtype, (int64_t)col * N + row, v, A.bias, row, A.accumulate);
+            store_out(A.y, A.y_dtype, (MODE == 1 ? (int64_t)blockIdx.z * N : (int64_t)col * N) + row, v, A.bias, row, A.accumulate);
     };
     // value i of matrix mt lives at float index mt*NV*32 + i; NV*32 is a multiple of the block size, so the
     // thread that owns i owns it for both matrices and can apply act(gate) * up itself
     auto finish = [&](int i, const float (&vm)[NM]) {
-        store_value(i, NM == 2 ? apply_act(vm[0], A.act) * vm[NM - 1] : vm[0]);
+        const float v = NM == 2 ? apply_act(vm[0], A.act) * vm[NM - 1] : vm[0];
+        store_value(i, MODE == 1 ? v * out_scale : v);
     };
     if (nsplit == 1) {
         for (int i = threadIdx.x; i < NV * 32; i += GEMV_WARPS * 32) {
@@ -609,10 +694,11 @@ static int pick_split(K kernel, int smem, int64_t groups, int64_t nb, int (&cach
 
 template <typename K>
 static void launch_kernel(K kernel, int smem, int64_t groups, int64_t nb, const GemvArgs& A, cudaStream_t st,
-                          int (&cache)[8]) {
-    const int split = pick_split(kernel, smem, groups, nb, cache);
+                          int (&cache)[8], int grid_z = 1) {
+    // nb = k-blocks one cluster splits; the cluster count that has to fit in one wave is groups * grid_z
+    const int split = pick_split(kernel, smem, groups * grid_z, nb, cache);
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3((unsigned)split, (unsigned)groups, 1);
+    cfg.gridDim = dim3((unsigned)split, (unsigned)groups, (unsigned)grid_z);
     cfg.blockDim = dim3(GEMV_WARPS * 32); cfg.dynamicSmemBytes = smem; cfg.stream = st;
     cudaLaunchAttribute at[2];
     int na = 0;
@@ -632,26 +718,36 @@ template <int QT, bool BF, int NS>
 static void launch_nt(int m, int64_t groups, int64_t nb, const GemvArgs& A, cudaStream_t st) {
     using SG = Staging<QT, BF>;
     static bool configured = false;     // per instantiation: raise the dynamic shared memory limit once
-    static int cache[6][8];
+    static int cache[8][8];
     if (!configured) {
         for (auto& row : cache) for (int& v : row) v = -1;
-        cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 1, 2, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, SG::smem_bytes(1, 2, 1));
-        cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 1, 4, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, SG::smem_bytes(1, 4, 1));
-        cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 2, 4, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, SG::smem_bytes(2, 4, 1));
-        cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 4, 4, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, SG::smem_bytes(4, 4, 1));
-        cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 1, 2, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, SG::smem_bytes(1, 2, 2));
-        cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 1, 4, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, SG::smem_bytes(1, 4, 2));
+        cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 1, 2, 1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, SG::smem_bytes(1, 2, 1));
+        cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 1, 4, 1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, SG::smem_bytes(1, 4, 1));
+        cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 2, 4, 1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, SG::smem_bytes(2, 4, 1));
+        cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 4, 4, 1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, SG::smem_bytes(4, 4, 1));
+        cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 1, 2, 2, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, SG::smem_bytes(1, 2, 2));
+        cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 1, 4, 2, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, SG::smem_bytes(1, 4, 2));
+        cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 1, 2, 2, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, SG::smem_bytes(1, 2, 2));
+        cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 1, 2, 1, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, SG::smem_bytes(1, 2, 1));
         configured = true;
     }
-    if (A.w2) {                          // fused MLP: M <= 8 only (the host falls back otherwise)
-        if (m == 1) launch_kernel(gemv_kernel<QT, BF, NS, 1, 2, 2>, SG::smem_bytes(1, 2, 2), groups, nb, A, st, cache[4]);
-        else launch_kernel(gemv_kernel<QT, BF, NS, 1, 4, 2>, SG::smem_bytes(1, 4, 2), groups, nb, A, st, cache[5]);
+    if (A.mode == 1) {                   // routed experts' gate/up: one slot per blockIdx.z (M == 1)
+        launch_kernel(gemv_kernel<QT, BF, NS, 1, 2, 2, 1>, SG::smem_bytes(1, 2, 2), groups, nb, A, st, cache[6], A.n_seg);
         return;
     }
-    if (m == 1) launch_kernel(gemv_kernel<QT, BF, NS, 1, 2, 1>, SG::smem_bytes(1, 2, 1), groups, nb, A, st, cache[0]);
-    else if (m <= 8) launch_kernel(gemv_kernel<QT, BF, NS, 1, 4, 1>, SG::smem_bytes(1, 4, 1), groups, nb, A, st, cache[1]);
-    else if (m <= 16) launch_kernel(gemv_kernel<QT, BF, NS, 2, 4, 1>, SG::smem_bytes(2, 4, 1), groups, nb, A, st, cache[2]);
-    else launch_kernel(gemv_kernel<QT, BF, NS, 4, 4, 1>, SG::smem_bytes(4, 4, 1), groups, nb, A, st, cache[3]);
+    if (A.mode == 2) {                   // routed experts' down projections, concatenated along K (M == 1)
+        launch_kernel(gemv_kernel<QT, BF, NS, 1, 2, 1, 2>, SG::smem_bytes(1, 2, 1), groups, nb * A.n_seg, A, st, cache[7]);
+        return;
+    }
+    if (A.w2) {                          // fused MLP: M <= 8 only (the host falls back otherwise)
+        if (m == 1) launch_kernel(gemv_kernel<QT, BF, NS, 1, 2, 2, 0>, SG::smem_bytes(1, 2, 2), groups, nb, A, st, cache[4]);
+        else launch_kernel(gemv_kernel<QT, BF, NS, 1, 4, 2, 0>, SG::smem_bytes(1, 4, 2), groups, nb, A, st, cache[5]);
+        return;
+    }
+    if (m == 1) launch_kernel(gemv_kernel<QT, BF, NS, 1, 2, 1, 0>, SG::smem_bytes(1, 2, 1), groups, nb, A, st, cache[0]);
+    else if (m <= 8) launch_kernel(gemv_kernel<QT, BF, NS, 1, 4, 1, 0>, SG::smem_bytes(1, 4, 1), groups, nb, A, st, cache[1]);
+    else if (m <= 16) launch_kernel(gemv_kernel<QT, BF, NS, 2, 4, 1, 0>, SG::smem_bytes(2, 4, 1), groups, nb, A, st, cache[2]);
+    else launch_kernel(gemv_kernel<QT, BF, NS, 4, 4, 1, 0>, SG::smem_bytes(4, 4, 1), groups, nb, A, st, cache[3]);
 }
 template <int QT>
 static void launch_qt(int x_dtype, int m, int64_t groups, int64_t nb, const GemvArgs& A, cudaStream_t st) {

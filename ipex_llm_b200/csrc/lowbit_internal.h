@@ -47,6 +47,25 @@ int gemv_launch_ex(const void* w, const void* w2, int act, int qt, int64_t n_row
 bool gemv_mlp_fused_supported(int qt, int64_t n_rows, int64_t k, int64_t m);
 int act_mul_launch(const float* gate, const float* up, void* y, int y_dtype, int64_t n, int act, cudaStream_t st);
 
+// one-token mixture-of-experts (reference xe_linear.moe_forward_vec)
+struct MoeParams {
+    const void* x; int x_dtype;                  // [hidden]
+    const void* ids; int ids_i64;                // [top_k] routed expert ids (device)
+    const void* weights; int w_dtype;            // [top_k] routing weights (device)
+    int top_k;
+    const unsigned long long* gates;             // [n_experts] device addresses of the tiled [inter][hidden] weights
+    const unsigned long long* ups;
+    const unsigned long long* downs;             // ... of the tiled [hidden][inter] weights
+    int n_experts;
+    int64_t hidden, inter;
+    int qtype, act;
+    void* y; int y_dtype; int accumulate;        // [hidden]
+    void* workspace; size_t workspace_bytes;
+};
+bool moe_supported(int qt, int64_t hidden, int64_t inter, int top_k);
+size_t moe_workspace_size(int64_t hidden, int64_t inter, int top_k, int x_dtype);
+int moe_launch(const MoeParams& P, cudaStream_t st);
+
 // gemm_tc.cu (tcgen05 prefill GEMM)
 bool gemm_tc_supported(int qt, int64_t n_rows, int64_t k);
 size_t gemm_tc_workspace_size(int64_t k, int64_t m, int x_dtype);

@@ -215,6 +215,32 @@ def lowbit_mlp_cuda(d_w_gate, d_w_up, qtype, n_rows, k, d_x, x_dtype, m, d_y, y_
                                 workspace, workspace_bytes, stream), "lowbit_mlp_cuda")
 
 
+_lib.lowbit_moe_supported.argtypes = [ctypes.c_int, ctypes.c_int64, ctypes.c_int64, ctypes.c_int]
+_lib.lowbit_moe_supported.restype = ctypes.c_int
+_lib.lowbit_moe_workspace_size.argtypes = [ctypes.c_int64, ctypes.c_int64, ctypes.c_int, ctypes.c_int]
+_lib.lowbit_moe_workspace_size.restype = ctypes.c_size_t
+_lib.lowbit_moe_cuda.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int,
+                                 ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int,
+                                 ctypes.c_int64, ctypes.c_int64, ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_int,
+                                 ctypes.c_int, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p]
+_lib.lowbit_moe_cuda.restype = ctypes.c_int
+
+
+def lowbit_moe_supported(qtype, hidden, inter, top_k):
+    return bool(_lib.lowbit_moe_supported(qtype, hidden, inter, top_k))
+
+
+def lowbit_moe_workspace_size(hidden, inter, top_k, x_dtype):
+    return _lib.lowbit_moe_workspace_size(hidden, inter, top_k, x_dtype)
+
+
+def lowbit_moe_cuda(d_x, x_dtype, d_ids, ids_dtype, d_weight, weight_dtype, top_k, d_gates, d_ups, d_downs, n_experts,
+                    hidden, inter, qtype, act, d_y, y_dtype, accumulate, workspace, workspace_bytes, stream):
+    _check(_lib.lowbit_moe_cuda(d_x, x_dtype, d_ids, ids_dtype, d_weight, weight_dtype, top_k, d_gates, d_ups, d_downs,
+                                n_experts, hidden, inter, qtype, act, d_y, y_dtype, int(accumulate), workspace,
+                                workspace_bytes, stream), "lowbit_moe_cuda")
+
+
 _lib.lowbit_set_programmatic_dependent_launch.argtypes = [ctypes.c_int]
 _lib.lowbit_set_programmatic_dependent_launch.restype = None
 

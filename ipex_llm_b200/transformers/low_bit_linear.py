@@ -289,6 +289,44 @@ def mlp_forward(x_2d: torch.Tensor, gate_weight: torch.Tensor, up_weight: torch.
     return out
 
 
+def use_fuse_moe(hidden: int, inter: int, top_k: int, qtype: int) -> bool:
+    """shape / qtype test of the fused one-token MoE (the reference's use_fuse_moe, models/utils.py)"""
+    return ggml.lowbit_moe_supported(qtype, hidden, inter, top_k)
+
+
+def moe_forward_vec(x: torch.Tensor, topk_ids: torch.Tensor, topk_weight: torch.Tensor, gates: torch.Tensor,
+                    ups: torch.Tensor, downs: torch.Tensor, hidden: int, inter: int, qtype: int, act: int = SILU,
+                    out: torch.Tensor = None, accumulate: bool = False):
+    """``xe_linear.moe_forward_vec`` (models/qwen3_moe.py:88-105, deepseek.py:296-312): the routed
+    experts' MLPs of ONE token.  ``gates`` / ``ups`` / ``downs`` are device tensors of the experts'
+    weight addresses (``expert.gate_proj.weight.data_ptr()`` ...), ``topk_ids`` / ``topk_weight``
+    the router's [1, top_k] outputs, read on the device.  Returns [1, hidden] in x's dtype."""
+    invalidInputError(x.dtype in _TORCH_TO_DT, f"unsupported activation dtype {x.dtype}")
+    invalidInputError(x.numel() == hidden, "moe_forward_vec handles one token")
+    invalidInputError(topk_ids.dtype in (torch.int32, torch.int64), "topk_ids must be int32 or int64")
+    invalidInputError(topk_weight.dtype in _TORCH_TO_DT, f"unsupported routing weight dtype {topk_weight.dtype}")
+    invalidInputError(topk_ids.numel() == topk_weight.numel(), "topk_ids and topk_weight differ in length")
+    invalidInputError(gates.numel() == ups.numel() == downs.numel() and gates.element_size() == 8,
+                      "gates / ups / downs must be equally long tensors of 64-bit addresses")
+    top_k = topk_ids.numel()
+    x = x.contiguous()
+    topk_ids, topk_weight = topk_ids.contiguous(), topk_weight.contiguous()
+    if out is None:
+        invalidInputError(not accumulate, "accumulate needs an output tensor")
+        out = torch.empty((1, hidden), dtype=x.dtype, device=x.device)
+    dev = x.device
+    dt = _TORCH_TO_DT[x.dtype]
+    ws = _get_workspace(dev, ggml.lowbit_moe_workspace_size(hidden, inter, top_k, dt))
+    with torch.cuda.device(dev):
+        ggml.lowbit_moe_cuda(ctypes.c_void_p(x.data_ptr()), dt, ctypes.c_void_p(topk_ids.data_ptr()),
+                             1 if topk_ids.dtype == torch.int64 else 0, ctypes.c_void_p(topk_weight.data_ptr()),
+                             _TORCH_TO_DT[topk_weight.dtype], top_k, ctypes.c_void_p(gates.data_ptr()),
+                             ctypes.c_void_p(ups.data_ptr()), ctypes.c_void_p(downs.data_ptr()), gates.numel(),
+                             hidden, inter, qtype, act, ctypes.c_void_p(out.data_ptr()), _TORCH_TO_DT[out.dtype],
+                             accumulate, ctypes.c_void_p(ws.data_ptr()), ws.numel(), _stream_ptr(dev))
+    return out
+
+
 def ggml_matmul_src1_x_src0_t(src0: torch.Tensor, src1: torch.Tensor, src0_shape: torch.Size, src0_qtype: int):
     """LBL:494-529: result[M,N] = src1[M,K] . W[N,K]^T with W = canonical packed blocks on the
     CPU; fp32 in, fp32 out, one call across the reference C ABI (which runs on the GPU here)."""
