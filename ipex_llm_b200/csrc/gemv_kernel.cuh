@@ -416,6 +416,26 @@ gemv_kernel(const GemvArgs A) {
         }
     }
     unsigned xoff = 0;              // byte offset of the current k-block from kb0 inside an x row
+    // x comes from L2 (each warp reads its own K slice; L1 is cold): the fragment of the NEXT k-block is
+    // requested one super-tile ahead so that the ~0.4 us round trip hides behind the current one
+    constexpr bool XPF = (NT * NS <= 3);
+    uint4 xn[XPF ? NT : 1][XPF ? NS : 1][2];
+    int xleft = 0;
+    auto fetch_x = [&](unsigned off) {
+#pragma unroll
+        for (int j = 0; j < (XPF ? NT : 0); j++)
+#pragma unroll
+            for (int p = 0; p < (XPF ? NS : 0); p++)
+                if (xvalid[j]) {
+                    xn[j][p][0] = ldg_cached16(xptr[j][p] + off);
+                    xn[j][p][1] = ldg_cached16(xptr[j][p] + off + 16);
+                }
+    };
+#pragma unroll
+    for (int j = 0; j < (XPF ? NT : 1); j++)
+#pragma unroll
+        for (int p = 0; p < (XPF ? NS : 1); p++) { xn[j][p][0] = make_uint4(0, 0, 0, 0); xn[j][p][1] = make_uint4(0, 0, 0, 0); }
+    if (XPF && n_super > 0) fetch_x(0u);
 
     uint32_t ones[4];
     ones[0] = ones[1] = ones[2] = ones[3] = BF ? 0x3f803f80u : 0x3c003c00u;
@@ -433,6 +453,7 @@ gemv_kernel(const GemvArgs A) {
     for (int mt = 0; mt < NM; mt++) {
     float (&acc)[RG_TILES][NT][ACC] = accm[mt];
     xoff = 0;
+    xleft = n_super;
     for (int z = z_first; z <= z_last; z++) {
     int s_a, s_n;
     const uint8_t* s_base;
@@ -449,14 +470,24 @@ gemv_kernel(const GemvArgs A) {
             if (i < ns) {
                 const uint32_t codes = stage + i * SUPER;
                 // ---- once per super-tile: x fragment, sum(x), scales of the lane's 8 rows
+                if (XPF) {
 #pragma unroll
-                for (int j = 0; j < NT; j++)
+                    for (int j = 0; j < (XPF ? NT : 0); j++)
 #pragma unroll
-                    for (int p = 0; p < NS; p++)
-                        if (xvalid[j]) {                        // L1/L2-cached: x is shared by every row group
-                            xb[j][p][0] = ldg_cached16(xptr[j][p] + xoff);
-                            xb[j][p][1] = ldg_cached16(xptr[j][p] + xoff + 16);
-                        }
+                        for (int p = 0; p < (XPF ? NS : 0); p++) { xb[j][p][0] = xn[j][p][0]; xb[j][p][1] = xn[j][p][1]; }
+                    xleft--;
+                    if (xleft > 0) fetch_x(xoff + 128u);
+                    else if (mt + 1 < NM) fetch_x(0u);         // the second matrix starts over at the slice's first block
+                } else {
+#pragma unroll
+                    for (int j = 0; j < NT; j++)
+#pragma unroll
+                        for (int p = 0; p < NS; p++)
+                            if (xvalid[j]) {                        // L1/L2-cached: x is shared by every row group
+                                xb[j][p][0] = ldg_cached16(xptr[j][p] + xoff);
+                                xb[j][p][1] = ldg_cached16(xptr[j][p] + xoff + 16);
+                            }
+                }
                 xoff += 128u;
                 // -8 * sum over the k-block of x (sym) / sum (asym) for columns 2t, 2t+1: a ones-row mma,
                 // two independent chains (the tensor pipe is ~13 % busy in this kernel; issue slots are scarce)
