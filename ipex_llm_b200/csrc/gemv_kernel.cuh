@@ -69,6 +69,11 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
         "bra WAIT_%=;\n\t"
         "DONE_%=:\n\t}" ::"r"(bar), "r"(parity) : "memory");
 }
+__device__ __forceinline__ bool elect_one() {       // one lane of the (converged) warp
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+    return pred != 0;
+}
 // TMA 1-D bulk copy global -> shared, completion counted in bytes on an mbarrier (SASS: UBLKCP)
 __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
@@ -276,7 +281,9 @@ gemv_kernel(const GemvArgs A) {
     static_assert(NVT * 128 <= S::kWarpBytes, "reduction slot must fit in the warp's ring");
     extern __shared__ __align__(128) uint8_t smem[];
 
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    // the warp index through a shuffle: the compiler then knows it is warp-uniform and keeps everything
+    // derived from it (ring addresses, copy sources) in uniform registers
+    const int lane = threadIdx.x & 31, warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);
     const int g = lane >> 2, t = lane & 3;
     const int nsplit = gridDim.x, slice = blockIdx.x, rg = blockIdx.y;
     const int nb = (int)A.G.nb;
@@ -303,9 +310,10 @@ gemv_kernel(const GemvArgs A) {
     }
 
     // this CTA's k-blocks [ck0, ck1), this warp's [kb0, kb1)
-    const int ck0 = (int)((int64_t)slice * nbt / nsplit), ck1 = (int)((int64_t)(slice + 1) * nbt / nsplit);
-    const int kb0 = ck0 + (int)((int64_t)warp * (ck1 - ck0) / GEMV_WARPS);
-    const int kb1 = ck0 + (int)((int64_t)(warp + 1) * (ck1 - ck0) / GEMV_WARPS);
+    const int ck0 = (int)((unsigned)slice * (unsigned)nbt / (unsigned)nsplit);
+    const int ck1 = (int)((unsigned)(slice + 1) * (unsigned)nbt / (unsigned)nsplit);
+    const int kb0 = ck0 + (int)((unsigned)warp * (unsigned)(ck1 - ck0) / (unsigned)GEMV_WARPS);
+    const int kb1 = ck0 + (int)((unsigned)(warp + 1) * (unsigned)(ck1 - ck0) / (unsigned)GEMV_WARPS);
     const int n_super = kb1 - kb0;
     // the warp's work is a list of segments: one per matrix (NM) and, in MODE 2, per routed slot its
     // range touches; a segment is `n` consecutive super-tiles starting at k-block `a` of matrix `base`
@@ -327,28 +335,43 @@ gemv_kernel(const GemvArgs A) {
     // this warp's private ring: [STAGES][codes | scales | mins]; the mbarriers sit after all rings
     const uint32_t ring = smem_u32(smem) + warp * S::kWarpBytes;
     const uint32_t bars = smem_u32(smem) + GEMV_WARPS * S::kWarpBytes + warp * (STAGES * 8);
-    // issue cursor: walks the segment list one chunk at a time (same state in every lane)
-    int i_mt = 0, i_z = z_first, i_lc = 0, i_c = 0, i_a = 0, i_n = 0;
-    const uint8_t* i_base = nullptr;
+    // issue cursor: walks the segment list one chunk at a time.  Warp-uniform state, called by the whole
+    // warp; one elected lane issues the copies.
+    static_assert((STAGES & (STAGES - 1)) == 0, "stage index is a mask of the chunk counter");
+    int i_mt = 0, i_z = z_first, i_left = 0;
+    unsigned i_c = 0;
+    const uint8_t* i_q = nullptr;                      // next chunk's codes; scales / mins follow at fixed offsets
+    const uint8_t* i_s = nullptr;
     bool i_live = n_super > 0;
-    if (i_live) seg_load(0, z_first, i_a, i_n, i_base);
-    auto issue_next = [&](bool doit) {                 // copy the cursor's chunk into stage i_c % STAGES, advance
+    auto seg_open = [&](int mt, int z) {
+        int a;
+        const uint8_t* base;
+        seg_load(mt, z, a, i_left, base);
+        const int64_t u = (int64_t)rg * nb + a;
+        i_q = base + u * SUPER;
+        i_s = base + A.G.off_s + u * 128;
+    };
+    if (i_live) seg_open(0, z_first);
+    const int64_t s_to_m = A.G.off_m - A.G.off_s;
+    auto issue_next = [&]() {                          // copy the cursor's chunk into stage i_c % STAGES, advance
         if (!i_live) return;
-        if (doit) {
-            const int st = i_c % STAGES;
-            const int ns = min(CH, i_n - i_lc * CH);
-            const int64_t u = (int64_t)rg * nb + i_a + i_lc * CH;
-            const uint32_t dst = ring + st * STAGE_BYTES, bar = bars + st * 8;
+        const int ns = min(CH, i_left);
+        const uint32_t st = i_c & (STAGES - 1);
+        const uint32_t dst = ring + st * STAGE_BYTES, bar = bars + st * 8;
+        if (elect_one()) {
             mbar_expect_tx(bar, ns * (SUPER + 128 + S::kMinBytes));
-            bulk_g2s(dst, i_base + u * SUPER, ns * SUPER, bar);
-            bulk_g2s(dst + CH * SUPER, i_base + A.G.off_s + u * 128, ns * 128, bar);
-            if (S::kMinBytes) bulk_g2s(dst + CH * (SUPER + 128), i_base + A.G.off_m + u * 128, ns * 128, bar);
+            bulk_g2s(dst, i_q, ns * SUPER, bar);
+            bulk_g2s(dst + CH * SUPER, i_s, ns * 128, bar);
+            if (S::kMinBytes) bulk_g2s(dst + CH * (SUPER + 128), i_s + s_to_m, ns * 128, bar);
         }
-        i_c++; i_lc++;
-        if (i_lc * CH >= i_n) {
-            i_lc = 0;
-            if (i_z < z_last) i_z++; else { i_z = z_first; i_mt++; }
-            if (i_mt == NM) i_live = false; else seg_load(i_mt, i_z, i_a, i_n, i_base);
+        i_c++; i_left -= CH;
+        i_q += CH * SUPER; i_s += CH * 128;
+        if (i_left <= 0) {
+            if (NM == 1 && MODE != 2) i_live = false;
+            else {
+                if (i_z < z_last) i_z++; else { i_z = z_first; i_mt++; }
+                if (i_mt == NM) i_live = false; else seg_open(i_mt, i_z);
+            }
         }
     };
 
@@ -370,9 +393,9 @@ gemv_kernel(const GemvArgs A) {
         // the cluster-scoped fence.mbarrier_init costs ~1 us here (it also invalidates L1)
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     }
-#pragma unroll
-    for (int s = 0; s < STAGES; s++) issue_next(lane == s);
     __syncwarp();
+#pragma unroll
+    for (int s = 0; s < STAGES; s++) issue_next();
     TS(1);
     // HBM is idle during a kernel's start-up, its reduction tail and the launch gap: about a third of a
     // 24 MB GEMV.  If the host told us which weights the NEXT matmul on this stream reads, every warp asks
@@ -404,7 +427,11 @@ gemv_kernel(const GemvArgs A) {
     // lane (g,t) reads x[8j+g][kb*64 + 16t .. +15] for n-tile j (plane p); rows >= M read as zero
     const char* xptr[NT][NS];
     bool xvalid[NT];
-    uint4 xb[NT][NS][2];            // lanes without a valid row keep zeros
+    constexpr bool XPF = (NT * NS <= 3);
+    constexpr int XPF_BUFS = XPF ? 2 : 1;
+    // two fragment buffers used alternately by even / odd super-tiles (no copies between them, so the
+    // compiler has no reason to delay the prefetch); lanes without a valid row keep zeros
+    uint4 xq[XPF_BUFS][NT][NS][2];
 #pragma unroll
     for (int j = 0; j < NT; j++) {
         xvalid[j] = (8 * j + g) < A.M;
@@ -412,30 +439,25 @@ gemv_kernel(const GemvArgs A) {
         for (int p = 0; p < NS; p++) {
             xptr[j][p] = reinterpret_cast<const char*>(A.x + p * A.plane_stride + (int64_t)(8 * j + g) * A.G.k + t * 16) +
                          (size_t)kb0 * 128;
-            xb[j][p][0] = make_uint4(0, 0, 0, 0); xb[j][p][1] = make_uint4(0, 0, 0, 0);
+#pragma unroll
+            for (int h = 0; h < XPF_BUFS; h++) { xq[h][j][p][0] = make_uint4(0, 0, 0, 0); xq[h][j][p][1] = make_uint4(0, 0, 0, 0); }
         }
     }
     unsigned xoff = 0;              // byte offset of the current k-block from kb0 inside an x row
     // x comes from L2 (each warp reads its own K slice; L1 is cold): the fragment of the NEXT k-block is
     // requested one super-tile ahead so that the ~0.4 us round trip hides behind the current one
-    constexpr bool XPF = (NT * NS <= 3);
-    uint4 xn[XPF ? NT : 1][XPF ? NS : 1][2];
     int xleft = 0;
-    auto fetch_x = [&](unsigned off) {
+    auto fetch_x = [&](uint4 (&dst)[NT][NS][2], unsigned off) {
 #pragma unroll
-        for (int j = 0; j < (XPF ? NT : 0); j++)
+        for (int j = 0; j < NT; j++)
 #pragma unroll
-            for (int p = 0; p < (XPF ? NS : 0); p++)
-                if (xvalid[j]) {
-                    xn[j][p][0] = ldg_cached16(xptr[j][p] + off);
-                    xn[j][p][1] = ldg_cached16(xptr[j][p] + off + 16);
+            for (int p = 0; p < NS; p++)
+                if (xvalid[j]) {                        // L1/L2-cached: x is shared by every row group
+                    dst[j][p][0] = ldg_cached16(xptr[j][p] + off);
+                    dst[j][p][1] = ldg_cached16(xptr[j][p] + off + 16);
                 }
     };
-#pragma unroll
-    for (int j = 0; j < (XPF ? NT : 1); j++)
-#pragma unroll
-        for (int p = 0; p < (XPF ? NS : 1); p++) { xn[j][p][0] = make_uint4(0, 0, 0, 0); xn[j][p][1] = make_uint4(0, 0, 0, 0); }
-    if (XPF && n_super > 0) fetch_x(0u);
+    if (XPF && n_super > 0) fetch_x(xq[0], 0u);
 
     uint32_t ones[4];
     ones[0] = ones[1] = ones[2] = ones[3] = BF ? 0x3f803f80u : 0x3c003c00u;
@@ -448,7 +470,7 @@ gemv_kernel(const GemvArgs A) {
 #pragma unroll
             for (int q = 0; q < ACC; q++) tot[r][j][q] = 0.0f;
 
-    int c = 0;                                         // chunks consumed so far (stage and phase follow from it)
+    unsigned c = 0;                                    // chunks consumed so far (stage and phase follow from it)
 #pragma unroll
     for (int mt = 0; mt < NM; mt++) {
     float (&acc)[RG_TILES][NT][ACC] = accm[mt];
@@ -458,35 +480,28 @@ gemv_kernel(const GemvArgs A) {
     int s_a, s_n;
     const uint8_t* s_base;
     seg_load(mt, z, s_a, s_n, s_base);
-    const int n_chunks = (s_n + CH - 1) / CH;
-    for (int lc = 0; lc < n_chunks; lc++, c++) {
-        const int st = c % STAGES;
-        const uint32_t stage = ring + st * STAGE_BYTES;
-        const int ns = min(CH, s_n - lc * CH);
-        mbar_wait(bars + st * 8, (uint32_t)((c / STAGES) & 1));
-        if (c == 0) TS(3);
+    uint32_t stage = 0;
+    for (int sidx = 0; sidx < s_n; sidx += 2) {
 #pragma unroll
-        for (int i = 0; i < CH; i++) {
-            if (i < ns) {
+        for (int h = 0; h < 2; h++) {
+            if (h == 0 || sidx + 1 < s_n) {
+                const int i = (CH == 2) ? h : 0;                  // super-tile index inside its stage
+                if (i == 0) {
+                    const uint32_t st = c & (STAGES - 1);
+                    stage = ring + st * STAGE_BYTES;
+                    mbar_wait(bars + st * 8, (c / STAGES) & 1u);
+                    if (c == 0) TS(3);
+                }
+                const bool last_of_stage = (i == CH - 1) || (sidx + h == s_n - 1);
                 const uint32_t codes = stage + i * SUPER;
+                uint4 (&xb)[NT][NS][2] = xq[XPF ? h : 0];
                 // ---- once per super-tile: x fragment, sum(x), scales of the lane's 8 rows
                 if (XPF) {
-#pragma unroll
-                    for (int j = 0; j < (XPF ? NT : 0); j++)
-#pragma unroll
-                        for (int p = 0; p < (XPF ? NS : 0); p++) { xb[j][p][0] = xn[j][p][0]; xb[j][p][1] = xn[j][p][1]; }
                     xleft--;
-                    if (xleft > 0) fetch_x(xoff + 128u);
-                    else if (mt + 1 < NM) fetch_x(0u);         // the second matrix starts over at the slice's first block
+                    if (xleft > 0) fetch_x(xq[XPF ? (h ^ 1) : 0], xoff + 128u);
+                    else if (mt + 1 < NM) fetch_x(xq[XPF ? (h ^ 1) : 0], 0u);   // the second matrix starts over at the slice's first block
                 } else {
-#pragma unroll
-                    for (int j = 0; j < NT; j++)
-#pragma unroll
-                        for (int p = 0; p < NS; p++)
-                            if (xvalid[j]) {                        // L1/L2-cached: x is shared by every row group
-                                xb[j][p][0] = ldg_cached16(xptr[j][p] + xoff);
-                                xb[j][p][1] = ldg_cached16(xptr[j][p] + xoff + 16);
-                            }
+                    fetch_x(xb, xoff);
                 }
                 xoff += 128u;
                 // -8 * sum over the k-block of x (sym) / sum (asym) for columns 2t, 2t+1: a ones-row mma,
@@ -560,11 +575,20 @@ gemv_kernel(const GemvArgs A) {
                         }
                     }
                 }
+                if (last_of_stage) {
+                    // every lane has consumed the stage (its data sits in registers already used): refill it
+                    __syncwarp();
+                    issue_next();
+                    c++;
+                }
             }
         }
-        // every lane has consumed the stage (its data sits in registers already used): refill it
-        __syncwarp();
-        if (lane == 0) issue_next(true);
+    }
+    if (XPF && (s_n & 1)) {                            // odd segment: the next one starts on buffer 0 again
+#pragma unroll
+        for (int j = 0; j < NT; j++)
+#pragma unroll
+            for (int p = 0; p < NS; p++) { xq[0][j][p][0] = xq[XPF_BUFS - 1][j][p][0]; xq[0][j][p][1] = xq[XPF_BUFS - 1][j][p][1]; }
     }
     if (MODE == 2) {                                   // slot z is done: fold it in with its routing weight
         bool ok;
