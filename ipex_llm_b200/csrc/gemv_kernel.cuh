@@ -231,7 +231,7 @@ template <int QT, bool BF> struct Staging {
     // + the leader CTA's receive buffer for its peers' CTA sums (push reduction, M <= 8 kernels):
     // (split-1) x NV x 32 floats
     static constexpr int smem_bytes(int nt, int acc, int nm) {
-        return GEMV_WARPS * kWarpBytes + kBarBytes + 8 + (nt == 1 ? (GEMV_MAX_SPLIT - 1) * (nm * RG_TILES * acc) * 128 : 0);
+        return GEMV_WARPS * kWarpBytes + kBarBytes + 8 + (nt == 1 ? (GEMV_MAX_SPLIT - 1) * (nm * RG_TILES * acc) * (acc == 2 ? 32 : 128) : 0);
     }
 };
 
@@ -618,85 +618,89 @@ gemv_kernel(const GemvArgs A) {
     }
     TS(4);
 
-    // ---- reduction.  Slot layout: value v = (r*NT + j)*ACC + c of lane l at float index v*32 + l.
+    // ---- reduction.  Slot layout: value v = (r*NT + j)*ACC + c of live lane l at float index v*LW + l.
+    // M == 1 (ACC == 2): only column 0 exists, i.e. only the lanes with t == 0 hold outputs (LW = 8).
+    constexpr int LW = (ACC == 2) ? 8 : 32;
+    constexpr int NVL = NV * LW;                       // floats per matrix and warp
     // 1) every warp parks its fragment in its own (now idle) ring
     float* slot = reinterpret_cast<float*>(smem + warp * S::kWarpBytes);
+    if (ACC != 2 || t == 0) {
+        const int l = (ACC == 2) ? g : lane;
 #pragma unroll
-    for (int mt = 0; mt < NM; mt++)
+        for (int mt = 0; mt < NM; mt++)
 #pragma unroll
-        for (int r = 0; r < RG_TILES; r++)
+            for (int r = 0; r < RG_TILES; r++)
 #pragma unroll
-            for (int j = 0; j < NT; j++)
+                for (int j = 0; j < NT; j++)
 #pragma unroll
-                for (int c = 0; c < ACC; c++) slot[(mt * NV + (r * NT + j) * ACC + c) * 32 + lane] = accm[mt][r][j][c];
-    __syncthreads();
-    // 2) the CTA's sum lands in warp 0's slot (fixed warp order)
-    float* cta = reinterpret_cast<float*>(smem);
-    for (int i = threadIdx.x; i < NVT * 32; i += GEMV_WARPS * 32) {
-        float v = cta[i];
-#pragma unroll
-        for (int w = 1; w < GEMV_WARPS; w++) v += reinterpret_cast<const float*>(smem + w * S::kWarpBytes)[i];
-        cta[i] = v;
+                    for (int c = 0; c < ACC; c++) slot[mt * NVL + ((r * NT + j) * ACC + c) * LW + l] = accm[mt][r][j][c];
     }
-    // 3) across the cluster, always in rank order.  M <= 8: every peer pushes its CTA sum into the
-    //    leader's receive buffer with st.async (completion counted on the leader's mbarrier) and exits;
-    //    the leader waits for the bytes, adds and stores.  Larger M: the leader pulls through
-    //    ld.shared::cluster between two cluster barriers.
+    __syncthreads();
     const int64_t N = A.G.rows;
     auto store_value = [&](int i, float v) {
-        const int l = i & 31, val = i >> 5, c = val % ACC, j = (val / ACC) % NT, r = val / (ACC * NT);
-        const int gg = l >> 2, tt = l & 3;
+        const int l = i % LW, val = i / LW, c = val % ACC, j = (val / ACC) % NT, r = val / (ACC * NT);
+        const int gg = (ACC == 2) ? l : (l >> 2), tt = (ACC == 2) ? 0 : (l & 3);
         const int hi = (ACC == 2) ? c : (c >> 1);                     // row g (0) or g+8 (1)
         const int col = 8 * j + 2 * tt + ((ACC == 2) ? 0 : (c & 1));
         const int64_t row = (int64_t)rg * RG_ROWS + r * 16 + gg + 8 * hi;
-        if (col < A.M && (ACC != 2 || tt == 0))
+        if (col < A.M)
             store_out(A.y, A.y_dtype, (MODE == 1 ? (int64_t)blockIdx.z * N : (int64_t)col * N) + row, v, A.bias, row, A.accumulate);
     };
-    // value i of matrix mt lives at float index mt*NV*32 + i; NV*32 is a multiple of the block size, so the
-    // thread that owns i owns it for both matrices and can apply act(gate) * up itself
-    auto finish = [&](int i, const float (&vm)[NM]) {
+    auto finish = [&](int i, const float (&vm)[NM]) {  // both matrices' sums of output i are in one thread
         const float v = NM == 2 ? apply_act(vm[0], A.act) * vm[NM - 1] : vm[0];
         store_value(i, MODE == 1 ? v * out_scale : v);
     };
-    if (nsplit == 1) {
-        for (int i = threadIdx.x; i < NV * 32; i += GEMV_WARPS * 32) {
-            float vm[NM];
-#pragma unroll
-            for (int mt = 0; mt < NM; mt++) vm[mt] = cta[mt * NV * 32 + i];
-            finish(i, vm);
-        }
-    } else if (PUSH) {
+    // 2) the CTA's sums (fixed warp order): thread i owns output i of every matrix from here on
+    // 3) across the cluster, always in rank order.  M <= 8: every peer pushes its CTA sums into the
+    //    leader's receive buffer with st.async (completion counted on the leader's mbarrier) and exits;
+    //    the leader waits for the bytes, adds and stores.  Larger M: the leader pulls through
+    //    ld.shared::cluster between two cluster barriers.
+    float* cta = reinterpret_cast<float*>(smem);
+    if (PUSH && nsplit > 1) {
         asm volatile("barrier.cluster.wait.aligned;" ::: "memory");   // the leader's barrier init is visible
-        if (slice != 0) {
-            const uint32_t rb = map_to_rank(rbar, 0);
-            for (int i = threadIdx.x; i < NVT * 32; i += GEMV_WARPS * 32)
-                st_async_f32(map_to_rank(smem_u32(recv + (slice - 1) * (NVT * 32) + i), 0), cta[i], rb);
-        } else {
-            if (threadIdx.x == 0) mbar_expect_tx(rbar, (uint32_t)((nsplit - 1) * NVT * 32 * 4));
-            mbar_wait(rbar, 0);
-            for (int i = threadIdx.x; i < NV * 32; i += GEMV_WARPS * 32) {
-                float vm[NM];
+        if (slice == 0 && threadIdx.x == 0) mbar_expect_tx(rbar, (uint32_t)((nsplit - 1) * NM * NVL * 4));
+    }
+    for (int i = threadIdx.x; i < NVL; i += GEMV_WARPS * 32) {
+        float vm[NM];
 #pragma unroll
-                for (int mt = 0; mt < NM; mt++) {
-                    float v = cta[mt * NV * 32 + i];
-                    for (int rk = 1; rk < nsplit; rk++) v += recv[(rk - 1) * (NVT * 32) + mt * NV * 32 + i];
-                    vm[mt] = v;
-                }
+        for (int mt = 0; mt < NM; mt++) {
+            float v = cta[mt * NVL + i];
+#pragma unroll
+            for (int w = 1; w < GEMV_WARPS; w++) v += reinterpret_cast<const float*>(smem + w * S::kWarpBytes)[mt * NVL + i];
+            vm[mt] = v;
+        }
+        if (nsplit == 1) {
+            finish(i, vm);
+        } else if (PUSH) {
+            if (slice != 0) {
+                const uint32_t rb = map_to_rank(rbar, 0);
+#pragma unroll
+                for (int mt = 0; mt < NM; mt++)
+                    st_async_f32(map_to_rank(smem_u32(recv + (slice - 1) * (NM * NVL) + mt * NVL + i), 0), vm[mt], rb);
+            } else {
+                mbar_wait(rbar, 0);
+#pragma unroll
+                for (int mt = 0; mt < NM; mt++)
+                    for (int rk = 1; rk < nsplit; rk++) vm[mt] += recv[(rk - 1) * (NM * NVL) + mt * NVL + i];
                 finish(i, vm);
             }
+        } else {
+#pragma unroll
+            for (int mt = 0; mt < NM; mt++) cta[mt * NVL + i] = vm[mt];
         }
-    } else {
+    }
+    if (!PUSH && nsplit > 1) {
         cluster_sync_all();
         if (slice == 0) {
-            for (int i = threadIdx.x; i < NV * 32; i += GEMV_WARPS * 32) {
+            for (int i = threadIdx.x; i < NVL; i += GEMV_WARPS * 32) {
                 float vm[NM];
 #pragma unroll
                 for (int mt = 0; mt < NM; mt++) {
                     float pv[GEMV_MAX_SPLIT - 1];
 #pragma unroll
                     for (int rk = 1; rk < GEMV_MAX_SPLIT; rk++)      // all remote loads in flight before the adds
-                        pv[rk - 1] = rk < nsplit ? ld_dsmem_f32(smem_u32(cta + mt * NV * 32 + i), (uint32_t)rk) : 0.0f;
-                    float v = cta[mt * NV * 32 + i];
+                        pv[rk - 1] = rk < nsplit ? ld_dsmem_f32(smem_u32(cta + mt * NVL + i), (uint32_t)rk) : 0.0f;
+                    float v = cta[mt * NVL + i];
 #pragma unroll
                     for (int rk = 1; rk < GEMV_MAX_SPLIT; rk++) v += pv[rk - 1];
                     vm[mt] = v;
