@@ -48,7 +48,7 @@ def _newest_header():
 
 def _compile(src, verbose, extra):
     obj = os.path.join(OBJ, src[:-3] + ".o")
-    cmd = [_nvcc()] + NVCC_FLAGS + extra + ["-c", os.path.join(CSRC, src), "-o", obj]
+    cmd = [_nvcc()] + NVCC_FLAGS + extra + os.environ.get("LOWBIT_NVCC_EXTRA", "").split() + ["-c", os.path.join(CSRC, src), "-o", obj]
     if verbose:
         print(" ".join(cmd), flush=True)
     r = subprocess.run(cmd, capture_output=True, text=True)

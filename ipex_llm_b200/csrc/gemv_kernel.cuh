@@ -51,7 +51,11 @@ __device__ __forceinline__ unsigned long long gtime() {
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
     return t;
 }
+#ifdef LOWBIT_GEMV_TIMESTAMPS     // development builds only: the checks cost issue slots in every warp
 #define TS(i) do { if (A.ts && lane == 0) A.ts[wid * 8 + (i)] = gtime(); } while (0)
+#else
+#define TS(i) do { } while (0)
+#endif
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
 __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
@@ -221,17 +225,29 @@ template <bool BF> struct Codec<QT_FP6, BF> {
 template <int QT, bool BF> struct Staging {
     using C = Codec<QT, BF>;
     static constexpr int kSuperCodes = RG_TILES * C::kTileBytes;                  // 2048 / 4096 / 3072
+#ifndef LOWBIT_GEMV_CH
     static constexpr int kChunk = kSuperCodes <= 2048 ? 2 : 1;                    // ~4 KB of codes per bulk copy
+#else
+    static constexpr int kChunk = LOWBIT_GEMV_CH;
+#endif
+#ifndef LOWBIT_GEMV_STAGES
     static constexpr int kStages = 2;
+#else
+    static constexpr int kStages = LOWBIT_GEMV_STAGES;
+#endif
     static constexpr int kMinBytes = (C::kOffset == 2) ? 128 : 0;
     static constexpr int kStageBytes = kChunk * (kSuperCodes + 128 + kMinBytes);
     static constexpr int kRingBytes = kStages * kStageBytes;
-    static constexpr int kWarpBytes = kRingBytes > 8192 ? kRingBytes : 8192;      // also holds the reduction slot (<= 8 KB)
     static constexpr int kBarBytes = GEMV_WARPS * kStages * 8 + 8;                // + the leader's receive barrier
-    // + the leader CTA's receive buffer for its peers' CTA sums (push reduction, M <= 8 kernels):
-    // (split-1) x NV x 32 floats
+    // bytes of one matrix' accumulators of one warp in the reduction slot (M == 1: 8 live lanes per value)
+    __host__ __device__ static constexpr int slot_bytes(int nt, int acc) { return RG_TILES * nt * acc * (acc == 2 ? 32 : 128); }
+    // a warp's region: its ring, which later holds its reduction slot
+    __host__ __device__ static constexpr int warp_bytes(int nt, int acc, int nm) {
+        return ((kRingBytes > nm * slot_bytes(nt, acc) ? kRingBytes : nm * slot_bytes(nt, acc)) + 127) / 128 * 128;
+    }
+    // + the leader CTA's receive buffer for its peers' CTA sums (push reduction, M <= 8 kernels)
     static constexpr int smem_bytes(int nt, int acc, int nm) {
-        return GEMV_WARPS * kWarpBytes + kBarBytes + 8 + (nt == 1 ? (GEMV_MAX_SPLIT - 1) * (nm * RG_TILES * acc) * (acc == 2 ? 32 : 128) : 0);
+        return GEMV_WARPS * warp_bytes(nt, acc, nm) + kBarBytes + 8 + (nt == 1 ? (GEMV_MAX_SPLIT - 1) * nm * slot_bytes(nt, acc) : 0);
     }
 };
 
@@ -269,7 +285,7 @@ __device__ __forceinline__ float ld_dsmem_f32(uint32_t local_addr, uint32_t rank
 // expert per blockIdx.z (used with NM = 2 for gate/up), 2 = the routed experts' down projections
 // concatenated along K, each slot's sums weighted by its routing weight.
 template <int QT, bool BF, int NS, int NT, int ACC, int NM, int MODE>
-__global__ void __launch_bounds__(GEMV_WARPS * 32)
+__global__ void __launch_bounds__(GEMV_WARPS * 32, (NT == 1 && NS == 1) ? 6 : 1)
 gemv_kernel(const GemvArgs A) {
     using C = Codec<QT, BF>;
     using S = Staging<QT, BF>;
@@ -278,7 +294,7 @@ gemv_kernel(const GemvArgs A) {
     constexpr int SUPER = S::kSuperCodes;
     constexpr int NV = RG_TILES * NT * ACC;            // accumulator floats per lane and matrix
     constexpr int NVT = NM * NV;
-    static_assert(NVT * 128 <= S::kWarpBytes, "reduction slot must fit in the warp's ring");
+    constexpr int WB = S::warp_bytes(NT, ACC, NM);     // bytes of one warp's ring / reduction slot
     extern __shared__ __align__(128) uint8_t smem[];
 
     // the warp index through a shuffle: the compiler then knows it is warp-uniform and keeps everything
@@ -310,8 +326,9 @@ gemv_kernel(const GemvArgs A) {
     }
 
     // this CTA's k-blocks [ck0, ck1), this warp's [kb0, kb1)
-    const int ck0 = (int)((unsigned)slice * (unsigned)nbt / (unsigned)nsplit);
-    const int ck1 = (int)((unsigned)(slice + 1) * (unsigned)nbt / (unsigned)nsplit);
+    // (the host passes nbt / nsplit and nbt % nsplit: the first `rem` slices take one block more)
+    const int ck0 = slice * A.slice_q + min(slice, A.slice_r);
+    const int ck1 = ck0 + A.slice_q + (slice < A.slice_r ? 1 : 0);
     const int kb0 = ck0 + (int)((unsigned)warp * (unsigned)(ck1 - ck0) / (unsigned)GEMV_WARPS);
     const int kb1 = ck0 + (int)((unsigned)(warp + 1) * (unsigned)(ck1 - ck0) / (unsigned)GEMV_WARPS);
     const int n_super = kb1 - kb0;
@@ -333,13 +350,12 @@ gemv_kernel(const GemvArgs A) {
     TS(0);
 
     // this warp's private ring: [STAGES][codes | scales | mins]; the mbarriers sit after all rings
-    const uint32_t ring = smem_u32(smem) + warp * S::kWarpBytes;
-    const uint32_t bars = smem_u32(smem) + GEMV_WARPS * S::kWarpBytes + warp * (STAGES * 8);
+    const uint32_t ring = smem_u32(smem) + warp * WB;
+    const uint32_t bars = smem_u32(smem) + GEMV_WARPS * WB + warp * (STAGES * 8);
     // issue cursor: walks the segment list one chunk at a time.  Warp-uniform state, called by the whole
     // warp; one elected lane issues the copies.
-    static_assert((STAGES & (STAGES - 1)) == 0, "stage index is a mask of the chunk counter");
     int i_mt = 0, i_z = z_first, i_left = 0;
-    unsigned i_c = 0;
+    uint32_t i_st = 0;                                 // stage the next chunk goes to
     const uint8_t* i_q = nullptr;                      // next chunk's codes; scales / mins follow at fixed offsets
     const uint8_t* i_s = nullptr;
     bool i_live = n_super > 0;
@@ -356,15 +372,15 @@ gemv_kernel(const GemvArgs A) {
     auto issue_next = [&]() {                          // copy the cursor's chunk into stage i_c % STAGES, advance
         if (!i_live) return;
         const int ns = min(CH, i_left);
-        const uint32_t st = i_c & (STAGES - 1);
-        const uint32_t dst = ring + st * STAGE_BYTES, bar = bars + st * 8;
+        const uint32_t dst = ring + i_st * STAGE_BYTES, bar = bars + i_st * 8;
         if (elect_one()) {
             mbar_expect_tx(bar, ns * (SUPER + 128 + S::kMinBytes));
             bulk_g2s(dst, i_q, ns * SUPER, bar);
             bulk_g2s(dst + CH * SUPER, i_s, ns * 128, bar);
             if (S::kMinBytes) bulk_g2s(dst + CH * (SUPER + 128), i_s + s_to_m, ns * 128, bar);
         }
-        i_c++; i_left -= CH;
+        i_st = (i_st + 1 == STAGES) ? 0 : i_st + 1;
+        i_left -= CH;
         i_q += CH * SUPER; i_s += CH * 128;
         if (i_left <= 0) {
             if (NM == 1 && MODE != 2) i_live = false;
@@ -376,8 +392,8 @@ gemv_kernel(const GemvArgs A) {
     };
 
     constexpr bool PUSH = (NT == 1);                   // peers push their sums into the leader (else the leader pulls)
-    const uint32_t rbar = smem_u32(smem) + GEMV_WARPS * S::kWarpBytes + GEMV_WARPS * STAGES * 8;
-    float* recv = reinterpret_cast<float*>(smem + GEMV_WARPS * S::kWarpBytes + S::kBarBytes + 8);
+    const uint32_t rbar = smem_u32(smem) + GEMV_WARPS * WB + GEMV_WARPS * STAGES * 8;
+    float* recv = reinterpret_cast<float*>(smem + GEMV_WARPS * WB + S::kBarBytes + 8);
     if (PUSH && nsplit > 1) {
         if (slice == 0 && threadIdx.x == 0) {
             mbar_init(rbar, 1);
@@ -425,7 +441,10 @@ gemv_kernel(const GemvArgs A) {
                 for (int c = 0; c < ACC; c++) accm[mt][r][j][c] = 0.0f;
 
     // lane (g,t) reads x[8j+g][kb*64 + 16t .. +15] for n-tile j (plane p); rows >= M read as zero
-    const char* xptr[NT][NS];
+    int64_t xptr[NT][NS];
+    // per-lane address of the fragment of n-tile 0 / plane 0 that is fetched next (advances 128 B per k-block)
+    const char* const xbase = reinterpret_cast<const char*>(A.x + (int64_t)g * A.G.k + t * 16) + (size_t)kb0 * 128;
+    const char* xrun = xbase;
     bool xvalid[NT];
     constexpr bool XPF = (NT * NS <= 3);
     constexpr int XPF_BUFS = XPF ? 2 : 1;
@@ -437,27 +456,26 @@ gemv_kernel(const GemvArgs A) {
         xvalid[j] = (8 * j + g) < A.M;
 #pragma unroll
         for (int p = 0; p < NS; p++) {
-            xptr[j][p] = reinterpret_cast<const char*>(A.x + p * A.plane_stride + (int64_t)(8 * j + g) * A.G.k + t * 16) +
-                         (size_t)kb0 * 128;
+            xptr[j][p] = (int64_t)2 * (p * A.plane_stride + (int64_t)(8 * j) * A.G.k);   // warp-uniform byte offset
 #pragma unroll
             for (int h = 0; h < XPF_BUFS; h++) { xq[h][j][p][0] = make_uint4(0, 0, 0, 0); xq[h][j][p][1] = make_uint4(0, 0, 0, 0); }
         }
     }
-    unsigned xoff = 0;              // byte offset of the current k-block from kb0 inside an x row
     // x comes from L2 (each warp reads its own K slice; L1 is cold): the fragment of the NEXT k-block is
     // requested one super-tile ahead so that the ~0.4 us round trip hides behind the current one
     int xleft = 0;
-    auto fetch_x = [&](uint4 (&dst)[NT][NS][2], unsigned off) {
+    auto fetch_x = [&](uint4 (&dst)[NT][NS][2]) {      // fetch the k-block at xrun, advance
 #pragma unroll
         for (int j = 0; j < NT; j++)
 #pragma unroll
             for (int p = 0; p < NS; p++)
                 if (xvalid[j]) {                        // L1/L2-cached: x is shared by every row group
-                    dst[j][p][0] = ldg_cached16(xptr[j][p] + off);
-                    dst[j][p][1] = ldg_cached16(xptr[j][p] + off + 16);
+                    dst[j][p][0] = ldg_cached16(xrun + xptr[j][p]);
+                    dst[j][p][1] = ldg_cached16(xrun + xptr[j][p] + 16);
                 }
+        xrun += 128;
     };
-    if (XPF && n_super > 0) fetch_x(xq[0], 0u);
+    if (XPF && n_super > 0) fetch_x(xq[0]);
 
     uint32_t ones[4];
     ones[0] = ones[1] = ones[2] = ones[3] = BF ? 0x3f803f80u : 0x3c003c00u;
@@ -470,12 +488,13 @@ gemv_kernel(const GemvArgs A) {
 #pragma unroll
             for (int q = 0; q < ACC; q++) tot[r][j][q] = 0.0f;
 
-    unsigned c = 0;                                    // chunks consumed so far (stage and phase follow from it)
+    uint32_t c_st = 0, c_ph = 0;                       // stage and mbarrier phase of the chunk being consumed
+    bool first_chunk = true;
 #pragma unroll
     for (int mt = 0; mt < NM; mt++) {
     float (&acc)[RG_TILES][NT][ACC] = accm[mt];
-    xoff = 0;
     xleft = n_super;
+    if (!XPF) xrun = xbase;
     for (int z = z_first; z <= z_last; z++) {
     int s_a, s_n;
     const uint8_t* s_base;
@@ -487,10 +506,9 @@ gemv_kernel(const GemvArgs A) {
             if (h == 0 || sidx + 1 < s_n) {
                 const int i = (CH == 2) ? h : 0;                  // super-tile index inside its stage
                 if (i == 0) {
-                    const uint32_t st = c & (STAGES - 1);
-                    stage = ring + st * STAGE_BYTES;
-                    mbar_wait(bars + st * 8, (c / STAGES) & 1u);
-                    if (c == 0) TS(3);
+                    stage = ring + c_st * STAGE_BYTES;
+                    mbar_wait(bars + c_st * 8, c_ph);
+                    if (first_chunk) { TS(3); first_chunk = false; }
                 }
                 const bool last_of_stage = (i == CH - 1) || (sidx + h == s_n - 1);
                 const uint32_t codes = stage + i * SUPER;
@@ -498,12 +516,14 @@ gemv_kernel(const GemvArgs A) {
                 // ---- once per super-tile: x fragment, sum(x), scales of the lane's 8 rows
                 if (XPF) {
                     xleft--;
-                    if (xleft > 0) fetch_x(xq[XPF ? (h ^ 1) : 0], xoff + 128u);
-                    else if (mt + 1 < NM) fetch_x(xq[XPF ? (h ^ 1) : 0], 0u);   // the second matrix starts over at the slice's first block
+                    if (xleft > 0) fetch_x(xq[XPF ? (h ^ 1) : 0]);
+                    else if (mt + 1 < NM) {            // the second matrix starts over at the slice's first block
+                        xrun = xbase;
+                        fetch_x(xq[XPF ? (h ^ 1) : 0]);
+                    }
                 } else {
-                    fetch_x(xb, xoff);
+                    fetch_x(xb);
                 }
-                xoff += 128u;
                 // -8 * sum over the k-block of x (sym) / sum (asym) for columns 2t, 2t+1: a ones-row mma,
                 // two independent chains (the tensor pipe is ~13 % busy in this kernel; issue slots are scarce)
                 float xs[NT][2];
@@ -579,7 +599,7 @@ gemv_kernel(const GemvArgs A) {
                     // every lane has consumed the stage (its data sits in registers already used): refill it
                     __syncwarp();
                     issue_next();
-                    c++;
+                    if (++c_st == STAGES) { c_st = 0; c_ph ^= 1u; }
                 }
             }
         }
@@ -623,7 +643,7 @@ gemv_kernel(const GemvArgs A) {
     constexpr int LW = (ACC == 2) ? 8 : 32;
     constexpr int NVL = NV * LW;                       // floats per matrix and warp
     // 1) every warp parks its fragment in its own (now idle) ring
-    float* slot = reinterpret_cast<float*>(smem + warp * S::kWarpBytes);
+    float* slot = reinterpret_cast<float*>(smem + warp * WB);
     if (ACC != 2 || t == 0) {
         const int l = (ACC == 2) ? g : lane;
 #pragma unroll
@@ -666,7 +686,7 @@ gemv_kernel(const GemvArgs A) {
         for (int mt = 0; mt < NM; mt++) {
             float v = cta[mt * NVL + i];
 #pragma unroll
-            for (int w = 1; w < GEMV_WARPS; w++) v += reinterpret_cast<const float*>(smem + w * S::kWarpBytes)[mt * NVL + i];
+            for (int w = 1; w < GEMV_WARPS; w++) v += reinterpret_cast<const float*>(smem + w * WB)[mt * NVL + i];
             vm[mt] = v;
         }
         if (nsplit == 1) {
@@ -756,6 +776,8 @@ static void launch_kernel(K kernel, int smem, int64_t groups, int64_t nb, const 
                           int (&cache)[8], int grid_z = 1) {
     // nb = k-blocks one cluster splits; the cluster count that has to fit in one wave is groups * grid_z
     const int split = pick_split(kernel, smem, groups * grid_z, nb, cache);
+    GemvArgs B = A;
+    B.slice_q = (int)(nb / split); B.slice_r = (int)(nb % split);
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)split, (unsigned)groups, (unsigned)grid_z);
     cfg.blockDim = dim3(GEMV_WARPS * 32); cfg.dynamicSmemBytes = smem; cfg.stream = st;
@@ -770,7 +792,7 @@ static void launch_kernel(K kernel, int smem, int64_t groups, int64_t nb, const 
         na++;
     }
     cfg.attrs = at; cfg.numAttrs = na;
-    cudaLaunchKernelEx(&cfg, kernel, A);
+    cudaLaunchKernelEx(&cfg, kernel, B);
 }
 
 template <int QT, bool BF, int NS>
