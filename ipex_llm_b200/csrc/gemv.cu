@@ -14,6 +14,7 @@ void gemv_launch_asym_int4(int x_dtype, int m, int64_t groups, int64_t nb, const
 void gemv_launch_fp8_e4m3(int x_dtype, int m, int64_t groups, int64_t nb, const GemvArgs& A, cudaStream_t st);
 void gemv_launch_fp8_e5m2(int x_dtype, int m, int64_t groups, int64_t nb, const GemvArgs& A, cudaStream_t st);
 void gemv_launch_fp6(int x_dtype, int m, int64_t groups, int64_t nb, const GemvArgs& A, cudaStream_t st);
+void gemv_launch_nf4(int x_dtype, int m, int64_t groups, int64_t nb, const GemvArgs& A, cudaStream_t st);
 
 // ------------------------------------------------------------------ generic (any qtype, tail rows)
 // one warp per output row, scalar decode; used for nf4 until its mma codec lands, and for the
@@ -96,7 +97,7 @@ size_t gemv_workspace_size(int64_t n_rows, int64_t k, int64_t m, int x_dtype) {
 }
 
 static bool has_mma_codec(int qt) {
-    return qt == QT_SYM_INT4 || qt == QT_ASYM_INT4 || qt == QT_FP8_E4M3 || qt == QT_FP8_E5M2 || qt == QT_FP6;
+    return qt == QT_SYM_INT4 || qt == QT_ASYM_INT4 || qt == QT_NF4 || qt == QT_FP8_E4M3 || qt == QT_FP8_E5M2 || qt == QT_FP6;
 }
 
 template <typename XT>
@@ -176,6 +177,7 @@ int gemv_launch_ex(const void* w, const void* w2, int act, int qt, int64_t n_row
                 case QT_FP8_E4M3:  gemv_launch_fp8_e4m3(x_dtype, (int)mc, groups, G.nb, A, st); break;
                 case QT_FP8_E5M2:  gemv_launch_fp8_e5m2(x_dtype, (int)mc, groups, G.nb, A, st); break;
                 case QT_FP6:       gemv_launch_fp6(x_dtype, (int)mc, groups, G.nb, A, st); break;
+                case QT_NF4:       gemv_launch_nf4(x_dtype, (int)mc, groups, G.nb, A, st); break;
                 default: return LB_ERR_ARG;
             }
             note_launch();
@@ -198,6 +200,7 @@ static int launch_by_qt(int qt, int x_dtype, int m, int64_t groups, int64_t nb, 
         case QT_FP8_E4M3:  gemv_launch_fp8_e4m3(x_dtype, m, groups, nb, A, st); break;
         case QT_FP8_E5M2:  gemv_launch_fp8_e5m2(x_dtype, m, groups, nb, A, st); break;
         case QT_FP6:       gemv_launch_fp6(x_dtype, m, groups, nb, A, st); break;
+        case QT_NF4:       gemv_launch_nf4(x_dtype, m, groups, nb, A, st); break;
         default: return LB_ERR_ARG;
     }
     note_launch();

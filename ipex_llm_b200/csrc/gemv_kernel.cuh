@@ -138,6 +138,8 @@ __device__ __forceinline__ uint32_t h2_to_bf2(uint32_t h) {
 // Tile       : the registers one lane holds for one tile
 // load       : read the lane's part of tile `r` of a staged super-tile from shared memory
 // frag       : A fragment (4 x b32) of k-step s: code values, UNSCALED, offset NOT applied
+// kPlanes    : fragments per k-step whose products add up to the weight (2 for nf4 x bf16: the table
+//              value split into two bf16), kLutBytes: shared-memory table the codec reads through `lut`
 template <int QT, bool BF> struct Codec;
 
 template <bool BF, int OFFSET> struct Codec4 {
@@ -146,10 +148,12 @@ template <bool BF, int OFFSET> struct Codec4 {
     static constexpr int kOffset = OFFSET;
     static constexpr float kLo = BF ? 1.0f : 16777216.0f;    // fp16 path: a0,a2 hold n * 2^-24
     static constexpr float kHi = BF ? 1.0f : 1048576.0f;     //            a1,a3 hold n * 2^-20
+    static constexpr int kPlanes = 1, kLutBytes = 0;
+    __device__ static __forceinline__ void fill_lut(uint8_t*, int) {}
     __device__ static __forceinline__ void load(Tile& t, uint32_t codes, int r, int lane) {
         t.q = lds16(codes + r * 512 + lane * 16);
     }
-    __device__ static __forceinline__ void frag(const Tile& t, int s, uint32_t (&a)[4]) {
+    __device__ static __forceinline__ void frag(const Tile& t, int s, uint32_t (&a)[4], uint32_t, int) {
         const uint32_t w = s == 0 ? t.q.x : s == 1 ? t.q.y : s == 2 ? t.q.z : t.q.w;
         if (!BF) {
             // fp16 subnormals: bits 0x000n = n * 2^-24, bits 0x00n0 = n * 2^-20 (exact, no offset)
@@ -166,6 +170,47 @@ template <bool BF, int OFFSET> struct Codec4 {
     }
 };
 template <bool BF> struct Codec<QT_SYM_INT4, BF> : Codec4<BF, 1> {};
+
+// nf4: w = T[code] * d with the 16-entry NormalFloat table.  Byte b of the lane's word s is the
+// code pair of fragment register a_b (tilednf4_pos), looked up in a 256-entry table of
+// (T[lo], T[hi]) pairs: fp16x2 for fp16 activations (table values rounded to fp16: 2^-12 relative),
+// two bf16x2 planes (value = hi + lo part, 2^-17) for bf16.  8 copies of every entry (32 bytes per
+// entry, copy = lane % 8) keep the lookups of a warp nearly free of bank conflicts.
+template <bool BF> struct Codec<QT_NF4, BF> {
+    struct Tile { uint4 q; };
+    static constexpr int kTileBytes = 512;
+    static constexpr int kOffset = 0;
+    static constexpr float kLo = 1.0f, kHi = 1.0f;
+    static constexpr int kPlanes = BF ? 2 : 1, kLutBytes = kPlanes * 8192;
+    __device__ static __forceinline__ uint32_t entry(int e, int plane) {
+        const float lo = kNF4Table[e & 15], hi = kNF4Table[e >> 4];
+        if (!BF) return h2_as_u32(__floats2half2_rn(lo, hi));
+        const __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
+        if (plane == 0) return bf2_as_u32(h);
+        const float2 hf = __bfloat1622float2(h);
+        return bf2_as_u32(__floats2bfloat162_rn(lo - hf.x, hi - hf.y));
+    }
+    __device__ static __forceinline__ void fill_lut(uint8_t* lut, int tid) {   // 128 threads, 256 entries per plane
+#pragma unroll
+        for (int plane = 0; plane < kPlanes; plane++)
+            for (int e = tid; e < 256; e += GEMV_WARPS * 32) {
+                const uint32_t v = entry(e, plane);
+                uint4* dst = reinterpret_cast<uint4*>(lut + plane * 8192 + e * 32);
+                dst[0] = make_uint4(v, v, v, v); dst[1] = make_uint4(v, v, v, v);
+            }
+    }
+    __device__ static __forceinline__ void load(Tile& t, uint32_t codes, int r, int lane) {
+        t.q = lds16(codes + r * 512 + lane * 16);
+    }
+    // lut = table address + 4 * (lane % 8)
+    __device__ static __forceinline__ void frag(const Tile& t, int s, uint32_t (&a)[4], uint32_t lut, int plane) {
+        const uint32_t w = s == 0 ? t.q.x : s == 1 ? t.q.y : s == 2 ? t.q.z : t.q.w;
+        a[0] = lds4(lut + plane * 8192 + ((w << 5) & 0x1fe0u));
+        a[1] = lds4(lut + plane * 8192 + ((w >> 3) & 0x1fe0u));
+        a[2] = lds4(lut + plane * 8192 + ((w >> 11) & 0x1fe0u));
+        a[3] = lds4(lut + plane * 8192 + ((w >> 19) & 0x1fe0u));
+    }
+};
 template <bool BF> struct Codec<QT_ASYM_INT4, BF> : Codec4<BF, 2> {};
 
 template <int QT, bool BF> struct Codec8 {
@@ -173,6 +218,8 @@ template <int QT, bool BF> struct Codec8 {
     static constexpr int kTileBytes = 1024;
     static constexpr int kOffset = 0;
     static constexpr float kLo = 1.0f, kHi = 1.0f;
+    static constexpr int kPlanes = 1, kLutBytes = 0;
+    __device__ static __forceinline__ void fill_lut(uint8_t*, int) {}
     __device__ static __forceinline__ void load(Tile& t, uint32_t codes, int r, int lane) {
         t.q0 = lds16(codes + r * 1024 + lane * 16);
         t.q1 = lds16(codes + r * 1024 + 512 + lane * 16);
@@ -187,7 +234,7 @@ template <int QT, bool BF> struct Codec8 {
         }
         return BF ? h2_to_bf2(h) : h;
     }
-    __device__ static __forceinline__ void frag(const Tile& t, int s, uint32_t (&a)[4]) {
+    __device__ static __forceinline__ void frag(const Tile& t, int s, uint32_t (&a)[4], uint32_t, int) {
         const uint32_t w0 = s == 0 ? t.q0.x : s == 1 ? t.q0.y : s == 2 ? t.q0.z : t.q0.w;
         const uint32_t w1 = s == 0 ? t.q1.x : s == 1 ? t.q1.y : s == 2 ? t.q1.z : t.q1.w;
         a[0] = pair(w0, 0); a[1] = pair(w1, 0); a[2] = pair(w0, 1); a[3] = pair(w1, 1);
@@ -201,6 +248,8 @@ template <bool BF> struct Codec<QT_FP6, BF> {
     static constexpr int kTileBytes = 768;
     static constexpr int kOffset = 0;
     static constexpr float kLo = 1.0f, kHi = 1.0f;
+    static constexpr int kPlanes = 1, kLutBytes = 0;
+    __device__ static __forceinline__ void fill_lut(uint8_t*, int) {}
     __device__ static __forceinline__ void load(Tile& t, uint32_t codes, int r, int lane) {
         t.lo = lds16(codes + r * 768 + lane * 16);
         t.hi = lds8(codes + r * 768 + 512 + lane * 8);
@@ -210,7 +259,7 @@ template <bool BF> struct Codec<QT_FP6, BF> {
         asm("cvt.rn.f16x2.e3m2x2 %0, %1;" : "=r"(h) : "h"(two));
         return BF ? h2_to_bf2(h) : h;
     }
-    __device__ static __forceinline__ void frag(const Tile& t, int s, uint32_t (&a)[4]) {
+    __device__ static __forceinline__ void frag(const Tile& t, int s, uint32_t (&a)[4], uint32_t, int) {
         const int u = s >> 1;
         const uint32_t l0 = u ? t.lo.y : t.lo.x, l1 = u ? t.lo.w : t.lo.z;
         const uint32_t sh = (s & 1) ? 4u : 0u;
@@ -247,7 +296,11 @@ template <int QT, bool BF> struct Staging {
     }
     // + the leader CTA's receive buffer for its peers' CTA sums (push reduction, M <= 8 kernels)
     static constexpr int smem_bytes(int nt, int acc, int nm) {
-        return GEMV_WARPS * warp_bytes(nt, acc, nm) + kBarBytes + 8 + (nt == 1 ? (GEMV_MAX_SPLIT - 1) * nm * slot_bytes(nt, acc) : 0);
+        return lut_offset(nt, acc, nm) + C::kLutBytes;
+    }
+    // the codec's lookup table (if any) sits last, 32-byte aligned
+    __host__ __device__ static constexpr int lut_offset(int nt, int acc, int nm) {
+        return (GEMV_WARPS * warp_bytes(nt, acc, nm) + kBarBytes + 8 + (nt == 1 ? (GEMV_MAX_SPLIT - 1) * nm * slot_bytes(nt, acc) : 0) + 31) / 32 * 32;
     }
 };
 
@@ -285,7 +338,7 @@ __device__ __forceinline__ float ld_dsmem_f32(uint32_t local_addr, uint32_t rank
 // expert per blockIdx.z (used with NM = 2 for gate/up), 2 = the routed experts' down projections
 // concatenated along K, each slot's sums weighted by its routing weight.
 template <int QT, bool BF, int NS, int NT, int ACC, int NM, int MODE>
-__global__ void __launch_bounds__(GEMV_WARPS * 32, (NT == 1 && NS == 1) ? 6 : 1)
+__global__ void __launch_bounds__(GEMV_WARPS * 32, (NT == 1 && NS == 1) ? (Codec<QT, BF>::kLutBytes ? 4 : 6) : 1)
 gemv_kernel(const GemvArgs A) {
     using C = Codec<QT, BF>;
     using S = Staging<QT, BF>;
@@ -352,6 +405,12 @@ gemv_kernel(const GemvArgs A) {
     // this warp's private ring: [STAGES][codes | scales | mins]; the mbarriers sit after all rings
     const uint32_t ring = smem_u32(smem) + warp * WB;
     const uint32_t bars = smem_u32(smem) + GEMV_WARPS * WB + warp * (STAGES * 8);
+    // the codec's lookup table (nf4): built once per CTA, read-only afterwards
+    const uint32_t lut = smem_u32(smem) + S::lut_offset(NT, ACC, NM) + 4 * (lane & 7);
+    if (C::kLutBytes) {
+        C::fill_lut(smem + S::lut_offset(NT, ACC, NM), threadIdx.x);
+        __syncthreads();
+    }
     // issue cursor: walks the segment list one chunk at a time.  Warp-uniform state, called by the whole
     // warp; one elected lane issues the copies.
     int i_mt = 0, i_z = z_first, i_left = 0;
@@ -558,15 +617,18 @@ gemv_kernel(const GemvArgs A) {
                 for (int s = 0; s < 4; s++) {
 #pragma unroll
                     for (int r = 0; r < RG_TILES; r++) {
-                        uint32_t a[4];
-                        C::frag(tile[r], s, a);
 #pragma unroll
-                        for (int j = 0; j < NT; j++)
+                        for (int pw = 0; pw < C::kPlanes; pw++) {
+                            uint32_t a[4];
+                            C::frag(tile[r], s, a, lut, pw);
 #pragma unroll
-                            for (int p = 0; p < NS; p++) {
-                                const uint4 v = xb[j][p][s >> 1];
-                                mma16816<BF>(cc[r][j], a, (s & 1) ? v.z : v.x, (s & 1) ? v.w : v.y);
-                            }
+                            for (int j = 0; j < NT; j++)
+#pragma unroll
+                                for (int p = 0; p < NS; p++) {
+                                    const uint4 v = xb[j][p][s >> 1];
+                                    mma16816<BF>(cc[r][j], a, (s & 1) ? v.z : v.x, (s & 1) ? v.w : v.y);
+                                }
+                        }
                     }
                 }
 #pragma unroll
@@ -752,6 +814,9 @@ static float occupancy_fraction() {
 template <typename K>
 static int pick_split(K kernel, int smem, int64_t groups, int64_t nb, int (&cache)[8]) {
     static const int sizes[8] = {8, 7, 6, 5, 4, 3, 2, 1};
+    static int forced = -1;                              // development: LOWBIT_GEMV_SPLIT pins the cluster size
+    if (forced < 0) { const char* e = getenv("LOWBIT_GEMV_SPLIT"); forced = e ? atoi(e) : 0; }
+    if (forced >= 1 && forced <= 8 && (int64_t)forced * GEMV_WARPS <= nb) return forced;
     for (int i = 0; i < 8; i++) {
         const int sz = sizes[i];
         if (sz > 1 && (int64_t)sz * GEMV_WARPS > nb) continue;

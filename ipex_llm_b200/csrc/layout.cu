@@ -48,7 +48,12 @@ __global__ void relayout_to_tiled_kernel(const uint8_t* __restrict__ src, uint8_
                     for (int s = 0; s < 4; s++)
                         out |= ((canonical_code(qt, rec(g + 8 * h), 16 * t + 4 * s + i) >> 4) & 0x03) << (2 * s);
                 }
-            } else {  // 4-bit types
+            } else if (qt == QT_NF4) {  // byte = fragment register: pair of codes (tilednf4_pos)
+                const int l = off >> 4, s = (off & 15) >> 2, pb = off & 3;
+                const int g = l >> 2, t = l & 3, h = pb & 1, ihi = pb >> 1;
+                for (int sub = 0; sub < 2; sub++)
+                    out |= canonical_code(qt, rec(g + 8 * h), 16 * t + 4 * s + 2 * ihi + sub) << (4 * sub);
+            } else {  // 4-bit integer types
                 const int l = off >> 4, s = (off & 15) >> 2, pb = off & 3;
                 const int g = l >> 2, t = l & 3;
                 for (int sub = 0; sub < 2; sub++) {

@@ -172,6 +172,16 @@ __host__ __device__ inline void tiled4_pos(int r, int j, int& byte_off, int& shi
     byte_off = 16 * (4 * g + t) + 4 * s + (p >> 1);
     shift = (p & 1) * 4;
 }
+// nf4 (table codes): same lane ownership and word s = elements 4s..4s+3 of both rows, but byte b of
+// the word is fragment register a_b of mma.m16n8k16 as a PAIR of codes (low nibble = first element):
+//   byte 0: (g, 4s), (g, 4s+1)   byte 1: (g+8, 4s), (g+8, 4s+1)
+//   byte 2: (g, 4s+2), (g, 4s+3) byte 3: (g+8, 4s+2), (g+8, 4s+3)
+// so that one 256-entry table lookup per byte yields the fp16x2 / bf16x2 register.
+__host__ __device__ inline void tilednf4_pos(int r, int j, int& byte_off, int& shift) {
+    const int g = r & 7, h = r >> 3, t = j >> 4, e = j & 15, s = e >> 2, i = e & 3;
+    byte_off = 16 * (4 * g + t) + 4 * s + h + 2 * (i >> 1);
+    shift = (i & 1) * 4;
+}
 // 8-bit codes: tile = 1024 bytes; half h of the tile (512 bytes) holds rows g+8h; lane's 16
 // bytes hold elements 16t..16t+15 of that row in natural order.
 __host__ __device__ inline int tiled8_pos(int r, int j) {
@@ -202,8 +212,11 @@ __host__ __device__ inline void tiled6_hi_pos(int r, int j, int& byte_off, int& 
 __device__ __forceinline__ uint32_t tiled_code(int qt, const uint8_t* tile, int r, int j) {
     int off, sh;
     switch (qt) {
-        case QT_SYM_INT4: case QT_ASYM_INT4: case QT_NF4:
+        case QT_SYM_INT4: case QT_ASYM_INT4:
             tiled4_pos(r, j, off, sh);
+            return (tile[off] >> sh) & 0x0f;
+        case QT_NF4:
+            tilednf4_pos(r, j, off, sh);
             return (tile[off] >> sh) & 0x0f;
         case QT_FP8_E4M3: case QT_FP8_E5M2:
             return tile[tiled8_pos(r, j)];
