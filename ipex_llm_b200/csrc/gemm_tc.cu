@@ -29,8 +29,9 @@ namespace lowbit {
 
 namespace gemmtc {
 
-constexpr int kStages = 3;
-constexpr int kThreads = 192;
+constexpr int kMaxStages = 6;        // pipeline depth = as many stages as fit in 227 KB, at most this
+constexpr int kDeqWarps = 8;         // dequant (then epilogue) warps: one 16x64 tile of the 128x64 B stage each
+constexpr int kThreads = 64 + 32 * kDeqWarps;
 constexpr int kTileN = 128;          // features per CTA (two 64-row groups)
 constexpr int kTileBytesAB = 128 * 128;   // one 128-row x 64-element 2-byte operand tile
 
@@ -114,8 +115,9 @@ template <int QT> struct Expand;
 template <int OFFSET> struct Expand4 {          // sym_int4 (OFFSET 1) / asym_int4 (OFFSET 2)
     static constexpr int kTileBytes = 512;
     static constexpr bool kHasMin = OFFSET == 2;
+    static constexpr int kLutBytes = 0;
     __device__ static __forceinline__ void run(uint32_t codes, int lane, int s, __half2 dlo, __half2 dhi, __half2 mlo,
-                                               __half2 mhi, uint32_t (&out)[4]) {
+                                               __half2 mhi, uint32_t, uint32_t (&out)[4]) {
         uint32_t w;
         asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w) : "r"(codes + lane * 16 + s * 4));
         const uint32_t w2 = w >> 8;
@@ -152,8 +154,9 @@ template <int QT> struct Expand8 {
         }
         return h;
     }
+    static constexpr int kLutBytes = 0;
     __device__ static __forceinline__ void run(uint32_t codes, int lane, int s, __half2 dlo, __half2 dhi, __half2, __half2,
-                                               uint32_t (&out)[4]) {
+                                               uint32_t, uint32_t (&out)[4]) {
         uint32_t w0, w1;
         asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w0) : "r"(codes + lane * 16 + s * 4));
         asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w1) : "r"(codes + 512 + lane * 16 + s * 4));
@@ -172,8 +175,9 @@ template <> struct Expand<QT_FP6> {
         asm("cvt.rn.f16x2.e3m2x2 %0, %1;" : "=r"(h) : "h"(two));
         return h;
     }
+    static constexpr int kLutBytes = 0;
     __device__ static __forceinline__ void run(uint32_t codes, int lane, int s, __half2 dlo, __half2 dhi, __half2, __half2,
-                                               uint32_t (&out)[4]) {
+                                               uint32_t, uint32_t (&out)[4]) {
         const int u = s >> 1;
         uint32_t l0, l1, h0, h1;
         asm volatile("ld.shared.u32 %0, [%1];" : "=r"(l0) : "r"(codes + lane * 16 + u * 4));
@@ -187,6 +191,32 @@ template <> struct Expand<QT_FP6> {
         out[1] = h2u(__hmul2(u2h(cvt2((unsigned short)(e1 & 0xffffu))), dhi));
         out[2] = h2u(__hmul2(u2h(cvt2((unsigned short)(e0 >> 16))), dlo));
         out[3] = h2u(__hmul2(u2h(cvt2((unsigned short)(e1 >> 16))), dhi));
+    }
+};
+
+// nf4: byte b of the lane's word s is the code pair of out[b] (tilednf4_pos); a 256-entry table of
+// fp16 pairs of NormalFloat values, 8 copies per entry (copy = lane % 8), sits in shared memory.
+template <> struct Expand<QT_NF4> {
+    static constexpr int kTileBytes = 512;
+    static constexpr bool kHasMin = false;
+    static constexpr int kLutBytes = 8192;
+    __device__ static __forceinline__ void fill_lut(uint8_t* lut, int tid, int nthreads) {
+        for (int e = tid; e < 256; e += nthreads) {
+            const uint32_t v = h2u(__floats2half2_rn(kNF4Table[e & 15], kNF4Table[e >> 4]));
+            uint4* dst = reinterpret_cast<uint4*>(lut + e * 32);
+            dst[0] = make_uint4(v, v, v, v); dst[1] = make_uint4(v, v, v, v);
+        }
+    }
+    __device__ static __forceinline__ void run(uint32_t codes, int lane, int s, __half2 dlo, __half2 dhi, __half2, __half2,
+                                               uint32_t lut, uint32_t (&out)[4]) {
+        uint32_t w, v0, v1, v2, v3;
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w) : "r"(codes + lane * 16 + s * 4));
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v0) : "r"(lut + ((w << 5) & 0x1fe0u)));
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v1) : "r"(lut + ((w >> 3) & 0x1fe0u)));
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v2) : "r"(lut + ((w >> 11) & 0x1fe0u)));
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v3) : "r"(lut + ((w >> 19) & 0x1fe0u)));
+        out[0] = h2u(__hmul2(u2h(v0), dlo)); out[1] = h2u(__hmul2(u2h(v1), dhi));
+        out[2] = h2u(__hmul2(u2h(v2), dlo)); out[3] = h2u(__hmul2(u2h(v3), dhi));
     }
 };
 
@@ -205,32 +235,60 @@ template <int QT> struct Smem {
     static constexpr int kPacked = ((2 * kPackedGroup + 127) / 128) * 128;
     // every stage starts 1024-byte aligned (the swizzled operand tiles sit at its start)
     __host__ __device__ static constexpr int stage_bytes(int mt) { return ((mt * kTileBytesAB + kTileBytesAB + kPacked + 1023) / 1024) * 1024; }
-    __host__ __device__ static constexpr int total(int mt) { return 1024 + kStages * stage_bytes(mt) + 256; }
+    // [align slack | stages | barriers (256) | codec lookup table]
+    __host__ __device__ static constexpr int stages(int mt) {
+        return (232448 - 1024 - 256 - Expand<QT>::kLutBytes) / stage_bytes(mt) < kMaxStages
+                   ? (232448 - 1024 - 256 - Expand<QT>::kLutBytes) / stage_bytes(mt) : kMaxStages;
+    }
+    __host__ __device__ static constexpr int total(int mt) { return 1024 + stages(mt) * stage_bytes(mt) + 256 + Expand<QT>::kLutBytes; }
 };
 
-__device__ __forceinline__ void store_vals(const GemmArgs& A, int64_t token, int64_t n0, const float (&v)[32]) {
+// 32 consecutive features of one token: 64 bytes (fp16 / bf16) or 128 bytes (fp32), written with
+// 16-byte stores (n0 is a multiple of 32 and N of 128, so the run is 64-byte aligned).  Scalar
+// 2-byte stores cost one 32-byte sector transaction each: 16x the traffic.
+__device__ __forceinline__ void store_vals(const GemmArgs& A, int64_t token, int64_t n0, float (&v)[32]) {
     const int64_t N = A.G.rows;
+    const int64_t idx = token * N + n0;
+    if (A.y_dtype == DT_F32) {
+        float4* p = reinterpret_cast<float4*>((float*)A.y + idx);
+        const float4* bp = reinterpret_cast<const float4*>((const float*)A.bias + n0);
 #pragma unroll
-    for (int i = 0; i < 32; i++) {
-        const int64_t row = n0 + i;
-        float val = v[i];
-        const int64_t idx = token * N + row;
-        if (A.y_dtype == DT_F32) {
-            float* p = (float*)A.y + idx;
-            if (A.bias) val += ((const float*)A.bias)[row];
-            if (A.accumulate) val += *p;
-            *p = val;
-        } else if (A.y_dtype == DT_F16) {
-            __half* p = (__half*)A.y + idx;
-            if (A.bias) val += __half2float(((const __half*)A.bias)[row]);
-            if (A.accumulate) val += __half2float(*p);
-            *p = __float2half_rn(val);
-        } else {
-            __nv_bfloat16* p = (__nv_bfloat16*)A.y + idx;
-            if (A.bias) val += __bfloat162float(((const __nv_bfloat16*)A.bias)[row]);
-            if (A.accumulate) val += __bfloat162float(*p);
-            *p = __float2bfloat16_rn(val);
+        for (int i = 0; i < 8; i++) {
+            float4 o = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+            if (A.bias) { const float4 b = bp[i]; o.x += b.x; o.y += b.y; o.z += b.z; o.w += b.w; }
+            if (A.accumulate) { const float4 c = p[i]; o.x += c.x; o.y += c.y; o.z += c.z; o.w += c.w; }
+            p[i] = o;
         }
+        return;
+    }
+    const bool f16 = A.y_dtype == DT_F16;
+    auto unpack = [&](uint32_t u, float& lo, float& hi) {
+        if (f16) { const float2 f = __half22float2(u2h(u)); lo = f.x; hi = f.y; }
+        else { lo = __uint_as_float(u << 16); hi = __uint_as_float(u & 0xffff0000u); }
+    };
+    auto pack = [&](float lo, float hi) -> uint32_t {
+        if (f16) return h2u(__floats2half2_rn(lo, hi));
+        __nv_bfloat162 b = __floats2bfloat162_rn(lo, hi);
+        return *reinterpret_cast<uint32_t*>(&b);
+    };
+    uint4* p = reinterpret_cast<uint4*>((uint16_t*)A.y + idx);
+    const uint4* bp = reinterpret_cast<const uint4*>((const uint16_t*)A.bias + n0);
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+        if (A.bias) {
+            const uint4 b = bp[i];
+            const uint32_t bw[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+            for (int j = 0; j < 4; j++) { float lo, hi; unpack(bw[j], lo, hi); v[8 * i + 2 * j] += lo; v[8 * i + 2 * j + 1] += hi; }
+        }
+        if (A.accumulate) {
+            const uint4 c = p[i];
+            const uint32_t cw[4] = {c.x, c.y, c.z, c.w};
+#pragma unroll
+            for (int j = 0; j < 4; j++) { float lo, hi; unpack(cw[j], lo, hi); v[8 * i + 2 * j] += lo; v[8 * i + 2 * j + 1] += hi; }
+        }
+        p[i] = make_uint4(pack(v[8 * i], v[8 * i + 1]), pack(v[8 * i + 2], v[8 * i + 3]), pack(v[8 * i + 4], v[8 * i + 5]),
+                          pack(v[8 * i + 6], v[8 * i + 7]));
     }
 }
 
@@ -241,6 +299,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap xmap, const GemmArgs A) {
     using E = Expand<QT>;
     using SM = Smem<QT>;
     constexpr int STAGE = SM::stage_bytes(MT);
+    constexpr int kStages = SM::stages(MT);
+    static_assert(kStages >= 2 && 3 * kStages * 8 + 16 <= 256, "barrier region is 256 bytes");
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;       // 128B swizzle wants 1024-byte alignment
     const uint32_t bars = base + kStages * STAGE;                      // full[s], deq[s], empty[s], tmem_full, tmem slot
@@ -251,13 +311,15 @@ gemm_kernel(const __grid_constant__ CUtensorMap xmap, const GemmArgs A) {
     const uint32_t tmem_slot = tmem_full + 8;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t lut = bars + 256 + 4 * (lane & 7);
+    if constexpr (E::kLutBytes > 0) E::fill_lut(smem_raw + (bars + 256 - smem_u32(smem_raw)), threadIdx.x, kThreads);   // visible after the __syncthreads below
     const int ftile = blockIdx.x;
     const int m0 = blockIdx.y * (128 * MT);
     const int nb = (int)A.G.nb;
     constexpr uint32_t TMEM_COLS = 128 * MT;
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < kStages; s++) { mbar_init(full_bar(s), 1); mbar_init(deq_bar(s), 128); mbar_init(empty_bar(s), 1); }
+        for (int s = 0; s < kStages; s++) { mbar_init(full_bar(s), 1); mbar_init(deq_bar(s), 32 * kDeqWarps); mbar_init(empty_bar(s), 1); }
         mbar_init(tmem_full, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -320,7 +382,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap xmap, const GemmArgs A) {
         }
     } else {
         // ================= dequant warps, then epilogue =================
-        const int dw = warp - 2;                             // 0..3: tile r = dw of both row groups
+        const int dw = (warp - 2) & 3;                       // tile r = dw of row group gi = (warp - 2) / 4
         const int g = lane >> 2, t = lane & 3;
         for (int kb = 0; kb < nb; kb++) {
             const int s = kb % kStages, round = kb / kStages;
@@ -328,8 +390,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap xmap, const GemmArgs A) {
             const uint32_t st = base + s * STAGE;
             const uint32_t btile = st + MT * kTileBytesAB;
             const uint32_t pk = st + (MT + 1) * kTileBytesAB;
-#pragma unroll
-            for (int gi = 0; gi < 2; gi++) {
+            {
+                const int gi = (warp - 2) >> 2;
                 const uint32_t grp = pk + gi * SM::kPackedGroup;
                 const uint32_t codes = grp + dw * E::kTileBytes;
                 uint32_t dq, mq = 0;
@@ -345,8 +407,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap xmap, const GemmArgs A) {
 #pragma unroll
                 for (int q = 0; q < 2; q++) {               // k-steps 2q, 2q+1 -> one 16-byte chunk per row
                     uint32_t a[4], b[4];
-                    E::run(codes, lane, 2 * q, dlo, dhi, mlo, mhi, a);
-                    E::run(codes, lane, 2 * q + 1, dlo, dhi, mlo, mhi, b);
+                    E::run(codes, lane, 2 * q, dlo, dhi, mlo, mhi, lut, a);
+                    E::run(codes, lane, 2 * q + 1, dlo, dhi, mlo, mhi, lut, b);
                     if (BF) {
 #pragma unroll
                         for (int i = 0; i < 4; i++) { a[i] = h2_to_bf2(a[i]); b[i] = h2_to_bf2(b[i]); }
@@ -362,12 +424,13 @@ gemm_kernel(const __grid_constant__ CUtensorMap xmap, const GemmArgs A) {
         // ---- epilogue: warp w may touch TMEM lanes 32*(w%4) .. +31
         mbar_wait(tmem_full, 0);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        const int quarter = warp & 3;
+        // two warps share each TMEM lane quarter: the first takes feature columns 0..63, the second 64..127
+        const int quarter = warp & 3, chalf = ((warp - 2) >> 2) * 64;
 #pragma unroll
         for (int mt = 0; mt < MT; mt++) {
             const int64_t token = (int64_t)m0 + mt * 128 + quarter * 32 + lane;
 #pragma unroll 1
-            for (int c = 0; c < 128; c += 32) {
+            for (int c = chalf; c < chalf + 64; c += 32) {
                 float v[32];
                 tmem_ld32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(mt * 128 + c), v);
                 if (token < A.M) store_vals(A, token, (int64_t)ftile * kTileN + c, v);
@@ -426,7 +489,7 @@ static int launch_qt(bool bf, int mt, const CUtensorMap& map, const GemmArgs& A,
 
 bool gemm_tc_supported(int qt, int64_t n_rows, int64_t k) {
     qt = canon_qtype(qt);
-    const bool q = qt == QT_SYM_INT4 || qt == QT_ASYM_INT4 || qt == QT_FP8_E4M3 || qt == QT_FP8_E5M2 || qt == QT_FP6;
+    const bool q = qt == QT_SYM_INT4 || qt == QT_ASYM_INT4 || qt == QT_NF4 || qt == QT_FP8_E4M3 || qt == QT_FP8_E5M2 || qt == QT_FP6;
     return q && n_rows >= 128 && (n_rows % 128) == 0 && k >= 64 && (k % 64) == 0;
 }
 
@@ -473,6 +536,7 @@ int gemm_tc_launch(const void* w, int qt, int64_t n_rows, int64_t k, const void*
     const dim3 grid((unsigned)(n_main / 128), (unsigned)((m + 128 * mt - 1) / (128 * mt)), 1);
     switch (qt) {
         case QT_SYM_INT4:  launch_qt<QT_SYM_INT4>(bf, mt, map, A, grid, st); break;
+        case QT_NF4:       launch_qt<QT_NF4>(bf, mt, map, A, grid, st); break;
         case QT_ASYM_INT4: launch_qt<QT_ASYM_INT4>(bf, mt, map, A, grid, st); break;
         case QT_FP8_E4M3:  launch_qt<QT_FP8_E4M3>(bf, mt, map, A, grid, st); break;
         case QT_FP8_E5M2:  launch_qt<QT_FP8_E5M2>(bf, mt, map, A, grid, st); break;

@@ -313,7 +313,7 @@ def test_tp_shards_reproduce_full_result(lbl, cuda_device, qtype):
 
 
 # ---------------------------------------------------------------- (c) prefill GEMM on tcgen05
-@pytest.mark.parametrize("qtype", ["sym_int4", "asym_int4", "fp8_e4m3", "fp8_e5m2", "fp6"])
+@pytest.mark.parametrize("qtype", ["sym_int4", "asym_int4", "nf4", "fp8_e4m3", "fp8_e5m2", "fp6"])
 @pytest.mark.parametrize("xdt,tol", [(torch.float16, 1e-3), (torch.bfloat16, 8e-3), (torch.float32, 8e-3)])
 @pytest.mark.parametrize("shape,M", [((256, 512), 64), ((128, 64), 33), ((384, 1024), 300)])
 def test_gemm_prefill_matches_oracle(lbl, cuda_device, qtype, xdt, tol, shape, M):
