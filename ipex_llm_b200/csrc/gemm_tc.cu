@@ -532,7 +532,15 @@ int gemm_tc_launch(const void* w, int qt, int64_t n_rows, int64_t k, const void*
     GemmArgs A;
     A.w = (const uint8_t*)w; A.G = make_geom(n_rows, k, qt); A.M = (int)m;
     A.y = y; A.y_dtype = y_dtype; A.bias = bias; A.accumulate = accumulate;
-    const int mt = m > 128 ? 2 : 1;
+    // token tile: 256 (two accumulator tiles per CTA, half the weight traffic) unless 128 gives fewer
+    // rounds of the 1-CTA-per-SM grid over the SMs
+    int mt = 1;
+    if (m > 128) {
+        const int64_t sms = sm_count();
+        const int64_t c2 = (n_main / 128) * ((m + 255) / 256), c1 = (n_main / 128) * ((m + 127) / 128);
+        const int64_t t2 = (c2 + sms - 1) / sms * 2, t1 = (c1 + sms - 1) / sms;
+        mt = 4 * t2 <= 5 * t1 ? 2 : 1;      // a 128-token tile re-reads the weights twice as often: ~25 % slower per token
+    }
     const dim3 grid((unsigned)(n_main / 128), (unsigned)((m + 128 * mt - 1) / (128 * mt)), 1);
     switch (qt) {
         case QT_SYM_INT4:  launch_qt<QT_SYM_INT4>(bf, mt, map, A, grid, st); break;

@@ -289,18 +289,23 @@ template <int QT, bool BF> struct Staging {
     static constexpr int kRingBytes = kStages * kStageBytes;
     static constexpr int kBarBytes = GEMV_WARPS * kStages * 8 + 8;                // + the leader's receive barrier
     // bytes of one matrix' accumulators of one warp in the reduction slot (M == 1: 8 live lanes per value)
-    __host__ __device__ static constexpr int slot_bytes(int nt, int acc) { return RG_TILES * nt * acc * (acc == 2 ? 32 : 128); }
+    // live lanes: only the lanes that hold existing activation rows take part in the reduction: the
+    // t-lanes 0 .. tl-1 with tl = ceil(M / 2) for M <= 8 (M == 1: tl = 1), all four beyond
+    __host__ __device__ static constexpr int live_t(int nt, int acc, int m) {
+        return acc == 2 ? 1 : (nt > 1 ? 4 : ((m < 8 ? m : 8) + 1) / 2);
+    }
+    __host__ __device__ static constexpr int slot_bytes(int nt, int acc, int tl = 4) { return RG_TILES * nt * acc * 32 * (acc == 2 ? 1 : tl); }
     // a warp's region: its ring, which later holds its reduction slot
     __host__ __device__ static constexpr int warp_bytes(int nt, int acc, int nm) {
         return ((kRingBytes > nm * slot_bytes(nt, acc) ? kRingBytes : nm * slot_bytes(nt, acc)) + 127) / 128 * 128;
     }
     // + the leader CTA's receive buffer for its peers' CTA sums (push reduction, M <= 8 kernels)
-    static constexpr int smem_bytes(int nt, int acc, int nm) {
-        return lut_offset(nt, acc, nm) + C::kLutBytes;
+    static constexpr int smem_bytes(int nt, int acc, int nm, int tl = 4) {
+        return lut_offset(nt, acc, nm, tl) + C::kLutBytes;
     }
     // the codec's lookup table (if any) sits last, 32-byte aligned
-    __host__ __device__ static constexpr int lut_offset(int nt, int acc, int nm) {
-        return (GEMV_WARPS * warp_bytes(nt, acc, nm) + kBarBytes + 8 + (nt == 1 ? (GEMV_MAX_SPLIT - 1) * nm * slot_bytes(nt, acc) : 0) + 31) / 32 * 32;
+    __host__ __device__ static constexpr int lut_offset(int nt, int acc, int nm, int tl = 4) {
+        return (GEMV_WARPS * warp_bytes(nt, acc, nm) + kBarBytes + 8 + (nt == 1 ? (GEMV_MAX_SPLIT - 1) * nm * slot_bytes(nt, acc, tl) : 0) + 31) / 32 * 32;
     }
 };
 
@@ -406,9 +411,10 @@ gemv_kernel(const GemvArgs A) {
     const uint32_t ring = smem_u32(smem) + warp * WB;
     const uint32_t bars = smem_u32(smem) + GEMV_WARPS * WB + warp * (STAGES * 8);
     // the codec's lookup table (nf4): built once per CTA, read-only afterwards
-    const uint32_t lut = smem_u32(smem) + S::lut_offset(NT, ACC, NM) + 4 * (lane & 7);
+    const int tl = S::live_t(NT, ACC, A.M);            // live t-lanes of the reduction (see Staging)
+    const uint32_t lut = smem_u32(smem) + S::lut_offset(NT, ACC, NM, tl) + 4 * (lane & 7);
     if (C::kLutBytes) {
-        C::fill_lut(smem + S::lut_offset(NT, ACC, NM), threadIdx.x);
+        C::fill_lut(smem + S::lut_offset(NT, ACC, NM, tl), threadIdx.x);
         __syncthreads();
     }
     // issue cursor: walks the segment list one chunk at a time.  Warp-uniform state, called by the whole
@@ -701,13 +707,13 @@ gemv_kernel(const GemvArgs A) {
     TS(4);
 
     // ---- reduction.  Slot layout: value v = (r*NT + j)*ACC + c of live lane l at float index v*LW + l.
-    // M == 1 (ACC == 2): only column 0 exists, i.e. only the lanes with t == 0 hold outputs (LW = 8).
-    constexpr int LW = (ACC == 2) ? 8 : 32;
-    constexpr int NVL = NV * LW;                       // floats per matrix and warp
+    // Only the t-lanes below tl hold existing activation rows (M == 1: tl = 1, LW = 8 lanes per value).
+    const int LW = 8 * tl;
+    const int NVL = NV * LW;                           // floats per matrix and warp
     // 1) every warp parks its fragment in its own (now idle) ring
     float* slot = reinterpret_cast<float*>(smem + warp * WB);
-    if (ACC != 2 || t == 0) {
-        const int l = (ACC == 2) ? g : lane;
+    if (t < tl) {
+        const int l = g * tl + t;
 #pragma unroll
         for (int mt = 0; mt < NM; mt++)
 #pragma unroll
@@ -721,7 +727,7 @@ gemv_kernel(const GemvArgs A) {
     const int64_t N = A.G.rows;
     auto store_value = [&](int i, float v) {
         const int l = i % LW, val = i / LW, c = val % ACC, j = (val / ACC) % NT, r = val / (ACC * NT);
-        const int gg = (ACC == 2) ? l : (l >> 2), tt = (ACC == 2) ? 0 : (l & 3);
+        const int gg = l / tl, tt = l - gg * tl;
         const int hi = (ACC == 2) ? c : (c >> 1);                     // row g (0) or g+8 (1)
         const int col = 8 * j + 2 * tt + ((ACC == 2) ? 0 : (c & 1));
         const int64_t row = (int64_t)rg * RG_ROWS + r * 16 + gg + 8 * hi;
@@ -865,8 +871,10 @@ static void launch_nt(int m, int64_t groups, int64_t nb, const GemvArgs& A, cuda
     using SG = Staging<QT, BF>;
     static bool configured = false;     // per instantiation: raise the dynamic shared memory limit once
     static int cache[8][8];
+    static int cache_tl[2][4][8];        // [fused MLP][live t-lanes - 1]: the M <= 8 kernels' shared memory depends on M
     if (!configured) {
         for (auto& row : cache) for (int& v : row) v = -1;
+        for (auto& a : cache_tl) for (auto& row : a) for (int& v : row) v = -1;
         cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 1, 2, 1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, SG::smem_bytes(1, 2, 1));
         cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 1, 4, 1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, SG::smem_bytes(1, 4, 1));
         cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 2, 4, 1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, SG::smem_bytes(2, 4, 1));
@@ -887,11 +895,13 @@ static void launch_nt(int m, int64_t groups, int64_t nb, const GemvArgs& A, cuda
     }
     if (A.w2) {                          // fused MLP: M <= 8 only (the host falls back otherwise)
         if (m == 1) launch_kernel(gemv_kernel<QT, BF, NS, 1, 2, 2, 0>, SG::smem_bytes(1, 2, 2), groups, nb, A, st, cache[4]);
-        else launch_kernel(gemv_kernel<QT, BF, NS, 1, 4, 2, 0>, SG::smem_bytes(1, 4, 2), groups, nb, A, st, cache[5]);
+        else launch_kernel(gemv_kernel<QT, BF, NS, 1, 4, 2, 0>, SG::smem_bytes(1, 4, 2, SG::live_t(1, 4, m)), groups, nb, A, st,
+                           cache_tl[1][SG::live_t(1, 4, m) - 1]);
         return;
     }
     if (m == 1) launch_kernel(gemv_kernel<QT, BF, NS, 1, 2, 1, 0>, SG::smem_bytes(1, 2, 1), groups, nb, A, st, cache[0]);
-    else if (m <= 8) launch_kernel(gemv_kernel<QT, BF, NS, 1, 4, 1, 0>, SG::smem_bytes(1, 4, 1), groups, nb, A, st, cache[1]);
+    else if (m <= 8) launch_kernel(gemv_kernel<QT, BF, NS, 1, 4, 1, 0>, SG::smem_bytes(1, 4, 1, SG::live_t(1, 4, m)), groups, nb, A, st,
+                                   cache_tl[0][SG::live_t(1, 4, m) - 1]);
     else if (m <= 16) launch_kernel(gemv_kernel<QT, BF, NS, 2, 4, 1, 0>, SG::smem_bytes(2, 4, 1), groups, nb, A, st, cache[2]);
     else launch_kernel(gemv_kernel<QT, BF, NS, 4, 4, 1, 0>, SG::smem_bytes(4, 4, 1), groups, nb, A, st, cache[3]);
 }
