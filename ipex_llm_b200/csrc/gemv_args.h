@@ -37,6 +37,7 @@ struct GemvArgs {
     //   mode 1: blockIdx.z = routed slot z; w / w2 = tab_w[sel[z]] / tab_w2[sel[z]]; y row z
     //   mode 2: the K axis is the concatenation of n_seg matrices tab_w[sel[z]] ([rows][k] each) and
     //           x is [n_seg][k]; slot z's partial sums are multiplied by seg_scale[z]
+    int ring_recv;            // M = 2..8: the leader receives its peers' sums in its rings (set at launch)
     int slice_q, slice_r;     // k-blocks per cluster rank: (blocks along K) / split and the remainder (set at launch)
     int mode;
     const unsigned long long* tab_w;

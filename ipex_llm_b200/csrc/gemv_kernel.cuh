@@ -297,15 +297,18 @@ template <int QT, bool BF> struct Staging {
     __host__ __device__ static constexpr int slot_bytes(int nt, int acc, int tl = 4) { return RG_TILES * nt * acc * 32 * (acc == 2 ? 1 : tl); }
     // a warp's region: its ring, which later holds its reduction slot
     __host__ __device__ static constexpr int warp_bytes(int nt, int acc, int nm) {
-        return ((kRingBytes > nm * slot_bytes(nt, acc) ? kRingBytes : nm * slot_bytes(nt, acc)) + 127) / 128 * 128;
+        // M = 2..8 kernels: the four rings together also receive the peers' sums (RINGRECV in the kernel)
+        const int need = (nt == 1 && acc == 4) ? (GEMV_MAX_SPLIT - 1) * nm * slot_bytes(nt, acc) / GEMV_WARPS : nm * slot_bytes(nt, acc);
+        return ((kRingBytes > need ? kRingBytes : need) + 127) / 128 * 128;
     }
     // + the leader CTA's receive buffer for its peers' CTA sums (push reduction, M <= 8 kernels)
-    static constexpr int smem_bytes(int nt, int acc, int nm, int tl = 4) {
-        return lut_offset(nt, acc, nm, tl) + C::kLutBytes;
+    static constexpr int smem_bytes(int nt, int acc, int nm, int tl = 4, bool ring = false) {
+        return lut_offset(nt, acc, nm, tl, ring) + C::kLutBytes;
     }
     // the codec's lookup table (if any) sits last, 32-byte aligned
-    __host__ __device__ static constexpr int lut_offset(int nt, int acc, int nm, int tl = 4) {
-        return (GEMV_WARPS * warp_bytes(nt, acc, nm) + kBarBytes + 8 + (nt == 1 ? (GEMV_MAX_SPLIT - 1) * nm * slot_bytes(nt, acc, tl) : 0) + 31) / 32 * 32;
+    // ring: the M = 2..8 kernel receives into its rings (no dedicated buffer)
+    __host__ __device__ static constexpr int lut_offset(int nt, int acc, int nm, int tl = 4, bool ring = false) {
+        return (GEMV_WARPS * warp_bytes(nt, acc, nm) + kBarBytes + 8 + ((nt == 1 && !(acc == 4 && ring)) ? (GEMV_MAX_SPLIT - 1) * nm * slot_bytes(nt, acc, tl) : 0) + 31) / 32 * 32;
     }
 };
 
@@ -351,7 +354,6 @@ gemv_kernel(const GemvArgs A) {
     constexpr int CH = S::kChunk, STAGES = S::kStages, STAGE_BYTES = S::kStageBytes;
     constexpr int SUPER = S::kSuperCodes;
     constexpr int NV = RG_TILES * NT * ACC;            // accumulator floats per lane and matrix
-    constexpr int NVT = NM * NV;
     constexpr int WB = S::warp_bytes(NT, ACC, NM);     // bytes of one warp's ring / reduction slot
     extern __shared__ __align__(128) uint8_t smem[];
 
@@ -412,9 +414,9 @@ gemv_kernel(const GemvArgs A) {
     const uint32_t bars = smem_u32(smem) + GEMV_WARPS * WB + warp * (STAGES * 8);
     // the codec's lookup table (nf4): built once per CTA, read-only afterwards
     const int tl = S::live_t(NT, ACC, A.M);            // live t-lanes of the reduction (see Staging)
-    const uint32_t lut = smem_u32(smem) + S::lut_offset(NT, ACC, NM, tl) + 4 * (lane & 7);
+    const uint32_t lut = smem_u32(smem) + S::lut_offset(NT, ACC, NM, tl, A.ring_recv != 0) + 4 * (lane & 7);
     if (C::kLutBytes) {
-        C::fill_lut(smem + S::lut_offset(NT, ACC, NM, tl), threadIdx.x);
+        C::fill_lut(smem + S::lut_offset(NT, ACC, NM, tl, A.ring_recv != 0), threadIdx.x);
         __syncthreads();
     }
     // issue cursor: walks the segment list one chunk at a time.  Warp-uniform state, called by the whole
@@ -457,6 +459,13 @@ gemv_kernel(const GemvArgs A) {
     };
 
     constexpr bool PUSH = (NT == 1);                   // peers push their sums into the leader (else the leader pulls)
+    // M == 1: the leader has a small dedicated receive buffer, and the cluster barrier that publishes its
+    // mbarrier is split around the main loop (arrive here, wait before the tail: free).  M = 2..8: up to
+    // 28 KB would cost a resident CTA per SM, so the peers push into the leader's idle rings instead, after
+    // a cluster barrier that follows the leader's own CTA sums (RINGRECV).  That late barrier costs about
+    // a microsecond, so the host asks for it (A.ring_recv) only when it buys a larger cluster.
+    const bool RINGRECV = PUSH && (ACC == 4) && A.ring_recv != 0;
+    static_assert(!(PUSH && ACC == 4) || (GEMV_MAX_SPLIT - 1) * NM * S::slot_bytes(NT, ACC, 4) <= GEMV_WARPS * WB, "receive area must fit in the rings");
     const uint32_t rbar = smem_u32(smem) + GEMV_WARPS * WB + GEMV_WARPS * STAGES * 8;
     float* recv = reinterpret_cast<float*>(smem + GEMV_WARPS * WB + S::kBarBytes + 8);
     if (PUSH && nsplit > 1) {
@@ -464,7 +473,7 @@ gemv_kernel(const GemvArgs A) {
             mbar_init(rbar, 1);
             asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         }
-        asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");   // matched by the wait before the tail
+        if (!RINGRECV) asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");   // matched by the wait before the tail
     }
     // lane s owns stage s during start-up (the barrier inits and first copies go out in parallel);
     // weights do not depend on the previous kernel: they start streaming before the PDL wait
@@ -744,6 +753,55 @@ gemv_kernel(const GemvArgs A) {
     //    the leader waits for the bytes, adds and stores.  Larger M: the leader pulls through
     //    ld.shared::cluster between two cluster barriers.
     float* cta = reinterpret_cast<float*>(smem);
+    if (ACC == 4 && RINGRECV && nsplit > 1) {
+        constexpr int ITERS = NV * 32 / (GEMV_WARPS * 32);            // NVL <= NV * 32
+        float vmall[ITERS][NM];
+#pragma unroll
+        for (int it = 0; it < ITERS; it++) {
+            const int i = threadIdx.x + it * GEMV_WARPS * 32;
+#pragma unroll
+            for (int mt = 0; mt < NM; mt++) {
+                float v = 0.0f;
+                if (i < NVL) {
+                    v = cta[mt * NVL + i];
+#pragma unroll
+                    for (int w = 1; w < GEMV_WARPS; w++) v += reinterpret_cast<const float*>(smem + w * WB)[mt * NVL + i];
+                }
+                vmall[it][mt] = v;
+            }
+        }
+        __syncthreads();                                              // every slot has been read: the rings are free
+        asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
+        asm volatile("barrier.cluster.wait.aligned;" ::: "memory");   // ... in every CTA of the cluster
+        float* rrecv = cta;                                           // leader's receive area = its rings
+        if (slice != 0) {
+            const uint32_t rb = map_to_rank(rbar, 0);
+#pragma unroll
+            for (int it = 0; it < ITERS; it++) {
+                const int i = threadIdx.x + it * GEMV_WARPS * 32;
+                if (i < NVL) {
+#pragma unroll
+                    for (int mt = 0; mt < NM; mt++)
+                        st_async_f32(map_to_rank(smem_u32(rrecv + (slice - 1) * (NM * NVL) + mt * NVL + i), 0), vmall[it][mt], rb);
+                }
+            }
+        } else {
+            if (threadIdx.x == 0) mbar_expect_tx(rbar, (uint32_t)((nsplit - 1) * NM * NVL * 4));
+            mbar_wait(rbar, 0);
+#pragma unroll
+            for (int it = 0; it < ITERS; it++) {
+                const int i = threadIdx.x + it * GEMV_WARPS * 32;
+                if (i < NVL) {
+#pragma unroll
+                    for (int mt = 0; mt < NM; mt++)
+                        for (int rk = 1; rk < nsplit; rk++) vmall[it][mt] += rrecv[(rk - 1) * (NM * NVL) + mt * NVL + i];
+                    finish(i, vmall[it]);
+                }
+            }
+        }
+        TS(5);
+        return;
+    }
     if (PUSH && nsplit > 1) {
         asm volatile("barrier.cluster.wait.aligned;" ::: "memory");   // the leader's barrier init is visible
         if (slice == 0 && threadIdx.x == 0) mbar_expect_tx(rbar, (uint32_t)((nsplit - 1) * NM * NVL * 4));
@@ -842,13 +900,21 @@ static int pick_split(K kernel, int smem, int64_t groups, int64_t nb, int (&cach
     return 1;
 }
 
+// smem_ring / cache_ring (optional): the same kernel receiving into its rings (GemvArgs::ring_recv): less shared
+// memory, a late cluster barrier; taken only if it allows a larger cluster.
 template <typename K>
 static void launch_kernel(K kernel, int smem, int64_t groups, int64_t nb, const GemvArgs& A, cudaStream_t st,
-                          int (&cache)[8], int grid_z = 1) {
+                          int (&cache)[8], int grid_z = 1, int smem_ring = 0, int (*cache_ring)[8] = nullptr) {
     // nb = k-blocks one cluster splits; the cluster count that has to fit in one wave is groups * grid_z
-    const int split = pick_split(kernel, smem, groups * grid_z, nb, cache);
+    int split = pick_split(kernel, smem, groups * grid_z, nb, cache);
     GemvArgs B = A;
+    B.ring_recv = 0;
+    if (cache_ring) {
+        const int split_ring = pick_split(kernel, smem_ring, groups * grid_z, nb, *cache_ring);
+        if (split_ring > split) { split = split_ring; smem = smem_ring; B.ring_recv = 1; }
+    }
     B.slice_q = (int)(nb / split); B.slice_r = (int)(nb % split);
+    (void)cache_ring;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)split, (unsigned)groups, (unsigned)grid_z);
     cfg.blockDim = dim3(GEMV_WARPS * 32); cfg.dynamicSmemBytes = smem; cfg.stream = st;
@@ -872,9 +938,11 @@ static void launch_nt(int m, int64_t groups, int64_t nb, const GemvArgs& A, cuda
     static bool configured = false;     // per instantiation: raise the dynamic shared memory limit once
     static int cache[8][8];
     static int cache_tl[2][4][8];        // [fused MLP][live t-lanes - 1]: the M <= 8 kernels' shared memory depends on M
+    static int cache_ring[2][8];         // ... receiving into the rings
     if (!configured) {
         for (auto& row : cache) for (int& v : row) v = -1;
         for (auto& a : cache_tl) for (auto& row : a) for (int& v : row) v = -1;
+        for (auto& row : cache_ring) for (int& v : row) v = -1;
         cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 1, 2, 1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, SG::smem_bytes(1, 2, 1));
         cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 1, 4, 1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, SG::smem_bytes(1, 4, 1));
         cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 2, 4, 1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, SG::smem_bytes(2, 4, 1));
@@ -896,12 +964,12 @@ static void launch_nt(int m, int64_t groups, int64_t nb, const GemvArgs& A, cuda
     if (A.w2) {                          // fused MLP: M <= 8 only (the host falls back otherwise)
         if (m == 1) launch_kernel(gemv_kernel<QT, BF, NS, 1, 2, 2, 0>, SG::smem_bytes(1, 2, 2), groups, nb, A, st, cache[4]);
         else launch_kernel(gemv_kernel<QT, BF, NS, 1, 4, 2, 0>, SG::smem_bytes(1, 4, 2, SG::live_t(1, 4, m)), groups, nb, A, st,
-                           cache_tl[1][SG::live_t(1, 4, m) - 1]);
+                           cache_tl[1][SG::live_t(1, 4, m) - 1], 1, SG::smem_bytes(1, 4, 2, 4, true), &cache_ring[1]);
         return;
     }
     if (m == 1) launch_kernel(gemv_kernel<QT, BF, NS, 1, 2, 1, 0>, SG::smem_bytes(1, 2, 1), groups, nb, A, st, cache[0]);
     else if (m <= 8) launch_kernel(gemv_kernel<QT, BF, NS, 1, 4, 1, 0>, SG::smem_bytes(1, 4, 1, SG::live_t(1, 4, m)), groups, nb, A, st,
-                                   cache_tl[0][SG::live_t(1, 4, m) - 1]);
+                                   cache_tl[0][SG::live_t(1, 4, m) - 1], 1, SG::smem_bytes(1, 4, 1, 4, true), &cache_ring[0]);
     else if (m <= 16) launch_kernel(gemv_kernel<QT, BF, NS, 2, 4, 1, 0>, SG::smem_bytes(2, 4, 1), groups, nb, A, st, cache[2]);
     else launch_kernel(gemv_kernel<QT, BF, NS, 4, 4, 1, 0>, SG::smem_bytes(4, 4, 1), groups, nb, A, st, cache[3]);
 }
