@@ -52,6 +52,14 @@ def n_launches():
     return LAYERS * (len(LAYER_SHAPES) - (1 if FUSED_MLP else 0)) + 1
 
 
+def workload_config():
+    """the workload both arms (ours and --impl reference) measure"""
+    return {"workload": "Llama-2-7B sym_int4 bs1 decode, LowBitLinear stream only: 161 matrices/token "
+                        "(32x[qkv 12288x4096, o 4096x4096, gate 11008x4096, up 11008x4096, down 4096x11008] + lm_head "
+                        "32000x4096); attention/norm/rope not included",
+            "block": "QK=64, 34 B"}
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
 
@@ -280,11 +288,9 @@ def run_ours(args):
         "value": world * 1e3 / ms_step, "unit": "tok/s", "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "u4 codes x f16 activations, f32 accumulate", "data": "synthetic",
-        "config": {"workload": "Llama-2-7B sym_int4 bs1 decode, LowBitLinear stream only: 161 matrices/token "
-                               "(32x[qkv 12288x4096, o 4096x4096, gate 11008x4096, up 11008x4096, down 4096x11008] + lm_head 32000x4096; gate+up run as one fused-MLP launch when fused_mlp is true); "
-                               "attention/norm/rope not included", "block": "QK=64, 34 B",
-                   "cache": "inputs larger than L2 (3.51 GB of weights per step)", "cuda_graph": True, "pdl": bool(args.pdl), "fused_mlp": FUSED_MLP, "l2_next_weight_hint": bool(args.l2_hint),
-                   "parallelism": "replicas" if world > 1 else "single"},
+        "config": dict(workload_config(), cache="inputs larger than L2 (3.51 GB of weights per step)", cuda_graph=True,
+                       pdl=bool(args.pdl), fused_mlp=FUSED_MLP, l2_next_weight_hint=bool(args.l2_hint),
+                       parallelism="replicas" if world > 1 else "single"),
         "e2e": {"value": world * 1e3 / (ms_e2e / args.steps), "unit": "tok/s", "h2d_bytes_per_step": HIDDEN * 2,
                 "d2h_bytes_per_step": 8},
         "gpu_launches": n_launches() * args.steps * 2,
@@ -312,8 +318,8 @@ def run_reference(args):
         "value": c["value"], "unit": "tok/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": c["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "u4 codes x int8 activations (ggml mode A), f32 accumulate", "data": "synthetic",
-        "config": {"workload": "Llama-2-7B sym_int4 bs1 decode, LowBitLinear stream only: 161 GEMVs/token; "
-                               "CPU restatement of the reference's ggml path (closed binary absent)"},
+        "config": dict(workload_config(), arm="CPU restatement of the reference's ggml path (closed binary absent), "
+                                              "all host threads, bounded sample per step"),
         "cpu_baseline": {"value": c["value"], "unit": "tok/s", "cores": c["cores"], "kind": "port", "sample": c["sample"]},
         "e2e": {"value": c["value"], "unit": "tok/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
