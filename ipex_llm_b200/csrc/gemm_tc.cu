@@ -31,7 +31,8 @@ namespace gemmtc {
 
 constexpr int kMaxStages = 6;        // pipeline depth = as many stages as fit in 227 KB, at most this
 constexpr int kDeqWarps = 8;         // dequant (then epilogue) warps: one 16x64 tile of the 128x64 B stage each
-constexpr int kThreads = 64 + 32 * kDeqWarps;
+constexpr int kEpiWarps = 4;         // epilogue warps: one per TMEM lane quarter (warp index % 4 must be 0..3 in order)
+constexpr int kThreads = 64 + 32 * kDeqWarps + 32 * kEpiWarps;
 constexpr int kTileN = 128;          // features per CTA (two 64-row groups)
 constexpr int kTileBytesAB = 128 * 128;   // one 128-row x 64-element 2-byte operand tile
 
@@ -293,6 +294,10 @@ __device__ __forceinline__ void store_vals(const GemmArgs& A, int64_t token, int
 }
 
 // grid = (N / 128 feature tiles, ceil(M / (128*MT)) token tiles)
+// Persistent: grid = min(tiles, SMs) CTAs; CTA c takes tiles c, c + grid, ... in token-tile-major order (the
+// CTAs running at one moment share the token tile's activations in L2 and stream different weights).
+// Warp roles: 0 TMA producer, 1 MMA issuer (owns TMEM), 2..9 dequant, 10..13 epilogue.  The accumulators
+// are double buffered in TMEM (2 x 128*MT columns), so the epilogue of tile i overlaps the main loop of i+1.
 template <int QT, bool BF, int MT>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap xmap, const GemmArgs A) {
@@ -300,27 +305,29 @@ gemm_kernel(const __grid_constant__ CUtensorMap xmap, const GemmArgs A) {
     using SM = Smem<QT>;
     constexpr int STAGE = SM::stage_bytes(MT);
     constexpr int kStages = SM::stages(MT);
-    static_assert(kStages >= 2 && 3 * kStages * 8 + 16 <= 256, "barrier region is 256 bytes");
+    static_assert(kStages >= 2 && 3 * kStages * 8 + 48 <= 256, "barrier region is 256 bytes");
     extern __shared__ uint8_t smem_raw[];
     const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;       // 128B swizzle wants 1024-byte alignment
-    const uint32_t bars = base + kStages * STAGE;                      // full[s], deq[s], empty[s], tmem_full, tmem slot
+    const uint32_t bars = base + kStages * STAGE;                      // full[s], deq[s], empty[s], tmem_full[2], tmem_empty[2], tmem slot
     auto full_bar = [&](int s) { return bars + s * 8; };
     auto deq_bar = [&](int s) { return bars + (kStages + s) * 8; };
     auto empty_bar = [&](int s) { return bars + (2 * kStages + s) * 8; };
-    const uint32_t tmem_full = bars + 3 * kStages * 8;
-    const uint32_t tmem_slot = tmem_full + 8;
+    auto tmem_full = [&](int b) { return bars + (3 * kStages + b) * 8; };
+    auto tmem_empty = [&](int b) { return bars + (3 * kStages + 2 + b) * 8; };
+    const uint32_t tmem_slot = bars + (3 * kStages + 4) * 8;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t lut = bars + 256 + 4 * (lane & 7);
     if constexpr (E::kLutBytes > 0) E::fill_lut(smem_raw + (bars + 256 - smem_u32(smem_raw)), threadIdx.x, kThreads);   // visible after the __syncthreads below
-    const int ftile = blockIdx.x;
-    const int m0 = blockIdx.y * (128 * MT);
     const int nb = (int)A.G.nb;
-    constexpr uint32_t TMEM_COLS = 128 * MT;
+    const int n_ftiles = (int)(A.G.rows / kTileN);
+    const int n_tiles = n_ftiles * ((A.M + 128 * MT - 1) / (128 * MT));
+    constexpr uint32_t ACC_COLS = 128 * MT;            // one accumulator buffer
+    constexpr uint32_t TMEM_COLS = 2 * ACC_COLS;       // 256 or 512 (powers of two)
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < kStages; s++) { mbar_init(full_bar(s), 1); mbar_init(deq_bar(s), 32 * kDeqWarps); mbar_init(empty_bar(s), 1); }
-        mbar_init(tmem_full, 1);
+        for (int b = 0; b < 2; b++) { mbar_init(tmem_full(b), 1); mbar_init(tmem_empty(b), 32 * kEpiWarps); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 1) {
@@ -336,22 +343,26 @@ gemm_kernel(const __grid_constant__ CUtensorMap xmap, const GemmArgs A) {
     if (warp == 0) {
         // ================= producer =================
         if (lane == 0) {
-            const int64_t rg0 = (int64_t)ftile * 2;
-            for (int kb = 0; kb < nb; kb++) {
-                const int s = kb % kStages, round = kb / kStages;
-                mbar_wait(empty_bar(s), (uint32_t)((round & 1) ^ 1));
-                const uint32_t st = base + s * STAGE;
-                mbar_expect_tx(full_bar(s), MT * kTileBytesAB + 2 * SM::kPackedGroup);
+            int it = 0;                                              // k-iterations issued so far (all tiles)
+            for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+                const int ftile = tile % n_ftiles, m0 = (tile / n_ftiles) * (128 * MT);
+                const int64_t rg0 = (int64_t)ftile * 2;
+                for (int kb = 0; kb < nb; kb++, it++) {
+                    const int s = it % kStages, round = it / kStages;
+                    mbar_wait(empty_bar(s), (uint32_t)((round & 1) ^ 1));
+                    const uint32_t st = base + s * STAGE;
+                    mbar_expect_tx(full_bar(s), MT * kTileBytesAB + 2 * SM::kPackedGroup);
 #pragma unroll
-                for (int mt = 0; mt < MT; mt++) tma_load_2d(st + mt * kTileBytesAB, &xmap, kb * 64, m0 + mt * 128, full_bar(s));
-                const uint32_t pk = st + (MT + 1) * kTileBytesAB;
+                    for (int mt = 0; mt < MT; mt++) tma_load_2d(st + mt * kTileBytesAB, &xmap, kb * 64, m0 + mt * 128, full_bar(s));
+                    const uint32_t pk = st + (MT + 1) * kTileBytesAB;
 #pragma unroll
-                for (int gi = 0; gi < 2; gi++) {
-                    const int64_t u = (rg0 + gi) * nb + kb;
-                    const uint32_t dst = pk + gi * SM::kPackedGroup;
-                    bulk_g2s(dst, A.w + u * SM::kSuper, SM::kSuper, full_bar(s));
-                    bulk_g2s(dst + SM::kSuper, A.w + A.G.off_s + u * 128, 128, full_bar(s));
-                    if (E::kHasMin) bulk_g2s(dst + SM::kSuper + 128, A.w + A.G.off_m + u * 128, 128, full_bar(s));
+                    for (int gi = 0; gi < 2; gi++) {
+                        const int64_t u = (rg0 + gi) * nb + kb;
+                        const uint32_t dst = pk + gi * SM::kPackedGroup;
+                        bulk_g2s(dst, A.w + u * SM::kSuper, SM::kSuper, full_bar(s));
+                        bulk_g2s(dst + SM::kSuper, A.w + A.G.off_s + u * 128, 128, full_bar(s));
+                        if (E::kHasMin) bulk_g2s(dst + SM::kSuper + 128, A.w + A.G.off_m + u * 128, 128, full_bar(s));
+                    }
                 }
             }
         }
@@ -360,38 +371,46 @@ gemm_kernel(const __grid_constant__ CUtensorMap xmap, const GemmArgs A) {
         if (lane == 0) {
             // c_format F32 (1<<4), a/b format (0 f16, 1 bf16), both K-major, N = 128 (>>3 at bit 17), M = 128 (>>4 at bit 24)
             const uint32_t idesc = (1u << 4) | ((BF ? 1u : 0u) << 7) | ((BF ? 1u : 0u) << 10) | ((128u >> 3) << 17) | ((128u >> 4) << 24);
-            for (int kb = 0; kb < nb; kb++) {
-                const int s = kb % kStages, round = kb / kStages;
-                mbar_wait(full_bar(s), (uint32_t)(round & 1));
-                mbar_wait(deq_bar(s), (uint32_t)(round & 1));
+            int it = 0, ti = 0;
+            for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ti++) {
+                const int buf = ti & 1;
+                mbar_wait(tmem_empty(buf), (uint32_t)(((ti >> 1) & 1) ^ 1));      // the epilogue has drained this buffer
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const uint32_t acc = tmem_base + buf * ACC_COLS;
+                for (int kb = 0; kb < nb; kb++, it++) {
+                    const int s = it % kStages, round = it / kStages;
+                    mbar_wait(full_bar(s), (uint32_t)(round & 1));
+                    mbar_wait(deq_bar(s), (uint32_t)(round & 1));
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                    const uint32_t st = base + s * STAGE;
+                    const uint32_t btile = st + MT * kTileBytesAB;
+#pragma unroll
+                    for (int mt = 0; mt < MT; mt++) {
+#pragma unroll
+                        for (int k4 = 0; k4 < 4; k4++) {
+                            const uint64_t ad = make_desc(st + mt * kTileBytesAB + k4 * 32);
+                            const uint64_t bd = make_desc(btile + k4 * 32);
+                            umma_f16(acc + mt * 128, ad, bd, idesc, (kb > 0 || k4 > 0) ? 1u : 0u);
+                        }
+                    }
+                    umma_commit(empty_bar(s));                  // stage reusable once these MMAs have read it
+                }
+                umma_commit(tmem_full(buf));                     // this tile's accumulators are complete
+            }
+        }
+    } else if (warp < 2 + kDeqWarps) {
+        // ================= dequant warps =================
+        const int dw = (warp - 2) & 3;                       // tile r = dw of row group gi = (warp - 2) / 4
+        const int gi = (warp - 2) >> 2;
+        const int g = lane >> 2, t = lane & 3;
+        int it = 0;
+        for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+            for (int kb = 0; kb < nb; kb++, it++) {
+                const int s = it % kStages, round = it / kStages;
+                mbar_wait(full_bar(s), (uint32_t)(round & 1));
                 const uint32_t st = base + s * STAGE;
                 const uint32_t btile = st + MT * kTileBytesAB;
-#pragma unroll
-                for (int mt = 0; mt < MT; mt++) {
-#pragma unroll
-                    for (int k4 = 0; k4 < 4; k4++) {
-                        const uint64_t ad = make_desc(st + mt * kTileBytesAB + k4 * 32);
-                        const uint64_t bd = make_desc(btile + k4 * 32);
-                        umma_f16(tmem_base + mt * 128, ad, bd, idesc, (kb > 0 || k4 > 0) ? 1u : 0u);
-                    }
-                }
-                umma_commit(empty_bar(s));                  // stage reusable once these MMAs have read it
-            }
-            umma_commit(tmem_full);                          // accumulators complete
-        }
-    } else {
-        // ================= dequant warps, then epilogue =================
-        const int dw = (warp - 2) & 3;                       // tile r = dw of row group gi = (warp - 2) / 4
-        const int g = lane >> 2, t = lane & 3;
-        for (int kb = 0; kb < nb; kb++) {
-            const int s = kb % kStages, round = kb / kStages;
-            mbar_wait(full_bar(s), (uint32_t)(round & 1));
-            const uint32_t st = base + s * STAGE;
-            const uint32_t btile = st + MT * kTileBytesAB;
-            const uint32_t pk = st + (MT + 1) * kTileBytesAB;
-            {
-                const int gi = (warp - 2) >> 2;
+                const uint32_t pk = st + (MT + 1) * kTileBytesAB;
                 const uint32_t grp = pk + gi * SM::kPackedGroup;
                 const uint32_t codes = grp + dw * E::kTileBytes;
                 uint32_t dq, mq = 0;
@@ -417,26 +436,32 @@ gemm_kernel(const __grid_constant__ CUtensorMap xmap, const GemmArgs A) {
                     asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(row_lo + chunk), "r"(a[0]), "r"(a[2]), "r"(b[0]), "r"(b[2]) : "memory");
                     asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(row_hi + chunk), "r"(a[1]), "r"(a[3]), "r"(b[1]), "r"(b[3]) : "memory");
                 }
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");      // generic-proxy writes -> async-proxy (UMMA) reads
+                mbar_arrive(deq_bar(s));
             }
-            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");      // generic-proxy writes -> async-proxy (UMMA) reads
-            mbar_arrive(deq_bar(s));
         }
-        // ---- epilogue: warp w may touch TMEM lanes 32*(w%4) .. +31
-        mbar_wait(tmem_full, 0);
-        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        // two warps share each TMEM lane quarter: the first takes feature columns 0..63, the second 64..127
-        const int quarter = warp & 3, chalf = ((warp - 2) >> 2) * 64;
+    } else {
+        // ================= epilogue warps: warp w may touch TMEM lanes 32*(w%4) .. +31 =================
+        const int quarter = warp & 3;
+        int ti = 0;
+        for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ti++) {
+            const int ftile = tile % n_ftiles, m0 = (tile / n_ftiles) * (128 * MT);
+            const int buf = ti & 1;
+            mbar_wait(tmem_full(buf), (uint32_t)((ti >> 1) & 1));
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 #pragma unroll
-        for (int mt = 0; mt < MT; mt++) {
-            const int64_t token = (int64_t)m0 + mt * 128 + quarter * 32 + lane;
+            for (int mt = 0; mt < MT; mt++) {
+                const int64_t token = (int64_t)m0 + mt * 128 + quarter * 32 + lane;
 #pragma unroll 1
-            for (int c = chalf; c < chalf + 64; c += 32) {
-                float v[32];
-                tmem_ld32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(mt * 128 + c), v);
-                if (token < A.M) store_vals(A, token, (int64_t)ftile * kTileN + c, v);
+                for (int c = 0; c < 128; c += 32) {
+                    float v[32];
+                    tmem_ld32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(buf * ACC_COLS + mt * 128 + c), v);
+                    if (token < A.M) store_vals(A, token, (int64_t)ftile * kTileN + c, v);
+                }
             }
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            mbar_arrive(tmem_empty(buf));                    // the MMA warp may overwrite this buffer
         }
-        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     }
     __syncthreads();
     if (warp == 1) {
@@ -541,7 +566,8 @@ int gemm_tc_launch(const void* w, int qt, int64_t n_rows, int64_t k, const void*
         const int64_t t2 = (c2 + sms - 1) / sms * 2, t1 = (c1 + sms - 1) / sms;
         mt = 4 * t2 <= 5 * t1 ? 2 : 1;      // a 128-token tile re-reads the weights twice as often: ~25 % slower per token
     }
-    const dim3 grid((unsigned)(n_main / 128), (unsigned)((m + 128 * mt - 1) / (128 * mt)), 1);
+    const int64_t n_tiles = (n_main / 128) * ((m + 128 * mt - 1) / (128 * mt));
+    const dim3 grid((unsigned)(n_tiles < sm_count() ? n_tiles : sm_count()), 1, 1);       // persistent CTAs
     switch (qt) {
         case QT_SYM_INT4:  launch_qt<QT_SYM_INT4>(bf, mt, map, A, grid, st); break;
         case QT_NF4:       launch_qt<QT_NF4>(bf, mt, map, A, grid, st); break;

@@ -333,6 +333,28 @@ def test_gemm_prefill_matches_oracle(lbl, cuda_device, qtype, xdt, tol, shape, M
     assert (np.abs(y - y64) <= bound).all(), float((np.abs(y - y64) / bound).max())
 
 
+def test_gemm_prefill_persistent_many_tiles(lbl, cuda_device):
+    """more tiles than SMs: every persistent CTA walks several tiles (both TMEM accumulator buffers, ragged
+    last token tile), checked against the fp32 product of the oracle-dequantised weights on the GPU"""
+    rng = np.random.default_rng(1300)
+    N, K, M = 128 * 44, 192, 1000                    # 44 feature tiles x 4 token tiles = 176 tiles of 256 tokens
+    w = rand_w(rng, N, K)
+    packed = oracle.quantize(w, "asym_int4")
+    wd = torch.from_numpy(oracle.dequantize(packed, (N, K), "asym_int4")).to(cuda_device)
+    x_t = torch.from_numpy(rng.standard_normal((M, K)).astype(np.float32)).half()
+    y = run_matmul(lbl, cuda_device, packed, (N, K), "asym_int4", x_t, out_dtype=torch.float32)
+    want = x_t.to(cuda_device).float() @ wd.T
+    bound = 1e-3 * (x_t.to(cuda_device).float().abs() @ wd.abs().T) + 1e-30
+    assert bool(((y - want).abs() <= bound).all()), float(((y - want).abs() / bound).max())
+    # bias + accumulate + fp16 output through the vector epilogue
+    bias = torch.from_numpy(rng.standard_normal(N).astype(np.float32)).half().to(cuda_device)
+    res = torch.from_numpy(rng.standard_normal((M, N)).astype(np.float32)).half().to(cuda_device)
+    out = res.clone()
+    run_matmul(lbl, cuda_device, packed, (N, K), "asym_int4", x_t, out=out, bias=bias, accumulate=True)
+    want2 = (want + bias.float() + res.float())
+    assert bool(((out.float() - want2).abs() <= bound + 2e-3 * want2.abs() + 1e-3).all())
+
+
 def test_gemm_prefill_epilogue_and_module(lbl, cuda_device):
     rng = np.random.default_rng(1300)
     N, K, M = 256, 512, 96
