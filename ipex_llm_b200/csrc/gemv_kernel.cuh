@@ -38,6 +38,8 @@
 //    programmatic dependent launch the weight stream of call i+1 overlaps the tail of call i.
 #pragma once
 #include <cstdlib>
+#include <mutex>
+#include <unordered_map>
 #include <cuda_fp8.h>
 #include "lowbit_common.cuh"
 #include "lowbit_internal.h"
@@ -52,7 +54,7 @@ __device__ __forceinline__ unsigned long long gtime() {
     return t;
 }
 #ifdef LOWBIT_GEMV_TIMESTAMPS     // development builds only: the checks cost issue slots in every warp
-#define TS(i) do { if (A.ts && lane == 0) A.ts[wid * 8 + (i)] = gtime(); } while (0)
+#define TS(i) do { if (A.ts && lane == 0) { A.ts[wid * 8 + (i)] = gtime(); if ((i) == 0) { unsigned sm; asm volatile("mov.u32 %0, %%smid;" : "=r"(sm)); A.ts[wid * 8 + 6] = sm + 1; } } } while (0)
 #else
 #define TS(i) do { } while (0)
 #endif
@@ -900,6 +902,45 @@ static int pick_split(K kernel, int smem, int64_t groups, int64_t nb, int (&cach
     return 1;
 }
 
+// co-resident clusters of `kernel` at cluster size sz with `smem` bytes of dynamic shared memory (memoised)
+template <typename K>
+static int max_clusters(K kernel, int sz, int smem) {
+    static std::mutex mu;
+    static std::unordered_map<unsigned long long, int> memo;
+    const unsigned long long key = ((unsigned long long)sz << 32) | (unsigned)smem;     // one map per kernel instantiation
+    std::lock_guard<std::mutex> lk(mu);
+    auto it = memo.find(key);
+    if (it != memo.end()) return it->second;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(sz, 64, 1); cfg.blockDim = dim3(GEMV_WARPS * 32); cfg.dynamicSmemBytes = smem;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = sz; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    int n = 0;
+    if (cudaOccupancyMaxActiveClusters(&n, kernel, &cfg) != cudaSuccess) { cudaGetLastError(); n = 0; }
+    memo[key] = n;
+    return n;
+}
+
+// The hardware fills an SM up to its resident-CTA limit before it moves on, and under PDL the CTAs of the next
+// launch take whatever slots free up first: with 6 slots per SM a 512-CTA launch ends up with 2 to 6 CTAs per SM,
+// and the launch lasts as long as its fullest SM (measured: finish time proportional to the CTA count, 2.7 us at
+// 3 CTAs, 5.1 us at 6).  So the launch asks for as much dynamic shared memory as makes ceil(CTAs / SMs) the
+// per-SM limit -- provided every cluster is still co-resident.  Returns the padded size (or `smem`).
+template <typename K>
+static int balance_smem(K kernel, int smem, int split, int64_t clusters) {
+    const int64_t ctas = clusters * split;
+    const int sms = sm_count();
+    for (int per_sm = (int)((ctas + sms - 1) / sms); per_sm <= 8; per_sm++) {
+        const int want = 232448 / per_sm - 1024 - 64;          // 1 KB per CTA is reserved by the system
+        if (want <= smem) break;                                // the natural footprint already allows no more than this
+        // 5 % slack: a launch that fills every slot leaves none for the next launch's early CTAs
+        if ((int64_t)max_clusters(kernel, split, want) * 20 >= clusters * 21) return want;
+    }
+    return smem;
+}
+
 // smem_ring / cache_ring (optional): the same kernel receiving into its rings (GemvArgs::ring_recv): less shared
 // memory, a late cluster barrier; taken only if it allows a larger cluster.
 template <typename K>
@@ -914,15 +955,31 @@ static void launch_kernel(K kernel, int smem, int64_t groups, int64_t nb, const 
         if (split_ring > split) { split = split_ring; smem = smem_ring; B.ring_recv = 1; }
     }
     B.slice_q = (int)(nb / split); B.slice_r = (int)(nb % split);
-    (void)cache_ring;
+    {
+        static int padl = -1;                            // development: LOWBIT_GEMV_PAD_L = resident CTAs per SM to allow
+        if (padl < 0) { const char* e = getenv("LOWBIT_GEMV_PAD_L"); padl = e ? atoi(e) : 0; }
+        if (padl >= 1 && padl <= 8) { const int want = 232448 / padl - 1024 - 64; if (want > smem) smem = want; }
+        else if (padl == 0) smem = balance_smem(kernel, smem, split, groups * grid_z);
+    }
+
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)split, (unsigned)groups, (unsigned)grid_z);
     cfg.blockDim = dim3(GEMV_WARPS * 32); cfg.dynamicSmemBytes = smem; cfg.stream = st;
-    cudaLaunchAttribute at[2];
+    cudaLaunchAttribute at[3];
     int na = 0;
     at[na].id = cudaLaunchAttributeClusterDimension;
     at[na].val.clusterDim.x = split; at[na].val.clusterDim.y = 1; at[na].val.clusterDim.z = 1;
     na++;
+    {
+        // load balancing: the default policy left 6 of 148 SMs without a single CTA of a 172 x 4 launch
+        static int policy = -1;                          // development: LOWBIT_GEMV_CLUSTER_POLICY = 0 default, 1 spread, 2 load balancing
+        if (policy < 0) { const char* e = getenv("LOWBIT_GEMV_CLUSTER_POLICY"); policy = e ? atoi(e) : 2; }
+        if (policy == 1 || policy == 2) {
+            at[na].id = cudaLaunchAttributeClusterSchedulingPolicyPreference;
+            at[na].val.clusterSchedulingPolicyPreference = policy == 1 ? cudaClusterSchedulingPolicySpread : cudaClusterSchedulingPolicyLoadBalancing;
+            na++;
+        }
+    }
     if (A.pdl) {
         at[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
         at[na].val.programmaticStreamSerializationAllowed = 1;
@@ -943,14 +1000,14 @@ static void launch_nt(int m, int64_t groups, int64_t nb, const GemvArgs& A, cuda
         for (auto& row : cache) for (int& v : row) v = -1;
         for (auto& a : cache_tl) for (auto& row : a) for (int& v : row) v = -1;
         for (auto& row : cache_ring) for (int& v : row) v = -1;
-        cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 1, 2, 1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, SG::smem_bytes(1, 2, 1));
-        cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 1, 4, 1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, SG::smem_bytes(1, 4, 1));
-        cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 2, 4, 1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, SG::smem_bytes(2, 4, 1));
-        cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 4, 4, 1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, SG::smem_bytes(4, 4, 1));
-        cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 1, 2, 2, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, SG::smem_bytes(1, 2, 2));
-        cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 1, 4, 2, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, SG::smem_bytes(1, 4, 2));
-        cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 1, 2, 2, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, SG::smem_bytes(1, 2, 2));
-        cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 1, 2, 1, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, SG::smem_bytes(1, 2, 1));
+        cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 1, 2, 1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448);
+        cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 1, 4, 1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448);
+        cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 2, 4, 1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448);
+        cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 4, 4, 1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448);
+        cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 1, 2, 2, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448);
+        cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 1, 4, 2, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448);
+        cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 1, 2, 2, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448);
+        cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 1, 2, 1, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448);
         configured = true;
     }
     if (A.mode == 1) {                   // routed experts' gate/up: one slot per blockIdx.z (M == 1)
