@@ -283,6 +283,15 @@ def run_ours(args):
     if world == 1 and not args.no_cpu_baseline:
         c = cpu_reference(steps=3, warmup=1)
         cpu = {"value": c["value"], "unit": "tok/s", "cores": c["cores"], "kind": "port", "sample": c["sample"]}
+    # DRAM traffic of the dominant kernel from the committed `ncu --set full` capture (profiles/): the capture is
+    # of one gate_proj launch (11008x4096, 23,953,408 algorithmic bytes); scaled to the average launch of the step
+    traffic = None
+    try:
+        prof = json.load(open(os.path.join(ROOT, "profiles", "ncu_full_gemv_r1_final_summary.json")))[0]
+        mb = float(prof["dram__bytes_read.sum"]) * 1e6 + float(prof["dram__bytes_write.sum"])
+        traffic = mb / (INTER * (HIDDEN // 64) * BLK) * algorithmic_bytes() / n_launches()
+    except Exception:  # noqa: BLE001
+        pass
     line = {
         "metric": "sym_int4 decode tok/s (Llama-2-7B, bs1); LowBitLinear GEMV GB/s vs HBM peak",
         "value": world * 1e3 / ms_step, "unit": "tok/s", "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
@@ -295,7 +304,9 @@ def run_ours(args):
                 "d2h_bytes_per_step": 8},
         "gpu_launches": n_launches() * args.steps * 2,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": None, "peak_source": "MEASURED_PEAKS.json hbm_gbs (copy)" if peaks else "fallback 6650",
+                     "traffic": traffic, "traffic_source": "profiles/ncu_full_gemv_r1_final_summary.json: dram read+write of one "
+                                                            "gate_proj launch = 1.0011 x its algorithmic bytes, scaled to the average launch",
+                     "peak_source": "MEASURED_PEAKS.json hbm_gbs (copy)" if peaks else "fallback 6650",
                      "kernel": "lowbit::gemv_kernel<sym_int4,f16,M=1>", "bytes_per_launch_avg": algorithmic_bytes() / n_launches()},
         "clocks": clocks.summary(),
     }

@@ -5,7 +5,10 @@
 
 namespace lowbit {
 
-constexpr int GEMV_WARPS = 4;              // warps per CTA (each warp is an independent pipeline)
+#ifndef LOWBIT_GEMV_WARPS
+#define LOWBIT_GEMV_WARPS 4
+#endif
+constexpr int GEMV_WARPS = LOWBIT_GEMV_WARPS;   // warps per CTA (each warp is an independent pipeline)
 constexpr int GEMV_MAX_SPLIT = 8;           // CTAs per cluster = K slices of one 64-row group
 constexpr int GEMV_MAX_NT = 4;             // n-tiles of 8 activation rows -> M <= 32 per pass
 
