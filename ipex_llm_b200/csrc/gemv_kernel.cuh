@@ -503,8 +503,6 @@ gemv_kernel(const GemvArgs A) {
                 asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(A.next_w + off), "r"((uint32_t)share) : "memory");
         }
     }
-    if (MODE == 0 && A.pdl) asm volatile("griddepcontrol.wait;" ::: "memory");
-    TS(2);
 
     float accm[NM][RG_TILES][NT][ACC];
 #pragma unroll
@@ -551,6 +549,10 @@ gemv_kernel(const GemvArgs A) {
                 }
         xrun += 128;
     };
+    // everything above is independent of the previous kernel's output: the wait sits right before the first
+    // read of x, so the set-up instructions of all resident warps run while the SM would be idle anyway
+    if (MODE == 0 && A.pdl) asm volatile("griddepcontrol.wait;" ::: "memory");
+    TS(2);
     if (XPF && n_super > 0) fetch_x(xq[0]);
 
     uint32_t ones[4];
