@@ -102,10 +102,17 @@ class ClockSampler:
 def cpu_reference(steps, warmup):
     """Time the CPU oracle (mode A) on one decoder layer + lm_head, scale to a full token."""
     import numpy as np
+    # torchrun exports OMP_NUM_THREADS=1 to its workers: the CPU arm uses every host core it can schedule on
+    # (libgomp reads the variable when the oracle library is loaded)
+    try:
+        ncores = len(os.sched_getaffinity(0))
+    except AttributeError:
+        ncores = os.cpu_count() or 1
+    if os.environ.get("LOCAL_RANK") is not None or "OMP_NUM_THREADS" not in os.environ:
+        os.environ["OMP_NUM_THREADS"] = str(ncores)
     import oracle
     rng = np.random.default_rng(0)
-    cores = os.cpu_count() or 1
-    os.environ.setdefault("OMP_NUM_THREADS", str(cores))
+    cores = int(os.environ["OMP_NUM_THREADS"])
     mats = []
     for name, n, k in LAYER_SHAPES + [LM_HEAD]:
         w = (rng.standard_normal((n, k)) * 0.02).astype(np.float32)
