@@ -300,7 +300,7 @@ template <int QT, bool BF> struct Staging {
     // a warp's region: its ring, which later holds its reduction slot
     __host__ __device__ static constexpr int warp_bytes(int nt, int acc, int nm) {
         // M = 2..8 kernels: the four rings together also receive the peers' sums (RINGRECV in the kernel)
-        const int need = (nt == 1 && acc == 4) ? (GEMV_MAX_SPLIT - 1) * nm * slot_bytes(nt, acc) / GEMV_WARPS : nm * slot_bytes(nt, acc);
+        const int need = (nt <= 2 && acc == 4) ? (GEMV_MAX_SPLIT - 1) * nm * slot_bytes(nt, acc) / GEMV_WARPS : nm * slot_bytes(nt, acc);
         return ((kRingBytes > need ? kRingBytes : need) + 127) / 128 * 128;
     }
     // + the leader CTA's receive buffer for its peers' CTA sums (push reduction, M <= 8 kernels)
@@ -460,13 +460,13 @@ gemv_kernel(const GemvArgs A) {
         }
     };
 
-    constexpr bool PUSH = (NT == 1);                   // peers push their sums into the leader (else the leader pulls)
+    constexpr bool PUSH = (NT <= 2);                   // peers push their sums into the leader (else the leader pulls)
     // M == 1: the leader has a small dedicated receive buffer, and the cluster barrier that publishes its
     // mbarrier is split around the main loop (arrive here, wait before the tail: free).  M = 2..8: up to
     // 28 KB would cost a resident CTA per SM, so the peers push into the leader's idle rings instead, after
     // a cluster barrier that follows the leader's own CTA sums (RINGRECV).  That late barrier costs about
     // a microsecond, so the host asks for it (A.ring_recv) only when it buys a larger cluster.
-    const bool RINGRECV = PUSH && (ACC == 4) && A.ring_recv != 0;
+    const bool RINGRECV = PUSH && (ACC == 4) && (NT == 2 || A.ring_recv != 0);       // M = 9..16: always into the rings
     static_assert(!(PUSH && ACC == 4) || (GEMV_MAX_SPLIT - 1) * NM * S::slot_bytes(NT, ACC, 4) <= GEMV_WARPS * WB, "receive area must fit in the rings");
     const uint32_t rbar = smem_u32(smem) + GEMV_WARPS * WB + GEMV_WARPS * STAGES * 8;
     float* recv = reinterpret_cast<float*>(smem + GEMV_WARPS * WB + S::kBarBytes + 8);
@@ -520,7 +520,7 @@ gemv_kernel(const GemvArgs A) {
     const char* const xbase = reinterpret_cast<const char*>(A.x + (int64_t)g * A.G.k + t * 16) + (size_t)kb0 * 128;
     const char* xrun = xbase;
     bool xvalid[NT];
-    constexpr bool XPF = (NT * NS <= 3);
+    constexpr bool XPF = (NT * NS <= 4);
     constexpr int XPF_BUFS = XPF ? 2 : 1;
     // two fragment buffers used alternately by even / odd super-tiles (no copies between them, so the
     // compiler has no reason to delay the prefetch); lanes without a valid row keep zeros
