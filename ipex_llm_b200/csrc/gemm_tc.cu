@@ -496,7 +496,10 @@ static EncodeTiledFn encode_fn() {
 template <int QT, bool BF, int MT>
 static int launch_one(const CUtensorMap& map, const GemmArgs& A, dim3 grid, cudaStream_t st) {
     constexpr int SMEM = Smem<QT>::total(MT);
-    static bool configured = false;
+    static bool configured_dev[64] = {};          // the attribute is per device context
+    int dev_id = 0;
+    cudaGetDevice(&dev_id);
+    bool& configured = configured_dev[dev_id & 63];
     if (!configured) {
         cudaFuncSetAttribute(gemm_kernel<QT, BF, MT>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
         configured = true;

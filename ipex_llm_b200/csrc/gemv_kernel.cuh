@@ -37,6 +37,7 @@
 //  * griddepcontrol.wait sits between the first weight copies and the first read of x, so under
 //    programmatic dependent launch the weight stream of call i+1 overlaps the tail of call i.
 #pragma once
+#include <cstdio>
 #include <cstdlib>
 #include <mutex>
 #include <unordered_map>
@@ -964,6 +965,13 @@ static void launch_kernel(K kernel, int smem, int64_t groups, int64_t nb, const 
         else if (padl == 0) smem = balance_smem(kernel, smem, split, groups * grid_z);
     }
 
+    {
+        static int dbg = -1;                             // development: LOWBIT_GEMV_DEBUG=1 prints every launch geometry
+        if (dbg < 0) { const char* e = getenv("LOWBIT_GEMV_DEBUG"); dbg = e ? atoi(e) : 0; }
+        if (dbg)
+            fprintf(stderr, "[gemv] groups %lld x z %d, nb %lld: cluster %d, smem %d B (ring_recv %d), co-resident clusters at this size %d\n",
+                    (long long)groups, grid_z, (long long)nb, split, smem, B.ring_recv, max_clusters(kernel, split, smem));
+    }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)split, (unsigned)groups, (unsigned)grid_z);
     cfg.blockDim = dim3(GEMV_WARPS * 32); cfg.dynamicSmemBytes = smem; cfg.stream = st;
@@ -994,14 +1002,22 @@ static void launch_kernel(K kernel, int smem, int64_t groups, int64_t nb, const 
 template <int QT, bool BF, int NS>
 static void launch_nt(int m, int64_t groups, int64_t nb, const GemvArgs& A, cudaStream_t st) {
     using SG = Staging<QT, BF>;
-    static bool configured = false;     // per instantiation: raise the dynamic shared memory limit once
+    // per instantiation and device: raise the dynamic shared memory limit once (the attribute is per context)
+    static bool configured_dev[64] = {};
+    int dev_id = 0;
+    cudaGetDevice(&dev_id);
+    bool& configured = configured_dev[dev_id & 63];
+    static bool caches_ready = false;
     static int cache[8][8];
     static int cache_tl[2][4][8];        // [fused MLP][live t-lanes - 1]: the M <= 8 kernels' shared memory depends on M
     static int cache_ring[2][8];         // ... receiving into the rings
-    if (!configured) {
+    if (!caches_ready) {
         for (auto& row : cache) for (int& v : row) v = -1;
         for (auto& a : cache_tl) for (auto& row : a) for (int& v : row) v = -1;
         for (auto& row : cache_ring) for (int& v : row) v = -1;
+        caches_ready = true;
+    }
+    if (!configured) {
         cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 1, 2, 1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448);
         cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 1, 4, 1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448);
         cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 2, 4, 1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448);

@@ -199,7 +199,7 @@ def test_gemv_matches_oracle(lbl, cuda_device, qtype, xdt, M):
 @pytest.mark.parametrize("qtype", ["sym_int4", "asym_int4", "fp8_e4m3"])
 @pytest.mark.parametrize("shape,M", [((16, 64), 1), ((4096, 4096), 1), ((11008, 4096), 2), ((4096, 11008), 1),
                                       ((1000, 704), 5), ((8, 4096), 1), ((250, 128), 12), ((512, 2048), 32),
-                                      ((512, 2048), 40)])
+                                      ((512, 2048), 40), ((1000, 704), 70)])
 def test_gemv_shapes(lbl, cuda_device, qtype, shape, M):
     rng = np.random.default_rng(700)
     N, K = shape
