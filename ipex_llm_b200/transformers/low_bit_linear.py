@@ -346,6 +346,51 @@ def ggml_matmul_src1_x_src0_t(src0: torch.Tensor, src1: torch.Tensor, src0_shape
     return result_t
 
 
+class MatMulLowBit(torch.autograd.Function):
+    """LBL:532-577, the autograd wrapper of the device matmul (QLoRA-style training freezes the packed
+    weight: only the activation gets a gradient).  forward = the dequant-GEMV / GEMM kernels,
+    backward = grad_output @ dequant(W) with W dequantised by the tiled-layout kernel."""
+
+    @staticmethod
+    def forward(ctx, A, weight, output_size):
+        shape = tuple(weight._shape)
+        invalidInputError(shape[0] == output_size, "output_size does not match the weight")
+        A_2d = A.reshape(-1, A.shape[-1])
+        result = lowbit_matmul(A_2d, weight.data, shape, weight.qtype).view(A.shape[:-1] + (output_size,))
+        ctx.tensors = (A, weight) if any(ctx.needs_input_grad[:2]) else (None, None)
+        return result
+
+    @staticmethod
+    def backward(ctx, grad_output):
+        A, weight = ctx.tensors
+        grad_A = None
+        if ctx.needs_input_grad[0]:
+            dequant_weight = dequantize_device_layout(weight.data, tuple(weight._shape), weight.qtype, dtype=grad_output.dtype)
+            grad_A = torch.matmul(grad_output, dequant_weight)
+        return grad_A, None, None
+
+
+class MatMulLowBitCPU(torch.autograd.Function):
+    """LBL:580-602: the host-pointer variant (canonical packed weight in CPU memory); this is the statement
+    of the "mode B" semantics the kernels are checked against: A @ dequant(W).T"""
+
+    @staticmethod
+    def forward(ctx, A, weight):
+        x0_fp32 = ggml_convert_fp32(weight.data, weight._shape, weight._shape[0] * weight._shape[1], weight.qtype)
+        result = torch.matmul(A, x0_fp32.T.to(A.dtype))
+        ctx.tensors = (A, weight) if any(ctx.needs_input_grad[:2]) else (None, None)
+        return result
+
+    @staticmethod
+    def backward(ctx, grad_output):
+        A, weight = ctx.tensors
+        grad_A = None
+        if ctx.needs_input_grad[0]:
+            x0_fp32 = ggml_convert_fp32(weight.data, weight._shape, weight._shape[0] * weight._shape[1], weight.qtype)
+            grad_A = torch.matmul(grad_output, x0_fp32.to(grad_output.dtype))
+        return grad_A, None, None
+
+
 class FP4Params(torch.nn.Parameter):
     """LBL:332-491.  Holds the packed weight; quantises on the first ``.to()``.
 

@@ -373,3 +373,31 @@ def test_gemm_prefill_epilogue_and_module(lbl, cuda_device):
     # the GEMV (M <= 32, exact) and the GEMM (fp16-rounded weights) agree to the GEMM's tolerance
     small = run_matmul(lbl, cuda_device, packed, (N, K), "sym_int4", x_t[:32], out_dtype=torch.float32)
     torch.testing.assert_close(base[:32], small, rtol=2e-3, atol=2e-3)
+
+
+# ---------------------------------------------------------------- autograd wrappers (LBL:532-602)
+@pytest.mark.parametrize("qtype", ["sym_int4", "nf4", "fp8_e4m3"])
+def test_matmul_lowbit_autograd(lbl, cuda_device, qtype):
+    """forward = the device kernels, backward = grad @ dequant(W): both against the oracle-dequantised weight"""
+    rng = np.random.default_rng(1500)
+    N, K, M = 192, 256, 5
+    packed = oracle.quantize(rand_w(rng, N, K), qtype)
+    wd = torch.from_numpy(oracle.dequantize(packed, (N, K), qtype)).to(cuda_device)
+    p = torch.from_numpy(packed)
+    if qtype == "nf4":
+        p = p.view(torch.bfloat16)
+    weight = lbl.FP4Params(p, quantized=True, _shape=torch.Size((N, K)), qtype=qid(qtype)).to(cuda_device)
+    x = torch.from_numpy(rng.standard_normal((2, M, K)).astype(np.float32)).to(cuda_device).requires_grad_(True)
+    y = lbl.MatMulLowBit.apply(x, weight, N)
+    assert y.shape == (2, M, N)
+    torch.testing.assert_close(y, x.detach() @ wd.T, rtol=2e-5, atol=2e-5)
+    g = torch.from_numpy(rng.standard_normal((2, M, N)).astype(np.float32)).to(cuda_device)
+    y.backward(g)
+    torch.testing.assert_close(x.grad, g @ wd, rtol=1e-5, atol=1e-5)
+    # host-pointer variant on the canonical CPU weight
+    wcpu = lbl.FP4Params(p, quantized=True, _shape=torch.Size((N, K)), qtype=qid(qtype))
+    xc = x.detach().cpu().requires_grad_(True)
+    yc = lbl.MatMulLowBitCPU.apply(xc, wcpu)
+    torch.testing.assert_close(yc, xc.detach() @ wd.cpu().T, rtol=1e-5, atol=1e-5)
+    yc.backward(g.cpu())
+    torch.testing.assert_close(xc.grad, g.cpu() @ wd.cpu(), rtol=1e-5, atol=1e-5)
