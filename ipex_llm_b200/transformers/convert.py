@@ -177,6 +177,20 @@ def convert_gptq(module, awq=False, llm_awq=False, act_order=False):
     return rec.reshape(-1), g_idx_map
 
 
+def convert_vllm_awq_or_gptq(module, gptq=False, act_order=False):
+    """vLLM's AWQ / GPTQ linear -> asym_int4 block records (reference CV:301-379).  Same repacking as
+    ``convert_gptq``; vLLM keeps the bit width and group size on ``module.quant_method.quant_config`` and uses
+    AutoAWQ's nibble order (0, 4, 1, 5, 2, 6, 3, 7) for AWQ, the natural order for GPTQ."""
+    import types
+    cfg = module.quant_method.quant_config
+    order = [0, 1, 2, 3, 4, 5, 6, 7] if gptq else [0, 4, 1, 5, 2, 6, 3, 7]
+    shim = types.SimpleNamespace(
+        qweight=module.qweight, qzeros=module.qzeros, scales=module.scales,
+        bits=int(cfg.weight_bits) if gptq else 4, group_size=int(cfg.group_size),
+        wf=(torch.tensor(order, dtype=torch.int32) * 4).unsqueeze(0), g_idx=getattr(module, "g_idx", None))
+    return convert_gptq(shim, awq=not gptq, llm_awq=False, act_order=act_order)
+
+
 def merge_quantized_qkv(q, k, v):
     """packed CANONICAL q, k, v (same qtype, same in_features) -> one packed qkv weight: rows are
     block-contiguous in the canonical layout, so this is a byte concatenation on the CPU side

@@ -69,3 +69,45 @@ def test_scale_search_policy_and_meta_conversion(native_lib):
     assert net.lm_head.optimize_lm_head and not net.a.optimize_lm_head
     with pytest.raises(RuntimeError):
         ggml_convert_low_bit(Net(), 8)                  # sym_int8: not implemented, loud
+
+
+def test_convert_vllm_awq_or_gptq(native_lib):
+    """vLLM flavour (attributes on quant_method.quant_config): GPTQ gives the reference bytes of the golden
+    fixture; AWQ (words along the output dimension, AutoAWQ nibble order, zero stored as is) dequantises to
+    (code - zero) * scale."""
+    from ipex_llm_b200.transformers.convert import convert_vllm_awq_or_gptq
+    g = np.load(os.path.join(GOLD, "ref_python_q4.npz"))
+    ints, zeros, scales = g["gptq_ints"].astype(np.int64), g["gptq_zeros"].astype(np.int64), g["gptq_scales"]
+    in_f, out_f = ints.shape
+    group = in_f // zeros.shape[0]
+    cfg = types.SimpleNamespace(weight_bits=4, group_size=group)
+    qm = types.SimpleNamespace(quant_config=cfg)
+
+    def pack_last(a, order):                      # [r, c] codes -> [r, c / 8] int32 words, code i of a word at nibble order[i]
+        w = np.zeros((a.shape[0], a.shape[1] // 8), dtype=np.int64)
+        for i in range(8):
+            w |= a[:, i::8] << (4 * order[i])
+        return torch.from_numpy(w.astype(np.uint32).view(np.int32))
+
+    nat = list(range(8))
+    qweight = pack_last(ints.T.copy(), nat).t().contiguous()                   # GPTQ: words along `in`
+    mod = types.SimpleNamespace(scales=torch.from_numpy(scales), qzeros=pack_last(zeros, nat), qweight=qweight, quant_method=qm)
+    packed, gmap = convert_vllm_awq_or_gptq(mod, gptq=True)
+    assert gmap is None
+    np.testing.assert_array_equal(packed.numpy(), g["gptq_bytes"])
+
+    rng = np.random.default_rng(7)
+    codes = rng.integers(0, 16, size=(in_f, out_f)).astype(np.int64)
+    z = rng.integers(0, 16, size=zeros.shape).astype(np.int64)
+
+    def pack_awq(a):                               # AutoAWQ: nibble p of a word holds column awq-order^-1
+        w = np.zeros((a.shape[0], a.shape[1] // 8), dtype=np.int64)
+        for p_, col in enumerate([0, 2, 4, 6, 1, 3, 5, 7]):
+            w |= a[:, col::8] << (4 * p_)
+        return torch.from_numpy(w.astype(np.uint32).view(np.int32))
+
+    mod = types.SimpleNamespace(scales=torch.from_numpy(scales), qzeros=pack_awq(z), qweight=pack_awq(codes), quant_method=qm)
+    packed, _ = convert_vllm_awq_or_gptq(mod, gptq=False)
+    want = (codes.T - np.repeat(z, group, axis=0).T) * np.repeat(scales.astype(np.float32), group, axis=0).T
+    got = oracle.dequantize(packed.numpy(), (out_f, in_f), "asym_int4")
+    np.testing.assert_allclose(got, want, rtol=0, atol=2e-3 * np.abs(want).max())
