@@ -100,6 +100,13 @@ int ggml_dequantize_cuda(const void* d_src, void* d_dst, size_t k, int qtype, in
 /* dequantize a [rows][k] weight held in the DEVICE (tiled) layout */
 int lowbit_dequantize_device_layout_cuda(const void* d_src, void* d_dst, int64_t rows, int64_t k,
                                          int qtype, int out_dtype, void* stream);
+/* rows of a device-layout [rows][k] weight picked by an index vector and dequantised -- the XPU op
+ * `xe_linear.dequantize_rows(ids, qweight, qtype, embedding_dim, num_embeddings)` behind LowBitEmbedding.forward
+ * (transformers/embedding.py:214-224).  d_ids: n_ids indices (ids_dtype 0 = int32, 1 = int64) read on the
+ * device; an index outside [0, rows) yields a zero row.  d_out: [n_ids][k] of out_dtype.  Same arithmetic as
+ * the dequantise kernels (bit-exact against the oracle). */
+int lowbit_dequantize_rows_cuda(const void* d_w, int qtype, int64_t rows, int64_t k, const void* d_ids,
+                                int ids_dtype, int64_t n_ids, void* d_out, int out_dtype, void* stream);
 /* canonical <-> device layout on device buffers (same byte size, src != dst).
  * to_device != 0: canonical -> tiled ; 0: tiled -> canonical. */
 int lowbit_relayout_cuda(const void* d_src, void* d_dst, int64_t rows, int64_t k, int qtype,

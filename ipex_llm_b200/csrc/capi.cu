@@ -137,6 +137,18 @@ int lowbit_dequantize_device_layout_cuda(const void* d_src, void* d_dst, int64_t
     return rc;
 }
 
+int lowbit_dequantize_rows_cuda(const void* d_w, int qtype, int64_t rows, int64_t k, const void* d_ids, int ids_dtype,
+                                int64_t n_ids, void* d_out, int out_dtype, void* stream) {
+    t_launches = 0;
+    if (!d_w || (n_ids > 0 && (!d_ids || !d_out)) || (ids_dtype != 0 && ids_dtype != 1)) {
+        set_error(LB_ERR_ARG, "lowbit_dequantize_rows_cuda: null pointer or bad ids_dtype");
+        return LB_ERR_ARG;
+    }
+    int rc = dequant_rows_launch(d_w, d_out, d_ids, ids_dtype, n_ids, rows, k, qtype, out_dtype, (cudaStream_t)stream);
+    if (rc == LB_ERR_ARG) set_error(rc, "lowbit_dequantize_rows_cuda: bad argument (rows %lld, k %lld, qtype %d)", (long long)rows, (long long)k, qtype);
+    return rc;
+}
+
 int lowbit_relayout_cuda(const void* d_src, void* d_dst, int64_t rows, int64_t k, int qtype, int to_device,
                          void* stream) {
     t_launches = 0;

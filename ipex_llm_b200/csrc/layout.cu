@@ -146,6 +146,37 @@ __global__ void dequant_kernel(const uint8_t* __restrict__ src, OutT* __restrict
     }
 }
 
+// rows of a TILED-layout weight picked by an index vector (LowBitEmbedding, reference embedding.py:214-224:
+// xe_linear.dequantize_rows): out[t][:] = dequant(W[ids[t]][:]); an index outside [0, rows) gives a zero row.
+template <typename OutT>
+__global__ void dequant_rows_kernel(const uint8_t* __restrict__ src, OutT* __restrict__ dst, const void* __restrict__ ids,
+                                    int ids_i64, int64_t n_ids, TiledGeom G, int qt) {
+    const int hdr = header_bytes(qt);
+    const int64_t n_elems = n_ids * G.k;
+    for (int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; idx < n_elems;
+         idx += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t t = idx / G.k, col = idx % G.k;
+        const int64_t row = ids_i64 ? ((const long long*)ids)[t] : (long long)((const int*)ids)[t];
+        if (row < 0 || row >= G.rows) { dst[idx] = from_float<OutT>(0.0f); continue; }
+        const int64_t kb = col / QK;
+        const int j = (int)(col % QK);
+        uint32_t code; uint16_t dh, mh = 0;
+        if (row < G.r64) {
+            code = tiled_code(qt, src + tile_code_offset(G, row, kb), (int)(row % 16), j);
+            dh = *(const uint16_t*)(src + G.off_s + scale_offset(G, row, kb));
+            if (G.has_m) mh = *(const uint16_t*)(src + G.off_m + scale_offset(G, row, kb));
+        } else {
+            const uint8_t* rec = src + G.off_tail + ((row - G.r64) * G.nb + kb) * G.blk_bytes;
+            dh = (uint16_t)rec[0] | ((uint16_t)rec[1] << 8);
+            if (G.has_m) mh = (uint16_t)rec[2] | ((uint16_t)rec[3] << 8);
+            code = canonical_code(qt, rec + hdr, j);
+        }
+        float v = __fmul_rn(code_value(qt, code), half_bits_to_float(dh));
+        if (G.has_m) v = __fadd_rn(v, half_bits_to_float(mh));
+        dst[idx] = from_float<OutT>(v);
+    }
+}
+
 static int grid_for(int64_t total, int threads) {
     int64_t b = (total + threads - 1) / threads;
     const int64_t cap = 148 * 32;
@@ -191,6 +222,23 @@ int dequant_tiled_launch(const void* src, void* dst, int64_t rows, int64_t k, in
     if (!supported(qt) || k <= 0 || k % QK || rows <= 0) return LB_ERR_ARG;
     TiledGeom G = make_geom(rows, k, qt);
     return dequant_dispatch<true>(src, dst, rows * k, G, qt, out_dtype, st);
+}
+
+int dequant_rows_launch(const void* src, void* dst, const void* ids, int ids_i64, int64_t n_ids, int64_t rows, int64_t k,
+                        int qt, int out_dtype, cudaStream_t st) {
+    qt = canon_qtype(qt);
+    if (!supported(qt) || k <= 0 || k % QK || rows <= 0 || n_ids < 0) return LB_ERR_ARG;
+    if (n_ids == 0) return LB_OK;
+    const TiledGeom G = make_geom(rows, k, qt);
+    const int grid = grid_for(n_ids * k, 256);
+    switch (out_dtype) {
+        case DT_F32: dequant_rows_kernel<float><<<grid, 256, 0, st>>>((const uint8_t*)src, (float*)dst, ids, ids_i64, n_ids, G, qt); break;
+        case DT_F16: dequant_rows_kernel<__half><<<grid, 256, 0, st>>>((const uint8_t*)src, (__half*)dst, ids, ids_i64, n_ids, G, qt); break;
+        case DT_BF16: dequant_rows_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>((const uint8_t*)src, (__nv_bfloat16*)dst, ids, ids_i64, n_ids, G, qt); break;
+        default: return LB_ERR_ARG;
+    }
+    note_launch();
+    return check_launch();
 }
 
 }  // namespace lowbit

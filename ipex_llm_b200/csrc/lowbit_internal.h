@@ -28,6 +28,9 @@ int dequant_canonical_launch(const void* src, void* dst, size_t n, int qt, int o
 int dequant_tiled_launch(const void* src, void* dst, int64_t rows, int64_t k, int qt, int out_dtype,
                          cudaStream_t st);
 
+int dequant_rows_launch(const void* src, void* dst, const void* ids, int ids_i64, int64_t n_ids, int64_t rows, int64_t k,
+                        int qt, int out_dtype, cudaStream_t st);
+
 // quantize.cu
 int quantize_launch(const float* src, void* dst, int qt, size_t n, int k, int64_t* hist, bool scale_search,
                     cudaStream_t st);

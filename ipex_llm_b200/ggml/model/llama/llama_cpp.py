@@ -197,6 +197,16 @@ def lowbit_matmul_cuda(d_w, qtype, n_rows, k, d_x, x_dtype, m, d_y, y_dtype, d_b
            "lowbit_matmul_cuda")
 
 
+_lib.lowbit_dequantize_rows_cuda.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_int64, ctypes.c_void_p,
+                                             ctypes.c_int, ctypes.c_int64, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p]
+_lib.lowbit_dequantize_rows_cuda.restype = ctypes.c_int
+
+
+def lowbit_dequantize_rows_cuda(d_w, qtype, rows, k, d_ids, ids_dtype, n_ids, d_out, out_dtype, stream):
+    _check(_lib.lowbit_dequantize_rows_cuda(d_w, qtype, rows, k, d_ids, ids_dtype, n_ids, d_out, out_dtype, stream),
+           "lowbit_dequantize_rows_cuda")
+
+
 _lib.lowbit_mlp_workspace_size.argtypes = [ctypes.c_int64, ctypes.c_int64, ctypes.c_int64, ctypes.c_int]
 _lib.lowbit_mlp_workspace_size.restype = ctypes.c_size_t
 _lib.lowbit_mlp_cuda.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_int64,

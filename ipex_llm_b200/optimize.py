@@ -95,6 +95,15 @@ def load_low_bit(model, model_path):
     return model
 
 
+def _embedding_qtype(name):
+    """``embedding_qtype=`` of from_pretrained / optimize_model (reference model.py:148, 436-439): the reference
+    offers its k-quants there; here any of the in-scope block formats."""
+    if name is None:
+        return None
+    invalidInputError(name in ggml_tensor_qtype, f"Unknown embedding_qtype: {name}")
+    return ggml_tensor_qtype[name]
+
+
 def optimize_model(model, low_bit="sym_int4", optimize_llm=True, modules_to_not_convert=None,
                    cpu_embedding=False, **kwargs):
     """OP:199-267.  Requires the model on cpu or meta (OP:236-239); returns it with its eligible linears
@@ -111,7 +120,8 @@ def optimize_model(model, low_bit="sym_int4", optimize_llm=True, modules_to_not_
     if low_bit is not None:
         model = ggml_convert_low_bit(model, qtype=ggml_tensor_qtype[low_bit], optimize_model=optimize_llm,
                                      modules_to_not_convert=modules_to_not_convert,
-                                     torch_dtype=kwargs.get("torch_dtype", "auto"))
+                                     torch_dtype=kwargs.get("torch_dtype", "auto"),
+                                     embedding_qtype=_embedding_qtype(kwargs.get("embedding_qtype", None)))
     model._bigdl_config = {"bigdl_transformers_low_bit": low_bit}
     model.save_low_bit = types.MethodType(_save_low_bit, model)
     return model

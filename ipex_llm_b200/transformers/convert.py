@@ -47,7 +47,7 @@ def use_scale_search(model_config, qtype):
 
 
 def _replace_with_low_bit_linear(model, qtype, modules_to_not_convert=None, convert_shape_only=False,
-                                 prefix_name="", model_config=None, enable_scale_search=False):
+                                 prefix_name="", model_config=None, enable_scale_search=False, embedding_qtype=None):
     """CV:472-752.  Linears whose in_features is not a multiple of 64 stay as they are (CV:615-617);
     lm_head (by name or vocab-sized output) gets ``optimize_lm_head`` unless IPEX_LLM_LAST_LM_HEAD=0
     (CV:504-513).  Quantisation happens inside ``FP4Params.to(device)`` of the module's own device."""
@@ -82,10 +82,15 @@ def _replace_with_low_bit_linear(model, qtype, modules_to_not_convert=None, conv
             model._modules[name].requires_grad_(False)
             has_been_replaced = True
             module.weight = None
+        elif embedding_qtype is not None and type(module) == nn.Embedding and module.embedding_dim % 64 == 0:
+            # CV:730-733: the embedding table in a low-bit block format, dequantised row by row on the GPU
+            from ipex_llm_b200.transformers.embedding import LowBitEmbedding
+            model._modules[name] = LowBitEmbedding.from_embedding(module, convert_shape_only, embedding_qtype)
         if len(list(module.children())) > 0:
             _, flag = _replace_with_low_bit_linear(module, qtype, modules_to_not_convert, convert_shape_only,
                                                    prefix_name=full_module_name, model_config=model_config,
-                                                   enable_scale_search=enable_scale_search)
+                                                   enable_scale_search=enable_scale_search,
+                                                   embedding_qtype=embedding_qtype)
             has_been_replaced = flag or has_been_replaced
     return model, has_been_replaced
 
@@ -100,7 +105,7 @@ def convert_bigdl_other_module(model, dtype):
 
 
 def ggml_convert_low_bit(model, qtype, optimize_model=True, convert_shape_only=False, device="cpu",
-                         modules_to_not_convert=None, torch_dtype="auto", **unused):
+                         modules_to_not_convert=None, torch_dtype="auto", embedding_qtype=None, **unused):
     """CV:1092-1193.  ``woq_int4`` is the same format as ``sym_int4`` (CV:1101-1109)."""
     if qtype == ggml_tensor_qtype["woq_int4"]:
         qtype = ggml_tensor_qtype["sym_int4"]
@@ -110,7 +115,8 @@ def ggml_convert_low_bit(model, qtype, optimize_model=True, convert_shape_only=F
     enable_scale_search = use_scale_search(model_config, qtype)
     model, has_been_replaced = _replace_with_low_bit_linear(model, qtype, modules_to_not_convert or [],
                                                             convert_shape_only, model_config=model_config,
-                                                            enable_scale_search=enable_scale_search)
+                                                            enable_scale_search=enable_scale_search,
+                                                            embedding_qtype=embedding_qtype)
     if not has_been_replaced:
         warnings.warn("No linear modules were found in your model.")
     elif device == "cpu" and torch_dtype != "auto":

@@ -401,3 +401,30 @@ def test_matmul_lowbit_autograd(lbl, cuda_device, qtype):
     torch.testing.assert_close(yc, xc.detach() @ wd.cpu().T, rtol=1e-5, atol=1e-5)
     yc.backward(g.cpu())
     torch.testing.assert_close(xc.grad, g.cpu() @ wd.cpu(), rtol=1e-5, atol=1e-5)
+
+
+# ---------------------------------------------------------------- LowBitEmbedding (reference embedding.py:179-241)
+@pytest.mark.parametrize("qtype", QTYPES)
+def test_lowbit_embedding_rows_bit_exact(cuda_device, native_lib, qtype):
+    from ipex_llm_b200.transformers.embedding import LowBitEmbedding
+    rng = np.random.default_rng(1600)
+    V, D = 203, 256                                   # ragged row count: the last 11 rows live in the canonical tail
+    table = rand_w(rng, V, D, "wide")
+    emb = torch.nn.Embedding(V, D)
+    emb.weight.data = torch.from_numpy(table)
+    low = LowBitEmbedding.from_embedding(emb, False, qid(qtype)).to(cuda_device)
+    want = oracle.dequantize(oracle.quantize(table, qtype), (V, D), qtype)
+    ids = torch.from_numpy(rng.integers(0, V, size=(3, 17))).to(cuda_device)
+    ids[0, 0], ids[0, 1], ids[2, 16] = 0, V - 1, 192
+    got = low(ids)
+    assert got.shape == (3, 17, D) and got.dtype == torch.float32
+    np.testing.assert_array_equal(got.cpu().numpy(), want[ids.cpu().numpy()])
+    got32 = low(ids.int())                            # int32 indices
+    assert torch.equal(got32, got)
+    bad = torch.tensor([[V, -1, 5]], device=cuda_device)
+    out = low(bad)
+    assert float(out[0, 0].abs().max()) == 0.0 and float(out[0, 1].abs().max()) == 0.0
+    np.testing.assert_array_equal(out[0, 2].cpu().numpy(), want[5])
+    # fp16 model dtype: values rounded once
+    low16 = LowBitEmbedding.from_embedding(emb.half(), False, qid(qtype)).to(cuda_device)
+    np.testing.assert_array_equal(low16(ids).float().cpu().numpy(), want[ids.cpu().numpy()].astype(np.float16).astype(np.float32))

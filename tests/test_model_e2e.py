@@ -104,3 +104,23 @@ def test_auto_model_surface_and_round_trip(native_lib, cuda_device, tmp_path):
     with torch.no_grad():
         lg = model(long_ids).logits
     assert torch.isfinite(lg).all()
+
+
+def test_optimize_model_low_bit_embedding(native_lib, cuda_device):
+    """embedding_qtype: the token embedding becomes a LowBitEmbedding (reference convert.py:730-733); logits match
+    the model whose embedding table and linears were replaced by their oracle-dequantised values."""
+    from ipex_llm_b200 import optimize_model
+    from ipex_llm_b200.transformers.embedding import LowBitEmbedding
+    base = tiny_llama()
+    ref = oracle_dequantised_copy(base, "sym_int4")
+    table = base.model.embed_tokens.weight.data.float().numpy()
+    ref.model.embed_tokens.weight.data = torch.from_numpy(
+        oracle.dequantize(oracle.quantize(table, "fp8_e4m3"), table.shape, "fp8_e4m3"))
+    model = optimize_model(base, low_bit="sym_int4", embedding_qtype="fp8_e4m3").to(cuda_device)
+    assert isinstance(model.model.embed_tokens, LowBitEmbedding)
+    ids = torch.randint(0, 320, (1, 8), generator=torch.Generator().manual_seed(3))
+    with torch.no_grad():
+        want = ref(ids).logits
+        got = model(ids.to(cuda_device)).logits.float().cpu()
+    rel = (got - want).abs().mean() / want.abs().mean()
+    assert rel < 2e-3, float(rel)
