@@ -425,6 +425,12 @@ def test_lowbit_embedding_rows_bit_exact(cuda_device, native_lib, qtype):
     out = low(bad)
     assert float(out[0, 0].abs().max()) == 0.0 and float(out[0, 1].abs().max()) == 0.0
     np.testing.assert_array_equal(out[0, 2].cpu().numpy(), want[5])
-    # fp16 model dtype: values rounded once
-    low16 = LowBitEmbedding.from_embedding(emb.half(), False, qid(qtype)).to(cuda_device)
-    np.testing.assert_array_equal(low16(ids).float().cpu().numpy(), want[ids.cpu().numpy()].astype(np.float16).astype(np.float32))
+    # fp16 model: the fp16 table is what gets quantised, and the output is rounded once to fp16
+    emb16 = torch.nn.Embedding(V, D)
+    emb16.weight.data = torch.from_numpy(table).half()
+    t16 = emb16.weight.data.float().numpy()
+    want16 = oracle.dequantize(oracle.quantize(t16, qtype), (V, D), qtype)
+    low16 = LowBitEmbedding.from_embedding(emb16, False, qid(qtype)).to(cuda_device)
+    got16 = low16(ids)
+    assert got16.dtype == torch.float16
+    np.testing.assert_array_equal(got16.float().cpu().numpy(), want16[ids.cpu().numpy()].astype(np.float16).astype(np.float32))
