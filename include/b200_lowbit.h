@@ -107,6 +107,30 @@ int lowbit_dequantize_device_layout_cuda(const void* d_src, void* d_dst, int64_t
  * the dequantise kernels (bit-exact against the oracle). */
 int lowbit_dequantize_rows_cuda(const void* d_w, int qtype, int64_t rows, int64_t k, const void* d_ids,
                                 int ids_dtype, int64_t n_ids, void* d_out, int out_dtype, void* stream);
+/* ---- FP8 key/value cache: DynamicFp8Cache (transformers/kv.py:33-77) keeps K and V as uint8
+ * [batch, kv_heads, len, head_dim].  The reference's xe_addons kernels are closed; the byte format here is
+ * BUILD-DEFINED: one e5m2 code per element (round to nearest even, saturating), no scales.
+ * Tensors are 4-D views [B][H][S][D] with D contiguous; strides[3] = element strides of B, H, S (host array).
+ * lowbit_kv_quantize_cuda   = xe_addons.quantize_key_value   (models/utils.py:132-134), one call per tensor
+ * lowbit_kv_dequantize_cuda = xe_addons.dequantize_key_value (models/utils.py:181-187) */
+int lowbit_kv_quantize_cuda(const void* d_src, int src_dtype, const int64_t* src_strides, void* d_dst,
+                            const int64_t* dst_strides, int64_t B, int64_t H, int64_t S, int64_t D, void* stream);
+int lowbit_kv_dequantize_cuda(const void* d_src, const int64_t* src_strides, void* d_dst, int dst_dtype,
+                              const int64_t* dst_strides, int64_t B, int64_t H, int64_t S, int64_t D, void* stream);
+/* Decode attention over the FP8 cache -- xe_addons.sdp_fp8(query, key, value, mask, scale)
+ * (models/common.py:279-283: key.dtype == uint8, seq_length <= 32).  q [B][Hq][S][D] (q_dtype), k / v uint8
+ * [B][Hkv][L][D] (GQA: Hq a multiple of Hkv), mask NULL or additive [B][1|Hq][S][L] (mask_strides[1] = 0
+ * broadcasts over heads), causal != 0: query token s sees keys <= L - S + s.  out [B][Hq][S][D] contiguous.
+ * Softmax and accumulation in fp32; split over the key axis with a deterministic merge (two launches).
+ * Key cache pointer and strides 16-byte aligned, value cache 4-byte.  D in {64, 96, 128, 192, 256}, S <= 32. */
+int lowbit_sdp_fp8_supported(int Hq, int Hkv, int S, int D);
+size_t lowbit_sdp_fp8_workspace_size(int B, int Hq, int Hkv, int S, int L, int D);
+int lowbit_sdp_fp8_cuda(const void* d_q, int q_dtype, const int64_t* q_strides, const void* d_k,
+                        const int64_t* k_strides, const void* d_v, const int64_t* v_strides, const void* d_mask,
+                        int mask_dtype, const int64_t* mask_strides, int causal, float scale, int B, int Hq, int Hkv,
+                        int S, int L, int D, void* d_out, int out_dtype, void* workspace, size_t workspace_bytes,
+                        void* stream);
+
 /* canonical <-> device layout on device buffers (same byte size, src != dst).
  * to_device != 0: canonical -> tiled ; 0: tiled -> canonical. */
 int lowbit_relayout_cuda(const void* d_src, void* d_dst, int64_t rows, int64_t k, int qtype,

@@ -27,6 +27,7 @@ void set_error(int code, const char* fmt, ...) {
     va_end(ap);
 }
 void note_launch() { t_launches++; }
+void reset_launch_count() { t_launches = 0; }
 int check_launch() {
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) { set_error(LB_ERR_CUDA, "CUDA error: %s", cudaGetErrorString(e)); return LB_ERR_CUDA; }

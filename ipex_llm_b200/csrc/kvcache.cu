@@ -1,0 +1,371 @@
+// kvcache.cu -- FP8 key/value cache and the decode attention that reads it.
+//
+// Reference: DynamicFp8Cache (transformers/kv.py:33-77) keeps K and V as uint8 [batch, kv_heads, len, head_dim]
+// (models/utils.py:103-139: init_fp8_kv_cache / append_fp8_kv_cache -> xe_addons.quantize_key_value, restore ->
+// xe_addons.dequantize_key_value) and scaled_dot_product_attention (models/common.py:250-306) calls
+// xe_addons.sdp_fp8* when key.dtype == uint8.  The xe_addons kernels are closed binaries; the byte format is
+// BUILD-DEFINED here: one e5m2 code per element (round-to-nearest-even, saturating to +-57344; no scales --
+// the cache tensor has exactly the shape of the fp16 one), i.e. the high byte of the fp16 value after rounding.
+//
+// Kernels:
+//   kv_quantize / kv_dequantize : elementwise, strided 4-D views (the cache is an as_strided view of a larger buffer)
+//   sdp_fp8_decode              : q rows <= 32 per (batch, kv head) incl. the GQA group; split-KV over blockIdx.x,
+//                                 one lane per key for q.k, one lane per 4 head-dim elements for p.v, online
+//                                 softmax in fp32; partial (m, l, o) per split -> sdp_fp8_combine
+#include <cuda_fp16.h>
+#include <cuda_bf16.h>
+#include <cuda_fp8.h>
+#include <math_constants.h>
+#include "../../include/b200_lowbit.h"
+#include "lowbit_common.cuh"
+#include "lowbit_internal.h"
+
+namespace lowbit {
+namespace {
+
+struct View4 {                 // [b][h][s][d] with d contiguous; strides in elements
+    int64_t sb, sh, ss;
+};
+
+__device__ __forceinline__ uint8_t to_e5m2(float v) {
+    return (uint8_t)__nv_cvt_float_to_fp8(v, __NV_SATFINITE, __NV_E5M2);
+}
+__device__ __forceinline__ float from_e5m2(uint8_t c) {
+    __half_raw hr; hr.x = (unsigned short)((unsigned short)c << 8);
+    return __half2float(__half(hr));
+}
+
+template <typename T>
+__global__ void kv_quantize_kernel(const T* __restrict__ src, View4 vs, uint8_t* __restrict__ dst, View4 vd,
+                                   int64_t B, int64_t H, int64_t S, int64_t D) {
+    const int64_t total = B * H * S * D;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t d = i % D, s = (i / D) % S, h = (i / (D * S)) % H, b = i / (D * S * H);
+        dst[b * vd.sb + h * vd.sh + s * vd.ss + d] = to_e5m2(to_float<T>(src[b * vs.sb + h * vs.sh + s * vs.ss + d]));
+    }
+}
+
+template <typename T>
+__global__ void kv_dequantize_kernel(const uint8_t* __restrict__ src, View4 vs, T* __restrict__ dst, View4 vd,
+                                     int64_t B, int64_t H, int64_t S, int64_t D) {
+    const int64_t total = B * H * S * D;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t d = i % D, s = (i / D) % S, h = (i / (D * S)) % H, b = i / (D * S * H);
+        dst[b * vd.sb + h * vd.sh + s * vd.ss + d] = from_float<T>(from_e5m2(src[b * vs.sb + h * vs.sh + s * vs.ss + d]));
+    }
+}
+
+int grid_for(int64_t total) {
+    int64_t b = (total + 255) / 256;
+    const int64_t cap = (int64_t)sm_count() * 16;
+    return (int)(b < 1 ? 1 : (b > cap ? cap : b));
+}
+
+
+// ------------------------------------------------------------------ decode attention over the FP8 cache
+constexpr int SDP_WARPS = 4;
+constexpr int SDP_RT = 4;                  // query rows per CTA (GQA group x new tokens, tiled by blockIdx.z)
+
+struct SdpArgs {
+    const void* q; int q_dtype; int64_t q_sb, q_sh, q_ss;        // [B][Hq][S][D]
+    const uint8_t* k; int64_t k_sb, k_sh, k_ss;                   // [B][Hkv][L][D] e5m2
+    const uint8_t* v; int64_t v_sb, v_sh, v_ss;
+    const void* mask; int mask_dtype; int64_t m_sb, m_sh, m_ss;   // additive [B][1|Hq][S][L] or NULL
+    int causal;                                                    // row s sees keys <= L - S + s
+    float scale_log2e;                                             // scale * log2(e)
+    int B, Hq, Hkv, S, L, D;
+    int n_split, keys_per_split;
+    float* part;                                                   // [B][Hkv][row tiles][n_split][RT * (D + 2)]
+    void* out; int out_dtype;                                      // [B][Hq][S][D] contiguous
+};
+
+__device__ __forceinline__ float load_as_float(const void* p, int dt, int64_t i) {
+    if (dt == DT_F32) return ((const float*)p)[i];
+    if (dt == DT_F16) return __half2float(((const __half*)p)[i]);
+    return __bfloat162float(((const __nv_bfloat16*)p)[i]);
+}
+
+// two e5m2 codes (bytes b0, b1 of `w` selected by sel) -> float2: e5m2 is the high byte of fp16
+__device__ __forceinline__ float2 e5m2x2(uint32_t w, uint32_t sel) {
+    const uint32_t h = __byte_perm(w, 0u, sel);
+    return __half22float2(*reinterpret_cast<const __half2*>(&h));
+}
+
+// DPL = head_dim / 32: elements of the output each lane owns
+template <int DPL>
+__global__ void __launch_bounds__(SDP_WARPS * 32)
+sdp_fp8_decode_kernel(const SdpArgs A) {
+    constexpr int D = DPL * 32;
+    __shared__ float q_s[SDP_RT][D];
+    __shared__ float red_m[SDP_WARPS][SDP_RT], red_l[SDP_WARPS][SDP_RT];
+    __shared__ float red_o[SDP_WARPS][SDP_RT][D];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int split = blockIdx.x, hkv = blockIdx.y % A.Hkv, b = blockIdx.y / A.Hkv, tile = blockIdx.z;
+    const int n_rep = A.Hq / A.Hkv, rows_total = n_rep * A.S;
+    const int row0 = tile * SDP_RT;
+    const int n_rows = min(SDP_RT, rows_total - row0);
+    // row r of the tile = (q head hkv * n_rep + rr / S, token rr % S) with rr = row0 + r
+    for (int i = threadIdx.x; i < SDP_RT * D; i += blockDim.x) {
+        const int r = i / D, d = i % D;
+        float v = 0.0f;
+        if (r < n_rows) {
+            const int rr = row0 + r, hq = hkv * n_rep + rr / A.S, st = rr % A.S;
+            v = load_as_float(A.q, A.q_dtype, b * A.q_sb + hq * A.q_sh + st * A.q_ss + d) * A.scale_log2e;
+        }
+        q_s[r][d] = v;
+    }
+    __syncthreads();
+
+    const int key_begin = split * A.keys_per_split;
+    const int key_end = min(A.L, key_begin + A.keys_per_split);
+    const uint8_t* kb = A.k + b * A.k_sb + hkv * A.k_sh;
+    const uint8_t* vb = A.v + b * A.v_sb + hkv * A.v_sh;
+
+    float m[SDP_RT], l[SDP_RT], acc[SDP_RT][DPL];
+#pragma unroll
+    for (int r = 0; r < SDP_RT; r++) {
+        m[r] = -CUDART_INF_F; l[r] = 0.0f;
+#pragma unroll
+        for (int e = 0; e < DPL; e++) acc[r][e] = 0.0f;
+    }
+
+    for (int c0 = key_begin + warp * 32; c0 < key_end; c0 += SDP_WARPS * 32) {
+        const int key = c0 + lane;
+        const bool live = key < key_end;
+        // ---- scores: one lane per key
+        float sc[SDP_RT];
+#pragma unroll
+        for (int r = 0; r < SDP_RT; r++) sc[r] = 0.0f;
+        if (live) {
+            const uint4* kr = reinterpret_cast<const uint4*>(kb + (int64_t)key * A.k_ss);
+#pragma unroll
+            for (int i = 0; i < D / 16; i++) {
+                const uint4 w = kr[i];
+                const uint32_t ws[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    const float2 a = e5m2x2(ws[j], 0x1404u), c = e5m2x2(ws[j], 0x3424u);   // bytes (0,1), (2,3)
+#pragma unroll
+                    for (int r = 0; r < SDP_RT; r++) {
+                        const float4 qv = *reinterpret_cast<const float4*>(&q_s[r][16 * i + 4 * j]);
+                        sc[r] = fmaf(a.x, qv.x, fmaf(a.y, qv.y, fmaf(c.x, qv.z, fmaf(c.y, qv.w, sc[r]))));
+                    }
+                }
+            }
+        }
+#pragma unroll
+        for (int r = 0; r < SDP_RT; r++) {
+            const int rr = row0 + r;
+            bool ok = live && r < n_rows;
+            if (ok && A.causal) ok = key <= A.L - A.S + (rr % A.S);
+            if (ok && A.mask) {
+                const int hq = hkv * n_rep + rr / A.S, st = rr % A.S;
+                sc[r] += load_as_float(A.mask, A.mask_dtype, b * A.m_sb + hq * A.m_sh + st * A.m_ss + key) * 1.4426950408889634f;
+            }
+            if (!ok) sc[r] = -CUDART_INF_F;
+        }
+        // ---- online softmax: new running maximum per row (the only cross-lane step of the chunk)
+        float p[SDP_RT];
+#pragma unroll
+        for (int r = 0; r < SDP_RT; r++) {
+            float mx = sc[r];
+#pragma unroll
+            for (int o = 16; o; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+            const float m_new = fmaxf(m[r], mx);
+            const float corr = (m_new == -CUDART_INF_F) ? 1.0f : exp2f(m[r] - m_new);
+            p[r] = (sc[r] == -CUDART_INF_F) ? 0.0f : exp2f(sc[r] - m_new);
+            l[r] = l[r] * corr + p[r];                   // per-lane partial sum; lanes are added up at the end
+#pragma unroll
+            for (int e = 0; e < DPL; e++) acc[r][e] *= corr;
+            m[r] = m_new;
+        }
+        // ---- p . V: one lane per DPL output elements, keys of the chunk one after the other
+        const int n_here = min(32, key_end - c0);
+        for (int j = 0; j < n_here; j++) {
+            const uint8_t* vr = vb + (int64_t)(c0 + j) * A.v_ss + lane * DPL;
+            float vv[DPL];
+            if (DPL == 4) {
+                const uint32_t w = *reinterpret_cast<const uint32_t*>(vr);
+                const float2 a = e5m2x2(w, 0x1404u), c = e5m2x2(w, 0x3424u);
+                vv[0] = a.x; vv[1] = a.y; vv[2 % DPL] = c.x; vv[3 % DPL] = c.y;
+            } else {
+#pragma unroll
+                for (int e = 0; e < DPL; e++) vv[e] = from_e5m2(vr[e]);
+            }
+#pragma unroll
+            for (int r = 0; r < SDP_RT; r++) {
+                const float pj = __shfl_sync(0xffffffffu, p[r], j);
+#pragma unroll
+                for (int e = 0; e < DPL; e++) acc[r][e] = fmaf(pj, vv[e], acc[r][e]);
+            }
+        }
+    }
+    // ---- combine: lanes (l), then warps (m, l, acc), fixed order
+#pragma unroll
+    for (int r = 0; r < SDP_RT; r++) {
+#pragma unroll
+        for (int o = 16; o; o >>= 1) l[r] += __shfl_xor_sync(0xffffffffu, l[r], o);
+        if (lane == 0) { red_m[warp][r] = m[r]; red_l[warp][r] = l[r]; }
+#pragma unroll
+        for (int e = 0; e < DPL; e++) red_o[warp][r][lane * DPL + e] = acc[r][e];
+    }
+    __syncthreads();
+    float* part = A.part + ((((int64_t)b * A.Hkv + hkv) * gridDim.z + tile) * A.n_split + split) * (SDP_RT * (D + 2));
+    for (int i = threadIdx.x; i < SDP_RT * D; i += blockDim.x) {
+        const int r = i / D, d = i % D;
+        float M = red_m[0][r];
+#pragma unroll
+        for (int w = 1; w < SDP_WARPS; w++) M = fmaxf(M, red_m[w][r]);
+        float o = 0.0f, lsum = 0.0f;
+#pragma unroll
+        for (int w = 0; w < SDP_WARPS; w++) {
+            const float f = (red_m[w][r] == -CUDART_INF_F) ? 0.0f : exp2f(red_m[w][r] - M);
+            o = fmaf(red_o[w][r][d], f, o);
+            lsum = fmaf(red_l[w][r], f, lsum);
+        }
+        part[r * (D + 2) + 2 + d] = o;
+        if (d == 0) { part[r * (D + 2)] = M; part[r * (D + 2) + 1] = lsum; }
+    }
+}
+
+// one thread per output element: merge the splits' (m, l, o) in split order
+__global__ void sdp_fp8_combine_kernel(const SdpArgs A, int n_tiles) {
+    const int D = A.D;
+    const int64_t total = (int64_t)A.B * A.Hq * A.S * D;
+    const int n_rep = A.Hq / A.Hkv;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int d = (int)(i % D), st = (int)((i / D) % A.S), hq = (int)((i / ((int64_t)D * A.S)) % A.Hq);
+        const int b = (int)(i / ((int64_t)D * A.S * A.Hq));
+        const int hkv = hq / n_rep, rr = (hq % n_rep) * A.S + st, tile = rr / SDP_RT, r = rr % SDP_RT;
+        const float* part = A.part + (((int64_t)b * A.Hkv + hkv) * n_tiles + tile) * A.n_split * (SDP_RT * (D + 2)) + r * (D + 2);
+        float M = -CUDART_INF_F;
+        for (int sp = 0; sp < A.n_split; sp++) M = fmaxf(M, part[(int64_t)sp * SDP_RT * (D + 2)]);
+        float o = 0.0f, l = 0.0f;
+        for (int sp = 0; sp < A.n_split; sp++) {
+            const float* ps = part + (int64_t)sp * SDP_RT * (D + 2);
+            const float f = (ps[0] == -CUDART_INF_F) ? 0.0f : exp2f(ps[0] - M);
+            o = fmaf(ps[2 + d], f, o);
+            l = fmaf(ps[1], f, l);
+        }
+        const float y = l > 0.0f ? o / l : 0.0f;           // a row with every key masked gives zeros
+        if (A.out_dtype == DT_F32) ((float*)A.out)[i] = y;
+        else if (A.out_dtype == DT_F16) ((__half*)A.out)[i] = __float2half_rn(y);
+        else ((__nv_bfloat16*)A.out)[i] = __float2bfloat16_rn(y);
+    }
+}
+
+int sdp_tiles(int Hq, int Hkv, int S) { return (Hq / Hkv * S + SDP_RT - 1) / SDP_RT; }
+
+// splits of the key axis: enough CTAs for ~2 per SM, at least 128 keys each
+int sdp_splits(int B, int Hq, int Hkv, int S, int L) {
+    const int base = B * Hkv * sdp_tiles(Hq, Hkv, S);
+    int want = (2 * sm_count() + base - 1) / base;
+    const int max_by_len = (L + 127) / 128;
+    if (want > max_by_len) want = max_by_len;
+    if (want > 64) want = 64;
+    return want < 1 ? 1 : want;
+}
+}  // namespace
+}  // namespace lowbit
+
+// ------------------------------------------------------------------ C ABI (declared in include/b200_lowbit.h)
+using namespace lowbit;
+
+static View4 view_of(const int64_t* st) { View4 v; v.sb = st[0]; v.sh = st[1]; v.ss = st[2]; return v; }
+
+extern "C" int lowbit_kv_quantize_cuda(const void* d_src, int src_dtype, const int64_t* src_strides, void* d_dst,
+                                       const int64_t* dst_strides, int64_t B, int64_t H, int64_t S, int64_t D, void* stream) {
+    reset_launch_count();
+    if (!d_src || !d_dst || !src_strides || !dst_strides || B < 0 || H < 0 || S < 0 || D <= 0 || src_dtype < 0 || src_dtype > 2) {
+        set_error(LB_ERR_ARG, "lowbit_kv_quantize_cuda: bad argument");
+        return LB_ERR_ARG;
+    }
+    const int64_t total = B * H * S * D;
+    if (total == 0) return LB_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    const View4 vs = view_of(src_strides), vd = view_of(dst_strides);
+    const int grid = grid_for(total);
+    if (src_dtype == DT_F32) kv_quantize_kernel<float><<<grid, 256, 0, st>>>((const float*)d_src, vs, (uint8_t*)d_dst, vd, B, H, S, D);
+    else if (src_dtype == DT_F16) kv_quantize_kernel<__half><<<grid, 256, 0, st>>>((const __half*)d_src, vs, (uint8_t*)d_dst, vd, B, H, S, D);
+    else kv_quantize_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>((const __nv_bfloat16*)d_src, vs, (uint8_t*)d_dst, vd, B, H, S, D);
+    note_launch();
+    return check_launch();
+}
+
+extern "C" int lowbit_kv_dequantize_cuda(const void* d_src, const int64_t* src_strides, void* d_dst, int dst_dtype,
+                                         const int64_t* dst_strides, int64_t B, int64_t H, int64_t S, int64_t D, void* stream) {
+    reset_launch_count();
+    if (!d_src || !d_dst || !src_strides || !dst_strides || B < 0 || H < 0 || S < 0 || D <= 0 || dst_dtype < 0 || dst_dtype > 2) {
+        set_error(LB_ERR_ARG, "lowbit_kv_dequantize_cuda: bad argument");
+        return LB_ERR_ARG;
+    }
+    const int64_t total = B * H * S * D;
+    if (total == 0) return LB_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    const View4 vs = view_of(src_strides), vd = view_of(dst_strides);
+    const int grid = grid_for(total);
+    if (dst_dtype == DT_F32) kv_dequantize_kernel<float><<<grid, 256, 0, st>>>((const uint8_t*)d_src, vs, (float*)d_dst, vd, B, H, S, D);
+    else if (dst_dtype == DT_F16) kv_dequantize_kernel<__half><<<grid, 256, 0, st>>>((const uint8_t*)d_src, vs, (__half*)d_dst, vd, B, H, S, D);
+    else kv_dequantize_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>((const uint8_t*)d_src, vs, (__nv_bfloat16*)d_dst, vd, B, H, S, D);
+    note_launch();
+    return check_launch();
+}
+
+extern "C" int lowbit_sdp_fp8_supported(int Hq, int Hkv, int S, int D) {
+    return Hq > 0 && Hkv > 0 && Hq % Hkv == 0 && S >= 1 && S <= 32 && (D == 64 || D == 96 || D == 128 || D == 192 || D == 256);
+}
+
+extern "C" size_t lowbit_sdp_fp8_workspace_size(int B, int Hq, int Hkv, int S, int L, int D) {
+    if (!lowbit_sdp_fp8_supported(Hq, Hkv, S, D) || B <= 0 || L <= 0) return 0;
+    return (size_t)B * Hkv * sdp_tiles(Hq, Hkv, S) * sdp_splits(B, Hq, Hkv, S, L) * SDP_RT * (D + 2) * sizeof(float);
+}
+
+extern "C" int lowbit_sdp_fp8_cuda(const void* d_q, int q_dtype, const int64_t* q_strides, const void* d_k,
+                                   const int64_t* k_strides, const void* d_v, const int64_t* v_strides, const void* d_mask,
+                                   int mask_dtype, const int64_t* mask_strides, int causal, float scale, int B, int Hq,
+                                   int Hkv, int S, int L, int D, void* d_out, int out_dtype, void* workspace,
+                                   size_t workspace_bytes, void* stream) {
+    reset_launch_count();
+    if (!d_q || !d_k || !d_v || !d_out || !q_strides || !k_strides || !v_strides || (d_mask && !mask_strides) ||
+        q_dtype < 0 || q_dtype > 2 || out_dtype < 0 || out_dtype > 2 || (d_mask && (mask_dtype < 0 || mask_dtype > 2)) ||
+        B <= 0 || L <= 0 || !lowbit_sdp_fp8_supported(Hq, Hkv, S, D)) {
+        set_error(LB_ERR_ARG, "lowbit_sdp_fp8_cuda: bad argument (B %d, Hq %d, Hkv %d, S %d, L %d, D %d)", B, Hq, Hkv, S, L, D);
+        return LB_ERR_ARG;
+    }
+    if (((uintptr_t)d_k & 15) || ((uintptr_t)d_v & 3) || (k_strides[0] & 15) || (k_strides[1] & 15) || (k_strides[2] & 15) ||
+        (v_strides[0] & 3) || (v_strides[1] & 3) || (v_strides[2] & 3)) {
+        set_error(LB_ERR_ARG, "lowbit_sdp_fp8_cuda: the key cache must be 16-byte aligned (pointer and strides), the value cache 4-byte");
+        return LB_ERR_ARG;
+    }
+    const size_t need = lowbit_sdp_fp8_workspace_size(B, Hq, Hkv, S, L, D);
+    if (!workspace || workspace_bytes < need) {
+        set_error(LB_ERR_WORKSPACE, "lowbit_sdp_fp8_cuda: workspace too small (%zu < %zu bytes)", workspace_bytes, need);
+        return LB_ERR_WORKSPACE;
+    }
+    SdpArgs A;
+    A.q = d_q; A.q_dtype = q_dtype; A.q_sb = q_strides[0]; A.q_sh = q_strides[1]; A.q_ss = q_strides[2];
+    A.k = (const uint8_t*)d_k; A.k_sb = k_strides[0]; A.k_sh = k_strides[1]; A.k_ss = k_strides[2];
+    A.v = (const uint8_t*)d_v; A.v_sb = v_strides[0]; A.v_sh = v_strides[1]; A.v_ss = v_strides[2];
+    A.mask = d_mask; A.mask_dtype = mask_dtype;
+    A.m_sb = d_mask ? mask_strides[0] : 0; A.m_sh = d_mask ? mask_strides[1] : 0; A.m_ss = d_mask ? mask_strides[2] : 0;
+    A.causal = causal; A.scale_log2e = scale * 1.4426950408889634f;
+    A.B = B; A.Hq = Hq; A.Hkv = Hkv; A.S = S; A.L = L; A.D = D;
+    A.n_split = sdp_splits(B, Hq, Hkv, S, L);
+    A.keys_per_split = ((L + A.n_split - 1) / A.n_split + 31) / 32 * 32;
+    A.part = (float*)workspace; A.out = d_out; A.out_dtype = out_dtype;
+    const int tiles = sdp_tiles(Hq, Hkv, S);
+    const dim3 grid((unsigned)A.n_split, (unsigned)(B * Hkv), (unsigned)tiles);
+    cudaStream_t st = (cudaStream_t)stream;
+    switch (D / 32) {
+        case 2: sdp_fp8_decode_kernel<2><<<grid, SDP_WARPS * 32, 0, st>>>(A); break;
+        case 3: sdp_fp8_decode_kernel<3><<<grid, SDP_WARPS * 32, 0, st>>>(A); break;
+        case 4: sdp_fp8_decode_kernel<4><<<grid, SDP_WARPS * 32, 0, st>>>(A); break;
+        case 6: sdp_fp8_decode_kernel<6><<<grid, SDP_WARPS * 32, 0, st>>>(A); break;
+        default: sdp_fp8_decode_kernel<8><<<grid, SDP_WARPS * 32, 0, st>>>(A); break;
+    }
+    note_launch();
+    const int64_t total = (int64_t)B * Hq * S * D;
+    sdp_fp8_combine_kernel<<<grid_for(total), 256, 0, st>>>(A, tiles);
+    note_launch();
+    return check_launch();
+}

@@ -18,6 +18,7 @@ enum {
 // per-thread error / launch bookkeeping (capi.cu)
 void set_error(int code, const char* fmt, ...);
 void note_launch();
+void reset_launch_count();
 int check_launch();   // cudaGetLastError() -> LB_OK / LB_ERR_CUDA (records the message)
 int sm_count();       // SMs of the current device (cached per device)
 

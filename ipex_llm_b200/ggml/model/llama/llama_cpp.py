@@ -207,6 +207,61 @@ def lowbit_dequantize_rows_cuda(d_w, qtype, rows, k, d_ids, ids_dtype, n_ids, d_
            "lowbit_dequantize_rows_cuda")
 
 
+_I64P = ctypes.POINTER(ctypes.c_int64)
+_lib.lowbit_kv_quantize_cuda.argtypes = [ctypes.c_void_p, ctypes.c_int, _I64P, ctypes.c_void_p, _I64P, ctypes.c_int64,
+                                         ctypes.c_int64, ctypes.c_int64, ctypes.c_int64, ctypes.c_void_p]
+_lib.lowbit_kv_quantize_cuda.restype = ctypes.c_int
+_lib.lowbit_kv_dequantize_cuda.argtypes = [ctypes.c_void_p, _I64P, ctypes.c_void_p, ctypes.c_int, _I64P, ctypes.c_int64,
+                                           ctypes.c_int64, ctypes.c_int64, ctypes.c_int64, ctypes.c_void_p]
+_lib.lowbit_kv_dequantize_cuda.restype = ctypes.c_int
+_lib.lowbit_sdp_fp8_supported.argtypes = [ctypes.c_int] * 4
+_lib.lowbit_sdp_fp8_supported.restype = ctypes.c_int
+_lib.lowbit_sdp_fp8_workspace_size.argtypes = [ctypes.c_int] * 6
+_lib.lowbit_sdp_fp8_workspace_size.restype = ctypes.c_size_t
+_lib.lowbit_sdp_fp8_cuda.argtypes = [ctypes.c_void_p, ctypes.c_int, _I64P, ctypes.c_void_p, _I64P, ctypes.c_void_p, _I64P,
+                                     ctypes.c_void_p, ctypes.c_int, _I64P, ctypes.c_int, ctypes.c_float] + [ctypes.c_int] * 6 + \
+                                    [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p]
+_lib.lowbit_sdp_fp8_cuda.restype = ctypes.c_int
+
+
+def _strides3(t):
+    return (ctypes.c_int64 * 3)(*t.stride()[:3])
+
+
+def lowbit_kv_quantize(src, dst, stream):
+    """src float [B,H,S,D] -> dst uint8 view of the same shape (both with D contiguous)"""
+    B, H, S, D = src.shape
+    _check(_lib.lowbit_kv_quantize_cuda(src.data_ptr(), _DT_OF[str(src.dtype)], _strides3(src), dst.data_ptr(), _strides3(dst),
+                                        B, H, S, D, stream), "lowbit_kv_quantize_cuda")
+
+
+def lowbit_kv_dequantize(src, dst, stream):
+    B, H, S, D = src.shape
+    _check(_lib.lowbit_kv_dequantize_cuda(src.data_ptr(), _strides3(src), dst.data_ptr(), _DT_OF[str(dst.dtype)], _strides3(dst),
+                                          B, H, S, D, stream), "lowbit_kv_dequantize_cuda")
+
+
+def lowbit_sdp_fp8_supported(hq, hkv, s, d):
+    return bool(_lib.lowbit_sdp_fp8_supported(hq, hkv, s, d))
+
+
+def lowbit_sdp_fp8_workspace_size(b, hq, hkv, s, l, d):
+    return _lib.lowbit_sdp_fp8_workspace_size(b, hq, hkv, s, l, d)
+
+
+def lowbit_sdp_fp8(q, k, v, mask, causal, scale, out, workspace, stream):
+    B, Hq, S, D = q.shape
+    Hkv, L = k.shape[1], k.shape[2]
+    _check(_lib.lowbit_sdp_fp8_cuda(q.data_ptr(), _DT_OF[str(q.dtype)], _strides3(q), k.data_ptr(), _strides3(k), v.data_ptr(),
+                                    _strides3(v), mask.data_ptr() if mask is not None else None,
+                                    _DT_OF[str(mask.dtype)] if mask is not None else 0,
+                                    _strides3(mask) if mask is not None else None, int(bool(causal)), float(scale),
+                                    B, Hq, Hkv, S, L, D, out.data_ptr(), _DT_OF[str(out.dtype)], workspace.data_ptr(),
+                                    workspace.numel() * workspace.element_size(), stream), "lowbit_sdp_fp8_cuda")
+
+
+_DT_OF = {"torch.float32": 0, "torch.float16": 1, "torch.bfloat16": 2}
+
 _lib.lowbit_mlp_workspace_size.argtypes = [ctypes.c_int64, ctypes.c_int64, ctypes.c_int64, ctypes.c_int]
 _lib.lowbit_mlp_workspace_size.restype = ctypes.c_size_t
 _lib.lowbit_mlp_cuda.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_int64,
