@@ -64,7 +64,7 @@ int grid_for(int64_t total) {
 
 // ------------------------------------------------------------------ decode attention over the FP8 cache
 constexpr int SDP_WARPS = 4;
-constexpr int SDP_RT = 4;                  // query rows per CTA (GQA group x new tokens, tiled by blockIdx.z)
+constexpr int SDP_RT = 4;                  // most query rows per CTA
 
 struct SdpArgs {
     const void* q; int q_dtype; int64_t q_sb, q_sh, q_ss;        // [B][Hq][S][D]
@@ -75,6 +75,7 @@ struct SdpArgs {
     float scale_log2e;                                             // scale * log2(e)
     int B, Hq, Hkv, S, L, D;
     int n_split, keys_per_split;
+    int rt;                                                        // query rows per CTA (1, 2 or 4)
     float* part;                                                   // [B][Hkv][row tiles][n_split][RT * (D + 2)]
     void* out; int out_dtype;                                      // [B][Hq][S][D] contiguous
 };
@@ -91,21 +92,45 @@ __device__ __forceinline__ float2 e5m2x2(uint32_t w, uint32_t sel) {
     return __half22float2(*reinterpret_cast<const __half2*>(&h));
 }
 
+// DPL consecutive e5m2 bytes of a value row -> up to two words, and back to floats
+template <int DPL> __device__ __forceinline__ void load_v(const uint8_t* p, uint32_t (&w)[2]) {
+    w[0] = 0; w[1] = 0;
+    if (DPL == 4) w[0] = *reinterpret_cast<const uint32_t*>(p);
+    else if (DPL == 8) { const uint2 t = *reinterpret_cast<const uint2*>(p); w[0] = t.x; w[1] = t.y; }
+    else if (DPL == 2) w[0] = *reinterpret_cast<const uint16_t*>(p);
+    else if (DPL == 6) {
+        const uint16_t* q = reinterpret_cast<const uint16_t*>(p);
+        w[0] = (uint32_t)q[0] | ((uint32_t)q[1] << 16); w[1] = q[2];
+    } else {
+#pragma unroll
+        for (int e = 0; e < DPL; e++) w[e >> 2] |= (uint32_t)p[e] << (8 * (e & 3));
+    }
+}
+template <int DPL> __device__ __forceinline__ void unpack_v(const uint32_t (&w)[2], float (&vv)[DPL]) {
+#pragma unroll
+    for (int e = 0; e < DPL; e += 2) {
+        const float2 f = e5m2x2(w[e >> 2], (e & 2) ? 0x3424u : 0x1404u);
+        vv[e] = f.x;
+        if (e + 1 < DPL) vv[e + 1] = f.y;
+    }
+}
+
 // DPL = head_dim / 32: elements of the output each lane owns
-template <int DPL>
+// RT = query rows per CTA (1, 2 or 4): the GQA group x new tokens, tiled by blockIdx.z
+template <int DPL, int RT>
 __global__ void __launch_bounds__(SDP_WARPS * 32)
 sdp_fp8_decode_kernel(const SdpArgs A) {
     constexpr int D = DPL * 32;
-    __shared__ float q_s[SDP_RT][D];
-    __shared__ float red_m[SDP_WARPS][SDP_RT], red_l[SDP_WARPS][SDP_RT];
-    __shared__ float red_o[SDP_WARPS][SDP_RT][D];
+    __shared__ float q_s[RT][D];
+    __shared__ float red_m[SDP_WARPS][RT], red_l[SDP_WARPS][RT];
+    __shared__ float red_o[SDP_WARPS][RT][D];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int split = blockIdx.x, hkv = blockIdx.y % A.Hkv, b = blockIdx.y / A.Hkv, tile = blockIdx.z;
     const int n_rep = A.Hq / A.Hkv, rows_total = n_rep * A.S;
-    const int row0 = tile * SDP_RT;
-    const int n_rows = min(SDP_RT, rows_total - row0);
+    const int row0 = tile * RT;
+    const int n_rows = min(RT, rows_total - row0);
     // row r of the tile = (q head hkv * n_rep + rr / S, token rr % S) with rr = row0 + r
-    for (int i = threadIdx.x; i < SDP_RT * D; i += blockDim.x) {
+    for (int i = threadIdx.x; i < RT * D; i += blockDim.x) {
         const int r = i / D, d = i % D;
         float v = 0.0f;
         if (r < n_rows) {
@@ -121,9 +146,9 @@ sdp_fp8_decode_kernel(const SdpArgs A) {
     const uint8_t* kb = A.k + b * A.k_sb + hkv * A.k_sh;
     const uint8_t* vb = A.v + b * A.v_sb + hkv * A.v_sh;
 
-    float m[SDP_RT], l[SDP_RT], acc[SDP_RT][DPL];
+    float m[RT], l[RT], acc[RT][DPL];
 #pragma unroll
-    for (int r = 0; r < SDP_RT; r++) {
+    for (int r = 0; r < RT; r++) {
         m[r] = -CUDART_INF_F; l[r] = 0.0f;
 #pragma unroll
         for (int e = 0; e < DPL; e++) acc[r][e] = 0.0f;
@@ -133,9 +158,9 @@ sdp_fp8_decode_kernel(const SdpArgs A) {
         const int key = c0 + lane;
         const bool live = key < key_end;
         // ---- scores: one lane per key
-        float sc[SDP_RT];
+        float sc[RT];
 #pragma unroll
-        for (int r = 0; r < SDP_RT; r++) sc[r] = 0.0f;
+        for (int r = 0; r < RT; r++) sc[r] = 0.0f;
         if (live) {
             const uint4* kr = reinterpret_cast<const uint4*>(kb + (int64_t)key * A.k_ss);
 #pragma unroll
@@ -146,7 +171,7 @@ sdp_fp8_decode_kernel(const SdpArgs A) {
                 for (int j = 0; j < 4; j++) {
                     const float2 a = e5m2x2(ws[j], 0x1404u), c = e5m2x2(ws[j], 0x3424u);   // bytes (0,1), (2,3)
 #pragma unroll
-                    for (int r = 0; r < SDP_RT; r++) {
+                    for (int r = 0; r < RT; r++) {
                         const float4 qv = *reinterpret_cast<const float4*>(&q_s[r][16 * i + 4 * j]);
                         sc[r] = fmaf(a.x, qv.x, fmaf(a.y, qv.y, fmaf(c.x, qv.z, fmaf(c.y, qv.w, sc[r]))));
                     }
@@ -154,7 +179,7 @@ sdp_fp8_decode_kernel(const SdpArgs A) {
             }
         }
 #pragma unroll
-        for (int r = 0; r < SDP_RT; r++) {
+        for (int r = 0; r < RT; r++) {
             const int rr = row0 + r;
             bool ok = live && r < n_rows;
             if (ok && A.causal) ok = key <= A.L - A.S + (rr % A.S);
@@ -165,9 +190,9 @@ sdp_fp8_decode_kernel(const SdpArgs A) {
             if (!ok) sc[r] = -CUDART_INF_F;
         }
         // ---- online softmax: new running maximum per row (the only cross-lane step of the chunk)
-        float p[SDP_RT];
+        float p[RT];
 #pragma unroll
-        for (int r = 0; r < SDP_RT; r++) {
+        for (int r = 0; r < RT; r++) {
             float mx = sc[r];
 #pragma unroll
             for (int o = 16; o; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
@@ -179,30 +204,33 @@ sdp_fp8_decode_kernel(const SdpArgs A) {
             for (int e = 0; e < DPL; e++) acc[r][e] *= corr;
             m[r] = m_new;
         }
-        // ---- p . V: one lane per DPL output elements, keys of the chunk one after the other
-        const int n_here = min(32, key_end - c0);
-        for (int j = 0; j < n_here; j++) {
-            const uint8_t* vr = vb + (int64_t)(c0 + j) * A.v_ss + lane * DPL;
-            float vv[DPL];
-            if (DPL == 4) {
-                const uint32_t w = *reinterpret_cast<const uint32_t*>(vr);
-                const float2 a = e5m2x2(w, 0x1404u), c = e5m2x2(w, 0x3424u);
-                vv[0] = a.x; vv[1] = a.y; vv[2 % DPL] = c.x; vv[3 % DPL] = c.y;
-            } else {
+        // ---- p . V: one lane per DPL output elements.  The value rows of 8 keys are requested together (a row
+        // is one coalesced DPL*32-byte read of the warp) before they are used: a key-by-key loop exposed one
+        // memory round trip per key.  Keys beyond the range are clamped to the last one; their p is 0.
 #pragma unroll
-                for (int e = 0; e < DPL; e++) vv[e] = from_e5m2(vr[e]);
+        for (int j0 = 0; j0 < 32; j0 += 8) {
+            uint32_t vw[8][2];
+#pragma unroll
+            for (int jj = 0; jj < 8; jj++) {
+                const int kj = min(c0 + j0 + jj, key_end - 1);
+                load_v<DPL>(vb + (int64_t)kj * A.v_ss + lane * DPL, vw[jj]);
             }
 #pragma unroll
-            for (int r = 0; r < SDP_RT; r++) {
-                const float pj = __shfl_sync(0xffffffffu, p[r], j);
+            for (int jj = 0; jj < 8; jj++) {
+                float vv[DPL];
+                unpack_v<DPL>(vw[jj], vv);
 #pragma unroll
-                for (int e = 0; e < DPL; e++) acc[r][e] = fmaf(pj, vv[e], acc[r][e]);
+                for (int r = 0; r < RT; r++) {
+                    const float pj = __shfl_sync(0xffffffffu, p[r], j0 + jj);
+#pragma unroll
+                    for (int e = 0; e < DPL; e++) acc[r][e] = fmaf(pj, vv[e], acc[r][e]);
+                }
             }
         }
     }
     // ---- combine: lanes (l), then warps (m, l, acc), fixed order
 #pragma unroll
-    for (int r = 0; r < SDP_RT; r++) {
+    for (int r = 0; r < RT; r++) {
 #pragma unroll
         for (int o = 16; o; o >>= 1) l[r] += __shfl_xor_sync(0xffffffffu, l[r], o);
         if (lane == 0) { red_m[warp][r] = m[r]; red_l[warp][r] = l[r]; }
@@ -210,8 +238,8 @@ sdp_fp8_decode_kernel(const SdpArgs A) {
         for (int e = 0; e < DPL; e++) red_o[warp][r][lane * DPL + e] = acc[r][e];
     }
     __syncthreads();
-    float* part = A.part + ((((int64_t)b * A.Hkv + hkv) * gridDim.z + tile) * A.n_split + split) * (SDP_RT * (D + 2));
-    for (int i = threadIdx.x; i < SDP_RT * D; i += blockDim.x) {
+    float* part = A.part + ((((int64_t)b * A.Hkv + hkv) * gridDim.z + tile) * A.n_split + split) * (RT * (D + 2));
+    for (int i = threadIdx.x; i < RT * D; i += blockDim.x) {
         const int r = i / D, d = i % D;
         float M = red_m[0][r];
 #pragma unroll
@@ -236,13 +264,13 @@ __global__ void sdp_fp8_combine_kernel(const SdpArgs A, int n_tiles) {
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
         const int d = (int)(i % D), st = (int)((i / D) % A.S), hq = (int)((i / ((int64_t)D * A.S)) % A.Hq);
         const int b = (int)(i / ((int64_t)D * A.S * A.Hq));
-        const int hkv = hq / n_rep, rr = (hq % n_rep) * A.S + st, tile = rr / SDP_RT, r = rr % SDP_RT;
-        const float* part = A.part + (((int64_t)b * A.Hkv + hkv) * n_tiles + tile) * A.n_split * (SDP_RT * (D + 2)) + r * (D + 2);
+        const int hkv = hq / n_rep, rr = (hq % n_rep) * A.S + st, tile = rr / A.rt, r = rr % A.rt;
+        const float* part = A.part + (((int64_t)b * A.Hkv + hkv) * n_tiles + tile) * A.n_split * (A.rt * (D + 2)) + r * (D + 2);
         float M = -CUDART_INF_F;
-        for (int sp = 0; sp < A.n_split; sp++) M = fmaxf(M, part[(int64_t)sp * SDP_RT * (D + 2)]);
+        for (int sp = 0; sp < A.n_split; sp++) M = fmaxf(M, part[(int64_t)sp * A.rt * (D + 2)]);
         float o = 0.0f, l = 0.0f;
         for (int sp = 0; sp < A.n_split; sp++) {
-            const float* ps = part + (int64_t)sp * SDP_RT * (D + 2);
+            const float* ps = part + (int64_t)sp * A.rt * (D + 2);
             const float f = (ps[0] == -CUDART_INF_F) ? 0.0f : exp2f(ps[0] - M);
             o = fmaf(ps[2 + d], f, o);
             l = fmaf(ps[1], f, l);
@@ -254,12 +282,14 @@ __global__ void sdp_fp8_combine_kernel(const SdpArgs A, int n_tiles) {
     }
 }
 
-int sdp_tiles(int Hq, int Hkv, int S) { return (Hq / Hkv * S + SDP_RT - 1) / SDP_RT; }
+// rows per CTA: the whole GQA group x new tokens if it is 1, 2 or <= 4 rows, else tiles of 4
+int sdp_rt(int Hq, int Hkv, int S) { const int rows = Hq / Hkv * S; return rows <= 1 ? 1 : (rows <= 2 ? 2 : SDP_RT); }
+int sdp_tiles(int Hq, int Hkv, int S) { const int rt = sdp_rt(Hq, Hkv, S); return (Hq / Hkv * S + rt - 1) / rt; }
 
-// splits of the key axis: enough CTAs for ~2 per SM, at least 128 keys each
+// splits of the key axis: enough CTAs for ~8 per SM (the loads are latency bound), at least 128 keys each
 int sdp_splits(int B, int Hq, int Hkv, int S, int L) {
     const int base = B * Hkv * sdp_tiles(Hq, Hkv, S);
-    int want = (2 * sm_count() + base - 1) / base;
+    int want = (8 * sm_count() + base - 1) / base;
     const int max_by_len = (L + 127) / 128;
     if (want > max_by_len) want = max_by_len;
     if (want > 64) want = 64;
@@ -317,7 +347,7 @@ extern "C" int lowbit_sdp_fp8_supported(int Hq, int Hkv, int S, int D) {
 
 extern "C" size_t lowbit_sdp_fp8_workspace_size(int B, int Hq, int Hkv, int S, int L, int D) {
     if (!lowbit_sdp_fp8_supported(Hq, Hkv, S, D) || B <= 0 || L <= 0) return 0;
-    return (size_t)B * Hkv * sdp_tiles(Hq, Hkv, S) * sdp_splits(B, Hq, Hkv, S, L) * SDP_RT * (D + 2) * sizeof(float);
+    return (size_t)B * Hkv * sdp_tiles(Hq, Hkv, S) * sdp_splits(B, Hq, Hkv, S, L) * sdp_rt(Hq, Hkv, S) * (D + 2) * sizeof(float);
 }
 
 extern "C" int lowbit_sdp_fp8_cuda(const void* d_q, int q_dtype, const int64_t* q_strides, const void* d_k,
@@ -356,13 +386,21 @@ extern "C" int lowbit_sdp_fp8_cuda(const void* d_q, int q_dtype, const int64_t* 
     const int tiles = sdp_tiles(Hq, Hkv, S);
     const dim3 grid((unsigned)A.n_split, (unsigned)(B * Hkv), (unsigned)tiles);
     cudaStream_t st = (cudaStream_t)stream;
+    A.rt = sdp_rt(Hq, Hkv, S);
+#define SDP_LAUNCH(DPL) \
+    do { \
+        if (A.rt == 1) sdp_fp8_decode_kernel<DPL, 1><<<grid, SDP_WARPS * 32, 0, st>>>(A); \
+        else if (A.rt == 2) sdp_fp8_decode_kernel<DPL, 2><<<grid, SDP_WARPS * 32, 0, st>>>(A); \
+        else sdp_fp8_decode_kernel<DPL, 4><<<grid, SDP_WARPS * 32, 0, st>>>(A); \
+    } while (0)
     switch (D / 32) {
-        case 2: sdp_fp8_decode_kernel<2><<<grid, SDP_WARPS * 32, 0, st>>>(A); break;
-        case 3: sdp_fp8_decode_kernel<3><<<grid, SDP_WARPS * 32, 0, st>>>(A); break;
-        case 4: sdp_fp8_decode_kernel<4><<<grid, SDP_WARPS * 32, 0, st>>>(A); break;
-        case 6: sdp_fp8_decode_kernel<6><<<grid, SDP_WARPS * 32, 0, st>>>(A); break;
-        default: sdp_fp8_decode_kernel<8><<<grid, SDP_WARPS * 32, 0, st>>>(A); break;
+        case 2: SDP_LAUNCH(2); break;
+        case 3: SDP_LAUNCH(3); break;
+        case 4: SDP_LAUNCH(4); break;
+        case 6: SDP_LAUNCH(6); break;
+        default: SDP_LAUNCH(8); break;
     }
+#undef SDP_LAUNCH
     note_launch();
     const int64_t total = (int64_t)B * Hq * S * D;
     sdp_fp8_combine_kernel<<<grid_for(total), 256, 0, st>>>(A, tiles);
