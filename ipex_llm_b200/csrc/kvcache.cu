@@ -256,44 +256,85 @@ sdp_fp8_decode_kernel(const SdpArgs A) {
     }
 }
 
-// one thread per output element: merge the splits' (m, l, o) in split order
-__global__ void sdp_fp8_combine_kernel(const SdpArgs A, int n_tiles) {
-    const int D = A.D;
-    const int64_t total = (int64_t)A.B * A.Hq * A.S * D;
+// one warp per output row: merge the splits' (m, l, o).  The (m, l) of the splits sit one per lane (two for more than
+// 32 splits) and are reduced with shuffles; every lane then owns columns lane, lane + 32, ... and walks the splits with
+// independent, coalesced loads.  Fixed order: the result does not depend on scheduling.
+constexpr int SDP_COMBINE_WARPS = 4;
+__global__ void __launch_bounds__(SDP_COMBINE_WARPS * 32) sdp_fp8_combine_kernel(const SdpArgs A, int n_tiles) {
+    const int D = A.D, lane = threadIdx.x & 31;
+    const int64_t row = (int64_t)blockIdx.x * SDP_COMBINE_WARPS + (threadIdx.x >> 5);
+    if (row >= (int64_t)A.B * A.Hq * A.S) return;
     const int n_rep = A.Hq / A.Hkv;
-    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-        const int d = (int)(i % D), st = (int)((i / D) % A.S), hq = (int)((i / ((int64_t)D * A.S)) % A.Hq);
-        const int b = (int)(i / ((int64_t)D * A.S * A.Hq));
-        const int hkv = hq / n_rep, rr = (hq % n_rep) * A.S + st, tile = rr / A.rt, r = rr % A.rt;
-        const float* part = A.part + (((int64_t)b * A.Hkv + hkv) * n_tiles + tile) * A.n_split * (A.rt * (D + 2)) + r * (D + 2);
-        float M = -CUDART_INF_F;
-        for (int sp = 0; sp < A.n_split; sp++) M = fmaxf(M, part[(int64_t)sp * A.rt * (D + 2)]);
-        float o = 0.0f, l = 0.0f;
-        for (int sp = 0; sp < A.n_split; sp++) {
-            const float* ps = part + (int64_t)sp * A.rt * (D + 2);
-            const float f = (ps[0] == -CUDART_INF_F) ? 0.0f : exp2f(ps[0] - M);
-            o = fmaf(ps[2 + d], f, o);
-            l = fmaf(ps[1], f, l);
-        }
-        const float y = l > 0.0f ? o / l : 0.0f;           // a row with every key masked gives zeros
-        if (A.out_dtype == DT_F32) ((float*)A.out)[i] = y;
-        else if (A.out_dtype == DT_F16) ((__half*)A.out)[i] = __float2half_rn(y);
-        else ((__nv_bfloat16*)A.out)[i] = __float2bfloat16_rn(y);
+    const int st = (int)(row % A.S), hq = (int)((row / A.S) % A.Hq), b = (int)(row / ((int64_t)A.S * A.Hq));
+    const int hkv = hq / n_rep, rr = (hq % n_rep) * A.S + st, tile = rr / A.rt, r = rr % A.rt;
+    const int64_t ps = (int64_t)A.rt * (D + 2);                                   // floats between two splits
+    const float* part = A.part + (((int64_t)b * A.Hkv + hkv) * n_tiles + tile) * A.n_split * ps + r * (D + 2);
+    float m2[2], l2[2];
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+        const int sp = lane + 32 * h;
+        m2[h] = sp < A.n_split ? part[sp * ps] : -CUDART_INF_F;
+        l2[h] = sp < A.n_split ? part[sp * ps + 1] : 0.0f;
     }
+    float M = fmaxf(m2[0], m2[1]);
+#pragma unroll
+    for (int o = 16; o; o >>= 1) M = fmaxf(M, __shfl_xor_sync(0xffffffffu, M, o));
+    float f2[2];
+#pragma unroll
+    for (int h = 0; h < 2; h++) f2[h] = (m2[h] == -CUDART_INF_F) ? 0.0f : exp2f(m2[h] - M);
+    float l = fmaf(l2[0], f2[0], l2[1] * f2[1]);
+#pragma unroll
+    for (int o = 16; o; o >>= 1) l += __shfl_xor_sync(0xffffffffu, l, o);
+    float acc[8];                                                                 // D <= 256
+#pragma unroll
+    for (int e = 0; e < 8; e++) acc[e] = 0.0f;
+#pragma unroll 4
+    for (int sp = 0; sp < A.n_split; sp++) {
+        const float f = __shfl_sync(0xffffffffu, sp < 32 ? f2[0] : f2[1], sp & 31);
+        const float* po = part + sp * ps + 2 + lane;
+#pragma unroll
+        for (int e = 0; e < 8; e++)
+            if (32 * e < D) acc[e] = fmaf(po[32 * e], f, acc[e]);
+    }
+    const float inv = l > 0.0f ? 1.0f / l : 0.0f;                                 // a row with every key masked gives zeros
+#pragma unroll
+    for (int e = 0; e < 8; e++)
+        if (32 * e < D) {
+            const int64_t i = row * D + 32 * e + lane;
+            const float y = acc[e] * inv;
+            if (A.out_dtype == DT_F32) ((float*)A.out)[i] = y;
+            else if (A.out_dtype == DT_F16) ((__half*)A.out)[i] = __float2half_rn(y);
+            else ((__nv_bfloat16*)A.out)[i] = __float2bfloat16_rn(y);
+        }
 }
 
-// rows per CTA: the whole GQA group x new tokens if it is 1, 2 or <= 4 rows, else tiles of 4
-int sdp_rt(int Hq, int Hkv, int S) { const int rows = Hq / Hkv * S; return rows <= 1 ? 1 : (rows <= 2 ? 2 : SDP_RT); }
-int sdp_tiles(int Hq, int Hkv, int S) { const int rt = sdp_rt(Hq, Hkv, S); return (Hq / Hkv * S + rt - 1) / rt; }
+#include "sdp_mma.cuh"
+
+// rows per CTA: the whole GQA group x new tokens if it is 1, 2 or 4 rows (8 on the tensor-core path), else tiles
+int sdp_rt(int Hq, int Hkv, int S, bool mma) {
+    const int rows = Hq / Hkv * S;
+    return rows <= 1 ? 1 : (rows <= 2 ? 2 : (rows <= 4 || !mma ? SDP_RT : SDP_MMA_ROWS));
+}
+int sdp_tiles(int Hq, int Hkv, int S, bool mma) { const int rt = sdp_rt(Hq, Hkv, S, mma); return (Hq / Hkv * S + rt - 1) / rt; }
+
+// the tensor-core kernel: fp16 / bf16 queries, head_dim 64 or 128 (LOWBIT_SDP_MMA=0 switches it off: development)
+bool sdp_use_mma(int q_dtype, int D) {
+    static const bool off = [] { const char* e = getenv("LOWBIT_SDP_MMA"); return e && e[0] == '0'; }();
+    return !off && q_dtype != DT_F32 && (D == 64 || D == 128);
+}
 
 // splits of the key axis: enough CTAs for ~8 per SM (the loads are latency bound), at least 128 keys each
-int sdp_splits(int B, int Hq, int Hkv, int S, int L) {
-    const int base = B * Hkv * sdp_tiles(Hq, Hkv, S);
-    int want = (8 * sm_count() + base - 1) / base;
+int sdp_splits(int B, int Hq, int Hkv, int S, int L, bool mma) {
+    static const int per_sm = [] { const char* e = getenv("LOWBIT_SDP_CTAS_PER_SM"); const int v = e ? atoi(e) : 0; return v > 0 ? v : 8; }();
+    const int base = B * Hkv * sdp_tiles(Hq, Hkv, S, mma);
+    int want = (per_sm * sm_count() + base - 1) / base;
     const int max_by_len = (L + 127) / 128;
     if (want > max_by_len) want = max_by_len;
     if (want > 64) want = 64;
     return want < 1 ? 1 : want;
+}
+size_t sdp_workspace(int B, int Hq, int Hkv, int S, int L, int D, bool mma) {
+    return (size_t)B * Hkv * sdp_tiles(Hq, Hkv, S, mma) * sdp_splits(B, Hq, Hkv, S, L, mma) * sdp_rt(Hq, Hkv, S, mma) * (D + 2) * sizeof(float);
 }
 }  // namespace
 }  // namespace lowbit
@@ -347,7 +388,9 @@ extern "C" int lowbit_sdp_fp8_supported(int Hq, int Hkv, int S, int D) {
 
 extern "C" size_t lowbit_sdp_fp8_workspace_size(int B, int Hq, int Hkv, int S, int L, int D) {
     if (!lowbit_sdp_fp8_supported(Hq, Hkv, S, D) || B <= 0 || L <= 0) return 0;
-    return (size_t)B * Hkv * sdp_tiles(Hq, Hkv, S) * sdp_splits(B, Hq, Hkv, S, L) * sdp_rt(Hq, Hkv, S) * (D + 2) * sizeof(float);
+    // the query dtype is not known here: room for either kernel
+    const size_t a = sdp_workspace(B, Hq, Hkv, S, L, D, false), m = sdp_workspace(B, Hq, Hkv, S, L, D, true);
+    return a > m ? a : m;
 }
 
 extern "C" int lowbit_sdp_fp8_cuda(const void* d_q, int q_dtype, const int64_t* q_strides, const void* d_k,
@@ -380,20 +423,29 @@ extern "C" int lowbit_sdp_fp8_cuda(const void* d_q, int q_dtype, const int64_t* 
     A.m_sb = d_mask ? mask_strides[0] : 0; A.m_sh = d_mask ? mask_strides[1] : 0; A.m_ss = d_mask ? mask_strides[2] : 0;
     A.causal = causal; A.scale_log2e = scale * 1.4426950408889634f;
     A.B = B; A.Hq = Hq; A.Hkv = Hkv; A.S = S; A.L = L; A.D = D;
-    A.n_split = sdp_splits(B, Hq, Hkv, S, L);
+    // the tensor-core kernel reads value rows in 16-byte (head_dim 128) / 8-byte (64) pieces
+    // ... and query rows as 16-byte pieces
+    const bool mma = sdp_use_mma(q_dtype, D) && !(((uintptr_t)d_v | (uintptr_t)v_strides[0] | (uintptr_t)v_strides[1] | (uintptr_t)v_strides[2]) & 15) &&
+                     !((uintptr_t)d_q & 15) && !((q_strides[0] | q_strides[1] | q_strides[2]) & 7);
+    A.n_split = sdp_splits(B, Hq, Hkv, S, L, mma);
     A.keys_per_split = ((L + A.n_split - 1) / A.n_split + 31) / 32 * 32;
     A.part = (float*)workspace; A.out = d_out; A.out_dtype = out_dtype;
-    const int tiles = sdp_tiles(Hq, Hkv, S);
+    const int tiles = sdp_tiles(Hq, Hkv, S, mma);
     const dim3 grid((unsigned)A.n_split, (unsigned)(B * Hkv), (unsigned)tiles);
     cudaStream_t st = (cudaStream_t)stream;
-    A.rt = sdp_rt(Hq, Hkv, S);
+    A.rt = sdp_rt(Hq, Hkv, S, mma);
 #define SDP_LAUNCH(DPL) \
     do { \
         if (A.rt == 1) sdp_fp8_decode_kernel<DPL, 1><<<grid, SDP_WARPS * 32, 0, st>>>(A); \
         else if (A.rt == 2) sdp_fp8_decode_kernel<DPL, 2><<<grid, SDP_WARPS * 32, 0, st>>>(A); \
         else sdp_fp8_decode_kernel<DPL, 4><<<grid, SDP_WARPS * 32, 0, st>>>(A); \
     } while (0)
-    switch (D / 32) {
+    if (mma) {
+        static const int occ = [] { const char* e = getenv("LOWBIT_SDP_OCC"); return e ? atoi(e) : 2; }();
+        if (D == 64) sdp_fp8_decode_mma_kernel<64, 4><<<grid, SDP_WARPS * 32, 0, st>>>(A);
+        else if (occ == 3) sdp_fp8_decode_mma_kernel<128, 3><<<grid, SDP_WARPS * 32, 0, st>>>(A);
+        else sdp_fp8_decode_mma_kernel<128, 2><<<grid, SDP_WARPS * 32, 0, st>>>(A);
+    } else switch (D / 32) {
         case 2: SDP_LAUNCH(2); break;
         case 3: SDP_LAUNCH(3); break;
         case 4: SDP_LAUNCH(4); break;
@@ -402,8 +454,8 @@ extern "C" int lowbit_sdp_fp8_cuda(const void* d_q, int q_dtype, const int64_t* 
     }
 #undef SDP_LAUNCH
     note_launch();
-    const int64_t total = (int64_t)B * Hq * S * D;
-    sdp_fp8_combine_kernel<<<grid_for(total), 256, 0, st>>>(A, tiles);
+    const int64_t out_rows = (int64_t)B * Hq * S;
+    sdp_fp8_combine_kernel<<<(unsigned)((out_rows + SDP_COMBINE_WARPS - 1) / SDP_COMBINE_WARPS), SDP_COMBINE_WARPS * 32, 0, st>>>(A, tiles);
     note_launch();
     return check_launch();
 }

@@ -1,36 +1,46 @@
 // sdp_mma.cuh -- included by kvcache.cu (inside namespace lowbit::{anonymous}, after SdpArgs and the helpers).
-// Decode attention over the e5m2 cache with q.k on the tensor cores (fp16 / bf16 queries, head_dim % 64 == 0).
+// Decode attention over the e5m2 cache with q.k AND p.v on the tensor cores (fp16 / bf16 queries, head_dim 64 or
+// 128, up to 8 query rows per CTA = the GQA group x new tokens).
 //
-// Per warp and chunk of 32 keys = four 8-key tiles:  S[rows(16, padded) x keys(8)] = Q . K^T as mma.m16n8k16 with
-//   A = Q (rows g < RT live; rows g+8 are zero padding), fp16, kept in registers for the whole kernel,
-//   B = K^T: lane (g,t) supplies key g of the tile; e5m2 -> fp16 is a byte permute (e5m2 = high byte of fp16).
-// The head dimension is consumed in a permuted order so that every lane reads 16 contiguous bytes of its key row:
-// k-step (c, s), c = 0..D/64-1, s = 0..3 covers d = 64c + 16t + 4s + {0,1 | 2,3} for lane t (the A fragment of Q
-// uses the same order; a dot product does not care).
-// Scores stay in the accumulator layout (lane (g,t): row g, keys 2t, 2t+1 of each tile); softmax runs there, and
-// p.V keeps the lane-per-DPL-outputs layout of the CUDA-core kernel, fetching p with one shuffle per key and row.
+// Per warp and chunk of 32 keys, both products are mma.m16n8k16 (fp16 in, fp32 accumulate) with M = query rows
+// (rows 0..7 live, rows 8..15 zero padding: a1 = a3 = 0 and the c2/c3 outputs are write-only dummies):
+//   S[rows x 8 keys] = Q . K^T, four 8-key tiles.  A = Q, converted to fp16 once and kept in registers;
+//     B = K^T: lane (g,t) supplies key g of the tile.  e5m2 -> fp16 is a byte permute (e5m2 = high byte of fp16).
+//     The head dimension is consumed in a permuted order so that every lane reads 16 contiguous bytes per 64
+//     elements of its key row: k-step (c,s) covers d = 64c + 16t + 4s + {0,1 | 2,3} for lane t; Q's fragments use
+//     the same order (a dot product does not care).
+//   O[rows x D] += P . V, two 16-key steps x D/8 column tiles.  The score accumulators ARE the A fragments of P
+//     (lane (g,t): row g, keys 2t, 2t+1 of each tile), rounded to fp16.  B = V: lane (g,t) reads D/8 contiguous
+//     bytes at column (D/8) g of the four value rows 2t, 2t+1, 2t+8, 2t+9 of the step; column tile u takes byte u
+//     of each, i.e. the tile's columns are d = (D/8) n + u, n = 0..7 -- again a permutation, undone when the
+//     accumulators are written out.  One extra column tile of ones accumulates the softmax denominator from the
+//     SAME rounded p.
+// Online softmax runs in the accumulator layout: a row's 32 scores of the chunk sit in the 4 lanes of a quad.
 // bf16 queries are converted to fp16 (exact inside fp16's normal range, which attention queries live in).
 
-__device__ __forceinline__ void mma16816_f16(float (&c)[4], uint32_t a0, uint32_t a2, uint32_t b0, uint32_t b1) {
+__device__ __forceinline__ void mma16816_f16(float& c0, float& c1, float& z0, float& z1, uint32_t a0, uint32_t a2, uint32_t b0, uint32_t b1) {
     asm("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
-        : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+        : "+f"(c0), "+f"(c1), "+f"(z0), "+f"(z1)
         : "r"(a0), "r"(0u), "r"(a2), "r"(0u), "r"(b0), "r"(b1));
 }
 
-template <int DPL, int RT>
-__global__ void __launch_bounds__(SDP_WARPS * 32)
+constexpr int SDP_MMA_ROWS = 8;
+
+template <int D, int OCC>
+__global__ void __launch_bounds__(SDP_WARPS * 32, OCC)
 sdp_fp8_decode_mma_kernel(const SdpArgs A) {
-    constexpr int D = DPL * 32;
-    constexpr int NC = D / 64;                       // 64-element groups of the head dimension
-    static_assert(D % 64 == 0, "head_dim must be a multiple of 64");
-    __shared__ float red_m[SDP_WARPS][RT], red_l[SDP_WARPS][RT];
-    __shared__ float red_o[SDP_WARPS][RT][D];
+    constexpr int NC = D / 64;                       // 16-byte pieces of a key row per lane
+    constexpr int BPL = D / 8;                       // bytes of a value row per lane = output column tiles
+    constexpr int VW = BPL / 4;                      // ... as 32-bit words
+    static_assert(D == 64 || D == 128, "head_dim 64 or 128");
+    __shared__ float red_m[SDP_WARPS][SDP_MMA_ROWS], red_l[SDP_WARPS][SDP_MMA_ROWS];
+    __shared__ __align__(16) float red_o[SDP_WARPS][SDP_MMA_ROWS][D + 16];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int g = lane >> 2, t = lane & 3;
     const int split = blockIdx.x, hkv = blockIdx.y % A.Hkv, b = blockIdx.y / A.Hkv, tile = blockIdx.z;
     const int n_rep = A.Hq / A.Hkv, rows_total = n_rep * A.S;
-    const int row0 = tile * RT;
-    const int n_rows = min(RT, rows_total - row0);
+    const int row0 = tile * A.rt;
+    const int n_rows = min(A.rt, rows_total - row0);
 
     // A fragments of Q: lane (g,t) holds row g, elements 64c + 16t .. +15 as 8 fp16 pairs (zeros for rows >= n_rows)
     uint32_t qa[NC][8];
@@ -42,13 +52,152 @@ sdp_fp8_decode_mma_kernel(const SdpArgs A) {
     if (g < n_rows) {
         const int rr = row0 + g;
         my_hq = hkv * n_rep + rr / A.S; my_st = rr % A.S;
-        const int64_t base = b * A.q_sb + my_hq * A.q_sh + my_st * A.q_ss;
+        const uint16_t* qrow = reinterpret_cast<const uint16_t*>(A.q) + b * A.q_sb + my_hq * A.q_sh + my_st * A.q_ss + 16 * t;
 #pragma unroll
-        for (int c = 0; c < NC; c++)
+        for (int c = 0; c < NC; c++) {
+            const uint4 w0 = *reinterpret_cast<const uint4*>(qrow + 64 * c), w1 = *reinterpret_cast<const uint4*>(qrow + 64 * c + 8);
+            const uint32_t ws[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
 #pragma unroll
             for (int i = 0; i < 8; i++) {
-                const int d = 64 * c + 16 * t + 2 * i;
-                const __half2 h = __floats2half2_rn(load_as_float(A.q, A.q_dtype, base + d), load_as_float(A.q, A.q_dtype, base + d + 1));
-                qa[c][i] = *reinterpret_cast<const uint32_t*>(&h);
+                if (A.q_dtype == DT_F16) qa[c][i] = ws[i];
+                else {                                  // bf16 pair -> fp16 pair
+                    const __half2 h = __floats2half2_rn(__uint_as_float(ws[i] << 16), __uint_as_float(ws[i] & 0xffff0000u));
+                    qa[c][i] = *reinterpret_cast<const uint32_t*>(&h);
+                }
             }
+        }
     }
+
+    const int key_begin = split * A.keys_per_split;
+    const int key_end = min(A.L, key_begin + A.keys_per_split);
+    const uint8_t* kb = A.k + b * A.k_sb + hkv * A.k_sh + 16 * t;
+    const uint8_t* vb = A.v + b * A.v_sb + hkv * A.v_sh + BPL * g;
+    const int64_t mask_base = b * A.m_sb + my_hq * A.m_sh + my_st * A.m_ss;
+    const int causal_last = A.causal ? A.L - A.S + my_st : A.L;       // last key this lane's row sees
+
+    float m_run = -CUDART_INF_F;                      // of row g, the same in the quad's four lanes
+    float o[BPL][2], ol[2] = {0.0f, 0.0f};            // row g: columns BPL (2t + i) + u;  ol = softmax denominator
+    float z[4][2];                                    // rows 8..15 of every accumulator tile: always zero
+#pragma unroll
+    for (int u = 0; u < BPL; u++) o[u][0] = o[u][1] = 0.0f;
+#pragma unroll
+    for (int i = 0; i < 4; i++) z[i][0] = z[i][1] = 0.0f;
+
+    for (int c0 = key_begin + warp * 32; c0 < key_end; c0 += SDP_WARPS * 32) {
+        // ---- all loads of the chunk first (one memory round trip per chunk).  Keys beyond the range are clamped
+        // to the last one; their p is 0.
+        uint4 kw[4][NC];
+#pragma unroll
+        for (int n = 0; n < 4; n++) {
+            const uint4* kr = reinterpret_cast<const uint4*>(kb + (int64_t)min(c0 + 8 * n + g, key_end - 1) * A.k_ss);
+#pragma unroll
+            for (int c = 0; c < NC; c++) kw[n][c] = kr[4 * c];
+        }
+        uint32_t vw[2][4][VW];                        // [16-key step][row 2t, 2t+1, 2t+8, 2t+9][word]
+#pragma unroll
+        for (int j = 0; j < 2; j++)
+#pragma unroll
+            for (int h = 0; h < 4; h++) {
+                const int key = min(c0 + 16 * j + 2 * t + (h & 1) + 8 * (h >> 1), key_end - 1);
+                const uint8_t* vr = vb + (int64_t)key * A.v_ss;
+                if (VW == 4) {
+                    const uint4 w = *reinterpret_cast<const uint4*>(vr);
+                    vw[j][h][0] = w.x; vw[j][h][1] = w.y; vw[j][h][VW - 2] = w.z; vw[j][h][VW - 1] = w.w;
+                } else {
+                    const uint2 w = *reinterpret_cast<const uint2*>(vr);
+                    vw[j][h][0] = w.x; vw[j][h][1] = w.y;
+                }
+            }
+        // ---- scores of 4 tiles x 8 keys
+        float sc[4][2];
+#pragma unroll
+        for (int n = 0; n < 4; n++) {
+            sc[n][0] = sc[n][1] = 0.0f;
+#pragma unroll
+            for (int c = 0; c < NC; c++) {
+                const uint32_t ws[4] = {kw[n][c].x, kw[n][c].y, kw[n][c].z, kw[n][c].w};
+#pragma unroll
+                for (int s = 0; s < 4; s++)
+                    mma16816_f16(sc[n][0], sc[n][1], z[n][0], z[n][1], qa[c][2 * s], qa[c][2 * s + 1],
+                                 __byte_perm(ws[s], 0u, 0x1404u), __byte_perm(ws[s], 0u, 0x3424u));
+            }
+        }
+        // ---- scale, mask: this lane's values are row g, keys c0 + 8n + 2t + i
+        float mx = -CUDART_INF_F;
+#pragma unroll
+        for (int n = 0; n < 4; n++)
+#pragma unroll
+            for (int i = 0; i < 2; i++) {
+                const int key = c0 + 8 * n + 2 * t + i;
+                float s = sc[n][i] * A.scale_log2e;
+                const bool ok = key < key_end && g < n_rows && key <= causal_last;
+                if (ok && A.mask) s += load_as_float(A.mask, A.mask_dtype, mask_base + key) * 1.4426950408889634f;
+                if (!ok) s = -CUDART_INF_F;
+                sc[n][i] = s;
+                mx = fmaxf(mx, s);
+            }
+        // ---- online softmax of row g: its 32 scores live in the 4 lanes of the quad
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+        const float m_new = fmaxf(m_run, mx);
+        const float corr = (m_new == -CUDART_INF_F) ? 1.0f : exp2f(m_run - m_new);
+        m_run = m_new;
+        uint32_t pa[4];                               // A fragments of P (fp16 pairs)
+#pragma unroll
+        for (int n = 0; n < 4; n++) {
+            const float p0 = (sc[n][0] == -CUDART_INF_F) ? 0.0f : exp2f(sc[n][0] - m_new);
+            const float p1 = (sc[n][1] == -CUDART_INF_F) ? 0.0f : exp2f(sc[n][1] - m_new);
+            const __half2 h = __floats2half2_rn(p0, p1);
+            pa[n] = *reinterpret_cast<const uint32_t*>(&h);
+        }
+        ol[0] *= corr; ol[1] *= corr;
+#pragma unroll
+        for (int u = 0; u < BPL; u++) { o[u][0] *= corr; o[u][1] *= corr; }
+        // ---- O += P . V (and the denominator through a tile of ones)
+#pragma unroll
+        for (int j = 0; j < 2; j++) {
+            mma16816_f16(ol[0], ol[1], z[j][0], z[j][1], pa[2 * j], pa[2 * j + 1], 0x3c003c00u, 0x3c003c00u);
+#pragma unroll
+            for (int q = 0; q < VW; q++) {
+                // bytes of keys (2t, 2t+1) and (2t+8, 2t+9) interleaved: [a0 b0 a1 b1], [a2 b2 a3 b3]
+                const uint32_t lo01 = __byte_perm(vw[j][0][q], vw[j][1][q], 0x5140u), lo23 = __byte_perm(vw[j][0][q], vw[j][1][q], 0x7362u);
+                const uint32_t hi01 = __byte_perm(vw[j][2][q], vw[j][3][q], 0x5140u), hi23 = __byte_perm(vw[j][2][q], vw[j][3][q], 0x7362u);
+#pragma unroll
+                for (int e = 0; e < 4; e++) {
+                    const uint32_t sel = (e & 1) ? 0x3424u : 0x1404u;
+                    const int u = 4 * q + e;
+                    mma16816_f16(o[u][0], o[u][1], z[e][0], z[e][1], pa[2 * j], pa[2 * j + 1],
+                                 __byte_perm(e < 2 ? lo01 : lo23, 0u, sel), __byte_perm(e < 2 ? hi01 : hi23, 0u, sel));
+                }
+            }
+        }
+    }
+    // ---- combine the warps (m, l, o) in a fixed order; the accumulator columns go back to their places
+    // (each lane owns runs of BPL consecutive columns; for D = 128 the 16-byte pieces of a run are XOR-swizzled
+    // by t and rows are padded by 16 floats so that the float4 stores of a quarter warp cover all 32 banks)
+    if (t == 0) { red_m[warp][g] = m_run; red_l[warp][g] = ol[0]; }
+#pragma unroll
+    for (int i = 0; i < 2; i++)
+#pragma unroll
+        for (int q = 0; q < VW; q++)
+            *reinterpret_cast<float4*>(&red_o[warp][g][BPL * (2 * t + i) + 4 * (D == 128 ? (q ^ t) : q)]) =
+                make_float4(o[4 * q][i], o[4 * q + 1][i], o[4 * q + 2][i], o[4 * q + 3][i]);
+    __syncthreads();
+    float* part = A.part + ((((int64_t)b * A.Hkv + hkv) * gridDim.z + tile) * A.n_split + split) * (A.rt * (D + 2));
+    for (int i = threadIdx.x; i < A.rt * D; i += blockDim.x) {
+        const int r = i / D, d = i % D;
+        const int pos = D == 128 ? ((d & ~12) | ((((d >> 2) ^ (d >> 5)) & 3) << 2)) : d;       // where column d was staged
+        float M = red_m[0][r];
+#pragma unroll
+        for (int w = 1; w < SDP_WARPS; w++) M = fmaxf(M, red_m[w][r]);
+        float acc = 0.0f, lsum = 0.0f;
+#pragma unroll
+        for (int w = 0; w < SDP_WARPS; w++) {
+            const float f = (red_m[w][r] == -CUDART_INF_F) ? 0.0f : exp2f(red_m[w][r] - M);
+            acc = fmaf(red_o[w][r][pos], f, acc);
+            lsum = fmaf(red_l[w][r], f, lsum);
+        }
+        part[r * (D + 2) + 2 + d] = acc;
+        if (d == 0) { part[r * (D + 2)] = M; part[r * (D + 2) + 1] = lsum; }
+    }
+}

@@ -30,6 +30,10 @@ def bench(B,Hq,Hkv,L,D=128,S=1,dt=torch.float16):
     for _ in range(20): torch.nn.functional.scaled_dot_product_attention(q,k16,v16)
     e1.record(); torch.cuda.synchronize()
     print(f"B={B} Hq={Hq} Hkv={Hkv} L={L} S={S}: {us:7.2f} us  {byts/us/1e6:5.2f} TB/s of fp8 KV | torch sdpa fp16 (dense KV, eager) {e0.elapsed_time(e1)/20*1e3:7.1f} us",flush=True)
-for L in (512,2048,8192,32768): bench(1,32,32,L)
-for L in (2048,8192,32768): bench(1,32,8,L)
-bench(16,32,8,4096); bench(4,32,32,4096); bench(1,32,8,8192,S=4)
+import os
+if os.environ.get("MB_SHORT"):
+    bench(1,32,32,2048); bench(1,32,32,32768); bench(1,32,8,8192); bench(16,32,8,4096)
+else:
+    for L in (512,2048,8192,32768): bench(1,32,32,L)
+    for L in (2048,8192,32768): bench(1,32,8,L)
+    bench(16,32,8,4096); bench(4,32,32,4096); bench(1,32,8,8192,S=4); bench(8,8,8,4096,D=64)
