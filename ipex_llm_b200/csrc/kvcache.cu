@@ -256,19 +256,21 @@ sdp_fp8_decode_kernel(const SdpArgs A) {
     }
 }
 
-// one warp per output row: merge the splits' (m, l, o).  The (m, l) of the splits sit one per lane (two for more than
-// 32 splits) and are reduced with shuffles; every lane then owns columns lane, lane + 32, ... and walks the splits with
-// independent, coalesced loads.  Fixed order: the result does not depend on scheduling.
+// one CTA per output row: merge the splits' (m, l, o).  The (m, l) of the splits sit one per lane (two for more than
+// 32 splits) and are reduced with shuffles; warp w then takes splits w, w + 4, ..., four at a time with all their loads
+// issued before the first use (a split-by-split loop exposed one memory round trip per split), every lane owning
+// columns lane, lane + 32, ...; the four warps' sums meet in shared memory.  Fixed order throughout.
 constexpr int SDP_COMBINE_WARPS = 4;
 __global__ void __launch_bounds__(SDP_COMBINE_WARPS * 32) sdp_fp8_combine_kernel(const SdpArgs A, int n_tiles) {
-    const int D = A.D, lane = threadIdx.x & 31;
-    const int64_t row = (int64_t)blockIdx.x * SDP_COMBINE_WARPS + (threadIdx.x >> 5);
-    if (row >= (int64_t)A.B * A.Hq * A.S) return;
+    __shared__ float red[SDP_COMBINE_WARPS][256];                                 // D <= 256
+    const int D = A.D, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t row = blockIdx.x;
     const int n_rep = A.Hq / A.Hkv;
     const int st = (int)(row % A.S), hq = (int)((row / A.S) % A.Hq), b = (int)(row / ((int64_t)A.S * A.Hq));
     const int hkv = hq / n_rep, rr = (hq % n_rep) * A.S + st, tile = rr / A.rt, r = rr % A.rt;
     const int64_t ps = (int64_t)A.rt * (D + 2);                                   // floats between two splits
     const float* part = A.part + (((int64_t)b * A.Hkv + hkv) * n_tiles + tile) * A.n_split * ps + r * (D + 2);
+    asm volatile("griddepcontrol.wait;" ::: "memory");                           // the partial results are complete
     float m2[2], l2[2];
 #pragma unroll
     for (int h = 0; h < 2; h++) {
@@ -285,27 +287,43 @@ __global__ void __launch_bounds__(SDP_COMBINE_WARPS * 32) sdp_fp8_combine_kernel
     float l = fmaf(l2[0], f2[0], l2[1] * f2[1]);
 #pragma unroll
     for (int o = 16; o; o >>= 1) l += __shfl_xor_sync(0xffffffffu, l, o);
-    float acc[8];                                                                 // D <= 256
+    float acc[8];
 #pragma unroll
     for (int e = 0; e < 8; e++) acc[e] = 0.0f;
-#pragma unroll 4
-    for (int sp = 0; sp < A.n_split; sp++) {
-        const float f = __shfl_sync(0xffffffffu, sp < 32 ? f2[0] : f2[1], sp & 31);
-        const float* po = part + sp * ps + 2 + lane;
+    for (int sp0 = warp; sp0 < A.n_split; sp0 += 4 * SDP_COMBINE_WARPS) {
+        float v[4][8];
 #pragma unroll
-        for (int e = 0; e < 8; e++)
-            if (32 * e < D) acc[e] = fmaf(po[32 * e], f, acc[e]);
+        for (int k = 0; k < 4; k++) {
+            const float* po = part + (int64_t)min(sp0 + SDP_COMBINE_WARPS * k, A.n_split - 1) * ps + 2 + lane;
+#pragma unroll
+            for (int e = 0; e < 8; e++)
+                if (32 * e < D) v[k][e] = po[32 * e];
+        }
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const int sp = sp0 + SDP_COMBINE_WARPS * k;
+            float f = __shfl_sync(0xffffffffu, sp < 32 ? f2[0] : f2[1], sp & 31);
+            if (sp >= A.n_split) f = 0.0f;
+#pragma unroll
+            for (int e = 0; e < 8; e++)
+                if (32 * e < D) acc[e] = fmaf(v[k][e], f, acc[e]);
+        }
     }
-    const float inv = l > 0.0f ? 1.0f / l : 0.0f;                                 // a row with every key masked gives zeros
 #pragma unroll
     for (int e = 0; e < 8; e++)
-        if (32 * e < D) {
-            const int64_t i = row * D + 32 * e + lane;
-            const float y = acc[e] * inv;
-            if (A.out_dtype == DT_F32) ((float*)A.out)[i] = y;
-            else if (A.out_dtype == DT_F16) ((__half*)A.out)[i] = __float2half_rn(y);
-            else ((__nv_bfloat16*)A.out)[i] = __float2bfloat16_rn(y);
-        }
+        if (32 * e < D) red[warp][32 * e + lane] = acc[e];
+    __syncthreads();
+    const float inv = l > 0.0f ? 1.0f / l : 0.0f;                                 // a row with every key masked gives zeros
+    for (int d = threadIdx.x; d < D; d += blockDim.x) {
+        float y = red[0][d];
+#pragma unroll
+        for (int w = 1; w < SDP_COMBINE_WARPS; w++) y += red[w][d];
+        y *= inv;
+        const int64_t i = row * D + d;
+        if (A.out_dtype == DT_F32) ((float*)A.out)[i] = y;
+        else if (A.out_dtype == DT_F16) ((__half*)A.out)[i] = __float2half_rn(y);
+        else ((__nv_bfloat16*)A.out)[i] = __float2bfloat16_rn(y);
+    }
 }
 
 #include "sdp_mma.cuh"
@@ -323,18 +341,35 @@ bool sdp_use_mma(int q_dtype, int D) {
     return !off && q_dtype != DT_F32 && (D == 64 || D == 128);
 }
 
-// splits of the key axis: enough CTAs for ~8 per SM (the loads are latency bound), at least 128 keys each
-int sdp_splits(int B, int Hq, int Hkv, int S, int L, bool mma) {
+// splits of the key axis, at least 128 keys each.
+// CUDA-core kernel: enough CTAs for ~8 per SM (its loads are latency bound).
+// Tensor-core kernel: the split count that minimises  waves x (fixed + keys per CTA)  with waves = CTAs / resident
+// CTAs rounded up and the fixed cost of a CTA (query fragments, first chunk's latency, merge) worth ~384 keys:
+// one full wave of long CTAs beats several waves of short ones.
+int sdp_splits(int B, int Hq, int Hkv, int S, int L, int D, bool mma) {
     static const int per_sm = [] { const char* e = getenv("LOWBIT_SDP_CTAS_PER_SM"); const int v = e ? atoi(e) : 0; return v > 0 ? v : 8; }();
+    static const int forced = [] { const char* e = getenv("LOWBIT_SDP_SPLITS"); return e ? atoi(e) : 0; }();
     const int base = B * Hkv * sdp_tiles(Hq, Hkv, S, mma);
+    int max_by_len = (L + 127) / 128;
+    if (max_by_len > 64) max_by_len = 64;
+    if (forced > 0) return forced < max_by_len ? forced : max_by_len;
+    if (mma) {
+        const int64_t cap = (int64_t)sm_count() * (D == 128 ? 2 : 4);
+        int best = 1; int64_t best_cost = INT64_MAX;
+        for (int n = 1; n <= max_by_len; n++) {
+            const int64_t waves = ((int64_t)base * n + cap - 1) / cap;
+            const int64_t keys = (((L + n - 1) / n + 127) / 128) * 128;
+            const int64_t cost = waves * (384 + keys);
+            if (cost < best_cost) { best_cost = cost; best = n; }
+        }
+        return best;
+    }
     int want = (per_sm * sm_count() + base - 1) / base;
-    const int max_by_len = (L + 127) / 128;
     if (want > max_by_len) want = max_by_len;
-    if (want > 64) want = 64;
     return want < 1 ? 1 : want;
 }
 size_t sdp_workspace(int B, int Hq, int Hkv, int S, int L, int D, bool mma) {
-    return (size_t)B * Hkv * sdp_tiles(Hq, Hkv, S, mma) * sdp_splits(B, Hq, Hkv, S, L, mma) * sdp_rt(Hq, Hkv, S, mma) * (D + 2) * sizeof(float);
+    return (size_t)B * Hkv * sdp_tiles(Hq, Hkv, S, mma) * sdp_splits(B, Hq, Hkv, S, L, D, mma) * sdp_rt(Hq, Hkv, S, mma) * (D + 2) * sizeof(float);
 }
 }  // namespace
 }  // namespace lowbit
@@ -425,9 +460,9 @@ extern "C" int lowbit_sdp_fp8_cuda(const void* d_q, int q_dtype, const int64_t* 
     A.B = B; A.Hq = Hq; A.Hkv = Hkv; A.S = S; A.L = L; A.D = D;
     // the tensor-core kernel reads value rows in 16-byte (head_dim 128) / 8-byte (64) pieces
     // ... and query rows as 16-byte pieces
-    const bool mma = sdp_use_mma(q_dtype, D) && !(((uintptr_t)d_v | (uintptr_t)v_strides[0] | (uintptr_t)v_strides[1] | (uintptr_t)v_strides[2]) & 15) &&
+    const bool mma = sdp_use_mma(q_dtype, D) && scale > 0.0f && !(((uintptr_t)d_v | (uintptr_t)v_strides[0] | (uintptr_t)v_strides[1] | (uintptr_t)v_strides[2]) & 15) &&
                      !((uintptr_t)d_q & 15) && !((q_strides[0] | q_strides[1] | q_strides[2]) & 7);
-    A.n_split = sdp_splits(B, Hq, Hkv, S, L, mma);
+    A.n_split = sdp_splits(B, Hq, Hkv, S, L, D, mma);
     A.keys_per_split = ((L + A.n_split - 1) / A.n_split + 31) / 32 * 32;
     A.part = (float*)workspace; A.out = d_out; A.out_dtype = out_dtype;
     const int tiles = sdp_tiles(Hq, Hkv, S, mma);
@@ -441,10 +476,26 @@ extern "C" int lowbit_sdp_fp8_cuda(const void* d_q, int q_dtype, const int64_t* 
         else sdp_fp8_decode_kernel<DPL, 4><<<grid, SDP_WARPS * 32, 0, st>>>(A); \
     } while (0)
     if (mma) {
-        static const int occ = [] { const char* e = getenv("LOWBIT_SDP_OCC"); return e ? atoi(e) : 2; }();
-        if (D == 64) sdp_fp8_decode_mma_kernel<64, 4><<<grid, SDP_WARPS * 32, 0, st>>>(A);
-        else if (occ == 3) sdp_fp8_decode_mma_kernel<128, 3><<<grid, SDP_WARPS * 32, 0, st>>>(A);
-        else sdp_fp8_decode_mma_kernel<128, 2><<<grid, SDP_WARPS * 32, 0, st>>>(A);
+        // head_dim 128: chunks staged through a per-warp cp.async ring (LOWBIT_SDP_RING = stages; 0 = loads into
+        // registers, the only variant for head_dim 64)
+        static const int nst = [] { const char* e = getenv("LOWBIT_SDP_RING"); return e ? atoi(e) : 3; }();
+        if (D == 64) sdp_fp8_decode_mma_kernel<64, 4, 0><<<grid, SDP_WARPS * 32, 0, st>>>(A);
+        else if (nst == 0) sdp_fp8_decode_mma_kernel<128, 2, 0><<<grid, SDP_WARPS * 32, 0, st>>>(A);
+        else {
+            auto kern = nst == 2 ? sdp_fp8_decode_mma_kernel<128, 3, 2> : (nst == 4 ? sdp_fp8_decode_mma_kernel<128, 1, 4> : sdp_fp8_decode_mma_kernel<128, 2, 3>);
+            const int smem = SDP_WARPS * (nst == 2 ? 2 : (nst == 4 ? 4 : 3)) * 8192;
+            static bool configured[64][3] = {};
+            int dev = 0; cudaGetDevice(&dev);
+            const int vi = nst == 2 ? 0 : (nst == 4 ? 2 : 1);
+            if (dev >= 0 && dev < 64 && !configured[dev][vi]) {
+                if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) {
+                    set_error(LB_ERR_CUDA, "lowbit_sdp_fp8_cuda: cannot reserve %d bytes of shared memory", smem);
+                    return LB_ERR_CUDA;
+                }
+                configured[dev][vi] = true;
+            }
+            kern<<<grid, SDP_WARPS * 32, smem, st>>>(A);
+        }
     } else switch (D / 32) {
         case 2: SDP_LAUNCH(2); break;
         case 3: SDP_LAUNCH(3); break;
@@ -454,8 +505,16 @@ extern "C" int lowbit_sdp_fp8_cuda(const void* d_q, int q_dtype, const int64_t* 
     }
 #undef SDP_LAUNCH
     note_launch();
+    // the merge is launched as a programmatic dependent of the kernel above: its CTAs are scheduled while that grid
+    // drains and wait (griddepcontrol.wait) until its partial results are complete and visible
     const int64_t out_rows = (int64_t)B * Hq * S;
-    sdp_fp8_combine_kernel<<<(unsigned)((out_rows + SDP_COMBINE_WARPS - 1) / SDP_COMBINE_WARPS), SDP_COMBINE_WARPS * 32, 0, st>>>(A, tiles);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)out_rows); cfg.blockDim = dim3(SDP_COMBINE_WARPS * 32); cfg.dynamicSmemBytes = 0; cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    cudaLaunchKernelEx(&cfg, sdp_fp8_combine_kernel, A, tiles);
     note_launch();
     return check_launch();
 }

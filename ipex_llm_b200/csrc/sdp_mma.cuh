@@ -24,23 +24,35 @@ __device__ __forceinline__ void mma16816_f16(float& c0, float& c1, float& z0, fl
         : "r"(a0), "r"(0u), "r"(a2), "r"(0u), "r"(b0), "r"(b1));
 }
 
+// 2^x, x <= 0 or -inf (-> 0): one MUFU, no range fix-up
+__device__ __forceinline__ float ex2_approx(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
 constexpr int SDP_MMA_ROWS = 8;
 
-template <int D, int OCC>
+template <int D, int OCC, int NST>
 __global__ void __launch_bounds__(SDP_WARPS * 32, OCC)
 sdp_fp8_decode_mma_kernel(const SdpArgs A) {
     constexpr int NC = D / 64;                       // 16-byte pieces of a key row per lane
     constexpr int BPL = D / 8;                       // bytes of a value row per lane = output column tiles
     constexpr int VW = BPL / 4;                      // ... as 32-bit words
     static_assert(D == 64 || D == 128, "head_dim 64 or 128");
+    static_assert(NST == 0 || D == 128, "the staged variant is written for 128-byte rows");
+    extern __shared__ __align__(128) uint8_t sdp_ring[];            // NST > 0: [warp][stage][K 4 KB | V 4 KB]
     __shared__ float red_m[SDP_WARPS][SDP_MMA_ROWS], red_l[SDP_WARPS][SDP_MMA_ROWS];
-    __shared__ __align__(16) float red_o[SDP_WARPS][SDP_MMA_ROWS][D + 16];
+    constexpr int RO = SDP_MMA_ROWS * (D + 16);       // floats of one warp's staged accumulators (NST > 0: in its ring)
+    __shared__ __align__(16) float red_o_static[NST > 0 ? 4 : SDP_WARPS * RO];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int g = lane >> 2, t = lane & 3;
     const int split = blockIdx.x, hkv = blockIdx.y % A.Hkv, b = blockIdx.y / A.Hkv, tile = blockIdx.z;
     const int n_rep = A.Hq / A.Hkv, rows_total = n_rep * A.S;
     const int row0 = tile * A.rt;
     const int n_rows = min(A.rt, rows_total - row0);
+
+    asm volatile("griddepcontrol.launch_dependents;");               // the merge kernel may be scheduled as CTAs here retire
 
     // A fragments of Q: lane (g,t) holds row g, elements 64c + 16t .. +15 as 8 fp16 pairs (zeros for rows >= n_rows)
     uint32_t qa[NC][8];
@@ -74,6 +86,7 @@ sdp_fp8_decode_mma_kernel(const SdpArgs A) {
     const uint8_t* vb = A.v + b * A.v_sb + hkv * A.v_sh + BPL * g;
     const int64_t mask_base = b * A.m_sb + my_hq * A.m_sh + my_st * A.m_ss;
     const int causal_last = A.causal ? A.L - A.S + my_st : A.L;       // last key this lane's row sees
+    const int causal_first = A.causal ? A.L - A.S : A.L;              // ... and the first row of the tile at least
 
     float m_run = -CUDART_INF_F;                      // of row g, the same in the quad's four lanes
     float o[BPL][2], ol[2] = {0.0f, 0.0f};            // row g: columns BPL (2t + i) + u;  ol = softmax denominator
@@ -83,17 +96,65 @@ sdp_fp8_decode_mma_kernel(const SdpArgs A) {
 #pragma unroll
     for (int i = 0; i < 4; i++) z[i][0] = z[i][1] = 0.0f;
 
+    // NST > 0: every warp streams its chunks through a ring of NST stages filled by cp.async (16 bytes per lane and
+    // instruction, rows coalesced), NST - 1 chunks ahead of the one being used.  Inside a stage the 16-byte pieces of
+    // a row are XOR-swizzled so that the fragment reads below are bank-conflict free: key rows by (row & 1) << 2
+    // (a quarter warp reads 4 pieces of 2 consecutive rows), value rows by ((row >> 1) & 3) << 1 (a quarter warp
+    // reads 2 pieces of rows 2t).
+    uint8_t* const ring = sdp_ring + warp * (NST * 8192);
+    const uint8_t* const kb0 = A.k + b * A.k_sb + hkv * A.k_sh + 16 * (lane & 7);
+    const uint8_t* const vb0 = A.v + b * A.v_sb + hkv * A.v_sh + 16 * (lane & 7);
+    const uint32_t ring_s = (uint32_t)__cvta_generic_to_shared(ring);
+    const int r0 = lane >> 3, unit = lane & 7;        // lane copies piece `unit` of rows r0, r0 + 4, ...
+    const uint32_t k_off = r0 * 128 + ((unit ^ ((r0 & 1) << 2)) << 4);
+    const uint32_t v_off0 = 4096 + r0 * 128 + ((unit ^ (((r0 >> 1) & 3) << 1)) << 4);          // rows r0 + 8i'
+    const uint32_t v_off1 = 4096 + (r0 + 4) * 128 + ((unit ^ ((((r0 >> 1) + 2) & 3) << 1)) << 4);   // rows r0 + 4 + 8i'
+    const bool rows_128 = A.k_ss == 128 && A.v_ss == 128;
+    auto stage_chunk = [&](int c0, int slot) {
+        if (c0 < key_end) {
+            const uint32_t dst = ring_s + slot * 8192;
+            if (c0 + 32 <= key_end && rows_128) {     // a whole chunk of densely stored rows: constant address steps
+                const uint8_t* kp = kb0 + (int64_t)(c0 + r0) * 128;
+                const uint8_t* vp = vb0 + (int64_t)(c0 + r0) * 128;
+#pragma unroll
+                for (int i = 0; i < 8; i++) {
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(dst + k_off + i * 512), "l"(kp + i * 512) : "memory");
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(dst + ((i & 1) ? v_off1 : v_off0) + (i >> 1) * 1024), "l"(vp + i * 512) : "memory");
+                }
+            } else {
+#pragma unroll
+                for (int i = 0; i < 8; i++) {
+                    const int64_t key = min(c0 + 4 * i + r0, key_end - 1);
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(dst + k_off + i * 512), "l"(kb0 + key * A.k_ss) : "memory");
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(dst + ((i & 1) ? v_off1 : v_off0) + (i >> 1) * 1024), "l"(vb0 + key * A.v_ss) : "memory");
+                }
+            }
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    if (NST > 0) {
+#pragma unroll
+        for (int s = 0; s < NST - 1; s++) stage_chunk(key_begin + (warp + SDP_WARPS * s) * 32, s);
+    }
+    int slot = 0;
     for (int c0 = key_begin + warp * 32; c0 < key_end; c0 += SDP_WARPS * 32) {
+        uint4 kw[4][NC];
+        uint32_t vw[2][4][VW];                        // [16-key step][row 2t, 2t+1, 2t+8, 2t+9][word]
+        const uint8_t* stage = ring + slot * 8192;
+        if (NST > 0) {
+            int ahead = slot + NST - 1; if (ahead >= NST) ahead -= NST;
+            stage_chunk(c0 + (NST - 1) * SDP_WARPS * 32, ahead);
+            asm volatile("cp.async.wait_group %0;" :: "n"(NST > 0 ? NST - 1 : 0) : "memory");
+            __syncwarp();
+        } else {
         // ---- all loads of the chunk first (one memory round trip per chunk).  Keys beyond the range are clamped
         // to the last one; their p is 0.
-        uint4 kw[4][NC];
 #pragma unroll
         for (int n = 0; n < 4; n++) {
             const uint4* kr = reinterpret_cast<const uint4*>(kb + (int64_t)min(c0 + 8 * n + g, key_end - 1) * A.k_ss);
 #pragma unroll
             for (int c = 0; c < NC; c++) kw[n][c] = kr[4 * c];
         }
-        uint32_t vw[2][4][VW];                        // [16-key step][row 2t, 2t+1, 2t+8, 2t+9][word]
 #pragma unroll
         for (int j = 0; j < 2; j++)
 #pragma unroll
@@ -108,6 +169,7 @@ sdp_fp8_decode_mma_kernel(const SdpArgs A) {
                     vw[j][h][0] = w.x; vw[j][h][1] = w.y;
                 }
             }
+        }
         // ---- scores of 4 tiles x 8 keys
         float sc[4][2];
 #pragma unroll
@@ -115,6 +177,7 @@ sdp_fp8_decode_mma_kernel(const SdpArgs A) {
             sc[n][0] = sc[n][1] = 0.0f;
 #pragma unroll
             for (int c = 0; c < NC; c++) {
+                if (NST > 0) kw[n][c] = *reinterpret_cast<const uint4*>(stage + (8 * n + g) * 128 + (((4 * c + t) ^ ((g & 1) << 2)) << 4));
                 const uint32_t ws[4] = {kw[n][c].x, kw[n][c].y, kw[n][c].z, kw[n][c].w};
 #pragma unroll
                 for (int s = 0; s < 4; s++)
@@ -122,40 +185,70 @@ sdp_fp8_decode_mma_kernel(const SdpArgs A) {
                                  __byte_perm(ws[s], 0u, 0x1404u), __byte_perm(ws[s], 0u, 0x3424u));
             }
         }
-        // ---- scale, mask: this lane's values are row g, keys c0 + 8n + 2t + i
-        float mx = -CUDART_INF_F;
-#pragma unroll
-        for (int n = 0; n < 4; n++)
-#pragma unroll
-            for (int i = 0; i < 2; i++) {
-                const int key = c0 + 8 * n + 2 * t + i;
-                float s = sc[n][i] * A.scale_log2e;
-                const bool ok = key < key_end && g < n_rows && key <= causal_last;
-                if (ok && A.mask) s += load_as_float(A.mask, A.mask_dtype, mask_base + key) * 1.4426950408889634f;
-                if (!ok) s = -CUDART_INF_F;
-                sc[n][i] = s;
-                mx = fmaxf(mx, s);
-            }
-        // ---- online softmax of row g: its 32 scores live in the 4 lanes of the quad
-        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
-        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
-        const float m_new = fmaxf(m_run, mx);
-        const float corr = (m_new == -CUDART_INF_F) ? 1.0f : exp2f(m_run - m_new);
-        m_run = m_new;
+        // ---- scale, mask, online softmax of row g (its 32 scores of the chunk live in the 4 lanes of the quad); this
+        // lane's values are keys c0 + 8n + 2t + i.  p = 2^(s - m_run) with m_run a reference point, not necessarily
+        // the exact running maximum.
         uint32_t pa[4];                               // A fragments of P (fp16 pairs)
+        float corr = 1.0f;
+        if (c0 + 32 <= key_end && c0 + 31 <= causal_first && !A.mask) {
+            // every key of the chunk is visible to every row (the common case): no predicates, the scale folded into
+            // the exponent, and the accumulators are rescaled only when some row's maximum grew by more than 2^8
+            // (p <= 256 then; fp16 holds it with the same relative precision)
+            float mx = fmaxf(fmaxf(fmaxf(sc[0][0], sc[0][1]), fmaxf(sc[1][0], sc[1][1])), fmaxf(fmaxf(sc[2][0], sc[2][1]), fmaxf(sc[3][0], sc[3][1])));
+            mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+            mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+            const float m_new = mx * A.scale_log2e;   // scale > 0 (checked by the launcher)
+            const bool grow = m_new > m_run + 8.0f;
+            if (__any_sync(0xffffffffu, grow)) {
+                if (grow) { corr = ex2_approx(m_run - m_new); m_run = m_new; }
+                ol[0] *= corr; ol[1] *= corr;
 #pragma unroll
-        for (int n = 0; n < 4; n++) {
-            const float p0 = (sc[n][0] == -CUDART_INF_F) ? 0.0f : exp2f(sc[n][0] - m_new);
-            const float p1 = (sc[n][1] == -CUDART_INF_F) ? 0.0f : exp2f(sc[n][1] - m_new);
-            const __half2 h = __floats2half2_rn(p0, p1);
-            pa[n] = *reinterpret_cast<const uint32_t*>(&h);
+                for (int u = 0; u < BPL; u++) { o[u][0] *= corr; o[u][1] *= corr; }
+            }
+#pragma unroll
+            for (int n = 0; n < 4; n++) {
+                const __half2 h = __floats2half2_rn(ex2_approx(fmaf(sc[n][0], A.scale_log2e, -m_run)), ex2_approx(fmaf(sc[n][1], A.scale_log2e, -m_run)));
+                pa[n] = *reinterpret_cast<const uint32_t*>(&h);
+            }
+        } else {
+            float mx = -CUDART_INF_F;
+#pragma unroll
+            for (int n = 0; n < 4; n++)
+#pragma unroll
+                for (int i = 0; i < 2; i++) {
+                    const int key = c0 + 8 * n + 2 * t + i;
+                    float s = sc[n][i] * A.scale_log2e;
+                    const bool ok = key < key_end && g < n_rows && key <= causal_last;
+                    if (ok && A.mask) s += load_as_float(A.mask, A.mask_dtype, mask_base + key) * 1.4426950408889634f;
+                    if (!ok) s = -CUDART_INF_F;
+                    sc[n][i] = s;
+                    mx = fmaxf(mx, s);
+                }
+            mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+            mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 2));
+            const float m_new = fmaxf(m_run, mx);
+            const float m_ref = (m_new == -CUDART_INF_F) ? 0.0f : m_new;          // all keys masked so far: p = 2^-inf = 0
+            corr = ex2_approx(m_run - m_ref);
+            m_run = m_new;
+#pragma unroll
+            for (int n = 0; n < 4; n++) {
+                const __half2 h = __floats2half2_rn(ex2_approx(sc[n][0] - m_ref), ex2_approx(sc[n][1] - m_ref));
+                pa[n] = *reinterpret_cast<const uint32_t*>(&h);
+            }
+            ol[0] *= corr; ol[1] *= corr;
+#pragma unroll
+            for (int u = 0; u < BPL; u++) { o[u][0] *= corr; o[u][1] *= corr; }
         }
-        ol[0] *= corr; ol[1] *= corr;
-#pragma unroll
-        for (int u = 0; u < BPL; u++) { o[u][0] *= corr; o[u][1] *= corr; }
         // ---- O += P . V (and the denominator through a tile of ones)
 #pragma unroll
         for (int j = 0; j < 2; j++) {
+            if (NST > 0) {
+#pragma unroll
+                for (int h = 0; h < 4; h++) {
+                    const uint4 w = *reinterpret_cast<const uint4*>(stage + 4096 + (16 * j + 2 * t + (h & 1) + 8 * (h >> 1)) * 128 + ((g ^ (2 * t)) << 4));
+                    vw[j][h][0] = w.x; vw[j][h][1] = w.y; vw[j][h][VW - 2] = w.z; vw[j][h][VW - 1] = w.w;
+                }
+            }
             mma16816_f16(ol[0], ol[1], z[j][0], z[j][1], pa[2 * j], pa[2 * j + 1], 0x3c003c00u, 0x3c003c00u);
 #pragma unroll
             for (int q = 0; q < VW; q++) {
@@ -171,16 +264,22 @@ sdp_fp8_decode_mma_kernel(const SdpArgs A) {
                 }
             }
         }
+        if (NST > 0) {
+            __syncwarp();                             // the stage is refilled by the next iteration's cp.async
+            if (++slot == NST) slot = 0;
+        }
     }
     // ---- combine the warps (m, l, o) in a fixed order; the accumulator columns go back to their places
     // (each lane owns runs of BPL consecutive columns; for D = 128 the 16-byte pieces of a run are XOR-swizzled
     // by t and rows are padded by 16 floats so that the float4 stores of a quarter warp cover all 32 banks)
+    if (NST > 0) { asm volatile("cp.async.wait_group 0;" ::: "memory"); __syncwarp(); }
+    auto red_o = [&](int w) -> float* { return NST > 0 ? reinterpret_cast<float*>(sdp_ring + w * (NST * 8192)) : red_o_static + w * RO; };
     if (t == 0) { red_m[warp][g] = m_run; red_l[warp][g] = ol[0]; }
 #pragma unroll
     for (int i = 0; i < 2; i++)
 #pragma unroll
         for (int q = 0; q < VW; q++)
-            *reinterpret_cast<float4*>(&red_o[warp][g][BPL * (2 * t + i) + 4 * (D == 128 ? (q ^ t) : q)]) =
+            *reinterpret_cast<float4*>(red_o(warp) + g * (D + 16) + BPL * (2 * t + i) + 4 * (D == 128 ? (q ^ t) : q)) =
                 make_float4(o[4 * q][i], o[4 * q + 1][i], o[4 * q + 2][i], o[4 * q + 3][i]);
     __syncthreads();
     float* part = A.part + ((((int64_t)b * A.Hkv + hkv) * gridDim.z + tile) * A.n_split + split) * (A.rt * (D + 2));
@@ -194,7 +293,7 @@ sdp_fp8_decode_mma_kernel(const SdpArgs A) {
 #pragma unroll
         for (int w = 0; w < SDP_WARPS; w++) {
             const float f = (red_m[w][r] == -CUDART_INF_F) ? 0.0f : exp2f(red_m[w][r] - M);
-            acc = fmaf(red_o[w][r][pos], f, acc);
+            acc = fmaf(red_o(w)[r * (D + 16) + pos], f, acc);
             lsum = fmaf(red_l[w][r], f, lsum);
         }
         part[r * (D + 2) + 2 + d] = acc;
