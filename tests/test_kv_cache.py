@@ -143,3 +143,48 @@ def test_prefill_falls_back_to_restored_cache(kv, cuda_device):
     out = kv.scaled_dot_product_attention(q, k_u8, v_u8, None, True)
     want = ref_attention(q, k_u8, v_u8, None, 1 / math.sqrt(D), True)
     assert float((out.double() - want).abs().max()) <= 2e-3 * float(want.abs().max())
+
+
+def test_sdp_fp8_growing_scores_and_long_cache(kv, cuda_device):
+    """keys whose scores keep growing along the cache (the running reference of the softmax is moved many times,
+    by small and by large steps) and a cache long enough for several chunks per warp and several splits"""
+    gen = torch.Generator(device=cuda_device).manual_seed(21)
+    B, Hq, Hkv, S, L, D = 1, 8, 2, 1, 9000, 128
+    q = torch.randn(B, Hq, S, D, device=cuda_device, generator=gen).half()
+    ramp = torch.linspace(0.05, 3.0, L, device=cuda_device)[None, None, :, None]
+    k = torch.randn(B, Hkv, L, D, device=cuda_device, generator=gen) * ramp
+    k[:, :, 5000] *= 4.0                               # one key far above the rest
+    v = torch.randn(B, Hkv, L, D, device=cuda_device, generator=gen)
+    cache = kv.DynamicFp8Cache()
+    k_u8, v_u8 = cache.update(k.half(), v.half(), 0)
+    for scale in (1 / math.sqrt(D), 1.0):
+        out = kv.scaled_dot_product_attention(q, k_u8, v_u8, None, False, scale)
+        want = ref_attention(q, k_u8, v_u8, None, scale, False)
+        assert float((out.double() - want).abs().max()) <= 1e-3 * float(want.abs().max()) + 1e-6
+
+
+def test_sdp_fp8_strided_and_misaligned_caches(kv, cuda_device):
+    """rows that are not densely stored (row stride 160 bytes: the staged copies take their general path) and a value
+    cache that is only 4-byte aligned (falls back to the CUDA-core kernel): same results as the dense cache"""
+    gen = torch.Generator(device=cuda_device).manual_seed(22)
+    B, Hq, Hkv, S, L, D = 2, 8, 2, 2, 700, 128
+    q = torch.randn(B, Hq, S, D, device=cuda_device, generator=gen).half()
+    cache = kv.DynamicFp8Cache()
+    k_u8, v_u8 = cache.update(torch.randn(B, Hkv, L, D, device=cuda_device, generator=gen).half(),
+                              torch.randn(B, Hkv, L, D, device=cuda_device, generator=gen).half(), 0)
+    scale = 1 / math.sqrt(D)
+    dense = kv.sdp_fp8(q, k_u8, v_u8, None, scale, True)
+    want = ref_attention(q, k_u8, v_u8, None, scale, True)
+    assert float((dense.double() - want).abs().max()) <= 1e-3 * float(want.abs().max()) + 1e-6
+    wide_k = torch.zeros(B, Hkv, L, 160, dtype=torch.uint8, device=cuda_device)
+    wide_v = torch.zeros(B, Hkv, L, 160, dtype=torch.uint8, device=cuda_device)
+    wide_k[..., :D] = k_u8
+    wide_v[..., :D] = v_u8
+    strided = kv.sdp_fp8(q, wide_k[..., :D], wide_v[..., :D], None, scale, True)
+    assert torch.equal(strided, dense)                 # same kernel, same order of operations
+    wide_v[..., 4:4 + D] = v_u8
+    shifted = kv.sdp_fp8(q, wide_k[..., :D], wide_v[..., 4:4 + D], None, scale, True)
+    assert float((shifted.double() - want).abs().max()) <= 1e-3 * float(want.abs().max()) + 1e-6
+    # a query that is a strided view (heads and tokens transposed, as decoders produce it)
+    q_t = q.transpose(1, 2).contiguous().transpose(1, 2)
+    assert torch.equal(kv.sdp_fp8(q_t, k_u8, v_u8, None, scale, True), dense)
