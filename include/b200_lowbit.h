@@ -117,6 +117,19 @@ int lowbit_kv_quantize_cuda(const void* d_src, int src_dtype, const int64_t* src
                             const int64_t* dst_strides, int64_t B, int64_t H, int64_t S, int64_t D, void* stream);
 int lowbit_kv_dequantize_cuda(const void* d_src, const int64_t* src_strides, void* d_dst, int dst_dtype,
                               const int64_t* dst_strides, int64_t B, int64_t H, int64_t S, int64_t D, void* stream);
+/* In-place rotary position embedding of the q and k heads of the merged qkv projection --
+ * xe_addons.rotary_half_inplaced / rotary_two_inplaced(inv_freq, position_ids, q, k) (models/llama.py:151-159,
+ * models/chatglm2.py:251) and rotary_half_with_cache_inplaced / rotary_two_with_cache_inplaced(q, k, cos, sin
+ * [, half_layout]) (models/common.py:354-367).  q [B][Hq][S][D], k [B][Hkv][S][D] (NULL: q only), same dtype,
+ * D contiguous, strides in elements.  R = rotary width (even, <= D; elements beyond stay).  two = 0 pairs element i
+ * with i + R/2, two != 0 pairs 2i with 2i + 1.  Angles: d_inv_freq (fp32 [R/2]) x d_position_ids (int64 [B][S],
+ * pos_strides = {batch, token}, batch stride 0 broadcasts) when d_inv_freq != NULL, else the tables d_cos / d_sin
+ * (cs_dtype, cs_strides = {batch, token}, last dimension contiguous; pair i reads entry i, or 2i when
+ * cs_interleaved != 0).  fp32 arithmetic, one rounding to the tensors' dtype. */
+int lowbit_rotary_inplaced_cuda(void* d_q, const int64_t* q_strides, int Hq, void* d_k, const int64_t* k_strides, int Hkv,
+                                int dtype, int B, int S, int D, int R, int two, const float* d_inv_freq,
+                                const int64_t* d_position_ids, const int64_t* pos_strides, const void* d_cos,
+                                const void* d_sin, int cs_dtype, const int64_t* cs_strides, int cs_interleaved, void* stream);
 /* Decode attention over the FP8 cache -- xe_addons.sdp_fp8(query, key, value, mask, scale)
  * (models/common.py:279-283: key.dtype == uint8, seq_length <= 32).  q [B][Hq][S][D] (q_dtype), k / v uint8
  * [B][Hkv][L][D] (GQA: Hq a multiple of Hkv), mask NULL or additive [B][1|Hq][S][L] (mask_strides[1] = 0

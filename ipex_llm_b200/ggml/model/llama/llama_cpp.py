@@ -353,3 +353,29 @@ _llama_initialized = False
 if not _llama_initialized:
     llama_init_backend()
     _llama_initialized = True
+
+
+_lib.lowbit_rotary_inplaced_cuda.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_int64), ctypes.c_int, ctypes.c_void_p,
+                                             ctypes.POINTER(ctypes.c_int64), ctypes.c_int, ctypes.c_int, ctypes.c_int,
+                                             ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_void_p,
+                                             ctypes.c_void_p, ctypes.POINTER(ctypes.c_int64), ctypes.c_void_p, ctypes.c_void_p,
+                                             ctypes.c_int, ctypes.POINTER(ctypes.c_int64), ctypes.c_int, ctypes.c_void_p]
+_lib.lowbit_rotary_inplaced_cuda.restype = ctypes.c_int
+
+
+def lowbit_rotary_inplaced(q, k, rotary_dim, two, inv_freq, position_ids, cos, sin, cs_interleaved, stream):
+    """q [B,Hq,S,D], k [B,Hkv,S,D] or None (views with D contiguous), rotated in place"""
+    B, Hq, S, D = q.shape
+    pos_strides = cs_strides = None
+    if inv_freq is not None:
+        pos_strides = (ctypes.c_int64 * 2)(position_ids.stride(0) if position_ids.shape[0] > 1 else 0, position_ids.stride(1))
+    else:
+        cs_strides = (ctypes.c_int64 * 2)(cos.stride(0) if cos.shape[0] > 1 else 0, cos.stride(1))
+    _check(_lib.lowbit_rotary_inplaced_cuda(q.data_ptr(), _strides3(q), Hq, k.data_ptr() if k is not None else None,
+                                            _strides3(k) if k is not None else None, k.shape[1] if k is not None else 0,
+                                            _DT_OF[str(q.dtype)], B, S, D, rotary_dim, int(bool(two)),
+                                            inv_freq.data_ptr() if inv_freq is not None else None,
+                                            position_ids.data_ptr() if inv_freq is not None else None, pos_strides,
+                                            cos.data_ptr() if cos is not None else None, sin.data_ptr() if sin is not None else None,
+                                            _DT_OF[str(cos.dtype)] if cos is not None else 0, cs_strides, int(bool(cs_interleaved)),
+                                            stream), "lowbit_rotary_inplaced_cuda")
