@@ -117,6 +117,24 @@ int lowbit_kv_quantize_cuda(const void* d_src, int src_dtype, const int64_t* src
                             const int64_t* dst_strides, int64_t B, int64_t H, int64_t S, int64_t D, void* stream);
 int lowbit_kv_dequantize_cuda(const void* d_src, const int64_t* src_strides, void* d_dst, int dst_dtype,
                               const int64_t* dst_strides, int64_t B, int64_t H, int64_t S, int64_t D, void* stream);
+/* All-reduce(sum) of the [M, hidden] results of the row-parallel linears in tensor-parallel decode -- the
+ * torch.distributed / DeepSpeed all_reduce of low_bit_linear.py:715-725 (after o_proj and down_proj), for one process
+ * per GPU on one node.  Every rank creates one buffer (lowbit_comm_create: device memory + a 64-byte IPC handle),
+ * the handles are exchanged by the host (torch.distributed all_gather), every rank maps the peers' buffers
+ * (lowbit_comm_open) and passes the world's pointers, own buffer at [rank], to every call.  The kernel publishes this
+ * rank's vector in its own buffer, signals the peers, waits (bounded) for theirs and sums all of them in rank order
+ * with loads over NVLink: every rank gets the same bits.  n * sizeof(dtype) must be a multiple of 16 and at most
+ * max_bytes (<= lowbit_comm_max_bytes() = 1 MiB; larger tensors belong to NCCL); d_in == d_out is allowed.  Every
+ * rank issues the same sequence of calls.  Call counters live in device memory: a captured CUDA graph replays.
+ * lowbit_comm_status reports 1 after a wait ran into its bound (a peer did not call). */
+size_t lowbit_comm_max_bytes(void);
+int lowbit_comm_create(size_t max_bytes, void** d_buffer, void* ipc_handle_64);
+int lowbit_comm_open(const void* ipc_handle_64, void** d_peer);
+int lowbit_comm_close(void* d_peer);
+int lowbit_comm_destroy(void* d_buffer);
+int lowbit_comm_status(const void* d_buffer, int* status);
+int lowbit_allreduce_sum_cuda(void* const* peer_buffers, int rank, int world, size_t max_bytes, const void* d_in, void* d_out,
+                              int64_t n, int dtype, void* stream);
 /* In-place rotary position embedding of the q and k heads of the merged qkv projection --
  * xe_addons.rotary_half_inplaced / rotary_two_inplaced(inv_freq, position_ids, q, k) (models/llama.py:151-159,
  * models/chatglm2.py:251) and rotary_half_with_cache_inplaced / rotary_two_with_cache_inplaced(q, k, cos, sin

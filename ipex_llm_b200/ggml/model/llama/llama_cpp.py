@@ -379,3 +379,59 @@ def lowbit_rotary_inplaced(q, k, rotary_dim, two, inv_freq, position_ids, cos, s
                                             cos.data_ptr() if cos is not None else None, sin.data_ptr() if sin is not None else None,
                                             _DT_OF[str(cos.dtype)] if cos is not None else 0, cs_strides, int(bool(cs_interleaved)),
                                             stream), "lowbit_rotary_inplaced_cuda")
+
+
+# ---- peer-memory all-reduce (csrc/comm.cu)
+_lib.lowbit_comm_max_bytes.argtypes = []
+_lib.lowbit_comm_max_bytes.restype = ctypes.c_size_t
+_lib.lowbit_comm_create.argtypes = [ctypes.c_size_t, ctypes.POINTER(ctypes.c_void_p), ctypes.c_void_p]
+_lib.lowbit_comm_create.restype = ctypes.c_int
+_lib.lowbit_comm_open.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_void_p)]
+_lib.lowbit_comm_open.restype = ctypes.c_int
+_lib.lowbit_comm_close.argtypes = [ctypes.c_void_p]
+_lib.lowbit_comm_close.restype = ctypes.c_int
+_lib.lowbit_comm_destroy.argtypes = [ctypes.c_void_p]
+_lib.lowbit_comm_destroy.restype = ctypes.c_int
+_lib.lowbit_comm_status.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_int)]
+_lib.lowbit_comm_status.restype = ctypes.c_int
+_lib.lowbit_allreduce_sum_cuda.argtypes = [ctypes.POINTER(ctypes.c_void_p), ctypes.c_int, ctypes.c_int, ctypes.c_size_t,
+                                           ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_int, ctypes.c_void_p]
+_lib.lowbit_allreduce_sum_cuda.restype = ctypes.c_int
+
+
+def lowbit_comm_max_bytes():
+    return _lib.lowbit_comm_max_bytes()
+
+
+def lowbit_comm_create(max_bytes):
+    """-> (device pointer, 64-byte IPC handle) of this rank's buffer on the current device"""
+    ptr = ctypes.c_void_p()
+    handle = ctypes.create_string_buffer(64)
+    _check(_lib.lowbit_comm_create(max_bytes, ctypes.byref(ptr), handle), "lowbit_comm_create")
+    return ptr.value, handle.raw
+
+
+def lowbit_comm_open(handle):
+    ptr = ctypes.c_void_p()
+    _check(_lib.lowbit_comm_open(ctypes.create_string_buffer(handle, 64), ctypes.byref(ptr)), "lowbit_comm_open")
+    return ptr.value
+
+
+def lowbit_comm_close(ptr):
+    _check(_lib.lowbit_comm_close(ptr), "lowbit_comm_close")
+
+
+def lowbit_comm_destroy(ptr):
+    _check(_lib.lowbit_comm_destroy(ptr), "lowbit_comm_destroy")
+
+
+def lowbit_comm_status(ptr):
+    v = ctypes.c_int()
+    _check(_lib.lowbit_comm_status(ptr, ctypes.byref(v)), "lowbit_comm_status")
+    return v.value
+
+
+def lowbit_allreduce_sum(peer_ptrs, rank, max_bytes, src, dst, stream):
+    arr = (ctypes.c_void_p * len(peer_ptrs))(*peer_ptrs)
+    _check(_lib.lowbit_allreduce_sum_cuda(arr, rank, len(peer_ptrs), max_bytes, src.data_ptr(), dst.data_ptr(), src.numel(),
+                                          _DT_OF[str(src.dtype)], stream), "lowbit_allreduce_sum_cuda")

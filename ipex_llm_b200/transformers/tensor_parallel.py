@@ -93,3 +93,65 @@ def make_parallel_linear(packed, shape, qtype, mode, rank, world, mp_group=None,
     if device is not None:
         lin = lin.to(device)
     return lin
+
+
+class PeerAllReduce:
+    """``mp_group`` object for row-parallel ``LowBitLinear`` modules (their forward calls ``mp_group.all_reduce``,
+    low_bit_linear.py:715-717 in the reference): the sum over the ranks of one node is computed by this library's
+    kernel (csrc/comm.cu) from the peers' buffers over NVLink instead of by NCCL -- for the small vectors of decode
+    (M x hidden, tens of KiB) the cost is one launch and one NVLink round trip.  Tensors larger than
+    ``lowbit_comm_max_bytes()`` (prefill), or whose byte size is not a multiple of 16, go to
+    ``torch.distributed.all_reduce`` on ``group``.
+
+    One communicator (buffer + mapped peer buffers) is created per payload size on first use; creation is a
+    collective over ``group`` (handles travel by ``all_gather_object``), so every rank must reduce the same sizes in
+    the same order -- which tensor-parallel decoding does.  Results are bit-identical on all ranks.
+    """
+
+    def __init__(self, group=None, device=None):
+        import torch.distributed as dist
+        self.group = group
+        self.rank = dist.get_rank(group)
+        self.world = dist.get_world_size(group)
+        self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        invalidInputError(self.world <= 8, "PeerAllReduce serves the GPUs of one node (world size <= 8)")
+        self._comms = {}                               # payload bytes -> (own pointer, [peer pointers])
+
+    def _comm(self, nbytes):
+        import torch.distributed as dist
+        c = self._comms.get(nbytes)
+        if c is None:
+            with torch.cuda.device(self.device):
+                own, handle = ggml.lowbit_comm_create(nbytes)
+                handles = [None] * self.world
+                dist.all_gather_object(handles, handle, group=self.group)
+                peers = [own if r == self.rank else ggml.lowbit_comm_open(handles[r]) for r in range(self.world)]
+            dist.barrier(group=self.group)             # every rank has mapped every buffer before the first use
+            c = (own, peers)
+            self._comms[nbytes] = c
+        return c
+
+    def all_reduce(self, tensor):
+        import torch.distributed as dist
+        nbytes = tensor.numel() * tensor.element_size()
+        if (self.world == 1 or not tensor.is_cuda or nbytes % 16 or nbytes > ggml.lowbit_comm_max_bytes() or not tensor.is_contiguous()
+                or tensor.dtype not in (torch.float32, torch.float16, torch.bfloat16) or tensor.data_ptr() % 16):
+            if self.world > 1:
+                dist.all_reduce(tensor, group=self.group)
+            return tensor
+        own, peers = self._comm(nbytes)
+        with torch.cuda.device(tensor.device):
+            ggml.lowbit_allreduce_sum(peers, self.rank, nbytes, tensor, tensor, torch.cuda.current_stream(tensor.device).cuda_stream)
+        return tensor
+
+    def timed_out(self):
+        """True if a wait inside a kernel ran into its bound (a peer did not take part).  Synchronises the device."""
+        return any(ggml.lowbit_comm_status(own) for own, _ in self._comms.values())
+
+    def close(self):
+        for own, peers in self._comms.values():
+            for r, p in enumerate(peers):
+                if r != self.rank:
+                    ggml.lowbit_comm_close(p)
+            ggml.lowbit_comm_destroy(own)
+        self._comms = {}
