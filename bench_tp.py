@@ -28,6 +28,8 @@ def main():
     ap.add_argument("--no-allreduce", action="store_true", help="skip the collectives (shows their cost)")
     ap.add_argument("--no-graph", action="store_true", help="eager launches (no CUDA graph)")
     ap.add_argument("--pdl", type=int, default=1)
+    ap.add_argument("--allreduce", choices=["peer", "nccl"], default="peer",
+                    help="peer: the library's one-shot kernel over IPC-mapped peer buffers (graph-capturable); nccl: torch.distributed")
     args = ap.parse_args()
     import torch
     import torch.distributed as dist
@@ -65,9 +67,17 @@ def main():
     hid = torch.empty(1, HIDDEN, device=dev, dtype=torch.float16)
     logits = torch.empty(1, VOCAB, device=dev, dtype=torch.float16)
 
+    peer = None
+    if world > 1 and not args.no_allreduce and args.allreduce == "peer":
+        from ipex_llm_b200.transformers.tensor_parallel import PeerAllReduce
+        peer = PeerAllReduce()
+
     def allreduce(t):
         if world > 1 and not args.no_allreduce:
-            dist.all_reduce(t)
+            if peer is not None:
+                peer.all_reduce(t)
+            else:
+                dist.all_reduce(t)
 
     def step():
         for L in layers:
@@ -92,7 +102,7 @@ def main():
         log("eager steps done")
         # torch's ProcessGroupNCCL collectives hung under CUDA-graph capture on the gpurun box (round 1, unresolved):
         # with collectives the step is launched eagerly (launch-bound: the number is a lower bound)
-        if not args.no_graph and (world == 1 or args.no_allreduce):
+        if not args.no_graph and (world == 1 or args.no_allreduce or peer is not None):
             graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(graph, stream=stream, capture_error_mode="thread_local"):
                 step()
@@ -100,10 +110,10 @@ def main():
     torch.cuda.synchronize()
 
     def replay():
-        if graph is not None:
-            graph.replay()
-        else:
-            with torch.cuda.stream(stream):
+        with torch.cuda.stream(stream):                # the events below are recorded on this stream
+            if graph is not None:
+                graph.replay()
+            else:
                 step()
 
     def barrier():
@@ -131,12 +141,15 @@ def main():
         print(json.dumps({
             "metric": "sym_int4 decode tok/s (Llama-2-70B LowBitLinear stream, bs1, tensor parallel)",
             "value": 1e3 / ms_step, "unit": "tok/s", "n_gpus": world, "steps": args.steps, "ms_per_step": ms_step,
-            "scaling": "strong", "layers": args.layers, "allreduce": not args.no_allreduce, "cuda_graph": graph is not None,
+            "scaling": "strong", "layers": args.layers, "allreduce": (args.allreduce if world > 1 and not args.no_allreduce else None), "cuda_graph": graph is not None,
             "collectives_per_step": 0 if (world == 1 or args.no_allreduce) else 2 * args.layers,
             "packed_bytes_per_rank": bytes_per_rank,
             "per_rank_GBps": bytes_per_rank / (ms_step * 1e-3) / 1e9,
-            "config": {"workload": "Llama-2-70B sym_int4 bs1 decode, LowBitLinear stream, column/row sharded, NCCL all-reduce "
+            "config": {"workload": "Llama-2-70B sym_int4 bs1 decode, LowBitLinear stream, column/row sharded, all-reduce "
                                    "of [1, 8192] fp16 after o_proj and down_proj", "parallelism": f"tp{world}"}}))
+    if peer is not None:
+        assert not peer.timed_out()
+        peer.close()
     if world > 1:
         dist.destroy_process_group()
 

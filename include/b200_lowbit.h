@@ -121,12 +121,13 @@ int lowbit_kv_dequantize_cuda(const void* d_src, const int64_t* src_strides, voi
  * torch.distributed / DeepSpeed all_reduce of low_bit_linear.py:715-725 (after o_proj and down_proj), for one process
  * per GPU on one node.  Every rank creates one buffer (lowbit_comm_create: device memory + a 64-byte IPC handle),
  * the handles are exchanged by the host (torch.distributed all_gather), every rank maps the peers' buffers
- * (lowbit_comm_open) and passes the world's pointers, own buffer at [rank], to every call.  The kernel publishes this
- * rank's vector in its own buffer, signals the peers, waits (bounded) for theirs and sums all of them in rank order
- * with loads over NVLink: every rank gets the same bits.  n * sizeof(dtype) must be a multiple of 16 and at most
- * max_bytes (<= lowbit_comm_max_bytes() = 1 MiB; larger tensors belong to NCCL); d_in == d_out is allowed.  Every
- * rank issues the same sequence of calls.  Call counters live in device memory: a captured CUDA graph replays.
- * lowbit_comm_status reports 1 after a wait ran into its bound (a peer did not call). */
+ * (lowbit_comm_open) and passes the world's pointers, own buffer at [rank], to every call.  The kernel writes this
+ * rank's vector into its inbox in every peer's buffer (8-byte stores over NVLink carrying 4 bytes of data and the call
+ * number), polls (bounded) its own inboxes for the peers' words and sums all vectors in rank order: every rank gets the
+ * same bits.  n * sizeof(dtype) must be a multiple of 16 and at most max_bytes (<= lowbit_comm_max_bytes() = 256 KiB:
+ * decode-sized vectors; larger tensors belong to NCCL); d_in == d_out is allowed.  Every rank issues the same sequence
+ * of calls.  Call counters live in device memory: a captured CUDA graph replays.  lowbit_comm_status reports 1 after a
+ * wait ran into its bound (a peer did not call). */
 size_t lowbit_comm_max_bytes(void);
 int lowbit_comm_create(size_t max_bytes, void** d_buffer, void* ipc_handle_64);
 int lowbit_comm_open(const void* ipc_handle_64, void** d_peer);

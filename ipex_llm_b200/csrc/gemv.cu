@@ -88,6 +88,7 @@ static thread_local unsigned long long t_next_bytes = 0;
 void gemv_set_next_weights(const void* w, size_t bytes) { t_next_w = (const uint8_t*)w; t_next_bytes = bytes; }
 static int g_pdl = 0;     // programmatic dependent launch for the GEMV kernels (set by the host engine)
 void gemv_set_pdl(int on) { g_pdl = on ? 1 : 0; }
+int gemv_get_pdl() { return g_pdl; }
 
 // The only scratch the matmul needs: three bf16 planes of an fp32 activation chunk.
 size_t gemv_workspace_size(int64_t n_rows, int64_t k, int64_t m, int x_dtype) {

@@ -98,8 +98,8 @@ def make_parallel_linear(packed, shape, qtype, mode, rank, world, mp_group=None,
 class PeerAllReduce:
     """``mp_group`` object for row-parallel ``LowBitLinear`` modules (their forward calls ``mp_group.all_reduce``,
     low_bit_linear.py:715-717 in the reference): the sum over the ranks of one node is computed by this library's
-    kernel (csrc/comm.cu) from the peers' buffers over NVLink instead of by NCCL -- for the small vectors of decode
-    (M x hidden, tens of KiB) the cost is one launch and one NVLink round trip.  Tensors larger than
+    kernel (csrc/comm.cu), which pushes every rank's vector into the peers' buffers over NVLink, instead of by NCCL -- for
+    the small vectors of decode (M x hidden, tens of KiB) the cost is one launch and one NVLink crossing.  Tensors larger than
     ``lowbit_comm_max_bytes()`` (prefill), or whose byte size is not a multiple of 16, go to
     ``torch.distributed.all_reduce`` on ``group``.
 
