@@ -1,6 +1,6 @@
 """The library's own all-reduce for tensor-parallel decode (csrc/comm.cu; the reference calls
-torch.distributed / DeepSpeed all_reduce at low_bit_linear.py:715-725).  Two ranks, one process per GPU: needs a
-box with at least 2 GPUs (skipped otherwise).  Expected values are the rank-ordered fp32 sums, rounded once to the
+torch.distributed / DeepSpeed all_reduce at low_bit_linear.py:715-725).  2, 4 and 8 ranks, one process per GPU
+(each case is skipped on a box with fewer GPUs).  Expected values are the rank-ordered fp32 sums, rounded once to the
 tensor's dtype: the kernel must match them bit for bit, on every rank.
 """
 import os
@@ -100,10 +100,10 @@ def _worker(rank, world, port, out):
         dist.destroy_process_group()
 
 
-def test_peer_allreduce_two_ranks(native_lib):
-    if torch.cuda.device_count() < 2:
-        pytest.skip("needs 2 GPUs")
-    world = 2
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_peer_allreduce_ranks(native_lib, world):
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
     ctx = mp.get_context("spawn")
     out = ctx.Manager().dict()
     port = _free_port()
