@@ -159,11 +159,12 @@ int lowbit_relayout_cuda(const void* d_src, void* d_dst, int64_t rows, int64_t k
 }
 
 static bool use_gemm(int qtype, int64_t n_rows, int64_t k, int64_t m) {
-    return m > kGemvMaxM && gemm_tc_supported(qtype, n_rows, k);
+    static const int64_t max_m = [] { const char* e = getenv("LOWBIT_GEMV_MAX_M"); return e ? (int64_t)atoi(e) : kGemvMaxM; }();   // development
+    return m > max_m && gemm_tc_supported(qtype, n_rows, k);
 }
 
 size_t lowbit_matmul_workspace_size(int64_t n_rows, int64_t k, int64_t m, int x_dtype) {
-    if (use_gemm(B200_QT_SYM_INT4, n_rows, k, m)) return gemm_tc_workspace_size(k, m, x_dtype);
+    if (use_gemm(B200_QT_SYM_INT4, n_rows, k, m)) return gemm_tc_workspace_size(n_rows, k, m, x_dtype);
     return gemv_workspace_size(n_rows, k, m, x_dtype);
 }
 

@@ -228,6 +228,8 @@ struct GemmArgs {
     void* y; int y_dtype;
     const void* bias;
     int accumulate;
+    int ksplit;              // K splits per output tile (1: the epilogue writes y)
+    float* part;             // ksplit > 1: fp32 partial sums [ksplit][M][N]
 };
 
 template <int QT> struct Smem {
@@ -294,7 +296,7 @@ __device__ __forceinline__ void store_vals(const GemmArgs& A, int64_t token, int
 }
 
 // grid = (N / 128 feature tiles, ceil(M / (128*MT)) token tiles)
-// Persistent: grid = min(tiles, SMs) CTAs; CTA c takes tiles c, c + grid, ... in token-tile-major order (the
+// Persistent: grid = min(units, SMs) CTAs; CTA c takes units c, c + grid, ... in token-tile-major order (the
 // CTAs running at one moment share the token tile's activations in L2 and stream different weights).
 // Warp roles: 0 TMA producer, 1 MMA issuer (owns TMEM), 2..9 dequant, 10..13 epilogue.  The accumulators
 // are double buffered in TMEM (2 x 128*MT columns), so the epilogue of tile i overlaps the main loop of i+1.
@@ -322,6 +324,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap xmap, const GemmArgs A) {
     const int nb = (int)A.G.nb;
     const int n_ftiles = (int)(A.G.rows / kTileN);
     const int n_tiles = n_ftiles * ((A.M + 128 * MT - 1) / (128 * MT));
+    // work units = tiles x K splits (A.ksplit > 1 when the tiles alone would leave most SMs idle); split ks covers the
+    // k-blocks [kb_begin(ks), kb_begin(ks + 1))
+    const int n_units = n_tiles * A.ksplit;
+    auto kb_begin = [&](int ks) { return A.ksplit == 1 ? ks * nb : (ks * nb) / A.ksplit; };      // ks * nb < 2^31
     constexpr uint32_t ACC_COLS = 128 * MT;            // one accumulator buffer
     constexpr uint32_t TMEM_COLS = 2 * ACC_COLS;       // 256 or 512 (powers of two)
 
@@ -344,10 +350,12 @@ gemm_kernel(const __grid_constant__ CUtensorMap xmap, const GemmArgs A) {
         // ================= producer =================
         if (lane == 0) {
             int it = 0;                                              // k-iterations issued so far (all tiles)
-            for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+            for (int unit = blockIdx.x; unit < n_units; unit += gridDim.x) {
+                const int tile = unit % n_tiles, ks = unit / n_tiles;
                 const int ftile = tile % n_ftiles, m0 = (tile / n_ftiles) * (128 * MT);
                 const int64_t rg0 = (int64_t)ftile * 2;
-                for (int kb = 0; kb < nb; kb++, it++) {
+                const int kb1 = kb_begin(ks + 1);
+                for (int kb = kb_begin(ks); kb < kb1; kb++, it++) {
                     const int s = it % kStages, round = it / kStages;
                     mbar_wait(empty_bar(s), (uint32_t)((round & 1) ^ 1));
                     const uint32_t st = base + s * STAGE;
@@ -372,12 +380,13 @@ gemm_kernel(const __grid_constant__ CUtensorMap xmap, const GemmArgs A) {
             // c_format F32 (1<<4), a/b format (0 f16, 1 bf16), both K-major, N = 128 (>>3 at bit 17), M = 128 (>>4 at bit 24)
             const uint32_t idesc = (1u << 4) | ((BF ? 1u : 0u) << 7) | ((BF ? 1u : 0u) << 10) | ((128u >> 3) << 17) | ((128u >> 4) << 24);
             int it = 0, ti = 0;
-            for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ti++) {
+            for (int unit = blockIdx.x; unit < n_units; unit += gridDim.x, ti++) {
                 const int buf = ti & 1;
                 mbar_wait(tmem_empty(buf), (uint32_t)(((ti >> 1) & 1) ^ 1));      // the epilogue has drained this buffer
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 const uint32_t acc = tmem_base + buf * ACC_COLS;
-                for (int kb = 0; kb < nb; kb++, it++) {
+                const int kb0 = kb_begin(unit / n_tiles), kb1 = kb_begin(unit / n_tiles + 1);
+                for (int kb = kb0; kb < kb1; kb++, it++) {
                     const int s = it % kStages, round = it / kStages;
                     mbar_wait(full_bar(s), (uint32_t)(round & 1));
                     mbar_wait(deq_bar(s), (uint32_t)(round & 1));
@@ -390,7 +399,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap xmap, const GemmArgs A) {
                         for (int k4 = 0; k4 < 4; k4++) {
                             const uint64_t ad = make_desc(st + mt * kTileBytesAB + k4 * 32);
                             const uint64_t bd = make_desc(btile + k4 * 32);
-                            umma_f16(acc + mt * 128, ad, bd, idesc, (kb > 0 || k4 > 0) ? 1u : 0u);
+                            umma_f16(acc + mt * 128, ad, bd, idesc, (kb > kb0 || k4 > 0) ? 1u : 0u);
                         }
                     }
                     umma_commit(empty_bar(s));                  // stage reusable once these MMAs have read it
@@ -404,8 +413,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap xmap, const GemmArgs A) {
         const int gi = (warp - 2) >> 2;
         const int g = lane >> 2, t = lane & 3;
         int it = 0;
-        for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-            for (int kb = 0; kb < nb; kb++, it++) {
+        for (int unit = blockIdx.x; unit < n_units; unit += gridDim.x) {
+            const int kb0 = kb_begin(unit / n_tiles), kb1 = kb_begin(unit / n_tiles + 1);
+            for (int kb = kb0; kb < kb1; kb++, it++) {
                 const int s = it % kStages, round = it / kStages;
                 mbar_wait(full_bar(s), (uint32_t)(round & 1));
                 const uint32_t st = base + s * STAGE;
@@ -444,7 +454,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap xmap, const GemmArgs A) {
         // ================= epilogue warps: warp w may touch TMEM lanes 32*(w%4) .. +31 =================
         const int quarter = warp & 3;
         int ti = 0;
-        for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ti++) {
+        for (int unit = blockIdx.x; unit < n_units; unit += gridDim.x, ti++) {
+            const int tile = unit % n_tiles, ks = unit / n_tiles;
             const int ftile = tile % n_ftiles, m0 = (tile / n_ftiles) * (128 * MT);
             const int buf = ti & 1;
             mbar_wait(tmem_full(buf), (uint32_t)((ti >> 1) & 1));
@@ -456,7 +467,13 @@ gemm_kernel(const __grid_constant__ CUtensorMap xmap, const GemmArgs A) {
                 for (int c = 0; c < 128; c += 32) {
                     float v[32];
                     tmem_ld32(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(buf * ACC_COLS + mt * 128 + c), v);
-                    if (token < A.M) store_vals(A, token, (int64_t)ftile * kTileN + c, v);
+                    if (token < A.M) {
+                        if (A.ksplit > 1) {             // K split: fp32 partial sums, added up by reduce_partials_kernel
+                            float4* pp = reinterpret_cast<float4*>(A.part + ((int64_t)ks * A.M + token) * A.G.rows + (int64_t)ftile * kTileN + c);
+#pragma unroll
+                            for (int i = 0; i < 8; i++) pp[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+                        } else store_vals(A, token, (int64_t)ftile * kTileN + c, v);
+                    }
                 }
             }
             asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -474,6 +491,28 @@ gemm_kernel(const __grid_constant__ CUtensorMap xmap, const GemmArgs A) {
 __global__ void f32_to_bf16_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ out, int64_t n) {
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
         out[i] = __float2bfloat16_rn(x[i]);
+}
+
+// K split: y[token][n] = sum over splits (in split order) of the fp32 partials, + bias, + y when accumulating
+__global__ void __launch_bounds__(256) reduce_partials_kernel(const float* __restrict__ part, int ksplit, int64_t mn, int64_t n_cols,
+                                                              void* y, int y_dtype, const void* bias, int accumulate) {
+    for (int64_t i = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) * 4; i < mn; i += (int64_t)gridDim.x * blockDim.x * 4) {
+        float4 a = *reinterpret_cast<const float4*>(part + i);
+        for (int ks = 1; ks < ksplit; ks++) {
+            const float4 b = *reinterpret_cast<const float4*>(part + ks * mn + i);
+            a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+        }
+        float v[4] = {a.x, a.y, a.z, a.w};
+        const int64_t col = i % n_cols;                           // n_cols % 128 == 0: the four values share a row
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            if (bias) v[j] += y_dtype == DT_F32 ? ((const float*)bias)[col + j]
+                            : (y_dtype == DT_F16 ? __half2float(((const __half*)bias)[col + j]) : __bfloat162float(((const __nv_bfloat16*)bias)[col + j]));
+            if (y_dtype == DT_F32) { float* p = (float*)y + i + j; *p = accumulate ? *p + v[j] : v[j]; }
+            else if (y_dtype == DT_F16) { __half* p = (__half*)y + i + j; *p = __float2half_rn(accumulate ? __half2float(*p) + v[j] : v[j]); }
+            else { __nv_bfloat16* p = (__nv_bfloat16*)y + i + j; *p = __float2bfloat16_rn(accumulate ? __bfloat162float(*p) + v[j] : v[j]); }
+        }
+    }
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
@@ -521,8 +560,32 @@ bool gemm_tc_supported(int qt, int64_t n_rows, int64_t k) {
     return q && n_rows >= 128 && (n_rows % 128) == 0 && k >= 64 && (k % 64) == 0;
 }
 
-size_t gemm_tc_workspace_size(int64_t k, int64_t m, int x_dtype) {
-    return x_dtype == DT_F32 ? (size_t)((m * k * 2 + 255) / 256 * 256) : 0;
+// K splits for one token tile (m <= 128) whose feature tiles alone leave SMs idle: the split count that minimises a
+// cost model in microseconds -- rounds of the grid x k-blocks per unit x 0.36 us (what one CTA's dequant warps need per
+// 128 x 64 block), plus, when split, the partial sums' round trip through memory at ~4 TB/s and the second launch.
+static int pick_ksplit(int64_t n_tiles, int64_t nb, int64_t m, int64_t n_main) {
+    static const int forced = [] { const char* e = getenv("LOWBIT_GEMM_KSPLIT"); return e ? atoi(e) : 0; }();   // development
+    const int64_t sms = sm_count();
+    const int64_t cap = nb < 16 ? nb : 16;
+    if (forced > 0) return (int)(forced < cap ? forced : cap);
+    if (n_tiles >= sms) return 1;
+    int best = 1; double best_cost = 1e30;
+    for (int64_t ks = 1; ks <= cap; ks++) {
+        const double rounds = (double)((n_tiles * ks + sms - 1) / sms);
+        double cost = rounds * (double)((nb + ks - 1) / ks) * 0.36;
+        if (ks > 1) cost += (double)ks * (double)m * (double)n_main * 8.0 / 4.0e6 + 2.0;
+        if (cost < best_cost - 1e-9) { best_cost = cost; best = (int)ks; }
+    }
+    return best;
+}
+
+static size_t x_convert_bytes(int64_t k, int64_t m, int x_dtype) { return x_dtype == DT_F32 ? (size_t)((m * k * 2 + 255) / 256 * 256) : 0; }
+
+size_t gemm_tc_workspace_size(int64_t n_rows, int64_t k, int64_t m, int x_dtype) {
+    const int64_t n_main = n_rows & ~int64_t(127);
+    const int64_t n_tiles = (n_main / 128) * ((m + 127) / 128);           // as gemm_tc_launch counts them for m <= 128
+    const int ks = m <= 128 ? pick_ksplit(n_tiles, k / 64, m, n_main) : 1;
+    return x_convert_bytes(k, m, x_dtype) + (ks > 1 ? (size_t)ks * m * n_main * sizeof(float) : 0);
 }
 
 // rows [0, n_main) with n_main = n_rows & ~127 are computed here; the caller handles the rest
@@ -539,7 +602,7 @@ int gemm_tc_launch(const void* w, int qt, int64_t n_rows, int64_t k, const void*
     const void* xa = x;
     bool bf = (x_dtype == DT_BF16);
     if (x_dtype == DT_F32) {
-        const size_t need = gemm_tc_workspace_size(k, m, x_dtype);
+        const size_t need = gemm_tc_workspace_size(n_rows, k, m, x_dtype);
         if (!workspace || workspace_bytes < need) return LB_ERR_WORKSPACE;
         const int64_t n = m * k;
         int sg = (int)((n + 255) / 256); if (sg > sm_count() * 16) sg = sm_count() * 16;
@@ -570,7 +633,15 @@ int gemm_tc_launch(const void* w, int qt, int64_t n_rows, int64_t k, const void*
         mt = 4 * t2 <= 5 * t1 ? 2 : 1;      // a 128-token tile re-reads the weights twice as often: ~25 % slower per token
     }
     const int64_t n_tiles = (n_main / 128) * ((m + 128 * mt - 1) / (128 * mt));
-    const dim3 grid((unsigned)(n_tiles < sm_count() ? n_tiles : sm_count()), 1, 1);       // persistent CTAs
+    A.ksplit = m <= 128 ? pick_ksplit(n_tiles, k / 64, m, n_main) : 1;      // one token tile: few output tiles
+    A.part = nullptr;
+    if (A.ksplit > 1) {
+        const size_t off = x_convert_bytes(k, m, x_dtype);
+        if (!workspace || workspace_bytes < off + (size_t)A.ksplit * m * n_main * sizeof(float)) return LB_ERR_WORKSPACE;
+        A.part = reinterpret_cast<float*>((uint8_t*)workspace + off);
+    }
+    const int64_t n_units = n_tiles * A.ksplit;
+    const dim3 grid((unsigned)(n_units < sm_count() ? n_units : sm_count()), 1, 1);       // persistent CTAs
     switch (qt) {
         case QT_SYM_INT4:  launch_qt<QT_SYM_INT4>(bf, mt, map, A, grid, st); break;
         case QT_NF4:       launch_qt<QT_NF4>(bf, mt, map, A, grid, st); break;
@@ -581,6 +652,12 @@ int gemm_tc_launch(const void* w, int qt, int64_t n_rows, int64_t k, const void*
         default: return LB_ERR_ARG;
     }
     note_launch();
+    if (A.ksplit > 1) {
+        const int64_t mn = m * n_main;
+        int rg = (int)((mn / 4 + 255) / 256); if (rg > sm_count() * 8) rg = sm_count() * 8;
+        reduce_partials_kernel<<<rg, 256, 0, st>>>(A.part, A.ksplit, mn, n_main, y, y_dtype, bias, accumulate);
+        note_launch();
+    }
     *n_done = n_main;
     return check_launch();
 }

@@ -73,7 +73,7 @@ int moe_launch(const MoeParams& P, cudaStream_t st);
 
 // gemm_tc.cu (tcgen05 prefill GEMM)
 bool gemm_tc_supported(int qt, int64_t n_rows, int64_t k);
-size_t gemm_tc_workspace_size(int64_t k, int64_t m, int x_dtype);
+size_t gemm_tc_workspace_size(int64_t n_rows, int64_t k, int64_t m, int x_dtype);
 int gemm_tc_launch(const void* w, int qt, int64_t n_rows, int64_t k, const void* x, int x_dtype, int64_t m, void* y,
                    int y_dtype, const void* bias, int accumulate, void* workspace, size_t workspace_bytes, cudaStream_t st,
                    int64_t* n_done);

@@ -355,6 +355,32 @@ def test_gemm_prefill_persistent_many_tiles(lbl, cuda_device):
     assert bool(((out.float() - want2).abs() <= bound + 2e-3 * want2.abs() + 1e-3).all())
 
 
+@pytest.mark.parametrize("shape,M,qtype", [((4096, 11008), 100, "asym_int4"), ((4096, 4096), 33, "sym_int4"), ((11008, 4096), 128, "fp8_e4m3"),
+                                           ((1024, 2048 + 64), 57, "nf4")])
+def test_gemm_small_batch_split_k(lbl, cuda_device, shape, M, qtype):
+    """one token tile and few feature tiles: the K range of every output tile is split over several CTAs (fp32
+    partial sums + a reduction launch); uneven splits (172 and 33 k-blocks), bias, accumulate, fp16 output"""
+    rng = np.random.default_rng(1400 + M)
+    N, K = shape
+    dev = cuda_device
+    w = torch.from_numpy(rand_w(rng, N, K)).to(dev)
+    tiled = lbl.FP4Params(w, qtype=qid(qtype)).to(dev).data
+    wd = lbl.dequantize_device_layout(tiled, (N, K), qid(qtype)).float()
+    x_t = torch.from_numpy(rng.standard_normal((M, K)).astype(np.float32)).half().to(dev)
+    y = lbl.lowbit_matmul(x_t, tiled, (N, K), qid(qtype), out_dtype=torch.float32)
+    if shape == (4096, 11008):
+        assert lbl.ggml.last_launch_count() == 2      # GEMM + reduction of the partial sums (other shapes: the cost model decides)
+    want = x_t.double() @ wd.double().T
+    bound = 1e-3 * (x_t.double().abs() @ wd.double().abs().T) + 1e-30
+    assert bool(((y.double() - want).abs() <= bound).all()), float(((y.double() - want).abs() / bound).max())
+    bias = torch.from_numpy(rng.standard_normal(N).astype(np.float32)).half().to(dev)
+    res = torch.from_numpy(rng.standard_normal((M, N)).astype(np.float32)).half().to(dev)
+    out = res.clone()
+    lbl.lowbit_matmul(x_t, tiled, (N, K), qid(qtype), out=out, bias=bias, accumulate=True)
+    want2 = y + bias.float() + res.float()
+    assert bool(((out.float() - want2).abs() <= 1e-3 * want2.abs() + 1e-3).all())
+
+
 def test_gemm_prefill_epilogue_and_module(lbl, cuda_device):
     rng = np.random.default_rng(1300)
     N, K, M = 256, 512, 96
