@@ -169,3 +169,50 @@ def test_config5_mixtral_moe_decode(lbl, cuda_device):
         mag += wts[0, z].double() * (h.abs() @ dd.abs().T)
     # one fp16 rounding of h may differ by an ulp (2^-11) where the fused value sits next to a rounding boundary
     assert bool(((out.double() - want).abs() <= 6e-4 * mag + 1e-9).all())
+
+
+def test_config5_mixtral_moe_tp_inside_experts(lbl, cuda_device):
+    """SURVEY 8e, MoE sharding (1): tensor parallelism inside every expert -- w1 / w3 column-sharded, w2 row-sharded
+    (14336 / 8 = 1792 = 28 blocks), the ranks' outputs summed by the same all-reduce as the dense layers.  Every
+    rank's fused one-token MoE is run on this one GPU; the sum over ranks must equal the unsharded MoE up to the
+    summation order and the fp16 rounding of the intermediate activations."""
+    from ipex_llm_b200.transformers import tensor_parallel as tpm
+    dev = cuda_device
+    q = qid("sym_int4")
+    hidden, inter, n_exp, top_k, tp = 4096, 14336, 4, 2, 8
+    gen = torch.Generator(device=dev).manual_seed(70)
+    packed = []                                          # canonical packed weights per expert: w1, w3 [inter, hidden], w2 [hidden, inter]
+    for e in range(n_exp):
+        ws = []
+        for shape in ((inter, hidden), (inter, hidden), (hidden, inter)):
+            w = torch.empty(shape, device=dev, dtype=torch.float32).normal_(0.0, 0.02, generator=gen)
+            ws.append(lbl.ggml_convert_qtype(w, q))
+            del w
+        packed.append(ws)
+    x = torch.randn(1, hidden, device=dev, generator=gen).half()
+    logits = torch.randn(1, n_exp, device=dev, generator=gen)
+    wts, ids = torch.topk(torch.softmax(logits, dim=-1), top_k, dim=-1)
+    wts = (wts / wts.sum(-1, keepdim=True)).half()
+
+    def run(shards, inter_local):
+        keep = [[lbl.ggml_q_format_convet_cpu2xpu(p, shp[0] * shp[1], q, shape=shp) for p, shp in ex] for ex in shards]
+        tabs = [torch.tensor([ex[i].data_ptr() for ex in keep], dtype=torch.uint64, device=dev) for i in range(3)]
+        assert lbl.use_fuse_moe(hidden, inter_local, top_k, q)
+        out = torch.empty((1, hidden), dtype=torch.float32, device=dev)
+        lbl.moe_forward_vec(x, ids, wts, tabs[0], tabs[1], tabs[2], hidden, inter_local, q, out=out)
+        torch.cuda.synchronize()
+        return out
+
+    full = run([[(p, s) for p, s in zip(ex, ((inter, hidden), (inter, hidden), (hidden, inter)))] for ex in packed], inter)
+    total = torch.zeros_like(full, dtype=torch.float64)
+    for rank in range(tp):
+        shards = []
+        for ex in packed:
+            g = tpm.shard_packed_column(ex[0], (inter, hidden), q, rank, tp)
+            u = tpm.shard_packed_column(ex[1], (inter, hidden), q, rank, tp)
+            d = tpm.shard_packed_row(ex[2], (hidden, inter), q, rank, tp)
+            shards.append([g, u, d])
+        assert shards[0][0][1] == (inter // tp, hidden) and shards[0][2][1] == (hidden, inter // tp)
+        total += run(shards, inter // tp).double()
+    scale = float(full.abs().max())
+    assert float((total - full.double()).abs().max()) <= 2e-3 * scale
