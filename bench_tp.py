@@ -28,8 +28,8 @@ def main():
     ap.add_argument("--no-allreduce", action="store_true", help="skip the collectives (shows their cost)")
     ap.add_argument("--no-graph", action="store_true", help="eager launches (no CUDA graph)")
     ap.add_argument("--pdl", type=int, default=1)
-    ap.add_argument("--allreduce", choices=["peer", "nccl"], default="peer",
-                    help="peer: the library's one-shot kernel over IPC-mapped peer buffers (graph-capturable); nccl: torch.distributed")
+    ap.add_argument("--allreduce", choices=["fused", "peer", "nccl"], default="fused",
+                    help="fused: the row-parallel GEMVs push their partial sums to the peers from their epilogue; peer: the library's one-shot kernel over IPC-mapped peer buffers (graph-capturable); nccl: torch.distributed")
     args = ap.parse_args()
     import torch
     import torch.distributed as dist
@@ -68,7 +68,7 @@ def main():
     logits = torch.empty(1, VOCAB, device=dev, dtype=torch.float16)
 
     peer = None
-    if world > 1 and not args.no_allreduce and args.allreduce == "peer":
+    if world > 1 and not args.no_allreduce and args.allreduce in ("peer", "fused"):
         from ipex_llm_b200.transformers.tensor_parallel import PeerAllReduce
         peer = PeerAllReduce()
 
@@ -79,14 +79,22 @@ def main():
             else:
                 dist.all_reduce(t)
 
+    fused = peer is not None and args.allreduce == "fused"
+
     def step():
         for L in layers:
             lbl.lowbit_matmul(x_h, L["qkv"], shapes["qkv"], qt, out=qkv_out)
-            lbl.lowbit_matmul(x_os, L["o"], shapes["o"], qt, out=hid)
-            allreduce(hid)
+            if fused:
+                peer.matmul_all_reduce(x_os, L["o"], shapes["o"], qt, out=hid)
+            else:
+                lbl.lowbit_matmul(x_os, L["o"], shapes["o"], qt, out=hid)
+                allreduce(hid)
             lbl.mlp_forward(x_h, L["gate"], L["up"], 1, HIDDEN, INTER // tp, lbl.SILU, qt, out=mlp_out)
-            lbl.lowbit_matmul(mlp_out, L["down"], shapes["down"], qt, out=hid)
-            allreduce(hid)
+            if fused:
+                peer.matmul_all_reduce(mlp_out, L["down"], shapes["down"], qt, out=hid)
+            else:
+                lbl.lowbit_matmul(mlp_out, L["down"], shapes["down"], qt, out=hid)
+                allreduce(hid)
         lbl.lowbit_matmul(x_h, lm_head, (VOCAB, HIDDEN), qt, out=logits)
 
     def log(msg):

@@ -28,6 +28,7 @@
 #include "../../include/b200_lowbit.h"
 #include "lowbit_common.cuh"
 #include "lowbit_internal.h"
+#include "gemv_args.h"
 
 namespace lowbit {
 namespace {
@@ -87,18 +88,22 @@ __global__ void __launch_bounds__(COMM_THREADS) allreduce_kernel(const CommArgs 
     uint8_t* own = A.peer[A.rank];
     uint32_t* epochs = reinterpret_cast<uint32_t*>(own);
     uint32_t* status = epochs + COMM_MAX_CTAS;
-    const uint32_t epoch = epochs[c] + 1;
-    const size_t slot_off = COMM_HEADER_BYTES + (epoch & 1) * (A.inbox_bytes * COMM_MAX_WORLD);
     const int64_t total_words = A.n * (DT == DT_F32 ? 4 : 2) / 4;
     const int64_t begin = (int64_t)c * (A.bytes_per_cta / 4);
     const int64_t end = begin + A.bytes_per_cta / 4 < total_words ? begin + A.bytes_per_cta / 4 : total_words;
     // Under programmatic dependent launch (lowbit_set_programmatic_dependent_launch): the next kernel of the stream
     // -- the following linear, which streams its weights before it looks at its input -- may start now; this grid
-    // itself waits here for the kernel that produces `in`.  Both are no-ops for ordinary launches.
+    // itself waits here for the kernel that produces `in`.  Both are no-ops for ordinary launches.  The call counter
+    // is read AFTER the wait: chains of early launches can start this grid before the previous call's grid has
+    // finished and advanced it.
     if (A.pdl) {
         asm volatile("griddepcontrol.launch_dependents;");
         asm volatile("griddepcontrol.wait;" ::: "memory");
     }
+    uint32_t epoch;
+    asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(epoch) : "l"(epochs + c) : "memory");
+    epoch += 1;
+    const size_t slot_off = COMM_HEADER_BYTES + (epoch & 1) * (A.inbox_bytes * COMM_MAX_WORLD);
     const uint32_t* in = reinterpret_cast<const uint32_t*>(A.in);
     uint32_t* out = reinterpret_cast<uint32_t*>(A.out);
     bool expired = false;
@@ -142,6 +147,85 @@ __global__ void __launch_bounds__(COMM_THREADS) allreduce_kernel(const CommArgs 
     }
     if (expired) atomicExch(status, 1u);
     // every thread has read epochs[c] before it is advanced
+    __syncthreads();
+    if (tid == 0) epochs[c] = epoch;
+}
+
+// Receive side of a row-parallel linear whose GEMV pushed its fp32 partial results itself (GemvArgs::push_*): every
+// rank's inbox -- the own one included -- holds one {fp32 value, call number} word per output element.  Poll, add
+// the ranks' values in rank order, add bias / the previous y, round once to y's dtype, advance the call counter.
+struct RecvArgs {
+    uint8_t* own; int world;
+    size_t inbox_bytes;
+    void* y; int y_dtype; const void* bias; int accumulate;
+    int64_t n_words, words_per_cta, n_cols;
+    int pdl;
+};
+
+__global__ void __launch_bounds__(COMM_THREADS) recv_sum_kernel(const RecvArgs A) {
+    const int c = blockIdx.x, tid = threadIdx.x;
+    uint32_t* epochs = reinterpret_cast<uint32_t*>(A.own);
+    uint32_t* status = epochs + COMM_MAX_CTAS;
+    // Under programmatic dependent launch: release the next kernel of the stream at once (a linear streams its weights
+    // first and waits for this grid before it reads y), then wait for the local GEMV -- and, through its own wait, for
+    // everything in front of it, the previous call's receive kernel included: only then is the call counter current.
+    if (A.pdl) {
+        asm volatile("griddepcontrol.launch_dependents;");
+        asm volatile("griddepcontrol.wait;" ::: "memory");
+    }
+    uint32_t epoch;
+    asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(epoch) : "l"(epochs + c) : "memory");
+    epoch += 1;
+    const size_t slot_off = COMM_HEADER_BYTES + (epoch & 1) * (A.inbox_bytes * COMM_MAX_WORLD);
+    const int64_t begin = (int64_t)c * A.words_per_cta;
+    const int64_t end = begin + A.words_per_cta < A.n_words ? begin + A.words_per_cta : A.n_words;
+    bool expired = false;
+    constexpr int BATCH = 4;
+    for (int64_t w0 = begin + tid; w0 < end; w0 += COMM_THREADS * BATCH) {
+        float v[BATCH];
+#pragma unroll
+        for (int j = 0; j < BATCH; j++) {
+            const int64_t w = w0 + j * COMM_THREADS;
+            v[j] = 0.0f;
+            if (w < end) {
+#pragma unroll
+                for (int r = 0; r < COMM_MAX_WORLD; r++)
+                    if (r < A.world) {
+                        const uint8_t* p = A.own + slot_off + r * A.inbox_bytes + w * 8;
+                        uint2 got = ld_word(p);
+                        uint32_t polls = 0;
+                        while (got.y != epoch && !expired) {
+                            if (++polls > COMM_SPIN_LIMIT) { expired = true; break; }
+                            if (polls > 64) __nanosleep(polls > 4096 ? 256 : 32);
+                            got = ld_word(p);
+                        }
+                        v[j] += __uint_as_float(got.x);
+                    }
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < BATCH; j++) {
+            const int64_t w = w0 + j * COMM_THREADS;
+            if (w < end) {
+                const int64_t col = w % A.n_cols;
+                float o = v[j];
+                if (A.y_dtype == DT_F32) {
+                    float* p = (float*)A.y + w;
+                    if (A.bias) o += ((const float*)A.bias)[col];
+                    *p = A.accumulate ? *p + o : o;
+                } else if (A.y_dtype == DT_F16) {
+                    __half* p = (__half*)A.y + w;
+                    if (A.bias) o += __half2float(((const __half*)A.bias)[col]);
+                    *p = __float2half_rn(A.accumulate ? __half2float(*p) + o : o);
+                } else {
+                    __nv_bfloat16* p = (__nv_bfloat16*)A.y + w;
+                    if (A.bias) o += __bfloat162float(((const __nv_bfloat16*)A.bias)[col]);
+                    *p = __float2bfloat16_rn(A.accumulate ? __bfloat162float(*p) + o : o);
+                }
+            }
+        }
+    }
+    if (expired) atomicExch(status, 1u);
     __syncthreads();
     if (tid == 0) epochs[c] = epoch;
 }
@@ -245,6 +329,58 @@ extern "C" int lowbit_allreduce_sum_cuda(void* const* peer_buffers, int rank, in
     if (dtype == DT_F32) cudaLaunchKernelEx(&cfg, allreduce_kernel<DT_F32>, A);
     else if (dtype == DT_F16) cudaLaunchKernelEx(&cfg, allreduce_kernel<DT_F16>, A);
     else cudaLaunchKernelEx(&cfg, allreduce_kernel<DT_BF16>, A);
+    note_launch();
+    return check_launch();
+}
+
+// Row-parallel linear + all-reduce in one call: the GEMV's leader CTAs push their fp32 sums to every rank as they
+// finish (no separate send pass, no kernel boundary in front of the collective), recv_sum_kernel adds them up.
+// m <= 32, n_rows % 64 == 0, m * n_rows * 4 <= max_bytes of the communicator.  bias / accumulate are applied once,
+// by the receiver, after the sum (low_bit_linear.py:715-725 adds the bias after the all-reduce).
+extern "C" int lowbit_matmul_allreduce_cuda(const void* d_w, int qtype, int64_t n_rows, int64_t k, const void* d_x, int x_dtype,
+                                            int64_t m, void* d_y, int y_dtype, const void* d_bias, int accumulate,
+                                            void* const* peer_buffers, int rank, int world, size_t max_bytes, void* workspace,
+                                            size_t workspace_bytes, void* stream) {
+    reset_launch_count();
+    const int64_t n_words = m * n_rows;
+    if (!peer_buffers || world < 1 || world > COMM_MAX_WORLD || rank < 0 || rank >= world || !d_w || !d_x || !d_y || m <= 0 || m > 32 ||
+        n_rows <= 0 || (n_rows % 64) || y_dtype < 0 || y_dtype > 2 || max_bytes == 0 || max_bytes > lowbit_comm_max_bytes() ||
+        (size_t)n_words * 4 > max_bytes) {
+        set_error(LB_ERR_ARG, "lowbit_matmul_allreduce_cuda: bad argument (rank %d of %d, M %lld, N %lld: M <= 32, N %% 64 == 0 and "
+                  "M * N * 4 bytes within the communicator's size)", rank, world, (long long)m, (long long)n_rows);
+        return LB_ERR_ARG;
+    }
+    for (int r = 0; r < world; r++)
+        if (!peer_buffers[r]) { set_error(LB_ERR_ARG, "lowbit_matmul_allreduce_cuda: peer buffer %d is NULL", r); return LB_ERR_ARG; }
+    const size_t inbox = comm_inbox_bytes(max_bytes);
+    GemvPush push = {};
+    push.world = world; push.slot_bytes = inbox * COMM_MAX_WORLD;
+    push.epochs = reinterpret_cast<const unsigned int*>(peer_buffers[rank]);
+    for (int r = 0; r < world; r++) push.inbox[r] = (unsigned long long)((uint8_t*)peer_buffers[r] + COMM_HEADER_BYTES + (size_t)rank * inbox);
+    gemv_set_push(&push);
+    int rc = gemv_launch(d_w, qtype, n_rows, k, d_x, x_dtype, m, d_y, y_dtype, nullptr, 0, workspace, workspace_bytes, (cudaStream_t)stream);
+    gemv_set_push(nullptr);
+    if (rc) {
+        if (rc == LB_ERR_ARG) set_error(rc, "lowbit_matmul_allreduce_cuda: the GEMV does not take this shape / qtype (qtype %d, N %lld, K %lld, M %lld)",
+                                        qtype, (long long)n_rows, (long long)k, (long long)m);
+        return rc;
+    }
+    RecvArgs A;
+    A.own = (uint8_t*)peer_buffers[rank]; A.world = world; A.inbox_bytes = inbox;
+    A.y = d_y; A.y_dtype = y_dtype; A.bias = d_bias; A.accumulate = accumulate;
+    A.n_words = n_words; A.n_cols = n_rows;
+    // the grid follows from max_bytes alone, as in lowbit_allreduce_sum_cuda (words of 4 payload bytes)
+    int ctas = (int)((max_bytes + COMM_CHUNK_BYTES - 1) / COMM_CHUNK_BYTES);
+    if (ctas > COMM_MAX_CTAS) ctas = COMM_MAX_CTAS;
+    A.words_per_cta = (int64_t)(((max_bytes + ctas - 1) / ctas + 15) / 16 * 16) / 4;
+    A.pdl = gemv_get_pdl();
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)ctas); cfg.blockDim = dim3(COMM_THREADS); cfg.dynamicSmemBytes = 0; cfg.stream = (cudaStream_t)stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = A.pdl ? 1 : 0;
+    cudaLaunchKernelEx(&cfg, recv_sum_kernel, A);
     note_launch();
     return check_launch();
 }

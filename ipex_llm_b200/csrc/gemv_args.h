@@ -49,6 +49,21 @@ struct GemvArgs {
     int n_experts;                         // ids outside [0, n_experts) contribute zero
     int n_seg;
     const void* seg_scale; int seg_scale_dtype;
+    // row-parallel linear under tensor parallelism (comm.cu): instead of storing y, the leader CTA of every row group
+    // pushes its fp32 sums, each with the communicator's call number, into this rank's inbox in every rank's buffer
+    // (8-byte stores over NVLink); the receive kernel that follows adds the ranks' words up.  push_world = 0: store y.
+    int push_world;
+    unsigned long long push_inbox[8];      // address of this rank's inbox (slot 0) inside rank r's buffer
+    unsigned long long push_slot_bytes;    // slot 1 = slot 0 + push_slot_bytes
+    const unsigned int* push_epochs;       // the communicator's device-resident call counter (own buffer)
+};
+
+// one-shot request consumed by the next gemv_launch_ex on this thread (see lowbit_matmul_allreduce_cuda)
+struct GemvPush {
+    int world;
+    unsigned long long inbox[8];
+    unsigned long long slot_bytes;
+    const unsigned int* epochs;
 };
 
 __device__ __forceinline__ void store_out(void* y, int dt, int64_t idx, float v, const void* bias, int64_t row, int acc) {

@@ -739,14 +739,30 @@ gemv_kernel(const GemvArgs A) {
     }
     __syncthreads();
     const int64_t N = A.G.rows;
+    // call number of the communicator: its counter is advanced by the receive kernel of the previous call, which this
+    // grid has waited for (stream order, or griddepcontrol.wait above)
+    unsigned int push_epoch = 0;
+    if (MODE == 0 && A.push_world > 0) {
+        asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(push_epoch) : "l"(A.push_epochs) : "memory");
+        push_epoch += 1;
+    }
     auto store_value = [&](int i, float v) {
         const int l = i % LW, val = i / LW, c = val % ACC, j = (val / ACC) % NT, r = val / (ACC * NT);
         const int gg = l / tl, tt = l - gg * tl;
         const int hi = (ACC == 2) ? c : (c >> 1);                     // row g (0) or g+8 (1)
         const int col = 8 * j + 2 * tt + ((ACC == 2) ? 0 : (c & 1));
         const int64_t row = (int64_t)rg * RG_ROWS + r * 16 + gg + 8 * hi;
-        if (col < A.M)
-            store_out(A.y, A.y_dtype, (MODE == 1 ? (int64_t)blockIdx.z * N : (int64_t)col * N) + row, v, A.bias, row, A.accumulate);
+        if (col < A.M) {
+            if (MODE == 0 && A.push_world > 0) {
+                // tensor parallel: word (col, row) of this rank's partial result goes to every rank's inbox
+                const unsigned long long off = (unsigned long long)(push_epoch & 1u) * A.push_slot_bytes + (unsigned long long)((int64_t)col * N + row) * 8ull;
+#pragma unroll
+                for (int pr = 0; pr < 8; pr++)
+                    if (pr < A.push_world)
+                        asm volatile("st.volatile.global.v2.u32 [%0], {%1,%2};" :: "l"(A.push_inbox[pr] + off), "r"(__float_as_uint(v)), "r"(push_epoch) : "memory");
+            } else
+                store_out(A.y, A.y_dtype, (MODE == 1 ? (int64_t)blockIdx.z * N : (int64_t)col * N) + row, v, A.bias, row, A.accumulate);
+        }
     };
     auto finish = [&](int i, const float (&vm)[NM]) {  // both matrices' sums of output i are in one thread
         const float v = NM == 2 ? apply_act(vm[0], A.act) * vm[NM - 1] : vm[0];

@@ -39,6 +39,8 @@ int quantize_launch(const float* src, void* dst, int qt, size_t n, int k, int64_
 // gemv.cu
 void gemv_set_pdl(int on);
 int gemv_get_pdl();
+struct GemvPush;
+void gemv_set_push(const GemvPush* p);   // the next gemv_launch_ex on this thread pushes its result to the peers (comm.cu)
 void gemv_set_next_weights(const void* w, size_t bytes);
 void gemv_set_debug_timestamps(void* p);
 size_t gemv_workspace_size(int64_t n_rows, int64_t k, int64_t m, int x_dtype);

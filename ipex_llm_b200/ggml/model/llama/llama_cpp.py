@@ -435,3 +435,19 @@ def lowbit_allreduce_sum(peer_ptrs, rank, max_bytes, src, dst, stream):
     arr = (ctypes.c_void_p * len(peer_ptrs))(*peer_ptrs)
     _check(_lib.lowbit_allreduce_sum_cuda(arr, rank, len(peer_ptrs), max_bytes, src.data_ptr(), dst.data_ptr(), src.numel(),
                                           _DT_OF[str(src.dtype)], stream), "lowbit_allreduce_sum_cuda")
+
+
+_lib.lowbit_matmul_allreduce_cuda.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_int64, ctypes.c_void_p, ctypes.c_int,
+                                              ctypes.c_int64, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int,
+                                              ctypes.POINTER(ctypes.c_void_p), ctypes.c_int, ctypes.c_int, ctypes.c_size_t,
+                                              ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p]
+_lib.lowbit_matmul_allreduce_cuda.restype = ctypes.c_int
+
+
+def lowbit_matmul_allreduce(w, qtype, n_rows, k, x, y, bias, accumulate, peer_ptrs, rank, max_bytes, workspace, stream):
+    arr = (ctypes.c_void_p * len(peer_ptrs))(*peer_ptrs)
+    _check(_lib.lowbit_matmul_allreduce_cuda(w.data_ptr(), qtype, n_rows, k, x.data_ptr(), _DT_OF[str(x.dtype)], x.shape[0],
+                                             y.data_ptr(), _DT_OF[str(y.dtype)], bias.data_ptr() if bias is not None else None,
+                                             int(bool(accumulate)), arr, rank, len(peer_ptrs), max_bytes,
+                                             workspace.data_ptr() if workspace is not None else None,
+                                             workspace.numel() if workspace is not None else 0, stream), "lowbit_matmul_allreduce_cuda")

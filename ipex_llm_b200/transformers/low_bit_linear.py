@@ -529,6 +529,13 @@ class LowBitLinear(nn.Linear):
                               f"activation on {x_2d.device}, weight on {self.weight.data.device}")
             if x_2d.dtype not in _TORCH_TO_DT:
                 x_2d = x_2d.float()
+            g = self.mp_group
+            if g is not None and hasattr(g, "matmul_all_reduce") and x_2d.dtype in _TORCH_TO_DT and \
+                    g.fused_supported(x_2d.shape[0], self.out_len, self.qtype):
+                # row-parallel decode: the GEMV pushes its partial sums to the peers itself; the bias is added once,
+                # after the sum (LBL:715-725)
+                result = g.matmul_all_reduce(x_2d, self.weight.data, self.weight_shape, self.qtype, bias=self.bias)
+                return result.view(new_shape).to(x.dtype)
             fuse_bias = self.bias is not None and self.mp_group is None
             nxt = self.next_linear.weight.data if (self.next_linear is not None and x_2d.shape[0] <= GEMV_MAX_M) else None
             result = lowbit_matmul(x_2d, self.weight.data, self.weight_shape, self.qtype,

@@ -17,6 +17,7 @@ import torch
 
 import ipex_llm_b200.ggml.model.llama.llama_cpp as ggml
 from ipex_llm_b200.utils.common import invalidInputError
+from ipex_llm_b200.ggml.quantize import B200_SUPPORTED_QTYPE_IDS
 
 
 def _as_bytes(packed):
@@ -143,6 +144,33 @@ class PeerAllReduce:
         with torch.cuda.device(tensor.device):
             ggml.lowbit_allreduce_sum(peers, self.rank, nbytes, tensor, tensor, torch.cuda.current_stream(tensor.device).cuda_stream)
         return tensor
+
+    def fused_supported(self, m, n_rows, qtype):
+        """can ``matmul_all_reduce`` take this row-parallel matmul?  (decode sizes: M <= 32, 64-row groups, fp32 partials
+        within the communicator limit)"""
+        return (self.world > 1 and 1 <= m <= 32 and n_rows % 64 == 0 and m * n_rows * 4 <= ggml.lowbit_comm_max_bytes()
+                and qtype in B200_SUPPORTED_QTYPE_IDS)
+
+    def matmul_all_reduce(self, x_2d, weight, weight_shape, qtype, bias=None, out=None, accumulate=False):
+        """``all_reduce(x_2d @ dequant(W).T) + bias`` of a row-parallel linear in one call: the GEMV pushes its fp32
+        partial sums to the peers from its epilogue (``lowbit_matmul_allreduce_cuda``)."""
+        from ipex_llm_b200.transformers import low_bit_linear as lbl
+        n_rows, k = weight_shape
+        m = x_2d.shape[0]
+        invalidInputError(self.fused_supported(m, n_rows, qtype), "matmul_all_reduce: shape outside the fused kernel's range")
+        x_2d = x_2d.contiguous()
+        if out is None:
+            out = torch.empty((m, n_rows), dtype=x_2d.dtype, device=x_2d.device)
+        if bias is not None and bias.dtype != out.dtype:
+            bias = bias.to(out.dtype)
+        own, peers = self._comm(m * n_rows * 4)
+        dt = lbl._TORCH_TO_DT[x_2d.dtype]
+        ws = lbl._get_workspace(x_2d.device, ggml.lowbit_matmul_workspace_size(n_rows, k, m, dt))
+        w = weight.view(torch.uint8) if weight.dtype != torch.uint8 else weight
+        with torch.cuda.device(x_2d.device):
+            ggml.lowbit_matmul_allreduce(w, qtype, n_rows, k, x_2d, out, bias, accumulate, peers, self.rank, m * n_rows * 4, ws,
+                                         torch.cuda.current_stream(x_2d.device).cuda_stream)
+        return out
 
     def timed_out(self):
         """True if a wait inside a kernel ran into its bound (a peer did not take part).  Synchronises the device."""

@@ -93,6 +93,44 @@ def _worker(rank, world, port, out):
         gathered = [torch.empty_like(y_tp) for _ in range(world)]
         dist.all_gather(gathered, y_tp)
         assert all(torch.equal(g, y_tp) for g in gathered)                   # the same bits on every rank
+        # the fused form: the GEMV pushes its fp32 partial sums itself (LowBitLinear uses it for M <= 32); the sum over
+        # ranks is taken before the rounding to fp16, so it is compared with the unsharded fp32 result
+        assert isinstance(part.mp_group, tp.PeerAllReduce) and group.fused_supported(1, N, qt)
+        for M in (1, 5, 16):
+            xm = torch.randn(M, K, device=dev, generator=gen).half()
+            bias = torch.randn(N, device=dev, generator=gen).half()
+            want32 = lbl.lowbit_matmul(xm, full.weight.data, (N, K), qt, out_dtype=torch.float32)
+            got = group.matmul_all_reduce(xm[:, k0:k1].contiguous(), part.weight.data, part.weight_shape, qt, bias=bias)
+            ref = (want32 + bias.float())
+            assert float((got.float() - ref).abs().max()) <= 1.5e-3 * float(ref.abs().max()), M
+            res = torch.randn(M, N, device=dev, generator=gen).half()
+            acc = res.clone()
+            for _ in range(3):                           # back to back: both slots, same buffers
+                acc.copy_(res)
+                group.matmul_all_reduce(xm[:, k0:k1].contiguous(), part.weight.data, part.weight_shape, qt, out=acc, accumulate=True)
+            assert float((acc.float() - (want32 + res.float())).abs().max()) <= 1.5e-3 * float((want32 + res.float()).abs().max()), M
+            gathered = [torch.empty_like(got) for _ in range(world)]
+            dist.all_gather(gathered, got)
+            assert all(torch.equal(g, got) for g in gathered)
+        # ... and interleaved with plain all-reduces on a communicator of the same size, inside a graph
+        yb = torch.empty(1, N, device=dev, dtype=torch.float16)
+        t32 = torch.zeros(N, device=dev, dtype=torch.float32)              # N * 4 bytes: the fused call's communicator
+        xs = xin[:, k0:k1].contiguous()
+        with torch.cuda.stream(stream):
+            group.all_reduce(t32)
+            torch.cuda.synchronize()
+            graph2 = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph2, stream=stream):
+                for _ in range(3):
+                    group.matmul_all_reduce(xs, part.weight.data, part.weight_shape, qt, out=yb)
+                    group.all_reduce(t32)
+            for it in range(4):
+                t32.fill_(float(rank + 1))
+                graph2.replay()
+                torch.cuda.synchronize()
+                assert float((yb.float() - y_full.float()).abs().max()) <= 2e-3 * float(y_full.float().abs().max())
+                base = float(sum(range(1, world + 1)))
+                assert torch.equal(t32, torch.full_like(t32, base * world * world)), it     # three all-reduces of the running value
         assert not group.timed_out()
         group.close()
         out[rank] = 1
