@@ -52,7 +52,7 @@ def _free_port():
     s = socket.socket(); s.bind(("127.0.0.1", 0)); p = s.getsockname()[1]; s.close(); return p
 
 
-def _tp_worker(rank, world, port, w, x, bias, qtype, out):
+def _tp_worker(rank, world, port, w, x, bias, qtype, out, peer_group=False):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
@@ -68,7 +68,10 @@ def _tp_worker(rank, world, port, w, x, bias, qtype, out):
         p_up = torch.from_numpy(oracle.quantize(w_up, qtype))
         p_down = torch.from_numpy(oracle.quantize(w_down, qtype))
         up = tp.make_parallel_linear(p_up, (I, K), QT[qtype], "column", rank, world)
-        down = tp.make_parallel_linear(p_down, (N, I), QT[qtype], "row", rank, world, mp_group=dist.group.WORLD,
+        # the group object of a row-parallel linear: a torch process group, or the library's PeerAllReduce (which hands
+        # tensors that are not on a GPU -- everything here -- to torch.distributed)
+        group = tp.PeerAllReduce(device="cpu") if peer_group else dist.group.WORLD
+        down = tp.make_parallel_linear(p_down, (N, I), QT[qtype], "row", rank, world, mp_group=group,
                                        bias=torch.from_numpy(bias))
         assert up.mp_group is None and down.mp_group is not None
         xt = torch.from_numpy(x)
@@ -84,8 +87,8 @@ def _tp_worker(rank, world, port, w, x, bias, qtype, out):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("qtype", ["sym_int4", "fp6"])
-def test_row_parallel_allreduce_gloo_world2(native_lib, qtype):
+@pytest.mark.parametrize("qtype,peer_group", [("sym_int4", False), ("fp6", False), ("sym_int4", True)])
+def test_row_parallel_allreduce_gloo_world2(native_lib, qtype, peer_group):
     rng = np.random.default_rng(3)
     N, K, M = 64, 256, 3
     w = (rng.standard_normal((N, K)) * 0.02).astype(np.float32)
@@ -95,7 +98,7 @@ def test_row_parallel_allreduce_gloo_world2(native_lib, qtype):
     ctx = mp.get_context("spawn")
     out = ctx.Manager().dict()
     port = _free_port()
-    procs = [ctx.Process(target=_tp_worker, args=(r, world, port, w, x, bias, qtype, out)) for r in range(world)]
+    procs = [ctx.Process(target=_tp_worker, args=(r, world, port, w, x, bias, qtype, out, peer_group)) for r in range(world)]
     for p in procs:
         p.start()
     for p in procs:
