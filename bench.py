@@ -108,6 +108,18 @@ def cpu_reference(steps, warmup):
         ncores = len(os.sched_getaffinity(0))
     except AttributeError:
         ncores = os.cpu_count() or 1
+    for quota_file, period_file in (("/sys/fs/cgroup/cpu.max", None),           # a container's CPU quota can be far
+                                    ("/sys/fs/cgroup/cpu/cpu.cfs_quota_us", "/sys/fs/cgroup/cpu/cpu.cfs_period_us")):   # below its visible cores
+        try:
+            if period_file is None:
+                quota, period = open(quota_file).read().split()[:2]
+            else:
+                quota, period = open(quota_file).read().strip(), open(period_file).read().strip()
+            if quota not in ("max", "-1"):
+                ncores = max(1, min(ncores, -(-int(quota) // int(period))))
+            break
+        except (OSError, ValueError):
+            continue
     if os.environ.get("LOCAL_RANK") is not None or "OMP_NUM_THREADS" not in os.environ:
         os.environ["OMP_NUM_THREADS"] = str(ncores)
     import oracle
