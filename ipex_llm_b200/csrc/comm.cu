@@ -119,6 +119,41 @@ __global__ void __launch_bounds__(COMM_THREADS) allreduce_kernel(const CommArgs 
                     if (r < A.world && r != A.rank) st_word(A.peer[r] + slot_off + A.rank * A.inbox_bytes + w * 8, mine[j], epoch);
             }
         }
+        // poll in rounds: every round loads all words that are still missing at once (one memory round trip per
+        // round, whatever the world size) and then looks at their call numbers
+        uint2 got[COMM_WPT][COMM_MAX_WORLD];
+        uint32_t missing = 0;                         // bit j * 8 + r
+#pragma unroll
+        for (int j = 0; j < COMM_WPT; j++)
+#pragma unroll
+            for (int r = 0; r < COMM_MAX_WORLD; r++)
+                if (r < A.world && r != A.rank && w0 + j * COMM_THREADS < end) missing |= 1u << (j * 8 + r);
+        // (first a plain spin on one word -- a single load in flight while nothing has arrived yet keeps the polling
+        // traffic out of the way of the incoming stores -- then everything else, which has usually arrived with it)
+        if (missing != 0) {
+            const int sb = __ffs(missing) - 1;
+            const uint8_t* p = own + slot_off + (sb & 7) * A.inbox_bytes + (w0 + (sb >> 3) * COMM_THREADS) * 8;
+            uint32_t polls = 0;
+            while (ld_word(p).y != epoch) {
+                if (++polls > COMM_SPIN_LIMIT) { expired = true; break; }
+                if (polls > 64) __nanosleep(polls > 4096 ? 256 : 32);
+            }
+        }
+        for (uint32_t polls = 0; missing != 0 && !expired; polls++) {
+            if (polls > COMM_SPIN_LIMIT) { expired = true; break; }
+            if (polls > 16) __nanosleep(polls > 1024 ? 256 : 32);
+#pragma unroll
+            for (int j = 0; j < COMM_WPT; j++)
+#pragma unroll
+                for (int r = 0; r < COMM_MAX_WORLD; r++)
+                    if (missing & (1u << (j * 8 + r)))
+                        got[j][r] = ld_word(own + slot_off + r * A.inbox_bytes + (w0 + j * COMM_THREADS) * 8);
+#pragma unroll
+            for (int j = 0; j < COMM_WPT; j++)
+#pragma unroll
+                for (int r = 0; r < COMM_MAX_WORLD; r++)
+                    if ((missing & (1u << (j * 8 + r))) && got[j][r].y == epoch) missing &= ~(1u << (j * 8 + r));
+        }
 #pragma unroll
         for (int j = 0; j < COMM_WPT; j++) {
             const int64_t w = w0 + j * COMM_THREADS;
@@ -128,17 +163,7 @@ __global__ void __launch_bounds__(COMM_THREADS) allreduce_kernel(const CommArgs 
                 for (int r = 0; r < COMM_MAX_WORLD; r++)
                     if (r < A.world) {
                         uint32_t v = mine[j];
-                        if (r != A.rank) {
-                            const uint8_t* p = own + slot_off + r * A.inbox_bytes + w * 8;
-                            uint2 got = ld_word(p);
-                            uint32_t polls = 0;
-                            while (got.y != epoch && !expired) {
-                                if (++polls > COMM_SPIN_LIMIT) { expired = true; break; }
-                                if (polls > 64) __nanosleep(polls > 4096 ? 256 : 32);
-                                got = ld_word(p);
-                            }
-                            v = got.x;
-                        }
+                        if (r != A.rank) v = got[j][r].x;
                         add_word<DT>(acc, v);
                     }
                 out[w] = pack_word<DT>(acc);
@@ -183,25 +208,43 @@ __global__ void __launch_bounds__(COMM_THREADS) recv_sum_kernel(const RecvArgs A
     constexpr int BATCH = 4;
     for (int64_t w0 = begin + tid; w0 < end; w0 += COMM_THREADS * BATCH) {
         float v[BATCH];
+        uint2 got[BATCH][COMM_MAX_WORLD];             // polled in rounds, as in allreduce_kernel
+        uint32_t missing = 0;
 #pragma unroll
-        for (int j = 0; j < BATCH; j++) {
-            const int64_t w = w0 + j * COMM_THREADS;
-            v[j] = 0.0f;
-            if (w < end) {
+        for (int j = 0; j < BATCH; j++)
+#pragma unroll
+            for (int r = 0; r < COMM_MAX_WORLD; r++)
+                if (r < A.world && w0 + j * COMM_THREADS < end) missing |= 1u << (j * 8 + r);
+        if (missing != 0) {                           // a plain spin on one word first, as in allreduce_kernel
+            const int sb = 31 - __clz(missing);       // the highest rank's word: the own rank's words arrive first
+            const uint8_t* p = A.own + slot_off + (sb & 7) * A.inbox_bytes + (w0 + (sb >> 3) * COMM_THREADS) * 8;
+            uint32_t polls = 0;
+            while (ld_word(p).y != epoch) {
+                if (++polls > COMM_SPIN_LIMIT) { expired = true; break; }
+                if (polls > 64) __nanosleep(polls > 4096 ? 256 : 32);
+            }
+        }
+        for (uint32_t polls = 0; missing != 0 && !expired; polls++) {
+            if (polls > COMM_SPIN_LIMIT) { expired = true; break; }
+            if (polls > 16) __nanosleep(polls > 1024 ? 256 : 32);
+#pragma unroll
+            for (int j = 0; j < BATCH; j++)
 #pragma unroll
                 for (int r = 0; r < COMM_MAX_WORLD; r++)
-                    if (r < A.world) {
-                        const uint8_t* p = A.own + slot_off + r * A.inbox_bytes + w * 8;
-                        uint2 got = ld_word(p);
-                        uint32_t polls = 0;
-                        while (got.y != epoch && !expired) {
-                            if (++polls > COMM_SPIN_LIMIT) { expired = true; break; }
-                            if (polls > 64) __nanosleep(polls > 4096 ? 256 : 32);
-                            got = ld_word(p);
-                        }
-                        v[j] += __uint_as_float(got.x);
-                    }
-            }
+                    if (missing & (1u << (j * 8 + r)))
+                        got[j][r] = ld_word(A.own + slot_off + r * A.inbox_bytes + (w0 + j * COMM_THREADS) * 8);
+#pragma unroll
+            for (int j = 0; j < BATCH; j++)
+#pragma unroll
+                for (int r = 0; r < COMM_MAX_WORLD; r++)
+                    if ((missing & (1u << (j * 8 + r))) && got[j][r].y == epoch) missing &= ~(1u << (j * 8 + r));
+        }
+#pragma unroll
+        for (int j = 0; j < BATCH; j++) {
+            v[j] = 0.0f;
+#pragma unroll
+            for (int r = 0; r < COMM_MAX_WORLD; r++)
+                if (r < A.world && w0 + j * COMM_THREADS < end) v[j] += __uint_as_float(got[j][r].x);
         }
 #pragma unroll
         for (int j = 0; j < BATCH; j++) {
