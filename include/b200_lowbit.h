@@ -164,7 +164,10 @@ int lowbit_rotary_inplaced_cuda(void* d_q, const int64_t* q_strides, int Hq, voi
  * [B][Hkv][L][D] (GQA: Hq a multiple of Hkv), mask NULL or additive [B][1|Hq][S][L] (mask_strides[1] = 0
  * broadcasts over heads), causal != 0: query token s sees keys <= L - S + s.  out [B][Hq][S][D] contiguous.
  * Softmax and accumulation in fp32; split over the key axis with a deterministic merge (two launches).
- * Key cache pointer and strides 16-byte aligned, value cache 4-byte.  D in {64, 96, 128, 192, 256}, S <= 32. */
+ * Key cache pointer and strides 16-byte aligned, value cache 4-byte.  D in {64, 96, 128, 192, 256}, S <= 32.
+ * fp16 / bf16 queries with D = 64 or 128, a positive scale, a 16-byte aligned value cache (pointer and strides) and
+ * 16-byte aligned query rows run on the tensor cores (q.k and p.v as mma.m16n8k16 from the fp8 bytes, P and Q as
+ * fp16); everything else takes a CUDA-core kernel with fp32 products. */
 int lowbit_sdp_fp8_supported(int Hq, int Hkv, int S, int D);
 size_t lowbit_sdp_fp8_workspace_size(int B, int Hq, int Hkv, int S, int L, int D);
 int lowbit_sdp_fp8_cuda(const void* d_q, int q_dtype, const int64_t* q_strides, const void* d_k,
