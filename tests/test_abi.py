@@ -72,3 +72,55 @@ def test_python_surface(native_lib):
     # meta -> meta sizes the packed buffer only
     m = FP4Params(torch.empty(32, 128, device="meta"), qtype=SYM_INT4).to("meta")
     assert m.quantized and m.data.shape == (32 * 2 * 34,) and tuple(m._shape) == (32, 128)
+
+
+def test_argument_checks_of_the_newer_entry_points(native_lib):
+    """bad arguments are refused before anything touches the device (so this runs without one): rotary embedding,
+    FP8 KV cache / decode attention, the tensor-parallel collective"""
+    lib = ctypes.CDLL(native_lib.LIB_PATH)
+    lib.b200_lowbit_last_error_string.restype = ctypes.c_char_p
+    st3 = (ctypes.c_int64 * 3)(1, 1, 1)
+    st2 = (ctypes.c_int64 * 2)(0, 1)
+    buf = ctypes.create_string_buffer(256)
+    p = ctypes.cast(buf, ctypes.c_void_p)
+
+    def refused(rc, needle):
+        msg = lib.b200_lowbit_last_error_string().decode()
+        lib.b200_lowbit_clear_error()
+        return rc != 0 and needle in msg
+
+    # rotary width larger than head_dim / odd width / neither inv_freq nor tables
+    lib.lowbit_rotary_inplaced_cuda.restype = ctypes.c_int
+    args = lambda R, inv: (p, st3, 2, None, None, 0, 1, 1, 1, 64, R, 0, inv, p if inv else None, st2 if inv else None,
+                           None, None, 0, None, 0, None)
+    assert refused(lib.lowbit_rotary_inplaced_cuda(*args(80, p)), "lowbit_rotary_inplaced_cuda")
+    assert refused(lib.lowbit_rotary_inplaced_cuda(*args(31, p)), "lowbit_rotary_inplaced_cuda")
+    assert refused(lib.lowbit_rotary_inplaced_cuda(*args(32, None)), "lowbit_rotary_inplaced_cuda")
+    # decode attention: unsupported head size, too many new tokens, workspace
+    lib.lowbit_sdp_fp8_supported.restype = ctypes.c_int
+    assert lib.lowbit_sdp_fp8_supported(32, 8, 1, 128) == 1 and lib.lowbit_sdp_fp8_supported(32, 8, 33, 128) == 0
+    assert lib.lowbit_sdp_fp8_supported(32, 8, 1, 80) == 0 and lib.lowbit_sdp_fp8_supported(32, 6, 1, 128) == 0
+    lib.lowbit_sdp_fp8_workspace_size.restype = ctypes.c_size_t
+    assert lib.lowbit_sdp_fp8_workspace_size(1, 32, 8, 1, 4096, 80) == 0
+    # the collective: sizes and ranks
+    lib.lowbit_comm_max_bytes.restype = ctypes.c_size_t
+    limit = lib.lowbit_comm_max_bytes()
+    assert limit == 256 * 1024
+    out = ctypes.c_void_p()
+    assert refused(lib.lowbit_comm_create(ctypes.c_size_t(0), ctypes.byref(out), buf), "lowbit_comm_create")
+    assert refused(lib.lowbit_comm_create(ctypes.c_size_t(limit + 1), ctypes.byref(out), buf), "lowbit_comm_create")
+    peers = (ctypes.c_void_p * 2)(p.value, p.value)
+    lib.lowbit_allreduce_sum_cuda.argtypes = [ctypes.POINTER(ctypes.c_void_p), ctypes.c_int, ctypes.c_int, ctypes.c_size_t,
+                                              ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_int, ctypes.c_void_p]
+    assert refused(lib.lowbit_allreduce_sum_cuda(peers, 2, 2, 4096, p, p, 1024, 1, None), "lowbit_allreduce_sum_cuda")    # rank out of range
+    assert refused(lib.lowbit_allreduce_sum_cuda(peers, 0, 9, 4096, p, p, 1024, 1, None), "lowbit_allreduce_sum_cuda")    # world > 8
+    assert refused(lib.lowbit_allreduce_sum_cuda(peers, 0, 2, 4096, p, p, 1001, 1, None), "lowbit_allreduce_sum_cuda")    # 2002 bytes: not x16
+    assert refused(lib.lowbit_allreduce_sum_cuda(peers, 0, 2, 4096, p, p, 4096, 1, None), "lowbit_allreduce_sum_cuda")    # larger than the communicator
+    lib.lowbit_matmul_allreduce_cuda.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_int64, ctypes.c_void_p, ctypes.c_int,
+                                                 ctypes.c_int64, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_int,
+                                                 ctypes.POINTER(ctypes.c_void_p), ctypes.c_int, ctypes.c_int, ctypes.c_size_t,
+                                                 ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p]
+    assert refused(lib.lowbit_matmul_allreduce_cuda(p, 2, 4096, 4096, p, 1, 33, p, 1, None, 0, peers, 0, 2, 1 << 18, None, 0, None),
+                   "lowbit_matmul_allreduce_cuda")                                                                         # M > 32
+    assert refused(lib.lowbit_matmul_allreduce_cuda(p, 2, 4100, 4096, p, 1, 1, p, 1, None, 0, peers, 0, 2, 1 << 18, None, 0, None),
+                   "lowbit_matmul_allreduce_cuda")                                                                         # rows not x64
