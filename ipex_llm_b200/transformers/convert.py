@@ -46,11 +46,17 @@ def use_scale_search(model_config, qtype):
     return False
 
 
+MIXED_LM_HEAD_QTYPE = "fp6"     # lm_head format under mixed_precision (the reference: q6_k)
+
+
 def _replace_with_low_bit_linear(model, qtype, modules_to_not_convert=None, convert_shape_only=False,
-                                 prefix_name="", model_config=None, enable_scale_search=False, embedding_qtype=None):
+                                 prefix_name="", model_config=None, enable_scale_search=False, embedding_qtype=None,
+                                 mixed_precision=False):
     """CV:472-752.  Linears whose in_features is not a multiple of 64 stay as they are (CV:615-617);
     lm_head (by name or vocab-sized output) gets ``optimize_lm_head`` unless IPEX_LLM_LAST_LM_HEAD=0
-    (CV:504-513).  Quantisation happens inside ``FP4Params.to(device)`` of the module's own device."""
+    (CV:504-513).  ``mixed_precision`` (CV:622-626) keeps a 4-bit model's lm_head at a finer format: the reference
+    picks q6_k, a k-quant (out of scope here); this build uses its own 6-bit block format, fp6 (MIXED_LM_HEAD_QTYPE).
+    Quantisation happens inside ``FP4Params.to(device)`` of the module's own device."""
     from ipex_llm_b200.transformers.low_bit_linear import LowBitLinear, FP4Params
     modules_to_not_convert = modules_to_not_convert or []
     has_been_replaced = False
@@ -65,15 +71,20 @@ def _replace_with_low_bit_linear(model, qtype, modules_to_not_convert=None, conv
                 continue
             optimize_lm_head = is_lm_head(name, model_config, out_features) and \
                 os.environ.get("IPEX_LLM_LAST_LM_HEAD", None) != "0"
+            cur_qtype, cur_scale_search = qtype, enable_scale_search
+            if mixed_precision and is_lm_head(name, model_config, out_features) and \
+                    qtype in (ggml_tensor_qtype["sym_int4"], ggml_tensor_qtype["asym_int4"]):
+                cur_qtype = ggml_tensor_qtype[MIXED_LM_HEAD_QTYPE]
+                cur_scale_search = use_scale_search(model_config, cur_qtype)
             with torch.device("meta"):
-                new_linear = LowBitLinear(in_features, out_features, qtype, module.bias is not None,
+                new_linear = LowBitLinear(in_features, out_features, cur_qtype, module.bias is not None,
                                           mp_group=mp_group, optimize_lm_head=optimize_lm_head,
-                                          enable_scale_search=enable_scale_search)
+                                          enable_scale_search=cur_scale_search)
             device = module.weight.data.device
             new_linear._parameters["weight"] = FP4Params(data=module.weight.data, requires_grad=False, quantized=False,
                                                          _shape=None, convert_shape_only=convert_shape_only,
-                                                         qtype=qtype, in_features=in_features,
-                                                         enable_scale_search=enable_scale_search).to(device)
+                                                         qtype=cur_qtype, in_features=in_features,
+                                                         enable_scale_search=cur_scale_search).to(device)
             if module.bias is not None:
                 new_linear._parameters["bias"] = nn.Parameter(module.bias.data, requires_grad=False).to(device)
             if not module.training:
@@ -90,7 +101,7 @@ def _replace_with_low_bit_linear(model, qtype, modules_to_not_convert=None, conv
             _, flag = _replace_with_low_bit_linear(module, qtype, modules_to_not_convert, convert_shape_only,
                                                    prefix_name=full_module_name, model_config=model_config,
                                                    enable_scale_search=enable_scale_search,
-                                                   embedding_qtype=embedding_qtype)
+                                                   embedding_qtype=embedding_qtype, mixed_precision=mixed_precision)
             has_been_replaced = flag or has_been_replaced
     return model, has_been_replaced
 
@@ -105,7 +116,8 @@ def convert_bigdl_other_module(model, dtype):
 
 
 def ggml_convert_low_bit(model, qtype, optimize_model=True, convert_shape_only=False, device="cpu",
-                         modules_to_not_convert=None, torch_dtype="auto", embedding_qtype=None, **unused):
+                         modules_to_not_convert=None, torch_dtype="auto", embedding_qtype=None, mixed_precision=False,
+                         **unused):
     """CV:1092-1193.  ``woq_int4`` is the same format as ``sym_int4`` (CV:1101-1109)."""
     if qtype == ggml_tensor_qtype["woq_int4"]:
         qtype = ggml_tensor_qtype["sym_int4"]
@@ -116,7 +128,7 @@ def ggml_convert_low_bit(model, qtype, optimize_model=True, convert_shape_only=F
     model, has_been_replaced = _replace_with_low_bit_linear(model, qtype, modules_to_not_convert or [],
                                                             convert_shape_only, model_config=model_config,
                                                             enable_scale_search=enable_scale_search,
-                                                            embedding_qtype=embedding_qtype)
+                                                            embedding_qtype=embedding_qtype, mixed_precision=mixed_precision)
     if not has_been_replaced:
         warnings.warn("No linear modules were found in your model.")
     elif device == "cpu" and torch_dtype != "auto":

@@ -44,16 +44,17 @@ class _BaseAutoModelClass:
         load_in_low_bit = kwargs.pop("load_in_low_bit", None)
         optimize_model = kwargs.pop("optimize_model", True)
         modules_to_not_convert = kwargs.pop("modules_to_not_convert", None)
+        mixed_precision = kwargs.pop("mixed_precision", False)
         for k in ("cpu_embedding", "speculative", "pipeline_parallel_stages", "embedding_qtype", "imatrix",
-                  "mixed_precision", "quantization_group_size", "disk_embedding"):
+                  "quantization_group_size", "disk_embedding"):
             kwargs.pop(k, None)
         if load_in_4bit or load_in_low_bit:
             q_k = load_in_low_bit if load_in_low_bit else "sym_int4"
-            return cls.load_convert(q_k, optimize_model, modules_to_not_convert, *args, **kwargs)
+            return cls.load_convert(q_k, optimize_model, modules_to_not_convert, *args, mixed_precision=mixed_precision, **kwargs)
         return cls.HF_MODEL.from_pretrained(*args, **kwargs)
 
     @classmethod
-    def load_convert(cls, q_k, optimize_model, modules_to_not_convert, *args, **kwargs):
+    def load_convert(cls, q_k, optimize_model, modules_to_not_convert, *args, mixed_precision=False, **kwargs):
         """MD:436-530"""
         from ipex_llm_b200.transformers.convert import ggml_convert_low_bit
         invalidInputError(q_k in ggml_tensor_qtype, f"Unknown load_in_low_bit value: {q_k}")
@@ -61,20 +62,23 @@ class _BaseAutoModelClass:
         model = model.to("cpu")
         model = ggml_convert_low_bit(model, ggml_tensor_qtype[q_k], optimize_model,
                                      modules_to_not_convert=modules_to_not_convert,
-                                     torch_dtype=kwargs.get("torch_dtype", "auto"))
-        return cls._finish(model, q_k)
+                                     torch_dtype=kwargs.get("torch_dtype", "auto"), mixed_precision=mixed_precision)
+        return cls._finish(model, q_k, mixed_precision)
 
     @classmethod
-    def from_model(cls, model, low_bit="sym_int4", optimize_model=True, modules_to_not_convert=None):
+    def from_model(cls, model, low_bit="sym_int4", optimize_model=True, modules_to_not_convert=None, mixed_precision=False):
         """convert an already-built Hugging Face model (random-init models in tests and benchmarks)"""
         from ipex_llm_b200.transformers.convert import ggml_convert_low_bit
         model = ggml_convert_low_bit(model.to("cpu"), ggml_tensor_qtype[low_bit], optimize_model,
-                                     modules_to_not_convert=modules_to_not_convert)
-        return cls._finish(model, low_bit)
+                                     modules_to_not_convert=modules_to_not_convert, mixed_precision=mixed_precision)
+        return cls._finish(model, low_bit, mixed_precision)
 
     @staticmethod
-    def _finish(model, q_k):
+    def _finish(model, q_k, mixed_precision=False):
         model.config.update({"bigdl_transformers_low_bit": q_k})
+        if mixed_precision:                              # recorded so that load_low_bit sizes the lm_head correctly
+            from ipex_llm_b200.transformers.convert import MIXED_LM_HEAD_QTYPE
+            model.config.update({"bigdl_lm_head_low_bit": MIXED_LM_HEAD_QTYPE})
         model.save_low_bit = types.MethodType(save_low_bit, model)
         return model
 
@@ -92,9 +96,11 @@ class _BaseAutoModelClass:
         from ipex_llm_b200.optimize import low_memory_init
         with low_memory_init():
             model = cls.HF_MODEL.from_config(config)
+        mixed_precision = bool(kwargs.pop("mixed_precision", False)) or config.to_dict().get("bigdl_lm_head_low_bit") is not None
         model = ggml_convert_low_bit(model, ggml_tensor_qtype[low_bit], kwargs.pop("optimize_model", True),
                                      convert_shape_only=True, device="meta",
-                                     modules_to_not_convert=kwargs.pop("modules_to_not_convert", None))
+                                     modules_to_not_convert=kwargs.pop("modules_to_not_convert", None),
+                                     mixed_precision=mixed_precision)
         state = torch.load(os.path.join(pretrained_model_name_or_path, PYTORCH_MODEL_NAME), map_location="cpu",
                            weights_only=True)
         assign_low_bit_state_dict(model, state)

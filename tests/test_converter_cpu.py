@@ -111,3 +111,46 @@ def test_convert_vllm_awq_or_gptq(native_lib):
     want = (codes.T - np.repeat(z, group, axis=0).T) * np.repeat(scales.astype(np.float32), group, axis=0).T
     got = oracle.dequantize(packed.numpy(), (out_f, in_f), "asym_int4")
     np.testing.assert_allclose(got, want, rtol=0, atol=2e-3 * np.abs(want).max())
+
+
+def test_mixed_precision_lm_head(native_lib, tmp_path):
+    """convert.py:622-626: with mixed_precision a 4-bit model keeps its lm_head at a finer format (the reference:
+    q6_k; this build: fp6, 50 bytes per 64 weights); the choice is recorded so that load_low_bit sizes the lm_head
+    buffer correctly, and other target formats are left alone"""
+    import json, os
+    from ipex_llm_b200.transformers.convert import ggml_convert_low_bit, MIXED_LM_HEAD_QTYPE
+    from ipex_llm_b200 import optimize
+    from ipex_llm_b200.ggml.quantize import ggml_tensor_qtype as Q
+
+    class Net(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.a = torch.nn.Linear(128, 64, bias=False)
+            self.lm_head = torch.nn.Linear(128, 320, bias=False)
+
+    def build(low_bit, mixed):
+        with torch.device("meta"):
+            net = Net()
+        return ggml_convert_low_bit(net, Q[low_bit], convert_shape_only=True, device="meta", mixed_precision=mixed)
+
+    net = build("sym_int4", True)
+    assert MIXED_LM_HEAD_QTYPE == "fp6"
+    assert net.a.qtype == Q["sym_int4"] and net.a.weight.data.shape == (64 * 2 * 34,)
+    assert net.lm_head.qtype == Q["fp6"] and net.lm_head.weight.data.shape == (320 * 2 * 50,)
+    assert net.lm_head.weight.enable_scale_search          # fp6 is quantised with the scale search (convert.py:459-469)
+    assert build("asym_int4", True).lm_head.qtype == Q["fp6"]
+    assert build("sym_int4", False).lm_head.qtype == Q["sym_int4"]
+    assert build("fp8_e4m3", True).lm_head.qtype == Q["fp8_e4m3"]      # only 4-bit targets are raised
+
+    # save / load: the state dict of a converted model and the recorded lm_head format
+    saved = {"a.weight": torch.arange(64 * 2 * 34, dtype=torch.int64).to(torch.uint8),
+             "lm_head.weight": torch.arange(320 * 2 * 50, dtype=torch.int64).to(torch.uint8)}
+    torch.save(saved, os.path.join(tmp_path, optimize.PYTORCH_MODEL_NAME))
+    with open(os.path.join(tmp_path, optimize.CONFIG_NAME), "w") as f:
+        json.dump({"bigdl_transformers_low_bit": "sym_int4", "bigdl_lm_head_low_bit": "fp6"}, f)
+    with optimize.low_memory_init():
+        fresh = Net()
+    loaded = optimize.load_low_bit(fresh, str(tmp_path))
+    assert loaded.lm_head.qtype == Q["fp6"] and loaded.lm_head.weight.quantized
+    assert torch.equal(loaded.lm_head.weight.data, saved["lm_head.weight"]) and torch.equal(loaded.a.weight.data, saved["a.weight"])
+    assert loaded._bigdl_config == {"bigdl_transformers_low_bit": "sym_int4", "bigdl_lm_head_low_bit": "fp6"}
