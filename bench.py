@@ -1,25 +1,25 @@
 #!/usr/bin/env python
-"""bench.py -- sym_int4 decode tok/s (Llama-2-7B, bs1) on the LowBitLinear GEMV stream.
+"""bench.py -- sym_int4 decode tok/s (Llama-2-7B, bs1) through generate(), and the LowBitLinear GEMV GB/s behind it.
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
 
-Workload (BASELINE.json configs[0]/metric): Llama-2-7B architecture (hidden 4096, inter 11008,
-32 layers, vocab 32000), random-init fp32 weights quantised to sym_int4 by our GPU quantiser,
-batch 1 decode.  One STEP = one decoded token's worth of the hot path: the 161 LowBitLinear
-forward calls of the reference's call stack (per layer qkv_proj 12288x4096, o_proj
-4096x4096, gate_proj/up_proj 11008x4096, down_proj 4096x11008; then lm_head 32000x4096), 3.51 GB
-of packed weights read once.  Attention / RMSNorm / RoPE kernels are outside the hot path this
-repo replaces and are not part of the step; the number is therefore the decode rate
-the low-bit linear path alone supports and is labelled so in `config.workload`.
+Workload (BASELINE.json configs[0] / metric): Llama-2-7B architecture (hidden 4096, inter 11008, 32 layers, vocab
+32000), random-init, converted by ipex_llm.transformers.AutoModelForCausalLM.from_model(load sym_int4: merge_qkv,
+ggml_quantize_tensor on the GPU, optimised forwards), batch 1, greedy, 512-token prompt.  One STEP = one decoded token
+of generate() after the first (the reference's "2+ avg latency", utils/benchmark_util_4_47.py:3391-3393): every linear
+(3.51 GB of packed weights read once), RMSNorm, rotary, FP8 KV-cache write, decode attention over 512+ keys, lm_head and
+the greedy pick, replayed from the recorded decode step.  Default K = 127 = tokens 2..128 of the 512-in / 128-out case.
 
-value : steps/s with activations and weights resident in HBM, the step replayed from a CUDA graph.
-e2e   : the same step driven through the public Python API (LowBitLinear.forward per call), the
-        token's activation copied from pinned host memory at the start of every step and the
-        lm_head logits' argmax read back to the host at the end (what a generate() loop does).
-roofline : dominant kernel = gemv_kernel; achieved = algorithmic bytes of the 161 launches / step time.
-cpu_baseline / --impl reference : the CPU oracle in ggml-faithful mode A (int8 activations,
-        AVX512-VNNI when the host has it, OpenMP) on a bounded sample (one decoder layer + lm_head
-        scaled to the full step) -- the reference's own CPU binary is closed source and absent.
+value : K / (device time of the K decode steps of one generate() call, CUDA events), mean of 3 trials, x N replicas.
+e2e   : the same call with the prompt in pinned host memory and a streamer: every token goes to the host as it is
+        produced and is fed back from the host (8 B each way per step, copy nodes of the step's graph), host clock.
+roofline : dominant kernel = the dequant-GEMV; achieved = algorithmic bytes of the token's 129 LowBitLinear launches /
+        their time when replayed alone (parsed.linear_stream), the kernel's own PDL chain.
+parsed.prefill : the tensor-core GEMM on the layer shapes at M = 512 / 2048; parsed.tp (N > 1): Llama-2-70B tensor parallel.
+cpu_baseline / --impl reference : the CPU oracle in ggml-faithful mode A (int8 activations, AVX512-VNNI when the host
+        has it, OpenMP) on a bounded sample (one decoder layer + lm_head scaled to the token's 161 matrices) -- the
+        reference's own CPU binary is closed source and absent.  It covers the linears only (every weight byte of a
+        token); attention, norms and rotary are not in the CPU sample.
 """
 import argparse
 import json
@@ -52,11 +52,12 @@ def n_launches():
     return LAYERS * (len(LAYER_SHAPES) - (1 if FUSED_MLP else 0)) + 1
 
 
-def workload_config():
+def workload_config(k_steps):
     """the workload both arms (ours and --impl reference) measure"""
-    return {"workload": "Llama-2-7B sym_int4 bs1 decode, LowBitLinear stream only: 161 matrices/token "
-                        "(32x[qkv 12288x4096, o 4096x4096, gate 11008x4096, up 11008x4096, down 4096x11008] + lm_head "
-                        "32000x4096); attention/norm/rope not included",
+    return {"workload": f"Llama-2-7B architecture, random-init, sym_int4 (QK=64, 34 B blocks), batch 1, greedy, 512-token "
+                        f"prompt, {k_steps + 1} new tokens through ipex_llm.transformers.AutoModelForCausalLM.from_model(...)"
+                        ".generate(); a step = one decoded token (tokens 2..): every linear, RMSNorm, rotary, FP8 KV cache "
+                        "write, decode attention, lm_head and the greedy pick",
             "block": "QK=64, 34 B"}
 
 
@@ -144,167 +145,350 @@ def cpu_reference(steps, warmup):
     for _ in range(max(1, warmup)):
         layer_pass()
     tl, th = [], []
+    t_begin = time.perf_counter()
     for _ in range(max(1, steps)):
         a, b = layer_pass()
         tl.append(a); th.append(b)
+        if time.perf_counter() - t_begin > 60.0:            # bounded sample: a slow or busy host stops after a minute
+            break
     t_layer, t_head = sum(tl) / len(tl), sum(th) / len(th)
     t_token = LAYERS * t_layer + t_head
     return {"value": 1.0 / t_token, "ms_per_step": t_token * 1e3, "cores": cores,
             "sample": f"one decoder layer (5 GEMVs, {sum(len(m[3]) for m in mats[:-1]) / 1e6:.1f} MB packed) x{LAYERS} + "
-                      f"lm_head, mode-A int8-activation kernel, vnni={oracle.uses_vnni()}, {max(1, steps)} passes"}
+                      f"lm_head, mode-A int8-activation kernel, vnni={oracle.uses_vnni()}, {len(tl)} passes"}
 
 
 # --------------------------------------------------------------------------- our arm
-def build_model(dev):
-    """Quantise random-init Llama-2-7B linears on the GPU into the tiled device layout."""
+PROMPT_LEN, NEW_TOKENS = 512, 128      # BASELINE.json configs[0]: 512-in / 128-out
+
+
+def build_llama(dev, layers=LAYERS):
+    """random-init Llama-2-7B (N(0, 0.02^2), fp16) built on the GPU and converted through the public loader API:
+    AutoModelForCausalLM.from_model -> merge_qkv, ggml_quantize_tensor on the GPU, optimised forwards"""
+    import torch
+    import transformers
+    from ipex_llm_b200.optimize import low_memory_init
+    from ipex_llm.transformers import AutoModelForCausalLM
+    cfg = transformers.LlamaConfig(hidden_size=HIDDEN, intermediate_size=INTER, num_hidden_layers=layers,
+                                   num_attention_heads=32, num_key_value_heads=32, vocab_size=VOCAB,
+                                   max_position_embeddings=4096, rms_norm_eps=1e-5, tie_word_embeddings=False)
+    with low_memory_init():
+        model = transformers.LlamaForCausalLM(cfg)
+    gen = torch.Generator(device=dev).manual_seed(0)
+    for mod in model.modules():
+        for pname, p in list(mod._parameters.items()):
+            if p is None:
+                continue
+            if pname == "weight" and mod.__class__.__name__.endswith("RMSNorm"):
+                t = torch.ones(p.shape, device=dev, dtype=torch.float16)
+            else:
+                t = torch.empty(p.shape, device=dev, dtype=torch.float16).normal_(0.0, 0.02, generator=gen)
+            mod._parameters[pname] = torch.nn.Parameter(t, requires_grad=False)
+    for mod in model.modules():                                  # non-persistent buffers (rotary inv_freq) follow
+        for bname, b in list(mod._buffers.items()):
+            if b is not None and b.device.type != "cuda":
+                mod._buffers[bname] = b.to(dev)
+    model = AutoModelForCausalLM.from_model(model.eval(), low_bit=QTYPE_NAME)
+    return model.to(dev).half()
+
+
+class TokenSink:
+    """a transformers-style streamer: the host receives every token as it is produced"""
+
+    def __init__(self):
+        self.tokens = []
+
+    def put(self, value):
+        self.tokens.append(value)
+
+    def end(self):
+        pass
+
+
+def linear_stream(model, dev, steps, warmup):
+    """the LowBitLinear launches of one token (qkv, o, fused gate+up, down per layer, lm_head) on constant inputs,
+    replayed from a CUDA graph: the GEMV kernel in its PDL chain with nothing else in between -- the number the
+    roofline is quoted on.  Returns (ms per token, launches per token)."""
     import torch
     from ipex_llm_b200.transformers import low_bit_linear as lbl
-    qt = lbl.ggml_tensor_qtype[QTYPE_NAME]
-    gen = torch.Generator(device=dev).manual_seed(0)
-    mods = []
-    shapes = [s for _ in range(LAYERS) for s in LAYER_SHAPES] + [LM_HEAD]
-    for name, n, k in shapes:
-        lin = lbl.LowBitLinear(k, n, qt, bias=False)
+    core = model.model
+    x_h = torch.randn(1, HIDDEN, device=dev).half()
+    x_i = torch.randn(1, INTER, device=dev).half()
+    outs = {}
+
+    def out_for(n):
+        if n not in outs:
+            outs[n] = torch.empty(1, n, device=dev, dtype=torch.float16)
+        return outs[n]
+
+    launches = [0]
+
+    def step():
+        launches[0] = 0
+        for layer in core.layers:
+            a, m = layer.self_attn, layer.mlp
+            for lin, x in ((a.qkv_proj, x_h), (a.o_proj, x_h)):
+                lbl.lowbit_matmul(x, lin.weight.data, lin.weight_shape, lin.qtype, out=out_for(lin.out_len))
+            lbl.mlp_forward(x_h, m.gate_proj.weight.data, m.up_proj.weight.data, 1, HIDDEN, INTER, lbl.SILU, m.gate_proj.qtype,
+                            out=out_for(INTER))
+            lbl.lowbit_matmul(x_i, m.down_proj.weight.data, m.down_proj.weight_shape, m.down_proj.qtype, out=out_for(HIDDEN))
+            launches[0] += 4
+        h = model.lm_head
+        lbl.lowbit_matmul(x_h, h.weight.data, h.weight_shape, h.qtype, out=out_for(h.out_len))
+        launches[0] += 1
+
+    stream = torch.cuda.Stream()
+    with torch.cuda.stream(stream):
+        for _ in range(2):
+            step()
+        torch.cuda.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph, stream=stream):
+            step()
+        torch.cuda.synchronize()
+        for _ in range(max(3, warmup)):
+            graph.replay()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(steps):
+            graph.replay()                                      # 3.5 GB of distinct weights per step >> 126 MB L2
+        e1.record()
+        torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / steps, launches[0]
+
+
+def prefill_numbers(model, dev, peaks):
+    """prefill GEMM (kernel (c)) on the layer shapes at config 1's and config 2's prompt lengths, timed alone with CUDA
+    events (L2 flushed between launches by the 200+ MB of other weights in the rotation), plus the whole model's
+    512-token prefill through the public forward"""
+    import torch
+    from ipex_llm_b200.transformers import low_bit_linear as lbl
+    core = model.model
+    burst = float(peaks.get("bf16_tflops", 1644.0))
+    out = {"peak_tflops": burst, "peak_source": "MEASURED_PEAKS.json bf16_tflops (burst: kernels timed alone)" if peaks else "fallback"}
+    for M in (512, 2048):
+        lins = []
+        for layer in core.layers[:8]:                            # rotate over 8 layers' weights: each launch reads cold weights
+            a, m = layer.self_attn, layer.mlp
+            lins += [a.qkv_proj, a.o_proj, m.gate_proj, m.up_proj, m.down_proj]
+        xs = {HIDDEN: torch.randn(M, HIDDEN, device=dev).half(), INTER: torch.randn(M, INTER, device=dev).half()}
+        ys = {n: torch.empty(M, n, device=dev, dtype=torch.float16) for n in {l.out_len for l in lins}}
+
+        def run():
+            for lin in lins:
+                lbl.lowbit_matmul(xs[lin.in_len], lin.weight.data, lin.weight_shape, lin.qtype, out=ys[lin.out_len])
+
+        for _ in range(2):
+            run()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        reps = 3
+        e0.record()
+        for _ in range(reps):
+            run()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / reps
+        flops = sum(2.0 * M * l.in_len * l.out_len for l in lins)
+        tf = flops / (ms * 1e-3) / 1e12
+        out[f"M{M}"] = {"ms_per_layer": ms / 8, "tflops": tf, "frac_of_peak": tf / burst,
+                        "tok_per_s_linears_only": M / (ms / 8 * LAYERS * 1e-3)}
+    ids = torch.randint(0, VOCAB, (1, PROMPT_LEN), device=dev)
+    with torch.no_grad():
+        for _ in range(2):
+            model(ids, use_cache=True)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        model(ids, use_cache=True)
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+    out["model_prefill_512"] = {"ms": dt * 1e3, "tok_per_s": PROMPT_LEN / dt,
+                                "note": "whole forward through the public API, eager launches (FP8 cache write, attention, norms included)"}
+    return out
+
+
+def tp_numbers(args, dev, world, rank):
+    """Llama-2-70B sym_int4 bs1 LowBitLinear stream, column/row sharded over the ranks with the all-reduce after o_proj and
+    down_proj (BASELINE.json configs[3]; the reference's AutoTP recipe), and the same stream on ONE GPU measured on rank 0
+    in the same run.  CUDA events, max over ranks."""
+    import torch
+    import torch.distributed as dist
+    from ipex_llm_b200.transformers import low_bit_linear as lbl
+    from ipex_llm_b200.transformers.tensor_parallel import PeerAllReduce
+    H70, I70, L70, KV70 = 8192, 28672, 80, 1024
+    qt = lbl.ggml_tensor_qtype["sym_int4"]
+    gen = torch.Generator(device=dev).manual_seed(1234 + rank)
+
+    def packed(n, k):
         w = torch.empty(n, k, device=dev, dtype=torch.float32).normal_(0.0, 0.02, generator=gen)
-        lin.weight = lbl.FP4Params(w, qtype=qt).to(dev)          # quantise + relayout on the GPU
-        del w
-        lin.to(dev)
-        mods.append((name, lin))
-    return mods
+        return lbl.FP4Params(w, qtype=qt).to(dev).data
+
+    def stream_for(tp, peer):
+        shapes = {"qkv": ((H70 + 2 * KV70) // tp, H70), "o": (H70, H70 // tp), "gate": (I70 // tp, H70),
+                  "up": (I70 // tp, H70), "down": (H70, I70 // tp)}
+        layers = [{k: packed(*s) for k, s in shapes.items()} for _ in range(L70)]
+        lm_head = packed(VOCAB, H70)
+        x_h = (torch.randn(1, H70, device=dev, generator=gen) * 0.1).half()
+        x_os = x_h[:, :H70 // tp].contiguous()
+        qkv_out = torch.empty(1, shapes["qkv"][0], device=dev, dtype=torch.float16)
+        mlp_out = torch.empty(1, I70 // tp, device=dev, dtype=torch.float16)
+        hid = torch.empty(1, H70, device=dev, dtype=torch.float16)
+        logits = torch.empty(1, VOCAB, device=dev, dtype=torch.float16)
+
+        def row_parallel(x, w, shape):
+            if peer is not None:
+                peer.matmul_all_reduce(x, w, shape, qt, out=hid)
+            else:
+                lbl.lowbit_matmul(x, w, shape, qt, out=hid)
+
+        def step():
+            for L in layers:
+                lbl.lowbit_matmul(x_h, L["qkv"], shapes["qkv"], qt, out=qkv_out)
+                row_parallel(x_os, L["o"], shapes["o"])
+                lbl.mlp_forward(x_h, L["gate"], L["up"], 1, H70, I70 // tp, lbl.SILU, qt, out=mlp_out)
+                row_parallel(mlp_out, L["down"], shapes["down"])
+            lbl.lowbit_matmul(x_h, lm_head, (VOCAB, H70), qt, out=logits)
+
+        return step
+
+    def timed(step, collective):
+        stream = torch.cuda.Stream()
+        with torch.cuda.stream(stream):
+            for _ in range(2):
+                step()
+            torch.cuda.synchronize()
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph, stream=stream, capture_error_mode="thread_local"):
+                step()
+            torch.cuda.synchronize()
+            if collective:
+                dist.barrier()
+            for _ in range(max(3, args.warmup)):
+                graph.replay()
+            torch.cuda.synchronize()
+            if collective:
+                dist.barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(args.steps):
+                graph.replay()
+            e1.record()
+            torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / args.steps
+
+    peer = PeerAllReduce()
+    ms_tp = timed(stream_for(world, peer), True)
+    timed_out = peer.timed_out()
+    ms_nocomm = timed(stream_for(world, None), False)
+    torch.cuda.empty_cache()
+    t = torch.tensor([ms_tp, ms_nocomm], device=dev, dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_tp, ms_nocomm = float(t[0]), float(t[1])
+    ms_tp1 = None
+    if rank == 0:
+        ms_tp1 = timed(stream_for(1, None), False)
+    dist.barrier()
+    peer.close()
+    if rank != 0:
+        return None
+    n_ar = 2 * L70
+    return {"model": "Llama-2-70B sym_int4 bs1 LowBitLinear stream (80 layers: qkv, o, fused gate+up, down; lm_head replicated)",
+            "nranks": world, "ms_per_token": ms_tp, "tok_per_s": 1e3 / ms_tp, "ms_per_token_no_collectives": ms_nocomm,
+            "allreduces_per_token": n_ar, "ms_per_allreduce": (ms_tp - ms_nocomm) / n_ar,
+            "allreduce": "row-parallel GEMV pushes fp32 partial sums to the peers' inboxes from its epilogue (lowbit_matmul_allreduce_cuda)",
+            "tp1_ms_per_token": ms_tp1, "speedup_vs_tp1": ms_tp1 / ms_tp, "strong_efficiency": ms_tp1 / ms_tp / world,
+            "wait_ran_out": bool(timed_out), "timing": "CUDA events over a replayed graph, max over ranks"}
 
 
 def run_ours(args):
     import torch
     import torch.distributed as dist
-    from ipex_llm_b200.transformers import low_bit_linear as lbl
     import ipex_llm_b200.ggml.model.llama.llama_cpp as ggml
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    if world > 1:
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
     ggml.lowbit_set_programmatic_dependent_launch(1 if args.pdl else 0)
-
-    mods = build_model(dev)
-    torch.manual_seed(1)
-    x_h = torch.randn(1, HIDDEN, device=dev).half()
-    x_i = torch.randn(1, INTER, device=dev).half()
-    outs = {n: torch.empty(1, n, device=dev, dtype=torch.float16) for n in {m[1].out_len for m in mods}}
-    x_host = torch.randn(1, HIDDEN).half().pin_memory()
-    tok_host = torch.zeros(1, dtype=torch.int64).pin_memory()
-
-    # the order of the linears in a decoder is static: each one names its successor so that the kernel can
-    # ask the L2 to prefetch the next weights (the last one wraps to the first: next token)
-    if args.l2_hint:
-        for i, (name, lin) in enumerate(mods):
-            lin.next_linear = mods[(i + 1) % len(mods)][1]
-
-    mlp_out = torch.empty(1, INTER, device=dev, dtype=torch.float16)
-
-    def step_kernels():
-        # resident-input step: raw kernel entry point, outputs into preallocated buffers
-        for i, (name, lin) in enumerate(mods):
-            if FUSED_MLP and name == "gate_proj":
-                up = mods[i + 1][1]
-                lbl.mlp_forward(x_h, lin.weight.data, up.weight.data, 1, HIDDEN, INTER, lbl.SILU, lin.qtype, out=mlp_out)
-                continue
-            if FUSED_MLP and name == "up_proj":
-                continue
-            x = x_i if lin.in_len == INTER else x_h
-            nxt = lin.next_linear.weight.data if lin.next_linear is not None else None
-            lbl.lowbit_matmul(x, lin.weight.data, lin.weight_shape, lin.qtype, out=outs[lin.out_len], next_weight=nxt)
-
-    # e2e: the public API a generate() loop uses -- LowBitLinear.forward per linear, recorded once by
-    # ipex_llm_b200.transformers.cuda_graph.capture_decode_step and replayed per token.  Every step
-    # copies the token's activation from pinned host memory and reads the argmax token back.
-    from ipex_llm_b200.transformers.cuda_graph import capture_decode_step
-    x_e2e = torch.zeros(1, HIDDEN, device=dev, dtype=torch.float16)
-    tok_dev = torch.zeros(1, dtype=torch.int64, device=dev)
-
-    def forward_api():
-        # the token's activation arrives from pinned host memory and the chosen token goes back to it: both copies
-        # are recorded with the step (memcpy nodes of the graph), so one launch per token covers them
-        x_e2e.copy_(x_host, non_blocking=True)              # H2D, 8 KB
-        y = None
-        for i, (name, lin) in enumerate(mods):
-            if FUSED_MLP and name == "gate_proj":
-                lbl.mlp_forward(x_e2e, lin.weight.data, mods[i + 1][1].weight.data, 1, HIDDEN, INTER, lbl.SILU, lin.qtype)
-                continue
-            if FUSED_MLP and name == "up_proj":
-                continue
-            y = lin(x_i if lin.in_len == INTER else x_e2e)
-        tok_dev.copy_(torch.argmax(y, dim=-1))
-        tok_host.copy_(tok_dev, non_blocking=True)          # D2H, 8 B
-        return tok_dev
-
-    graphed = capture_decode_step(forward_api)
-
-    def step_e2e():
-        graphed.replay()                                    # H2D copy, 129 launches, argmax, D2H copy
-        graphed.stream.synchronize()
-        return int(tok_host[0])
-
-    stream = torch.cuda.Stream()
-    with torch.cuda.stream(stream):
-        for _ in range(2):
-            step_kernels()
-        torch.cuda.synchronize()
-        graph = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(graph, stream=stream):
-            step_kernels()
-    torch.cuda.synchronize()
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    for _ in range(max(3, args.warmup)):
-        graph.replay()
-    barrier()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    with ClockSampler(local_rank) as clocks:
-        e0.record()
-        for _ in range(args.steps):
-            graph.replay()                      # 3.5 GB of distinct weights per step >> 126 MB L2
-        e1.record()
+    model = build_llama(dev)
+    K = args.steps                                             # timed decode steps = tokens 2 .. K+1 of one generate() call
+    W = max(3, args.warmup)
+    prompt_host = torch.randint(0, VOCAB, (1, PROMPT_LEN), generator=torch.Generator().manual_seed(1)).pin_memory()
+    prompt_dev = prompt_host.to(dev)
+    gen_kwargs = dict(do_sample=False, pad_token_id=0)
+    with torch.no_grad():
+        # warm-up: one untimed generate() of W decode steps records the step's graph; a second one of the timed shape
+        model.generate(prompt_dev, max_new_tokens=W + 1, min_new_tokens=W + 1, **gen_kwargs)
+        model.generate(prompt_dev, max_new_tokens=K + 1, min_new_tokens=K + 1, **gen_kwargs)
+        sink = TokenSink()
+        model.generate(prompt_dev, max_new_tokens=W + 1, min_new_tokens=W + 1, streamer=sink, **gen_kwargs)
         barrier()
-        ms_dev = e0.elapsed_time(e1)
-        # e2e leg
-        for _ in range(max(3, args.warmup)):
-            step_e2e()
-        barrier()
-        t0 = time.perf_counter()
-        for _ in range(args.steps):
-            step_e2e()
-        barrier()
-        ms_e2e = (time.perf_counter() - t0) * 1e3
+        with ClockSampler(local_rank) as clocks:
+            # value: inputs resident in HBM; the K decode steps of generate() timed on the device (CUDA events around the
+            # K graph replays) between synchronisations -- 1000 / "2+ avg latency" of the reference's BenchmarkWrapper
+            trials = []
+            for _ in range(3):                                 # num_trials 3 (all-in-one/run.py)
+                out_dev = model.generate(prompt_dev, max_new_tokens=K + 1, min_new_tokens=K + 1, **gen_kwargs)
+                trials.append((model.rest_cost_mean_device, model.rest_cost_mean, model.first_cost))
+            barrier()
+            ms_dev = 1e3 * sum(t[0] for t in trials) / len(trials)
+            ms_wall = 1e3 * sum(t[1] for t in trials) / len(trials)
+            first_ms = 1e3 * sum(t[2] for t in trials) / len(trials)
+            launches_per_token = model.last_decode_launches_per_token
+            # e2e: the same call with the prompt in pinned HOST memory, every token delivered to the host as it is produced
+            # (streamer) and fed back from the host: per step 8 B H2D + 8 B D2H inside the step's graph, host clock
+            e2e_trials = []
+            for _ in range(3):
+                sink = TokenSink()
+                t0 = time.perf_counter()
+                out = model.generate(prompt_host.to(dev, non_blocking=True), max_new_tokens=K + 1, min_new_tokens=K + 1,
+                                     streamer=sink, **gen_kwargs)
+                out_host = out.cpu()
+                t_total = time.perf_counter() - t0
+                e2e_trials.append((model.rest_cost_mean, t_total))
+                assert len(sink.tokens) == K + 2 and torch.equal(out_host, out_dev.cpu()), "streamed and resident runs disagree"
+            barrier()
+            ms_e2e = 1e3 * sum(t[0] for t in e2e_trials) / len(e2e_trials)
+            e2e_total_ms = 1e3 * sum(t[1] for t in e2e_trials) / len(e2e_trials)
+            # the LowBitLinear launches alone (roofline of the GEMV kernel in its PDL chain)
+            ms_stream, stream_launches = linear_stream(model, dev, max(K, 20), W)
+            barrier()
     if world > 1:
-        t = torch.tensor([ms_dev, ms_e2e], device=dev, dtype=torch.float64)
+        t = torch.tensor([ms_dev, ms_e2e, ms_stream], device=dev, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms_dev, ms_e2e = float(t[0]), float(t[1])
-    if rank != 0:
-        if world > 1:
-            dist.destroy_process_group()
-        return
-    ms_step = ms_dev / args.steps
+        ms_dev, ms_e2e, ms_stream = float(t[0]), float(t[1]), float(t[2])
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
     except Exception:  # noqa: BLE001
         pass
+    prefill = prefill_numbers(model, dev, peaks) if (rank == 0 and not args.no_prefill) else None
+    del model
+    torch.cuda.empty_cache()
+    tp = None
+    if world > 1 and not args.no_tp:
+        tp = tp_numbers(args, dev, world, rank)
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
     peak = float(peaks.get("hbm_gbs", 6650.0))
-    achieved = algorithmic_bytes() / (ms_step * 1e-3) / 1e9
+    achieved = algorithmic_bytes() / (ms_stream * 1e-3) / 1e9
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
         c = cpu_reference(steps=3, warmup=1)
         cpu = {"value": c["value"], "unit": "tok/s", "cores": c["cores"], "kind": "port", "sample": c["sample"]}
-    # DRAM traffic of the dominant kernel from the committed `ncu --set full` capture (profiles/): the capture is
-    # of one gate_proj launch (11008x4096, 23,953,408 algorithmic bytes); scaled to the average launch of the step
     traffic = None
     try:
         prof = json.load(open(os.path.join(ROOT, "profiles", "ncu_full_gemv_r1_final_summary.json")))[0]
@@ -314,22 +498,40 @@ def run_ours(args):
         pass
     line = {
         "metric": "sym_int4 decode tok/s (Llama-2-7B, bs1); LowBitLinear GEMV GB/s vs HBM peak",
-        "value": world * 1e3 / ms_step, "unit": "tok/s", "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
-        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "u4 codes x f16 activations, f32 accumulate", "data": "synthetic",
-        "config": dict(workload_config(), cache="inputs larger than L2 (3.51 GB of weights per step)", cuda_graph=True,
-                       pdl=bool(args.pdl), fused_mlp=FUSED_MLP, l2_next_weight_hint=bool(args.l2_hint),
-                       parallelism="replicas" if world > 1 else "single"),
-        "e2e": {"value": world * 1e3 / (ms_e2e / args.steps), "unit": "tok/s", "h2d_bytes_per_step": HIDDEN * 2,
-                "d2h_bytes_per_step": 8},
-        "gpu_launches": n_launches() * args.steps * 2,
+        "value": world * 1e3 / ms_dev, "unit": "tok/s", "n_gpus": world, "steps": K, "warmup": W,
+        "ms_per_step": ms_dev, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "u4 codes x f16 activations, f32 accumulate; e5m2 KV cache", "data": "synthetic",
+        "config": dict(workload_config(K), **{"cache": "inputs larger than L2 (3.51 GB of weights per step)", "cuda_graph": True,
+                   "pdl": bool(args.pdl), "trials": 3,
+                   "parallelism": (f"replicas x{world} (value: independent copies of the 7B model, no data-path collective); "
+                                   f"parsed.tp: Llama-2-70B tensor parallel tp{world}") if world > 1 else "single"}),
+        "e2e": {"value": world * 1e3 / ms_e2e, "unit": "tok/s", "h2d_bytes_per_step": 8, "d2h_bytes_per_step": 8,
+                "how": "generate() with the prompt in pinned host memory and a streamer: every step's token goes to the host and is "
+                       "fed back from it (copy nodes of the step's graph), host clock over the decode steps",
+                "whole_call_ms": e2e_total_ms, "prompt_h2d_bytes": PROMPT_LEN * 8, "result_d2h_bytes": (PROMPT_LEN + K + 1) * 8},
+        "gpu_launches": int(launches_per_token * K * 6 + stream_launches * max(K, 20)),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": traffic, "traffic_source": "profiles/ncu_full_gemv_r1_final_summary.json: dram read+write of one "
                                                             "gate_proj launch = 1.0011 x its algorithmic bytes, scaled to the average launch",
                      "peak_source": "MEASURED_PEAKS.json hbm_gbs (copy)" if peaks else "fallback 6650",
-                     "kernel": "lowbit::gemv_kernel<sym_int4,f16,M=1>", "bytes_per_launch_avg": algorithmic_bytes() / n_launches()},
+                     "kernel": "lowbit::gemv_kernel<sym_int4,f16,M=1>", "bytes_per_launch_avg": algorithmic_bytes() / n_launches(),
+                     "measured_on": "parsed.linear_stream: the token's 129 LowBitLinear launches replayed alone from a CUDA graph "
+                                    "(the kernel's PDL chain without the attention / norm launches in between)",
+                     "launch_ms_avg": ms_stream / n_launches()},
+        "parsed": {
+            "generate": {"first_token_ms": first_ms, "rest_token_ms_device": ms_dev, "rest_token_ms_wall": ms_wall,
+                         "kernels_per_token": launches_per_token,
+                         "weights_GBps_in_generate": algorithmic_bytes() / (ms_dev * 1e-3) / 1e9,
+                         "frac_of_hbm_peak_in_generate": algorithmic_bytes() / (ms_dev * 1e-3) / 1e9 / peak},
+            "linear_stream": {"ms_per_token": ms_stream, "tok_per_s": 1e3 / ms_stream, "launches_per_token": stream_launches,
+                              "GBps": achieved, "note": "round 1's headline: LowBitLinear launches only, constant activations"},
+        },
         "clocks": clocks.summary(),
     }
+    if prefill:
+        line["parsed"]["prefill"] = prefill
+    if tp:
+        line["parsed"]["tp"] = tp
     if cpu:
         line["cpu_baseline"] = cpu
     print(json.dumps(line))
@@ -349,8 +551,11 @@ def run_reference(args):
         "value": c["value"], "unit": "tok/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": c["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "u4 codes x int8 activations (ggml mode A), f32 accumulate", "data": "synthetic",
-        "config": dict(workload_config(), arm="CPU restatement of the reference's ggml path (closed binary absent), "
-                                              "all host threads, bounded sample per step"),
+        "config": dict(workload_config(args.steps),
+                       arm="CPU restatement of the reference's ggml path (closed binary absent), all host threads; each step = a "
+                           "bounded sample of the token: one decoder layer's five GEMVs x32 + lm_head = the 161 LowBitLinear "
+                           "matrices (every weight byte of the token); attention over the KV cache, norms and rotary are NOT in "
+                           "the CPU sample (the GPU arm's step includes them)"),
         "cpu_baseline": {"value": c["value"], "unit": "tok/s", "cores": c["cores"], "kind": "port", "sample": c["sample"]},
         "e2e": {"value": c["value"], "unit": "tok/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
@@ -360,12 +565,14 @@ def run_reference(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=127)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--pdl", type=int, default=1)
     ap.add_argument("--l2-hint", type=int, default=0, dest="l2_hint")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-prefill", action="store_true")
+    ap.add_argument("--no-tp", action="store_true")
     ap.add_argument("--fused-mlp", type=int, default=1, dest="fused_mlp")
     args = ap.parse_args()
     global FUSED_MLP

@@ -176,14 +176,59 @@ int lowbit_sdp_fp8_cuda(const void* d_q, int q_dtype, const int64_t* q_strides, 
                         int S, int L, int D, void* d_out, int out_dtype, void* workspace, size_t workspace_bytes,
                         void* stream);
 
+/* lowbit_sdp_fp8_cuda for a decode step that is replayed from a CUDA graph: the key count is read on the device,
+ * L = min(*d_len + len_add, L_max), so one recorded launch serves every step.  L_max (the cache capacity the step
+ * was recorded for) fixes the grid and the workspace size (lowbit_sdp_fp8_workspace_size with L = L_max); no mask;
+ * causal as above.  No counterpart in the reference, whose XPU path issues every op from Python with host-side
+ * shapes (models/common.py:279-283). */
+int lowbit_sdp_fp8_devlen_cuda(const void* d_q, int q_dtype, const int64_t* q_strides, const void* d_k,
+                               const int64_t* k_strides, const void* d_v, const int64_t* v_strides, int causal,
+                               float scale, int B, int Hq, int Hkv, int S, int L_max, const int32_t* d_len,
+                               int len_add, int D, void* d_out, int out_dtype, void* workspace,
+                               size_t workspace_bytes, void* stream);
+
+/* RMSNorm -- xe_addons.rms_norm(weight, x_2d, eps) (models/common.py:187-200), with the arithmetic of the torch
+ * statement the reference uses off-XPU (models/common.py:201-205 = transformers' LlamaRMSNorm): fp32 statistics,
+ * x * rsqrt(mean(x^2) + eps) rounded to x_dtype, then times weight, rounded to y_dtype.  x [rows][hidden] and
+ * y [rows][hidden] with row strides in elements; weight [hidden]. */
+int lowbit_rms_norm_cuda(const void* d_x, int x_dtype, int64_t x_row_stride, const void* d_weight, int w_dtype,
+                         float eps, int64_t rows, int64_t hidden, void* d_y, int y_dtype, int64_t y_row_stride,
+                         void* stream);
+
+/* Rotary embedding of the merged qkv projection's output and the FP8 cache write in one launch -- the pair
+ * rotary_half_with_cache_inplaced(q, k, cos, sin) + DynamicFp8Cache.update -> xe_addons.quantize_key_value of the
+ * reference's attention forward (models/llama.py:146-183, models/utils.py:119-139).  d_qkv [B][S][(Hq + 2 Hkv) * D]
+ * (strides in elements): q heads are rotated in place; k heads are rotated, rounded to `dtype` and stored as e5m2 at
+ * cache position p0 + s; v heads are stored as e5m2.  p0 = (d_pos ? *d_pos : 0) + pos_add, read on the device.
+ * d_cos / d_sin: [n_positions][>= D/2] tables indexed by absolute position, rotate_half layout (full-width rotary,
+ * R == D).  Caches: uint8 [B][Hkv][capacity][D], strides {batch, head, position} in bytes; positions >= capacity are
+ * not written.  Same bytes as lowbit_rotary_inplaced_cuda followed by lowbit_kv_quantize_cuda. */
+int lowbit_rope_kv_append_cuda(void* d_qkv, int dtype, int64_t batch_stride, int64_t token_stride, int B, int S,
+                               int Hq, int Hkv, int D, const void* d_cos, const void* d_sin, int cs_dtype,
+                               int64_t cs_row_stride, int n_positions, const int32_t* d_pos, int pos_add,
+                               void* d_k_cache, const int64_t* k_strides, void* d_v_cache, const int64_t* v_strides,
+                               int capacity, void* stream);
+
+/* Greedy pick and step bookkeeping of a recorded decode step -- the torch.argmax + append of the reference's
+ * generate loop (utils/benchmark_util_4_47.py:3340-3380), done on the device so that steps replay without a host
+ * round trip.  logits [B][V]: d_next_ids[b] = index of the largest value (lowest index among equals);
+ * d_tokens[b][d_state[1]] = the same; then d_state[0] (tokens in the cache) and d_state[1] (tokens generated) += 1.
+ * d_state: int32[8] {cache length, tokens generated, 0 (the kernel's arrival counter), suppress_below, n_suppress, ...}.
+ * d_suppress_ids (may be NULL): while d_state[1] < suppress_below, the first n_suppress (<= 8) ids in it cannot be
+ * picked -- transformers' min_new_tokens rule for end-of-sequence ids. */
+int lowbit_greedy_advance_cuda(const void* d_logits, int dtype, int64_t row_stride, int B, int V, int64_t* d_next_ids,
+                               int64_t* d_tokens, int64_t tokens_row_stride, int tokens_capacity, int32_t* d_state,
+                               const int64_t* d_suppress_ids, void* stream);
+
 /* canonical <-> device layout on device buffers (same byte size, src != dst).
  * to_device != 0: canonical -> tiled ; 0: tiled -> canonical. */
 int lowbit_relayout_cuda(const void* d_src, void* d_dst, int64_t rows, int64_t k, int qtype,
                          int to_device, void* stream);
 
-/* bytes of workspace lowbit_matmul_cuda needs for this problem (split-K partials, arrival
- * counters, fp32-activation split planes).  The workspace must be zero-filled once before
- * its first use and may then be reused by any number of calls that do not overlap in time. */
+/* bytes of workspace lowbit_matmul_cuda needs for this problem: the three bf16 planes an fp32 activation
+ * chunk is split into (GEMV), or the fp32 partial sums of the K-split small-batch GEMM; 0 for fp16 / bf16
+ * activations on the GEMV.  Nothing in it has to be initialised; it may be reused by any number of calls
+ * that do not overlap in time. */
 size_t lowbit_matmul_workspace_size(int64_t n_rows, int64_t k, int64_t m, int x_dtype);
 
 /* y[M][N] (+)= x[M][K] . dequant(W[N][K])^T  -- the XPU-side op `xe_linear.forward_new` /
@@ -191,9 +236,15 @@ size_t lowbit_matmul_workspace_size(int64_t n_rows, int64_t k, int64_t m, int x_
  * d_w: weight in the DEVICE (tiled) layout.  d_x: [M][K] of x_dtype, row stride k.
  * d_y: [M][N] of y_dtype, row stride n_rows.  d_bias: NULL or [N] of y_dtype (added once).
  * accumulate != 0: y += result (residual add), else y = result.
- * workspace: NULL (library-owned per-device workspace; serialises callers on one device) or a
- * zero-initialised buffer of at least lowbit_matmul_workspace_size() bytes.
- * Any M >= 1: M <= 64 runs the HBM-bound GEMV kernel, larger M the tensor-core GEMM. */
+ * workspace: a buffer of at least lowbit_matmul_workspace_size() bytes, or NULL = one library-owned buffer per
+ * device.  The NULL mode is for ONE stream per device and must not be used under stream capture: calls are
+ * serialised on the host only (two streams would race on the buffer on the GPU), and growing the buffer
+ * synchronises the device and reallocates.
+ * Any M >= 1.  fp16 / bf16 activations: M <= 32 runs the HBM-bound GEMV kernel, larger M the tensor-core GEMM
+ * (activations and expanded weights enter the MMA as fp16 / bf16, fp32 accumulation: about 1e-3 * sum|x w|).
+ * fp32 activations: always the GEMV (chunks of 32 rows), which keeps them to 2^-24 -- the fp32-in / fp32-out
+ * contract of ggml_compute_forward_mul_mat_q_fp32; cast to fp16 first to trade that precision for the GEMM,
+ * as the reference's XPU path does (LBL:700-705). */
 int lowbit_matmul_cuda(const void* d_w, int qtype, int64_t n_rows, int64_t k,
                        const void* d_x, int x_dtype, int64_t m,
                        void* d_y, int y_dtype, const void* d_bias, int accumulate,
@@ -252,6 +303,7 @@ int lowbit_matmul_f32_noalloc_cuda(const void* d_w, int qtype, int64_t n_rows, i
  * kernel may start streaming its weights while the previous kernel on the stream drains; it
  * reads activations only after griddepcontrol.wait.  Process-wide switch, default off. */
 void lowbit_set_programmatic_dependent_launch(int on);
+int lowbit_get_programmatic_dependent_launch(void);
 
 /* One-shot hint consumed by the next lowbit_matmul_cuda on the calling thread: the device
  * pointer and size of the weights the FOLLOWING matmul on the same stream will read (in a decoder

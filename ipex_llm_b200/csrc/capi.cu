@@ -110,6 +110,7 @@ int b200_lowbit_last_launch_count(void) { return t_launches; }
 int b200_lowbit_sm_count(void) { return have_device() ? sm_count() : 0; }
 void b200_lowbit_set_row_length(int k) { t_row_len = k; }
 void lowbit_set_programmatic_dependent_launch(int on) { gemv_set_pdl(on); }
+int lowbit_get_programmatic_dependent_launch(void) { return gemv_get_pdl(); }
 void lowbit_hint_next_weights(const void* d_w, size_t bytes) { gemv_set_next_weights(d_w, bytes); }
 /* development aid, not in the public header: per-warp phase timestamps of the GEMV kernel */
 void lowbit_debug_set_timestamps(void* dev_ptr) { gemv_set_debug_timestamps(dev_ptr); }
@@ -158,20 +159,24 @@ int lowbit_relayout_cuda(const void* d_src, void* d_dst, int64_t rows, int64_t k
     return rc;
 }
 
-static bool use_gemm(int qtype, int64_t n_rows, int64_t k, int64_t m) {
+// fp32 activations never take the tensor-core GEMM: it rounds them to one bf16 plane (2^-9), while the GEMV keeps
+// them to 2^-24 (three planes) -- the fp32-in / fp32-out contract of ggml_compute_forward_mul_mat_q_fp32
+// (LBL:494-529).  Larger fp32 batches run as chunks of the GEMV; a caller that accepts half precision casts first,
+// as the reference's XPU path does (LBL:700-705, conver_to_half).
+static bool use_gemm(int qtype, int64_t n_rows, int64_t k, int64_t m, int x_dtype) {
     static const int64_t max_m = [] { const char* e = getenv("LOWBIT_GEMV_MAX_M"); return e ? (int64_t)atoi(e) : kGemvMaxM; }();   // development
-    return m > max_m && gemm_tc_supported(qtype, n_rows, k);
+    return x_dtype != DT_F32 && m > max_m && gemm_tc_supported(qtype, n_rows, k);
 }
 
 size_t lowbit_matmul_workspace_size(int64_t n_rows, int64_t k, int64_t m, int x_dtype) {
-    if (use_gemm(B200_QT_SYM_INT4, n_rows, k, m)) return gemm_tc_workspace_size(n_rows, k, m, x_dtype);
+    if (use_gemm(B200_QT_SYM_INT4, n_rows, k, m, x_dtype)) return gemm_tc_workspace_size(n_rows, k, m, x_dtype);
     return gemv_workspace_size(n_rows, k, m, x_dtype);
 }
 
 static int matmul_dispatch(const void* d_w, int qtype, int64_t n_rows, int64_t k, const void* d_x, int x_dtype, int64_t m,
                            void* d_y, int y_dtype, const void* d_bias, int accumulate, void* workspace, size_t workspace_bytes,
                            cudaStream_t st) {
-    if (use_gemm(qtype, n_rows, k, m)) {
+    if (use_gemm(qtype, n_rows, k, m, x_dtype)) {
         int64_t done = 0;
         return gemm_tc_launch(d_w, qtype, n_rows, k, d_x, x_dtype, m, d_y, y_dtype, d_bias, accumulate, workspace,
                               workspace_bytes, st, &done);

@@ -328,8 +328,9 @@ extern "C" int lowbit_matmul_f32_noalloc_cuda(const void* d_w, int qtype, int64_
                                               int64_t m, void* d_y, int y_dtype, const void* d_bias, int accumulate,
                                               void* stream) {
     using namespace lowbit;
+    reset_launch_count();
     if (m == 0 || n_rows == 0) return LB_OK;
-    if (m < 0 || k <= 0 || (uint64_t)m * (uint64_t)k > kNoAllocMaxElems) {
+    if (m < 0 || k <= 0 || (uint64_t)m > kNoAllocMaxElems / (uint64_t)k) {       // no m * k product: it could wrap
         set_error(LB_ERR_ARG, "lowbit_matmul_f32_noalloc_cuda: m * k = %lld x %lld exceeds the built-in scratch (%zu activation "
                   "elements); use lowbit_matmul_cuda with a caller workspace", (long long)m, (long long)k, kNoAllocMaxElems);
         return LB_ERR_ARG;
@@ -343,5 +344,7 @@ extern "C" int lowbit_matmul_f32_noalloc_cuda(const void* d_w, int qtype, int64_
                      sizeof(g_noalloc_scratch), (cudaStream_t)stream);
     if (rc == LB_ERR_ARG) set_error(rc, "lowbit_matmul_f32_noalloc_cuda: bad argument (qtype %d, N %lld, K %lld, M %lld)", qtype,
                                     (long long)n_rows, (long long)k, (long long)m);
+    else if (rc == LB_ERR_WORKSPACE) set_error(rc, "lowbit_matmul_f32_noalloc_cuda: built-in scratch too small for M %lld, K %lld",
+                                               (long long)m, (long long)k);
     return rc;
 }

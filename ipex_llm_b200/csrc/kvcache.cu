@@ -75,10 +75,21 @@ struct SdpArgs {
     float scale_log2e;                                             // scale * log2(e)
     int B, Hq, Hkv, S, L, D;
     int n_split, keys_per_split;
+    const int* len_ptr; int len_add;                               // non-NULL: the key count is *len_ptr + len_add (<= L), read on the device
     int rt;                                                        // query rows per CTA (1, 2 or 4)
     float* part;                                                   // [B][Hkv][row tiles][n_split][RT * (D + 2)]
     void* out; int out_dtype;                                      // [B][Hq][S][D] contiguous
 };
+
+// key count and keys per split of this launch: the host's values, or -- when the cache length lives in device memory
+// (a decode step replayed from a CUDA graph) -- derived from it with the host's split count
+__device__ __forceinline__ void sdp_lengths(const SdpArgs& A, int& L, int& keys_per_split) {
+    L = A.L; keys_per_split = A.keys_per_split;
+    if (A.len_ptr) {
+        L = min(max(*A.len_ptr + A.len_add, 0), A.L);
+        keys_per_split = ((L + A.n_split - 1) / A.n_split + 31) / 32 * 32;
+    }
+}
 
 __device__ __forceinline__ float load_as_float(const void* p, int dt, int64_t i) {
     if (dt == DT_F32) return ((const float*)p)[i];
@@ -141,8 +152,10 @@ sdp_fp8_decode_kernel(const SdpArgs A) {
     }
     __syncthreads();
 
-    const int key_begin = split * A.keys_per_split;
-    const int key_end = min(A.L, key_begin + A.keys_per_split);
+    int L, keys_per_split;
+    sdp_lengths(A, L, keys_per_split);
+    const int key_begin = split * keys_per_split;
+    const int key_end = min(L, key_begin + keys_per_split);
     const uint8_t* kb = A.k + b * A.k_sb + hkv * A.k_sh;
     const uint8_t* vb = A.v + b * A.v_sb + hkv * A.v_sh;
 
@@ -182,7 +195,7 @@ sdp_fp8_decode_kernel(const SdpArgs A) {
         for (int r = 0; r < RT; r++) {
             const int rr = row0 + r;
             bool ok = live && r < n_rows;
-            if (ok && A.causal) ok = key <= A.L - A.S + (rr % A.S);
+            if (ok && A.causal) ok = key <= L - A.S + (rr % A.S);
             if (ok && A.mask) {
                 const int hq = hkv * n_rep + rr / A.S, st = rr % A.S;
                 sc[r] += load_as_float(A.mask, A.mask_dtype, b * A.m_sb + hq * A.m_sh + st * A.m_ss + key) * 1.4426950408889634f;
@@ -428,11 +441,11 @@ extern "C" size_t lowbit_sdp_fp8_workspace_size(int B, int Hq, int Hkv, int S, i
     return a > m ? a : m;
 }
 
-extern "C" int lowbit_sdp_fp8_cuda(const void* d_q, int q_dtype, const int64_t* q_strides, const void* d_k,
-                                   const int64_t* k_strides, const void* d_v, const int64_t* v_strides, const void* d_mask,
-                                   int mask_dtype, const int64_t* mask_strides, int causal, float scale, int B, int Hq,
-                                   int Hkv, int S, int L, int D, void* d_out, int out_dtype, void* workspace,
-                                   size_t workspace_bytes, void* stream) {
+static int sdp_launch(const void* d_q, int q_dtype, const int64_t* q_strides, const void* d_k,
+                      const int64_t* k_strides, const void* d_v, const int64_t* v_strides, const void* d_mask,
+                      int mask_dtype, const int64_t* mask_strides, int causal, float scale, int B, int Hq,
+                      int Hkv, int S, int L, int D, void* d_out, int out_dtype, void* workspace,
+                      size_t workspace_bytes, void* stream, const int* d_len, int len_add) {
     reset_launch_count();
     if (!d_q || !d_k || !d_v || !d_out || !q_strides || !k_strides || !v_strides || (d_mask && !mask_strides) ||
         q_dtype < 0 || q_dtype > 2 || out_dtype < 0 || out_dtype > 2 || (d_mask && (mask_dtype < 0 || mask_dtype > 2)) ||
@@ -458,6 +471,7 @@ extern "C" int lowbit_sdp_fp8_cuda(const void* d_q, int q_dtype, const int64_t* 
     A.m_sb = d_mask ? mask_strides[0] : 0; A.m_sh = d_mask ? mask_strides[1] : 0; A.m_ss = d_mask ? mask_strides[2] : 0;
     A.causal = causal; A.scale_log2e = scale * 1.4426950408889634f;
     A.B = B; A.Hq = Hq; A.Hkv = Hkv; A.S = S; A.L = L; A.D = D;
+    A.len_ptr = d_len; A.len_add = len_add;
     // the tensor-core kernel reads value rows in 16-byte (head_dim 128) / 8-byte (64) pieces
     // ... and query rows as 16-byte pieces
     const bool mma = sdp_use_mma(q_dtype, D) && scale > 0.0f && !(((uintptr_t)d_v | (uintptr_t)v_strides[0] | (uintptr_t)v_strides[1] | (uintptr_t)v_strides[2]) & 15) &&
@@ -517,4 +531,23 @@ extern "C" int lowbit_sdp_fp8_cuda(const void* d_q, int q_dtype, const int64_t* 
     cudaLaunchKernelEx(&cfg, sdp_fp8_combine_kernel, A, tiles);
     note_launch();
     return check_launch();
+}
+
+extern "C" int lowbit_sdp_fp8_cuda(const void* d_q, int q_dtype, const int64_t* q_strides, const void* d_k,
+                                   const int64_t* k_strides, const void* d_v, const int64_t* v_strides, const void* d_mask,
+                                   int mask_dtype, const int64_t* mask_strides, int causal, float scale, int B, int Hq,
+                                   int Hkv, int S, int L, int D, void* d_out, int out_dtype, void* workspace,
+                                   size_t workspace_bytes, void* stream) {
+    return sdp_launch(d_q, q_dtype, q_strides, d_k, k_strides, d_v, v_strides, d_mask, mask_dtype, mask_strides, causal, scale,
+                      B, Hq, Hkv, S, L, D, d_out, out_dtype, workspace, workspace_bytes, stream, nullptr, 0);
+}
+
+extern "C" int lowbit_sdp_fp8_devlen_cuda(const void* d_q, int q_dtype, const int64_t* q_strides, const void* d_k,
+                                          const int64_t* k_strides, const void* d_v, const int64_t* v_strides, int causal,
+                                          float scale, int B, int Hq, int Hkv, int S, int L_max, const int32_t* d_len,
+                                          int len_add, int D, void* d_out, int out_dtype, void* workspace,
+                                          size_t workspace_bytes, void* stream) {
+    if (!d_len) { set_error(LB_ERR_ARG, "lowbit_sdp_fp8_devlen_cuda: d_len is NULL"); return LB_ERR_ARG; }
+    return sdp_launch(d_q, q_dtype, q_strides, d_k, k_strides, d_v, v_strides, nullptr, 0, nullptr, causal, scale,
+                      B, Hq, Hkv, S, L_max, D, d_out, out_dtype, workspace, workspace_bytes, stream, d_len, len_add);
 }

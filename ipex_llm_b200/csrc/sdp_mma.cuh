@@ -80,13 +80,15 @@ sdp_fp8_decode_mma_kernel(const SdpArgs A) {
         }
     }
 
-    const int key_begin = split * A.keys_per_split;
-    const int key_end = min(A.L, key_begin + A.keys_per_split);
+    int L, keys_per_split;
+    sdp_lengths(A, L, keys_per_split);
+    const int key_begin = split * keys_per_split;
+    const int key_end = min(L, key_begin + keys_per_split);
     const uint8_t* kb = A.k + b * A.k_sb + hkv * A.k_sh + 16 * t;
     const uint8_t* vb = A.v + b * A.v_sb + hkv * A.v_sh + BPL * g;
     const int64_t mask_base = b * A.m_sb + my_hq * A.m_sh + my_st * A.m_ss;
-    const int causal_last = A.causal ? A.L - A.S + my_st : A.L;       // last key this lane's row sees
-    const int causal_first = A.causal ? A.L - A.S : A.L;              // ... and the first row of the tile at least
+    const int causal_last = A.causal ? L - A.S + my_st : L;           // last key this lane's row sees
+    const int causal_first = A.causal ? L - A.S : L;                  // ... and the first row of the tile at least
 
     float m_run = -CUDART_INF_F;                      // of row g, the same in the quad's four lanes
     float o[BPL][2], ol[2] = {0.0f, 0.0f};            // row g: columns BPL (2t + i) + u;  ol = softmax denominator

@@ -308,10 +308,16 @@ def lowbit_moe_cuda(d_x, x_dtype, d_ids, ids_dtype, d_weight, weight_dtype, top_
 
 _lib.lowbit_set_programmatic_dependent_launch.argtypes = [ctypes.c_int]
 _lib.lowbit_set_programmatic_dependent_launch.restype = None
+_lib.lowbit_get_programmatic_dependent_launch.argtypes = []
+_lib.lowbit_get_programmatic_dependent_launch.restype = ctypes.c_int
 
 
 def lowbit_set_programmatic_dependent_launch(on):
     _lib.lowbit_set_programmatic_dependent_launch(int(bool(on)))
+
+
+def lowbit_get_programmatic_dependent_launch():
+    return bool(_lib.lowbit_get_programmatic_dependent_launch())
 
 
 _lib.lowbit_hint_next_weights.argtypes = [ctypes.c_void_p, ctypes.c_size_t]
@@ -451,3 +457,59 @@ def lowbit_matmul_allreduce(w, qtype, n_rows, k, x, y, bias, accumulate, peer_pt
                                              int(bool(accumulate)), arr, rank, len(peer_ptrs), max_bytes,
                                              workspace.data_ptr() if workspace is not None else None,
                                              workspace.numel() if workspace is not None else 0, stream), "lowbit_matmul_allreduce_cuda")
+
+
+# ---- the small operators of a recorded decode step (csrc/decode_ops.cu, csrc/kvcache.cu)
+_I32P = ctypes.c_void_p
+_lib.lowbit_rms_norm_cuda.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_void_p, ctypes.c_int, ctypes.c_float,
+                                      ctypes.c_int64, ctypes.c_int64, ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_void_p]
+_lib.lowbit_rms_norm_cuda.restype = ctypes.c_int
+_lib.lowbit_rope_kv_append_cuda.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_int64] + [ctypes.c_int] * 5 + \
+                                           [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_int, _I32P, ctypes.c_int,
+                                            ctypes.c_void_p, _I64P, ctypes.c_void_p, _I64P, ctypes.c_int, ctypes.c_void_p]
+_lib.lowbit_rope_kv_append_cuda.restype = ctypes.c_int
+_lib.lowbit_sdp_fp8_devlen_cuda.argtypes = [ctypes.c_void_p, ctypes.c_int, _I64P, ctypes.c_void_p, _I64P, ctypes.c_void_p, _I64P,
+                                            ctypes.c_int, ctypes.c_float] + [ctypes.c_int] * 5 + [_I32P, ctypes.c_int, ctypes.c_int,
+                                            ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p]
+_lib.lowbit_sdp_fp8_devlen_cuda.restype = ctypes.c_int
+_lib.lowbit_greedy_advance_cuda.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_int, ctypes.c_int, ctypes.c_void_p,
+                                            ctypes.c_void_p, ctypes.c_int64, ctypes.c_int, _I32P, ctypes.c_void_p, ctypes.c_void_p]
+_lib.lowbit_greedy_advance_cuda.restype = ctypes.c_int
+
+
+def lowbit_rms_norm(x_2d, weight, eps, out, stream):
+    """x_2d [rows, hidden] (last dim contiguous), weight [hidden] -> out [rows, hidden]"""
+    rows, hidden = x_2d.shape
+    _check(_lib.lowbit_rms_norm_cuda(x_2d.data_ptr(), _DT_OF[str(x_2d.dtype)], x_2d.stride(0), weight.data_ptr(),
+                                     _DT_OF[str(weight.dtype)], float(eps), rows, hidden, out.data_ptr(), _DT_OF[str(out.dtype)],
+                                     out.stride(0), stream), "lowbit_rms_norm_cuda")
+
+
+def lowbit_rope_kv_append(qkv, n_heads, n_kv_heads, head_dim, cos, sin, pos, pos_add, k_cache, v_cache, stream):
+    """qkv [B, S, (Hq + 2 Hkv) * D]; cos / sin [positions, >= D/2] tables; pos: int32 device scalar or None;
+    k_cache / v_cache uint8 [B, Hkv, capacity, D]"""
+    B, S = qkv.shape[0], qkv.shape[1]
+    _check(_lib.lowbit_rope_kv_append_cuda(qkv.data_ptr(), _DT_OF[str(qkv.dtype)], qkv.stride(0), qkv.stride(1), B, S, n_heads,
+                                           n_kv_heads, head_dim, cos.data_ptr(), sin.data_ptr(), _DT_OF[str(cos.dtype)],
+                                           cos.stride(0), cos.shape[0], pos.data_ptr() if pos is not None else None, int(pos_add),
+                                           k_cache.data_ptr(), _strides3(k_cache), v_cache.data_ptr(), _strides3(v_cache),
+                                           k_cache.shape[2], stream), "lowbit_rope_kv_append_cuda")
+
+
+def lowbit_sdp_fp8_devlen(q, k, v, causal, scale, kv_len, len_add, out, workspace, stream):
+    """q [B, Hq, S, D] view; k / v uint8 [B, Hkv, capacity, D]; kv_len: int32 device scalar (keys = kv_len + len_add)"""
+    B, Hq, S, D = q.shape
+    Hkv, L_max = k.shape[1], k.shape[2]
+    _check(_lib.lowbit_sdp_fp8_devlen_cuda(q.data_ptr(), _DT_OF[str(q.dtype)], _strides3(q), k.data_ptr(), _strides3(k), v.data_ptr(),
+                                           _strides3(v), int(bool(causal)), float(scale), B, Hq, Hkv, S, L_max, kv_len.data_ptr(),
+                                           int(len_add), D, out.data_ptr(), _DT_OF[str(out.dtype)], workspace.data_ptr(),
+                                           workspace.numel() * workspace.element_size(), stream), "lowbit_sdp_fp8_devlen_cuda")
+
+
+def lowbit_greedy_advance(logits, next_ids, tokens, state, stream, suppress_ids=None):
+    """logits [B, V]; next_ids int64 [B]; tokens int64 [B, capacity]; state int32 [8]; suppress_ids int64 [8] or None"""
+    B, V = logits.shape
+    _check(_lib.lowbit_greedy_advance_cuda(logits.data_ptr(), _DT_OF[str(logits.dtype)], logits.stride(0), B, V, next_ids.data_ptr(),
+                                           tokens.data_ptr(), tokens.stride(0), tokens.shape[1], state.data_ptr(),
+                                           suppress_ids.data_ptr() if suppress_ids is not None else None, stream),
+           "lowbit_greedy_advance_cuda")

@@ -87,11 +87,13 @@ def load_low_bit(model, model_path):
     low_bit = cfg.get("bigdl_transformers_low_bit", False)
     invalidInputError(low_bit, "Detect this model is not a low-bit model, please use optimize_model first.")
     qtype = ggml_tensor_qtype[low_bit]
-    model = ggml_convert_low_bit(model, qtype=qtype, convert_shape_only=True, device="meta",
+    # the saved keys follow the forwards the model was saved with (merged qkv_proj or separate q/k/v)
+    model = ggml_convert_low_bit(model, qtype=qtype, optimize_model=bool(cfg.get("bigdl_optimize_llm", True)),
+                                 convert_shape_only=True, device="meta",
                                  mixed_precision=cfg.get("bigdl_lm_head_low_bit") is not None)
     state = torch.load(os.path.join(model_path, PYTORCH_MODEL_NAME), map_location="cpu", weights_only=True)
     assign_low_bit_state_dict(model, state)
-    model._bigdl_config = {"bigdl_transformers_low_bit": low_bit}
+    model._bigdl_config = {"bigdl_transformers_low_bit": low_bit, "bigdl_optimize_llm": bool(cfg.get("bigdl_optimize_llm", True))}
     if cfg.get("bigdl_lm_head_low_bit") is not None:
         model._bigdl_config["bigdl_lm_head_low_bit"] = cfg["bigdl_lm_head_low_bit"]
     model.save_low_bit = types.MethodType(_save_low_bit, model)
@@ -126,7 +128,7 @@ def optimize_model(model, low_bit="sym_int4", optimize_llm=True, modules_to_not_
                                      torch_dtype=kwargs.get("torch_dtype", "auto"),
                                      embedding_qtype=_embedding_qtype(kwargs.get("embedding_qtype", None)),
                                      mixed_precision=bool(kwargs.get("mixed_precision", False)))
-    model._bigdl_config = {"bigdl_transformers_low_bit": low_bit}
+    model._bigdl_config = {"bigdl_transformers_low_bit": low_bit, "bigdl_optimize_llm": bool(optimize_llm)}
     if low_bit is not None and kwargs.get("mixed_precision", False):
         from ipex_llm_b200.transformers.convert import MIXED_LM_HEAD_QTYPE
         model._bigdl_config["bigdl_lm_head_low_bit"] = MIXED_LM_HEAD_QTYPE

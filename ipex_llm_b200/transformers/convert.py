@@ -3,10 +3,13 @@ reference's ipex_llm/transformers/convert.py (CV below) that CONSTRUCTS the hot 
 (``is_linear_module`` CV:138-234, ``is_lm_head`` CV:126-130, ``use_scale_search`` CV:459-469,
 ``_replace_with_low_bit_linear`` CV:472-752, ``ggml_convert_low_bit`` CV:1092-1193).
 
-Out of scope here: GPTQ/AWQ importers, vLLM/DeepSpeed module detection, embeddings,
-and the per-model forward patches of ``_optimize_pre`` / ``_optimize_post`` (qkv merging, fused MLP,
-attention kernels) -- the stock Hugging Face forwards run unchanged on top of ``LowBitLinear``.
+``_optimize_pre`` (CV:890-1089) and ``_optimize_post`` (CV:1275-2140) are built for the two model families the
+hot path's configs name, llama (CV:1000-1003, 1327-1340) and mistral (CV:1007-1009, 1724-1735): q/k/v merged
+into one ``qkv_proj`` before quantisation, and the attention / MLP / RMSNorm / model forwards replaced by the ones
+in ``transformers/models`` that call the fused operators.  ``optimize_model=False`` leaves the stock Hugging Face
+forwards on top of ``LowBitLinear``.  The reference's 40 other model families are out of scope.
 """
+import types
 import logging
 import os
 import warnings
@@ -21,10 +24,18 @@ logger = logging.getLogger("ipex_llm_b200")
 
 
 def is_linear_module(module):
-    """CV:138-234 reduced to the plain ``nn.Linear`` case: (is_linear, (in, out, mp_group))"""
+    """CV:138-234: (is_linear, (in, out, mp_group)).  Besides ``nn.Linear`` this recognises DeepSpeed AutoTP's
+    already-sharded layers (CV:217-228) by class name -- ``LinearLayer`` (column-parallel: no communication) and
+    ``LinearAllreduce`` (row-parallel: carries ``mp_group``, the output is summed over it) -- whose ``weight`` is the
+    local ``[out, in]`` shard; DeepSpeed itself is not imported."""
     from ipex_llm_b200.transformers.low_bit_linear import LowBitLinear
     if isinstance(module, nn.Linear) and not isinstance(module, LowBitLinear):
         return True, (module.in_features, module.out_features, None)
+    cls = module.__class__.__name__
+    if cls in ("LinearLayer", "LinearAllreduce") and getattr(module, "weight", None) is not None and module.weight.dim() == 2:
+        out_features, in_features = module.weight.shape
+        mp_group = getattr(module, "mp_group", None) if cls == "LinearAllreduce" else None
+        return True, (in_features, out_features, mp_group)
     return False, None
 
 
@@ -115,6 +126,58 @@ def convert_bigdl_other_module(model, dtype):
         module.to(dtype)
 
 
+def convert_forward(m, target_m, new_forward):
+    """CV:1232-1242 (convert_forward): rebind ``forward`` on every module of class ``target_m``"""
+    for _, sub_m in m.named_children():
+        if sub_m.__class__ == target_m:
+            bound_method = new_forward.__get__(sub_m, sub_m.__class__)
+            setattr(sub_m, "forward", bound_method)
+        convert_forward(sub_m, target_m, new_forward)
+
+
+def _optimize_pre(model, qtype=None):
+    """CV:890-1089, llama (CV:1000-1003) and mistral (CV:1007-1009) branches: merge q/k/v into ``qkv_proj``
+    BEFORE the linears are quantised (one GEMV instead of three per layer)."""
+    model_type = getattr(getattr(model, "config", None), "model_type", None)
+    if model_type == "llama":
+        from ipex_llm_b200.transformers.models.llama import merge_qkv
+        model.apply(merge_qkv)
+    elif model_type == "mistral":
+        from ipex_llm_b200.transformers.models.mistral import merge_qkv
+        model.apply(merge_qkv)
+    return model
+
+
+def _optimize_post(model):
+    """CV:1275-2140, llama (CV:1327-1340) and mistral (CV:1724-1735) branches: RMSNorm -> rms_norm_forward, MLP ->
+    mlp_silu_forward (fused gate/up at decode sizes), Model -> *_model_forward (KV-cache class), Attention ->
+    *_attention_forward (qkv GEMV, in-place rotary, FP8 cache, fused decode attention).  Also installs the recorded
+    decode step behind ``generate`` (transformers/decode_graph.py)."""
+    import importlib
+    model_type = getattr(getattr(model, "config", None), "model_type", None)
+    from ipex_llm_b200.transformers.models.common import rms_norm_forward, mlp_silu_forward
+    if model_type == "llama":
+        module = importlib.import_module(model.__class__.__module__)
+        from ipex_llm_b200.transformers.models.llama import llama_model_forward, llama_attention_forward
+        convert_forward(model, module.LlamaRMSNorm, rms_norm_forward)
+        convert_forward(model, module.LlamaMLP, mlp_silu_forward)
+        convert_forward(model, module.LlamaModel, llama_model_forward)
+        convert_forward(model, module.LlamaAttention, llama_attention_forward)
+    elif model_type == "mistral":
+        module = importlib.import_module(model.__class__.__module__)
+        from ipex_llm_b200.transformers.models.mistral import mistral_model_forward, mistral_attention_forward
+        convert_forward(model, module.MistralRMSNorm, rms_norm_forward)
+        convert_forward(model, module.MistralMLP, mlp_silu_forward)
+        convert_forward(model, module.MistralModel, mistral_model_forward)
+        convert_forward(model, module.MistralAttention, mistral_attention_forward)
+    else:
+        return model
+    if hasattr(model, "generate"):
+        from ipex_llm_b200.transformers.decode_graph import install_fast_generate
+        install_fast_generate(model)
+    return model
+
+
 def ggml_convert_low_bit(model, qtype, optimize_model=True, convert_shape_only=False, device="cpu",
                          modules_to_not_convert=None, torch_dtype="auto", embedding_qtype=None, mixed_precision=False,
                          **unused):
@@ -124,6 +187,8 @@ def ggml_convert_low_bit(model, qtype, optimize_model=True, convert_shape_only=F
     invalidInputError(qtype in B200_SUPPORTED_QTYPE_IDS,
                       f"qtype {qtype} is not implemented by the B200 low-bit kernels")
     model_config = getattr(model, "config", None)
+    if optimize_model:
+        model = _optimize_pre(model, qtype)                 # CV:1133
     enable_scale_search = use_scale_search(model_config, qtype)
     model, has_been_replaced = _replace_with_low_bit_linear(model, qtype, modules_to_not_convert or [],
                                                             convert_shape_only, model_config=model_config,
@@ -133,6 +198,8 @@ def ggml_convert_low_bit(model, qtype, optimize_model=True, convert_shape_only=F
         warnings.warn("No linear modules were found in your model.")
     elif device == "cpu" and torch_dtype != "auto":
         convert_bigdl_other_module(model, torch_dtype)
+    if optimize_model:
+        model = _optimize_post(model)                       # CV:1174
     return model
 
 

@@ -8,12 +8,16 @@ scheme.  The byte format (e5m2, no scales) is defined by the kernels in csrc/kvc
 import math
 from typing import Any, Dict, Optional, Tuple
 
+import os
+
 import torch
+from transformers.cache_utils import Cache, DynamicLayer
 
 import ipex_llm_b200.ggml.model.llama.llama_cpp as ggml
 from ipex_llm_b200.utils.common import invalidInputError
 
 FP8_KV_ALLOC_LENGTH = 512
+KV_ALLOC_BLOCK_LENGTH = int(os.environ.get("KV_CACHE_ALLOC_BLOCK_LENGTH", 256))
 
 
 def _stream(device):
@@ -68,42 +72,137 @@ def restore_fp8_kv_cache(k_cache, v_cache, dtype):
     return key_states, value_states
 
 
-class DynamicFp8Cache:
-    """kv.py:33-77.  Same ``update`` contract as the reference class (returns the uint8 cache views of the layer).
-    The reference subclasses transformers' DynamicCache; its internals changed across transformers versions
-    (the reference carries work-arounds for 4.37 / 4.39 / 4.45), so this class keeps its own two lists and
-    offers the methods decoders use: ``update``, ``get_seq_length``, ``__len__``, ``__getitem__``."""
+class Fp8KVLayer(DynamicLayer):
+    """One layer of the FP8 cache: uint8 views [B, H, len, D] over a storage that is allocated FP8_KV_ALLOC_LENGTH
+    positions ahead (init_fp8_kv_cache / append_fp8_kv_cache, the reference's scheme).  ``reserve`` = positions to
+    allocate at once (a generate() call knows prompt + new tokens); ``storage`` = (k, v) uint8 [B, H, capacity, D]
+    tensors owned by somebody else (the recorded decode step keeps its caches at fixed addresses)."""
 
-    def __init__(self, num_hidden_layers: Optional[int] = None) -> None:
-        self.key_cache = []
-        self.value_cache = []
-        self._seen_tokens = 0
+    def __init__(self, reserve: int = 0, storage=None):
+        super().__init__()
+        self.reserve = int(reserve)
+        self.storage = storage
 
-    def update(self, key_states: torch.Tensor, value_states: torch.Tensor, layer_idx: int,
-               cache_kwargs: Optional[Dict[str, Any]] = None) -> Tuple[torch.Tensor, torch.Tensor]:
+    def lazy_initialization(self, key_states, value_states):
+        self.dtype, self.device = key_states.dtype, key_states.device
         batch_size, num_heads, seq_len, head_dim = key_states.shape
-        if layer_idx == 0:
-            self._seen_tokens += seq_len
-        if len(self.key_cache) <= layer_idx:
-            k_cache, v_cache = init_fp8_kv_cache(batch_size, num_heads, seq_len, head_dim, device=key_states.device)
-            k_cache, v_cache = append_fp8_kv_cache(k_cache, v_cache, key_states, value_states)
-            self.key_cache.append(k_cache)
-            self.value_cache.append(v_cache)
+        if self.storage is not None:
+            ks, vs = self.storage
+            invalidInputError(ks.shape[0] == batch_size and ks.shape[1] == num_heads and ks.shape[3] == head_dim,
+                              "bound cache storage does not match the key states")
+            self.keys = ks.as_strided((batch_size, num_heads, 0, head_dim), ks.stride(), storage_offset=0)
+            self.values = vs.as_strided((batch_size, num_heads, 0, head_dim), vs.stride(), storage_offset=0)
         else:
-            k_cache, v_cache = append_fp8_kv_cache(self.key_cache[layer_idx], self.value_cache[layer_idx],
-                                                   key_states, value_states)
-            self.key_cache[layer_idx] = k_cache
-            self.value_cache[layer_idx] = v_cache
-        return self.key_cache[layer_idx], self.value_cache[layer_idx]
+            self.keys, self.values = init_fp8_kv_cache(batch_size, num_heads, max(seq_len, self.reserve - FP8_KV_ALLOC_LENGTH),
+                                                       head_dim, key_states.device)
+        self.is_initialized = True
 
-    def get_seq_length(self, layer_idx: int = 0) -> int:
-        return 0 if len(self.key_cache) <= layer_idx else self.key_cache[layer_idx].shape[2]
+    def update(self, key_states, value_states, *args, **kwargs):
+        if not self.is_initialized:
+            self.lazy_initialization(key_states, value_states)
+        self.keys, self.values = append_fp8_kv_cache(self.keys, self.values, key_states, value_states)
+        return self.keys, self.values
 
-    def __len__(self):
-        return len(self.key_cache)
+    def set_length(self, length: int):
+        """the views after ``length`` positions were written behind the host's back (the recorded decode step)"""
+        b, h, _, d = self.keys.shape
+        self.keys = self.keys.as_strided((b, h, length, d), self.keys.stride(), storage_offset=0)
+        self.values = self.values.as_strided((b, h, length, d), self.values.stride(), storage_offset=0)
+
+
+class _LayeredCache(Cache):
+    """transformers' ``Cache`` (a list of per-layer objects) with the ``key_cache`` / ``value_cache`` lists the
+    reference's cache classes expose"""
+    LAYER = None
+
+    def __init__(self, num_hidden_layers: Optional[int] = None, reserve: int = 0) -> None:
+        super().__init__(layers=[])
+        self.reserve = reserve
+
+    def new_layer(self):
+        return self.LAYER(self.reserve)
+
+    def update(self, key_states, value_states, layer_idx, *args, **kwargs):
+        while len(self.layers) <= layer_idx:
+            self.layers.append(self.new_layer())
+        return self.layers[layer_idx].update(key_states, value_states)
+
+    @property
+    def key_cache(self):
+        return [l.keys for l in self.layers]
+
+    @property
+    def value_cache(self):
+        return [l.values for l in self.layers]
 
     def __getitem__(self, layer_idx):
-        return self.key_cache[layer_idx], self.value_cache[layer_idx]
+        return self.layers[layer_idx].keys, self.layers[layer_idx].values
+
+    @classmethod
+    def from_legacy_cache(cls, past_key_values=None, **kwargs):
+        """an empty or missing cache -> a new one of this class; a filled one is re-stored layer by layer
+        (the reference's from_legacy_cache, kv.py / transformers DynamicCache)"""
+        cache = cls(**kwargs)
+        if past_key_values is None:
+            return cache
+        layers = getattr(past_key_values, "layers", None)
+        pairs = [(l.keys, l.values) for l in layers if getattr(l, "is_initialized", False) and l.get_seq_length() > 0] \
+            if layers is not None else list(past_key_values)
+        for i, (k, v) in enumerate(pairs):
+            cache.update(k, v, i)
+        return cache
+
+
+class DynamicFp8Cache(_LayeredCache):
+    """kv.py:33-77: K and V as e5m2 bytes; ``update`` returns the uint8 views of the layer."""
+    LAYER = Fp8KVLayer
+
+
+class NormalKVLayer(DynamicLayer):
+    """One layer of the floating-point cache, grown in blocks of KV_ALLOC_BLOCK_LENGTH positions instead of
+    torch.cat per token (kv.py:80-140, models/utils.py init_kv_cache / extend_kv_cache / append_kv_cache)."""
+
+    def __init__(self, reserve: int = 0):
+        super().__init__()
+        self.reserve = int(reserve)
+
+    def lazy_initialization(self, key_states, value_states):
+        self.dtype, self.device = key_states.dtype, key_states.device
+        self.keys = self.values = None
+        self.is_initialized = True
+
+    def _alloc(self, like, length, capacity):
+        b, h, _, d = like.shape
+        storage = torch.empty(b, h, capacity, d, dtype=like.dtype, device=like.device)
+        return storage.as_strided((b, h, length, d), storage.stride(), storage_offset=0)
+
+    def update(self, key_states, value_states, *args, **kwargs):
+        if not self.is_initialized:
+            self.lazy_initialization(key_states, value_states)
+        cur = 0 if self.keys is None else self.keys.size(2)
+        new_len = cur + key_states.size(2)
+        if self.keys is None or self.keys.stride(1) < new_len * self.keys.size(3):
+            cap = max(new_len, self.reserve) + KV_ALLOC_BLOCK_LENGTH
+            nk, nv = self._alloc(key_states, new_len, cap), self._alloc(value_states, new_len, cap)
+            if cur:
+                nk[:, :, :cur, :] = self.keys
+                nv[:, :, :cur, :] = self.values
+            self.keys, self.values = nk, nv
+        else:
+            b, h, _, d = self.keys.shape
+            self.keys = self.keys.as_strided((b, h, new_len, d), self.keys.stride(), storage_offset=0)
+            self.values = self.values.as_strided((b, h, new_len, d), self.values.stride(), storage_offset=0)
+        self.keys[:, :, cur:new_len, :] = key_states
+        self.values[:, :, cur:new_len, :] = value_states
+        return self.keys, self.values
+
+    def get_seq_length(self) -> int:
+        return 0 if (not self.is_initialized or self.keys is None) else self.keys.shape[-2]
+
+
+class DynamicNormalCache(_LayeredCache):
+    """kv.py:80-140"""
+    LAYER = NormalKVLayer
 
 
 _sdp_workspaces = {}
@@ -137,6 +236,13 @@ def sdp_fp8(query, key, value, mask, scale, is_causal=False):
     return out
 
 
+def _additive_mask(mask, dtype):
+    """transformers >= 5 hands attention a boolean mask (True = attend); the kernels take an additive one"""
+    if mask is not None and mask.dtype == torch.bool:
+        return torch.zeros(mask.shape, dtype=dtype, device=mask.device).masked_fill_(~mask, float("-inf"))
+    return mask
+
+
 def scaled_dot_product_attention(query: torch.Tensor, key: torch.Tensor, value: torch.Tensor, mask: torch.Tensor = None,
                                  is_causal: bool = False, scale: float = None) -> torch.Tensor:
     """models/common.py:250-306.  uint8 key/value = the FP8 cache: new tokens <= 32 (decode) go to the fused kernel
@@ -147,6 +253,7 @@ def scaled_dot_product_attention(query: torch.Tensor, key: torch.Tensor, value: 
     scale = 1 / math.sqrt(head_dim) if scale is None else scale
     if key.dtype == torch.uint8:
         if seq_length <= 32 and ggml.lowbit_sdp_fp8_supported(n_heads, n_kv_heads, seq_length, head_dim):
+            mask = _additive_mask(mask, query.dtype if query.dtype != torch.bfloat16 else torch.float32)
             return sdp_fp8(query, key, value, mask, scale, is_causal and mask is None)
         key, value = restore_fp8_kv_cache(key, value, query.dtype)
     if n_heads != n_kv_heads:
@@ -154,5 +261,11 @@ def scaled_dot_product_attention(query: torch.Tensor, key: torch.Tensor, value: 
         value = value.repeat_interleave(n_heads // n_kv_heads, dim=1)
     if mask is not None:
         mask = mask[..., :seq_length, :kv_length]
-        return torch.nn.functional.scaled_dot_product_attention(query, key, value, mask, scale=scale)
-    return torch.nn.functional.scaled_dot_product_attention(query, key, value, is_causal=is_causal and seq_length > 1, scale=scale)
+    kwargs = dict(attn_mask=mask, scale=scale) if mask is not None else dict(is_causal=is_causal and seq_length > 1, scale=scale)
+    if query.dtype == torch.float32 and query.device.type == "cuda":
+        # an fp32 model asks for fp32 arithmetic (the CPU reference's contract): the plain softmax(QK^T)V statement,
+        # not a fused kernel that may feed the tensor cores reduced-precision operands
+        from torch.nn.attention import SDPBackend, sdpa_kernel
+        with sdpa_kernel(SDPBackend.MATH):
+            return torch.nn.functional.scaled_dot_product_attention(query, key, value, **kwargs)
+    return torch.nn.functional.scaled_dot_product_attention(query, key, value, **kwargs)

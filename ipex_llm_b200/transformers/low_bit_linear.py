@@ -536,6 +536,10 @@ class LowBitLinear(nn.Linear):
                 # after the sum (LBL:715-725)
                 result = g.matmul_all_reduce(x_2d, self.weight.data, self.weight_shape, self.qtype, bias=self.bias)
                 return result.view(new_shape).to(x.dtype)
+            if x_2d.dtype == torch.float32 and self.conver_to_half and x_2d.shape[0] > GEMV_MAX_M:
+                # LBL:700-705: a prefill-sized fp32 batch is computed in half precision (tensor-core GEMM);
+                # conver_to_half=False keeps fp32 activations on the exact (2^-24) GEMV path at any batch size
+                x_2d = x_2d.half()
             fuse_bias = self.bias is not None and self.mp_group is None
             nxt = self.next_linear.weight.data if (self.next_linear is not None and x_2d.shape[0] <= GEMV_MAX_M) else None
             result = lowbit_matmul(x_2d, self.weight.data, self.weight_shape, self.qtype,

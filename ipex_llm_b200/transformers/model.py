@@ -63,19 +63,24 @@ class _BaseAutoModelClass:
         model = ggml_convert_low_bit(model, ggml_tensor_qtype[q_k], optimize_model,
                                      modules_to_not_convert=modules_to_not_convert,
                                      torch_dtype=kwargs.get("torch_dtype", "auto"), mixed_precision=mixed_precision)
-        return cls._finish(model, q_k, mixed_precision)
+        return cls._finish(model, q_k, mixed_precision, optimize_model)
 
     @classmethod
     def from_model(cls, model, low_bit="sym_int4", optimize_model=True, modules_to_not_convert=None, mixed_precision=False):
-        """convert an already-built Hugging Face model (random-init models in tests and benchmarks)"""
+        """convert an already-built Hugging Face model (random-init models in tests and benchmarks).  A model that
+        already sits on a GPU is quantised there, linear by linear (FP4Params.to quantises on the weight's device)."""
         from ipex_llm_b200.transformers.convert import ggml_convert_low_bit
-        model = ggml_convert_low_bit(model.to("cpu"), ggml_tensor_qtype[low_bit], optimize_model,
+        first = next(model.parameters(), None)
+        if first is None or first.device.type != "cuda":
+            model = model.to("cpu")
+        model = ggml_convert_low_bit(model, ggml_tensor_qtype[low_bit], optimize_model,
                                      modules_to_not_convert=modules_to_not_convert, mixed_precision=mixed_precision)
-        return cls._finish(model, low_bit, mixed_precision)
+        return cls._finish(model, low_bit, mixed_precision, optimize_model)
 
     @staticmethod
-    def _finish(model, q_k, mixed_precision=False):
-        model.config.update({"bigdl_transformers_low_bit": q_k})
+    def _finish(model, q_k, mixed_precision=False, optimize_model=True):
+        # bigdl_optimize_model: whether q/k/v were merged (the saved keys differ); read back by load_low_bit
+        model.config.update({"bigdl_transformers_low_bit": q_k, "bigdl_optimize_model": bool(optimize_model)})
         if mixed_precision:                              # recorded so that load_low_bit sizes the lm_head correctly
             from ipex_llm_b200.transformers.convert import MIXED_LM_HEAD_QTYPE
             model.config.update({"bigdl_lm_head_low_bit": MIXED_LM_HEAD_QTYPE})
@@ -97,7 +102,8 @@ class _BaseAutoModelClass:
         with low_memory_init():
             model = cls.HF_MODEL.from_config(config)
         mixed_precision = bool(kwargs.pop("mixed_precision", False)) or config.to_dict().get("bigdl_lm_head_low_bit") is not None
-        model = ggml_convert_low_bit(model, ggml_tensor_qtype[low_bit], kwargs.pop("optimize_model", True),
+        optimize_model = bool(kwargs.pop("optimize_model", config.to_dict().get("bigdl_optimize_model", True)))
+        model = ggml_convert_low_bit(model, ggml_tensor_qtype[low_bit], optimize_model,
                                      convert_shape_only=True, device="meta",
                                      modules_to_not_convert=kwargs.pop("modules_to_not_convert", None),
                                      mixed_precision=mixed_precision)
@@ -107,7 +113,7 @@ class _BaseAutoModelClass:
         if hasattr(model, "tie_weights"):
             model.tie_weights()
         model.eval()
-        return cls._finish(model, low_bit)
+        return cls._finish(model, low_bit, optimize_model=optimize_model)
 
 
 class AutoModelForCausalLM(_BaseAutoModelClass):

@@ -85,3 +85,90 @@ def rotary_two_with_cache_inplaced(query_states, key_states, cos, sin, half_layo
     with torch.cuda.device(query_states.device):
         ggml.lowbit_rotary_inplaced(query_states, key_states, cos.shape[-1], True, None, None, cos, sin, not half_layout,
                                     _stream(query_states.device))
+
+
+# ------------------------------------------------------------------ callers of the low-bit linears
+# (reference models/common.py: merge_linear / merge_qkv_base :23-53, fuse_mlp_base / mlp_silu_forward /
+# mlp_gelu_forward :146-171, rms_norm_forward :187-205, scaled_dot_product_attention :250-306)
+from typing import List                                                   # noqa: E402
+
+from ipex_llm_b200.transformers.kv import scaled_dot_product_attention   # noqa: E402,F401  (re-export, reference location)
+
+
+def merge_linear(linears: List[torch.nn.Linear]) -> torch.nn.Linear:
+    """:23-37: one Linear whose weight is the row concatenation of the given ones (before quantisation; block
+    records never straddle rows, so quantising the merged weight gives the concatenation of the parts' bytes)"""
+    if not hasattr(linears[0], "weight"):
+        return None
+    new_weight = torch.cat([linear.weight.data for linear in linears], dim=0)
+    has_bias = linears[0].bias is not None
+    with torch.device("meta"):
+        new_linear = torch.nn.Linear(1, 1, bias=has_bias)
+    if has_bias:
+        new_linear.bias = torch.nn.Parameter(torch.cat([linear.bias.data for linear in linears], dim=0), requires_grad=False)
+    new_linear.weight = torch.nn.Parameter(new_weight, requires_grad=False)
+    new_linear.in_features = new_weight.size(1)
+    new_linear.out_features = new_weight.size(0)
+    return new_linear
+
+
+def merge_qkv_base(module: torch.nn.Module, attention_class):
+    """:40-53: q_proj, k_proj, v_proj -> qkv_proj on every attention module of the given class (or class name)"""
+    if (isinstance(attention_class, str) and module.__class__.__name__ == attention_class
+            or not isinstance(attention_class, str) and isinstance(module, attention_class)):
+        if not all(hasattr(module, n) for n in ("q_proj", "k_proj", "v_proj")):
+            return
+        qkv_proj = merge_linear([module.q_proj, module.k_proj, module.v_proj])
+        if qkv_proj is not None:
+            module.qkv_proj = qkv_proj
+            del module.q_proj, module.k_proj, module.v_proj
+
+
+def fuse_mlp_base(module: torch.nn.Module, act: int, x: torch.Tensor):
+    """:146-161: gate and up projections + activation * multiply in one kernel at decode sizes
+    (xe_linear.mlp_forward_xpu -> lowbit_mlp_cuda), then down_proj"""
+    from ipex_llm_b200.transformers.models.utils import mlp_fusion_check
+    from ipex_llm_b200.transformers.low_bit_linear import LowBitLinear, mlp_forward
+    gate, up = module.gate_proj, module.up_proj
+    qtype = getattr(gate, "qtype", None)
+    if (isinstance(gate, LowBitLinear) and isinstance(up, LowBitLinear) and gate.bias is None and up.bias is None
+            and gate.mp_group is None and getattr(up, "qtype", None) == qtype and mlp_fusion_check(x, qtype, module.training)):
+        x_2d = x.contiguous().view(-1, x.size(-1))
+        hidden = mlp_forward(x_2d, gate.weight.data, up.weight.data, x_2d.size(0), x_2d.size(1), gate.out_len, act, qtype)
+        return module.down_proj(hidden.view(x.shape[:-1] + (gate.out_len,)))
+    return module.down_proj(module.act_fn(module.gate_proj(x)) * module.up_proj(x))
+
+
+def mlp_silu_forward(self, x: torch.Tensor):
+    """:164-166"""
+    from ipex_llm_b200.transformers.models.utils import SILU
+    return fuse_mlp_base(self, SILU, x)
+
+
+def mlp_gelu_forward(self, x: torch.Tensor):
+    """:169-171"""
+    from ipex_llm_b200.transformers.models.utils import GELU
+    return fuse_mlp_base(self, GELU, x)
+
+
+def rms_norm_forward(self, hidden_states: torch.Tensor):
+    """:187-205: xe_addons.rms_norm -> lowbit_rms_norm_cuda on the GPU, the torch statement elsewhere"""
+    weight = self.weight
+    eps = getattr(self, "variance_epsilon", None)
+    if eps is None:
+        eps = getattr(self, "epsilon", None)
+    if eps is None:
+        eps = self.eps
+    if hidden_states.device.type == "cuda" and hidden_states.dtype in (torch.float, torch.half, torch.bfloat16) \
+            and weight.dtype in (torch.float, torch.half, torch.bfloat16):
+        x_2d = hidden_states.reshape(-1, hidden_states.size(-1))
+        if x_2d.stride(-1) != 1:
+            x_2d = x_2d.contiguous()
+        out = torch.empty(x_2d.shape, dtype=torch.promote_types(weight.dtype, x_2d.dtype), device=x_2d.device)
+        with torch.cuda.device(x_2d.device):
+            ggml.lowbit_rms_norm(x_2d, weight, eps, out, _stream(x_2d.device))
+        return out.reshape(hidden_states.shape)
+    input_dtype = hidden_states.dtype
+    variance = hidden_states.to(torch.float32).pow(2).mean(dim=-1, keepdim=True)
+    hidden_states = hidden_states.to(torch.float32) * torch.rsqrt(variance + eps)
+    return weight * hidden_states.to(input_dtype)

@@ -43,10 +43,12 @@ def test_optimize_model_forward_matches_oracle_model(native_lib, cuda_device, qt
     ref = oracle_dequantised_copy(base, qtype)
     model = optimize_model(base, low_bit=qtype)
     lins = [m for m in model.modules() if isinstance(m, LowBitLinear)]
-    assert len(lins) == 2 * 7 + 1 and all(l.weight.quantized for l in lins)           # q,k,v,o,gate,up,down x2 + lm_head
-    # packed bytes on the CPU are the canonical layout the oracle produces
-    w0 = tiny_llama().model.layers[0].self_attn.q_proj.weight.data.numpy()
-    got = model.model.layers[0].self_attn.q_proj.weight.data.view(torch.uint8).numpy()
+    assert len(lins) == 2 * 5 + 1 and all(l.weight.quantized for l in lins)           # qkv,o,gate,up,down x2 + lm_head
+    # packed bytes on the CPU are the canonical layout the oracle produces; q, k, v were merged into qkv_proj before
+    # quantisation (reference convert.py:1000-1003), which is the row concatenation of their packed bytes
+    a0 = tiny_llama().model.layers[0].self_attn
+    w0 = torch.cat([a0.q_proj.weight.data, a0.k_proj.weight.data, a0.v_proj.weight.data]).numpy()
+    got = model.model.layers[0].self_attn.qkv_proj.weight.data.view(torch.uint8).numpy()
     np.testing.assert_array_equal(got, oracle.quantize(w0, qtype))
 
     model = model.to(cuda_device)
@@ -73,7 +75,7 @@ def test_optimize_model_forward_matches_oracle_model(native_lib, cuda_device, qt
     with low_memory_init():
         shell = tiny_llama()
     loaded = load_low_bit(shell, save_dir)
-    np.testing.assert_array_equal(loaded.model.layers[0].self_attn.q_proj.weight.data.view(torch.uint8).numpy(),
+    np.testing.assert_array_equal(loaded.model.layers[0].self_attn.qkv_proj.weight.data.view(torch.uint8).numpy(),
                                   oracle.quantize(w0, qtype))
     loaded = loaded.to(cuda_device)
     with torch.no_grad():
@@ -124,3 +126,94 @@ def test_optimize_model_low_bit_embedding(native_lib, cuda_device):
         got = model(ids.to(cuda_device)).logits.float().cpu()
     rel = (got - want).abs().mean() / want.abs().mean()
     assert rel < 2e-3, float(rel)
+
+
+def test_optimize_model_true_vs_false(native_lib, cuda_device, tmp_path):
+    """the reference's own check (test/inference/test_transformers_api.py:151-169): logits of the optimised forwards
+    against the stock forwards on the same low-bit weights; and a model saved without the optimisations loads back
+    with its own key layout"""
+    from ipex_llm.transformers import AutoModelForCausalLM
+    from ipex_llm.transformers.low_bit_linear import LowBitLinear
+    plain = AutoModelForCausalLM.from_model(tiny_llama(), low_bit="sym_int4", optimize_model=False)
+    fast = AutoModelForCausalLM.from_model(tiny_llama(), low_bit="sym_int4", optimize_model=True)
+    assert hasattr(plain.model.layers[0].self_attn, "q_proj") and hasattr(fast.model.layers[0].self_attn, "qkv_proj")
+    assert sum(isinstance(m, LowBitLinear) for m in plain.modules()) == 2 * 7 + 1
+    assert plain.generate.__func__.__name__ == "generate"
+    plain, fast = plain.to(cuda_device), fast.to(cuda_device)
+    ids = torch.randint(0, 320, (2, 9), generator=torch.Generator().manual_seed(5)).to(cuda_device)
+    with torch.no_grad():
+        a, b = plain(ids).logits.float(), fast(ids).logits.float()
+    assert float((a - b).abs().mean() / a.abs().mean()) < 1e-4            # the reference's bar is 0.05
+    with torch.no_grad():
+        ta = plain.generate(ids[:1], max_new_tokens=12, do_sample=False)
+        tb = fast.generate(ids[:1], max_new_tokens=12, do_sample=False)
+    assert torch.equal(ta, tb)
+    d = str(tmp_path / "plain")
+    plain.save_low_bit(d)
+    again = AutoModelForCausalLM.load_low_bit(d).to(cuda_device)
+    assert hasattr(again.model.layers[0].self_attn, "q_proj")
+    with torch.no_grad():
+        torch.testing.assert_close(again(ids).logits.float(), a, rtol=0, atol=0)
+
+
+def tiny_mistral(seed=0):
+    cfg = transformers.MistralConfig(hidden_size=256, intermediate_size=512, num_hidden_layers=2, num_attention_heads=4,
+                                     num_key_value_heads=2, vocab_size=320, max_position_embeddings=256, sliding_window=None,
+                                     head_dim=64, tie_word_embeddings=False)
+    torch.manual_seed(seed)
+    return transformers.MistralForCausalLM(cfg).eval()
+
+
+@pytest.mark.parametrize("family,qtype,dtype", [("llama", "sym_int4", torch.float16), ("mistral", "fp8_e4m3", torch.float16),
+                                                ("mistral", "fp6", torch.bfloat16), ("llama", "asym_int4", torch.bfloat16)])
+def test_recorded_decode_step_matches_the_eager_forwards(native_lib, cuda_device, family, qtype, dtype):
+    """half-precision model, FP8 KV cache: ``generate`` replays the recorded decode step (CUDA graph); the same
+    request through transformers' generate loop runs the patched forwards one kernel at a time.  Same kernels, same
+    roundings -> same tokens; and the logits stay close to the oracle-dequantised fp32 model's."""
+    from ipex_llm.transformers import AutoModelForCausalLM
+    from ipex_llm_b200.transformers import kv
+    base = tiny_llama() if family == "llama" else tiny_mistral()
+    model = AutoModelForCausalLM.from_model(base, low_bit=qtype).to(cuda_device).to(dtype)
+    assert model.generate.__func__.__name__ == "generate_greedy_graph"
+    ids = torch.randint(0, 320, (1, 40), generator=torch.Generator().manual_seed(7)).to(cuda_device)
+    with torch.no_grad():
+        fast = model.generate(ids, max_new_tokens=24, do_sample=False)
+        assert getattr(model, "last_decode_launches_per_token", 0) > 0              # the recorded path ran
+        slow = model._hf_generate(ids, max_new_tokens=24, do_sample=False)
+        out = model(ids, use_cache=True)
+    assert isinstance(out.past_key_values, kv.DynamicFp8Cache) and out.past_key_values.key_cache[0].dtype == torch.uint8
+    assert fast.shape == (1, 64) and torch.equal(fast[:, :40], ids)
+    assert torch.equal(fast, slow), (fast[0, 40:].tolist(), slow[0, 40:].tolist())
+    # a second call reuses the recorded step and its cache arena and gives the same answer; batch 2 records another
+    with torch.no_grad():
+        again = model.generate(ids, max_new_tokens=24, do_sample=False)
+        ids2 = torch.cat([ids, ids.flip(1)], dim=0)
+        fast2 = model.generate(ids2, max_new_tokens=8, do_sample=False)
+        slow2 = model._hf_generate(ids2, max_new_tokens=8, do_sample=False)
+    assert torch.equal(again, fast) and torch.equal(fast2, slow2)
+    assert torch.equal(fast2[0], fast[0, :48])
+    assert model.rest_cost_mean > 0 and model.first_cost > 0
+
+
+def test_generate_stops_at_eos_and_falls_back(native_lib, cuda_device):
+    from ipex_llm.transformers import AutoModelForCausalLM
+    model = AutoModelForCausalLM.from_model(tiny_llama(), low_bit="sym_int4").to(cuda_device).half()
+    ids = torch.randint(0, 320, (1, 20), generator=torch.Generator().manual_seed(9)).to(cuda_device)
+    with torch.no_grad():
+        free = model.generate(ids, max_new_tokens=16, do_sample=False)
+        eos = int(free[0, 20 + 5])                                  # the 6th new token becomes the end-of-sequence id
+        first = [int(t) for t in free[0, 20:]].index(eos)
+        stopped = model.generate(ids, max_new_tokens=16, do_sample=False, eos_token_id=eos, pad_token_id=0)
+        want = model._hf_generate(ids, max_new_tokens=16, do_sample=False, eos_token_id=eos, pad_token_id=0)
+    assert stopped.shape[1] == 20 + first + 1 and int(stopped[0, -1]) == eos
+    assert torch.equal(stopped, want)
+    # requests the recorded step does not serve go to transformers' generate (sampling here) and still work
+    torch.manual_seed(0)
+    with torch.no_grad():
+        sampled = model.generate(ids, max_new_tokens=8, do_sample=True, top_k=5)
+    assert sampled.shape == (1, 28)
+    # fp32 model: floating-point cache, eager path
+    model32 = AutoModelForCausalLM.from_model(tiny_llama(), low_bit="sym_int4").to(cuda_device)
+    with torch.no_grad():
+        t32 = model32.generate(ids, max_new_tokens=8, do_sample=False)
+    assert t32.shape == (1, 28)
