@@ -153,4 +153,5 @@ def test_mixed_precision_lm_head(native_lib, tmp_path):
     loaded = optimize.load_low_bit(fresh, str(tmp_path))
     assert loaded.lm_head.qtype == Q["fp6"] and loaded.lm_head.weight.quantized
     assert torch.equal(loaded.lm_head.weight.data, saved["lm_head.weight"]) and torch.equal(loaded.a.weight.data, saved["a.weight"])
-    assert loaded._bigdl_config == {"bigdl_transformers_low_bit": "sym_int4", "bigdl_lm_head_low_bit": "fp6"}
+    assert loaded._bigdl_config == {"bigdl_transformers_low_bit": "sym_int4", "bigdl_lm_head_low_bit": "fp6",
+                                    "bigdl_optimize_llm": True}
