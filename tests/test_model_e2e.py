@@ -164,6 +164,26 @@ def tiny_mistral(seed=0):
     return transformers.MistralForCausalLM(cfg).eval()
 
 
+def assert_same_tokens_up_to_a_tie(model, a, b, dtype):
+    """The recorded step and the eager forwards run the same kernels, except that the decode attention splits the keys
+    for the cache CAPACITY in one case and for the current LENGTH in the other: partial sums meet in a different order,
+    an output may move by one unit in the last place, and a greedy choice between two nearly equal logits may flip.
+    Sequences must therefore agree up to the first position where the model itself is undecided: there the two
+    candidates' logits (eager forward on the common prefix) differ by no more than a few units in the last place."""
+    if torch.equal(a, b):
+        return
+    rows = (a != b).any(dim=1).nonzero()[:, 0].tolist()
+    for r in rows:
+        i = int((a[r] != b[r]).nonzero()[0, 0])
+        with torch.no_grad():
+            logits = model(a[r:r + 1, :i]).logits[0, -1].float()
+        eps = 2.0 ** -10 if dtype == torch.float16 else 2.0 ** -7
+        gap = abs(float(logits[a[r, i]] - logits[b[r, i]]))
+        assert gap <= 4 * eps * float(logits.abs().max()), (r, i, gap, a[r, i - 2:i + 3].tolist(), b[r, i - 2:i + 3].tolist())
+        top2 = torch.topk(logits, 2).indices.tolist()
+        assert int(a[r, i]) in top2 and int(b[r, i]) in top2
+
+
 @pytest.mark.parametrize("family,qtype,dtype", [("llama", "sym_int4", torch.float16), ("mistral", "fp8_e4m3", torch.float16),
                                                 ("mistral", "fp6", torch.bfloat16), ("llama", "asym_int4", torch.bfloat16)])
 def test_recorded_decode_step_matches_the_eager_forwards(native_lib, cuda_device, family, qtype, dtype):
@@ -183,15 +203,16 @@ def test_recorded_decode_step_matches_the_eager_forwards(native_lib, cuda_device
         out = model(ids, use_cache=True)
     assert isinstance(out.past_key_values, kv.DynamicFp8Cache) and out.past_key_values.key_cache[0].dtype == torch.uint8
     assert fast.shape == (1, 64) and torch.equal(fast[:, :40], ids)
-    assert torch.equal(fast, slow), (fast[0, 40:].tolist(), slow[0, 40:].tolist())
+    assert_same_tokens_up_to_a_tie(model, fast, slow, dtype)
     # a second call reuses the recorded step and its cache arena and gives the same answer; batch 2 records another
     with torch.no_grad():
         again = model.generate(ids, max_new_tokens=24, do_sample=False)
         ids2 = torch.cat([ids, ids.flip(1)], dim=0)
         fast2 = model.generate(ids2, max_new_tokens=8, do_sample=False)
         slow2 = model._hf_generate(ids2, max_new_tokens=8, do_sample=False)
-    assert torch.equal(again, fast) and torch.equal(fast2, slow2)
-    assert torch.equal(fast2[0], fast[0, :48])
+    assert torch.equal(again, fast)
+    assert_same_tokens_up_to_a_tie(model, fast2, slow2, dtype)
+    assert_same_tokens_up_to_a_tie(model, fast2[:1], fast[:, :48], dtype)
     assert model.rest_cost_mean > 0 and model.first_cost > 0
 
 
