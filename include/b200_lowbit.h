@@ -209,6 +209,23 @@ int lowbit_rope_kv_append_cuda(void* d_qkv, int dtype, int64_t batch_stride, int
                                void* d_k_cache, const int64_t* k_strides, void* d_v_cache, const int64_t* v_strides,
                                int capacity, void* stream);
 
+/* The whole attention of one decode step (one new token per sequence) -- the middle of the reference's attention forward
+ * (models/llama.py:146-196): rotary embedding of q and k, DynamicFp8Cache.update, scaled_dot_product_attention -> sdp_fp8.
+ * d_qkv [B][(Hq + 2 Hkv) * D] = the merged projection's output (batch stride in elements); *d_len = tokens already in
+ * the cache = position of the new token (read on the device: the call can be replayed from a CUDA graph); tables and
+ * caches as in lowbit_rope_kv_append_cuda; d_out [B][Hq][D] contiguous.  For fp16 / bf16 activations with head_dim 128
+ * this is ONE launch: every CTA rotates its query rows itself, the CTA that owns the new position computes the new key /
+ * value row (and tile 0 stores it in the cache), and the key splits of a (sequence, kv head) form a thread-block cluster
+ * whose members push their partial softmax sums into the leader's shared memory (deterministic merge, no second launch,
+ * no global scratch).  Other shapes, and caches long enough to want more than 8 splits, run the separate kernels
+ * (lowbit_rope_kv_append_cuda, lowbit_sdp_fp8_devlen_cuda) and need the workspace.  Same results as the separate calls. */
+size_t lowbit_decode_attention_workspace_size(int B, int Hq, int Hkv, int capacity, int D);
+int lowbit_decode_attention_cuda(void* d_qkv, int dtype, int64_t batch_stride, int B, int Hq, int Hkv, int D,
+                                 const void* d_cos, const void* d_sin, int cs_dtype, int64_t cs_row_stride, int n_positions,
+                                 const int32_t* d_len, void* d_k_cache, const int64_t* k_strides, void* d_v_cache,
+                                 const int64_t* v_strides, int capacity, float scale, void* d_out, int out_dtype,
+                                 void* workspace, size_t workspace_bytes, void* stream);
+
 /* Greedy pick and step bookkeeping of a recorded decode step -- the torch.argmax + append of the reference's
  * generate loop (utils/benchmark_util_4_47.py:3340-3380), done on the device so that steps replay without a host
  * round trip.  logits [B][V]: d_next_ids[b] = index of the largest value (lowest index among equals);

@@ -76,6 +76,11 @@ struct SdpArgs {
     int B, Hq, Hkv, S, L, D;
     int n_split, keys_per_split;
     const int* len_ptr; int len_add;                               // non-NULL: the key count is *len_ptr + len_add (<= L), read on the device
+    // fused decode step (sdp_mma.cuh, FUSED): one new token per sequence; q, the new key and the new value come straight
+    // from the merged qkv projection's output, the rotary embedding is applied here and the new row is written to the cache
+    const void* qkv; int64_t qkv_sb;                               // [B][(Hq + 2 Hkv) * D] of q_dtype
+    const void* cos; const void* sin; int cs_dtype; int64_t cs_row; int n_pos;    // [positions][>= D/2]
+    uint8_t* kw; uint8_t* vw;                                      // the caches, writable
     int rt;                                                        // query rows per CTA (1, 2 or 4)
     float* part;                                                   // [B][Hkv][row tiles][n_split][RT * (D + 2)]
     void* out; int out_dtype;                                      // [B][Hq][S][D] contiguous
@@ -493,10 +498,10 @@ static int sdp_launch(const void* d_q, int q_dtype, const int64_t* q_strides, co
         // head_dim 128: chunks staged through a per-warp cp.async ring (LOWBIT_SDP_RING = stages; 0 = loads into
         // registers, the only variant for head_dim 64)
         static const int nst = [] { const char* e = getenv("LOWBIT_SDP_RING"); return e ? atoi(e) : 3; }();
-        if (D == 64) sdp_fp8_decode_mma_kernel<64, 4, 0><<<grid, SDP_WARPS * 32, 0, st>>>(A);
-        else if (nst == 0) sdp_fp8_decode_mma_kernel<128, 2, 0><<<grid, SDP_WARPS * 32, 0, st>>>(A);
+        if (D == 64) sdp_fp8_decode_mma_kernel<64, 4, 0, 0><<<grid, SDP_WARPS * 32, 0, st>>>(A);
+        else if (nst == 0) sdp_fp8_decode_mma_kernel<128, 2, 0, 0><<<grid, SDP_WARPS * 32, 0, st>>>(A);
         else {
-            auto kern = nst == 2 ? sdp_fp8_decode_mma_kernel<128, 3, 2> : (nst == 4 ? sdp_fp8_decode_mma_kernel<128, 1, 4> : sdp_fp8_decode_mma_kernel<128, 2, 3>);
+            auto kern = nst == 2 ? sdp_fp8_decode_mma_kernel<128, 3, 2, 0> : (nst == 4 ? sdp_fp8_decode_mma_kernel<128, 1, 4, 0> : sdp_fp8_decode_mma_kernel<128, 2, 3, 0>);
             const int smem = SDP_WARPS * (nst == 2 ? 2 : (nst == 4 ? 4 : 3)) * 8192;
             static bool configured[64][3] = {};
             int dev = 0; cudaGetDevice(&dev);
@@ -550,4 +555,105 @@ extern "C" int lowbit_sdp_fp8_devlen_cuda(const void* d_q, int q_dtype, const in
     if (!d_len) { set_error(LB_ERR_ARG, "lowbit_sdp_fp8_devlen_cuda: d_len is NULL"); return LB_ERR_ARG; }
     return sdp_launch(d_q, q_dtype, q_strides, d_k, k_strides, d_v, v_strides, nullptr, 0, nullptr, causal, scale,
                       B, Hq, Hkv, S, L_max, D, d_out, out_dtype, workspace, workspace_bytes, stream, d_len, len_add);
+}
+
+// ------------------------------------------------------------------ the attention of one decode step, one call
+extern "C" int lowbit_rope_kv_append_cuda(void* d_qkv, int dtype, int64_t batch_stride, int64_t token_stride, int B, int S,
+                                          int Hq, int Hkv, int D, const void* d_cos, const void* d_sin, int cs_dtype,
+                                          int64_t cs_row_stride, int n_positions, const int32_t* d_pos, int pos_add,
+                                          void* d_k_cache, const int64_t* k_strides, void* d_v_cache,
+                                          const int64_t* v_strides, int capacity, void* stream);
+
+// key splits of the fused kernel: the merge runs inside a thread-block cluster, so at most 8; same cost model as sdp_splits
+static int fused_splits(int B, int Hq, int Hkv, int L, int D) {
+    const int base = B * Hkv * sdp_tiles(Hq, Hkv, 1, true);
+    int max_by_len = (L + 127) / 128;
+    if (max_by_len > 8) max_by_len = 8;
+    const int64_t cap = (int64_t)sm_count() * 2;
+    int best = 1; int64_t best_cost = INT64_MAX;
+    for (int n = 1; n <= max_by_len; n++) {
+        const int64_t waves = ((int64_t)base * n + cap - 1) / cap;
+        const int64_t keys = (((L + n - 1) / n + 127) / 128) * 128;
+        const int64_t cost = waves * (384 + keys);
+        if (cost < best_cost) { best_cost = cost; best = n; }
+    }
+    return best;
+}
+
+extern "C" size_t lowbit_decode_attention_workspace_size(int B, int Hq, int Hkv, int capacity, int D) {
+    return lowbit_sdp_fp8_workspace_size(B, Hq, Hkv, 1, capacity, D);
+}
+
+extern "C" int lowbit_decode_attention_cuda(void* d_qkv, int dtype, int64_t batch_stride, int B, int Hq, int Hkv, int D,
+                                            const void* d_cos, const void* d_sin, int cs_dtype, int64_t cs_row_stride,
+                                            int n_positions, const int32_t* d_len, void* d_k_cache, const int64_t* k_strides,
+                                            void* d_v_cache, const int64_t* v_strides, int capacity, float scale, void* d_out,
+                                            int out_dtype, void* workspace, size_t workspace_bytes, void* stream) {
+    reset_launch_count();
+    if (!d_qkv || !d_cos || !d_sin || !d_len || !d_k_cache || !d_v_cache || !k_strides || !v_strides || !d_out || dtype < 0 ||
+        dtype > 2 || cs_dtype < 0 || cs_dtype > 2 || out_dtype < 0 || out_dtype > 2 || B <= 0 || capacity <= 0 || n_positions <= 0 ||
+        !lowbit_sdp_fp8_supported(Hq, Hkv, 1, D) || batch_stride < (int64_t)(Hq + 2 * Hkv) * D || cs_row_stride < D / 2) {
+        set_error(LB_ERR_ARG, "lowbit_decode_attention_cuda: bad argument (B %d, Hq %d, Hkv %d, D %d, capacity %d)", B, Hq, Hkv, D, capacity);
+        return LB_ERR_ARG;
+    }
+    static const bool fused_off = [] { const char* e = getenv("LOWBIT_DECODE_ATTN_FUSED"); return e && e[0] == '0'; }();   // development
+    const int esz = 2;
+    // the one-launch kernel: half-precision activations, head_dim 128, 16-byte aligned rows everywhere, a split count
+    // that fits a cluster.  Long caches with few heads want more than 8 splits: they take the separate kernels below.
+    const bool aligned = !(((uintptr_t)d_qkv | (uintptr_t)d_k_cache | (uintptr_t)d_v_cache) & 15) && !((batch_stride * esz) & 15) &&
+                         !((k_strides[0] | k_strides[1] | k_strides[2] | v_strides[0] | v_strides[1] | v_strides[2]) & 15) &&
+                         (cs_dtype == DT_F32 || (!(((uintptr_t)d_cos | (uintptr_t)d_sin) & 15) && !((cs_row_stride * 2) & 15)));
+    const int want = sdp_splits(B, Hq, Hkv, 1, capacity, D, true);
+    if (!fused_off && dtype != DT_F32 && D == 128 && scale > 0.0f && aligned && want <= 8) {
+        SdpArgs A = {};
+        A.q = nullptr; A.q_dtype = dtype;
+        A.k = (const uint8_t*)d_k_cache; A.k_sb = k_strides[0]; A.k_sh = k_strides[1]; A.k_ss = k_strides[2];
+        A.v = (const uint8_t*)d_v_cache; A.v_sb = v_strides[0]; A.v_sh = v_strides[1]; A.v_ss = v_strides[2];
+        A.kw = (uint8_t*)d_k_cache; A.vw = (uint8_t*)d_v_cache;
+        A.mask = nullptr; A.causal = 0; A.scale_log2e = scale * 1.4426950408889634f;
+        A.B = B; A.Hq = Hq; A.Hkv = Hkv; A.S = 1; A.L = capacity; A.D = D;
+        A.len_ptr = d_len; A.len_add = 1;
+        A.qkv = d_qkv; A.qkv_sb = batch_stride; A.cos = d_cos; A.sin = d_sin; A.cs_dtype = cs_dtype; A.cs_row = cs_row_stride;
+        A.n_pos = n_positions;
+        A.n_split = fused_splits(B, Hq, Hkv, capacity, D);
+        A.keys_per_split = ((capacity + A.n_split - 1) / A.n_split + 31) / 32 * 32;
+        A.rt = sdp_rt(Hq, Hkv, 1, true);
+        A.part = nullptr; A.out = d_out; A.out_dtype = out_dtype;
+        const int tiles = sdp_tiles(Hq, Hkv, 1, true);
+        auto kern = sdp_fp8_decode_mma_kernel<128, 2, 3, 1>;
+        const int smem = SDP_WARPS * 3 * 8192 + 16 + (A.n_split - 1) * A.rt * (D + 2) * (int)sizeof(float);
+        static int configured[64] = {};
+        int dev = 0; cudaGetDevice(&dev);
+        if (dev >= 0 && dev < 64 && configured[dev] < smem) {
+            const int ask = SDP_WARPS * 3 * 8192 + 16 + 7 * SDP_MMA_ROWS * (128 + 2) * (int)sizeof(float);
+            if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, ask) != cudaSuccess) {
+                set_error(LB_ERR_CUDA, "lowbit_decode_attention_cuda: cannot reserve %d bytes of shared memory", ask);
+                return LB_ERR_CUDA;
+            }
+            configured[dev] = ask;
+        }
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3((unsigned)A.n_split, (unsigned)(B * Hkv), (unsigned)tiles);
+        cfg.blockDim = dim3(SDP_WARPS * 32); cfg.dynamicSmemBytes = (size_t)smem; cfg.stream = (cudaStream_t)stream;
+        cudaLaunchAttribute at[2];
+        int na = 0;
+        at[na].id = cudaLaunchAttributeClusterDimension;
+        at[na].val.clusterDim.x = (unsigned)A.n_split; at[na].val.clusterDim.y = 1; at[na].val.clusterDim.z = 1; na++;
+        if (gemv_get_pdl()) {
+            at[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+            at[na].val.programmaticStreamSerializationAllowed = 1; na++;
+        }
+        cfg.attrs = at; cfg.numAttrs = na;
+        if (cudaLaunchKernelEx(&cfg, kern, A) != cudaSuccess) return check_launch();
+        note_launch();
+        return check_launch();
+    }
+    // separate kernels: rotary + cache write, attention with the device-side length, merge
+    int rc = lowbit_rope_kv_append_cuda(d_qkv, dtype, batch_stride, batch_stride, B, 1, Hq, Hkv, D, d_cos, d_sin, cs_dtype, cs_row_stride,
+                                        n_positions, d_len, 0, d_k_cache, k_strides, d_v_cache, v_strides, capacity, stream);
+    if (rc) return rc;
+    const int64_t q_strides[3] = {batch_stride, (int64_t)D, batch_stride};
+    rc = sdp_launch(d_qkv, dtype, q_strides, d_k_cache, k_strides, d_v_cache, v_strides, nullptr, 0, nullptr, 0, scale, B, Hq, Hkv, 1,
+                    capacity, D, d_out, out_dtype, workspace, workspace_bytes, stream, d_len, 1);
+    return rc;
 }

@@ -33,7 +33,48 @@ __device__ __forceinline__ float ex2_approx(float x) {
 
 constexpr int SDP_MMA_ROWS = 8;
 
-template <int D, int OCC, int NST>
+// ---- pieces of the fused decode step (FUSED = 1): mbarrier / cluster primitives for the in-cluster merge
+__device__ __forceinline__ uint32_t sdp_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void sdp_mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void sdp_mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void sdp_mbar_wait(uint32_t bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}" ::"r"(bar), "r"(parity) : "memory");
+}
+__device__ __forceinline__ uint32_t sdp_map_to_rank(uint32_t local_addr, uint32_t rank) {
+    uint32_t remote;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local_addr), "r"(rank));
+    return remote;
+}
+// remote store whose 4 bytes are counted on the destination CTA's mbarrier: the sender needs no fence and may exit
+__device__ __forceinline__ void sdp_st_async_f32(uint32_t remote_addr, float v, uint32_t remote_bar) {
+    asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.b32 [%0], %1, [%2];"
+                 ::"r"(remote_addr), "r"(__float_as_uint(v)), "r"(remote_bar) : "memory");
+}
+__device__ __forceinline__ float sdp_round_to(float v, int dt) {
+    if (dt == DT_F16) return __half2float(__float2half_rn(v));
+    if (dt == DT_BF16) return __bfloat162float(__float2bfloat16_rn(v));
+    return v;
+}
+
+// FUSED = 1 is the whole attention of ONE decode step in one launch (S = 1, D = 128, NST > 0): the query rows are
+// read from the merged qkv projection's output and rotated here; the new key (rotated, rounded to the activation dtype,
+// then e5m2) and the new value (e5m2) are computed by every CTA whose key range holds the new position -- it patches them
+// into its staged chunk, so nobody depends on another CTA's write -- and written to the cache by tile 0; the key splits of a
+// (sequence, kv head) form a thread-block cluster (<= 8 CTAs) whose members PUSH their partial (m, l, o) into the leader's
+// shared memory (st.async + mbarrier transaction count, as the GEMV's split-K reduction does); the leader merges in rank
+// order and writes the output.  Same arithmetic as the separate kernels (rope.cu, kv_quantize, this kernel + the merge
+// kernel): rotate -> round -> quantise, the same split-local softmax, the same merge formula.
+template <int D, int OCC, int NST, int FUSED>
 __global__ void __launch_bounds__(SDP_WARPS * 32, OCC)
 sdp_fp8_decode_mma_kernel(const SdpArgs A) {
     constexpr int NC = D / 64;                       // 16-byte pieces of a key row per lane
@@ -41,6 +82,7 @@ sdp_fp8_decode_mma_kernel(const SdpArgs A) {
     constexpr int VW = BPL / 4;                      // ... as 32-bit words
     static_assert(D == 64 || D == 128, "head_dim 64 or 128");
     static_assert(NST == 0 || D == 128, "the staged variant is written for 128-byte rows");
+    static_assert(!FUSED || (NST > 0 && D == 128), "the fused decode step is written for head_dim 128 and staged chunks");
     extern __shared__ __align__(128) uint8_t sdp_ring[];            // NST > 0: [warp][stage][K 4 KB | V 4 KB]
     __shared__ float red_m[SDP_WARPS][SDP_MMA_ROWS], red_l[SDP_WARPS][SDP_MMA_ROWS];
     constexpr int RO = SDP_MMA_ROWS * (D + 16);       // floats of one warp's staged accumulators (NST > 0: in its ring)
@@ -53,6 +95,19 @@ sdp_fp8_decode_mma_kernel(const SdpArgs A) {
     const int n_rows = min(A.rt, rows_total - row0);
 
     asm volatile("griddepcontrol.launch_dependents;");               // the merge kernel may be scheduled as CTAs here retire
+    // FUSED: leader's receive barrier; the cluster barrier that publishes it is split around the main loop (free)
+    const uint32_t rbar = sdp_smem_u32(sdp_ring) + SDP_WARPS * NST * 8192;
+    float* const recv = reinterpret_cast<float*>(sdp_ring + SDP_WARPS * NST * 8192 + 16);
+    if (FUSED) {
+        if (A.n_split > 1) {
+            if (split == 0 && threadIdx.x == 0) {
+                sdp_mbar_init(rbar, 1);
+                asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+            }
+            asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
+        }
+        asm volatile("griddepcontrol.wait;" ::: "memory");           // qkv and the cache length come from earlier kernels
+    }
 
     // A fragments of Q: lane (g,t) holds row g, elements 64c + 16t .. +15 as 8 fp16 pairs (zeros for rows >= n_rows)
     uint32_t qa[NC][8];
@@ -61,6 +116,53 @@ sdp_fp8_decode_mma_kernel(const SdpArgs A) {
 #pragma unroll
         for (int i = 0; i < 8; i++) qa[c][i] = 0u;
     int my_hq = 0, my_st = 0;                         // query head / token of this lane's row
+    int L, keys_per_split;
+    sdp_lengths(A, L, keys_per_split);
+    const int new_pos = L - 1;                        // FUSED: position of the token being decoded
+    if (FUSED) {
+        if (g < n_rows) {
+            my_hq = hkv * n_rep + row0 + g;
+            const uint16_t* qrow = reinterpret_cast<const uint16_t*>(A.qkv) + b * A.qkv_sb + (int64_t)my_hq * D + 16 * t;
+            const int pr = min(max(new_pos, 0), A.n_pos - 1);
+            uint4 xw[2][2], cw[2], sw[2];             // x: [c][half of 16], cos / sin: 16 entries of the row
+#pragma unroll
+            for (int c = 0; c < 2; c++) { xw[c][0] = *reinterpret_cast<const uint4*>(qrow + 64 * c); xw[c][1] = *reinterpret_cast<const uint4*>(qrow + 64 * c + 8); }
+            float cf[16], sf[16];
+            if (A.cs_dtype == DT_F32) {
+#pragma unroll
+                for (int e = 0; e < 16; e++) { cf[e] = ((const float*)A.cos)[pr * A.cs_row + 16 * t + e]; sf[e] = ((const float*)A.sin)[pr * A.cs_row + 16 * t + e]; }
+            } else {
+                const uint16_t* cr = reinterpret_cast<const uint16_t*>(A.cos) + pr * A.cs_row + 16 * t;
+                const uint16_t* sr = reinterpret_cast<const uint16_t*>(A.sin) + pr * A.cs_row + 16 * t;
+                cw[0] = *reinterpret_cast<const uint4*>(cr); cw[1] = *reinterpret_cast<const uint4*>(cr + 8);
+                sw[0] = *reinterpret_cast<const uint4*>(sr); sw[1] = *reinterpret_cast<const uint4*>(sr + 8);
+                const uint16_t* ce = reinterpret_cast<const uint16_t*>(cw);
+                const uint16_t* se = reinterpret_cast<const uint16_t*>(sw);
+#pragma unroll
+                for (int e = 0; e < 16; e++) {
+                    if (A.cs_dtype == DT_F16) { __half_raw a, c2; a.x = ce[e]; c2.x = se[e]; cf[e] = __half2float(__half(a)); sf[e] = __half2float(__half(c2)); }
+                    else { cf[e] = __uint_as_float((uint32_t)ce[e] << 16); sf[e] = __uint_as_float((uint32_t)se[e] << 16); }
+                }
+            }
+            const uint16_t* x0e = reinterpret_cast<const uint16_t*>(xw[0]);
+            const uint16_t* x1e = reinterpret_cast<const uint16_t*>(xw[1]);
+            float y0[16], y1[16];
+#pragma unroll
+            for (int e = 0; e < 16; e++) {
+                float x0, x1;
+                if (A.q_dtype == DT_F16) { __half_raw a, c2; a.x = x0e[e]; c2.x = x1e[e]; x0 = __half2float(__half(a)); x1 = __half2float(__half(c2)); }
+                else { x0 = __uint_as_float((uint32_t)x0e[e] << 16); x1 = __uint_as_float((uint32_t)x1e[e] << 16); }
+                y0[e] = sdp_round_to(fmaf(x0, cf[e], -x1 * sf[e]), A.q_dtype);
+                y1[e] = sdp_round_to(fmaf(x1, cf[e], x0 * sf[e]), A.q_dtype);
+            }
+#pragma unroll
+            for (int i = 0; i < 8; i++) {
+                const __half2 h0 = __floats2half2_rn(y0[2 * i], y0[2 * i + 1]), h1 = __floats2half2_rn(y1[2 * i], y1[2 * i + 1]);
+                qa[0][i] = *reinterpret_cast<const uint32_t*>(&h0);
+                qa[1 % NC][i] = *reinterpret_cast<const uint32_t*>(&h1);
+            }
+        }
+    } else
     if (g < n_rows) {
         const int rr = row0 + g;
         my_hq = hkv * n_rep + rr / A.S; my_st = rr % A.S;
@@ -80,10 +182,34 @@ sdp_fp8_decode_mma_kernel(const SdpArgs A) {
         }
     }
 
-    int L, keys_per_split;
-    sdp_lengths(A, L, keys_per_split);
     const int key_begin = split * keys_per_split;
     const int key_end = min(L, key_begin + keys_per_split);
+    // FUSED: the new row of this kv head -- lane l owns key elements l, l + 32, l + 64, l + 96 (two rotary pairs) and
+    // value elements 4l .. 4l + 3 -- for every CTA whose range holds the new position; tile 0 also writes it to the cache
+    const bool has_new = FUSED && new_pos >= key_begin && new_pos < key_end;
+    uint32_t knew = 0, vnew = 0;
+    if (has_new) {
+        const int64_t kbase = b * A.qkv_sb + (int64_t)(A.Hq + hkv) * D, vbase = kbase + (int64_t)A.Hkv * D;
+        const int pr = min(new_pos, A.n_pos - 1);
+        float kx[4];
+#pragma unroll
+        for (int j = 0; j < 4; j++) kx[j] = load_as_float(A.qkv, A.q_dtype, kbase + lane + 32 * j);
+#pragma unroll
+        for (int j = 0; j < 2; j++) {                  // pairs (lane + 32 j, lane + 32 j + 64)
+            const float c = load_as_float(A.cos, A.cs_dtype, pr * A.cs_row + lane + 32 * j), sn = load_as_float(A.sin, A.cs_dtype, pr * A.cs_row + lane + 32 * j);
+            const float y0 = sdp_round_to(fmaf(kx[j], c, -kx[j + 2] * sn), A.q_dtype), y1 = sdp_round_to(fmaf(kx[j + 2], c, kx[j] * sn), A.q_dtype);
+            knew |= (uint32_t)to_e5m2(y0) << (8 * j);
+            knew |= (uint32_t)to_e5m2(y1) << (8 * (j + 2));
+        }
+#pragma unroll
+        for (int j = 0; j < 4; j++) vnew |= (uint32_t)to_e5m2(load_as_float(A.qkv, A.q_dtype, vbase + 4 * lane + j)) << (8 * j);
+        if (tile == 0 && warp == 0) {
+            uint8_t* kd = A.kw + b * A.k_sb + hkv * A.k_sh + (int64_t)new_pos * A.k_ss;
+#pragma unroll
+            for (int j = 0; j < 4; j++) kd[lane + 32 * j] = (uint8_t)(knew >> (8 * j));
+            *reinterpret_cast<uint32_t*>(A.vw + b * A.v_sb + hkv * A.v_sh + (int64_t)new_pos * A.v_ss + 4 * lane) = vnew;
+        }
+    }
     const uint8_t* kb = A.k + b * A.k_sb + hkv * A.k_sh + 16 * t;
     const uint8_t* vb = A.v + b * A.v_sb + hkv * A.v_sh + BPL * g;
     const int64_t mask_base = b * A.m_sb + my_hq * A.m_sh + my_st * A.m_ss;
@@ -147,6 +273,19 @@ sdp_fp8_decode_mma_kernel(const SdpArgs A) {
             int ahead = slot + NST - 1; if (ahead >= NST) ahead -= NST;
             stage_chunk(c0 + (NST - 1) * SDP_WARPS * 32, ahead);
             asm volatile("cp.async.wait_group %0;" :: "n"(NST > 0 ? NST - 1 : 0) : "memory");
+            if (has_new && new_pos >= c0 && new_pos < c0 + 32) {
+                // the chunk holds the new position: its row comes from this CTA's own registers, not from the cache
+                __syncwarp();
+                const int r = new_pos - c0;
+                uint8_t* st8 = ring + slot * 8192;
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    const int d = lane + 32 * j;
+                    st8[r * 128 + ((((d >> 4) ^ ((r & 1) << 2))) << 4) + (d & 15)] = (uint8_t)(knew >> (8 * j));
+                }
+                const int dv = 4 * lane;
+                *reinterpret_cast<uint32_t*>(st8 + 4096 + r * 128 + ((((dv >> 4) ^ (((r >> 1) & 3) << 1))) << 4) + (dv & 15)) = vnew;
+            }
             __syncwarp();
         } else {
         // ---- all loads of the chunk first (one memory round trip per chunk).  Keys beyond the range are clamped
@@ -284,7 +423,13 @@ sdp_fp8_decode_mma_kernel(const SdpArgs A) {
             *reinterpret_cast<float4*>(red_o(warp) + g * (D + 16) + BPL * (2 * t + i) + 4 * (D == 128 ? (q ^ t) : q)) =
                 make_float4(o[4 * q][i], o[4 * q + 1][i], o[4 * q + 2][i], o[4 * q + 3][i]);
     __syncthreads();
-    float* part = A.part + ((((int64_t)b * A.Hkv + hkv) * gridDim.z + tile) * A.n_split + split) * (A.rt * (D + 2));
+    float* part = FUSED ? nullptr : A.part + ((((int64_t)b * A.Hkv + hkv) * gridDim.z + tile) * A.n_split + split) * (A.rt * (D + 2));
+    const int ps = A.rt * (D + 2);                                    // floats of one CTA's partial result
+    if (FUSED && A.n_split > 1) {
+        asm volatile("barrier.cluster.wait.aligned;" ::: "memory");  // the leader's barrier init is visible
+        if (split == 0 && threadIdx.x == 0) sdp_mbar_expect_tx(rbar, (uint32_t)((A.n_split - 1) * ps * 4));
+    }
+    const uint32_t rb = FUSED ? sdp_map_to_rank(rbar, 0) : 0u;
     for (int i = threadIdx.x; i < A.rt * D; i += blockDim.x) {
         const int r = i / D, d = i % D;
         const int pos = D == 128 ? ((d & ~12) | ((((d >> 2) ^ (d >> 5)) & 3) << 2)) : d;       // where column d was staged
@@ -298,7 +443,38 @@ sdp_fp8_decode_mma_kernel(const SdpArgs A) {
             acc = fmaf(red_o(w)[r * (D + 16) + pos], f, acc);
             lsum = fmaf(red_l[w][r], f, lsum);
         }
-        part[r * (D + 2) + 2 + d] = acc;
-        if (d == 0) { part[r * (D + 2)] = M; part[r * (D + 2) + 1] = lsum; }
+        if (!FUSED) {
+            part[r * (D + 2) + 2 + d] = acc;
+            if (d == 0) { part[r * (D + 2)] = M; part[r * (D + 2) + 1] = lsum; }
+        } else if (split != 0) {
+            // a peer: push (m, l, o) of the row into the leader's receive area and be done
+            const uint32_t dst = sdp_smem_u32(recv + (split - 1) * ps + r * (D + 2));
+            sdp_st_async_f32(sdp_map_to_rank(dst + 4 * (2 + d), 0), acc, rb);
+            if (d == 0) {
+                sdp_st_async_f32(sdp_map_to_rank(dst, 0), M, rb);
+                sdp_st_async_f32(sdp_map_to_rank(dst + 4, 0), lsum, rb);
+            }
+        } else {
+            // the leader: merge the splits in rank order (the merge kernel's formula), normalise, store
+            if (A.n_split > 1) sdp_mbar_wait(rbar, 0);
+            float Mall = M;
+            for (int k = 1; k < A.n_split; k++) Mall = fmaxf(Mall, recv[(k - 1) * ps + r * (D + 2)]);
+            const float f0 = (M == -CUDART_INF_F) ? 0.0f : exp2f(M - Mall);
+            float o = acc * f0, l = lsum * f0;
+            for (int k = 1; k < A.n_split; k++) {
+                const float* pk = recv + (k - 1) * ps + r * (D + 2);
+                const float f = (pk[0] == -CUDART_INF_F) ? 0.0f : exp2f(pk[0] - Mall);
+                o = fmaf(pk[2 + d], f, o);
+                l = fmaf(pk[1], f, l);
+            }
+            const int rr = row0 + r;
+            if (rr < rows_total) {
+                const float y = l > 0.0f ? o / l : 0.0f;
+                const int64_t oi = ((int64_t)b * A.Hq + (hkv * n_rep + rr)) * D + d;          // S == 1
+                if (A.out_dtype == DT_F32) ((float*)A.out)[oi] = y;
+                else if (A.out_dtype == DT_F16) ((__half*)A.out)[oi] = __float2half_rn(y);
+                else ((__nv_bfloat16*)A.out)[oi] = __float2bfloat16_rn(y);
+            }
+        }
     }
 }

@@ -118,16 +118,13 @@ class DecodeGraph:
         else:
             self.h.copy_(emb(self.next_ids))
         qkv2d, attn2d = self.qkv.view(B, -1), self.attn.view(B, -1)
-        q_view = self.qkv.view(B, 1, self.Hq + 2 * self.Hkv, self.D).transpose(1, 2)[:, :self.Hq]
         for i, layer in enumerate(core.layers):
             attn, mlp = layer.self_attn, layer.mlp
             self._rms(layer.input_layernorm, self.h, self.xn)
             self._linear(attn.qkv_proj, self.xn, qkv2d)
-            ggml.lowbit_rope_kv_append(self.qkv, self.Hq, self.Hkv, self.D, self.cos, self.sin, self.state, 0,
-                                       self.k_cache[i], self.v_cache[i], st)
-            ggml.lowbit_sdp_fp8_devlen(q_view, self.k_cache[i], self.v_cache[i], False, attn.scaling, self.state, 1,
-                                       self.attn, self.sdp_ws, st)
-            self.launches_per_step += 3
+            ggml.lowbit_decode_attention(self.qkv, self.Hq, self.Hkv, self.D, self.cos, self.sin, self.state,
+                                         self.k_cache[i], self.v_cache[i], attn.scaling, self.attn, self.sdp_ws, st)
+            self.launches_per_step += ggml.last_launch_count()
             self._linear(attn.o_proj, attn2d, self.h, accumulate=True)
             self._rms(layer.post_attention_layernorm, self.h, self.xn)
             gate, up = mlp.gate_proj, mlp.up_proj

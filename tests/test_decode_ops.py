@@ -134,3 +134,46 @@ def test_greedy_advance_min_new_tokens_rule(native_lib, cuda_device):
     for _ in range(3):
         ggml.lowbit_greedy_advance(logits, nxt, tokens, state, _st(dev), sup)
     assert tokens[0, :3].tolist() == [3, 3, 7]
+
+
+@pytest.mark.parametrize("B,Hq,Hkv,dtype", [(1, 32, 32, torch.float16), (2, 32, 8, torch.bfloat16), (1, 64, 8, torch.float16),
+                                             (3, 8, 1, torch.float16), (1, 40, 40, torch.float16)])
+def test_decode_attention_one_launch_equals_the_separate_kernels(native_lib, cuda_device, B, Hq, Hkv, dtype):
+    """lowbit_decode_attention_cuda (rotary + cache write + attention + in-cluster merge in one launch) against
+    lowbit_rope_kv_append_cuda + lowbit_sdp_fp8_devlen_cuda and against float64 attention on the same cache bytes"""
+    ggml, dev = native_lib, cuda_device
+    gen = torch.Generator(device=dev).manual_seed(5)
+    D, cap = 128, 768
+    tot = (Hq + 2 * Hkv) * D
+    inv_freq = 1.0 / (10000.0 ** (torch.arange(0, D, 2, device=dev, dtype=torch.float32) / D))
+    ang = torch.arange(cap, device=dev, dtype=torch.float32)[:, None] * inv_freq[None, :]
+    emb = torch.cat([ang, ang], dim=-1)
+    cos, sin = emb.cos().to(dtype), emb.sin().to(dtype)
+    k0 = torch.randn(B, Hkv, cap, D, device=dev, generator=gen).to(torch.float8_e5m2).view(torch.uint8)
+    v0 = torch.randn(B, Hkv, cap, D, device=dev, generator=gen).to(torch.float8_e5m2).view(torch.uint8)
+    ws = torch.empty(max(256, ggml.lowbit_decode_attention_workspace_size(B, Hq, Hkv, cap, D)), dtype=torch.uint8, device=dev)
+    scale = 1 / math.sqrt(D)
+    launches = set()
+    for P in (0, 5, 31, 32, 95, 200, 511, 700, cap - 1):
+        qkv = torch.randn(B, 1, tot, device=dev, generator=gen).to(dtype)
+        state = torch.tensor([P, 0, 0, 0, 0, 0, 0, 0], dtype=torch.int32, device=dev)
+        # separate kernels
+        qa, ka, va = qkv.clone(), k0.clone(), v0.clone()
+        ggml.lowbit_rope_kv_append(qa, Hq, Hkv, D, cos, sin, state, 0, ka, va, _st(dev))
+        q_view = qa.view(B, 1, Hq + 2 * Hkv, D).transpose(1, 2)[:, :Hq]
+        want = torch.empty(B, Hq, 1, D, dtype=dtype, device=dev)
+        ggml.lowbit_sdp_fp8_devlen(q_view, ka, va, False, scale, state, 1, want, ws, _st(dev))
+        # one call
+        qb, kb, vb = qkv.clone(), k0.clone(), v0.clone()
+        got = torch.full((B, Hq, 1, D), float("nan"), dtype=dtype, device=dev)
+        ggml.lowbit_decode_attention(qb, Hq, Hkv, D, cos, sin, state, kb, vb, scale, got, ws, _st(dev))
+        launches.add(ggml.last_launch_count())
+        assert torch.equal(kb, ka) and torch.equal(vb, va), P                     # the new row, and nothing else, was written
+        L = P + 1
+        kd = ka[:, :, :L].view(torch.float8_e5m2).double().repeat_interleave(Hq // Hkv, 1)
+        vd = va[:, :, :L].view(torch.float8_e5m2).double().repeat_interleave(Hq // Hkv, 1)
+        exact = torch.softmax(q_view.double() @ kd.transpose(-1, -2) * scale, -1) @ vd
+        tol = (1e-3 if dtype == torch.float16 else 8e-3) * float(exact.abs().max())
+        assert float((got.double() - exact).abs().max()) <= tol, P
+        assert float((got.double() - want.double()).abs().max()) <= tol, P
+    assert launches == {1}, launches                     # every case here fits the one-launch kernel
