@@ -126,8 +126,11 @@ int lowbit_kv_dequantize_cuda(const void* d_src, const int64_t* src_strides, voi
  * number), polls (bounded) its own inboxes for the peers' words and sums all vectors in rank order: every rank gets the
  * same bits.  n * sizeof(dtype) must be a multiple of 16 and at most max_bytes (<= lowbit_comm_max_bytes() = 256 KiB:
  * decode-sized vectors; larger tensors belong to NCCL); d_in == d_out is allowed.  Every rank issues the same sequence
- * of calls.  Call counters live in device memory: a captured CUDA graph replays.  lowbit_comm_status reports 1 after a
- * wait ran into its bound (a peer did not call). */
+ * of calls.  Call counters live in device memory (they skip 0, the fresh buffer's state, when they wrap): a captured
+ * CUDA graph replays.  A wait is bounded (LOWBIT_COMM_TIMEOUT_S seconds, default 20): if a peer never calls, the words
+ * waited for become NaN, the communicator's status word is set for good and every later call on it writes NaN without
+ * waiting -- a stalled rank fails loudly instead of yielding a plausible wrong sum.  lowbit_comm_status reports 1 then
+ * (it synchronises the device); destroy the communicator and create a new one to go on. */
 size_t lowbit_comm_max_bytes(void);
 int lowbit_comm_create(size_t max_bytes, void** d_buffer, void* ipc_handle_64);
 int lowbit_comm_open(const void* ipc_handle_64, void** d_peer);

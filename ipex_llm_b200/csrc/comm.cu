@@ -12,9 +12,11 @@
 // Per thread (no thread waits for another thread of its grid, there is no barrier):
 //   1. epoch = epochs[cta] + 1 (device-resident, so a captured CUDA graph replays); slot = epoch & 1;
 //   2. for its 4-byte words w: read in[w]; store {in[w], epoch} to peer r's slot[rank][w] for every r != rank;
-//   3. for every r != rank: poll own slot[r][w] until its call number is epoch.  The poll is bounded
-//      (COMM_SPIN_LIMIT polls with nanosleep back-off, about a second): on expiry the status word is set and the kernel
-//      carries on, so a missing peer cannot hang the GPU;
+//   3. for every r != rank: poll own slot[r][w] until its call number is epoch.  The poll is bounded (spin_limit polls
+//      with nanosleep back-off: about LOWBIT_COMM_TIMEOUT_S = 20 seconds, far above any host-side skew between the ranks'
+//      processes) so that a missing peer cannot hang the GPU.  Expiry is LOUD: the words that were waited for become NaN,
+//      the communicator's status word is set and stays set, and every later call on the communicator writes NaN at once
+//      (it is unusable: a rank that gave up may be calls ahead of its peers, the two-slot argument below no longer holds);
 //   4. out[w] = sum over ranks in rank order (fp32 accumulate); last: epochs[cta] = epoch.
 // Two slots are enough: a rank can only start call e + 2 (same slot as e) after it received every peer's call e + 1
 // words, which a peer sends after its call-e kernel has finished reading.
@@ -25,6 +27,7 @@
 #include <cuda_bf16.h>
 #include <stdint.h>
 #include <string.h>
+#include <stdlib.h>
 #include "../../include/b200_lowbit.h"
 #include "lowbit_common.cuh"
 #include "lowbit_internal.h"
@@ -38,7 +41,8 @@ constexpr int COMM_MAX_CTAS = 64;
 constexpr int COMM_THREADS = 256;
 constexpr int COMM_CHUNK_BYTES = COMM_THREADS * 8;              // two 4-byte words per thread
 constexpr size_t COMM_HEADER_BYTES = 1024;                      // epochs 256 B, status
-constexpr uint32_t COMM_SPIN_LIMIT = 1u << 22;
+// polls per second of waiting, roughly (a poll = one volatile load round trip + a 256 ns sleep once the wait is long)
+constexpr double COMM_POLLS_PER_SECOND = 1.5e6;
 static_assert(COMM_MAX_CTAS * 4 + 4 <= COMM_HEADER_BYTES, "header too small");
 
 struct CommArgs {
@@ -49,7 +53,14 @@ struct CommArgs {
     int64_t n; int dtype;
     int64_t bytes_per_cta;               // multiple of 16
     int pdl;
+    uint32_t spin_limit;
 };
+
+// call numbers: 1, 2, 3, ... ; 0 is the "never written" state of a fresh buffer, so the counter skips it when it wraps
+// (after 2^32 calls; 0xffffffff is odd, 2 is even: the two slots keep alternating)
+__device__ __forceinline__ uint32_t next_epoch(uint32_t prev) { const uint32_t e = prev + 1u; return e == 0u ? 2u : e; }
+template <int DT> __device__ __forceinline__ uint32_t nan_word() { return DT == DT_F32 ? 0x7fc00000u : (DT == DT_F16 ? 0x7e007e00u : 0x7fc07fc0u); }
+
 
 __device__ __forceinline__ void st_word(uint8_t* p, uint32_t data, uint32_t epoch) {
     asm volatile("st.volatile.global.v2.u32 [%0], {%1,%2};" :: "l"(p), "r"(data), "r"(epoch) : "memory");
@@ -100,13 +111,14 @@ __global__ void __launch_bounds__(COMM_THREADS) allreduce_kernel(const CommArgs 
         asm volatile("griddepcontrol.launch_dependents;");
         asm volatile("griddepcontrol.wait;" ::: "memory");
     }
-    uint32_t epoch;
+    uint32_t epoch, dead;
     asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(epoch) : "l"(epochs + c) : "memory");
-    epoch += 1;
+    asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(dead) : "l"(status) : "memory");
+    epoch = next_epoch(epoch);
     const size_t slot_off = COMM_HEADER_BYTES + (epoch & 1) * (A.inbox_bytes * COMM_MAX_WORLD);
     const uint32_t* in = reinterpret_cast<const uint32_t*>(A.in);
     uint32_t* out = reinterpret_cast<uint32_t*>(A.out);
-    bool expired = false;
+    bool expired = dead != 0;                         // an earlier wait ran out: no sends, no waits, NaN results
     for (int64_t w0 = begin + tid; w0 < end; w0 += COMM_THREADS * COMM_WPT) {
         uint32_t mine[COMM_WPT];
 #pragma unroll
@@ -116,7 +128,7 @@ __global__ void __launch_bounds__(COMM_THREADS) allreduce_kernel(const CommArgs 
                 mine[j] = in[w];
 #pragma unroll
                 for (int r = 0; r < COMM_MAX_WORLD; r++)
-                    if (r < A.world && r != A.rank) st_word(A.peer[r] + slot_off + A.rank * A.inbox_bytes + w * 8, mine[j], epoch);
+                    if (!expired && r < A.world && r != A.rank) st_word(A.peer[r] + slot_off + A.rank * A.inbox_bytes + w * 8, mine[j], epoch);
             }
         }
         // poll in rounds: every round loads all words that are still missing at once (one memory round trip per
@@ -130,17 +142,17 @@ __global__ void __launch_bounds__(COMM_THREADS) allreduce_kernel(const CommArgs 
                 if (r < A.world && r != A.rank && w0 + j * COMM_THREADS < end) missing |= 1u << (j * 8 + r);
         // (first a plain spin on one word -- a single load in flight while nothing has arrived yet keeps the polling
         // traffic out of the way of the incoming stores -- then everything else, which has usually arrived with it)
-        if (missing != 0) {
+        if (missing != 0 && !expired) {
             const int sb = __ffs(missing) - 1;
             const uint8_t* p = own + slot_off + (sb & 7) * A.inbox_bytes + (w0 + (sb >> 3) * COMM_THREADS) * 8;
             uint32_t polls = 0;
             while (ld_word(p).y != epoch) {
-                if (++polls > COMM_SPIN_LIMIT) { expired = true; break; }
+                if (++polls > A.spin_limit) { expired = true; break; }
                 if (polls > 64) __nanosleep(polls > 4096 ? 256 : 32);
             }
         }
         for (uint32_t polls = 0; missing != 0 && !expired; polls++) {
-            if (polls > COMM_SPIN_LIMIT) { expired = true; break; }
+            if (polls > A.spin_limit) { expired = true; break; }
             if (polls > 16) __nanosleep(polls > 1024 ? 256 : 32);
 #pragma unroll
             for (int j = 0; j < COMM_WPT; j++)
@@ -166,7 +178,7 @@ __global__ void __launch_bounds__(COMM_THREADS) allreduce_kernel(const CommArgs 
                         if (r != A.rank) v = got[j][r].x;
                         add_word<DT>(acc, v);
                     }
-                out[w] = pack_word<DT>(acc);
+                out[w] = expired ? nan_word<DT>() : pack_word<DT>(acc);
             }
         }
     }
@@ -185,6 +197,7 @@ struct RecvArgs {
     void* y; int y_dtype; const void* bias; int accumulate;
     int64_t n_words, words_per_cta, n_cols;
     int pdl;
+    uint32_t spin_limit;
 };
 
 __global__ void __launch_bounds__(COMM_THREADS) recv_sum_kernel(const RecvArgs A) {
@@ -198,13 +211,14 @@ __global__ void __launch_bounds__(COMM_THREADS) recv_sum_kernel(const RecvArgs A
         asm volatile("griddepcontrol.launch_dependents;");
         asm volatile("griddepcontrol.wait;" ::: "memory");
     }
-    uint32_t epoch;
+    uint32_t epoch, dead;
     asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(epoch) : "l"(epochs + c) : "memory");
-    epoch += 1;
+    asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(dead) : "l"(status) : "memory");
+    epoch = next_epoch(epoch);
     const size_t slot_off = COMM_HEADER_BYTES + (epoch & 1) * (A.inbox_bytes * COMM_MAX_WORLD);
     const int64_t begin = (int64_t)c * A.words_per_cta;
     const int64_t end = begin + A.words_per_cta < A.n_words ? begin + A.words_per_cta : A.n_words;
-    bool expired = false;
+    bool expired = dead != 0;
     constexpr int BATCH = 4;
     for (int64_t w0 = begin + tid; w0 < end; w0 += COMM_THREADS * BATCH) {
         float v[BATCH];
@@ -215,17 +229,17 @@ __global__ void __launch_bounds__(COMM_THREADS) recv_sum_kernel(const RecvArgs A
 #pragma unroll
             for (int r = 0; r < COMM_MAX_WORLD; r++)
                 if (r < A.world && w0 + j * COMM_THREADS < end) missing |= 1u << (j * 8 + r);
-        if (missing != 0) {                           // a plain spin on one word first, as in allreduce_kernel
+        if (missing != 0 && !expired) {               // a plain spin on one word first, as in allreduce_kernel
             const int sb = 31 - __clz(missing);       // the highest rank's word: the own rank's words arrive first
             const uint8_t* p = A.own + slot_off + (sb & 7) * A.inbox_bytes + (w0 + (sb >> 3) * COMM_THREADS) * 8;
             uint32_t polls = 0;
             while (ld_word(p).y != epoch) {
-                if (++polls > COMM_SPIN_LIMIT) { expired = true; break; }
+                if (++polls > A.spin_limit) { expired = true; break; }
                 if (polls > 64) __nanosleep(polls > 4096 ? 256 : 32);
             }
         }
         for (uint32_t polls = 0; missing != 0 && !expired; polls++) {
-            if (polls > COMM_SPIN_LIMIT) { expired = true; break; }
+            if (polls > A.spin_limit) { expired = true; break; }
             if (polls > 16) __nanosleep(polls > 1024 ? 256 : 32);
 #pragma unroll
             for (int j = 0; j < BATCH; j++)
@@ -244,7 +258,8 @@ __global__ void __launch_bounds__(COMM_THREADS) recv_sum_kernel(const RecvArgs A
             v[j] = 0.0f;
 #pragma unroll
             for (int r = 0; r < COMM_MAX_WORLD; r++)
-                if (r < A.world && w0 + j * COMM_THREADS < end) v[j] += __uint_as_float(got[j][r].x);
+                if (!expired && r < A.world && w0 + j * COMM_THREADS < end) v[j] += __uint_as_float(got[j][r].x);
+            if (expired) v[j] = __uint_as_float(0x7fc00000u);        // a wait ran out: the result is NaN, not a guess
         }
 #pragma unroll
         for (int j = 0; j < BATCH; j++) {
@@ -276,6 +291,19 @@ __global__ void __launch_bounds__(COMM_THREADS) recv_sum_kernel(const RecvArgs A
 }  // namespace lowbit
 
 using namespace lowbit;
+
+// bound of a wait inside the kernels, from LOWBIT_COMM_TIMEOUT_S (seconds, default 20; clamped to [0.05, 1800])
+static uint32_t comm_spin_limit() {
+    static const uint32_t lim = [] {
+        const char* e = getenv("LOWBIT_COMM_TIMEOUT_S");
+        double sec = e ? atof(e) : 20.0;
+        if (!(sec >= 0.05)) sec = 0.05;
+        if (sec > 1800.0) sec = 1800.0;
+        const double polls = sec * COMM_POLLS_PER_SECOND;
+        return polls > 4.0e9 ? 4000000000u : (uint32_t)polls;
+    }();
+    return lim;
+}
 
 extern "C" size_t lowbit_comm_max_bytes(void) { return (size_t)256 << 10; }     // decode-sized vectors (M <= 16 x hidden 8192 x fp16)
 
@@ -363,6 +391,7 @@ extern "C" int lowbit_allreduce_sum_cuda(void* const* peer_buffers, int rank, in
     if (ctas > COMM_MAX_CTAS) ctas = COMM_MAX_CTAS;
     A.bytes_per_cta = (int64_t)(((max_bytes + ctas - 1) / ctas + 15) / 16 * 16);
     A.pdl = gemv_get_pdl();
+    A.spin_limit = comm_spin_limit();
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)ctas); cfg.blockDim = dim3(COMM_THREADS); cfg.dynamicSmemBytes = 0; cfg.stream = (cudaStream_t)stream;
     cudaLaunchAttribute at[1];
@@ -417,6 +446,7 @@ extern "C" int lowbit_matmul_allreduce_cuda(const void* d_w, int qtype, int64_t 
     if (ctas > COMM_MAX_CTAS) ctas = COMM_MAX_CTAS;
     A.words_per_cta = (int64_t)(((max_bytes + ctas - 1) / ctas + 15) / 16 * 16) / 4;
     A.pdl = gemv_get_pdl();
+    A.spin_limit = comm_spin_limit();
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)ctas); cfg.blockDim = dim3(COMM_THREADS); cfg.dynamicSmemBytes = 0; cfg.stream = (cudaStream_t)stream;
     cudaLaunchAttribute at[1];

@@ -745,6 +745,7 @@ gemv_kernel(const GemvArgs A) {
     if (MODE == 0 && A.push_world > 0) {
         asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(push_epoch) : "l"(A.push_epochs) : "memory");
         push_epoch += 1;
+        if (push_epoch == 0u) push_epoch = 2u;         // 0 = "never written": skipped when the counter wraps (comm.cu next_epoch)
     }
     auto store_value = [&](int i, float v) {
         const int l = i % LW, val = i / LW, c = val % ACC, j = (val / ACC) % NT, r = val / (ACC * NT);

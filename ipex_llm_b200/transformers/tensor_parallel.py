@@ -176,7 +176,19 @@ class PeerAllReduce:
         """True if a wait inside a kernel ran into its bound (a peer did not take part).  Synchronises the device."""
         return any(ggml.lowbit_comm_status(own) for own, _ in self._comms.values())
 
+    def check(self):
+        """raise if a wait inside a kernel ever ran out on one of the communicators (their results are NaN from then
+        on).  Synchronises the device: call it at a point where the host waits for results anyway."""
+        invalidInputError(not self.timed_out(),
+                          "PeerAllReduce: a rank did not take part in an all-reduce within LOWBIT_COMM_TIMEOUT_S seconds; "
+                          "the results since then are NaN and the communicator is unusable")
+
     def close(self):
+        dead = self.timed_out() if self._comms else False
+        self._close()
+        invalidInputError(not dead, "PeerAllReduce: a wait ran out during this communicator's life (results were NaN)")
+
+    def _close(self):
         for own, peers in self._comms.values():
             for r, p in enumerate(peers):
                 if r != self.rank:

@@ -155,3 +155,58 @@ def test_peer_allreduce_ranks(native_lib, world):
             p.kill()
     assert all(p.exitcode == 0 for p in procs), [p.exitcode for p in procs]
     assert sorted(out.keys()) == list(range(world))
+
+
+def _expiry_worker(rank, world, port, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), LOWBIT_COMM_TIMEOUT_S="0.3")
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("cpu:gloo,cuda:nccl", rank=rank, world_size=world, device_id=dev)
+    try:
+        from ipex_llm_b200.transformers import tensor_parallel as tp
+        group = tp.PeerAllReduce()
+        x = torch.ones(4096, device=dev, dtype=torch.float16)
+        group.all_reduce(x)                                   # a normal call: every rank takes part
+        torch.cuda.synchronize()
+        assert torch.equal(x, torch.full_like(x, float(world))) and not group.timed_out()
+        dist.barrier()
+        if rank == 0:
+            # the peer never makes this call: the wait runs out, the result is NaN (not a partial sum), the communicator
+            # reports it, and every later call on it gives NaN at once
+            y = torch.ones(4096, device=dev, dtype=torch.float16)
+            group.all_reduce(y)
+            torch.cuda.synchronize()
+            assert bool(torch.isnan(y).all())
+            assert group.timed_out()
+            with pytest.raises(RuntimeError):
+                group.check()
+            z = torch.ones(4096, device=dev, dtype=torch.float16)
+            group.all_reduce(z)
+            torch.cuda.synchronize()
+            assert bool(torch.isnan(z).all())
+            with pytest.raises(RuntimeError):
+                group.close()
+        dist.barrier()
+        if rank != 0:
+            group.close()
+        out[rank] = 1
+    finally:
+        dist.destroy_process_group()
+
+
+def test_peer_allreduce_missing_peer_fails_loudly(native_lib):
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    ctx = mp.get_context("spawn")
+    out = ctx.Manager().dict()
+    port = _free_port()
+    procs = [ctx.Process(target=_expiry_worker, args=(r, 2, port, out)) for r in range(2)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(timeout=120)
+    for p in procs:
+        if p.is_alive():
+            p.kill()
+    assert all(p.exitcode == 0 for p in procs), [p.exitcode for p in procs]
+    assert sorted(out.keys()) == [0, 1]

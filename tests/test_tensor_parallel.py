@@ -105,3 +105,101 @@ def test_row_parallel_allreduce_gloo_world2(native_lib, qtype, peer_group):
         p.join(timeout=120)
     assert all(p.exitcode == 0 for p in procs), [p.exitcode for p in procs]
     assert sorted(out.keys()) == list(range(world))
+
+
+class LinearLayer(torch.nn.Module):
+    """stand-in for deepspeed.module_inject.layers.LinearLayer: a column-parallel shard, weight [out / world, in]"""
+
+    def __init__(self, weight, bias=None):
+        super().__init__()
+        self.weight = torch.nn.Parameter(weight, requires_grad=False)
+        self.bias = None if bias is None else torch.nn.Parameter(bias, requires_grad=False)
+
+    def forward(self, x):
+        y = x @ self.weight.t()
+        return y if self.bias is None else y + self.bias
+
+
+class LinearAllreduce(LinearLayer):
+    """stand-in for deepspeed's LinearAllreduce: a row-parallel shard, weight [out, in / world]; the partial outputs
+    are summed over ``mp_group`` and the bias is added once"""
+
+    def __init__(self, weight, bias=None, mp_group=None):
+        super().__init__(weight, bias)
+        self.mp_group = mp_group
+
+    def forward(self, x):
+        y = x @ self.weight.t()
+        dist.all_reduce(y, group=self.mp_group)
+        return y if self.bias is None else y + self.bias
+
+
+class ShardedMLP(torch.nn.Module):
+    def __init__(self, up, down):
+        super().__init__()
+        self.up_proj, self.down_proj = up, down
+
+    def forward(self, x):
+        return self.down_proj(self.up_proj(x))
+
+
+def _autotp_worker(rank, world, port, w_up, w_down, bias, x, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        import ctypes
+        import ipex_llm_b200.ggml.model.llama.llama_cpp as ggml
+        from ipex_llm_b200 import optimize_model
+        from ipex_llm_b200.transformers import low_bit_linear as lbl
+        # CPU stand-ins for the two native calls (the product refuses to compute without a GPU)
+        lbl.ggml_matmul_src1_x_src0_t = lambda w_, x_, shape, qt: torch.from_numpy(
+            oracle.matmul(w_.view(torch.uint8).numpy(), tuple(shape), "sym_int4", x_.float().numpy()))
+
+        def quantize_on_cpu(src, dst, qtype, n, k, hist, scale_search):
+            a = np.ctypeslib.as_array(src, shape=(n // k, k))
+            packed = oracle.quantize(np.ascontiguousarray(a), "sym_int4")
+            ctypes.memmove(dst, packed.ctypes.data, packed.nbytes)
+            return packed.nbytes
+
+        ggml.ggml_quantize_tensor = quantize_on_cpu
+        I, K = w_up.shape
+        N = w_down.shape[0]
+        i0, i1 = rank * I // world, (rank + 1) * I // world
+        # the AutoTP recipe (example/GPU/Deepspeed-AutoTP/deepspeed_autotp.py:81-90): the fp model is sharded first
+        # (deepspeed.init_inference replaces the linears), THEN optimize_model quantises every local shard
+        model = ShardedMLP(LinearLayer(torch.from_numpy(w_up[i0:i1].copy())),
+                           LinearAllreduce(torch.from_numpy(np.ascontiguousarray(w_down[:, i0:i1])), torch.from_numpy(bias.copy()),
+                                           mp_group=dist.group.WORLD))
+        model = optimize_model(model, low_bit="sym_int4")
+        assert isinstance(model.up_proj, lbl.LowBitLinear) and model.up_proj.mp_group is None
+        assert isinstance(model.down_proj, lbl.LowBitLinear) and model.down_proj.mp_group is dist.group.WORLD
+        assert model.up_proj.weight_shape == (I // world, K) and model.down_proj.weight_shape == (N, I // world)
+        # the local shards were quantised like any other weight: same bytes as slicing the unsharded packed weight
+        np.testing.assert_array_equal(model.up_proj.weight.data.numpy(), oracle.quantize(w_up[i0:i1], "sym_int4"))
+        y = model(torch.from_numpy(x))
+        h_full = oracle.matmul(oracle.quantize(w_up, "sym_int4"), (I, K), "sym_int4", x)
+        y_full = oracle.matmul(oracle.quantize(w_down, "sym_int4"), (N, I), "sym_int4", h_full) + bias
+        np.testing.assert_allclose(y.numpy(), y_full, rtol=1e-5, atol=1e-6)
+        out[rank] = 1
+    finally:
+        dist.destroy_process_group()
+
+
+def test_autotp_sharded_model_through_optimize_model_gloo_world2(native_lib):
+    rng = np.random.default_rng(11)
+    K, I, N, M = 128, 256, 64, 2
+    w_up = (rng.standard_normal((I, K)) * 0.05).astype(np.float32)
+    w_down = (rng.standard_normal((N, I)) * 0.05).astype(np.float32)
+    bias = rng.standard_normal(N).astype(np.float32)
+    x = rng.standard_normal((M, K)).astype(np.float32)
+    world = 2
+    ctx = mp.get_context("spawn")
+    out = ctx.Manager().dict()
+    port = _free_port()
+    procs = [ctx.Process(target=_autotp_worker, args=(r, world, port, w_up, w_down, bias, x, out)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(timeout=120)
+    assert all(p.exitcode == 0 for p in procs), [p.exitcode for p in procs]
+    assert sorted(out.keys()) == list(range(world))
