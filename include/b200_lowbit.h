@@ -139,13 +139,13 @@ int lowbit_comm_destroy(void* d_buffer);
 int lowbit_comm_status(const void* d_buffer, int* status);
 int lowbit_allreduce_sum_cuda(void* const* peer_buffers, int rank, int world, size_t max_bytes, const void* d_in, void* d_out,
                               int64_t n, int dtype, void* stream);
-/* Row-parallel linear and its all-reduce in one call (M <= 32, n_rows % 64 == 0, M * n_rows * 4 <= max_bytes): the
- * decode GEMV's leader CTAs push their fp32 partial sums -- tagged with the communicator's call number -- straight into
- * every rank's inbox as each 64-row group finishes, and a receive kernel (started early under programmatic dependent
- * launch) polls the inboxes, adds the ranks' values in rank order, then bias / accumulate, and rounds once to y_dtype.
- * Replaces lowbit_matmul_cuda + lowbit_allreduce_sum_cuda for the reference's
+/* Row-parallel linear and its all-reduce in ONE kernel (M <= 32, n_rows % 64 == 0, M * n_rows * 4 <= max_bytes): the
+ * decode GEMV's leader CTAs send their fp32 partial sums -- tagged with the communicator's call number -- into every
+ * peer's inbox as each 64-row group finishes, wait (bounded) for the peers' words of the same rows in the own buffer, add
+ * the ranks' values in rank order, then bias / accumulate, and round once to y_dtype; the last leader advances the call
+ * counter.  Replaces lowbit_matmul_cuda + lowbit_allreduce_sum_cuda for the reference's
  * `result = matmul(...); all_reduce(result); result += bias` (low_bit_linear.py:704-725).  The sum is taken over the
- * fp32 partials (the separate all-reduce sums values already rounded to y_dtype). */
+ * fp32 partials (the separate all-reduce sums values already rounded to y_dtype); same bits on every rank. */
 int lowbit_matmul_allreduce_cuda(const void* d_w, int qtype, int64_t n_rows, int64_t k, const void* d_x, int x_dtype, int64_t m,
                                  void* d_y, int y_dtype, const void* d_bias, int accumulate, void* const* peer_buffers, int rank,
                                  int world, size_t max_bytes, void* workspace, size_t workspace_bytes, void* stream);

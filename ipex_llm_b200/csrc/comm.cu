@@ -43,7 +43,7 @@ constexpr int COMM_CHUNK_BYTES = COMM_THREADS * 8;              // two 4-byte wo
 constexpr size_t COMM_HEADER_BYTES = 1024;                      // epochs 256 B, status
 // polls per second of waiting, roughly (a poll = one volatile load round trip + a 256 ns sleep once the wait is long)
 constexpr double COMM_POLLS_PER_SECOND = 1.5e6;
-static_assert(COMM_MAX_CTAS * 4 + 4 <= COMM_HEADER_BYTES, "header too small");
+static_assert(COMM_MAX_CTAS * 4 + 8 <= COMM_HEADER_BYTES, "header too small");   // epochs, status, finished-leader count
 
 struct CommArgs {
     uint8_t* peer[COMM_MAX_WORLD];       // every rank's buffer as mapped into this process (peer[rank] = own)
@@ -188,105 +188,6 @@ __global__ void __launch_bounds__(COMM_THREADS) allreduce_kernel(const CommArgs 
     if (tid == 0) epochs[c] = epoch;
 }
 
-// Receive side of a row-parallel linear whose GEMV pushed its fp32 partial results itself (GemvArgs::push_*): every
-// rank's inbox -- the own one included -- holds one {fp32 value, call number} word per output element.  Poll, add
-// the ranks' values in rank order, add bias / the previous y, round once to y's dtype, advance the call counter.
-struct RecvArgs {
-    uint8_t* own; int world;
-    size_t inbox_bytes;
-    void* y; int y_dtype; const void* bias; int accumulate;
-    int64_t n_words, words_per_cta, n_cols;
-    int pdl;
-    uint32_t spin_limit;
-};
-
-__global__ void __launch_bounds__(COMM_THREADS) recv_sum_kernel(const RecvArgs A) {
-    const int c = blockIdx.x, tid = threadIdx.x;
-    uint32_t* epochs = reinterpret_cast<uint32_t*>(A.own);
-    uint32_t* status = epochs + COMM_MAX_CTAS;
-    // Under programmatic dependent launch: release the next kernel of the stream at once (a linear streams its weights
-    // first and waits for this grid before it reads y), then wait for the local GEMV -- and, through its own wait, for
-    // everything in front of it, the previous call's receive kernel included: only then is the call counter current.
-    if (A.pdl) {
-        asm volatile("griddepcontrol.launch_dependents;");
-        asm volatile("griddepcontrol.wait;" ::: "memory");
-    }
-    uint32_t epoch, dead;
-    asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(epoch) : "l"(epochs + c) : "memory");
-    asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(dead) : "l"(status) : "memory");
-    epoch = next_epoch(epoch);
-    const size_t slot_off = COMM_HEADER_BYTES + (epoch & 1) * (A.inbox_bytes * COMM_MAX_WORLD);
-    const int64_t begin = (int64_t)c * A.words_per_cta;
-    const int64_t end = begin + A.words_per_cta < A.n_words ? begin + A.words_per_cta : A.n_words;
-    bool expired = dead != 0;
-    constexpr int BATCH = 4;
-    for (int64_t w0 = begin + tid; w0 < end; w0 += COMM_THREADS * BATCH) {
-        float v[BATCH];
-        uint2 got[BATCH][COMM_MAX_WORLD];             // polled in rounds, as in allreduce_kernel
-        uint32_t missing = 0;
-#pragma unroll
-        for (int j = 0; j < BATCH; j++)
-#pragma unroll
-            for (int r = 0; r < COMM_MAX_WORLD; r++)
-                if (r < A.world && w0 + j * COMM_THREADS < end) missing |= 1u << (j * 8 + r);
-        if (missing != 0 && !expired) {               // a plain spin on one word first, as in allreduce_kernel
-            const int sb = 31 - __clz(missing);       // the highest rank's word: the own rank's words arrive first
-            const uint8_t* p = A.own + slot_off + (sb & 7) * A.inbox_bytes + (w0 + (sb >> 3) * COMM_THREADS) * 8;
-            uint32_t polls = 0;
-            while (ld_word(p).y != epoch) {
-                if (++polls > A.spin_limit) { expired = true; break; }
-                if (polls > 64) __nanosleep(polls > 4096 ? 256 : 32);
-            }
-        }
-        for (uint32_t polls = 0; missing != 0 && !expired; polls++) {
-            if (polls > A.spin_limit) { expired = true; break; }
-            if (polls > 16) __nanosleep(polls > 1024 ? 256 : 32);
-#pragma unroll
-            for (int j = 0; j < BATCH; j++)
-#pragma unroll
-                for (int r = 0; r < COMM_MAX_WORLD; r++)
-                    if (missing & (1u << (j * 8 + r)))
-                        got[j][r] = ld_word(A.own + slot_off + r * A.inbox_bytes + (w0 + j * COMM_THREADS) * 8);
-#pragma unroll
-            for (int j = 0; j < BATCH; j++)
-#pragma unroll
-                for (int r = 0; r < COMM_MAX_WORLD; r++)
-                    if ((missing & (1u << (j * 8 + r))) && got[j][r].y == epoch) missing &= ~(1u << (j * 8 + r));
-        }
-#pragma unroll
-        for (int j = 0; j < BATCH; j++) {
-            v[j] = 0.0f;
-#pragma unroll
-            for (int r = 0; r < COMM_MAX_WORLD; r++)
-                if (!expired && r < A.world && w0 + j * COMM_THREADS < end) v[j] += __uint_as_float(got[j][r].x);
-            if (expired) v[j] = __uint_as_float(0x7fc00000u);        // a wait ran out: the result is NaN, not a guess
-        }
-#pragma unroll
-        for (int j = 0; j < BATCH; j++) {
-            const int64_t w = w0 + j * COMM_THREADS;
-            if (w < end) {
-                const int64_t col = w % A.n_cols;
-                float o = v[j];
-                if (A.y_dtype == DT_F32) {
-                    float* p = (float*)A.y + w;
-                    if (A.bias) o += ((const float*)A.bias)[col];
-                    *p = A.accumulate ? *p + o : o;
-                } else if (A.y_dtype == DT_F16) {
-                    __half* p = (__half*)A.y + w;
-                    if (A.bias) o += __half2float(((const __half*)A.bias)[col]);
-                    *p = __float2half_rn(A.accumulate ? __half2float(*p) + o : o);
-                } else {
-                    __nv_bfloat16* p = (__nv_bfloat16*)A.y + w;
-                    if (A.bias) o += __bfloat162float(((const __nv_bfloat16*)A.bias)[col]);
-                    *p = __float2bfloat16_rn(A.accumulate ? __bfloat162float(*p) + o : o);
-                }
-            }
-        }
-    }
-    if (expired) atomicExch(status, 1u);
-    __syncthreads();
-    if (tid == 0) epochs[c] = epoch;
-}
 }  // namespace
 }  // namespace lowbit
 
@@ -405,10 +306,11 @@ extern "C" int lowbit_allreduce_sum_cuda(void* const* peer_buffers, int rank, in
     return check_launch();
 }
 
-// Row-parallel linear + all-reduce in one call: the GEMV's leader CTAs push their fp32 sums to every rank as they
-// finish (no separate send pass, no kernel boundary in front of the collective), recv_sum_kernel adds them up.
-// m <= 32, n_rows % 64 == 0, m * n_rows * 4 <= max_bytes of the communicator.  bias / accumulate are applied once,
-// by the receiver, after the sum (low_bit_linear.py:715-725 adds the bias after the all-reduce).
+// Row-parallel linear + all-reduce in ONE kernel: the GEMV's leader CTAs send their fp32 sums to every peer as they
+// finish, wait for the peers' words of the same rows in the own buffer, add the ranks' values in rank order and store y
+// with bias / accumulate applied once after the sum (low_bit_linear.py:715-725 adds the bias after the all-reduce).  No
+// send pass, no receive kernel, no kernel boundary between the matmul and the collective: a decode-sized all-reduce costs
+// one NVLink crossing at the end of the row groups' tails.  m <= 32, n_rows % 64 == 0, m * n_rows * 4 <= max_bytes.
 extern "C" int lowbit_matmul_allreduce_cuda(const void* d_w, int qtype, int64_t n_rows, int64_t k, const void* d_x, int x_dtype,
                                             int64_t m, void* d_y, int y_dtype, const void* d_bias, int accumulate,
                                             void* const* peer_buffers, int rank, int world, size_t max_bytes, void* workspace,
@@ -426,34 +328,16 @@ extern "C" int lowbit_matmul_allreduce_cuda(const void* d_w, int qtype, int64_t 
         if (!peer_buffers[r]) { set_error(LB_ERR_ARG, "lowbit_matmul_allreduce_cuda: peer buffer %d is NULL", r); return LB_ERR_ARG; }
     const size_t inbox = comm_inbox_bytes(max_bytes);
     GemvPush push = {};
-    push.world = world; push.slot_bytes = inbox * COMM_MAX_WORLD;
-    push.epochs = reinterpret_cast<const unsigned int*>(peer_buffers[rank]);
+    push.world = world; push.rank = rank; push.slot_bytes = inbox * COMM_MAX_WORLD; push.inbox_bytes = inbox;
+    push.epochs = reinterpret_cast<unsigned int*>(peer_buffers[rank]);
+    push.own = (unsigned long long)((uint8_t*)peer_buffers[rank] + COMM_HEADER_BYTES);
+    push.spin_limit = comm_spin_limit();
     for (int r = 0; r < world; r++) push.inbox[r] = (unsigned long long)((uint8_t*)peer_buffers[r] + COMM_HEADER_BYTES + (size_t)rank * inbox);
     gemv_set_push(&push);
-    int rc = gemv_launch(d_w, qtype, n_rows, k, d_x, x_dtype, m, d_y, y_dtype, nullptr, 0, workspace, workspace_bytes, (cudaStream_t)stream);
+    int rc = gemv_launch_ex(d_w, nullptr, 0, qtype, n_rows, k, d_x, x_dtype, m, d_y, y_dtype, d_bias, accumulate, workspace, workspace_bytes,
+                            (cudaStream_t)stream);
     gemv_set_push(nullptr);
-    if (rc) {
-        if (rc == LB_ERR_ARG) set_error(rc, "lowbit_matmul_allreduce_cuda: the GEMV does not take this shape / qtype (qtype %d, N %lld, K %lld, M %lld)",
-                                        qtype, (long long)n_rows, (long long)k, (long long)m);
-        return rc;
-    }
-    RecvArgs A;
-    A.own = (uint8_t*)peer_buffers[rank]; A.world = world; A.inbox_bytes = inbox;
-    A.y = d_y; A.y_dtype = y_dtype; A.bias = d_bias; A.accumulate = accumulate;
-    A.n_words = n_words; A.n_cols = n_rows;
-    // the grid follows from max_bytes alone, as in lowbit_allreduce_sum_cuda (words of 4 payload bytes)
-    int ctas = (int)((max_bytes + COMM_CHUNK_BYTES - 1) / COMM_CHUNK_BYTES);
-    if (ctas > COMM_MAX_CTAS) ctas = COMM_MAX_CTAS;
-    A.words_per_cta = (int64_t)(((max_bytes + ctas - 1) / ctas + 15) / 16 * 16) / 4;
-    A.pdl = gemv_get_pdl();
-    A.spin_limit = comm_spin_limit();
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3((unsigned)ctas); cfg.blockDim = dim3(COMM_THREADS); cfg.dynamicSmemBytes = 0; cfg.stream = (cudaStream_t)stream;
-    cudaLaunchAttribute at[1];
-    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    at[0].val.programmaticStreamSerializationAllowed = 1;
-    cfg.attrs = at; cfg.numAttrs = A.pdl ? 1 : 0;
-    cudaLaunchKernelEx(&cfg, recv_sum_kernel, A);
-    note_launch();
-    return check_launch();
+    if (rc == LB_ERR_ARG) set_error(rc, "lowbit_matmul_allreduce_cuda: the GEMV does not take this shape / qtype (qtype %d, N %lld, K %lld, M %lld)",
+                                    qtype, (long long)n_rows, (long long)k, (long long)m);
+    return rc;
 }

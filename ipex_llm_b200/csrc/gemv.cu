@@ -144,8 +144,8 @@ int gemv_launch_ex(const void* w, const void* w2, int act, int qt, int64_t n_row
     qt = canon_qtype(qt);
     const GemvPush push = t_push;                      // one-shot
     t_push = GemvPush{};
-    // pushing to the peers: one pass (m <= 32), every row in the tensor-core part, bias / accumulate left to the receiver
-    if (push.world > 0 && (w2 || m > 8 * GEMV_MAX_NT || !has_mma_codec(qt) || n_rows % RG_ROWS || bias || accumulate)) return LB_ERR_ARG;
+    // fused all-reduce: one pass (m <= 32), every row in the tensor-core part
+    if (push.world > 0 && (w2 || m > 8 * GEMV_MAX_NT || !has_mma_codec(qt) || n_rows % RG_ROWS)) return LB_ERR_ARG;
     if (w2 && (!gemv_mlp_fused_supported(qt, n_rows, k, m) || ((uintptr_t)w2 & 15) || bias || accumulate)) return LB_ERR_ARG;
     if (!supported(qt) || k <= 0 || k % QK || n_rows <= 0 || m <= 0) return LB_ERR_ARG;
     if (x_dtype < 0 || x_dtype > 2 || y_dtype < 0 || y_dtype > 2) return LB_ERR_ARG;
@@ -167,7 +167,8 @@ int gemv_launch_ex(const void* w, const void* w2, int act, int qt, int64_t n_row
             A.pdl = g_pdl; A.ts = g_ts;
             A.next_w = t_next_w; A.next_bytes = t_next_bytes;
             t_next_w = nullptr; t_next_bytes = 0;            // one-shot hint
-            A.push_world = push.world; A.push_slot_bytes = push.slot_bytes; A.push_epochs = push.epochs;
+            A.push_world = push.world; A.push_rank = push.rank; A.push_slot_bytes = push.slot_bytes; A.push_epochs = push.epochs;
+            A.push_own = push.own; A.push_inbox_bytes = push.inbox_bytes; A.push_spin_limit = push.spin_limit;
             for (int r = 0; r < 8; r++) A.push_inbox[r] = push.inbox[r];
             if (x_dtype == DT_F32) {
                 const size_t need = gemv_workspace_size(n_rows, k, mc, x_dtype);

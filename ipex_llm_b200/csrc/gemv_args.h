@@ -49,21 +49,28 @@ struct GemvArgs {
     int n_experts;                         // ids outside [0, n_experts) contribute zero
     int n_seg;
     const void* seg_scale; int seg_scale_dtype;
-    // row-parallel linear under tensor parallelism (comm.cu): instead of storing y, the leader CTA of every row group
-    // pushes its fp32 sums, each with the communicator's call number, into this rank's inbox in every rank's buffer
-    // (8-byte stores over NVLink); the receive kernel that follows adds the ranks' words up.  push_world = 0: store y.
-    int push_world;
+    // row-parallel linear under tensor parallelism (comm.cu): the matmul and its all-reduce are ONE kernel.  The leader
+    // CTA of every 64-row group sends its fp32 sums, each with the communicator's call number, into this rank's inbox in
+    // every PEER's buffer (8-byte stores over NVLink), then waits for the peers' words of the same rows in its own buffer,
+    // adds the ranks' values in rank order (every rank gets the same bits), applies bias / accumulate and stores y.  The
+    // last leader to finish advances the call counter.  push_world = 0: an ordinary matmul.
+    int push_world, push_rank;
     unsigned long long push_inbox[8];      // address of this rank's inbox (slot 0) inside rank r's buffer
+    unsigned long long push_own;           // slot 0 of rank 0's inbox inside the OWN buffer (the words to wait for)
+    unsigned long long push_inbox_bytes;   // rank r's inbox = rank 0's + r * push_inbox_bytes
     unsigned long long push_slot_bytes;    // slot 1 = slot 0 + push_slot_bytes
-    const unsigned int* push_epochs;       // the communicator's device-resident call counter (own buffer)
+    unsigned int* push_epochs;             // own buffer's header: [0..63] call counter (kept equal), [64] status, [65] finished leaders
+    unsigned int push_spin_limit;          // bound of the wait, in polls
 };
 
 // one-shot request consumed by the next gemv_launch_ex on this thread (see lowbit_matmul_allreduce_cuda)
 struct GemvPush {
-    int world;
+    int world, rank;
     unsigned long long inbox[8];
+    unsigned long long own, inbox_bytes;
     unsigned long long slot_bytes;
-    const unsigned int* epochs;
+    unsigned int* epochs;
+    unsigned int spin_limit;
 };
 
 __device__ __forceinline__ void store_out(void* y, int dt, int64_t idx, float v, const void* bias, int64_t row, int acc) {

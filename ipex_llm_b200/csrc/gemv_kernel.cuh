@@ -359,6 +359,7 @@ gemv_kernel(const GemvArgs A) {
     constexpr int NV = RG_TILES * NT * ACC;            // accumulator floats per lane and matrix
     constexpr int WB = S::warp_bytes(NT, ACC, NM);     // bytes of one warp's ring / reduction slot
     extern __shared__ __align__(128) uint8_t smem[];
+    __shared__ int s_comm_last;                        // tensor parallel: this leader CTA finished last (comm_done)
 
     // the warp index through a shuffle: the compiler then knows it is warp-uniform and keeps everything
     // derived from it (ring addresses, copy sources) in uniform registers
@@ -741,9 +742,10 @@ gemv_kernel(const GemvArgs A) {
     const int64_t N = A.G.rows;
     // call number of the communicator: its counter is advanced by the receive kernel of the previous call, which this
     // grid has waited for (stream order, or griddepcontrol.wait above)
-    unsigned int push_epoch = 0;
+    unsigned int push_epoch = 0, push_dead = 0;
     if (MODE == 0 && A.push_world > 0) {
         asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(push_epoch) : "l"(A.push_epochs) : "memory");
+        asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(push_dead) : "l"(A.push_epochs + 64) : "memory");
         push_epoch += 1;
         if (push_epoch == 0u) push_epoch = 2u;         // 0 = "never written": skipped when the counter wraps (comm.cu next_epoch)
     }
@@ -755,14 +757,65 @@ gemv_kernel(const GemvArgs A) {
         const int64_t row = (int64_t)rg * RG_ROWS + r * 16 + gg + 8 * hi;
         if (col < A.M) {
             if (MODE == 0 && A.push_world > 0) {
-                // tensor parallel: word (col, row) of this rank's partial result goes to every rank's inbox
+                // tensor parallel: word (col, row) of this rank's partial result goes to every peer's inbox ...
                 const unsigned long long off = (unsigned long long)(push_epoch & 1u) * A.push_slot_bytes + (unsigned long long)((int64_t)col * N + row) * 8ull;
+                bool bad = push_dead != 0;             // an earlier wait on this communicator ran out: NaN, no waiting
 #pragma unroll
                 for (int pr = 0; pr < 8; pr++)
-                    if (pr < A.push_world)
+                    if (!bad && pr < A.push_world && pr != A.push_rank)
                         asm volatile("st.volatile.global.v2.u32 [%0], {%1,%2};" :: "l"(A.push_inbox[pr] + off), "r"(__float_as_uint(v)), "r"(push_epoch) : "memory");
+                // ... and the peers' words of the same element arrive in the own buffer: poll in rounds (every round loads
+                // all words still missing at once -- one memory round trip whatever the world size), bounded
+                float got[8];
+                unsigned int missing = 0;
+#pragma unroll
+                for (int pr = 0; pr < 8; pr++) {
+                    got[pr] = 0.0f;
+                    if (!bad && pr < A.push_world && pr != A.push_rank) missing |= 1u << pr;
+                }
+                for (unsigned int polls = 0; missing != 0; polls++) {
+                    if (polls > A.push_spin_limit) { bad = true; break; }
+                    if (polls > 16) __nanosleep(polls > 1024 ? 256 : 32);
+                    unsigned int tag[8];
+#pragma unroll
+                    for (int pr = 0; pr < 8; pr++)
+                        if (missing & (1u << pr)) {
+                            unsigned int data;
+                            asm volatile("ld.volatile.global.v2.u32 {%0,%1}, [%2];" : "=r"(data), "=r"(tag[pr])
+                                         : "l"(A.push_own + (unsigned long long)pr * A.push_inbox_bytes + off) : "memory");
+                            got[pr] = __uint_as_float(data);
+                        }
+#pragma unroll
+                    for (int pr = 0; pr < 8; pr++)
+                        if ((missing & (1u << pr)) && tag[pr] == push_epoch) missing &= ~(1u << pr);
+                }
+                float sum = 0.0f;                      // rank order: the same additions, the same bits, on every rank
+#pragma unroll
+                for (int pr = 0; pr < 8; pr++)
+                    if (pr < A.push_world) sum += (pr == A.push_rank) ? v : got[pr];
+                if (bad) {
+                    sum = __uint_as_float(0x7fc00000u);
+                    if (!push_dead) atomicExch(A.push_epochs + 64, 1u);
+                }
+                store_out(A.y, A.y_dtype, (int64_t)col * N + row, sum, A.bias, row, A.accumulate);
             } else
                 store_out(A.y, A.y_dtype, (MODE == 1 ? (int64_t)blockIdx.z * N : (int64_t)col * N) + row, v, A.bias, row, A.accumulate);
+        }
+    };
+    // tensor parallel: the last leader CTA to finish advances the communicator's call counter (every leader has read it
+    // by then; the next call reads it after griddepcontrol.wait / stream order on this grid)
+    auto comm_done = [&]() {
+        if (MODE == 0 && A.push_world > 0 && slice == 0) {
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                __threadfence();
+                s_comm_last = atomicAdd(A.push_epochs + 65, 1u) == gridDim.y - 1;
+            }
+            __syncthreads();
+            if (s_comm_last) {
+                if (threadIdx.x < 64) A.push_epochs[threadIdx.x] = push_epoch;
+                if (threadIdx.x == 0) A.push_epochs[65] = 0u;
+            }
         }
     };
     auto finish = [&](int i, const float (&vm)[NM]) {  // both matrices' sums of output i are in one thread
@@ -821,6 +874,7 @@ gemv_kernel(const GemvArgs A) {
                 }
             }
         }
+        comm_done();
         TS(5);
         return;
     }
@@ -878,6 +932,7 @@ gemv_kernel(const GemvArgs A) {
         }
         cluster_sync_all();                                      // peers' smem must outlive the reads
     }
+    comm_done();
     TS(5);
 }
 
