@@ -308,6 +308,35 @@ def prefill_numbers(model, dev, peaks):
     return out
 
 
+def quantize_numbers(dev, peaks):
+    """kernel (a): ggml_quantize_tensor on the GPU, 12288 x 4096 fp32 (the merged qkv projection) -> sym_int4; algorithmic
+    bytes = 4 B read + 34/64 B written per element; rotating over 4 source tensors (805 MB > L2)"""
+    import ctypes
+    import torch
+    import ipex_llm_b200.ggml.model.llama.llama_cpp as ggml
+    n_rows, k = 3 * HIDDEN, HIDDEN
+    srcs = [torch.randn(n_rows, k, device=dev) * 0.02 for _ in range(4)]
+    dst = torch.empty(n_rows * (k // 64) * BLK, dtype=torch.uint8, device=dev)
+    st = ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+
+    def run():
+        for src in srcs:
+            ggml.ggml_quantize_tensor_cuda(ctypes.c_void_p(src.data_ptr()), ctypes.c_void_p(dst.data_ptr()), 2, n_rows * k, k, None, False, st)
+
+    run()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(5):
+        run()
+    e1.record()
+    torch.cuda.synchronize()
+    us = e0.elapsed_time(e1) * 1e3 / 20
+    gbs = n_rows * k * (4 + BLK / 64) / (us * 1e-6) / 1e9
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    return {"shape": [n_rows, k], "us": us, "GBps": gbs, "frac_of_hbm_peak": gbs / peak}
+
+
 def tp_numbers(args, dev, world, rank):
     """Llama-2-70B sym_int4 bs1 LowBitLinear stream, column/row sharded over the ranks with the all-reduce after o_proj and
     down_proj (BASELINE.json configs[3]; the reference's AutoTP recipe), and the same stream on ONE GPU measured on rank 0
@@ -482,6 +511,7 @@ def run_ours(args):
     except Exception:  # noqa: BLE001
         pass
     prefill = prefill_numbers(model, dev, peaks) if (rank == 0 and not args.no_prefill) else None
+    quant = quantize_numbers(dev, peaks) if (rank == 0 and not args.no_prefill) else None
     del model
     torch.cuda.empty_cache()
     tp = None
@@ -538,6 +568,8 @@ def run_ours(args):
     }
     if prefill:
         line["parsed"]["prefill"] = prefill
+    if quant:
+        line["parsed"]["quantize"] = quant
     if tp:
         line["parsed"]["tp"] = tp
     if cpu:

@@ -359,7 +359,6 @@ gemv_kernel(const GemvArgs A) {
     constexpr int NV = RG_TILES * NT * ACC;            // accumulator floats per lane and matrix
     constexpr int WB = S::warp_bytes(NT, ACC, NM);     // bytes of one warp's ring / reduction slot
     extern __shared__ __align__(128) uint8_t smem[];
-    __shared__ int s_comm_last;                        // tensor parallel: this leader CTA finished last (comm_done)
 
     // the warp index through a shuffle: the compiler then knows it is warp-uniform and keeps everything
     // derived from it (ring addresses, copy sources) in uniform registers
@@ -806,13 +805,14 @@ gemv_kernel(const GemvArgs A) {
     // by then; the next call reads it after griddepcontrol.wait / stream order on this grid)
     auto comm_done = [&]() {
         if (MODE == 0 && A.push_world > 0 && slice == 0) {
+            volatile int* s_last = reinterpret_cast<volatile int*>(smem);   // the rings are idle by now
             __syncthreads();
             if (threadIdx.x == 0) {
                 __threadfence();
-                s_comm_last = atomicAdd(A.push_epochs + 65, 1u) == gridDim.y - 1;
+                *s_last = atomicAdd(A.push_epochs + 65, 1u) == gridDim.y - 1;
             }
             __syncthreads();
-            if (s_comm_last) {
+            if (*s_last) {
                 if (threadIdx.x < 64) A.push_epochs[threadIdx.x] = push_epoch;
                 if (threadIdx.x == 0) A.push_epochs[65] = 0u;
             }

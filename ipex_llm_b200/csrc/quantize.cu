@@ -11,7 +11,8 @@
 //   nf4      : d = absmax, code = nearest NormalFloat4 entry (ties to the lower index)
 //   fp8/fp6  : d = absmax / MAX, code = RNE-saturating e4m3 / e5m2 / e3m2 of x*(1/d);
 //              scale_search tries 9 multipliers of d and keeps the least squared error.
-// HBM-bound: 4 bytes read per element, ~0.53-1.03 written.
+// HBM-bound: 4 bytes read per element, ~0.53-1.03 written.  A warp takes 8 consecutive blocks per pass (all loads first,
+// redux.sync reductions, records staged in shared memory and stored in 16-byte pieces); see quantize_kernel.
 #include <cuda_fp8.h>
 #include <cuda_fp6.h>
 #include "lowbit_common.cuh"
@@ -75,7 +76,26 @@ __device__ __forceinline__ uint32_t nf4_encode(float v) {
 static __device__ __constant__ float kSearchFactors[9] = {1.0f, 0.95f, 1.05f, 0.9f, 1.1f, 0.85f, 1.15f, 0.8f, 1.2f};
 
 constexpr int QUANT_WARPS = 8;
+constexpr int QUANT_GROUP = 8;      // consecutive blocks a warp takes at once: 8 records are a multiple of 16 bytes
 
+// monotonic unsigned key of a float (a < b  <=>  key(a) < key(b); -0 < +0)
+__device__ __forceinline__ uint32_t ordered_key(float v) {
+    const uint32_t u = __float_as_uint(v);
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+// the element (index in 0..63, value) a serial scan "if (x better than best) best = x" over the block ends with, given
+// that `hit0` / `hit1` say whether this lane's element l / l + 32 compares EQUAL to the block's best: the first hit
+__device__ __forceinline__ float first_hit_value(bool hit0, bool hit1, float x0, float x1) {
+    const uint32_t b0 = __ballot_sync(0xffffffffu, hit0), b1 = __ballot_sync(0xffffffffu, hit1);
+    const int src = b0 ? (__ffs(b0) - 1) : (__ffs(b1) - 1);
+    const float v0 = __shfl_sync(0xffffffffu, x0, src), v1 = __shfl_sync(0xffffffffu, x1, src);
+    return b0 ? v0 : v1;
+}
+
+// One warp quantises QUANT_GROUP consecutive blocks per pass: all of the group's elements are requested first (2 KB per
+// warp in flight: the kernel is HBM-bound and needs the memory-level parallelism), the block extrema come from redux.sync
+// (one instruction per reduction) + a ballot that finds the first element equal to the extremum (the serial scan's
+// "first wins"), the records are assembled in shared memory and leave as 16-byte stores.
 template <int QT>
 __global__ void __launch_bounds__(QUANT_WARPS * 32)
 quantize_kernel(const float* __restrict__ src, uint8_t* __restrict__ dst, size_t nblk,
@@ -83,22 +103,39 @@ quantize_kernel(const float* __restrict__ src, uint8_t* __restrict__ dst, size_t
     constexpr int BS = (QT == QT_ASYM_INT4) ? 36 : (QT == QT_FP8_E4M3 || QT == QT_FP8_E5M2) ? 66
                      : (QT == QT_FP6) ? 50 : 34;
     constexpr bool IS4 = (QT == QT_SYM_INT4 || QT == QT_ASYM_INT4 || QT == QT_NF4);
+    constexpr bool SEARCH = (QT == QT_FP8_E4M3 || QT == QT_FP6 || QT == QT_FP8_E5M2);
+    static_assert((QUANT_GROUP * BS) % 16 == 0, "a group of records must be a whole number of 16-byte pieces");
     __shared__ unsigned int s_hist[16];
-    __shared__ float s_err[QUANT_WARPS][9][64];   // scale search only (fp8 / fp6)
+    __shared__ float s_err[SEARCH ? QUANT_WARPS : 1][9][64];   // scale search only (fp8 / fp6)
+    __shared__ __align__(16) uint8_t s_rec[QUANT_WARPS][QUANT_GROUP * BS];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     if (IS4 && hist) { if (threadIdx.x < 16) s_hist[threadIdx.x] = 0; __syncthreads(); }
 
+    const size_t ngroups = (nblk + QUANT_GROUP - 1) / QUANT_GROUP;
     const size_t wstride = (size_t)gridDim.x * QUANT_WARPS;
-    for (size_t b = (size_t)blockIdx.x * QUANT_WARPS + warp; b < nblk; b += wstride) {
-        const float x0 = src[b * 64 + lane], x1 = src[b * 64 + 32 + lane];
-        uint8_t* out = dst + b * BS;
+    for (size_t grp = (size_t)blockIdx.x * QUANT_WARPS + warp; grp < ngroups; grp += wstride) {
+        const size_t b_first = grp * QUANT_GROUP;
+        const int nb = (int)((nblk - b_first) < (size_t)QUANT_GROUP ? (nblk - b_first) : (size_t)QUANT_GROUP);
+        float xa[QUANT_GROUP], xb[QUANT_GROUP];
+#pragma unroll
+        for (int j = 0; j < QUANT_GROUP; j++) {
+            xa[j] = 0.0f; xb[j] = 0.0f;
+            if (j < nb) {
+                xa[j] = __ldcs(src + (b_first + j) * 64 + lane);          // streamed once: evict-first
+                xb[j] = __ldcs(src + (b_first + j) * 64 + 32 + lane);
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < QUANT_GROUP; j++) {
+        if (j < nb) {
+        const float x0 = xa[j], x1 = xb[j];
+        uint8_t* out = s_rec[warp] + j * BS;
         uint32_t q0 = 0, q1 = 0;
         if (QT == QT_SYM_INT4) {
-            float a0 = fabsf(x0), a1 = fabsf(x1);
-            float key = a0, val = x0; int idx = lane;
-            if (a1 > a0) { key = a1; val = x1; idx = lane + 32; }
-            warp_argbest(key, idx, val, true);
-            const float d = (key > 0.0f) ? __fdiv_rn(val, -8.0f) : __fdiv_rn(0.0f, -8.0f);
+            const uint32_t a0 = __float_as_uint(x0) & 0x7fffffffu, a1 = __float_as_uint(x1) & 0x7fffffffu;
+            const uint32_t amax = __reduce_max_sync(0xffffffffu, max(a0, a1));        // |x| bits order like |x|
+            const float val = first_hit_value(a0 == amax, a1 == amax, x0, x1);        // the first element with |x| == max
+            const float d = (amax != 0u) ? __fmul_rn(val, -0.125f) : -0.0f;      // x / -8: exact as a product
             const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
             int i0 = (int)(signed char)(int)__fadd_rn(__fmul_rn(x0, id), 8.5f);
             int i1 = (int)(signed char)(int)__fadd_rn(__fmul_rn(x1, id), 8.5f);
@@ -106,13 +143,13 @@ quantize_kernel(const float* __restrict__ src, uint8_t* __restrict__ dst, size_t
             if (lane == 0) store_half_bits(out, d);
             out[2 + lane] = (uint8_t)(q0 | (q1 << 4));
         } else if (QT == QT_ASYM_INT4) {
-            float kmin = x0, vmin = x0; int imin = lane;
-            if (x1 < x0) { kmin = x1; vmin = x1; imin = lane + 32; }
-            warp_argbest(kmin, imin, vmin, false);
-            float kmax = x0, vmax = x0; int imax = lane;
-            if (x1 > x0) { kmax = x1; vmax = x1; imax = lane + 32; }
-            warp_argbest(kmax, imax, vmax, true);
-            const float mn = vmin, mx = vmax;
+            const uint32_t k0 = ordered_key(x0), k1 = ordered_key(x1);
+            const uint32_t lo = __reduce_min_sync(0xffffffffu, min(k0, k1)), hi = __reduce_max_sync(0xffffffffu, max(k0, k1));
+            // back to floats; the serial scan keeps the FIRST element that compares equal to the extremum (-0 == +0)
+            const float lo_f = __uint_as_float((lo & 0x80000000u) ? (lo & 0x7fffffffu) : ~lo);
+            const float hi_f = __uint_as_float((hi & 0x80000000u) ? (hi & 0x7fffffffu) : ~hi);
+            const float mn = first_hit_value(x0 == lo_f, x1 == lo_f, x0, x1);
+            const float mx = first_hit_value(x0 == hi_f, x1 == hi_f, x0, x1);
             const float d = __fdiv_rn(__fsub_rn(mx, mn), 15.0f);
             const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
             int i0 = (int)(signed char)(int)__fadd_rn(__fmul_rn(__fsub_rn(x0, mn), id), 0.5f);
@@ -123,13 +160,15 @@ quantize_kernel(const float* __restrict__ src, uint8_t* __restrict__ dst, size_t
             }
             out[4 + lane] = (uint8_t)(q0 | (q1 << 4));
         } else if (QT == QT_NF4) {
-            const float d = warp_max(fmaxf(fabsf(x0), fabsf(x1)));
+            const uint32_t a0 = __float_as_uint(x0) & 0x7fffffffu, a1 = __float_as_uint(x1) & 0x7fffffffu;
+            const float d = __uint_as_float(__reduce_max_sync(0xffffffffu, max(a0, a1)));
             const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
             q0 = nf4_encode(__fmul_rn(x0, id)); q1 = nf4_encode(__fmul_rn(x1, id));
             if (lane == 0) store_half_bits(out, d);
             out[2 + lane] = (uint8_t)(q0 | (q1 << 4));
         } else {
-            const float amax = warp_max(fmaxf(fabsf(x0), fabsf(x1)));
+            const uint32_t a0 = __float_as_uint(x0) & 0x7fffffffu, a1 = __float_as_uint(x1) & 0x7fffffffu;
+            const float amax = __uint_as_float(__reduce_max_sync(0xffffffffu, max(a0, a1)));
             const float d0 = __fdiv_rn(amax, fmt_max<QT>());
             float d = d0;
             if (scale_search && d0 != 0.0f) {
@@ -143,12 +182,12 @@ quantize_kernel(const float* __restrict__ src, uint8_t* __restrict__ dst, size_t
                     const float d16 = __half2float(__float2half_rn(dc));
                     const float e0 = __fsub_rn(__fmul_rn(mini_decode<QT>(mini_encode<QT>(__fmul_rn(x0, idc))), d16), x0);
                     const float e1 = __fsub_rn(__fmul_rn(mini_decode<QT>(mini_encode<QT>(__fmul_rn(x1, idc))), d16), x1);
-                    s_err[warp][c][lane] = __fmul_rn(e0, e0);
-                    s_err[warp][c][lane + 32] = __fmul_rn(e1, e1);
+                    s_err[SEARCH ? warp : 0][c][lane] = __fmul_rn(e0, e0);
+                    s_err[SEARCH ? warp : 0][c][lane + 32] = __fmul_rn(e1, e1);
                 }
                 __syncwarp();
                 float err = 0.0f;
-                if (lane < 9) for (int j = 0; j < 64; j++) err = __fadd_rn(err, s_err[warp][lane][j]);
+                if (lane < 9) for (int e = 0; e < 64; e++) err = __fadd_rn(err, s_err[SEARCH ? warp : 0][lane][e]);
                 float best = __int_as_float(0x7f800000); int bc = 0;
                 for (int c = 0; c < 9; c++) {
                     const float ec = __shfl_sync(0xffffffffu, err, c);
@@ -169,10 +208,10 @@ quantize_kernel(const float* __restrict__ src, uint8_t* __restrict__ dst, size_t
                     w0 |= (__shfl_sync(0xffffffffu, q0, base + i) & 0x3f) << (6 * i);
                     w1 |= (__shfl_sync(0xffffffffu, q1, base + i) & 0x3f) << (6 * i);
                 }
-                const int byte = lane & 3, grp = lane >> 2;
+                const int byte = lane & 3, g4 = lane >> 2;
                 if (byte < 3) {
-                    out[2 + 3 * grp + byte] = (uint8_t)(w0 >> (8 * byte));
-                    out[2 + 3 * (grp + 8) + byte] = (uint8_t)(w1 >> (8 * byte));
+                    out[2 + 3 * g4 + byte] = (uint8_t)(w0 >> (8 * byte));
+                    out[2 + 3 * (g4 + 8) + byte] = (uint8_t)(w1 >> (8 * byte));
                 }
             } else {
                 out[2 + lane] = (uint8_t)q0;
@@ -180,6 +219,20 @@ quantize_kernel(const float* __restrict__ src, uint8_t* __restrict__ dst, size_t
             }
         }
         if (IS4 && hist) { atomicAdd(&s_hist[q0], 1u); atomicAdd(&s_hist[q1], 1u); }
+        }
+        }
+        __syncwarp();
+        // the group's records: 16-byte pieces when the group is complete (its offset, 8 * BS * grp, is 16-byte aligned
+        // whenever dst is), bytes for the tail group and unaligned destinations
+        uint8_t* gdst = dst + b_first * BS;
+        if (nb == QUANT_GROUP && !((uintptr_t)gdst & 15)) {
+            constexpr int NV = QUANT_GROUP * BS / 16;
+            for (int v = lane; v < NV; v += 32)
+                __stcs(reinterpret_cast<uint4*>(gdst) + v, reinterpret_cast<const uint4*>(s_rec[warp])[v]);
+        } else {
+            for (int v = lane; v < nb * BS; v += 32) gdst[v] = s_rec[warp][v];
+        }
+        __syncwarp();
     }
     if (IS4 && hist) {
         __syncthreads();
@@ -196,8 +249,25 @@ int quantize_launch(const float* src, void* dst, int qt, size_t n, int k, int64_
     if (hist) {
         if (cudaMemsetAsync(hist, 0, 16 * sizeof(int64_t), st) != cudaSuccess) return check_launch();
     }
-    size_t blocks = (nblk + QUANT_WARPS - 1) / QUANT_WARPS;
-    const size_t cap = (size_t)sm_count() * 8;
+    size_t blocks = ((nblk + QUANT_GROUP - 1) / QUANT_GROUP + QUANT_WARPS - 1) / QUANT_WARPS;
+    // one wave: as many CTAs as are resident at once (the kernel loops over its groups)
+    static int per_sm[6] = {0, 0, 0, 0, 0, 0};
+    const int qi = qt == QT_SYM_INT4 ? 0 : qt == QT_ASYM_INT4 ? 1 : qt == QT_NF4 ? 2 : qt == QT_FP8_E4M3 ? 3 : qt == QT_FP8_E5M2 ? 4 : 5;
+    if (!per_sm[qi]) {
+        int n = 0;
+        cudaError_t e = cudaErrorUnknown;
+        switch (qt) {
+            case QT_SYM_INT4:  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, quantize_kernel<QT_SYM_INT4>, QUANT_WARPS * 32, 0); break;
+            case QT_ASYM_INT4: e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, quantize_kernel<QT_ASYM_INT4>, QUANT_WARPS * 32, 0); break;
+            case QT_NF4:       e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, quantize_kernel<QT_NF4>, QUANT_WARPS * 32, 0); break;
+            case QT_FP8_E4M3:  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, quantize_kernel<QT_FP8_E4M3>, QUANT_WARPS * 32, 0); break;
+            case QT_FP8_E5M2:  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, quantize_kernel<QT_FP8_E5M2>, QUANT_WARPS * 32, 0); break;
+            default:           e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, quantize_kernel<QT_FP6>, QUANT_WARPS * 32, 0); break;
+        }
+        if (e != cudaSuccess || n <= 0) { cudaGetLastError(); n = 4; }
+        per_sm[qi] = n;
+    }
+    const size_t cap = (size_t)sm_count() * per_sm[qi];
     const int grid = (int)(blocks > cap ? cap : blocks);
     unsigned long long* h = (unsigned long long*)hist;
     uint8_t* o = (uint8_t*)dst;

@@ -39,6 +39,11 @@ def is_linear_module(module):
     return False, None
 
 
+def _is_fused_experts(module):
+    from ipex_llm_b200.transformers.models.mixtral import is_fused_experts
+    return is_fused_experts(module)
+
+
 def is_lm_head(name, model_config, out_features):
     """CV:126-130"""
     return name == "lm_head" or getattr(model_config, "vocab_size", None) == out_features
@@ -104,6 +109,13 @@ def _replace_with_low_bit_linear(model, qtype, modules_to_not_convert=None, conv
             model._modules[name].requires_grad_(False)
             has_been_replaced = True
             module.weight = None
+        elif _is_fused_experts(module) and module.gate_up_proj.shape[2] % 64 == 0 and module.down_proj.shape[2] % 64 == 0:
+            # transformers >= 5 mixture-of-experts layers: every expert of the layer in two 3-D parameters (SURVEY 7,
+            # "hard parts"); they become per-expert LowBitLinear modules, quantised like any other linear
+            from ipex_llm_b200.transformers.models.mixtral import LowBitExperts
+            model._modules[name] = LowBitExperts.from_fused(module, qtype, convert_shape_only, enable_scale_search)
+            has_been_replaced = True
+            continue
         elif embedding_qtype is not None and type(module) == nn.Embedding and module.embedding_dim % 64 == 0:
             # CV:730-733: the embedding table in a low-bit block format, dequantised row by row on the GPU
             from ipex_llm_b200.transformers.embedding import LowBitEmbedding
@@ -145,6 +157,9 @@ def _optimize_pre(model, qtype=None):
     elif model_type == "mistral":
         from ipex_llm_b200.transformers.models.mistral import merge_qkv
         model.apply(merge_qkv)
+    elif model_type == "mixtral":
+        from ipex_llm_b200.transformers.models.mixtral import merge_qkv
+        model.apply(merge_qkv)
     return model
 
 
@@ -170,6 +185,12 @@ def _optimize_post(model):
         convert_forward(model, module.MistralMLP, mlp_silu_forward)
         convert_forward(model, module.MistralModel, mistral_model_forward)
         convert_forward(model, module.MistralAttention, mistral_attention_forward)
+    elif model_type == "mixtral":
+        module = importlib.import_module(model.__class__.__module__)
+        from ipex_llm_b200.transformers.models.mixtral import mixtral_model_forward, mixtral_attention_forward
+        convert_forward(model, module.MixtralRMSNorm, rms_norm_forward)
+        convert_forward(model, module.MixtralModel, mixtral_model_forward)
+        convert_forward(model, module.MixtralAttention, mixtral_attention_forward)
     else:
         return model
     if hasattr(model, "generate"):

@@ -70,7 +70,9 @@ class DecodeGraph:
         self.h, self.xn = z(B, self.H), z(B, self.H)
         self.qkv = z(B, 1, tot)
         self.attn = z(B, self.Hq, 1, self.D)
-        inter = core.layers[0].mlp.gate_proj.out_features
+        mlp0 = core.layers[0].mlp
+        self.moe = hasattr(mlp0, "experts") and hasattr(mlp0, "gate")          # mixture-of-experts layers (Mixtral)
+        inter = mlp0.experts.intermediate_dim if self.moe else mlp0.gate_proj.out_features
         self.act = z(B, inter)
         self.logits = z(B, model.lm_head.out_features)
         self.k_cache = [z(B, self.Hkv, capacity, self.D, dt=torch.uint8) for _ in range(self.n_layers)]
@@ -98,12 +100,28 @@ class DecodeGraph:
                 and (lin.bias is None or lin.bias.dtype == out.dtype):
             lowbit_matmul(x, lin.weight.data, lin.weight_shape, lin.qtype, out=out, bias=lin.bias, accumulate=accumulate)
             self.launches_per_step += ggml.last_launch_count()
+        elif isinstance(lin, LowBitLinear) and hasattr(lin.mp_group, "matmul_all_reduce") and not lin.act_order \
+                and lin.mp_group.fused_supported(x.shape[0], lin.out_len, lin.qtype):
+            # row-parallel linear under tensor parallelism: matmul, all-reduce, bias and residual in one kernel
+            lin.mp_group.matmul_all_reduce(x, lin.weight.data, lin.weight_shape, lin.qtype, bias=lin.bias, out=out, accumulate=accumulate)
+            self.launches_per_step += ggml.last_launch_count()
         else:
             y = lin(x)
             if accumulate:
                 out.add_(y)
             else:
                 out.copy_(y)
+
+    def _moe(self, block):
+        """router (torch: an 8-row matmul, softmax, top-k) + the routed experts' MLPs of the token in two launches
+        (moe_forward_vec reads the routed ids on the device), accumulated into the residual stream"""
+        from ipex_llm_b200.transformers.models.mixtral import LowBitExperts
+        _, weights, index = block.gate(self.xn)
+        if self.B == 1 and isinstance(block.experts, LowBitExperts):
+            block.experts.fused_one_token(self.xn, index, weights, out=self.h, accumulate=True)
+            self.launches_per_step += ggml.last_launch_count()
+        else:
+            self.h.add_(block.experts(self.xn, index, weights))
 
     def _rms(self, norm, x, out):
         ggml.lowbit_rms_norm(x, norm.weight, self.eps, out, _stream(self.device))
@@ -127,6 +145,9 @@ class DecodeGraph:
             self.launches_per_step += ggml.last_launch_count()
             self._linear(attn.o_proj, attn2d, self.h, accumulate=True)
             self._rms(layer.post_attention_layernorm, self.h, self.xn)
+            if self.moe:
+                self._moe(mlp)
+                continue
             gate, up = mlp.gate_proj, mlp.up_proj
             if self.fuse_mlp and isinstance(gate, LowBitLinear) and isinstance(up, LowBitLinear) and gate.bias is None \
                     and up.bias is None and gate.mp_group is None and gate.qtype == up.qtype \
@@ -267,7 +288,7 @@ def _plan(model, inputs, generation_config, kwargs):
     # the step is written for the FP8 cache (half-precision models) and full-width rotary embedding; a sliding-window
     # model is served while the whole sequence fits the window (the cache never evicts, like the reference's)
     window = getattr(cfg, "sliding_window", None)
-    if not (w.dtype in (torch.float16, torch.bfloat16) and use_quantize_kv_cache(core.layers[0].mlp.down_proj, w)
+    if not (w.dtype in (torch.float16, torch.bfloat16) and use_quantize_kv_cache(core.layers[0].self_attn.o_proj, w)
             and ggml.lowbit_sdp_fp8_supported(n_q, n_kv, 1, attn.head_dim)
             and (not window or prompt_len + max_new <= window)):
         return None

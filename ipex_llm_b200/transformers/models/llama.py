@@ -17,7 +17,7 @@ def pick_kv_cache(self, inputs, past_key_values, use_cache):
     """LL:66-90 without the SnapKV branch (KV compression is out of scope): FP8 cache or block-grown fp cache"""
     if not use_cache:
         return past_key_values
-    use_quantize_kv = use_quantize_kv_cache(self.layers[0].mlp.down_proj, inputs, self.config.num_attention_heads,
+    use_quantize_kv = use_quantize_kv_cache(self.layers[0].self_attn.o_proj, inputs, self.config.num_attention_heads,
                                             self.config.num_key_value_heads)
     if use_quantize_kv and not isinstance(past_key_values, DynamicFp8Cache):
         past_key_values = DynamicFp8Cache.from_legacy_cache(past_key_values)
