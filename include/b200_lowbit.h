@@ -221,13 +221,18 @@ int lowbit_rope_kv_append_cuda(void* d_qkv, int dtype, int64_t batch_stride, int
  * value row (and tile 0 stores it in the cache), and the key splits of a (sequence, kv head) form a thread-block cluster
  * whose members push their partial softmax sums into the leader's shared memory (deterministic merge, no second launch,
  * no global scratch).  Other shapes, and caches long enough to want more than 8 splits, run the separate kernels
- * (lowbit_rope_kv_append_cuda, lowbit_sdp_fp8_devlen_cuda) and need the workspace.  Same results as the separate calls. */
+ * (lowbit_rope_kv_append_cuda, lowbit_sdp_fp8_devlen_cuda) and need the workspace.  Same results as the separate calls.
+ * cache_complete != 0: the caller guarantees that *d_len and the cached rows below it were written by work that has
+ * COMPLETED when this call's kernel starts -- under programmatic dependent launch that means an ordinarily launched
+ * kernel (or a stream synchronisation) lies between their producers and this call, as between two decode steps; the
+ * kernel then stages its first chunks of the cache while the previous kernel (the qkv projection) still drains.  0 is
+ * always safe. */
 size_t lowbit_decode_attention_workspace_size(int B, int Hq, int Hkv, int capacity, int D);
 int lowbit_decode_attention_cuda(void* d_qkv, int dtype, int64_t batch_stride, int B, int Hq, int Hkv, int D,
                                  const void* d_cos, const void* d_sin, int cs_dtype, int64_t cs_row_stride, int n_positions,
                                  const int32_t* d_len, void* d_k_cache, const int64_t* k_strides, void* d_v_cache,
                                  const int64_t* v_strides, int capacity, float scale, void* d_out, int out_dtype,
-                                 void* workspace, size_t workspace_bytes, void* stream);
+                                 int cache_complete, void* workspace, size_t workspace_bytes, void* stream);
 
 /* Greedy pick and step bookkeeping of a recorded decode step -- the torch.argmax + append of the reference's
  * generate loop (utils/benchmark_util_4_47.py:3340-3380), done on the device so that steps replay without a host

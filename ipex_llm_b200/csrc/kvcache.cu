@@ -81,6 +81,7 @@ struct SdpArgs {
     const void* qkv; int64_t qkv_sb;                               // [B][(Hq + 2 Hkv) * D] of q_dtype
     const void* cos; const void* sin; int cs_dtype; int64_t cs_row; int n_pos;    // [positions][>= D/2]
     uint8_t* kw; uint8_t* vw;                                      // the caches, writable
+    int early;                                                     // FUSED: cached rows and the length are complete: prefetch before griddepcontrol.wait
     int rt;                                                        // query rows per CTA (1, 2 or 4)
     float* part;                                                   // [B][Hkv][row tiles][n_split][RT * (D + 2)]
     void* out; int out_dtype;                                      // [B][Hq][S][D] contiguous
@@ -569,6 +570,8 @@ static int fused_splits(int B, int Hq, int Hkv, int L, int D) {
     const int base = B * Hkv * sdp_tiles(Hq, Hkv, 1, true);
     int max_by_len = (L + 127) / 128;
     if (max_by_len > 8) max_by_len = 8;
+    const char* forced = getenv("LOWBIT_DECODE_ATTN_SPLITS");          // development: fixed split count
+    if (forced && atoi(forced) > 0) return atoi(forced) < max_by_len ? atoi(forced) : max_by_len;
     const int64_t cap = (int64_t)sm_count() * 2;
     int best = 1; int64_t best_cost = INT64_MAX;
     for (int n = 1; n <= max_by_len; n++) {
@@ -588,7 +591,7 @@ extern "C" int lowbit_decode_attention_cuda(void* d_qkv, int dtype, int64_t batc
                                             const void* d_cos, const void* d_sin, int cs_dtype, int64_t cs_row_stride,
                                             int n_positions, const int32_t* d_len, void* d_k_cache, const int64_t* k_strides,
                                             void* d_v_cache, const int64_t* v_strides, int capacity, float scale, void* d_out,
-                                            int out_dtype, void* workspace, size_t workspace_bytes, void* stream) {
+                                            int out_dtype, int cache_complete, void* workspace, size_t workspace_bytes, void* stream) {
     reset_launch_count();
     if (!d_qkv || !d_cos || !d_sin || !d_len || !d_k_cache || !d_v_cache || !k_strides || !v_strides || !d_out || dtype < 0 ||
         dtype > 2 || cs_dtype < 0 || cs_dtype > 2 || out_dtype < 0 || out_dtype > 2 || B <= 0 || capacity <= 0 || n_positions <= 0 ||
@@ -612,7 +615,7 @@ extern "C" int lowbit_decode_attention_cuda(void* d_qkv, int dtype, int64_t batc
         A.kw = (uint8_t*)d_k_cache; A.vw = (uint8_t*)d_v_cache;
         A.mask = nullptr; A.causal = 0; A.scale_log2e = scale * 1.4426950408889634f;
         A.B = B; A.Hq = Hq; A.Hkv = Hkv; A.S = 1; A.L = capacity; A.D = D;
-        A.len_ptr = d_len; A.len_add = 1;
+        A.len_ptr = d_len; A.len_add = 1; A.early = cache_complete ? 1 : 0;
         A.qkv = d_qkv; A.qkv_sb = batch_stride; A.cos = d_cos; A.sin = d_sin; A.cs_dtype = cs_dtype; A.cs_row = cs_row_stride;
         A.n_pos = n_positions;
         A.n_split = fused_splits(B, Hq, Hkv, capacity, D);

@@ -106,7 +106,56 @@ sdp_fp8_decode_mma_kernel(const SdpArgs A) {
             }
             asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
         }
-        asm volatile("griddepcontrol.wait;" ::: "memory");           // qkv and the cache length come from earlier kernels
+        // qkv comes from the previous kernel.  The cache length and the cached rows come from earlier steps: a caller that
+        // knows them complete (A.early: an ordinarily launched kernel lies between their producers and this call) lets the
+        // first chunks stream in while the previous kernel drains; otherwise nothing is read before the wait.
+        if (!A.early) asm volatile("griddepcontrol.wait;" ::: "memory");
+    }
+    int L, keys_per_split;
+    sdp_lengths(A, L, keys_per_split);
+    const int new_pos = L - 1;                        // FUSED: position of the token being decoded
+    const int key_begin = split * keys_per_split;
+    const int key_end = min(L, key_begin + keys_per_split);
+    // NST > 0: every warp streams its chunks through a ring of NST stages filled by cp.async (16 bytes per lane and
+    // instruction, rows coalesced), NST - 1 chunks ahead of the one being used.  Inside a stage the 16-byte pieces of
+    // a row are XOR-swizzled so that the fragment reads below are bank-conflict free: key rows by (row & 1) << 2
+    // (a quarter warp reads 4 pieces of 2 consecutive rows), value rows by ((row >> 1) & 3) << 1 (a quarter warp
+    // reads 2 pieces of rows 2t).
+    uint8_t* const ring = sdp_ring + warp * (NST * 8192);
+    const uint8_t* const kb0 = A.k + b * A.k_sb + hkv * A.k_sh + 16 * (lane & 7);
+    const uint8_t* const vb0 = A.v + b * A.v_sb + hkv * A.v_sh + 16 * (lane & 7);
+    const uint32_t ring_s = (uint32_t)__cvta_generic_to_shared(ring);
+    const int r0 = lane >> 3, unit = lane & 7;        // lane copies piece `unit` of rows r0, r0 + 4, ...
+    const uint32_t k_off = r0 * 128 + ((unit ^ ((r0 & 1) << 2)) << 4);
+    const uint32_t v_off0 = 4096 + r0 * 128 + ((unit ^ (((r0 >> 1) & 3) << 1)) << 4);          // rows r0 + 8i'
+    const uint32_t v_off1 = 4096 + (r0 + 4) * 128 + ((unit ^ ((((r0 >> 1) + 2) & 3) << 1)) << 4);   // rows r0 + 4 + 8i'
+    const bool rows_128 = A.k_ss == 128 && A.v_ss == 128;
+    auto stage_chunk = [&](int c0, int slot) {
+        if (c0 < key_end) {
+            const uint32_t dst = ring_s + slot * 8192;
+            if (c0 + 32 <= key_end && rows_128) {     // a whole chunk of densely stored rows: constant address steps
+                const uint8_t* kp = kb0 + (int64_t)(c0 + r0) * 128;
+                const uint8_t* vp = vb0 + (int64_t)(c0 + r0) * 128;
+#pragma unroll
+                for (int i = 0; i < 8; i++) {
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(dst + k_off + i * 512), "l"(kp + i * 512) : "memory");
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(dst + ((i & 1) ? v_off1 : v_off0) + (i >> 1) * 1024), "l"(vp + i * 512) : "memory");
+                }
+            } else {
+#pragma unroll
+                for (int i = 0; i < 8; i++) {
+                    const int64_t key = min(c0 + 4 * i + r0, key_end - 1);
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(dst + k_off + i * 512), "l"(kb0 + key * A.k_ss) : "memory");
+                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(dst + ((i & 1) ? v_off1 : v_off0) + (i >> 1) * 1024), "l"(vb0 + key * A.v_ss) : "memory");
+                }
+            }
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    if (FUSED && A.early) {
+#pragma unroll
+        for (int s = 0; s < NST - 1; s++) stage_chunk(key_begin + (warp + SDP_WARPS * s) * 32, s);
+        asm volatile("griddepcontrol.wait;" ::: "memory");
     }
 
     // A fragments of Q: lane (g,t) holds row g, elements 64c + 16t .. +15 as 8 fp16 pairs (zeros for rows >= n_rows)
@@ -116,9 +165,6 @@ sdp_fp8_decode_mma_kernel(const SdpArgs A) {
 #pragma unroll
         for (int i = 0; i < 8; i++) qa[c][i] = 0u;
     int my_hq = 0, my_st = 0;                         // query head / token of this lane's row
-    int L, keys_per_split;
-    sdp_lengths(A, L, keys_per_split);
-    const int new_pos = L - 1;                        // FUSED: position of the token being decoded
     if (FUSED) {
         if (g < n_rows) {
             my_hq = hkv * n_rep + row0 + g;
@@ -182,8 +228,6 @@ sdp_fp8_decode_mma_kernel(const SdpArgs A) {
         }
     }
 
-    const int key_begin = split * keys_per_split;
-    const int key_end = min(L, key_begin + keys_per_split);
     // FUSED: the new row of this kv head -- lane l owns key elements l, l + 32, l + 64, l + 96 (two rotary pairs) and
     // value elements 4l .. 4l + 3 -- for every CTA whose range holds the new position; tile 0 also writes it to the cache
     const bool has_new = FUSED && new_pos >= key_begin && new_pos < key_end;
@@ -224,43 +268,7 @@ sdp_fp8_decode_mma_kernel(const SdpArgs A) {
 #pragma unroll
     for (int i = 0; i < 4; i++) z[i][0] = z[i][1] = 0.0f;
 
-    // NST > 0: every warp streams its chunks through a ring of NST stages filled by cp.async (16 bytes per lane and
-    // instruction, rows coalesced), NST - 1 chunks ahead of the one being used.  Inside a stage the 16-byte pieces of
-    // a row are XOR-swizzled so that the fragment reads below are bank-conflict free: key rows by (row & 1) << 2
-    // (a quarter warp reads 4 pieces of 2 consecutive rows), value rows by ((row >> 1) & 3) << 1 (a quarter warp
-    // reads 2 pieces of rows 2t).
-    uint8_t* const ring = sdp_ring + warp * (NST * 8192);
-    const uint8_t* const kb0 = A.k + b * A.k_sb + hkv * A.k_sh + 16 * (lane & 7);
-    const uint8_t* const vb0 = A.v + b * A.v_sb + hkv * A.v_sh + 16 * (lane & 7);
-    const uint32_t ring_s = (uint32_t)__cvta_generic_to_shared(ring);
-    const int r0 = lane >> 3, unit = lane & 7;        // lane copies piece `unit` of rows r0, r0 + 4, ...
-    const uint32_t k_off = r0 * 128 + ((unit ^ ((r0 & 1) << 2)) << 4);
-    const uint32_t v_off0 = 4096 + r0 * 128 + ((unit ^ (((r0 >> 1) & 3) << 1)) << 4);          // rows r0 + 8i'
-    const uint32_t v_off1 = 4096 + (r0 + 4) * 128 + ((unit ^ ((((r0 >> 1) + 2) & 3) << 1)) << 4);   // rows r0 + 4 + 8i'
-    const bool rows_128 = A.k_ss == 128 && A.v_ss == 128;
-    auto stage_chunk = [&](int c0, int slot) {
-        if (c0 < key_end) {
-            const uint32_t dst = ring_s + slot * 8192;
-            if (c0 + 32 <= key_end && rows_128) {     // a whole chunk of densely stored rows: constant address steps
-                const uint8_t* kp = kb0 + (int64_t)(c0 + r0) * 128;
-                const uint8_t* vp = vb0 + (int64_t)(c0 + r0) * 128;
-#pragma unroll
-                for (int i = 0; i < 8; i++) {
-                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(dst + k_off + i * 512), "l"(kp + i * 512) : "memory");
-                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(dst + ((i & 1) ? v_off1 : v_off0) + (i >> 1) * 1024), "l"(vp + i * 512) : "memory");
-                }
-            } else {
-#pragma unroll
-                for (int i = 0; i < 8; i++) {
-                    const int64_t key = min(c0 + 4 * i + r0, key_end - 1);
-                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(dst + k_off + i * 512), "l"(kb0 + key * A.k_ss) : "memory");
-                    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(dst + ((i & 1) ? v_off1 : v_off0) + (i >> 1) * 1024), "l"(vb0 + key * A.v_ss) : "memory");
-                }
-            }
-        }
-        asm volatile("cp.async.commit_group;" ::: "memory");
-    };
-    if (NST > 0) {
+    if (NST > 0 && !(FUSED && A.early)) {
 #pragma unroll
         for (int s = 0; s < NST - 1; s++) stage_chunk(key_begin + (warp + SDP_WARPS * s) * 32, s);
     }

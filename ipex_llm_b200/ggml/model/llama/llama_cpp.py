@@ -520,7 +520,7 @@ _lib.lowbit_decode_attention_workspace_size.restype = ctypes.c_size_t
 _lib.lowbit_decode_attention_cuda.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int64] + [ctypes.c_int] * 4 + \
                                              [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_int, _I32P,
                                               ctypes.c_void_p, _I64P, ctypes.c_void_p, _I64P, ctypes.c_int, ctypes.c_float,
-                                              ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p]
+                                              ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p]
 _lib.lowbit_decode_attention_cuda.restype = ctypes.c_int
 
 
@@ -528,7 +528,8 @@ def lowbit_decode_attention_workspace_size(b, hq, hkv, capacity, d):
     return _lib.lowbit_decode_attention_workspace_size(b, hq, hkv, capacity, d)
 
 
-def lowbit_decode_attention(qkv, n_heads, n_kv_heads, head_dim, cos, sin, cache_len, k_cache, v_cache, scale, out, workspace, stream):
+def lowbit_decode_attention(qkv, n_heads, n_kv_heads, head_dim, cos, sin, cache_len, k_cache, v_cache, scale, out, workspace, stream,
+                            cache_complete=False):
     """qkv [B, (Hq + 2 Hkv) * D] (or [B, 1, ...]); cos / sin [positions, >= D/2]; cache_len: int32 device scalar = tokens
     already cached; k_cache / v_cache uint8 [B, Hkv, capacity, D]; out [B, Hq, 1, D] contiguous"""
     B = qkv.shape[0]
@@ -536,5 +537,5 @@ def lowbit_decode_attention(qkv, n_heads, n_kv_heads, head_dim, cos, sin, cache_
                                              cos.data_ptr(), sin.data_ptr(), _DT_OF[str(cos.dtype)], cos.stride(0), cos.shape[0],
                                              cache_len.data_ptr(), k_cache.data_ptr(), _strides3(k_cache), v_cache.data_ptr(),
                                              _strides3(v_cache), k_cache.shape[2], float(scale), out.data_ptr(),
-                                             _DT_OF[str(out.dtype)], workspace.data_ptr(),
+                                             _DT_OF[str(out.dtype)], int(bool(cache_complete)), workspace.data_ptr(),
                                              workspace.numel() * workspace.element_size(), stream), "lowbit_decode_attention_cuda")

@@ -140,8 +140,11 @@ class DecodeGraph:
             attn, mlp = layer.self_attn, layer.mlp
             self._rms(layer.input_layernorm, self.h, self.xn)
             self._linear(attn.qkv_proj, self.xn, qkv2d)
+            # cache_complete: the rows below the cache length and the length itself come from earlier steps, and every
+            # step starts with an ordinarily launched kernel (the embedding lookup above) that nothing overtakes
             ggml.lowbit_decode_attention(self.qkv, self.Hq, self.Hkv, self.D, self.cos, self.sin, self.state,
-                                         self.k_cache[i], self.v_cache[i], attn.scaling, self.attn, self.sdp_ws, st)
+                                         self.k_cache[i], self.v_cache[i], attn.scaling, self.attn, self.sdp_ws, st,
+                                         cache_complete=True)
             self.launches_per_step += ggml.last_launch_count()
             self._linear(attn.o_proj, attn2d, self.h, accumulate=True)
             self._rms(layer.post_attention_layernorm, self.h, self.xn)

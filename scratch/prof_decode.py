@@ -12,6 +12,7 @@ from ipex_llm_b200.transformers import decode_graph as dg
 ap = argparse.ArgumentParser()
 ap.add_argument("--layers", type=int, default=32)
 ap.add_argument("--ncu", action="store_true")
+ap.add_argument("--only-full", action="store_true", dest="only_full")
 ap.add_argument("--prompt", type=int, default=512)
 args = ap.parse_args()
 dev = torch.device("cuda", 0)
@@ -39,18 +40,16 @@ if args.ncu:
     sys.exit(0)
 
 run("full step")
+if args.only_full:
+    sys.exit(0)
 noop = lambda *a, **k: None
-saved = {n: getattr(ggml, n) for n in ("lowbit_rms_norm", "lowbit_rope_kv_append", "lowbit_sdp_fp8_devlen", "lowbit_greedy_advance")}
-for name in saved:
-    setattr(ggml, name, noop if name != "lowbit_greedy_advance" else saved[name])
-    if name == "lowbit_greedy_advance":
-        continue
-    run("without " + name)
-    setattr(ggml, name, saved[name])
-for name in ("lowbit_rms_norm", "lowbit_rope_kv_append", "lowbit_sdp_fp8_devlen"):
-    setattr(ggml, name, noop)
-run("linears + embed + greedy only")
-for name in saved:
-    setattr(ggml, name, saved[name])
+names = ("lowbit_rms_norm", "lowbit_decode_attention")
+saved = {n: getattr(ggml, n) for n in names}
+for group in (("lowbit_rms_norm",), ("lowbit_decode_attention",), names):
+    for n in group:
+        setattr(ggml, n, noop)
+    run("without " + " + ".join(g.replace("lowbit_", "") for g in group))
+    for n in group:
+        setattr(ggml, n, saved[n])
 os.environ["IPEX_LLM_B200_DECODE_PDL"] = "0"
 run("full step, no PDL")

@@ -166,7 +166,7 @@ def test_decode_attention_one_launch_equals_the_separate_kernels(native_lib, cud
         # one call
         qb, kb, vb = qkv.clone(), k0.clone(), v0.clone()
         got = torch.full((B, Hq, 1, D), float("nan"), dtype=dtype, device=dev)
-        ggml.lowbit_decode_attention(qb, Hq, Hkv, D, cos, sin, state, kb, vb, scale, got, ws, _st(dev))
+        ggml.lowbit_decode_attention(qb, Hq, Hkv, D, cos, sin, state, kb, vb, scale, got, ws, _st(dev), cache_complete=bool(P % 2))
         launches.add(ggml.last_launch_count())
         assert torch.equal(kb, ka) and torch.equal(vb, va), P                     # the new row, and nothing else, was written
         L = P + 1
