@@ -55,6 +55,50 @@ __global__ void kv_dequantize_kernel(const uint8_t* __restrict__ src, View4 vs, 
     }
 }
 
+// 8 consecutive elements of a row per thread (head_dim % 8 == 0, rows 16- / 8-byte aligned): one 16-byte load (two
+// for fp32) and one 8-byte store -- the prefill writes and restores 4 M elements per layer through these kernels
+template <typename T>
+__global__ void __launch_bounds__(256) kv_quantize_vec_kernel(const T* __restrict__ src, View4 vs, uint8_t* __restrict__ dst, View4 vd,
+                                                              int64_t B, int64_t H, int64_t S, int64_t D) {
+    const int64_t D8 = D / 8, total = B * H * S * D8;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t d = (i % D8) * 8, s = (i / D8) % S, h = (i / (D8 * S)) % H, b = i / (D8 * S * H);
+        const T* p = src + b * vs.sb + h * vs.sh + s * vs.ss + d;
+        T v[8];
+        if (sizeof(T) == 4) { *reinterpret_cast<uint4*>(&v[0]) = *reinterpret_cast<const uint4*>(p); *reinterpret_cast<uint4*>(&v[4]) = *reinterpret_cast<const uint4*>(p + 4); }
+        else *reinterpret_cast<uint4*>(&v[0]) = *reinterpret_cast<const uint4*>(p);
+        uint32_t w0 = 0, w1 = 0;
+#pragma unroll
+        for (int e = 0; e < 4; e++) {
+            w0 |= (uint32_t)to_e5m2(to_float<T>(v[e])) << (8 * e);
+            w1 |= (uint32_t)to_e5m2(to_float<T>(v[4 + e])) << (8 * e);
+        }
+        *reinterpret_cast<uint2*>(dst + b * vd.sb + h * vd.sh + s * vd.ss + d) = make_uint2(w0, w1);
+    }
+}
+template <typename T>
+__global__ void __launch_bounds__(256) kv_dequantize_vec_kernel(const uint8_t* __restrict__ src, View4 vs, T* __restrict__ dst, View4 vd,
+                                                                int64_t B, int64_t H, int64_t S, int64_t D) {
+    const int64_t D8 = D / 8, total = B * H * S * D8;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t d = (i % D8) * 8, s = (i / D8) % S, h = (i / (D8 * S)) % H, b = i / (D8 * S * H);
+        const uint2 w = *reinterpret_cast<const uint2*>(src + b * vs.sb + h * vs.sh + s * vs.ss + d);
+        T v[8];
+#pragma unroll
+        for (int e = 0; e < 4; e++) {
+            v[e] = from_float<T>(from_e5m2((uint8_t)(w.x >> (8 * e))));
+            v[4 + e] = from_float<T>(from_e5m2((uint8_t)(w.y >> (8 * e))));
+        }
+        T* q = dst + b * vd.sb + h * vd.sh + s * vd.ss + d;
+        if (sizeof(T) == 4) { *reinterpret_cast<uint4*>(q) = *reinterpret_cast<const uint4*>(&v[0]); *reinterpret_cast<uint4*>(q + 4) = *reinterpret_cast<const uint4*>(&v[4]); }
+        else *reinterpret_cast<uint4*>(q) = *reinterpret_cast<const uint4*>(&v[0]);
+    }
+}
+// both views allow the 8-element path: D % 8 == 0, every stride a multiple of 8 elements, 16-byte aligned bases
+static bool kv_vec_ok(const void* fp, int fp_esz, const View4& vf, const void* u8, const View4& vu, int64_t D) {
+    return D % 8 == 0 && !((vf.sb | vf.sh | vf.ss | vu.sb | vu.sh | vu.ss) & 7) && !((uintptr_t)fp & 15) && !((uintptr_t)u8 & 7) && fp_esz > 0;
+}
+
 int grid_for(int64_t total) {
     int64_t b = (total + 255) / 256;
     const int64_t cap = (int64_t)sm_count() * 16;
@@ -409,6 +453,14 @@ extern "C" int lowbit_kv_quantize_cuda(const void* d_src, int src_dtype, const i
     if (total == 0) return LB_OK;
     cudaStream_t st = (cudaStream_t)stream;
     const View4 vs = view_of(src_strides), vd = view_of(dst_strides);
+    if (kv_vec_ok(d_src, src_dtype == DT_F32 ? 4 : 2, vs, d_dst, vd, D)) {
+        const int grid = grid_for(total / 8);
+        if (src_dtype == DT_F32) kv_quantize_vec_kernel<float><<<grid, 256, 0, st>>>((const float*)d_src, vs, (uint8_t*)d_dst, vd, B, H, S, D);
+        else if (src_dtype == DT_F16) kv_quantize_vec_kernel<__half><<<grid, 256, 0, st>>>((const __half*)d_src, vs, (uint8_t*)d_dst, vd, B, H, S, D);
+        else kv_quantize_vec_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>((const __nv_bfloat16*)d_src, vs, (uint8_t*)d_dst, vd, B, H, S, D);
+        note_launch();
+        return check_launch();
+    }
     const int grid = grid_for(total);
     if (src_dtype == DT_F32) kv_quantize_kernel<float><<<grid, 256, 0, st>>>((const float*)d_src, vs, (uint8_t*)d_dst, vd, B, H, S, D);
     else if (src_dtype == DT_F16) kv_quantize_kernel<__half><<<grid, 256, 0, st>>>((const __half*)d_src, vs, (uint8_t*)d_dst, vd, B, H, S, D);
@@ -428,6 +480,14 @@ extern "C" int lowbit_kv_dequantize_cuda(const void* d_src, const int64_t* src_s
     if (total == 0) return LB_OK;
     cudaStream_t st = (cudaStream_t)stream;
     const View4 vs = view_of(src_strides), vd = view_of(dst_strides);
+    if (kv_vec_ok(d_dst, dst_dtype == DT_F32 ? 4 : 2, vd, d_src, vs, D)) {
+        const int grid = grid_for(total / 8);
+        if (dst_dtype == DT_F32) kv_dequantize_vec_kernel<float><<<grid, 256, 0, st>>>((const uint8_t*)d_src, vs, (float*)d_dst, vd, B, H, S, D);
+        else if (dst_dtype == DT_F16) kv_dequantize_vec_kernel<__half><<<grid, 256, 0, st>>>((const uint8_t*)d_src, vs, (__half*)d_dst, vd, B, H, S, D);
+        else kv_dequantize_vec_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>((const uint8_t*)d_src, vs, (__nv_bfloat16*)d_dst, vd, B, H, S, D);
+        note_launch();
+        return check_launch();
+    }
     const int grid = grid_for(total);
     if (dst_dtype == DT_F32) kv_dequantize_kernel<float><<<grid, 256, 0, st>>>((const uint8_t*)d_src, vs, (float*)d_dst, vd, B, H, S, D);
     else if (dst_dtype == DT_F16) kv_dequantize_kernel<__half><<<grid, 256, 0, st>>>((const uint8_t*)d_src, vs, (__half*)d_dst, vd, B, H, S, D);

