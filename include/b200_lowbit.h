@@ -179,6 +179,18 @@ int lowbit_sdp_fp8_cuda(const void* d_q, int q_dtype, const int64_t* q_strides, 
                         int S, int L, int D, void* d_out, int out_dtype, void* workspace, size_t workspace_bytes,
                         void* stream);
 
+/* Attention of MANY new tokens over the FP8 cache -- xe_addons.sdp_fp8_causal / sdp_fp8_non_causal(query, key, value, mask,
+ * scale) (models/common.py:264-286: the prefill, and any call with more than 32 query tokens).  Arguments as
+ * lowbit_sdp_fp8_cuda (causal != 0: query token s sees keys <= L - S + s; additive mask optional), any S >= 1, no
+ * workspace.  fp16 / bf16 queries with head_dim 128 (lowbit_sdp_fp8_prefill_supported); 16-byte aligned caches, query rows
+ * and output.  One CTA per 64 query rows of a query head; the 32-key chunks are staged once per CTA through a cp.async ring
+ * and both products run on the tensor cores from the e5m2 bytes (csrc/sdp_prefill.cuh).  Same tolerance as the decode kernel. */
+int lowbit_sdp_fp8_prefill_supported(int Hq, int Hkv, int D, int q_dtype);
+int lowbit_sdp_fp8_prefill_cuda(const void* d_q, int q_dtype, const int64_t* q_strides, const void* d_k,
+                                const int64_t* k_strides, const void* d_v, const int64_t* v_strides, const void* d_mask,
+                                int mask_dtype, const int64_t* mask_strides, int causal, float scale, int B, int Hq, int Hkv,
+                                int S, int L, int D, void* d_out, int out_dtype, void* stream);
+
 /* lowbit_sdp_fp8_cuda for a decode step that is replayed from a CUDA graph: the key count is read on the device,
  * L = min(*d_len + len_add, L_max), so one recorded launch serves every step.  L_max (the cache capacity the step
  * was recorded for) fixes the grid and the workspace size (lowbit_sdp_fp8_workspace_size with L = L_max); no mask;

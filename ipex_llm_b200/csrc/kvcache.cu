@@ -390,6 +390,7 @@ __global__ void __launch_bounds__(SDP_COMBINE_WARPS * 32) sdp_fp8_combine_kernel
 }
 
 #include "sdp_mma.cuh"
+#include "sdp_prefill.cuh"
 
 // rows per CTA: the whole GQA group x new tokens if it is 1, 2 or 4 rows (8 on the tensor-core path), else tiles
 int sdp_rt(int Hq, int Hkv, int S, bool mma) {
@@ -616,6 +617,43 @@ extern "C" int lowbit_sdp_fp8_devlen_cuda(const void* d_q, int q_dtype, const in
     if (!d_len) { set_error(LB_ERR_ARG, "lowbit_sdp_fp8_devlen_cuda: d_len is NULL"); return LB_ERR_ARG; }
     return sdp_launch(d_q, q_dtype, q_strides, d_k, k_strides, d_v, v_strides, nullptr, 0, nullptr, causal, scale,
                       B, Hq, Hkv, S, L_max, D, d_out, out_dtype, workspace, workspace_bytes, stream, d_len, len_add);
+}
+
+// ------------------------------------------------------------------ prefill attention over the e5m2 cache
+extern "C" int lowbit_sdp_fp8_prefill_supported(int Hq, int Hkv, int D, int q_dtype) {
+    return Hq > 0 && Hkv > 0 && Hq % Hkv == 0 && D == 128 && (q_dtype == DT_F16 || q_dtype == DT_BF16);
+}
+
+extern "C" int lowbit_sdp_fp8_prefill_cuda(const void* d_q, int q_dtype, const int64_t* q_strides, const void* d_k,
+                                           const int64_t* k_strides, const void* d_v, const int64_t* v_strides, const void* d_mask,
+                                           int mask_dtype, const int64_t* mask_strides, int causal, float scale, int B, int Hq,
+                                           int Hkv, int S, int L, int D, void* d_out, int out_dtype, void* stream) {
+    reset_launch_count();
+    if (!d_q || !d_k || !d_v || !d_out || !q_strides || !k_strides || !v_strides || (d_mask && !mask_strides) || out_dtype < 0 ||
+        out_dtype > 2 || (d_mask && (mask_dtype < 0 || mask_dtype > 2)) || B <= 0 || S <= 0 || L < S || !(scale > 0.0f) ||
+        !lowbit_sdp_fp8_prefill_supported(Hq, Hkv, D, q_dtype)) {
+        set_error(LB_ERR_ARG, "lowbit_sdp_fp8_prefill_cuda: bad argument (B %d, Hq %d, Hkv %d, S %d, L %d, D %d, q_dtype %d)", B, Hq, Hkv, S, L, D, q_dtype);
+        return LB_ERR_ARG;
+    }
+    if ((((uintptr_t)d_k | (uintptr_t)d_v | (uintptr_t)d_q | (uintptr_t)d_out) & 15) ||
+        ((k_strides[0] | k_strides[1] | k_strides[2] | v_strides[0] | v_strides[1] | v_strides[2]) & 15) ||
+        ((q_strides[0] | q_strides[1] | q_strides[2]) & 7)) {
+        set_error(LB_ERR_ARG, "lowbit_sdp_fp8_prefill_cuda: caches, query rows and output must be 16-byte aligned (pointers and strides)");
+        return LB_ERR_ARG;
+    }
+    SdpArgs A = {};
+    A.q = d_q; A.q_dtype = q_dtype; A.q_sb = q_strides[0]; A.q_sh = q_strides[1]; A.q_ss = q_strides[2];
+    A.k = (const uint8_t*)d_k; A.k_sb = k_strides[0]; A.k_sh = k_strides[1]; A.k_ss = k_strides[2];
+    A.v = (const uint8_t*)d_v; A.v_sb = v_strides[0]; A.v_sh = v_strides[1]; A.v_ss = v_strides[2];
+    A.mask = d_mask; A.mask_dtype = mask_dtype;
+    A.m_sb = d_mask ? mask_strides[0] : 0; A.m_sh = d_mask ? mask_strides[1] : 0; A.m_ss = d_mask ? mask_strides[2] : 0;
+    A.causal = causal; A.scale_log2e = scale * 1.4426950408889634f;
+    A.B = B; A.Hq = Hq; A.Hkv = Hkv; A.S = S; A.L = L; A.D = D;
+    A.out = d_out; A.out_dtype = out_dtype;
+    const dim3 grid((unsigned)((S + PF_ROWS - 1) / PF_ROWS), (unsigned)(B * Hq), 1);
+    sdp_fp8_prefill_kernel<<<grid, PF_WARPS * 32, 0, (cudaStream_t)stream>>>(A);
+    note_launch();
+    return check_launch();
 }
 
 // ------------------------------------------------------------------ the attention of one decode step, one call

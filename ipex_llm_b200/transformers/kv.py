@@ -236,6 +236,40 @@ def sdp_fp8(query, key, value, mask, scale, is_causal=False):
     return out
 
 
+def sdp_fp8_prefill(query, key, value, mask, scale, is_causal):
+    """xe_addons.sdp_fp8_causal / sdp_fp8_non_causal: attention of many new tokens straight from the uint8 cache"""
+    B, Hq, S, D = query.shape
+    if query.stride(-1) != 1:
+        query = query.contiguous()
+    if mask is not None:
+        if mask.stride(-1) != 1:
+            mask = mask.contiguous()
+        mask = mask.expand(B, Hq, S, key.shape[2])
+    out = torch.empty((B, Hq, S, D), dtype=query.dtype, device=query.device)
+    with torch.cuda.device(query.device):
+        ggml.lowbit_sdp_fp8_prefill(query, key, value, mask, is_causal, scale, out, _stream(query.device))
+    return out
+
+
+def sdp_fp8_causal(query, key, value, mask, scale):
+    """models/common.py:273"""
+    return sdp_fp8_prefill(query, key, value, mask, scale, mask is None)
+
+
+def sdp_fp8_non_causal(query, key, value, mask, scale):
+    """models/common.py:284"""
+    return sdp_fp8_prefill(query, key, value, mask, scale, False)
+
+
+def _prefill_kernel_ok(query, key, value, mask):
+    def aligned(t, unit):
+        return t.data_ptr() % 16 == 0 and all(s % unit == 0 for s in t.stride()[:3])
+    return (ggml.lowbit_sdp_fp8_prefill_supported(query.shape[1], key.shape[1], query.shape[3], query.dtype)
+            and os.environ.get("IPEX_LLM_B200_SDP_PREFILL", "1") != "0"
+            and aligned(key, 16) and aligned(value, 16) and key.stride(-1) == 1 and value.stride(-1) == 1
+            and (query.stride(-1) != 1 or aligned(query, 8)) and key.shape[2] >= query.shape[2])
+
+
 def _additive_mask(mask, dtype):
     """transformers >= 5 hands attention a boolean mask (True = attend); the kernels take an additive one"""
     if mask is not None and mask.dtype == torch.bool:
@@ -246,8 +280,9 @@ def _additive_mask(mask, dtype):
 def scaled_dot_product_attention(query: torch.Tensor, key: torch.Tensor, value: torch.Tensor, mask: torch.Tensor = None,
                                  is_causal: bool = False, scale: float = None) -> torch.Tensor:
     """models/common.py:250-306.  uint8 key/value = the FP8 cache: new tokens <= 32 (decode) go to the fused kernel
-    (sdp_fp8); longer queries (prefill) restore the cache to the query dtype and use torch's attention, as does a
-    floating-point cache."""
+    (sdp_fp8); longer queries (prefill) to the many-token kernel (sdp_fp8_causal / sdp_fp8_non_causal; fp16 / bf16, head_dim
+    128); what neither serves restores the cache to the query dtype and uses torch's attention, as does a floating-point
+    cache."""
     bsz, n_heads, seq_length, head_dim = query.shape
     _, n_kv_heads, kv_length, _ = key.shape
     scale = 1 / math.sqrt(head_dim) if scale is None else scale
@@ -255,7 +290,12 @@ def scaled_dot_product_attention(query: torch.Tensor, key: torch.Tensor, value: 
         if seq_length <= 32 and ggml.lowbit_sdp_fp8_supported(n_heads, n_kv_heads, seq_length, head_dim):
             mask = _additive_mask(mask, query.dtype if query.dtype != torch.bfloat16 else torch.float32)
             return sdp_fp8(query, key, value, mask, scale, is_causal and mask is None)
-        key, value = restore_fp8_kv_cache(key, value, query.dtype)
+        if _prefill_kernel_ok(query, key, value, mask):
+            mask = _additive_mask(mask, query.dtype)
+            if mask is not None:
+                mask = mask[..., :seq_length, :kv_length]
+            return sdp_fp8_prefill(query, key, value, mask, scale, is_causal and mask is None)
+        key, value = restore_fp8_kv_cache(key, value, query.dtype)      # other head sizes / fp32 queries: torch on the restored cache
     if n_heads != n_kv_heads:
         key = key.repeat_interleave(n_heads // n_kv_heads, dim=1)
         value = value.repeat_interleave(n_heads // n_kv_heads, dim=1)

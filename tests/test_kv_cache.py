@@ -188,3 +188,45 @@ def test_sdp_fp8_strided_and_misaligned_caches(kv, cuda_device):
     # a query that is a strided view (heads and tokens transposed, as decoders produce it)
     q_t = q.transpose(1, 2).contiguous().transpose(1, 2)
     assert torch.equal(kv.sdp_fp8(q_t, k_u8, v_u8, None, scale, True), dense)
+
+
+@pytest.mark.parametrize("B,Hq,Hkv,S,L,dtype,causal", [
+    (1, 32, 32, 512, 512, torch.float16, True),        # Llama-2-7B prefill, 512-token prompt
+    (2, 8, 2, 100, 300, torch.bfloat16, True),         # GQA, a chunked prefill behind 200 cached tokens, ragged tiles
+    (1, 4, 4, 70, 70, torch.float16, False),           # non-causal
+    (1, 4, 1, 33, 33, torch.float16, True),            # the smallest query count that leaves the decode kernel
+    (1, 2, 2, 257, 1100, torch.float16, True),
+])
+def test_sdp_fp8_many_tokens_matches_float64(kv, cuda_device, B, Hq, Hkv, S, L, dtype, causal):
+    """sdp_fp8_causal / sdp_fp8_non_causal (csrc/sdp_prefill.cuh): more than 32 new tokens over the e5m2 cache"""
+    gen = torch.Generator(device=cuda_device).manual_seed(21)
+    D = 128
+    q = torch.randn(B, Hq, S, D, device=cuda_device, generator=gen).to(dtype)
+    cache = kv.DynamicFp8Cache()
+    k_u8, v_u8 = cache.update(torch.randn(B, Hkv, L, D, device=cuda_device, generator=gen).to(dtype),
+                              torch.randn(B, Hkv, L, D, device=cuda_device, generator=gen).to(dtype), 0)
+    scale = 1 / math.sqrt(D)
+    out = kv.scaled_dot_product_attention(q, k_u8, v_u8, None, causal, scale)
+    direct = kv.sdp_fp8_causal(q, k_u8, v_u8, None, scale) if causal else kv.sdp_fp8_non_causal(q, k_u8, v_u8, None, scale)
+    assert torch.equal(out, direct)                                   # the dispatcher took the many-token kernel
+    want = ref_attention(q, k_u8, v_u8, None, scale, causal)
+    tol = (1e-3 if dtype == torch.float16 else 8e-3) * float(want.abs().max())
+    assert float((out.double() - want).abs().max()) <= tol
+    # an additive mask (left padding of sequence 0 + a finite bias), with and without the causal rule on top of it
+    mask = torch.zeros(B, 1, S, L, device=cuda_device, dtype=dtype)
+    mask[0, :, :, :7] = float("-inf")
+    mask[-1, :, :, 9:20] = -2.5
+    if causal:
+        i = torch.arange(S, device=cuda_device)[:, None]
+        j = torch.arange(L, device=cuda_device)[None, :]
+        mask = mask.masked_fill(j > (L - S + i), float("-inf"))
+    out = kv.scaled_dot_product_attention(q, k_u8, v_u8, mask, causal, scale)
+    want = torch.nan_to_num(ref_attention(q, k_u8, v_u8, mask, scale, False), nan=0.0)     # a row with every key masked gives zeros
+    assert float((out.double() - want).abs().max()) <= tol
+    # a boolean mask (what transformers >= 5 passes) and a strided query view (the rotated slice of the qkv projection)
+    qkv = torch.randn(B, S, (Hq + 2 * Hkv) * D, device=cuda_device, generator=gen).to(dtype)
+    q_view = qkv.view(B, S, Hq + 2 * Hkv, D).transpose(1, 2)[:, :Hq]
+    bmask = torch.isfinite(mask)
+    out = kv.scaled_dot_product_attention(q_view, k_u8, v_u8, bmask, False, scale)
+    want = torch.nan_to_num(ref_attention(q_view, k_u8, v_u8, torch.zeros_like(mask).masked_fill(~bmask, float("-inf")), scale, False), nan=0.0)
+    assert float((out.double() - want).abs().max()) <= tol
