@@ -298,6 +298,10 @@ def _plan(model, inputs, generation_config, kwargs):
     partial = getattr(cfg, "partial_rotary_factor", None)
     if partial not in (None, 1, 1.0):
         return None
+    # the step indexes cos / sin tables computed once per arena: rotary variants whose frequencies depend on the
+    # sequence length seen so far ("dynamic", "longrope") keep to the eager forwards
+    if getattr(getattr(core, "rotary_emb", None), "rope_type", "default") not in ("default", "linear", "llama3", "yarn"):
+        return None
     pad = gc.pad_token_id if gc.pad_token_id is not None else (eos[0] if eos else 0)
     return input_ids, max_new, min_new, eos, pad
 
