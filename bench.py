@@ -498,6 +498,14 @@ def run_ours(args):
             barrier()
             ms_e2e = 1e3 * sum(t[0] for t in e2e_trials) / len(e2e_trials)
             e2e_total_ms = 1e3 * sum(t[1] for t in e2e_trials) / len(e2e_trials)
+            # batch 4 and 16 decode (BASELINE.json configs[1]'s batch sizes), same prompt length, 32 decode steps
+            batch_rates = {}
+            for bsz in (4, 16):
+                pb = torch.randint(0, VOCAB, (bsz, PROMPT_LEN), device=dev)
+                model.generate(pb, max_new_tokens=9, min_new_tokens=9, **gen_kwargs)
+                model.generate(pb, max_new_tokens=33, min_new_tokens=33, **gen_kwargs)
+                batch_rates[f"batch{bsz}_tok_per_s"] = bsz / model.rest_cost_mean_device
+                batch_rates[f"batch{bsz}_ms_per_step"] = model.rest_cost_mean_device * 1e3
             # the LowBitLinear launches alone (roofline of the GEMV kernel in its PDL chain)
             ms_stream, stream_launches = linear_stream(model, dev, max(K, 20), W)
             barrier()
@@ -558,7 +566,7 @@ def run_ours(args):
                      "launch_ms_avg": ms_stream / n_launches()},
         "parsed": {
             "generate": {"first_token_ms": first_ms, "rest_token_ms_device": ms_dev, "rest_token_ms_wall": ms_wall,
-                         "kernels_per_token": launches_per_token,
+                         "kernels_per_token": launches_per_token, **batch_rates,
                          "weights_GBps_in_generate": algorithmic_bytes() / (ms_dev * 1e-3) / 1e9,
                          "frac_of_hbm_peak_in_generate": algorithmic_bytes() / (ms_dev * 1e-3) / 1e9 / peak},
             "linear_stream": {"ms_per_token": ms_stream, "tok_per_s": 1e3 / ms_stream, "launches_per_token": stream_launches,

@@ -29,7 +29,7 @@ from ipex_llm_b200.transformers import kv as kvmod
 from ipex_llm_b200.transformers.low_bit_linear import LowBitLinear, lowbit_matmul, mlp_forward
 from ipex_llm_b200.transformers.models.utils import SILU, mlp_fusion_check, use_quantize_kv_cache
 
-MAX_BATCH = 8                 # the GEMV's fused-MLP path and the decode attention are sized for a handful of sequences
+MAX_BATCH = 32                # rows the decode GEMV takes in one pass (the fused gate/up kernel serves <= 8 of them)
 CAPACITY_STEP = 256           # cache capacities are rounded up to this many positions (one graph per capacity)
 MAX_GRAPHS = 4                # recorded steps kept per model (each owns its KV arena)
 
@@ -154,7 +154,8 @@ class DecodeGraph:
             gate, up = mlp.gate_proj, mlp.up_proj
             if self.fuse_mlp and isinstance(gate, LowBitLinear) and isinstance(up, LowBitLinear) and gate.bias is None \
                     and up.bias is None and gate.mp_group is None and gate.qtype == up.qtype \
-                    and mlp_fusion_check(self.xn, gate.qtype, False):
+                    and gate.weight.data.device.type == "cuda":
+                # one launch for <= 8 sequences; lowbit_mlp_cuda runs two matmuls and one activation kernel beyond
                 mlp_forward(self.xn, gate.weight.data, up.weight.data, B, self.H, gate.out_len, SILU, gate.qtype, out=self.act)
                 self.launches_per_step += ggml.last_launch_count()
             else:

@@ -212,6 +212,12 @@ def test_recorded_decode_step_matches_the_eager_forwards(native_lib, cuda_device
         slow2 = model._hf_generate(ids2, max_new_tokens=8, do_sample=False)
     assert torch.equal(again, fast)
     assert_same_tokens_up_to_a_tie(model, fast2, slow2, dtype)
+    if family == "llama" and qtype == "sym_int4":                   # a batch beyond the fused gate/up kernel's 8 rows
+        ids12 = torch.randint(0, 320, (12, 20), generator=torch.Generator().manual_seed(11)).to(cuda_device)
+        with torch.no_grad():
+            fast12 = model.generate(ids12, max_new_tokens=6, do_sample=False)
+            slow12 = model._hf_generate(ids12, max_new_tokens=6, do_sample=False)
+        assert_same_tokens_up_to_a_tie(model, fast12, slow12, dtype)
     assert_same_tokens_up_to_a_tie(model, fast2[:1], fast[:, :48], dtype)
     assert model.rest_cost_mean > 0 and model.first_cost > 0
 
@@ -238,3 +244,61 @@ def test_generate_stops_at_eos_and_falls_back(native_lib, cuda_device):
     with torch.no_grad():
         t32 = model32.generate(ids, max_new_tokens=8, do_sample=False)
     assert t32.shape == (1, 28)
+
+
+def test_from_pretrained_load_in_4bit_and_low_bit(native_lib, cuda_device, tmp_path):
+    """the reference's headline call: AutoModelForCausalLM.from_pretrained(path, load_in_4bit=True) (model.py:111-388;
+    load_in_4bit == load_in_low_bit="sym_int4", model.py:327), from a checkpoint directory written by transformers"""
+    from ipex_llm.transformers import AutoModelForCausalLM
+    from ipex_llm.transformers.low_bit_linear import LowBitLinear
+    from ipex_llm.ggml.quantize import ggml_tensor_qtype
+    d = str(tmp_path / "hf")
+    tiny_llama().save_pretrained(d)
+    model = AutoModelForCausalLM.from_pretrained(d, load_in_4bit=True)
+    assert model.config.to_dict()["bigdl_transformers_low_bit"] == "sym_int4"
+    qkv = model.model.layers[0].self_attn.qkv_proj
+    assert isinstance(qkv, LowBitLinear) and qkv.qtype == ggml_tensor_qtype["sym_int4"] and qkv.weight.data.device.type == "cpu"
+    a0 = tiny_llama().model.layers[0].self_attn
+    w0 = torch.cat([a0.q_proj.weight.data, a0.k_proj.weight.data, a0.v_proj.weight.data]).numpy()
+    np.testing.assert_array_equal(qkv.weight.data.numpy(), oracle.quantize(w0, "sym_int4"))
+    ids = torch.randint(0, 320, (1, 12), generator=torch.Generator().manual_seed(6))
+    ref = oracle_dequantised_copy(tiny_llama(), "sym_int4")
+    model = model.to(cuda_device)
+    with torch.no_grad():
+        got = model.generate(ids.to(cuda_device), max_new_tokens=10, do_sample=False, pad_token_id=0).cpu()
+        want = ref.generate(ids, max_new_tokens=10, do_sample=False, pad_token_id=0)
+    assert torch.equal(got, want)
+    # another format, the stock forwards, a module left alone
+    m2 = AutoModelForCausalLM.from_pretrained(d, load_in_low_bit="fp8_e4m3", optimize_model=False, modules_to_not_convert=["lm_head"])
+    assert m2.model.layers[1].mlp.up_proj.qtype == ggml_tensor_qtype["fp8_e4m3"] and not isinstance(m2.lm_head, LowBitLinear)
+    assert hasattr(m2.model.layers[0].self_attn, "q_proj")
+    with pytest.raises(RuntimeError):
+        AutoModelForCausalLM.from_pretrained(d, load_in_low_bit="q4_k")           # a format outside this build: loud, not silent
+
+
+def test_mistral_sliding_window_mask_is_honoured(native_lib, cuda_device):
+    """Mistral-7B-v0.1 style config (sliding_window set): transformers hands the attention a sliding-window mask; the
+    optimised forwards keep every position in the cache (like the reference) and apply the mask"""
+    from ipex_llm.transformers import AutoModelForCausalLM
+    cfg = transformers.MistralConfig(hidden_size=256, intermediate_size=512, num_hidden_layers=2, num_attention_heads=2,
+                                     num_key_value_heads=2, vocab_size=320, max_position_embeddings=256, sliding_window=16,
+                                     head_dim=128, tie_word_embeddings=False)
+    torch.manual_seed(3)
+    base = transformers.MistralForCausalLM(cfg).eval()
+    ref = transformers.MistralForCausalLM(cfg).eval()
+    ref.load_state_dict(base.state_dict())
+    for mod in ref.modules():
+        if isinstance(mod, torch.nn.Linear) and mod.in_features % 64 == 0:
+            w = mod.weight.data.float().numpy()
+            mod.weight.data = torch.from_numpy(oracle.dequantize(oracle.quantize(w, "sym_int4"), w.shape, "sym_int4"))
+    model = AutoModelForCausalLM.from_model(base, low_bit="sym_int4").to(cuda_device)
+    ids = torch.randint(0, 320, (1, 40), generator=torch.Generator().manual_seed(8))     # longer than the window
+    with torch.no_grad():
+        want = ref(ids).logits[:, -1:, :]
+        got = model(ids.to(cuda_device)).logits.float().cpu()
+    assert float((got - want).abs().mean() / want.abs().mean()) < 2e-3
+    # half precision, FP8 cache, prompt + new tokens beyond the window: transformers' loop on the patched forwards
+    model = model.half()
+    with torch.no_grad():
+        out = model.generate(ids.to(cuda_device), max_new_tokens=6, do_sample=False, pad_token_id=0)
+    assert out.shape == (1, 46)
