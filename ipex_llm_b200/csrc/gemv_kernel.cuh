@@ -140,9 +140,10 @@ __device__ __forceinline__ uint32_t h2_to_bf2(uint32_t h) {
 // kLo / kHi  : fp32 factors that undo the scaling of fragment rows g (regs a0,a2) / g+8 (a1,a3)
 // Tile       : the registers one lane holds for one tile
 // load       : read the lane's part of tile `r` of a staged super-tile from shared memory
-// frag       : A fragment (4 x b32) of k-step s: code values, UNSCALED, offset NOT applied
+// frag       : the A fragments (kPlanes x 4 x b32) of k-step s: code values, UNSCALED, offset NOT applied
 // kPlanes    : fragments per k-step whose products add up to the weight (2 for nf4 x bf16: the table
 //              value split into two bf16), kLutBytes: shared-memory table the codec reads through `lut`
+//              at the lane's `lane_slot`
 template <int QT, bool BF> struct Codec;
 
 template <bool BF, int OFFSET> struct Codec4 {
@@ -152,11 +153,14 @@ template <bool BF, int OFFSET> struct Codec4 {
     static constexpr float kLo = BF ? 1.0f : 16777216.0f;    // fp16 path: a0,a2 hold n * 2^-24
     static constexpr float kHi = BF ? 1.0f : 1048576.0f;     //            a1,a3 hold n * 2^-20
     static constexpr int kPlanes = 1, kLutBytes = 0;
+    static constexpr bool kRowSplit = false;
     __device__ static __forceinline__ void fill_lut(uint8_t*, int) {}
     __device__ static __forceinline__ void load(Tile& t, uint32_t codes, int r, int lane) {
         t.q = lds16(codes + r * 512 + lane * 16);
     }
-    __device__ static __forceinline__ void frag(const Tile& t, int s, uint32_t (&a)[4], uint32_t, int) {
+    __device__ static __forceinline__ uint32_t lane_slot(int) { return 0u; }
+    __device__ static __forceinline__ void frag(const Tile& t, int s, uint32_t (&ap)[1][4], uint32_t, uint32_t) {
+        uint32_t (&a)[4] = ap[0];
         const uint32_t w = s == 0 ? t.q.x : s == 1 ? t.q.y : s == 2 ? t.q.z : t.q.w;
         if (!BF) {
             // fp16 subnormals: bits 0x000n = n * 2^-24, bits 0x00n0 = n * 2^-20 (exact, no offset)
@@ -177,14 +181,17 @@ template <bool BF> struct Codec<QT_SYM_INT4, BF> : Codec4<BF, 1> {};
 // nf4: w = T[code] * d with the 16-entry NormalFloat table.  Byte b of the lane's word s is the
 // code pair of fragment register a_b (tilednf4_pos), looked up in a 256-entry table of
 // (T[lo], T[hi]) pairs: fp16x2 for fp16 activations (table values rounded to fp16: 2^-12 relative),
-// two bf16x2 planes (value = hi + lo part, 2^-17) for bf16.  8 copies of every entry (32 bytes per
-// entry, copy = lane % 8) keep the lookups of a warp nearly free of bank conflicts.
+// two bf16x2 planes (value = hi + lo part, 2^-17) for bf16.  An entry is 128 bytes, one slot per lane, so that no
+// two lanes of a load ever meet in a bank (8 slots per entry cost 3.1 wavefronts per LDS, and the kernel was bound
+// by them): fp16 = 32 slots of 4 bytes; bf16 = 16 slots of {hi, lo} read with one LDS.64, which the hardware
+// serves half-warp by half-warp -- lanes l and l + 16 share a slot and never collide.  32 KB per CTA.
 template <bool BF> struct Codec<QT_NF4, BF> {
     struct Tile { uint4 q; };
     static constexpr int kTileBytes = 512;
     static constexpr int kOffset = 0;
     static constexpr float kLo = 1.0f, kHi = 1.0f;
-    static constexpr int kPlanes = BF ? 2 : 1, kLutBytes = kPlanes * 8192;
+    static constexpr int kPlanes = BF ? 2 : 1, kLutBytes = 256 * 128;
+    static constexpr bool kRowSplit = BF;      // see frag
     __device__ static __forceinline__ uint32_t entry(int e, int plane) {
         const float lo = kNF4Table[e & 15], hi = kNF4Table[e >> 4];
         if (!BF) return h2_as_u32(__floats2half2_rn(lo, hi));
@@ -193,25 +200,36 @@ template <bool BF> struct Codec<QT_NF4, BF> {
         const float2 hf = __bfloat1622float2(h);
         return bf2_as_u32(__floats2bfloat162_rn(lo - hf.x, hi - hf.y));
     }
-    __device__ static __forceinline__ void fill_lut(uint8_t* lut, int tid) {   // 128 threads, 256 entries per plane
+    __device__ static __forceinline__ void fill_lut(uint8_t* lut, int tid) {   // 128 threads, 256 entries
+        for (int e = tid; e < 256; e += GEMV_WARPS * 32) {
+            const uint32_t v0 = entry(e, 0), v1 = BF ? entry(e, 1) : v0;
+            uint4* dst = reinterpret_cast<uint4*>(lut + e * 128);
 #pragma unroll
-        for (int plane = 0; plane < kPlanes; plane++)
-            for (int e = tid; e < 256; e += GEMV_WARPS * 32) {
-                const uint32_t v = entry(e, plane);
-                uint4* dst = reinterpret_cast<uint4*>(lut + plane * 8192 + e * 32);
-                dst[0] = make_uint4(v, v, v, v); dst[1] = make_uint4(v, v, v, v);
-            }
+            for (int c = 0; c < 8; c++) dst[c] = make_uint4(v0, v1, v0, v1);
+        }
     }
+    __device__ static __forceinline__ uint32_t lane_slot(int lane) { return BF ? 8u * (lane & 15) : 4u * lane; }
     __device__ static __forceinline__ void load(Tile& t, uint32_t codes, int r, int lane) {
         t.q = lds16(codes + r * 512 + lane * 16);
     }
-    // lut = table address + 4 * (lane % 8)
-    __device__ static __forceinline__ void frag(const Tile& t, int s, uint32_t (&a)[4], uint32_t lut, int plane) {
+    // lut: the table (warp-uniform); slot = lane_slot(lane)
+    __device__ static __forceinline__ void frag(const Tile& t, int s, uint32_t (&a)[kPlanes][4], uint32_t lut, uint32_t slot) {
         const uint32_t w = s == 0 ? t.q.x : s == 1 ? t.q.y : s == 2 ? t.q.z : t.q.w;
-        a[0] = lds4(lut + plane * 8192 + ((w << 5) & 0x1fe0u));
-        a[1] = lds4(lut + plane * 8192 + ((w >> 3) & 0x1fe0u));
-        a[2] = lds4(lut + plane * 8192 + ((w >> 11) & 0x1fe0u));
-        a[3] = lds4(lut + plane * 8192 + ((w >> 19) & 0x1fe0u));
+        // byte b -> entry address: one PRMT (extract) and one IMAD (x 128 + the lane's slot in the table)
+        const uint32_t base = lut + slot;
+        const uint32_t i0 = __byte_perm(w, 0u, 0x4440u) * 128u, i1 = __byte_perm(w, 0u, 0x4441u) * 128u;
+        const uint32_t i2 = __byte_perm(w, 0u, 0x4442u) * 128u, i3 = __byte_perm(w, 0u, 0x4443u) * 128u;
+        if (BF) {
+            const uint2 v0 = lds8(base + i0), v1 = lds8(base + i1), v2 = lds8(base + i2), v3 = lds8(base + i3);
+            // an LDS.64 leaves {hi, lo} in a register pair and the MMA wants its A quad in four consecutive registers:
+            // fragment 0 = {hi, lo} of bytes 0 and 2 (weight row g), fragment 1 = those of bytes 1 and 3 (row g + 8).
+            // The MMA's "rows 8..15" are then the lo parts of the same weight row (kRowSplit): the kernel keeps one
+            // accumulator quad per fragment and adds c0 + c2, c1 + c3 afterwards.  No register moves.
+            a[0][0] = v0.x; a[0][1] = v0.y; a[0][2] = v2.x; a[0][3] = v2.y;
+            a[kPlanes - 1][0] = v1.x; a[kPlanes - 1][1] = v1.y; a[kPlanes - 1][2] = v3.x; a[kPlanes - 1][3] = v3.y;
+        } else {
+            a[0][0] = lds4(base + i0); a[0][1] = lds4(base + i1); a[0][2] = lds4(base + i2); a[0][3] = lds4(base + i3);
+        }
     }
 };
 template <bool BF> struct Codec<QT_ASYM_INT4, BF> : Codec4<BF, 2> {};
@@ -222,6 +240,7 @@ template <int QT, bool BF> struct Codec8 {
     static constexpr int kOffset = 0;
     static constexpr float kLo = 1.0f, kHi = 1.0f;
     static constexpr int kPlanes = 1, kLutBytes = 0;
+    static constexpr bool kRowSplit = false;
     __device__ static __forceinline__ void fill_lut(uint8_t*, int) {}
     __device__ static __forceinline__ void load(Tile& t, uint32_t codes, int r, int lane) {
         t.q0 = lds16(codes + r * 1024 + lane * 16);
@@ -237,7 +256,9 @@ template <int QT, bool BF> struct Codec8 {
         }
         return BF ? h2_to_bf2(h) : h;
     }
-    __device__ static __forceinline__ void frag(const Tile& t, int s, uint32_t (&a)[4], uint32_t, int) {
+    __device__ static __forceinline__ uint32_t lane_slot(int) { return 0u; }
+    __device__ static __forceinline__ void frag(const Tile& t, int s, uint32_t (&ap)[1][4], uint32_t, uint32_t) {
+        uint32_t (&a)[4] = ap[0];
         const uint32_t w0 = s == 0 ? t.q0.x : s == 1 ? t.q0.y : s == 2 ? t.q0.z : t.q0.w;
         const uint32_t w1 = s == 0 ? t.q1.x : s == 1 ? t.q1.y : s == 2 ? t.q1.z : t.q1.w;
         a[0] = pair(w0, 0); a[1] = pair(w1, 0); a[2] = pair(w0, 1); a[3] = pair(w1, 1);
@@ -252,6 +273,7 @@ template <bool BF> struct Codec<QT_FP6, BF> {
     static constexpr int kOffset = 0;
     static constexpr float kLo = 1.0f, kHi = 1.0f;
     static constexpr int kPlanes = 1, kLutBytes = 0;
+    static constexpr bool kRowSplit = false;
     __device__ static __forceinline__ void fill_lut(uint8_t*, int) {}
     __device__ static __forceinline__ void load(Tile& t, uint32_t codes, int r, int lane) {
         t.lo = lds16(codes + r * 768 + lane * 16);
@@ -262,7 +284,9 @@ template <bool BF> struct Codec<QT_FP6, BF> {
         asm("cvt.rn.f16x2.e3m2x2 %0, %1;" : "=r"(h) : "h"(two));
         return BF ? h2_to_bf2(h) : h;
     }
-    __device__ static __forceinline__ void frag(const Tile& t, int s, uint32_t (&a)[4], uint32_t, int) {
+    __device__ static __forceinline__ uint32_t lane_slot(int) { return 0u; }
+    __device__ static __forceinline__ void frag(const Tile& t, int s, uint32_t (&ap)[1][4], uint32_t, uint32_t) {
+        uint32_t (&a)[4] = ap[0];
         const int u = s >> 1;
         const uint32_t l0 = u ? t.lo.y : t.lo.x, l1 = u ? t.lo.w : t.lo.z;
         const uint32_t sh = (s & 1) ? 4u : 0u;
@@ -417,7 +441,8 @@ gemv_kernel(const GemvArgs A) {
     const uint32_t bars = smem_u32(smem) + GEMV_WARPS * WB + warp * (STAGES * 8);
     // the codec's lookup table (nf4): built once per CTA, read-only afterwards
     const int tl = S::live_t(NT, ACC, A.M);            // live t-lanes of the reduction (see Staging)
-    const uint32_t lut = smem_u32(smem) + S::lut_offset(NT, ACC, NM, tl, A.ring_recv != 0) + 4 * (lane & 7);
+    const uint32_t lut = smem_u32(smem) + S::lut_offset(NT, ACC, NM, tl, A.ring_recv != 0);      // warp-uniform
+    const uint32_t lut_slot = C::lane_slot(lane);
     if (C::kLutBytes) {
         C::fill_lut(smem + S::lut_offset(NT, ACC, NM, tl, A.ring_recv != 0), threadIdx.x);
         __syncthreads();
@@ -539,7 +564,15 @@ gemv_kernel(const GemvArgs A) {
     // x comes from L2 (each warp reads its own K slice; L1 is cold): the fragment of the NEXT k-block is
     // requested one super-tile ahead so that the ~0.4 us round trip hides behind the current one
     int xleft = 0;
+    constexpr bool CAN_NORM = (MODE == 0 && NT == 1 && NS == 1);
+    uint32_t xs_base = 0, xs_run = 0;                  // fused RMSNorm: this lane's fragment address in the normalised slice
+    bool normed = false;
     auto fetch_x = [&](uint4 (&dst)[NT][NS][2]) {      // fetch the k-block at xrun, advance
+        if (CAN_NORM && normed) {
+            if (xvalid[0]) { dst[0][0][0] = lds16(xs_run); dst[0][0][1] = lds16(xs_run + 16); }
+            xs_run += 128;
+            return;
+        }
 #pragma unroll
         for (int j = 0; j < NT; j++)
 #pragma unroll
@@ -554,6 +587,110 @@ gemv_kernel(const GemvArgs A) {
     // read of x, so the set-up instructions of all resident warps run while the SM would be idle anyway
     if (MODE == 0 && A.pdl) asm volatile("griddepcontrol.wait;" ::: "memory");
     TS(2);
+    if (CAN_NORM && A.norm_w) {
+        // ---- fused RMSNorm (transformers' statement, decode_ops.cu): statistics of the whole row(s), then the normalised
+        // K slice of this CTA in shared memory.  128 threads stand in for rms_norm_vec_kernel's 512: thread i sums the
+        // vectors of its "virtual" threads i, i + 128, i + 256, i + 384 separately and warp w reduces virtual warps
+        // w, w + 4, w + 8, w + 12 with the same shuffle tree, so the sum -- and every rounded output -- has the same bits.
+        // One L2 round trip: the four vectors of a pass are requested together (the next pass's before this one's
+        // arithmetic), the norm weights of the warp's own part with them, and a vector that lies in the CTA's slice is
+        // dropped into shared memory as it goes by.
+        float* red = reinterpret_cast<float*>(smem + A.xs_off);                 // [8 rows][16 virtual warps]
+        uint8_t* xs = smem + A.xs_off + 512;
+        const int K = (int)A.G.k, nvec = K / 8;
+        const int sv0 = ck0 * 8, svec = (ck1 - ck0) * 8;                        // the slice in 16-byte pieces
+        const int wv0 = (kb0 - ck0) * 8, wsv = n_super * 8;                     // this warp's part of it
+        const int items = A.M * wsv;                                            // (row, piece) pairs this warp normalises
+        const uint4* wp = reinterpret_cast<const uint4*>(A.norm_w) + sv0 + wv0;
+        uint4 wpre[2];
+#pragma unroll
+        for (int i = 0; i < 2; i++) {
+            const int idx = lane + 32 * i;
+            if (idx < items) wpre[i] = __ldg(wp + idx % wsv);
+        }
+        const int nj = (nvec + 511) / 512, passes = A.M * nj;
+        uint4 cur[4], nxt[4];
+        auto request = [&](int pass, uint4 (&dst)[4]) {
+            const int row = pass / nj, j0 = (pass - row * nj) * 512;
+            const uint4* xp = reinterpret_cast<const uint4*>(A.x + (int64_t)row * K);
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                const int v = j0 + (int)threadIdx.x + 128 * q;
+                if (v < nvec) dst[q] = __ldcg(xp + v);
+            }
+        };
+        request(0, cur);
+        float ss[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+        for (int pass = 0; pass < passes; pass++) {
+            if (pass + 1 < passes) request(pass + 1, nxt);
+            const int row = pass / nj, j0 = (pass - row * nj) * 512;
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                const int v = j0 + (int)threadIdx.x + 128 * q;
+                if (v < nvec) {
+                    const uint16_t* e = reinterpret_cast<const uint16_t*>(&cur[q]);
+#pragma unroll
+                    for (int i = 0; i < 8; i++) {
+                        const float f = BF ? __uint_as_float((uint32_t)e[i] << 16) : half_bits_to_float(e[i]);
+                        ss[q] = fmaf(f, f, ss[q]);
+                    }
+                    const int sv = v - sv0;
+                    if (sv >= 0 && sv < svec) *reinterpret_cast<uint4*>(xs + ((int64_t)row * svec + sv) * 16) = cur[q];
+                }
+            }
+            if (j0 + 512 >= nvec) {                     // the row is complete
+#pragma unroll
+                for (int o = 16; o; o >>= 1)
+#pragma unroll
+                    for (int q = 0; q < 4; q++) ss[q] += __shfl_xor_sync(0xffffffffu, ss[q], o);
+#pragma unroll
+                for (int q = 0; q < 4; q++) {
+                    if (lane == 0) red[row * 16 + warp + 4 * q] = ss[q];
+                    ss[q] = 0.0f;
+                }
+            }
+#pragma unroll
+            for (int q = 0; q < 4; q++) cur[q] = nxt[q];
+        }
+        __syncthreads();
+        // every warp normalises its own k-blocks in place: a warp-level barrier is all the main loop waits for
+        int have_row = -1;
+        float r = 0.0f;
+        for (int idx = lane, i = 0; idx < items; idx += 32, i++) {
+            const int row = idx / wsv, v = idx - row * wsv;
+            if (row != have_row) {
+                float tot = 0.0f;
+#pragma unroll
+                for (int w = 0; w < 16; w++) tot += red[row * 16 + w];
+                r = 1.0f / sqrtf(tot / (float)K + A.norm_eps);
+                have_row = row;
+            }
+            uint4* slot = reinterpret_cast<uint4*>(xs + ((int64_t)row * svec + wv0 + v) * 16);
+            const uint4 xv = *slot;
+            const uint4 wv = i < 2 ? wpre[i] : __ldg(wp + v);
+            const uint16_t* e = reinterpret_cast<const uint16_t*>(&xv);
+            const uint16_t* we = reinterpret_cast<const uint16_t*>(&wv);
+            uint4 ov;
+            uint16_t* oe = reinterpret_cast<uint16_t*>(&ov);
+#pragma unroll
+            for (int k8 = 0; k8 < 8; k8++) {
+                if (BF) {
+                    const float n = __bfloat162float(__float2bfloat16_rn(__uint_as_float((uint32_t)e[k8] << 16) * r));
+                    const __nv_bfloat16 o = __float2bfloat16_rn(__uint_as_float((uint32_t)we[k8] << 16) * n);
+                    oe[k8] = *reinterpret_cast<const uint16_t*>(&o);
+                } else {
+                    const float n = __half2float(__float2half_rn(half_bits_to_float(e[k8]) * r));
+                    const __half o = __float2half_rn(half_bits_to_float(we[k8]) * n);
+                    oe[k8] = *reinterpret_cast<const uint16_t*>(&o);
+                }
+            }
+            *slot = ov;
+        }
+        __syncwarp();
+        normed = true;
+        xs_base = smem_u32(xs) + (uint32_t)(g * svec * 16 + t * 32 + (kb0 - ck0) * 128);
+        xs_run = xs_base;
+    }
     if (XPF && n_super > 0) fetch_x(xq[0]);
 
     uint32_t ones[4];
@@ -573,7 +710,7 @@ gemv_kernel(const GemvArgs A) {
     for (int mt = 0; mt < NM; mt++) {
     float (&acc)[RG_TILES][NT][ACC] = accm[mt];
     xleft = n_super;
-    if (!XPF) xrun = xbase;
+    if (!XPF) { xrun = xbase; xs_run = xs_base; }
     for (int z = z_first; z <= z_last; z++) {
     int s_a, s_n;
     const uint8_t* s_base;
@@ -597,7 +734,7 @@ gemv_kernel(const GemvArgs A) {
                     xleft--;
                     if (xleft > 0) fetch_x(xq[XPF ? (h ^ 1) : 0]);
                     else if (mt + 1 < NM) {            // the second matrix starts over at the slice's first block
-                        xrun = xbase;
+                        xrun = xbase; xs_run = xs_base;
                         fetch_x(xq[XPF ? (h ^ 1) : 0]);
                     }
                 } else {
@@ -633,23 +770,44 @@ gemv_kernel(const GemvArgs A) {
 #pragma unroll
                     for (int j = 0; j < NT; j++) cc[r][j][0] = cc[r][j][1] = cc[r][j][2] = cc[r][j][3] = 0.0f;
                 }
+                // row-split codecs (nf4 x bf16): fragment 1 = weight row g + 8, accumulated apart and folded in below
+                constexpr bool RS = C::kRowSplit;
+                float cc2[RS ? RG_TILES : 1][NT][4];
+                if (RS) {
+#pragma unroll
+                    for (int r = 0; r < RG_TILES; r++)
+#pragma unroll
+                        for (int j = 0; j < NT; j++) cc2[r][j][0] = cc2[r][j][1] = cc2[r][j][2] = cc2[r][j][3] = 0.0f;
+                }
 #pragma unroll
                 for (int s = 0; s < 4; s++) {
 #pragma unroll
                     for (int r = 0; r < RG_TILES; r++) {
 #pragma unroll
+                        uint32_t af[C::kPlanes][4];
+                        C::frag(tile[r], s, af, lut, lut_slot);
+#pragma unroll
                         for (int pw = 0; pw < C::kPlanes; pw++) {
-                            uint32_t a[4];
-                            C::frag(tile[r], s, a, lut, pw);
+                            uint32_t (&a)[4] = af[pw];
 #pragma unroll
                             for (int j = 0; j < NT; j++)
 #pragma unroll
                                 for (int p = 0; p < NS; p++) {
                                     const uint4 v = xb[j][p][s >> 1];
-                                    mma16816<BF>(cc[r][j], a, (s & 1) ? v.z : v.x, (s & 1) ? v.w : v.y);
+                                    mma16816<BF>((RS && pw == 1) ? cc2[RS ? r : 0][j] : cc[r][j], a, (s & 1) ? v.z : v.x, (s & 1) ? v.w : v.y);
                                 }
                         }
                     }
+                }
+                if (RS) {
+#pragma unroll
+                    for (int r = 0; r < RG_TILES; r++)
+#pragma unroll
+                        for (int j = 0; j < NT; j++) {
+                            const float g0 = cc[r][j][0] + cc[r][j][2], g1 = cc[r][j][1] + cc[r][j][3];
+                            const float h0 = cc2[r][j][0] + cc2[r][j][2], h1 = cc2[r][j][1] + cc2[r][j][3];
+                            cc[r][j][0] = g0; cc[r][j][1] = g1; cc[r][j][2] = h0; cc[r][j][3] = h1;
+                        }
                 }
 #pragma unroll
                 for (int r = 0; r < RG_TILES; r++) {
@@ -1030,6 +1188,11 @@ static void launch_kernel(K kernel, int smem, int64_t groups, int64_t nb, const 
         if (split_ring > split) { split = split_ring; smem = smem_ring; B.ring_recv = 1; }
     }
     B.slice_q = (int)(nb / split); B.slice_r = (int)(nb % split);
+    if (B.norm_w) {
+        // fused RMSNorm: 512 bytes of row statistics + the normalised K slice of the CTA (M rows x up to slice_q + 1 blocks)
+        B.xs_off = (smem + 15) & ~15;
+        smem = B.xs_off + 512 + B.M * (B.slice_q + 1) * 128;
+    }
     {
         static int padl = -1;                            // development: LOWBIT_GEMV_PAD_L = resident CTAs per SM to allow
         if (padl < 0) { const char* e = getenv("LOWBIT_GEMV_PAD_L"); padl = e ? atoi(e) : 0; }
