@@ -210,17 +210,6 @@ int lowbit_rms_norm_cuda(const void* d_x, int x_dtype, int64_t x_row_stride, con
                          float eps, int64_t rows, int64_t hidden, void* d_y, int y_dtype, int64_t y_row_stride,
                          void* stream);
 
-/* RMSNorm folded into the matmul that consumes it.  lowbit_fuse_rms_norm(d_norm_weight, eps) makes the NEXT
- * lowbit_matmul_cuda / lowbit_mlp_cuda on the calling thread treat d_x as the un-normalised rows and apply
- * lowbit_rms_norm_cuda's statement to them while loading (norm weight [K] of x's dtype, 16-byte aligned): every CTA
- * computes the row statistics itself, in the summation order of the stand-alone kernel, and keeps the normalised part
- * of the rows it needs in shared memory -- same bits as the two separate calls, one launch and one dependency hop
- * less per norm in a decode step.  Served for M <= 8, fp16 / bf16 activations, n_rows % 64 == 0; any other call fails
- * with an argument error and the request is dropped.  No counterpart in the reference (xe_addons.rms_norm is a separate
- * op there, models/common.py:187-200). */
-void lowbit_fuse_rms_norm(const void* d_norm_weight, float eps);
-int lowbit_fuse_rms_norm_supported(int qtype, int64_t n_rows, int64_t k, int64_t m, int x_dtype);
-
 /* Rotary embedding of the merged qkv projection's output and the FP8 cache write in one launch -- the pair
  * rotary_half_with_cache_inplaced(q, k, cos, sin) + DynamicFp8Cache.update -> xe_addons.quantize_key_value of the
  * reference's attention forward (models/llama.py:146-183, models/utils.py:119-139).  d_qkv [B][S][(Hq + 2 Hkv) * D]

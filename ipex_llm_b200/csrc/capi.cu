@@ -112,7 +112,6 @@ void b200_lowbit_set_row_length(int k) { t_row_len = k; }
 void lowbit_set_programmatic_dependent_launch(int on) { gemv_set_pdl(on); }
 int lowbit_get_programmatic_dependent_launch(void) { return gemv_get_pdl(); }
 void lowbit_hint_next_weights(const void* d_w, size_t bytes) { gemv_set_next_weights(d_w, bytes); }
-void lowbit_fuse_rms_norm(const void* d_norm_weight, float eps) { gemv_set_norm(d_norm_weight, eps); }
 /* development aid, not in the public header: per-warp phase timestamps of the GEMV kernel */
 void lowbit_debug_set_timestamps(void* dev_ptr) { gemv_set_debug_timestamps(dev_ptr); }
 
@@ -174,15 +173,10 @@ size_t lowbit_matmul_workspace_size(int64_t n_rows, int64_t k, int64_t m, int x_
     return gemv_workspace_size(n_rows, k, m, x_dtype);
 }
 
-int lowbit_fuse_rms_norm_supported(int qtype, int64_t n_rows, int64_t k, int64_t m, int x_dtype) {
-    return !use_gemm(qtype, n_rows, k, m, x_dtype) && gemv_norm_supported(qtype, n_rows, k, m, x_dtype);
-}
-
 static int matmul_dispatch(const void* d_w, int qtype, int64_t n_rows, int64_t k, const void* d_x, int x_dtype, int64_t m,
                            void* d_y, int y_dtype, const void* d_bias, int accumulate, void* workspace, size_t workspace_bytes,
                            cudaStream_t st) {
     if (use_gemm(qtype, n_rows, k, m, x_dtype)) {
-        if (gemv_take_norm()) return LB_ERR_ARG;       // the fused RMSNorm belongs to the decode GEMV (M <= 8)
         int64_t done = 0;
         return gemm_tc_launch(d_w, qtype, n_rows, k, d_x, x_dtype, m, d_y, y_dtype, d_bias, accumulate, workspace,
                               workspace_bytes, st, &done);
@@ -229,10 +223,6 @@ int lowbit_mlp_cuda(const void* d_w_gate, const void* d_w_up, int qtype, int64_t
     if (act != 0 && act != 1) { set_error(LB_ERR_ARG, "lowbit_mlp_cuda: act must be 0 (SILU) or 1 (GELU), got %d", act); return LB_ERR_ARG; }
     if (!d_w_gate || !d_w_up || !d_x || !d_y || m < 0 || n_rows < 0) { set_error(LB_ERR_ARG, "lowbit_mlp_cuda: null pointer or negative size"); return LB_ERR_ARG; }
     const bool fused = gemv_mlp_fused_supported(qtype, n_rows, k, m);
-    if (!fused && gemv_take_norm()) {                   // the two-matmul route below would normalise only the first one
-        set_error(LB_ERR_ARG, "lowbit_mlp_cuda: the fused RMSNorm needs the one-launch MLP (M <= 8)");
-        return LB_ERR_ARG;
-    }
     const size_t base = (lowbit_matmul_workspace_size(n_rows, k, m, x_dtype) + 255) / 256 * 256;
     const size_t need = base + (fused ? 0 : 2 * (size_t)m * n_rows * sizeof(float));
     std::unique_lock<std::mutex> lk(g_mu, std::defer_lock);

@@ -86,19 +86,6 @@ void gemv_set_debug_timestamps(void* p) { g_ts = (unsigned long long*)p; }
 static thread_local const uint8_t* t_next_w = nullptr;     // L2 prefetch hint for the next launch (one-shot)
 static thread_local unsigned long long t_next_bytes = 0;
 void gemv_set_next_weights(const void* w, size_t bytes) { t_next_w = (const uint8_t*)w; t_next_bytes = bytes; }
-static thread_local const void* t_norm_w = nullptr;        // one-shot: the next launch applies RMSNorm to its activations
-static thread_local float t_norm_eps = 0.0f;
-void gemv_set_norm(const void* w, float eps) { t_norm_w = w; t_norm_eps = eps; }
-bool gemv_take_norm() { const bool pending = t_norm_w != nullptr; t_norm_w = nullptr; return pending; }
-static bool has_mma_codec(int qt);
-// the launches that can apply RMSNorm while loading: one pass of at most 8 half-precision rows of at most 16384 elements
-// (the range of the stand-alone kernel whose summation order the prologue reproduces), every output row in the
-// tensor-core part of the kernel
-bool gemv_norm_supported(int qt, int64_t n_rows, int64_t k, int64_t m, int x_dtype) {
-    qt = canon_qtype(qt);
-    return supported(qt) && has_mma_codec(qt) && m >= 1 && m <= 8 && k > 0 && k % QK == 0 && k <= 16384 &&
-           (x_dtype == DT_F16 || x_dtype == DT_BF16) && n_rows > 0 && n_rows % RG_ROWS == 0;
-}
 static int g_pdl = 0;     // programmatic dependent launch for the GEMV kernels (set by the host engine)
 void gemv_set_pdl(int on) { g_pdl = on ? 1 : 0; }
 int gemv_get_pdl() { return g_pdl; }
@@ -157,15 +144,10 @@ int gemv_launch_ex(const void* w, const void* w2, int act, int qt, int64_t n_row
     qt = canon_qtype(qt);
     const GemvPush push = t_push;                      // one-shot
     t_push = GemvPush{};
-    const void* norm_w = t_norm_w;                     // one-shot
-    const float norm_eps = t_norm_eps;
-    t_norm_w = nullptr;
     // fused all-reduce: one pass (m <= 32), every row in the tensor-core part
     if (push.world > 0 && (w2 || m > 8 * GEMV_MAX_NT || !has_mma_codec(qt) || n_rows % RG_ROWS)) return LB_ERR_ARG;
     if (w2 && (!gemv_mlp_fused_supported(qt, n_rows, k, m) || ((uintptr_t)w2 & 15) || bias || accumulate)) return LB_ERR_ARG;
     if (!supported(qt) || k <= 0 || k % QK || n_rows <= 0 || m <= 0) return LB_ERR_ARG;
-    if (norm_w && (!gemv_norm_supported(qt, n_rows, k, m, x_dtype) || ((uintptr_t)norm_w & 15) || push.world > 0))
-        return LB_ERR_ARG;
     if (x_dtype < 0 || x_dtype > 2 || y_dtype < 0 || y_dtype > 2) return LB_ERR_ARG;
     if (((uintptr_t)w & 15) || ((uintptr_t)x & 15)) return LB_ERR_ARG;        // TMA bulk / 128-bit loads
     const TiledGeom G = make_geom(n_rows, k, qt);
@@ -183,7 +165,6 @@ int gemv_launch_ex(const void* w, const void* w2, int act, int qt, int64_t n_row
             A.y = yc; A.y_dtype = y_dtype; A.bias = bias; A.accumulate = accumulate;
             A.plane_stride = mc * k;
             A.pdl = g_pdl; A.ts = g_ts;
-            A.norm_w = norm_w; A.norm_eps = norm_eps;
             A.next_w = t_next_w; A.next_bytes = t_next_bytes;
             t_next_w = nullptr; t_next_bytes = 0;            // one-shot hint
             A.push_world = push.world; A.push_rank = push.rank; A.push_slot_bytes = push.slot_bytes; A.push_epochs = push.epochs;

@@ -36,12 +36,6 @@ struct GemvArgs {
     const uint8_t* next_w;    // hint: weights of the NEXT matmul on this stream, prefetched into L2 (or NULL)
     unsigned long long next_bytes;
     unsigned long long* ts;   // development: per-warp phase timestamps (8 per warp) or NULL
-    // fused RMSNorm (M <= 8, fp16 / bf16): x is the un-normalised residual stream; every CTA computes the row statistics
-    // itself (same summation order as rms_norm_vec_kernel in decode_ops.cu) and keeps the normalised K slice it needs in
-    // shared memory at byte offset xs_off -- the norm costs no launch and no dependency hop
-    const void* norm_w;       // NULL (x is used as it is) or the norm's weight [K], same dtype as x
-    float norm_eps;
-    int xs_off;               // set at launch
     // mixture-of-experts decode (reference xe_linear.moe_forward_vec), M == 1:
     //   mode 1: blockIdx.z = routed slot z; w / w2 = tab_w[sel[z]] / tab_w2[sel[z]]; y row z
     //   mode 2: the K axis is the concatenation of n_seg matrices tab_w[sel[z]] ([rows][k] each) and

@@ -564,15 +564,7 @@ gemv_kernel(const GemvArgs A) {
     // x comes from L2 (each warp reads its own K slice; L1 is cold): the fragment of the NEXT k-block is
     // requested one super-tile ahead so that the ~0.4 us round trip hides behind the current one
     int xleft = 0;
-    constexpr bool CAN_NORM = (MODE == 0 && NT == 1 && NS == 1);
-    uint32_t xs_base = 0, xs_run = 0;                  // fused RMSNorm: this lane's fragment address in the normalised slice
-    bool normed = false;
     auto fetch_x = [&](uint4 (&dst)[NT][NS][2]) {      // fetch the k-block at xrun, advance
-        if (CAN_NORM && normed) {
-            if (xvalid[0]) { dst[0][0][0] = lds16(xs_run); dst[0][0][1] = lds16(xs_run + 16); }
-            xs_run += 128;
-            return;
-        }
 #pragma unroll
         for (int j = 0; j < NT; j++)
 #pragma unroll
@@ -587,110 +579,6 @@ gemv_kernel(const GemvArgs A) {
     // read of x, so the set-up instructions of all resident warps run while the SM would be idle anyway
     if (MODE == 0 && A.pdl) asm volatile("griddepcontrol.wait;" ::: "memory");
     TS(2);
-    if (CAN_NORM && A.norm_w) {
-        // ---- fused RMSNorm (transformers' statement, decode_ops.cu): statistics of the whole row(s), then the normalised
-        // K slice of this CTA in shared memory.  128 threads stand in for rms_norm_vec_kernel's 512: thread i sums the
-        // vectors of its "virtual" threads i, i + 128, i + 256, i + 384 separately and warp w reduces virtual warps
-        // w, w + 4, w + 8, w + 12 with the same shuffle tree, so the sum -- and every rounded output -- has the same bits.
-        // One L2 round trip: the four vectors of a pass are requested together (the next pass's before this one's
-        // arithmetic), the norm weights of the warp's own part with them, and a vector that lies in the CTA's slice is
-        // dropped into shared memory as it goes by.
-        float* red = reinterpret_cast<float*>(smem + A.xs_off);                 // [8 rows][16 virtual warps]
-        uint8_t* xs = smem + A.xs_off + 512;
-        const int K = (int)A.G.k, nvec = K / 8;
-        const int sv0 = ck0 * 8, svec = (ck1 - ck0) * 8;                        // the slice in 16-byte pieces
-        const int wv0 = (kb0 - ck0) * 8, wsv = n_super * 8;                     // this warp's part of it
-        const int items = A.M * wsv;                                            // (row, piece) pairs this warp normalises
-        const uint4* wp = reinterpret_cast<const uint4*>(A.norm_w) + sv0 + wv0;
-        uint4 wpre[2];
-#pragma unroll
-        for (int i = 0; i < 2; i++) {
-            const int idx = lane + 32 * i;
-            if (idx < items) wpre[i] = __ldg(wp + idx % wsv);
-        }
-        const int nj = (nvec + 511) / 512, passes = A.M * nj;
-        uint4 cur[4], nxt[4];
-        auto request = [&](int pass, uint4 (&dst)[4]) {
-            const int row = pass / nj, j0 = (pass - row * nj) * 512;
-            const uint4* xp = reinterpret_cast<const uint4*>(A.x + (int64_t)row * K);
-#pragma unroll
-            for (int q = 0; q < 4; q++) {
-                const int v = j0 + (int)threadIdx.x + 128 * q;
-                if (v < nvec) dst[q] = __ldcg(xp + v);
-            }
-        };
-        request(0, cur);
-        float ss[4] = {0.0f, 0.0f, 0.0f, 0.0f};
-        for (int pass = 0; pass < passes; pass++) {
-            if (pass + 1 < passes) request(pass + 1, nxt);
-            const int row = pass / nj, j0 = (pass - row * nj) * 512;
-#pragma unroll
-            for (int q = 0; q < 4; q++) {
-                const int v = j0 + (int)threadIdx.x + 128 * q;
-                if (v < nvec) {
-                    const uint16_t* e = reinterpret_cast<const uint16_t*>(&cur[q]);
-#pragma unroll
-                    for (int i = 0; i < 8; i++) {
-                        const float f = BF ? __uint_as_float((uint32_t)e[i] << 16) : half_bits_to_float(e[i]);
-                        ss[q] = fmaf(f, f, ss[q]);
-                    }
-                    const int sv = v - sv0;
-                    if (sv >= 0 && sv < svec) *reinterpret_cast<uint4*>(xs + ((int64_t)row * svec + sv) * 16) = cur[q];
-                }
-            }
-            if (j0 + 512 >= nvec) {                     // the row is complete
-#pragma unroll
-                for (int o = 16; o; o >>= 1)
-#pragma unroll
-                    for (int q = 0; q < 4; q++) ss[q] += __shfl_xor_sync(0xffffffffu, ss[q], o);
-#pragma unroll
-                for (int q = 0; q < 4; q++) {
-                    if (lane == 0) red[row * 16 + warp + 4 * q] = ss[q];
-                    ss[q] = 0.0f;
-                }
-            }
-#pragma unroll
-            for (int q = 0; q < 4; q++) cur[q] = nxt[q];
-        }
-        __syncthreads();
-        // every warp normalises its own k-blocks in place: a warp-level barrier is all the main loop waits for
-        int have_row = -1;
-        float r = 0.0f;
-        for (int idx = lane, i = 0; idx < items; idx += 32, i++) {
-            const int row = idx / wsv, v = idx - row * wsv;
-            if (row != have_row) {
-                float tot = 0.0f;
-#pragma unroll
-                for (int w = 0; w < 16; w++) tot += red[row * 16 + w];
-                r = 1.0f / sqrtf(tot / (float)K + A.norm_eps);
-                have_row = row;
-            }
-            uint4* slot = reinterpret_cast<uint4*>(xs + ((int64_t)row * svec + wv0 + v) * 16);
-            const uint4 xv = *slot;
-            const uint4 wv = i < 2 ? wpre[i] : __ldg(wp + v);
-            const uint16_t* e = reinterpret_cast<const uint16_t*>(&xv);
-            const uint16_t* we = reinterpret_cast<const uint16_t*>(&wv);
-            uint4 ov;
-            uint16_t* oe = reinterpret_cast<uint16_t*>(&ov);
-#pragma unroll
-            for (int k8 = 0; k8 < 8; k8++) {
-                if (BF) {
-                    const float n = __bfloat162float(__float2bfloat16_rn(__uint_as_float((uint32_t)e[k8] << 16) * r));
-                    const __nv_bfloat16 o = __float2bfloat16_rn(__uint_as_float((uint32_t)we[k8] << 16) * n);
-                    oe[k8] = *reinterpret_cast<const uint16_t*>(&o);
-                } else {
-                    const float n = __half2float(__float2half_rn(half_bits_to_float(e[k8]) * r));
-                    const __half o = __float2half_rn(half_bits_to_float(we[k8]) * n);
-                    oe[k8] = *reinterpret_cast<const uint16_t*>(&o);
-                }
-            }
-            *slot = ov;
-        }
-        __syncwarp();
-        normed = true;
-        xs_base = smem_u32(xs) + (uint32_t)(g * svec * 16 + t * 32 + (kb0 - ck0) * 128);
-        xs_run = xs_base;
-    }
     if (XPF && n_super > 0) fetch_x(xq[0]);
 
     uint32_t ones[4];
@@ -710,7 +598,7 @@ gemv_kernel(const GemvArgs A) {
     for (int mt = 0; mt < NM; mt++) {
     float (&acc)[RG_TILES][NT][ACC] = accm[mt];
     xleft = n_super;
-    if (!XPF) { xrun = xbase; xs_run = xs_base; }
+    if (!XPF) xrun = xbase;
     for (int z = z_first; z <= z_last; z++) {
     int s_a, s_n;
     const uint8_t* s_base;
@@ -734,7 +622,7 @@ gemv_kernel(const GemvArgs A) {
                     xleft--;
                     if (xleft > 0) fetch_x(xq[XPF ? (h ^ 1) : 0]);
                     else if (mt + 1 < NM) {            // the second matrix starts over at the slice's first block
-                        xrun = xbase; xs_run = xs_base;
+                        xrun = xbase;
                         fetch_x(xq[XPF ? (h ^ 1) : 0]);
                     }
                 } else {
@@ -1188,11 +1076,6 @@ static void launch_kernel(K kernel, int smem, int64_t groups, int64_t nb, const 
         if (split_ring > split) { split = split_ring; smem = smem_ring; B.ring_recv = 1; }
     }
     B.slice_q = (int)(nb / split); B.slice_r = (int)(nb % split);
-    if (B.norm_w) {
-        // fused RMSNorm: 512 bytes of row statistics + the normalised K slice of the CTA (M rows x up to slice_q + 1 blocks)
-        B.xs_off = (smem + 15) & ~15;
-        smem = B.xs_off + 512 + B.M * (B.slice_q + 1) * 128;
-    }
     {
         static int padl = -1;                            // development: LOWBIT_GEMV_PAD_L = resident CTAs per SM to allow
         if (padl < 0) { const char* e = getenv("LOWBIT_GEMV_PAD_L"); padl = e ? atoi(e) : 0; }

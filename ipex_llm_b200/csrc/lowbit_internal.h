@@ -42,9 +42,6 @@ int gemv_get_pdl();
 struct GemvPush;
 void gemv_set_push(const GemvPush* p);   // the next gemv_launch_ex on this thread pushes its result to the peers (comm.cu)
 void gemv_set_next_weights(const void* w, size_t bytes);
-bool gemv_norm_supported(int qt, int64_t n_rows, int64_t k, int64_t m, int x_dtype);
-bool gemv_take_norm();                          // drops a pending request; true if there was one
-void gemv_set_norm(const void* w, float eps);   // the next gemv_launch_ex on this thread normalises its activations (RMSNorm)
 void gemv_set_debug_timestamps(void* p);
 size_t gemv_workspace_size(int64_t n_rows, int64_t k, int64_t m, int x_dtype);
 int gemv_launch(const void* w, int qt, int64_t n_rows, int64_t k, const void* x, int x_dtype, int64_t m,

@@ -562,19 +562,3 @@ def lowbit_sdp_fp8_prefill(q, k, v, mask, causal, scale, out, stream):
                                             _DT_OF[str(mask.dtype)] if mask is not None else 0,
                                             _strides3(mask) if mask is not None else None, int(bool(causal)), float(scale),
                                             B, Hq, Hkv, S, L, D, out.data_ptr(), _DT_OF[str(out.dtype)], stream), "lowbit_sdp_fp8_prefill_cuda")
-
-
-_lib.lowbit_fuse_rms_norm.argtypes = [ctypes.c_void_p, ctypes.c_float]
-_lib.lowbit_fuse_rms_norm.restype = None
-_lib.lowbit_fuse_rms_norm_supported.argtypes = [ctypes.c_int, ctypes.c_int64, ctypes.c_int64, ctypes.c_int64, ctypes.c_int]
-_lib.lowbit_fuse_rms_norm_supported.restype = ctypes.c_int
-
-
-def lowbit_fuse_rms_norm(weight, eps):
-    """the next lowbit_matmul_cuda / lowbit_mlp_cuda on this thread applies RMSNorm(weight, eps) to its activations"""
-    _lib.lowbit_fuse_rms_norm(weight.data_ptr() if weight is not None else None, float(eps))
-
-
-def lowbit_fuse_rms_norm_supported(qtype, n_rows, k, m, x_dtype):
-    """whether lowbit_matmul_cuda / lowbit_mlp_cuda of this shape can apply the RMSNorm while loading x"""
-    return bool(_lib.lowbit_fuse_rms_norm_supported(qtype, n_rows, k, m, _DT_OF[str(x_dtype)]))

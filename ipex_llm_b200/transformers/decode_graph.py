@@ -84,8 +84,6 @@ class DecodeGraph:
         self.sdp_ws = torch.empty(max(256, ggml.lowbit_sdp_fp8_workspace_size(B, self.Hq, self.Hkv, 1, capacity, self.D)),
                                   dtype=torch.uint8, device=dev)
         self.fuse_mlp = cfg.hidden_act == "silu"
-        # RMSNorm inside the GEMV that reads it (<= 8 sequences); IPEX_LLM_B200_DECODE_FUSE_NORM=0: separate launches
-        self.fuse_norm = os.environ.get("IPEX_LLM_B200_DECODE_FUSE_NORM", "0") == "1"
         self.launches_per_step = 0
         # host-in-the-loop variant (streaming, end-of-sequence checks, host-side token choice): the step's input token
         # comes from pinned host memory and its output token goes back there, as copy nodes of the same graph
@@ -95,25 +93,12 @@ class DecodeGraph:
         self.graph_host = None
 
     # ---- pieces of the step
-    def _plain(self, lin):
-        """a quantised linear this process owns whole (no tensor-parallel group, no act-order permutation)"""
-        return isinstance(lin, LowBitLinear) and lin.mp_group is None and not lin.act_order and lin.weight.data.device.type == "cuda"
-
-    def _norm_in_gemv(self, norm, *lins):
-        """(weight, eps) if the RMSNorm can run inside the kernels of ``lins`` (its only consumers), else None"""
-        if not self.fuse_norm or norm.weight.dtype != self.dtype or not norm.weight.is_contiguous():
-            return None
-        for lin in lins:
-            if not (self._plain(lin) and (lin.bias is None or lin.bias.dtype == self.dtype)
-                    and ggml.lowbit_fuse_rms_norm_supported(lin.qtype, lin.out_len, self.H, self.B, self.dtype)):
-                return None
-        return (norm.weight, self.eps)
-
-    def _linear(self, lin, x, out, accumulate=False, norm=None):
+    def _linear(self, lin, x, out, accumulate=False):
         """out (+)= lin(x): the GEMV with its fused epilogue when the module allows it, the module's own forward
-        (tensor-parallel groups, unquantised or act-order linears) otherwise.  norm: see _norm_in_gemv"""
-        if self._plain(lin) and (lin.bias is None or lin.bias.dtype == out.dtype):
-            lowbit_matmul(x, lin.weight.data, lin.weight_shape, lin.qtype, out=out, bias=lin.bias, accumulate=accumulate, norm=norm)
+        (tensor-parallel groups, unquantised or act-order linears) otherwise"""
+        if isinstance(lin, LowBitLinear) and lin.mp_group is None and not lin.act_order and lin.weight.data.device.type == "cuda" \
+                and (lin.bias is None or lin.bias.dtype == out.dtype):
+            lowbit_matmul(x, lin.weight.data, lin.weight_shape, lin.qtype, out=out, bias=lin.bias, accumulate=accumulate)
             self.launches_per_step += ggml.last_launch_count()
         elif isinstance(lin, LowBitLinear) and hasattr(lin.mp_group, "matmul_all_reduce") and not lin.act_order \
                 and lin.mp_group.fused_supported(x.shape[0], lin.out_len, lin.qtype):
@@ -153,10 +138,8 @@ class DecodeGraph:
         qkv2d, attn2d = self.qkv.view(B, -1), self.attn.view(B, -1)
         for i, layer in enumerate(core.layers):
             attn, mlp = layer.self_attn, layer.mlp
-            fused = self._norm_in_gemv(layer.input_layernorm, attn.qkv_proj)
-            if fused is None:
-                self._rms(layer.input_layernorm, self.h, self.xn)
-            self._linear(attn.qkv_proj, self.xn if fused is None else self.h, qkv2d, norm=fused)
+            self._rms(layer.input_layernorm, self.h, self.xn)
+            self._linear(attn.qkv_proj, self.xn, qkv2d)
             # cache_complete: the rows below the cache length and the length itself come from earlier steps, and every
             # step starts with an ordinarily launched kernel (the embedding lookup above) that nothing overtakes
             ggml.lowbit_decode_attention(self.qkv, self.Hq, self.Hkv, self.D, self.cos, self.sin, self.state,
@@ -164,30 +147,22 @@ class DecodeGraph:
                                          cache_complete=True)
             self.launches_per_step += ggml.last_launch_count()
             self._linear(attn.o_proj, attn2d, self.h, accumulate=True)
+            self._rms(layer.post_attention_layernorm, self.h, self.xn)
             if self.moe:
-                self._rms(layer.post_attention_layernorm, self.h, self.xn)
                 self._moe(mlp)
                 continue
             gate, up = mlp.gate_proj, mlp.up_proj
             if self.fuse_mlp and isinstance(gate, LowBitLinear) and isinstance(up, LowBitLinear) and gate.bias is None \
                     and up.bias is None and gate.mp_group is None and gate.qtype == up.qtype \
                     and gate.weight.data.device.type == "cuda":
-                # one launch for <= 8 sequences (the norm included); lowbit_mlp_cuda runs two matmuls and one
-                # activation kernel beyond
-                fused = self._norm_in_gemv(layer.post_attention_layernorm, gate, up)
-                if fused is None:
-                    self._rms(layer.post_attention_layernorm, self.h, self.xn)
-                mlp_forward(self.xn if fused is None else self.h, gate.weight.data, up.weight.data, B, self.H, gate.out_len,
-                            SILU, gate.qtype, out=self.act, norm=fused)
+                # one launch for <= 8 sequences; lowbit_mlp_cuda runs two matmuls and one activation kernel beyond
+                mlp_forward(self.xn, gate.weight.data, up.weight.data, B, self.H, gate.out_len, SILU, gate.qtype, out=self.act)
                 self.launches_per_step += ggml.last_launch_count()
             else:
-                self._rms(layer.post_attention_layernorm, self.h, self.xn)
                 self.act.copy_(mlp.act_fn(gate(self.xn)) * up(self.xn))
             self._linear(mlp.down_proj, self.act, self.h, accumulate=True)
-        fused = self._norm_in_gemv(core.norm, self.model.lm_head)
-        if fused is None:
-            self._rms(core.norm, self.h, self.xn)
-        self._linear(self.model.lm_head, self.xn if fused is None else self.h, self.logits, norm=fused)
+        self._rms(core.norm, self.h, self.xn)
+        self._linear(self.model.lm_head, self.xn, self.logits)
         ggml.lowbit_greedy_advance(self.logits, self.next_ids, self.tokens, self.state, st, self.suppress_ids)
         self.launches_per_step += 1
 

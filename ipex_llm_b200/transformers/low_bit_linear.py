@@ -221,13 +221,11 @@ def _get_workspace(device, need):
 
 
 def lowbit_matmul(x_2d: torch.Tensor, weight: torch.Tensor, weight_shape, qtype: int, out: torch.Tensor = None,
-                  bias: torch.Tensor = None, accumulate: bool = False, out_dtype=None, next_weight: torch.Tensor = None,
-                  norm=None):
+                  bias: torch.Tensor = None, accumulate: bool = False, out_dtype=None, next_weight: torch.Tensor = None):
     """x_2d [M,K] (fp32/fp16/bf16, CUDA) @ dequant(W [N,K], tiled device layout).T -> [M,N].
 
     The B200 twin of ``xe_linear.forward_new(x_2d, w, qtype, out_len)`` (LBL:704-708); ``out`` /
-    ``accumulate`` / ``bias`` expose the fused epilogue of the kernel.  ``norm = (weight, eps)``: x_2d is the
-    un-normalised input of an RMSNorm that the kernel applies while loading (M <= 8, half precision, N % 64 == 0).
+    ``accumulate`` / ``bias`` expose the fused epilogue of the kernel.
     """
     N, K = weight_shape
     M = x_2d.shape[0]
@@ -251,10 +249,6 @@ def lowbit_matmul(x_2d: torch.Tensor, weight: torch.Tensor, weight_shape, qtype:
     ws = _get_workspace(dev, need)
     if next_weight is not None:      # L2 prefetch hint: the weights the following matmul on this stream reads
         ggml.lowbit_hint_next_weights(ctypes.c_void_p(next_weight.data_ptr()), next_weight.numel() * next_weight.element_size())
-    if norm is not None:
-        invalidInputError(norm[0].dtype == x_2d.dtype and norm[0].numel() == K and norm[0].is_contiguous(),
-                          "the fused norm's weight must be a contiguous [K] tensor of the activation dtype")
-        ggml.lowbit_fuse_rms_norm(norm[0], norm[1])
     with torch.cuda.device(dev):
         ggml.lowbit_matmul_cuda(ctypes.c_void_p(w.data_ptr()), qtype, N, K,
                                 ctypes.c_void_p(x_2d.data_ptr()), _TORCH_TO_DT[x_2d.dtype], M,
@@ -269,7 +263,7 @@ GELU = 1
 
 
 def mlp_forward(x_2d: torch.Tensor, gate_weight: torch.Tensor, up_weight: torch.Tensor, M: int, K: int, N: int,
-                act: int, qtype: int, out: torch.Tensor = None, norm=None):
+                act: int, qtype: int, out: torch.Tensor = None):
     """``xe_linear.mlp_forward_xpu(x_2d, gate_w, up_w, M, K, N, act, qtype)`` (models/common.py:146-161):
     act(x . Wgate^T) * (x . Wup^T) -> [M, N] in the activation dtype.  Both weights are [N, K]
     in the tiled device layout; at decode sizes (M <= 8) one kernel streams both matrices."""
@@ -288,10 +282,6 @@ def mlp_forward(x_2d: torch.Tensor, gate_weight: torch.Tensor, up_weight: torch.
     ws = _get_workspace(dev, ggml.lowbit_mlp_workspace_size(N, K, M, dt))
     g = gate_weight.view(torch.uint8) if gate_weight.dtype != torch.uint8 else gate_weight
     u = up_weight.view(torch.uint8) if up_weight.dtype != torch.uint8 else up_weight
-    if norm is not None:                                  # (weight, eps) of an RMSNorm applied to x_2d inside the kernel, M <= 8
-        invalidInputError(norm[0].dtype == x_2d.dtype and norm[0].numel() == K and M <= 8,
-                          "the fused norm needs M <= 8 and a [K] weight of the activation dtype")
-        ggml.lowbit_fuse_rms_norm(norm[0], norm[1])
     with torch.cuda.device(dev):
         ggml.lowbit_mlp_cuda(ctypes.c_void_p(g.data_ptr()), ctypes.c_void_p(u.data_ptr()), qtype, N, K,
                              ctypes.c_void_p(x_2d.data_ptr()), dt, M, ctypes.c_void_p(out.data_ptr()),

@@ -177,91 +177,3 @@ def test_decode_attention_one_launch_equals_the_separate_kernels(native_lib, cud
         assert float((got.double() - exact).abs().max()) <= tol, P
         assert float((got.double() - want.double()).abs().max()) <= tol, P
     assert launches == {1}, launches                     # every case here fits the one-launch kernel
-
-
-# ------------------------------------------------------------------ RMSNorm inside the consuming GEMV
-def _tiled_weight(dev, rows, k, qtype, seed):
-    from ipex_llm_b200.ggml.quantize import ggml_tensor_qtype
-    from ipex_llm_b200.transformers import low_bit_linear as lbl
-    gen = torch.Generator(device=dev).manual_seed(seed)
-    w = torch.randn(rows, k, device=dev, generator=gen) * 0.05
-    q = ggml_tensor_qtype[qtype]
-    packed = lbl.ggml_convert_qtype(w, q, device=dev)
-    return lbl.ggml_q_format_convet_cpu2xpu(packed, rows * k, q, shape=(rows, k)), q
-
-
-@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
-@pytest.mark.parametrize("qtype", ["sym_int4", "asym_int4", "fp8_e5m2", "nf4"])
-@pytest.mark.parametrize("M,N,K", [(1, 12288, 4096), (1, 192, 1024), (3, 4096, 4096), (8, 1024, 2048), (5, 256, 16384)])
-def test_fused_rms_norm_gemv_equals_the_two_launches(native_lib, cuda_device, dtype, qtype, M, N, K):
-    """lowbit_fuse_rms_norm + lowbit_matmul_cuda on the raw rows == lowbit_rms_norm_cuda, then lowbit_matmul_cuda: the
-    prologue reproduces the stand-alone kernel's summation order, so the outputs carry the same bits"""
-    from ipex_llm_b200.transformers import low_bit_linear as lbl
-    ggml, dev = native_lib, cuda_device
-    if not ggml.lowbit_fuse_rms_norm_supported(lbl.ggml_tensor_qtype[qtype], N, K, M, dtype):
-        pytest.skip("format without a tensor-core codec")
-    w, q = _tiled_weight(dev, N, K, qtype, 11)
-    gen = torch.Generator(device=dev).manual_seed(12)
-    x = (torch.randn(M, K, device=dev, generator=gen) * 2.5).to(dtype)
-    nw = (1 + 0.2 * torch.randn(K, device=dev, generator=gen)).to(dtype)
-    eps = 1e-5
-    xn = torch.empty_like(x)
-    ggml.lowbit_rms_norm(x, nw, eps, xn, _st(dev))
-    for out_dtype in (dtype, torch.float32):
-        want = lbl.lowbit_matmul(xn, w, (N, K), q, out_dtype=out_dtype)
-        got = lbl.lowbit_matmul(x, w, (N, K), q, out_dtype=out_dtype, norm=(nw, eps))
-        assert ggml.last_launch_count() == 1
-        assert torch.equal(got, want), float((got.float() - want.float()).abs().max())
-    # the request is one-shot: the next call is an ordinary matmul of the raw rows
-    plain = lbl.lowbit_matmul(x, w, (N, K), q)
-    assert torch.equal(plain, lbl.lowbit_matmul(x, w, (N, K), q))
-    assert not torch.equal(plain.float(), want)
-    # bias and accumulate go through the same epilogue
-    bias = torch.randn(N, device=dev, generator=gen).to(dtype)
-    base = torch.randn(M, N, device=dev, generator=gen).to(dtype)
-    a, b = base.clone(), base.clone()
-    lbl.lowbit_matmul(xn, w, (N, K), q, out=a, bias=bias, accumulate=True)
-    lbl.lowbit_matmul(x, w, (N, K), q, out=b, bias=bias, accumulate=True, norm=(nw, eps))
-    assert torch.equal(a, b)
-
-
-@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
-@pytest.mark.parametrize("M", [1, 2, 7, 8])
-def test_fused_rms_norm_mlp_equals_the_two_launches(native_lib, cuda_device, dtype, M):
-    from ipex_llm_b200.transformers import low_bit_linear as lbl
-    ggml, dev = native_lib, cuda_device
-    K, N = 4096, 11008
-    wg, q = _tiled_weight(dev, N, K, "sym_int4", 21)
-    wu, _ = _tiled_weight(dev, N, K, "sym_int4", 22)
-    gen = torch.Generator(device=dev).manual_seed(23)
-    x = (torch.randn(M, K, device=dev, generator=gen) * 0.7).to(dtype)
-    nw = (1 + 0.2 * torch.randn(K, device=dev, generator=gen)).to(dtype)
-    xn = torch.empty_like(x)
-    ggml.lowbit_rms_norm(x, nw, 1e-6, xn, _st(dev))
-    want = torch.empty(M, N, device=dev, dtype=dtype)
-    got = torch.empty_like(want)
-    lbl.mlp_forward(xn, wg, wu, M, K, N, 0, q, out=want)
-    lbl.mlp_forward(x, wg, wu, M, K, N, 0, q, out=got, norm=(nw, 1e-6))
-    assert ggml.last_launch_count() == 1
-    assert torch.equal(got, want), float((got.float() - want.float()).abs().max())
-
-
-def test_fused_rms_norm_is_refused_where_it_cannot_run(native_lib, cuda_device):
-    """M > 8, fp32 rows or an output length off the 64-row grid: an argument error, and the request is dropped"""
-    from ipex_llm_b200.transformers import low_bit_linear as lbl
-    ggml, dev = native_lib, cuda_device
-    K = 1024
-    nw16 = torch.ones(K, device=dev, dtype=torch.float16)
-    for M, N, dt in [(9, 256, torch.float16), (40, 256, torch.float16), (2, 256, torch.float32), (2, 208, torch.float16)]:
-        w, q = _tiled_weight(dev, N, K, "sym_int4", 31)
-        x = torch.randn(M, K, device=dev).to(dt)
-        assert not ggml.lowbit_fuse_rms_norm_supported(q, N, K, M, dt)
-        with pytest.raises(Exception):
-            lbl.lowbit_matmul(x, w, (N, K), q, norm=(nw16.to(dt), 1e-5))
-        ref = lbl.lowbit_matmul(x, w, (N, K), q)              # nothing is left pending
-        assert torch.equal(ref, lbl.lowbit_matmul(x, w, (N, K), q))
-    # the two-matmul MLP route (M > 8) refuses it as well
-    wg, q = _tiled_weight(dev, 256, K, "sym_int4", 32)
-    x = torch.randn(12, K, device=dev).half()
-    with pytest.raises(Exception):
-        lbl.mlp_forward(x, wg, wg, 12, K, 256, 0, q, norm=(nw16, 1e-5))
