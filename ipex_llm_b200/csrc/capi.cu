@@ -168,7 +168,19 @@ static bool use_gemm(int qtype, int64_t n_rows, int64_t k, int64_t m, int x_dtyp
     return x_dtype != DT_F32 && m > max_m && gemm_tc_supported(qtype, n_rows, k);
 }
 
+// Batches between the GEMV's best range and a full 128-token tile take the tensor-core kernel with the operands swapped
+// (gemm_skinny_launch): weights rounded once to the activation dtype, the prefill kernel's precision contract.
+// Measured on 11008x4096 sym_int4: GEMV 12 us at M = 16 and 22 us at M = 32, this kernel 15.5 us for 9 <= M <= 32, 17-20 us
+// up to 64 (the split-K prefill kernel: 22-25 us), 29 us at 96-128 -- hence the window 17..64.
+// LOWBIT_SKINNY_MIN_M / LOWBIT_SKINNY_MAX_M (development) move the window; MIN_M above MAX_M switches the kernel off.
+static bool use_skinny(int qtype, int64_t n_rows, int64_t k, int64_t m, int x_dtype) {
+    static const int64_t min_m = [] { const char* e = getenv("LOWBIT_SKINNY_MIN_M"); return e ? (int64_t)atoi(e) : (int64_t)17; }();
+    static const int64_t max_m = [] { const char* e = getenv("LOWBIT_SKINNY_MAX_M"); return e ? (int64_t)atoi(e) : (int64_t)64; }();
+    return m >= min_m && m <= max_m && gemm_skinny_supported(qtype, n_rows, k, m, x_dtype);
+}
+
 size_t lowbit_matmul_workspace_size(int64_t n_rows, int64_t k, int64_t m, int x_dtype) {
+    if (use_skinny(B200_QT_SYM_INT4, n_rows, k, m, x_dtype)) return gemm_skinny_workspace_size(n_rows, k, m);
     if (use_gemm(B200_QT_SYM_INT4, n_rows, k, m, x_dtype)) return gemm_tc_workspace_size(n_rows, k, m, x_dtype);
     return gemv_workspace_size(n_rows, k, m, x_dtype);
 }
@@ -176,6 +188,9 @@ size_t lowbit_matmul_workspace_size(int64_t n_rows, int64_t k, int64_t m, int x_
 static int matmul_dispatch(const void* d_w, int qtype, int64_t n_rows, int64_t k, const void* d_x, int x_dtype, int64_t m,
                            void* d_y, int y_dtype, const void* d_bias, int accumulate, void* workspace, size_t workspace_bytes,
                            cudaStream_t st) {
+    if (use_skinny(qtype, n_rows, k, m, x_dtype))
+        return gemm_skinny_launch(d_w, qtype, n_rows, k, d_x, x_dtype, m, d_y, y_dtype, d_bias, accumulate, workspace,
+                                  workspace_bytes, st, gemv_get_pdl());
     if (use_gemm(qtype, n_rows, k, m, x_dtype)) {
         int64_t done = 0;
         return gemm_tc_launch(d_w, qtype, n_rows, k, d_x, x_dtype, m, d_y, y_dtype, d_bias, accumulate, workspace,

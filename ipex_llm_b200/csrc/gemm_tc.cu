@@ -76,6 +76,28 @@ __device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t adesc, uint64
         "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
         ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
 }
+// The same two for a whole warp in warp-uniform control flow: `leader` is true in one elected lane.  With every operand
+// computed identically by all lanes the compiler keeps descriptors and addresses in uniform registers; a single-lane
+// branch made it move every operand into a uniform register per instruction (~23 instructions and 45 ns per MMA).
+__device__ __forceinline__ void umma_f16_w(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate, uint32_t leader) {
+    asm volatile(
+        "{\n\t.reg .pred p, q;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "setp.ne.b32 q, %5, 0;\n\t"
+        "@q tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate), "r"(leader) : "memory");
+}
+__device__ __forceinline__ void umma_commit_w(uint32_t bar, uint32_t leader) {
+    asm volatile(
+        "{\n\t.reg .pred q;\n\t"
+        "setp.ne.b32 q, %1, 0;\n\t"
+        "@q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}" ::"r"(bar), "r"(leader) : "memory");
+}
+__device__ __forceinline__ uint32_t elect_leader() {
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+    return pred;
+}
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
 }
@@ -318,7 +340,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap xmap, const GemmArgs A) {
     auto tmem_empty = [&](int b) { return bars + (3 * kStages + 2 + b) * 8; };
     const uint32_t tmem_slot = bars + (3 * kStages + 4) * 8;
 
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    // the warp index through a shuffle: the compiler then treats everything derived from it as warp-uniform
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
     const uint32_t lut = bars + 256 + 4 * (lane & 7);
     if constexpr (E::kLutBytes > 0) E::fill_lut(smem_raw + (bars + 256 - smem_u32(smem_raw)), threadIdx.x, kThreads);   // visible after the __syncthreads below
     const int nb = (int)A.G.nb;
@@ -375,8 +398,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap xmap, const GemmArgs A) {
             }
         }
     } else if (warp == 1) {
-        // ================= MMA issuer =================
-        if (lane == 0) {
+        // ================= MMA issuer: the whole warp runs the loop, one elected lane issues (see umma_f16_w) =================
+        {
+            const uint32_t leader = elect_leader();
             // c_format F32 (1<<4), a/b format (0 f16, 1 bf16), both K-major, N = 128 (>>3 at bit 17), M = 128 (>>4 at bit 24)
             const uint32_t idesc = (1u << 4) | ((BF ? 1u : 0u) << 7) | ((BF ? 1u : 0u) << 10) | ((128u >> 3) << 17) | ((128u >> 4) << 24);
             int it = 0, ti = 0;
@@ -392,19 +416,17 @@ gemm_kernel(const __grid_constant__ CUtensorMap xmap, const GemmArgs A) {
                     mbar_wait(deq_bar(s), (uint32_t)(round & 1));
                     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                     const uint32_t st = base + s * STAGE;
-                    const uint32_t btile = st + MT * kTileBytesAB;
+                    const uint64_t ad0 = make_desc(st), bd0 = make_desc(st + MT * kTileBytesAB);
 #pragma unroll
                     for (int mt = 0; mt < MT; mt++) {
 #pragma unroll
-                        for (int k4 = 0; k4 < 4; k4++) {
-                            const uint64_t ad = make_desc(st + mt * kTileBytesAB + k4 * 32);
-                            const uint64_t bd = make_desc(btile + k4 * 32);
-                            umma_f16(acc + mt * 128, ad, bd, idesc, (kb > kb0 || k4 > 0) ? 1u : 0u);
-                        }
+                        for (int k4 = 0; k4 < 4; k4++)       // the address field counts 16-byte units
+                            umma_f16_w(acc + mt * 128, ad0 + (uint64_t)((mt * kTileBytesAB + k4 * 32) >> 4), bd0 + (uint64_t)((k4 * 32) >> 4), idesc,
+                                       (kb > kb0 || k4 > 0) ? 1u : 0u, leader);
                     }
-                    umma_commit(empty_bar(s));                  // stage reusable once these MMAs have read it
+                    umma_commit_w(empty_bar(s), leader);        // stage reusable once these MMAs have read it
                 }
-                umma_commit(tmem_full(buf));                     // this tile's accumulators are complete
+                umma_commit_w(tmem_full(buf), leader);           // this tile's accumulators are complete
             }
         }
     } else if (warp < 2 + kDeqWarps) {
@@ -552,6 +574,353 @@ static int launch_qt(bool bf, int mt, const CUtensorMap& map, const GemmArgs& A,
     return mt == 2 ? launch_one<QT, false, 2>(map, A, grid, st) : launch_one<QT, false, 1>(map, A, grid, st);
 }
 
+
+// ====================================================================================================================
+// Skinny variant: 9 <= M <= 128 activation rows (batched decode, short prefills).  The roles of the operands are swapped:
+// the EXPANDED WEIGHTS are the 128-row A operand and the tokens are the N dimension (16 / 32 / 64 / 128), so nothing is
+// padded to a 128-token tile, an activation stage is NTOK x 256 bytes and the accumulator is NTOK TMEM columns.
+//   * work = the linear sequence of (128-feature tile, PAIR of k-blocks) items, cut into gridDim.x contiguous ranges of
+//     equal length (stream-K): every SM expands the same number of blocks whatever the matrix shape; a range that crosses
+//     a tile boundary produces one partial result per tile it touches (fp32, in the workspace) and a second,
+//     programmatic-dependent launch adds a tile's partials in CTA order (deterministic) and applies bias / accumulate;
+//   * an item is 128 k: the barrier handshakes, the MMA thread's loop and the bulk copies are per item, and measured they,
+//     not the arithmetic, set the pace (0.34 us per handshake round with nothing else in the kernel);
+//   * warp 0 streams PACKED weights + the activation k-slices through a ring of stages (the bytes in flight keep HBM
+//     busy; the weights of the first round are requested before griddepcontrol.wait);
+//   * 16 dequant warps in two groups take alternate items; a group owns one 128 x 128 K-major 128B-swizzled A tile
+//     (two 16 KB atoms) and every warp expands its 16 rows of both k-blocks -- one group's barrier waits, LDS / STS
+//     latency and proxy fence overlap the other group's arithmetic;
+//   * warp 1 issues tcgen05.mma M = 128, N = NTOK, K = 16 (8 per item) into one of two TMEM accumulators; ONE commit per
+//     item frees both the stage (for the producer) and the group's A tile;  4 epilogue warps read TMEM (lane = feature,
+//     column = token).
+constexpr int kSkStagesMax = 12;
+constexpr int kSkDeqWarps = 16;
+constexpr int kSkThreads = 64 + 32 * kSkDeqWarps + 128;
+
+#ifdef LOWBIT_SK_TIMESTAMPS
+__device__ unsigned long long g_sk_ts[6][64];
+#define SKTS(row, it) do { if (blockIdx.x == 0 && lane == 0 && (it) < 64) { unsigned long long t_; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_)); g_sk_ts[row][it] = t_; } } while (0)
+#else
+#define SKTS(row, it) do { } while (0)
+#endif
+
+struct SkinnyArgs {
+    const uint8_t* w;
+    TiledGeom G;
+    int M;
+    float* part;             // [gridDim.x * max_seg][NTOK][128] fp32 partial tiles
+    int max_seg;
+    int pdl;
+    int dbg;                 // development (LOWBIT_SK_DBG): 1 no MMAs, 2 no expansion, 4 no activation loads, 8 no reduction
+};
+
+template <int QT, int NTOK> struct SkSmem {
+    static constexpr int kSuper = Smem<QT>::kSuper;
+    static constexpr int kAux = Expand<QT>::kHasMin ? 512 : 256;                // scales (+ minima) of the two k-blocks
+    static constexpr int kGroup = 2 * kSuper + kAux;                            // one 64-row group, two k-blocks
+    static constexpr int kX = NTOK * 256;                                       // two [NTOK][64] atoms
+    static constexpr int kStage = ((kX + 2 * kGroup + 1023) / 1024) * 1024;     // the x atoms sit first (1024-byte aligned)
+    static constexpr int kA = 2 * 2 * kTileBytesAB;                             // two groups x two atoms
+    static constexpr int kFree = 232448 - 1024 - kA - 512 - Expand<QT>::kLutBytes;
+    static constexpr int kFit = kFree / kStage < kSkStagesMax ? kFree / kStage : kSkStagesMax;
+    static constexpr int kStages = kFit & ~1;                                   // even: a stage always serves the same group
+    static constexpr int kTotal = 1024 + kA + kStages * kStage + 512 + Expand<QT>::kLutBytes;
+};
+
+template <int N> __device__ __forceinline__ void tmem_ld_cols(uint32_t taddr, float (&v)[N]);
+template <> __device__ __forceinline__ void tmem_ld_cols<32>(uint32_t taddr, float (&v)[32]) { tmem_ld32(taddr, v); }
+template <> __device__ __forceinline__ void tmem_ld_cols<16>(uint32_t taddr, float (&v)[16]) {
+    uint32_t r[16];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 16; i++) v[i] = __uint_as_float(r[i]);
+}
+
+template <int QT, bool BF, int NTOK>
+__global__ void __launch_bounds__(kSkThreads, 1)
+skinny_kernel(const __grid_constant__ CUtensorMap xmap, const SkinnyArgs A) {
+    using E = Expand<QT>;
+    using SM = SkSmem<QT, NTOK>;
+    constexpr int NS = SM::kStages, STAGE = SM::kStage;
+    static_assert(NS >= 2 && (NS & 1) == 0, "ring depth");
+    constexpr uint32_t ACC_COLS = NTOK, TMEM_COLS = 2 * NTOK < 32 ? 32 : 2 * NTOK;
+    extern __shared__ uint8_t smem_raw[];
+    const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t atiles = base, ring = base + SM::kA, bars = ring + NS * STAGE;
+    auto full_bar = [&](int s) { return bars + s * 8; };
+    auto done_bar = [&](int s) { return bars + (kSkStagesMax + s) * 8; };
+    auto afull_bar = [&](int q) { return bars + (2 * kSkStagesMax + q) * 8; };
+    auto tmem_full = [&](int b) { return bars + (2 * kSkStagesMax + 2 + b) * 8; };
+    auto tmem_empty = [&](int b) { return bars + (2 * kSkStagesMax + 4 + b) * 8; };
+    const uint32_t tmem_slot = bars + (2 * kSkStagesMax + 6) * 8;
+
+    // the warp index through a shuffle: the compiler then treats everything derived from it as warp-uniform
+    const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
+    if (A.pdl) asm volatile("griddepcontrol.launch_dependents;");
+    const uint32_t lut = bars + 512 + 4 * (lane & 7);
+    if constexpr (E::kLutBytes > 0) E::fill_lut(smem_raw + (bars + 512 - smem_u32(smem_raw)), threadIdx.x, kSkThreads);
+    const int nb = (int)A.G.nb, np = nb >> 1;                // k-blocks / pairs of k-blocks per tile (nb is even)
+    const int64_t total = (A.G.rows / kTileN) * (int64_t)np;
+    const int64_t i_begin = (int64_t)blockIdx.x * total / gridDim.x, i_end = (int64_t)(blockIdx.x + 1) * total / gridDim.x;
+    const int n_items = (int)(i_end - i_begin);
+    const int ft0 = (int)(i_begin / np), p_first = (int)(i_begin - (int64_t)ft0 * np);
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < NS; s++) { mbar_init(full_bar(s), 1); mbar_init(done_bar(s), 1); }
+        for (int q = 0; q < 2; q++) mbar_init(afull_bar(q), 32 * (kSkDeqWarps / 2));
+        for (int b = 0; b < 2; b++) { mbar_init(tmem_full(b), 1); mbar_init(tmem_empty(b), 128); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot), "r"(TMEM_COLS) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    uint32_t tmem_base;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+
+    if (warp == 0) {
+        // ================= producer =================
+        if (lane == 0) {
+            auto locate = [&](int it, int& ft, int& kb) {
+                int p = p_first + it;
+                ft = ft0;
+                while (p >= np) { p -= np; ft++; }
+                kb = 2 * p;
+            };
+            auto weights = [&](int it) {               // packed codes / scales / minima of both k-blocks into the stage
+                int ft, kb;
+                locate(it, ft, kb);
+                const int s = it % NS;
+                const uint32_t pk = ring + s * STAGE + SM::kX;
+                mbar_expect_tx(full_bar(s), ((A.dbg & 4) ? 0 : SM::kX) + 2 * SM::kGroup);
+#pragma unroll
+                for (int gi = 0; gi < 2; gi++) {
+                    const int64_t u = ((int64_t)ft * 2 + gi) * nb + kb;          // units kb and kb + 1 are adjacent in memory
+                    const uint32_t dst = pk + gi * SM::kGroup;
+                    bulk_g2s(dst, A.w + u * SM::kSuper, 2 * SM::kSuper, full_bar(s));
+                    bulk_g2s(dst + 2 * SM::kSuper, A.w + A.G.off_s + u * 128, 256, full_bar(s));
+                    if (E::kHasMin) bulk_g2s(dst + 2 * SM::kSuper + 256, A.w + A.G.off_m + u * 128, 256, full_bar(s));
+                }
+            };
+            auto acts = [&](int it) {                  // the k-slices of the activations: 2 x [NTOK tokens] x [64]
+                if (A.dbg & 4) return;
+                int ft, kb;
+                locate(it, ft, kb);
+                const int s = it % NS;
+                tma_load_2d(ring + s * STAGE, &xmap, kb * 64, 0, full_bar(s));
+                tma_load_2d(ring + s * STAGE + NTOK * 128, &xmap, kb * 64 + 64, 0, full_bar(s));
+            };
+            // the first round's weights do not depend on the previous kernel: they are on their way before the wait
+            const int first = n_items < NS ? n_items : NS;
+            for (int it = 0; it < first; it++) weights(it);
+            if (A.pdl) asm volatile("griddepcontrol.wait;" ::: "memory");
+            for (int it = 0; it < first; it++) acts(it);
+            for (int it = first; it < n_items; it++) {
+                const int s = it % NS;
+                mbar_wait(done_bar(s), (uint32_t)((it / NS - 1) & 1));
+                SKTS(0, it);
+                weights(it);
+                acts(it);
+            }
+        }
+    } else if (warp == 1) {
+        // ================= MMA issuer: the whole warp runs the loop, one elected lane issues =================
+        {
+            const uint32_t leader = elect_leader();
+            // c F32 (1<<4), a/b format (0 f16, 1 bf16), both K-major, N = NTOK (>>3 at bit 17), M = 128 (>>4 at bit 24)
+            const uint32_t idesc = (1u << 4) | ((BF ? 1u : 0u) << 7) | ((BF ? 1u : 0u) << 10) | (((uint32_t)NTOK >> 3) << 17) | ((128u >> 4) << 24);
+            int p = p_first, seg = 0;
+            bool fresh = true;
+            if (n_items > 0) {
+                mbar_wait(tmem_empty(0), 1u);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            }
+            for (int it = 0; it < n_items; it++) {
+                const int s = it % NS, q = it & 1;
+                mbar_wait(full_bar(s), (uint32_t)((it / NS) & 1));
+                mbar_wait(afull_bar(q), (uint32_t)((it >> 1) & 1));
+                SKTS(1, it);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const uint32_t acc = tmem_base + (uint32_t)(seg & 1) * ACC_COLS;
+                const uint64_t ad = make_desc(atiles + q * (2 * kTileBytesAB)), xd = make_desc(ring + s * STAGE);
+                if (!(A.dbg & 1)) {
+#pragma unroll
+                    for (int kk = 0; kk < 2; kk++)
+#pragma unroll
+                        for (int k4 = 0; k4 < 4; k4++)       // the address field counts 16-byte units
+                            umma_f16_w(acc, ad + (uint64_t)((kk * kTileBytesAB + k4 * 32) >> 4), xd + (uint64_t)((kk * NTOK * 128 + k4 * 32) >> 4),
+                                       idesc, (!fresh || kk > 0 || k4 > 0) ? 1u : 0u, leader);
+                }
+                fresh = false;
+                umma_commit_w(done_bar(s), leader);          // frees the stage (producer) and the group's A tile (dequant warps)
+                SKTS(2, it);
+                if (++p == np || it + 1 == n_items) {        // the tile (or this CTA's part of it) is complete
+                    umma_commit_w(tmem_full(seg & 1), leader);
+                    p = 0; seg++; fresh = true;
+                    if (it + 1 < n_items) {
+                        mbar_wait(tmem_empty(seg & 1), (uint32_t)(((seg >> 1) & 1) ^ 1));
+                        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                    }
+                }
+            }
+        }
+    } else if (warp < 2 + kSkDeqWarps) {
+        // ================= dequant warps: group q = (warp - 2) / 8 takes the items of its parity =================
+        const int q = (warp - 2) >> 3, w8 = (warp - 2) & 7;
+        const int dw = w8 & 3, gi = w8 >> 2;                 // tile r = dw of row group gi, both k-blocks
+        const int g = lane >> 2, t = lane & 3;
+        const int f_lo = 64 * gi + 16 * dw + g;
+        const uint32_t atile = atiles + q * (2 * kTileBytesAB);
+        const uint32_t row_lo0 = atile + (f_lo >> 3) * 1024 + (f_lo & 7) * 128;
+        for (int it = q; it < n_items; it += 2) {
+            const int s = it % NS;
+            mbar_wait(full_bar(s), (uint32_t)((it / NS) & 1));
+            if (it >= 2) mbar_wait(done_bar((it - 2) % NS), (uint32_t)(((it - 2) / NS) & 1));     // the MMAs that read the tile last
+            if (w8 == 0) SKTS(3, it);
+            const uint32_t grp = ring + s * STAGE + SM::kX + gi * SM::kGroup;
+            uint32_t dq[2], mq[2] = {0u, 0u};
+#pragma unroll
+            for (int kk = 0; kk < 2; kk++) {
+                asm volatile("ld.shared.u32 %0, [%1];" : "=r"(dq[kk]) : "r"(grp + 2 * SM::kSuper + kk * 128 + g * 16 + dw * 4));
+                if (E::kHasMin) asm volatile("ld.shared.u32 %0, [%1];" : "=r"(mq[kk]) : "r"(grp + 2 * SM::kSuper + 256 + kk * 128 + g * 16 + dw * 4));
+            }
+#pragma unroll
+            for (int kk = 0; kk < 2; kk++) {
+                if (A.dbg & 2) break;
+                const uint32_t codes = grp + kk * SM::kSuper + dw * E::kTileBytes;
+                const __half2 d2 = u2h(dq[kk]), m2 = u2h(mq[kk]);
+                const __half2 dlo = __low2half2(d2), dhi = __high2half2(d2);
+                const __half2 mlo = __low2half2(m2), mhi = __high2half2(m2);
+                const uint32_t row_lo = row_lo0 + kk * kTileBytesAB, row_hi = row_lo + 1024;
+#pragma unroll
+                for (int h = 0; h < 2; h++) {
+                    uint32_t va[4], vb[4];
+                    E::run(codes, lane, 2 * h, dlo, dhi, mlo, mhi, lut, va);
+                    E::run(codes, lane, 2 * h + 1, dlo, dhi, mlo, mhi, lut, vb);
+                    if (BF) {
+#pragma unroll
+                        for (int i = 0; i < 4; i++) { va[i] = h2_to_bf2(va[i]); vb[i] = h2_to_bf2(vb[i]); }
+                    }
+                    const uint32_t chunk = (uint32_t)((2 * t + h) ^ g) * 16;
+                    asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(row_lo + chunk), "r"(va[0]), "r"(va[2]), "r"(vb[0]), "r"(vb[2]) : "memory");
+                    asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(row_hi + chunk), "r"(va[1]), "r"(va[3]), "r"(vb[1]), "r"(vb[3]) : "memory");
+                }
+            }
+            if (w8 == 0) SKTS(4, it);
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            mbar_arrive(afull_bar(q));
+            if (w8 == 0) SKTS(5, it);
+        }
+    } else {
+        // ================= epilogue warps: TMEM lanes 32 * (warp % 4) .. + 31 = features, columns = tokens =================
+        const int quarter = warp & 3;
+        const int n_seg = n_items > 0 ? (int)((i_end - 1) / np) - ft0 + 1 : 0;
+        if (A.pdl) asm volatile("griddepcontrol.wait;" ::: "memory");      // the workspace may still be read by the previous reduction
+        for (int seg = 0; seg < n_seg; seg++) {
+            mbar_wait(tmem_full(seg & 1), (uint32_t)((seg >> 1) & 1));
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            float* dst = A.part + ((int64_t)blockIdx.x * A.max_seg + seg) * (NTOK * 128) + quarter * 32 + lane;
+            constexpr int CH = NTOK < 32 ? 16 : 32;
+#pragma unroll 1
+            for (int c = 0; c < NTOK; c += CH) {
+                float v[CH];
+                tmem_ld_cols<CH>(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)((seg & 1) * ACC_COLS + c), v);
+#pragma unroll
+                for (int j = 0; j < CH; j++)
+                    if (c + j < A.M) dst[(c + j) * 128] = v[j];          // a warp writes 128 contiguous bytes per token
+            }
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            mbar_arrive(tmem_empty(seg & 1));
+        }
+    }
+    __syncthreads();
+    if (warp == 1) {
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(TMEM_COLS) : "memory");
+    }
+}
+
+// y[token][feature] = sum over the CTAs whose range touches the feature's tile, in CTA order, + bias (+ y).
+// grid = (feature tiles, ceil(M / 8)); a block adds eight tokens of one tile, thread = feature.
+struct SkReduceArgs {
+    const float* part; int max_seg, grid, np, ntok, M;
+    int64_t total, n_cols;
+    void* y; int y_dtype; const void* bias; int accumulate; int pdl;
+};
+__global__ void __launch_bounds__(128) skinny_reduce_kernel(const SkReduceArgs A) {
+    if (A.pdl) {
+        asm volatile("griddepcontrol.launch_dependents;");
+        asm volatile("griddepcontrol.wait;" ::: "memory");
+    }
+    const int ft = blockIdx.x, f = threadIdx.x;
+    // CTA of item i = the largest c with c * total / grid <= i
+    auto cta_of = [&](int64_t i) { return (int)(((i + 1) * A.grid + A.total - 1) / A.total - 1); };
+    const int c_lo = cta_of((int64_t)ft * A.np), c_hi = cta_of((int64_t)(ft + 1) * A.np - 1);
+    const int t0 = blockIdx.y * 8;
+    float v[8];
+#pragma unroll
+    for (int j = 0; j < 8; j++) v[j] = 0.0f;
+    for (int c = c_lo; c <= c_hi; c++) {
+        const int seg = ft - (int)(((int64_t)c * A.total / A.grid) / A.np);
+        const float* src = A.part + ((int64_t)c * A.max_seg + seg) * (A.ntok * 128) + f;
+#pragma unroll
+        for (int j = 0; j < 8; j++)
+            if (t0 + j < A.M) v[j] += src[(t0 + j) * 128];
+    }
+    const int64_t col = (int64_t)ft * kTileN + f;
+    float b = 0.0f;
+    if (A.bias) b = A.y_dtype == DT_F32 ? ((const float*)A.bias)[col]
+                  : A.y_dtype == DT_F16 ? __half2float(((const __half*)A.bias)[col]) : __bfloat162float(((const __nv_bfloat16*)A.bias)[col]);
+#pragma unroll
+    for (int j = 0; j < 8; j++) {
+        if (t0 + j >= A.M) break;
+        const int64_t idx = (int64_t)(t0 + j) * A.n_cols + col;
+        const float r = v[j] + b;
+        if (A.y_dtype == DT_F32) { float* p = (float*)A.y + idx; *p = A.accumulate ? *p + r : r; }
+        else if (A.y_dtype == DT_F16) { __half* p = (__half*)A.y + idx; *p = __float2half_rn(A.accumulate ? __half2float(*p) + r : r); }
+        else { __nv_bfloat16* p = (__nv_bfloat16*)A.y + idx; *p = __float2bfloat16_rn(A.accumulate ? __bfloat162float(*p) + r : r); }
+    }
+}
+
+template <int QT, bool BF, int NTOK>
+static int sk_launch_one(const CUtensorMap& map, const SkinnyArgs& A, int grid, cudaStream_t st) {
+    constexpr int SMEM = SkSmem<QT, NTOK>::kTotal;
+    static bool configured_dev[64] = {};
+    int dev_id = 0;
+    cudaGetDevice(&dev_id);
+    bool& configured = configured_dev[dev_id & 63];
+    if (!configured) {
+        cudaFuncSetAttribute(skinny_kernel<QT, BF, NTOK>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM);
+        configured = true;
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)grid); cfg.blockDim = dim3(kSkThreads); cfg.dynamicSmemBytes = SMEM; cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = A.pdl ? 1 : 0;
+    cudaLaunchKernelEx(&cfg, skinny_kernel<QT, BF, NTOK>, map, A);
+    return 0;
+}
+template <int QT>
+static int sk_launch_qt(bool bf, int ntok, const CUtensorMap& map, const SkinnyArgs& A, int grid, cudaStream_t st) {
+#define SK_CASE(N) case N: return bf ? sk_launch_one<QT, true, N>(map, A, grid, st) : sk_launch_one<QT, false, N>(map, A, grid, st);
+    switch (ntok) { SK_CASE(16) SK_CASE(32) SK_CASE(64) SK_CASE(128) }
+#undef SK_CASE
+    return LB_ERR_ARG;
+}
+static int sk_ntok(int64_t m) { return m <= 16 ? 16 : m <= 32 ? 32 : m <= 64 ? 64 : 128; }
+static int sk_grid(int64_t total) { const int sms = sm_count(); return (int)(total < sms ? total : sms); }
+static int sk_max_seg(int64_t total, int grid, int64_t np) { return (int)(((total + grid - 1) / grid + np - 1) / np + 1); }
 }  // namespace gemmtc
 
 bool gemm_tc_supported(int qt, int64_t n_rows, int64_t k) {
@@ -659,6 +1028,74 @@ int gemm_tc_launch(const void* w, int qt, int64_t n_rows, int64_t k, const void*
         note_launch();
     }
     *n_done = n_main;
+    return check_launch();
+}
+
+#ifdef LOWBIT_SK_TIMESTAMPS
+extern "C" int lowbit_debug_skinny_timestamps(unsigned long long* out) {
+    return (int)cudaMemcpyFromSymbol(out, gemmtc::g_sk_ts, sizeof(gemmtc::g_sk_ts));
+}
+#endif
+// ---- skinny variant (9 <= m <= 128, fp16 / bf16 activations): see gemmtc::skinny_kernel
+bool gemm_skinny_supported(int qt, int64_t n_rows, int64_t k, int64_t m, int x_dtype) {
+    return (x_dtype == DT_F16 || x_dtype == DT_BF16) && m >= 1 && m <= 128 && gemm_tc_supported(qt, n_rows, k) && (n_rows % 128) == 0 &&
+           (k % 128) == 0;                                 // an item is a pair of k-blocks
+}
+size_t gemm_skinny_workspace_size(int64_t n_rows, int64_t k, int64_t m) {
+    using namespace gemmtc;
+    const int64_t np = k / 128, total = (n_rows / 128) * np;
+    const int grid = sk_grid(total);
+    return (size_t)grid * sk_max_seg(total, grid, np) * sk_ntok(m) * 128 * sizeof(float);
+}
+int gemm_skinny_launch(const void* w, int qt, int64_t n_rows, int64_t k, const void* x, int x_dtype, int64_t m, void* y, int y_dtype,
+                       const void* bias, int accumulate, void* workspace, size_t workspace_bytes, cudaStream_t st, int pdl) {
+    using namespace gemmtc;
+    qt = canon_qtype(qt);
+    if (!gemm_skinny_supported(qt, n_rows, k, m, x_dtype)) return LB_ERR_ARG;
+    EncodeTiledFn enc = encode_fn();
+    if (!enc) { set_error(LB_ERR_CUDA, "cuTensorMapEncodeTiled is not available from this driver"); return LB_ERR_CUDA; }
+    if (((uintptr_t)x & 15) || ((uintptr_t)w & 15)) return LB_ERR_ARG;
+    if (!workspace || workspace_bytes < gemm_skinny_workspace_size(n_rows, k, m)) return LB_ERR_WORKSPACE;
+    const bool bf = x_dtype == DT_BF16;
+    const int ntok = sk_ntok(m);
+    CUtensorMap map;
+    const cuuint64_t gdim[2] = {(cuuint64_t)k, (cuuint64_t)m};
+    const cuuint64_t gstride[1] = {(cuuint64_t)k * 2};
+    const cuuint32_t box[2] = {64, (cuuint32_t)ntok};
+    const cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(&map, bf ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(x), gdim,
+                     gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                     CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { set_error(LB_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d)", (int)r); return LB_ERR_CUDA; }
+    SkinnyArgs A;
+    A.w = (const uint8_t*)w; A.G = make_geom(n_rows, k, qt); A.M = (int)m;
+    const int64_t np = k / 128, total = (n_rows / 128) * np;
+    const int grid = sk_grid(total);
+    A.part = (float*)workspace; A.max_seg = sk_max_seg(total, grid, np); A.pdl = pdl;
+    { static const int dbg = [] { const char* e = getenv("LOWBIT_SK_DBG"); return e ? atoi(e) : 0; }(); A.dbg = dbg; }
+    int rc;
+    switch (qt) {
+        case QT_SYM_INT4:  rc = sk_launch_qt<QT_SYM_INT4>(bf, ntok, map, A, grid, st); break;
+        case QT_NF4:       rc = sk_launch_qt<QT_NF4>(bf, ntok, map, A, grid, st); break;
+        case QT_ASYM_INT4: rc = sk_launch_qt<QT_ASYM_INT4>(bf, ntok, map, A, grid, st); break;
+        case QT_FP8_E4M3:  rc = sk_launch_qt<QT_FP8_E4M3>(bf, ntok, map, A, grid, st); break;
+        case QT_FP8_E5M2:  rc = sk_launch_qt<QT_FP8_E5M2>(bf, ntok, map, A, grid, st); break;
+        case QT_FP6:       rc = sk_launch_qt<QT_FP6>(bf, ntok, map, A, grid, st); break;
+        default: return LB_ERR_ARG;
+    }
+    if (rc) return rc;
+    note_launch();
+    SkReduceArgs R;
+    R.part = A.part; R.max_seg = A.max_seg; R.grid = grid; R.np = (int)np; R.ntok = ntok; R.M = (int)m;
+    R.total = total; R.n_cols = n_rows; R.y = y; R.y_dtype = y_dtype; R.bias = bias; R.accumulate = accumulate; R.pdl = pdl;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(n_rows / 128), (unsigned)((m + 7) / 8)); cfg.blockDim = dim3(128); cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at; cfg.numAttrs = pdl ? 1 : 0;
+    if (!(A.dbg & 8)) cudaLaunchKernelEx(&cfg, skinny_reduce_kernel, R);
+    note_launch();
     return check_launch();
 }
 

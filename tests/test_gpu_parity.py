@@ -210,8 +210,8 @@ def test_gemv_shapes(lbl, cuda_device, qtype, shape, M):
     y = run_matmul(lbl, cuda_device, packed, shape, qtype, x_t, out_dtype=torch.float32).cpu().numpy()
     y64 = oracle.matmul_f64(packed, shape, qtype, x)
     bound = matmul_bound(packed, shape, qtype, x)
-    if M > 32 and N % 128 == 0:
-        bound = bound * 500          # tensor-core GEMM path: weights rounded once to fp16 (1e-3 * sum|x w|)
+    if M >= 17 and N % 128 == 0:
+        bound = bound * 500          # tensor-core paths (17..64 rows: skinny kernel, beyond: prefill GEMM): weights rounded once to fp16 (1e-3 * sum|x w|)
     assert (np.abs(y - y64) <= bound).all(), float((np.abs(y - y64) / bound).max())
 
 
@@ -379,6 +379,60 @@ def test_gemm_small_batch_split_k(lbl, cuda_device, shape, M, qtype):
     lbl.lowbit_matmul(x_t, tiled, (N, K), qid(qtype), out=out, bias=bias, accumulate=True)
     want2 = y + bias.float() + res.float()
     assert bool(((out.float() - want2).abs() <= 1e-3 * want2.abs() + 1e-3).all())
+
+
+@pytest.mark.parametrize("qtype", ["sym_int4", "asym_int4", "nf4", "fp8_e4m3", "fp8_e5m2", "fp6"])
+@pytest.mark.parametrize("xdt,tol", [(torch.float16, 1e-3), (torch.bfloat16, 8e-3)])
+@pytest.mark.parametrize("shape,M", [((256, 512), 17), ((384, 1024), 32), ((128 * 9, 128 * 5), 33), ((256, 128), 64), ((4096, 4096), 24)])
+def test_gemm_skinny_matches_oracle(lbl, cuda_device, qtype, xdt, tol, shape, M):
+    """17..64 rows go to the tensor-core kernel with the operands swapped (weights = the 128-row operand, tokens = N,
+    stream-K ranges + a reduction launch): the prefill kernel's contract, |diff| <= tol * sum|x w|; shapes with fewer
+    items than SMs, ranges that cross several tiles (9 tiles x 5 pairs over 45 CTAs... ) and a full-size layer"""
+    rng = np.random.default_rng(1250 + M)
+    N, K = shape
+    packed = oracle.quantize(rand_w(rng, N, K), qtype)
+    x_t = torch.from_numpy(rng.standard_normal((M, K)).astype(np.float32)).to(xdt)
+    x = x_t.float().numpy()
+    y = run_matmul(lbl, cuda_device, packed, shape, qtype, x_t, out_dtype=torch.float32)
+    assert lbl.ggml.last_launch_count() == 2
+    y = y.cpu().numpy()
+    y64 = oracle.matmul_f64(packed, shape, qtype, x)
+    wd = np.abs(oracle.dequantize(packed, shape, qtype)).astype(np.float64)
+    bound = tol * (np.abs(x).astype(np.float64) @ wd.T) + 1e-30
+    assert np.isfinite(y).all()
+    assert (np.abs(y - y64) <= bound).all(), float((np.abs(y - y64) / bound).max())
+
+
+def test_gemm_skinny_epilogue_window_and_determinism(lbl, cuda_device):
+    rng = np.random.default_rng(1260)
+    N, K, M = 1024, 2048, 40
+    packed = oracle.quantize(rand_w(rng, N, K), "sym_int4")
+    x_t = torch.from_numpy(rng.standard_normal((M, K)).astype(np.float32)).half()
+    base = run_matmul(lbl, cuda_device, packed, (N, K), "sym_int4", x_t, out_dtype=torch.float32)
+    again = run_matmul(lbl, cuda_device, packed, (N, K), "sym_int4", x_t, out_dtype=torch.float32)
+    assert torch.equal(base, again)                                  # partial sums are added in CTA order
+    bias = torch.from_numpy(rng.standard_normal(N).astype(np.float32)).to(cuda_device)
+    yb = run_matmul(lbl, cuda_device, packed, (N, K), "sym_int4", x_t, out_dtype=torch.float32, bias=bias)
+    torch.testing.assert_close(yb, base + bias, rtol=0, atol=1e-5)
+    res = torch.from_numpy(rng.standard_normal((M, N)).astype(np.float32)).to(cuda_device)
+    out = res.clone()
+    run_matmul(lbl, cuda_device, packed, (N, K), "sym_int4", x_t, out=out, accumulate=True)
+    torch.testing.assert_close(out, res + base, rtol=0, atol=1e-5)
+    for dt in (torch.float16, torch.bfloat16):
+        yh = run_matmul(lbl, cuda_device, packed, (N, K), "sym_int4", x_t, out_dtype=dt)
+        torch.testing.assert_close(yh.float(), base.to(dt).float(), rtol=0, atol=0)
+    # the window: 16 rows stay on the GEMV (one launch, exact), 17 take this kernel, fp32 rows never do, nor does a K that
+    # is not a whole number of k-block pairs
+    run_matmul(lbl, cuda_device, packed, (N, K), "sym_int4", x_t[:16], out_dtype=torch.float32)
+    assert lbl.ggml.last_launch_count() == 1
+    small = run_matmul(lbl, cuda_device, packed, (N, K), "sym_int4", x_t[:17], out_dtype=torch.float32)
+    assert lbl.ggml.last_launch_count() == 2
+    torch.testing.assert_close(small, base[:17], rtol=1e-6, atol=1e-6)     # a row's result does not depend on the batch around it
+    y32 = run_matmul(lbl, cuda_device, packed, (N, K), "sym_int4", x_t[:24].float(), out_dtype=torch.float32)
+    torch.testing.assert_close(y32, base[:24], rtol=2e-3, atol=2e-3)
+    odd = oracle.quantize(rand_w(rng, 256, 192), "sym_int4")
+    run_matmul(lbl, cuda_device, odd, (256, 192), "sym_int4", x_t[:24, :192].contiguous(), out_dtype=torch.float32)
+    assert lbl.ggml.last_launch_count() == 1
 
 
 def test_gemm_prefill_epilogue_and_module(lbl, cuda_device):
