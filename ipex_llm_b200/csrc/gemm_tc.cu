@@ -9,13 +9,16 @@
 //   warp 0   producer : TMA 2-D tiled loads (128B swizzle) of the activation tile(s) and 1-D TMA
 //                       bulk copies of the PACKED weights of the tile's two 64-row groups (codes +
 //                       fp16 scales [+ minima]) -- weights cross HBM->SM at 4.25-8.25 bits each;
-//   warps 2-5 dequant : expand the packed codes to fp16/bf16 (magic-number trick / cvt, scale
-//                       applied with one fused multiply-add per pair) straight into the K-major
-//                       128B-swizzled B operand tile in shared memory; later the same warps are
-//                       the epilogue (tcgen05.ld of their 32 TMEM lanes -> bias/accumulate -> store);
-//   warp 1   MMA      : one elected thread issues tcgen05.mma.cta_group::1.kind::f16 (M=128, N=128,
-//                       K=16; 4 per k-block per token sub-tile), accumulators in TMEM (128*MT columns),
-//                       tcgen05.commit releases the stage and finally signals the epilogue.
+//   warps 2-17 dequant: two groups of 8 take alternate k-blocks and expand the packed codes to fp16/bf16
+//                       (magic-number trick / cvt, scale applied with one multiply per pair) straight into
+//                       the K-major 128B-swizzled B operand tile in shared memory;
+//   warps 18-21       : epilogue (tcgen05.ld of their 32 TMEM lanes -> bias/accumulate -> 16-byte stores);
+//   warp 1   MMA      : the whole warp runs the issue loop in warp-uniform control flow and one elected lane
+//                       issues tcgen05.mma.cta_group::1.kind::f16 (M=128, N=128, K=16; 4 per k-block per token
+//                       sub-tile), accumulators in TMEM (128*MT columns), tcgen05.commit releases the stage and
+//                       finally signals the epilogue.  (Round 2: with the loop inside a single-lane branch every
+//                       operand was moved into a uniform register per instruction, ~45 ns per MMA: the issue
+//                       thread, not shared-memory bandwidth, set the pace -- 1017 -> 1262 TFLOP/s.)
 // The expanded weights never touch HBM; both token sub-tiles reuse one expanded B tile.
 // Weight rounding: (code - offset) * d is rounded ONCE to fp16 (11 bits) -- or to bf16 when the
 // activations are bf16 -- which is the precision contract of this path (tests: 2e-3 * sum|x w|).
@@ -30,7 +33,8 @@ namespace lowbit {
 namespace gemmtc {
 
 constexpr int kMaxStages = 6;        // pipeline depth = as many stages as fit in 227 KB, at most this
-constexpr int kDeqWarps = 8;         // dequant (then epilogue) warps: one 16x64 tile of the 128x64 B stage each
+constexpr int kDeqWarps = 16;        // dequant warps in two groups of 8 that take alternate k-blocks; a warp expands one 16x64 tile of the
+                                     // 128x64 B stage (one group alone: 0.4 us per k-block, the pace of the whole kernel at <= 128-token tiles)
 constexpr int kEpiWarps = 4;         // epilogue warps: one per TMEM lane quarter (warp index % 4 must be 0..3 in order)
 constexpr int kThreads = 64 + 32 * kDeqWarps + 32 * kEpiWarps;
 constexpr int kTileN = 128;          // features per CTA (two 64-row groups)
@@ -144,19 +148,23 @@ template <int OFFSET> struct Expand4 {          // sym_int4 (OFFSET 1) / asym_in
         uint32_t w;
         asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w) : "r"(codes + lane * 16 + s * 4));
         const uint32_t w2 = w >> 8;
-        const __half2 k1024 = __floats2half2_rn(1024.0f, 1024.0f), k16th = __floats2half2_rn(0.0625f, 0.0625f);
-        const __half2 k64 = __floats2half2_rn(64.0f, 64.0f);
+        const __half2 k16th = __floats2half2_rn(0.0625f, 0.0625f);
         // 0x6400 | n = 1024 + n ; 0x6400 | (n << 4) = 1024 + 16 n  (exact in fp16)
-        const __half2 v0 = __hsub2(u2h(and_or(w, 0x000f000fu, 0x64006400u)), k1024);                 // n
-        const __half2 v1 = __hfma2(u2h(and_or(w, 0x00f000f0u, 0x64006400u)), k16th, __hneg2(k64));   // n
-        const __half2 v2 = __hsub2(u2h(and_or(w2, 0x000f000fu, 0x64006400u)), k1024);
-        const __half2 v3 = __hfma2(u2h(and_or(w2, 0x00f000f0u, 0x64006400u)), k16th, __hneg2(k64));
         if (OFFSET == 1) {
-            // (n - 8) * d: n - 8 is exact, the product is rounded once
-            const __half2 k8 = __floats2half2_rn(8.0f, 8.0f);
-            out[0] = h2u(__hmul2(__hsub2(v0, k8), dlo)); out[1] = h2u(__hmul2(__hsub2(v1, k8), dhi));
-            out[2] = h2u(__hmul2(__hsub2(v2, k8), dlo)); out[3] = h2u(__hmul2(__hsub2(v3, k8), dhi));
+            // n - 8 straight from the magic number (exact): one subtraction / one fma per pair, then the product, rounded once
+            const __half2 k1032 = __floats2half2_rn(1032.0f, 1032.0f), km72 = __floats2half2_rn(-72.0f, -72.0f);
+            const __half2 v0 = __hsub2(u2h(and_or(w, 0x000f000fu, 0x64006400u)), k1032);
+            const __half2 v1 = __hfma2(u2h(and_or(w, 0x00f000f0u, 0x64006400u)), k16th, km72);
+            const __half2 v2 = __hsub2(u2h(and_or(w2, 0x000f000fu, 0x64006400u)), k1032);
+            const __half2 v3 = __hfma2(u2h(and_or(w2, 0x00f000f0u, 0x64006400u)), k16th, km72);
+            out[0] = h2u(__hmul2(v0, dlo)); out[1] = h2u(__hmul2(v1, dhi));
+            out[2] = h2u(__hmul2(v2, dlo)); out[3] = h2u(__hmul2(v3, dhi));
         } else {
+            const __half2 k1024 = __floats2half2_rn(1024.0f, 1024.0f), km64 = __floats2half2_rn(-64.0f, -64.0f);
+            const __half2 v0 = __hsub2(u2h(and_or(w, 0x000f000fu, 0x64006400u)), k1024);                 // n
+            const __half2 v1 = __hfma2(u2h(and_or(w, 0x00f000f0u, 0x64006400u)), k16th, km64);           // n
+            const __half2 v2 = __hsub2(u2h(and_or(w2, 0x000f000fu, 0x64006400u)), k1024);
+            const __half2 v3 = __hfma2(u2h(and_or(w2, 0x00f000f0u, 0x64006400u)), k16th, km64);
             out[0] = h2u(__hfma2(v0, dlo, mlo)); out[1] = h2u(__hfma2(v1, dhi, mhi));
             out[2] = h2u(__hfma2(v2, dlo, mlo)); out[3] = h2u(__hfma2(v3, dhi, mhi));
         }
@@ -320,7 +328,7 @@ __device__ __forceinline__ void store_vals(const GemmArgs& A, int64_t token, int
 // grid = (N / 128 feature tiles, ceil(M / (128*MT)) token tiles)
 // Persistent: grid = min(units, SMs) CTAs; CTA c takes units c, c + grid, ... in token-tile-major order (the
 // CTAs running at one moment share the token tile's activations in L2 and stream different weights).
-// Warp roles: 0 TMA producer, 1 MMA issuer (owns TMEM), 2..9 dequant, 10..13 epilogue.  The accumulators
+// Warp roles: 0 TMA producer, 1 MMA issuer (owns TMEM), 2..17 dequant, 18..21 epilogue.  The accumulators
 // are double buffered in TMEM (2 x 128*MT columns), so the epilogue of tile i overlaps the main loop of i+1.
 template <int QT, bool BF, int MT>
 __global__ void __launch_bounds__(kThreads, 1)
@@ -355,7 +363,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap xmap, const GemmArgs A) {
     constexpr uint32_t TMEM_COLS = 2 * ACC_COLS;       // 256 or 512 (powers of two)
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < kStages; s++) { mbar_init(full_bar(s), 1); mbar_init(deq_bar(s), 32 * kDeqWarps); mbar_init(empty_bar(s), 1); }
+        for (int s = 0; s < kStages; s++) { mbar_init(full_bar(s), 1); mbar_init(deq_bar(s), 32 * (kDeqWarps / 2)); mbar_init(empty_bar(s), 1); }
         for (int b = 0; b < 2; b++) { mbar_init(tmem_full(b), 1); mbar_init(tmem_empty(b), 32 * kEpiWarps); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -430,14 +438,16 @@ gemm_kernel(const __grid_constant__ CUtensorMap xmap, const GemmArgs A) {
             }
         }
     } else if (warp < 2 + kDeqWarps) {
-        // ================= dequant warps =================
-        const int dw = (warp - 2) & 3;                       // tile r = dw of row group gi = (warp - 2) / 4
-        const int gi = (warp - 2) >> 2;
+        // ================= dequant warps: group (warp - 2) / 8 takes the k-iterations of its parity =================
+        const int grp_id = (warp - 2) >> 3;
+        const int dw = (warp - 2) & 3;                       // tile r = dw of row group gi
+        const int gi = ((warp - 2) >> 2) & 1;
         const int g = lane >> 2, t = lane & 3;
         int it = 0;
         for (int unit = blockIdx.x; unit < n_units; unit += gridDim.x) {
             const int kb0 = kb_begin(unit / n_tiles), kb1 = kb_begin(unit / n_tiles + 1);
             for (int kb = kb0; kb < kb1; kb++, it++) {
+                if ((it & 1) != grp_id) continue;
                 const int s = it % kStages, round = it / kStages;
                 mbar_wait(full_bar(s), (uint32_t)(round & 1));
                 const uint32_t st = base + s * STAGE;

@@ -372,8 +372,13 @@ __device__ __forceinline__ float ld_dsmem_f32(uint32_t local_addr, uint32_t rank
 // MODE 1 / 2 are the two launches of the mixture-of-experts decode (see GemvArgs): 1 = one routed
 // expert per blockIdx.z (used with NM = 2 for gate/up), 2 = the routed experts' down projections
 // concatenated along K, each slot's sums weighted by its routing weight.
+// resident CTAs per SM the register budget allows: 6 (80 registers) for one token; the 2..8-token kernels carry twice the
+// accumulators and spilled at 80 -- 5 (102 registers) measured 7-9 % faster at M = 4 / 8 than 6, and than 4
+#ifndef LOWBIT_GEMV_ACC4_CTAS
+#define LOWBIT_GEMV_ACC4_CTAS 5
+#endif
 template <int QT, bool BF, int NS, int NT, int ACC, int NM, int MODE>
-__global__ void __launch_bounds__(GEMV_WARPS * 32, (NT == 1 && NS == 1) ? (Codec<QT, BF>::kLutBytes ? 4 : 6) : 1)
+__global__ void __launch_bounds__(GEMV_WARPS * 32, (NT == 1 && NS == 1) ? (Codec<QT, BF>::kLutBytes ? 4 : (ACC == 4 ? LOWBIT_GEMV_ACC4_CTAS : 6)) : 1)
 gemv_kernel(const GemvArgs A) {
     using C = Codec<QT, BF>;
     using S = Staging<QT, BF>;

@@ -200,6 +200,15 @@ def reshape_lm_head_input(x):
 
 
 GEMV_MAX_M = 32   # rows of x the HBM-bound GEMV kernel takes in one pass (gemv_args.h)
+SKINNY_MIN_M, SKINNY_MAX_M = 17, 64   # half-precision batches in this window take the skinny tensor-core kernel (capi.cu use_skinny)
+
+
+def takes_tensor_core_path(M: int, N: int, K: int, x_dtype) -> bool:
+    """whether lowbit_matmul runs this shape on the tcgen05 kernels (weights rounded once to the activation dtype:
+    the prefill precision contract) rather than on the GEMV (exact up to fp32 summation order)"""
+    if x_dtype == torch.float32 or N % 128 or K % 64 or N < 128:
+        return False
+    return M > GEMV_MAX_M or (SKINNY_MIN_M <= M <= SKINNY_MAX_M and K % 128 == 0)
 
 
 def use_batch_forward(x: torch.Tensor, qtype: int, output_len: int):

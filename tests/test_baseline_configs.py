@@ -46,7 +46,7 @@ def check_matmul(lbl, dev, tiled, dense, shape, qtype, M, xdt=torch.float16, see
     xd = x.double()
     want = xd @ dense.T
     mag = xd.abs() @ dense.abs().T
-    gemm = M > lbl.GEMV_MAX_M and shape[0] % 128 == 0
+    gemm = lbl.takes_tensor_core_path(M, shape[0], shape[1], xdt)
     rel = 1e-3 if gemm else (2.6e-4 if qtype == "nf4" else 2e-6)
     if gemm and xdt != torch.float16:
         rel = 8e-3
