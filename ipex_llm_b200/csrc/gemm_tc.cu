@@ -121,6 +121,11 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
     for (int i = 0; i < 32; i++) v[i] = __uint_as_float(r[i]);
 }
 
+__device__ __forceinline__ uint4 lds128(uint32_t a) {
+    uint4 r;
+    asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "r"(a));
+    return r;
+}
 __device__ __forceinline__ uint32_t h2u(__half2 h) { return *reinterpret_cast<uint32_t*>(&h); }
 __device__ __forceinline__ __half2 u2h(uint32_t u) { return *reinterpret_cast<__half2*>(&u); }
 __device__ __forceinline__ uint32_t h2_to_bf2(uint32_t h) {
@@ -143,10 +148,12 @@ template <int OFFSET> struct Expand4 {          // sym_int4 (OFFSET 1) / asym_in
     static constexpr int kTileBytes = 512;
     static constexpr bool kHasMin = OFFSET == 2;
     static constexpr int kLutBytes = 0;
-    __device__ static __forceinline__ void run(uint32_t codes, int lane, int s, __half2 dlo, __half2 dhi, __half2 mlo,
+    // the lane's 16 bytes of the tile in one conflict-free LDS.128 (four LDS.32 at a 16-byte lane stride cost 4 wavefronts each)
+    struct Codes { uint4 q; };
+    __device__ static __forceinline__ void load(uint32_t codes, int lane, Codes& c) { c.q = lds128(codes + lane * 16); }
+    __device__ static __forceinline__ void run(const Codes& c, int s, __half2 dlo, __half2 dhi, __half2 mlo,
                                                __half2 mhi, uint32_t, uint32_t (&out)[4]) {
-        uint32_t w;
-        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w) : "r"(codes + lane * 16 + s * 4));
+        const uint32_t w = s == 0 ? c.q.x : s == 1 ? c.q.y : s == 2 ? c.q.z : c.q.w;
         const uint32_t w2 = w >> 8;
         const __half2 k16th = __floats2half2_rn(0.0625f, 0.0625f);
         // 0x6400 | n = 1024 + n ; 0x6400 | (n << 4) = 1024 + 16 n  (exact in fp16)
@@ -186,11 +193,14 @@ template <int QT> struct Expand8 {
         return h;
     }
     static constexpr int kLutBytes = 0;
-    __device__ static __forceinline__ void run(uint32_t codes, int lane, int s, __half2 dlo, __half2 dhi, __half2, __half2,
+    struct Codes { uint4 q0, q1; };
+    __device__ static __forceinline__ void load(uint32_t codes, int lane, Codes& c) {
+        c.q0 = lds128(codes + lane * 16); c.q1 = lds128(codes + 512 + lane * 16);
+    }
+    __device__ static __forceinline__ void run(const Codes& c, int s, __half2 dlo, __half2 dhi, __half2, __half2,
                                                uint32_t, uint32_t (&out)[4]) {
-        uint32_t w0, w1;
-        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w0) : "r"(codes + lane * 16 + s * 4));
-        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w1) : "r"(codes + 512 + lane * 16 + s * 4));
+        const uint32_t w0 = s == 0 ? c.q0.x : s == 1 ? c.q0.y : s == 2 ? c.q0.z : c.q0.w;
+        const uint32_t w1 = s == 0 ? c.q1.x : s == 1 ? c.q1.y : s == 2 ? c.q1.z : c.q1.w;
         out[0] = h2u(__hmul2(u2h(pair(w0, 0)), dlo)); out[1] = h2u(__hmul2(u2h(pair(w1, 0)), dhi));
         out[2] = h2u(__hmul2(u2h(pair(w0, 1)), dlo)); out[3] = h2u(__hmul2(u2h(pair(w1, 1)), dhi));
     }
@@ -207,14 +217,15 @@ template <> struct Expand<QT_FP6> {
         return h;
     }
     static constexpr int kLutBytes = 0;
-    __device__ static __forceinline__ void run(uint32_t codes, int lane, int s, __half2 dlo, __half2 dhi, __half2, __half2,
+    struct Codes { uint4 lo; uint2 hi; };
+    __device__ static __forceinline__ void load(uint32_t codes, int lane, Codes& c) {
+        c.lo = lds128(codes + lane * 16);
+        asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(c.hi.x), "=r"(c.hi.y) : "r"(codes + 512 + lane * 8));
+    }
+    __device__ static __forceinline__ void run(const Codes& c, int s, __half2 dlo, __half2 dhi, __half2, __half2,
                                                uint32_t, uint32_t (&out)[4]) {
         const int u = s >> 1;
-        uint32_t l0, l1, h0, h1;
-        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(l0) : "r"(codes + lane * 16 + u * 4));
-        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(l1) : "r"(codes + lane * 16 + 8 + u * 4));
-        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(h0) : "r"(codes + 512 + lane * 8));
-        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(h1) : "r"(codes + 512 + lane * 8 + 4));
+        const uint32_t l0 = u ? c.lo.y : c.lo.x, l1 = u ? c.lo.w : c.lo.z, h0 = c.hi.x, h1 = c.hi.y;
         const uint32_t sh = (s & 1) ? 4u : 0u;
         const uint32_t e0 = ((l0 >> sh) & 0x0f0f0f0fu) | (((h0 >> (2 * s)) & 0x03030303u) << 4);
         const uint32_t e1 = ((l1 >> sh) & 0x0f0f0f0fu) | (((h1 >> (2 * s)) & 0x03030303u) << 4);
@@ -226,26 +237,31 @@ template <> struct Expand<QT_FP6> {
 };
 
 // nf4: byte b of the lane's word s is the code pair of out[b] (tilednf4_pos); a 256-entry table of
-// fp16 pairs of NormalFloat values, 8 copies per entry (copy = lane % 8), sits in shared memory.
+// fp16 pairs of NormalFloat values sits in shared memory, 128 bytes per entry = one 4-byte slot per lane, so that no two
+// lanes of a lookup meet in a bank (the first layout, 8 slots per entry, cost 3.1 wavefronts per LDS -- see the GEMV codec).
 template <> struct Expand<QT_NF4> {
     static constexpr int kTileBytes = 512;
     static constexpr bool kHasMin = false;
-    static constexpr int kLutBytes = 8192;
+    static constexpr int kLutBytes = 256 * 128;
     __device__ static __forceinline__ void fill_lut(uint8_t* lut, int tid, int nthreads) {
         for (int e = tid; e < 256; e += nthreads) {
             const uint32_t v = h2u(__floats2half2_rn(kNF4Table[e & 15], kNF4Table[e >> 4]));
-            uint4* dst = reinterpret_cast<uint4*>(lut + e * 32);
-            dst[0] = make_uint4(v, v, v, v); dst[1] = make_uint4(v, v, v, v);
+            uint4* dst = reinterpret_cast<uint4*>(lut + e * 128);
+#pragma unroll
+            for (int c = 0; c < 8; c++) dst[c] = make_uint4(v, v, v, v);
         }
     }
-    __device__ static __forceinline__ void run(uint32_t codes, int lane, int s, __half2 dlo, __half2 dhi, __half2, __half2,
+    struct Codes { uint4 q; };
+    __device__ static __forceinline__ void load(uint32_t codes, int lane, Codes& c) { c.q = lds128(codes + lane * 16); }
+    // lut = table address + 4 * lane
+    __device__ static __forceinline__ void run(const Codes& c, int s, __half2 dlo, __half2 dhi, __half2, __half2,
                                                uint32_t lut, uint32_t (&out)[4]) {
-        uint32_t w, v0, v1, v2, v3;
-        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w) : "r"(codes + lane * 16 + s * 4));
-        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v0) : "r"(lut + ((w << 5) & 0x1fe0u)));
-        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v1) : "r"(lut + ((w >> 3) & 0x1fe0u)));
-        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v2) : "r"(lut + ((w >> 11) & 0x1fe0u)));
-        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v3) : "r"(lut + ((w >> 19) & 0x1fe0u)));
+        const uint32_t w = s == 0 ? c.q.x : s == 1 ? c.q.y : s == 2 ? c.q.z : c.q.w;
+        uint32_t v0, v1, v2, v3;
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v0) : "r"(lut + __byte_perm(w, 0u, 0x4440u) * 128u));
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v1) : "r"(lut + __byte_perm(w, 0u, 0x4441u) * 128u));
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v2) : "r"(lut + __byte_perm(w, 0u, 0x4442u) * 128u));
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v3) : "r"(lut + __byte_perm(w, 0u, 0x4443u) * 128u));
         out[0] = h2u(__hmul2(u2h(v0), dlo)); out[1] = h2u(__hmul2(u2h(v1), dhi));
         out[2] = h2u(__hmul2(u2h(v2), dlo)); out[3] = h2u(__hmul2(u2h(v3), dhi));
     }
@@ -350,7 +366,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap xmap, const GemmArgs A) {
 
     // the warp index through a shuffle: the compiler then treats everything derived from it as warp-uniform
     const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
-    const uint32_t lut = bars + 256 + 4 * (lane & 7);
+    const uint32_t lut = bars + 256 + 4 * lane;
     if constexpr (E::kLutBytes > 0) E::fill_lut(smem_raw + (bars + 256 - smem_u32(smem_raw)), threadIdx.x, kThreads);   // visible after the __syncthreads below
     const int nb = (int)A.G.nb;
     const int n_ftiles = (int)(A.G.rows / kTileN);
@@ -447,9 +463,12 @@ gemm_kernel(const __grid_constant__ CUtensorMap xmap, const GemmArgs A) {
         for (int unit = blockIdx.x; unit < n_units; unit += gridDim.x) {
             const int kb0 = kb_begin(unit / n_tiles), kb1 = kb_begin(unit / n_tiles + 1);
             for (int kb = kb0; kb < kb1; kb++, it++) {
-                if ((it & 1) != grp_id) continue;
                 const int s = it % kStages, round = it / kStages;
+                // both groups wait for every stage, also the other group's: with an odd ring depth a stage alternates
+                // between the groups, and a warp that skipped a phase of full_bar(s) could take the parity of the phase
+                // before last for the one it is waiting for (parity waits are only safe one phase behind)
                 mbar_wait(full_bar(s), (uint32_t)(round & 1));
+                if ((it & 1) != grp_id) continue;
                 const uint32_t st = base + s * STAGE;
                 const uint32_t btile = st + MT * kTileBytesAB;
                 const uint32_t pk = st + (MT + 1) * kTileBytesAB;
@@ -465,11 +484,13 @@ gemm_kernel(const __grid_constant__ CUtensorMap xmap, const GemmArgs A) {
                 const int f_lo = 64 * gi + 16 * dw + g;
                 const uint32_t row_lo = btile + (f_lo >> 3) * 1024 + (f_lo & 7) * 128;
                 const uint32_t row_hi = row_lo + 1024;      // f + 8: next 8-row group, same row inside it
+                typename E::Codes cw;
+                E::load(codes, lane, cw);
 #pragma unroll
                 for (int q = 0; q < 2; q++) {               // k-steps 2q, 2q+1 -> one 16-byte chunk per row
                     uint32_t a[4], b[4];
-                    E::run(codes, lane, 2 * q, dlo, dhi, mlo, mhi, lut, a);
-                    E::run(codes, lane, 2 * q + 1, dlo, dhi, mlo, mhi, lut, b);
+                    E::run(cw, 2 * q, dlo, dhi, mlo, mhi, lut, a);
+                    E::run(cw, 2 * q + 1, dlo, dhi, mlo, mhi, lut, b);
                     if (BF) {
 #pragma unroll
                         for (int i = 0; i < 4; i++) { a[i] = h2_to_bf2(a[i]); b[i] = h2_to_bf2(b[i]); }
@@ -673,7 +694,7 @@ skinny_kernel(const __grid_constant__ CUtensorMap xmap, const SkinnyArgs A) {
     // the warp index through a shuffle: the compiler then treats everything derived from it as warp-uniform
     const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
     if (A.pdl) asm volatile("griddepcontrol.launch_dependents;");
-    const uint32_t lut = bars + 512 + 4 * (lane & 7);
+    const uint32_t lut = bars + 512 + 4 * lane;
     if constexpr (E::kLutBytes > 0) E::fill_lut(smem_raw + (bars + 512 - smem_u32(smem_raw)), threadIdx.x, kSkThreads);
     const int nb = (int)A.G.nb, np = nb >> 1;                // k-blocks / pairs of k-blocks per tile (nb is even)
     const int64_t total = (A.G.rows / kTileN) * (int64_t)np;
@@ -811,11 +832,13 @@ skinny_kernel(const __grid_constant__ CUtensorMap xmap, const SkinnyArgs A) {
                 const __half2 dlo = __low2half2(d2), dhi = __high2half2(d2);
                 const __half2 mlo = __low2half2(m2), mhi = __high2half2(m2);
                 const uint32_t row_lo = row_lo0 + kk * kTileBytesAB, row_hi = row_lo + 1024;
+                typename E::Codes cw;
+                E::load(codes, lane, cw);
 #pragma unroll
                 for (int h = 0; h < 2; h++) {
                     uint32_t va[4], vb[4];
-                    E::run(codes, lane, 2 * h, dlo, dhi, mlo, mhi, lut, va);
-                    E::run(codes, lane, 2 * h + 1, dlo, dhi, mlo, mhi, lut, vb);
+                    E::run(cw, 2 * h, dlo, dhi, mlo, mhi, lut, va);
+                    E::run(cw, 2 * h + 1, dlo, dhi, mlo, mhi, lut, vb);
                     if (BF) {
 #pragma unroll
                         for (int i = 0; i < 4; i++) { va[i] = h2_to_bf2(va[i]); vb[i] = h2_to_bf2(vb[i]); }

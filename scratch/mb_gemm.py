@@ -25,4 +25,4 @@ for M in (64,128,512,2048):
     bench(4096,4096,M)
 for M in (512,2048):
     bench(11008,4096,M); bench(4096,11008,M); bench(12288,4096,M)
-bench(11008,4096,2048,qt=3); bench(11008,4096,2048,qt=15); bench(11008,4096,2048,qt=29); bench(11008,4096,2048,xdt=torch.bfloat16)
+bench(11008,4096,2048,qt=3); bench(11008,4096,2048,qt=10); bench(11008,4096,2048,qt=15); bench(11008,4096,2048,qt=29); bench(11008,4096,2048,xdt=torch.bfloat16)

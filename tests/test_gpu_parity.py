@@ -435,6 +435,26 @@ def test_gemm_skinny_epilogue_window_and_determinism(lbl, cuda_device):
     assert lbl.ggml.last_launch_count() == 1
 
 
+@pytest.mark.timeout(300)
+@pytest.mark.parametrize("qtype,M", [("fp8_e4m3", 1024), ("sym_int4", 512), ("fp6", 300)])
+def test_gemm_prefill_repeatable_with_odd_ring_depth(lbl, cuda_device, qtype, M):
+    """8-bit weights at 256-token tiles leave room for three stages: a stage then alternates between the two dequant groups,
+    and a warp that waited only for its own items could mistake an old phase of the stage's barrier for the new one
+    (parity waits are safe one phase behind, no more).  Fifty launches over a long K must give the same bits every time."""
+    rng = np.random.default_rng(1350)
+    N, K = 1024, 11008
+    tiled = lbl.FP4Params(torch.from_numpy(rand_w(rng, N, K)).to(cuda_device), qtype=qid(qtype)).to(cuda_device).data
+    x_t = torch.from_numpy(rng.standard_normal((M, K)).astype(np.float32)).half().to(cuda_device)
+    first = lbl.lowbit_matmul(x_t, tiled, (N, K), qid(qtype), out_dtype=torch.float32)
+    wd = lbl.dequantize_device_layout(tiled, (N, K), qid(qtype)).double()
+    want = x_t.double() @ wd.T
+    bound = 1e-3 * (x_t.double().abs() @ wd.abs().T) + 1e-30
+    assert bool(((first.double() - want).abs() <= bound).all())
+    for _ in range(50):
+        again = lbl.lowbit_matmul(x_t, tiled, (N, K), qid(qtype), out_dtype=torch.float32)
+        assert torch.equal(first, again)
+
+
 def test_gemm_prefill_epilogue_and_module(lbl, cuda_device):
     rng = np.random.default_rng(1300)
     N, K, M = 256, 512, 96
