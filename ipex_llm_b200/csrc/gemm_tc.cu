@@ -1031,8 +1031,10 @@ int gemm_tc_launch(const void* w, int qt, int64_t n_rows, int64_t k, const void*
     if (m > 128) {
         const int64_t sms = sm_count();
         const int64_t c2 = (n_main / 128) * ((m + 255) / 256), c1 = (n_main / 128) * ((m + 127) / 128);
-        const int64_t t2 = (c2 + sms - 1) / sms * 2, t1 = (c1 + sms - 1) / sms;
-        mt = 4 * t2 <= 5 * t1 ? 2 : 1;      // a 128-token tile re-reads the weights twice as often: ~25 % slower per token
+        // rounds of the grid x time per k-block of a unit: measured 0.46 us for a 256-token unit (one expansion serves two
+        // token sub-tiles) against 0.33 us for a 128-token one
+        const int64_t t2 = (c2 + sms - 1) / sms * 14, t1 = (c1 + sms - 1) / sms * 10;
+        mt = t2 <= t1 ? 2 : 1;
     }
     const int64_t n_tiles = (n_main / 128) * ((m + 128 * mt - 1) / (128 * mt));
     A.ksplit = m <= 128 ? pick_ksplit(n_tiles, k / 64, m, n_main) : 1;      // one token tile: few output tiles
