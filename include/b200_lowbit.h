@@ -277,8 +277,10 @@ size_t lowbit_matmul_workspace_size(int64_t n_rows, int64_t k, int64_t m, int x_
  * device.  The NULL mode is for ONE stream per device and must not be used under stream capture: calls are
  * serialised on the host only (two streams would race on the buffer on the GPU), and growing the buffer
  * synchronises the device and reallocates.
- * Any M >= 1.  fp16 / bf16 activations: M <= 32 runs the HBM-bound GEMV kernel, larger M the tensor-core GEMM
- * (activations and expanded weights enter the MMA as fp16 / bf16, fp32 accumulation: about 1e-3 * sum|x w|).
+ * Any M >= 1.  fp16 / bf16 activations: M <= 16 runs the HBM-bound GEMV kernel (so does 17 <= M <= 32 when n_rows is
+ * not a multiple of 128 or k not of 128), larger M the tensor-core kernels -- 17..64 rows the "skinny" one with the
+ * weights as the 128-row operand, beyond that the prefill GEMM (activations and expanded weights enter the MMA as
+ * fp16 / bf16, fp32 accumulation: about 1e-3 * sum|x w|); both may use a second, reduction launch.
  * fp32 activations: always the GEMV (chunks of 32 rows), which keeps them to 2^-24 -- the fp32-in / fp32-out
  * contract of ggml_compute_forward_mul_mat_q_fp32; cast to fp16 first to trade that precision for the GEMM,
  * as the reference's XPU path does (LBL:700-705). */
