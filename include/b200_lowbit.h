@@ -292,8 +292,8 @@ int lowbit_matmul_cuda(const void* d_w, int qtype, int64_t n_rows, int64_t k,
 /* Fused MLP front half: y[M][N] = act(x . Wgate^T) * (x . Wup^T) -- the XPU op
  * `xe_linear.mlp_forward_xpu(x_2d, gate_w, up_w, M, K, N, act, qtype)` called from fuse_mlp_base
  * (transformers/models/common.py:146-161; act ids from models/utils.py: SILU 0, GELU 1).
- * d_w_gate / d_w_up: two [N][K] weights of the SAME qtype in the device layout.  For M <= 8, N a
- * multiple of 64 and a tensor-core qtype this is ONE kernel launch that streams both matrices once
+ * d_w_gate / d_w_up: two [N][K] weights of the SAME qtype in the device layout.  For M <= 8 (M <= 16 with fp16 /
+ * bf16 activations), N a multiple of 64 and a tensor-core qtype this is ONE kernel launch that streams both matrices once
  * and never writes the two intermediate vectors; otherwise it runs the two matmuls into fp32
  * scratch and one elementwise kernel (same result up to fp32 rounding of the intermediates).
  * workspace: NULL (library-owned) or lowbit_mlp_workspace_size() bytes. */

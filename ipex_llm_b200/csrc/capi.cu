@@ -237,7 +237,7 @@ int lowbit_mlp_cuda(const void* d_w_gate, const void* d_w_up, int qtype, int64_t
     if (m == 0 || n_rows == 0) return LB_OK;
     if (act != 0 && act != 1) { set_error(LB_ERR_ARG, "lowbit_mlp_cuda: act must be 0 (SILU) or 1 (GELU), got %d", act); return LB_ERR_ARG; }
     if (!d_w_gate || !d_w_up || !d_x || !d_y || m < 0 || n_rows < 0) { set_error(LB_ERR_ARG, "lowbit_mlp_cuda: null pointer or negative size"); return LB_ERR_ARG; }
-    const bool fused = gemv_mlp_fused_supported(qtype, n_rows, k, m);
+    const bool fused = gemv_mlp_fused_supported(qtype, n_rows, k, m, x_dtype);
     const size_t base = (lowbit_matmul_workspace_size(n_rows, k, m, x_dtype) + 255) / 256 * 256;
     const size_t need = base + (fused ? 0 : 2 * (size_t)m * n_rows * sizeof(float));
     std::unique_lock<std::mutex> lk(g_mu, std::defer_lock);

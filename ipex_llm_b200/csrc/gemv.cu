@@ -126,9 +126,11 @@ int act_mul_launch(const float* gate, const float* up, void* y, int y_dtype, int
     return check_launch();
 }
 
-bool gemv_mlp_fused_supported(int qt, int64_t n_rows, int64_t k, int64_t m) {
+// up to 8 rows of any activation dtype; 9..16 rows in half precision (two n-tiles; fp32 rows would need three planes of each)
+bool gemv_mlp_fused_supported(int qt, int64_t n_rows, int64_t k, int64_t m, int x_dtype) {
     qt = canon_qtype(qt);
-    return supported(qt) && has_mma_codec(qt) && n_rows > 0 && n_rows % RG_ROWS == 0 && k > 0 && k % QK == 0 && m >= 1 && m <= 8;
+    return supported(qt) && has_mma_codec(qt) && n_rows > 0 && n_rows % RG_ROWS == 0 && k > 0 && k % QK == 0 && m >= 1 &&
+           (m <= 8 || (m <= 16 && x_dtype != DT_F32));
 }
 
 int gemv_launch(const void* w, int qt, int64_t n_rows, int64_t k, const void* x, int x_dtype, int64_t m,
@@ -146,7 +148,7 @@ int gemv_launch_ex(const void* w, const void* w2, int act, int qt, int64_t n_row
     t_push = GemvPush{};
     // fused all-reduce: one pass (m <= 32), every row in the tensor-core part
     if (push.world > 0 && (w2 || m > 8 * GEMV_MAX_NT || !has_mma_codec(qt) || n_rows % RG_ROWS)) return LB_ERR_ARG;
-    if (w2 && (!gemv_mlp_fused_supported(qt, n_rows, k, m) || ((uintptr_t)w2 & 15) || bias || accumulate)) return LB_ERR_ARG;
+    if (w2 && (!gemv_mlp_fused_supported(qt, n_rows, k, m, x_dtype) || ((uintptr_t)w2 & 15) || bias || accumulate)) return LB_ERR_ARG;
     if (!supported(qt) || k <= 0 || k % QK || n_rows <= 0 || m <= 0) return LB_ERR_ARG;
     if (x_dtype < 0 || x_dtype > 2 || y_dtype < 0 || y_dtype > 2) return LB_ERR_ARG;
     if (((uintptr_t)w & 15) || ((uintptr_t)x & 15)) return LB_ERR_ARG;        // TMA bulk / 128-bit loads

@@ -1147,6 +1147,7 @@ static void launch_nt(int m, int64_t groups, int64_t nb, const GemvArgs& A, cuda
         cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 4, 4, 1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448);
         cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 1, 2, 2, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448);
         cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 1, 4, 2, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448);
+        if constexpr (NS == 1) cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 2, 4, 2, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448);
         cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 1, 2, 2, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448);
         cudaFuncSetAttribute(gemv_kernel<QT, BF, NS, 1, 2, 1, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448);
         configured = true;
@@ -1159,7 +1160,14 @@ static void launch_nt(int m, int64_t groups, int64_t nb, const GemvArgs& A, cuda
         launch_kernel(gemv_kernel<QT, BF, NS, 1, 2, 1, 2>, SG::smem_bytes(1, 2, 1), groups, nb * A.n_seg, A, st, cache[7]);
         return;
     }
-    if (A.w2) {                          // fused MLP: M <= 8 only (the host falls back otherwise)
+    if (A.w2) {                          // fused MLP: M <= 8, and 9..16 half-precision rows (the host falls back otherwise)
+        if constexpr (NS == 1) {
+            if (m > 8) {
+                static int cache_nt2[8] = {-1, -1, -1, -1, -1, -1, -1, -1};
+                launch_kernel(gemv_kernel<QT, BF, NS, 2, 4, 2, 0>, SG::smem_bytes(2, 4, 2), groups, nb, A, st, cache_nt2);
+                return;
+            }
+        }
         if (m == 1) launch_kernel(gemv_kernel<QT, BF, NS, 1, 2, 2, 0>, SG::smem_bytes(1, 2, 2), groups, nb, A, st, cache[4]);
         else launch_kernel(gemv_kernel<QT, BF, NS, 1, 4, 2, 0>, SG::smem_bytes(1, 4, 2, SG::live_t(1, 4, m)), groups, nb, A, st,
                            cache_tl[1][SG::live_t(1, 4, m) - 1], 1, SG::smem_bytes(1, 4, 2, 4, true), &cache_ring[1]);

@@ -51,7 +51,7 @@ int gemv_launch(const void* w, int qt, int64_t n_rows, int64_t k, const void* x,
 int gemv_launch_ex(const void* w, const void* w2, int act, int qt, int64_t n_rows, int64_t k, const void* x, int x_dtype,
                    int64_t m, void* y, int y_dtype, const void* bias, int accumulate, void* workspace,
                    size_t workspace_bytes, cudaStream_t st);
-bool gemv_mlp_fused_supported(int qt, int64_t n_rows, int64_t k, int64_t m);
+bool gemv_mlp_fused_supported(int qt, int64_t n_rows, int64_t k, int64_t m, int x_dtype);
 int act_mul_launch(const float* gate, const float* up, void* y, int y_dtype, int64_t n, int act, cudaStream_t st);
 
 // one-token mixture-of-experts (reference xe_linear.moe_forward_vec)

@@ -61,7 +61,7 @@ def mlp_expect(pg, pu, shape, qtype, x, act, xdt=None):
 
 @pytest.mark.parametrize("qtype", ["sym_int4", "asym_int4", "fp8_e4m3", "fp8_e5m2", "fp6", "nf4"])
 @pytest.mark.parametrize("xdt", [torch.float16, torch.bfloat16, torch.float32])
-@pytest.mark.parametrize("M,act", [(1, 0), (4, 1), (8, 0)])
+@pytest.mark.parametrize("M,act", [(1, 0), (4, 1), (8, 0), (12, 0), (16, 1)])
 def test_mlp_fused_matches_oracle(lbl, cuda_device, qtype, xdt, M, act):
     rng = np.random.default_rng(4100 + M)
     N, K = 192, 1024
@@ -73,6 +73,9 @@ def test_mlp_fused_matches_oracle(lbl, cuda_device, qtype, xdt, M, act):
     out = torch.empty((M, N), dtype=torch.float32, device=cuda_device)
     lbl.mlp_forward(x_t.to(cuda_device), to_tiled(lbl, cuda_device, pg, (N, K), qtype),
                     to_tiled(lbl, cuda_device, pu, (N, K), qtype), M, K, N, act, qid(qtype), out=out)
+    # one launch up to 8 rows, and up to 16 in half precision (two n-tiles)
+    if xdt != torch.float32:                           # (fp32 rows add the launch that splits them into bf16 planes)
+        assert lbl.ggml.last_launch_count() == 1
     want, tol = mlp_expect(pg, pu, (N, K), qtype, x, act, xdt)
     got = out.cpu().numpy().astype(np.float64)
     assert (np.abs(got - want) <= tol).all(), float((np.abs(got - want) / tol).max())
