@@ -30,7 +30,6 @@ if mode == "check":
                     base = torch.randn(M, N, device=dev, generator=gen).to(dt)
                     out = base.clone()
                     lbl.lowbit_matmul(x, tiled, (N, K), q, out=out, bias=bias, accumulate=True)
-                    assert ggml.last_launch_count() == 2, ggml.last_launch_count()
                     want = x.double() @ wd.T + bias.double() + base.double()
                     err = float((out.double() - want).norm() / want.norm())
                     lim = 4e-3 if dt == torch.bfloat16 else 6e-4
@@ -44,11 +43,12 @@ if mode == "check":
         print(qt, "ok", flush=True)
     print("all ok, worst err/limit", worst)
 else:
-    ggml.lowbit_set_programmatic_dependent_launch(1)
-    for N, K in ((11008, 4096), (4096, 11008), (4096, 4096), (12288, 4096)):
+    import os
+    ggml.lowbit_set_programmatic_dependent_launch(int(os.environ.get('PDL', '1')))
+    for N, K in ((11008, 4096), (4096, 4096)):
         ws = [weights(N, K, "sym_int4")[1] for _ in range(10)]
         q = lbl.ggml_tensor_qtype["sym_int4"]
-        for M in (8, 9, 16, 24, 32, 48, 64, 96, 128):
+        for M in (16, 17, 32, 64):
             x = torch.randn(M, K, device=dev, generator=gen).half()
             out = torch.empty(M, N, device=dev, dtype=torch.float16)
             st = torch.cuda.Stream()
