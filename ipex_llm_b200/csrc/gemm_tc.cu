@@ -97,6 +97,20 @@ __device__ __forceinline__ void umma_commit_w(uint32_t bar, uint32_t leader) {
         "setp.ne.b32 q, %1, 0;\n\t"
         "@q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}" ::"r"(bar), "r"(leader) : "memory");
 }
+__device__ __forceinline__ void mbar_expect_tx_w(uint32_t bar, uint32_t bytes, uint32_t leader) {
+    asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.b32 q, %2, 0;\n\t@q mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n\t}"
+                 ::"r"(bar), "r"(bytes), "r"(leader) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s_w(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar, uint32_t leader) {
+    asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.b32 q, %4, 0;\n\t"
+                 "@q cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n\t}"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar), "r"(leader) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d_w(uint32_t dst, const CUtensorMap* map, int c0, int c1, uint32_t bar, uint32_t leader) {
+    asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.b32 q, %5, 0;\n\t"
+                 "@q cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];\n\t}"
+                 ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(bar), "r"(leader) : "memory");
+}
 __device__ __forceinline__ uint32_t elect_leader() {
     uint32_t pred;
     asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
@@ -394,8 +408,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap xmap, const GemmArgs A) {
     asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
 
     if (warp == 0) {
-        // ================= producer =================
-        if (lane == 0) {
+        // ================= producer: the whole warp runs the loop, one elected lane issues the copies (see umma_f16_w) =================
+        {
+            const uint32_t leader = elect_leader();
             int it = 0;                                              // k-iterations issued so far (all tiles)
             for (int unit = blockIdx.x; unit < n_units; unit += gridDim.x) {
                 const int tile = unit % n_tiles, ks = unit / n_tiles;
@@ -406,17 +421,17 @@ gemm_kernel(const __grid_constant__ CUtensorMap xmap, const GemmArgs A) {
                     const int s = it % kStages, round = it / kStages;
                     mbar_wait(empty_bar(s), (uint32_t)((round & 1) ^ 1));
                     const uint32_t st = base + s * STAGE;
-                    mbar_expect_tx(full_bar(s), MT * kTileBytesAB + 2 * SM::kPackedGroup);
+                    mbar_expect_tx_w(full_bar(s), MT * kTileBytesAB + 2 * SM::kPackedGroup, leader);
 #pragma unroll
-                    for (int mt = 0; mt < MT; mt++) tma_load_2d(st + mt * kTileBytesAB, &xmap, kb * 64, m0 + mt * 128, full_bar(s));
+                    for (int mt = 0; mt < MT; mt++) tma_load_2d_w(st + mt * kTileBytesAB, &xmap, kb * 64, m0 + mt * 128, full_bar(s), leader);
                     const uint32_t pk = st + (MT + 1) * kTileBytesAB;
 #pragma unroll
                     for (int gi = 0; gi < 2; gi++) {
                         const int64_t u = (rg0 + gi) * nb + kb;
                         const uint32_t dst = pk + gi * SM::kPackedGroup;
-                        bulk_g2s(dst, A.w + u * SM::kSuper, SM::kSuper, full_bar(s));
-                        bulk_g2s(dst + SM::kSuper, A.w + A.G.off_s + u * 128, 128, full_bar(s));
-                        if (E::kHasMin) bulk_g2s(dst + SM::kSuper + 128, A.w + A.G.off_m + u * 128, 128, full_bar(s));
+                        bulk_g2s_w(dst, A.w + u * SM::kSuper, SM::kSuper, full_bar(s), leader);
+                        bulk_g2s_w(dst + SM::kSuper, A.w + A.G.off_s + u * 128, 128, full_bar(s), leader);
+                        if (E::kHasMin) bulk_g2s_w(dst + SM::kSuper + 128, A.w + A.G.off_m + u * 128, 128, full_bar(s), leader);
                     }
                 }
             }
@@ -719,8 +734,9 @@ skinny_kernel(const __grid_constant__ CUtensorMap xmap, const SkinnyArgs A) {
     asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
 
     if (warp == 0) {
-        // ================= producer =================
-        if (lane == 0) {
+        // ================= producer: the whole warp runs the loop, one elected lane issues the copies =================
+        {
+            const uint32_t leader = elect_leader();
             auto locate = [&](int it, int& ft, int& kb) {
                 int p = p_first + it;
                 ft = ft0;
@@ -732,14 +748,14 @@ skinny_kernel(const __grid_constant__ CUtensorMap xmap, const SkinnyArgs A) {
                 locate(it, ft, kb);
                 const int s = it % NS;
                 const uint32_t pk = ring + s * STAGE + SM::kX;
-                mbar_expect_tx(full_bar(s), ((A.dbg & 4) ? 0 : SM::kX) + 2 * SM::kGroup);
+                mbar_expect_tx_w(full_bar(s), ((A.dbg & 4) ? 0 : SM::kX) + 2 * SM::kGroup, leader);
 #pragma unroll
                 for (int gi = 0; gi < 2; gi++) {
                     const int64_t u = ((int64_t)ft * 2 + gi) * nb + kb;          // units kb and kb + 1 are adjacent in memory
                     const uint32_t dst = pk + gi * SM::kGroup;
-                    bulk_g2s(dst, A.w + u * SM::kSuper, 2 * SM::kSuper, full_bar(s));
-                    bulk_g2s(dst + 2 * SM::kSuper, A.w + A.G.off_s + u * 128, 256, full_bar(s));
-                    if (E::kHasMin) bulk_g2s(dst + 2 * SM::kSuper + 256, A.w + A.G.off_m + u * 128, 256, full_bar(s));
+                    bulk_g2s_w(dst, A.w + u * SM::kSuper, 2 * SM::kSuper, full_bar(s), leader);
+                    bulk_g2s_w(dst + 2 * SM::kSuper, A.w + A.G.off_s + u * 128, 256, full_bar(s), leader);
+                    if (E::kHasMin) bulk_g2s_w(dst + 2 * SM::kSuper + 256, A.w + A.G.off_m + u * 128, 256, full_bar(s), leader);
                 }
             };
             auto acts = [&](int it) {                  // the k-slices of the activations: 2 x [NTOK tokens] x [64]
@@ -747,8 +763,8 @@ skinny_kernel(const __grid_constant__ CUtensorMap xmap, const SkinnyArgs A) {
                 int ft, kb;
                 locate(it, ft, kb);
                 const int s = it % NS;
-                tma_load_2d(ring + s * STAGE, &xmap, kb * 64, 0, full_bar(s));
-                tma_load_2d(ring + s * STAGE + NTOK * 128, &xmap, kb * 64 + 64, 0, full_bar(s));
+                tma_load_2d_w(ring + s * STAGE, &xmap, kb * 64, 0, full_bar(s), leader);
+                tma_load_2d_w(ring + s * STAGE + NTOK * 128, &xmap, kb * 64 + 64, 0, full_bar(s), leader);
             };
             // the first round's weights do not depend on the previous kernel: they are on their way before the wait
             const int first = n_items < NS ? n_items : NS;
