@@ -11,8 +11,9 @@
 //   nf4      : d = absmax, code = nearest NormalFloat4 entry (ties to the lower index)
 //   fp8/fp6  : d = absmax / MAX, code = RNE-saturating e4m3 / e5m2 / e3m2 of x*(1/d);
 //              scale_search tries 9 multipliers of d and keeps the least squared error.
-// HBM-bound: 4 bytes read per element, ~0.53-1.03 written.  A warp takes 8 consecutive blocks per pass (all loads first,
-// redux.sync reductions, records staged in shared memory and stored in 16-byte pieces); see quantize_kernel.
+// 4 bytes read per element, ~0.53-1.03 written.  The 4-bit formats take four lanes per block (quantize4_kernel: 0.73 of the
+// copy peak for sym_int4); the others, and every call that wants the code histogram, one warp per block with 8 consecutive
+// blocks per pass (all loads first, redux.sync reductions, records staged in shared memory, 16-byte stores): quantize_kernel.
 #include <cuda_fp8.h>
 #include <cuda_fp6.h>
 #include "lowbit_common.cuh"
@@ -240,6 +241,163 @@ quantize_kernel(const float* __restrict__ src, uint8_t* __restrict__ dst, size_t
     }
 }
 
+// The 4-bit formats without a histogram request: FOUR lanes per block, eight blocks per warp instruction.  A block's scalar
+// work (the extremum's reduction, "first wins", 1 / d, the record header) costs the same warp instructions whether 32 or 4
+// lanes share it, so eight blocks per instruction cut the instructions per element from 0.8 (one block per warp) to about
+// 0.4 -- the kernel was bound by them (0.48 of the copy peak; 0.68 with eight lanes per block).  Lane l of a block's four
+// owns elements 8l..8l+7 and 32+8l..32+8l+7: exactly the code pairs of bytes 8l..8l+7 of the record
+// (byte j = code[j] | code[j+32] << 4), loaded as four float4.  "First wins" in element order = the lowest lane with a
+// hit among the low halves, else among the high halves (two ballots).
+#ifndef LOWBIT_QUANT4_GROUP
+#define LOWBIT_QUANT4_GROUP 8
+#endif
+constexpr int QUANT4_GROUP = LOWBIT_QUANT4_GROUP;
+constexpr int QUANT4_LPB = 4;                      // lanes per block
+template <int QT>
+__global__ void __launch_bounds__(QUANT_WARPS * 32)
+quantize4_kernel(const float* __restrict__ src, uint8_t* __restrict__ dst, size_t nblk) {
+    constexpr int LPB = QUANT4_LPB, EL = 32 / LPB;          // elements per lane and half (8)
+    constexpr int BPP = 32 / LPB;                            // blocks per pass (8)
+    constexpr int QG = QUANT4_GROUP, NP = QG / BPP;          // blocks per warp and group; passes
+    static_assert(QG % BPP == 0 && NP >= 1, "group = whole passes");
+    constexpr int BS = (QT == QT_ASYM_INT4) ? 36 : 34;
+    constexpr int HDR = (QT == QT_ASYM_INT4) ? 4 : 2;
+    static_assert(QT == QT_SYM_INT4 || QT == QT_ASYM_INT4 || QT == QT_NF4, "4-bit formats");
+    __shared__ __align__(16) uint8_t s_rec[QUANT_WARPS][QG * BS];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int sub = lane / LPB, ls = lane % LPB;
+    const size_t ngroups = (nblk + QG - 1) / QG;
+    const size_t wstride = (size_t)gridDim.x * QUANT_WARPS;
+    for (size_t grp = (size_t)blockIdx.x * QUANT_WARPS + warp; grp < ngroups; grp += wstride) {
+        const size_t b_first = grp * QG;
+        const int nb = (int)((nblk - b_first) < (size_t)QG ? (nblk - b_first) : (size_t)QG);
+        float4 raw[NP][EL / 2];                        // [pass][lo 0..EL/4-1 | hi]
+#pragma unroll
+        for (int p = 0; p < NP; p++) {                 // all loads first: 64 bytes per lane and pass in flight
+            const int j = p * BPP + sub;
+#pragma unroll
+            for (int v = 0; v < EL / 2; v++) raw[p][v] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+            if (j < nb) {
+                const float4* bp = reinterpret_cast<const float4*>(src + (b_first + j) * 64);
+#pragma unroll
+                for (int v = 0; v < EL / 4; v++) {
+                    raw[p][v] = __ldcs(bp + ls * (EL / 4) + v);
+                    raw[p][EL / 4 + v] = __ldcs(bp + 8 + ls * (EL / 4) + v);
+                }
+            }
+        }
+#pragma unroll
+        for (int p = 0; p < NP; p++) {
+            const int j = p * BPP + sub;
+            float x[2 * EL];                           // [0, EL): elements EL*ls.. ; [EL, 2 EL): 32 + EL*ls..
+#pragma unroll
+            for (int v = 0; v < EL / 2; v++) { x[4 * v] = raw[p][v].x; x[4 * v + 1] = raw[p][v].y; x[4 * v + 2] = raw[p][v].z; x[4 * v + 3] = raw[p][v].w; }
+            uint8_t* out = s_rec[warp] + j * BS;
+            uint32_t q[2 * EL];
+            float d = 0.0f, mn = 0.0f;
+            // the first of the block's 64 elements (index order) for which hit[] holds, given the lane's own flags
+            auto first_hit = [&](const bool (&hit)[2 * EL]) -> float {
+                bool hl = false, hh = false;
+                float vl = x[EL - 1], vh = x[2 * EL - 1];
+#pragma unroll
+                for (int i = EL - 1; i >= 0; i--) {    // descending: the lowest index is assigned last
+                    hl |= hit[i]; hh |= hit[EL + i];
+                    vl = hit[i] ? x[i] : vl; vh = hit[EL + i] ? x[EL + i] : vh;
+                }
+                const uint32_t bl = (__ballot_sync(0xffffffffu, hl) >> (LPB * sub)) & ((1u << LPB) - 1u);
+                const uint32_t bh = (__ballot_sync(0xffffffffu, hh) >> (LPB * sub)) & ((1u << LPB) - 1u);
+                const int srcl = LPB * sub + (bl ? (__ffs(bl) - 1) : bh ? (__ffs(bh) - 1) : 0);
+                return __shfl_sync(0xffffffffu, bl ? vl : vh, srcl);
+            };
+            if (QT == QT_SYM_INT4 || QT == QT_NF4) {
+                uint32_t a[2 * EL];
+                uint32_t amax = 0u;
+#pragma unroll
+                for (int i = 0; i < 2 * EL; i++) { a[i] = __float_as_uint(x[i]) & 0x7fffffffu; amax = max(amax, a[i]); }
+#pragma unroll
+                for (int o = 1; o < LPB; o <<= 1) amax = max(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+                if (QT == QT_SYM_INT4) {
+                    bool hit[2 * EL];
+#pragma unroll
+                    for (int i = 0; i < 2 * EL; i++) hit[i] = a[i] == amax;
+                    const float val = first_hit(hit);                                      // the first element with |x| == max
+                    d = (amax != 0u) ? __fmul_rn(val, -0.125f) : -0.0f;                    // x / -8: exact as a product
+                    const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
+#pragma unroll
+                    for (int i = 0; i < 2 * EL; i++) q[i] = (uint32_t)min(15, (int)(signed char)(int)__fadd_rn(__fmul_rn(x[i], id), 8.5f));
+                } else {
+                    d = __uint_as_float(amax);
+                    const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
+#pragma unroll
+                    for (int i = 0; i < 2 * EL; i++) q[i] = nf4_encode(__fmul_rn(x[i], id));
+                }
+            } else {
+                uint32_t klo = 0xffffffffu, khi = 0u;
+#pragma unroll
+                for (int i = 0; i < 2 * EL; i++) { const uint32_t kk = ordered_key(x[i]); klo = min(klo, kk); khi = max(khi, kk); }
+#pragma unroll
+                for (int o = 1; o < LPB; o <<= 1) {
+                    klo = min(klo, __shfl_xor_sync(0xffffffffu, klo, o));
+                    khi = max(khi, __shfl_xor_sync(0xffffffffu, khi, o));
+                }
+                // back to floats; the serial scan keeps the FIRST element that compares equal to the extremum (-0 == +0)
+                const float lo_f = __uint_as_float((klo & 0x80000000u) ? (klo & 0x7fffffffu) : ~klo);
+                const float hi_f = __uint_as_float((khi & 0x80000000u) ? (khi & 0x7fffffffu) : ~khi);
+                bool hit[2 * EL];
+#pragma unroll
+                for (int i = 0; i < 2 * EL; i++) hit[i] = x[i] == lo_f;
+                mn = first_hit(hit);
+#pragma unroll
+                for (int i = 0; i < 2 * EL; i++) hit[i] = x[i] == hi_f;
+                const float mx = first_hit(hit);
+                d = __fdiv_rn(__fsub_rn(mx, mn), 15.0f);
+                const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
+#pragma unroll
+                for (int i = 0; i < 2 * EL; i++)
+                    q[i] = (uint32_t)min(15, (int)(signed char)(int)__fadd_rn(__fmul_rn(__fsub_rn(x[i], mn), id), 0.5f));
+            }
+            if (j < nb) {
+                uint8_t* o8 = out + HDR + EL * ls;     // 34 j + 2 + 8 l (2-byte aligned) / 36 j + 4 + 8 l (4-byte aligned)
+#pragma unroll
+                for (int w = 0; w < EL / 4; w++) {
+                    const int i = 4 * w;
+                    const uint32_t word = (q[i] | (q[EL + i] << 4)) | ((q[i + 1] | (q[EL + i + 1] << 4)) << 8) |
+                                          ((q[i + 2] | (q[EL + i + 2] << 4)) << 16) | ((q[i + 3] | (q[EL + i + 3] << 4)) << 24);
+                    if (QT == QT_ASYM_INT4) *reinterpret_cast<uint32_t*>(o8 + 4 * w) = word;
+                    else {
+                        *reinterpret_cast<unsigned short*>(o8 + 4 * w) = (unsigned short)(word & 0xffffu);
+                        *reinterpret_cast<unsigned short*>(o8 + 4 * w + 2) = (unsigned short)(word >> 16);
+                    }
+                }
+                if (ls == 0) {
+                    store_half_bits(out, d);
+                    if (QT == QT_ASYM_INT4) store_half_bits(out + 2, mn);
+                }
+            }
+        }
+        __syncwarp();
+        uint8_t* gdst = dst + b_first * BS;
+        if (nb == QG && !((uintptr_t)gdst & 15)) {
+            constexpr int NV = QG * BS / 16;
+            for (int v = lane; v < NV; v += 32)
+                __stcs(reinterpret_cast<uint4*>(gdst) + v, reinterpret_cast<const uint4*>(s_rec[warp])[v]);
+        } else {
+            for (int v = lane; v < nb * BS; v += 32) gdst[v] = s_rec[warp][v];
+        }
+        __syncwarp();
+    }
+}
+
+template <typename K>
+static int resident_ctas(K kernel, int& cache) {
+    if (!cache) {
+        int n = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel, QUANT_WARPS * 32, 0) != cudaSuccess || n <= 0) { cudaGetLastError(); n = 4; }
+        cache = n;
+    }
+    return cache;
+}
+
 int quantize_launch(const float* src, void* dst, int qt, size_t n, int k, int64_t* hist, bool scale_search,
                     cudaStream_t st) {
     qt = canon_qtype(qt);
@@ -250,6 +408,20 @@ int quantize_launch(const float* src, void* dst, int qt, size_t n, int k, int64_
         if (cudaMemsetAsync(hist, 0, 16 * sizeof(int64_t), st) != cudaSuccess) return check_launch();
     }
     size_t blocks = ((nblk + QUANT_GROUP - 1) / QUANT_GROUP + QUANT_WARPS - 1) / QUANT_WARPS;
+    const size_t blocks4 = ((nblk + QUANT4_GROUP - 1) / QUANT4_GROUP + QUANT_WARPS - 1) / QUANT_WARPS;
+    if (!hist && !((uintptr_t)src & 15) && (qt == QT_SYM_INT4 || qt == QT_ASYM_INT4 || qt == QT_NF4)) {
+        // eight lanes per block (see quantize4_kernel); one resident wave of CTAs, each looping over its groups
+        static int c4[3] = {0, 0, 0};
+        const int per = qt == QT_SYM_INT4 ? resident_ctas(quantize4_kernel<QT_SYM_INT4>, c4[0])
+                      : qt == QT_ASYM_INT4 ? resident_ctas(quantize4_kernel<QT_ASYM_INT4>, c4[1]) : resident_ctas(quantize4_kernel<QT_NF4>, c4[2]);
+        const size_t cap4 = (size_t)sm_count() * per;
+        const int grid4 = (int)(blocks4 > cap4 ? cap4 : blocks4);
+        if (qt == QT_SYM_INT4) quantize4_kernel<QT_SYM_INT4><<<grid4, QUANT_WARPS * 32, 0, st>>>(src, (uint8_t*)dst, nblk);
+        else if (qt == QT_ASYM_INT4) quantize4_kernel<QT_ASYM_INT4><<<grid4, QUANT_WARPS * 32, 0, st>>>(src, (uint8_t*)dst, nblk);
+        else quantize4_kernel<QT_NF4><<<grid4, QUANT_WARPS * 32, 0, st>>>(src, (uint8_t*)dst, nblk);
+        note_launch();
+        return check_launch();
+    }
     // one wave: as many CTAs as are resident at once (the kernel loops over its groups)
     static int per_sm[6] = {0, 0, 0, 0, 0, 0};
     const int qi = qt == QT_SYM_INT4 ? 0 : qt == QT_ASYM_INT4 ? 1 : qt == QT_NF4 ? 2 : qt == QT_FP8_E4M3 ? 3 : qt == QT_FP8_E5M2 ? 4 : 5;
