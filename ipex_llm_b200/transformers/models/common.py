@@ -124,6 +124,9 @@ def merge_qkv_base(module: torch.nn.Module, attention_class):
             del module.q_proj, module.k_proj, module.v_proj
 
 
+PREFILL_MLP_MAX_SCRATCH = 256 << 20      # bytes of fp32 scratch (2 x tokens x intermediate x 4) the prefill MLP may ask for
+
+
 def fuse_mlp_base(module: torch.nn.Module, act: int, x: torch.Tensor):
     """:146-161: gate and up projections + activation * multiply in one kernel at decode sizes
     (xe_linear.mlp_forward_xpu -> lowbit_mlp_cuda), then down_proj"""
@@ -133,6 +136,17 @@ def fuse_mlp_base(module: torch.nn.Module, act: int, x: torch.Tensor):
     qtype = getattr(gate, "qtype", None)
     if (isinstance(gate, LowBitLinear) and isinstance(up, LowBitLinear) and gate.bias is None and up.bias is None
             and gate.mp_group is None and getattr(up, "qtype", None) == qtype and mlp_fusion_check(x, qtype, module.training)):
+        x_2d = x.contiguous().view(-1, x.size(-1))
+        hidden = mlp_forward(x_2d, gate.weight.data, up.weight.data, x_2d.size(0), x_2d.size(1), gate.out_len, act, qtype)
+        return module.down_proj(hidden.view(x.shape[:-1] + (gate.out_len,)))
+    if (isinstance(gate, LowBitLinear) and isinstance(up, LowBitLinear) and gate.bias is None and up.bias is None
+            and gate.mp_group is None and getattr(up, "qtype", None) == qtype and x.device.type == "cuda"
+            and x.dtype in (torch.float16, torch.bfloat16) and not module.training and not x.requires_grad
+            and not gate.act_order and gate.weight.data.device.type == "cuda"
+            and 8 * (x.numel() // x.size(-1)) * gate.out_len <= PREFILL_MLP_MAX_SCRATCH):
+        # prefill-sized batches: the same entry point runs the two matmuls into fp32 scratch and one activation kernel --
+        # three launches from one host call, where the module-by-module statement below is five ops and as many allocations
+        # (the 512-token prefill of a 7B model is bound by the host's launch rate between its GEMMs)
         x_2d = x.contiguous().view(-1, x.size(-1))
         hidden = mlp_forward(x_2d, gate.weight.data, up.weight.data, x_2d.size(0), x_2d.size(1), gate.out_len, act, qtype)
         return module.down_proj(hidden.view(x.shape[:-1] + (gate.out_len,)))
