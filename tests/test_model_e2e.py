@@ -218,6 +218,12 @@ def test_recorded_decode_step_matches_the_eager_forwards(native_lib, cuda_device
             fast12 = model.generate(ids12, max_new_tokens=6, do_sample=False)
             slow12 = model._hf_generate(ids12, max_new_tokens=6, do_sample=False)
         assert_same_tokens_up_to_a_tie(model, fast12, slow12, dtype)
+        # 24 sequences: the linears whose shapes allow it take the skinny tensor-core kernel, in the recorded step and in the eager forward
+        ids24 = torch.randint(0, 320, (24, 20), generator=torch.Generator().manual_seed(12)).to(cuda_device)
+        with torch.no_grad():
+            fast24 = model.generate(ids24, max_new_tokens=6, do_sample=False)
+            slow24 = model._hf_generate(ids24, max_new_tokens=6, do_sample=False)
+        assert_same_tokens_up_to_a_tie(model, fast24, slow24, dtype)
     assert_same_tokens_up_to_a_tie(model, fast2[:1], fast[:, :48], dtype)
     assert model.rest_cost_mean > 0 and model.first_cost > 0
 
