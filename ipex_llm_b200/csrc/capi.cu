@@ -261,11 +261,15 @@ int lowbit_mlp_cuda(const void* d_w_gate, const void* d_w_up, int qtype, int64_t
         rc = gemv_launch_ex(d_w_gate, d_w_up, act + 1, qtype, n_rows, k, d_x, x_dtype, m, d_y, y_dtype, nullptr, 0, workspace,
                             workspace_bytes, st);
     } else {
-        float* tg = (float*)((char*)workspace + base);
-        float* tu = tg + (size_t)m * n_rows;
-        rc = matmul_dispatch(d_w_gate, qtype, n_rows, k, d_x, x_dtype, m, tg, DT_F32, nullptr, 0, workspace, base, st);
-        if (!rc) rc = matmul_dispatch(d_w_up, qtype, n_rows, k, d_x, x_dtype, m, tu, DT_F32, nullptr, 0, workspace, base, st);
-        if (!rc) rc = act_mul_launch(tg, tu, d_y, y_dtype, m * n_rows, act + 1, st);
+        // the two intermediates: fp32 behind the exact GEMV; behind the tensor-core kernels (whose contract rounds the weights to
+        // the activation dtype anyway) in y's half-precision dtype -- half the bytes through the GEMM epilogue and the activation
+        const bool tc = use_skinny(qtype, n_rows, k, m, x_dtype) || use_gemm(qtype, n_rows, k, m, x_dtype);
+        const int t_dtype = (tc && y_dtype != DT_F32) ? y_dtype : DT_F32;
+        char* tg = (char*)workspace + base;
+        char* tu = tg + (size_t)m * n_rows * (t_dtype == DT_F32 ? 4 : 2);
+        rc = matmul_dispatch(d_w_gate, qtype, n_rows, k, d_x, x_dtype, m, tg, t_dtype, nullptr, 0, workspace, base, st);
+        if (!rc) rc = matmul_dispatch(d_w_up, qtype, n_rows, k, d_x, x_dtype, m, tu, t_dtype, nullptr, 0, workspace, base, st);
+        if (!rc) rc = act_mul_launch(tg, tu, t_dtype, d_y, y_dtype, m * n_rows, act + 1, st);
     }
     if (rc == LB_ERR_ARG) set_error(rc, "lowbit_mlp_cuda: bad argument (qtype %d, N %lld, K %lld, M %lld)", qtype, (long long)n_rows, (long long)k, (long long)m);
     if (rc == LB_ERR_WORKSPACE) set_error(rc, "lowbit_mlp_cuda: workspace too small (%zu bytes)", workspace_bytes);

@@ -112,16 +112,53 @@ static void launch_generic(const void* w, const TiledGeom& G, int qt, int64_t r0
                                                         bias, accumulate);
 }
 
-// y = act(g) * u elementwise (the unfused tail of the MLP when the fused GEMV does not apply)
-__global__ void act_mul_kernel(const float* __restrict__ gate, const float* __restrict__ up, void* y, int y_dtype, int64_t n,
+// y = act(g) * u elementwise (the unfused tail of the MLP when the fused GEMV does not apply).  gate / up: fp32, or the
+// activation dtype when they come from the tensor-core kernels (whose precision contract rounds there anyway).
+__device__ __forceinline__ float in_at(const void* p, int dt, int64_t i) {
+    return dt == DT_F32 ? ((const float*)p)[i] : dt == DT_F16 ? __half2float(((const __half*)p)[i]) : __bfloat162float(((const __nv_bfloat16*)p)[i]);
+}
+__global__ void act_mul_kernel(const void* __restrict__ gate, const void* __restrict__ up, int in_dtype, void* y, int y_dtype, int64_t n,
                                int act) {
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
-        store_out(y, y_dtype, i, apply_act(gate[i], act) * up[i], nullptr, 0, 0);
+        store_out(y, y_dtype, i, apply_act(in_at(gate, in_dtype, i), act) * in_at(up, in_dtype, i), nullptr, 0, 0);
+}
+// eight elements per thread, 16-byte loads and stores: half-precision in and out (the prefill route)
+template <bool BF>
+__global__ void __launch_bounds__(256) act_mul_vec_kernel(const uint4* __restrict__ gate, const uint4* __restrict__ up, uint4* __restrict__ y,
+                                                          int64_t n8, int act) {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n8; i += (int64_t)gridDim.x * blockDim.x) {
+        const uint4 g = __ldcs(gate + i), u = __ldcs(up + i);
+        const uint32_t gw[4] = {g.x, g.y, g.z, g.w}, uw[4] = {u.x, u.y, u.z, u.w};
+        uint32_t ow[4];
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            float g0, g1, u0, u1;
+            if (BF) {
+                g0 = __uint_as_float(gw[j] << 16); g1 = __uint_as_float(gw[j] & 0xffff0000u);
+                u0 = __uint_as_float(uw[j] << 16); u1 = __uint_as_float(uw[j] & 0xffff0000u);
+            } else {
+                const float2 gf = __half22float2(*reinterpret_cast<const __half2*>(&gw[j])), uf = __half22float2(*reinterpret_cast<const __half2*>(&uw[j]));
+                g0 = gf.x; g1 = gf.y; u0 = uf.x; u1 = uf.y;
+            }
+            const float r0 = apply_act(g0, act) * u0, r1 = apply_act(g1, act) * u1;
+            if (BF) { const __nv_bfloat162 b = __floats2bfloat162_rn(r0, r1); ow[j] = *reinterpret_cast<const uint32_t*>(&b); }
+            else { const __half2 h = __floats2half2_rn(r0, r1); ow[j] = *reinterpret_cast<const uint32_t*>(&h); }
+        }
+        y[i] = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+    }
 }
 
-int act_mul_launch(const float* gate, const float* up, void* y, int y_dtype, int64_t n, int act, cudaStream_t st) {
+int act_mul_launch(const void* gate, const void* up, int in_dtype, void* y, int y_dtype, int64_t n, int act, cudaStream_t st) {
+    if (in_dtype != DT_F32 && in_dtype == y_dtype && n % 8 == 0 && !(((uintptr_t)gate | (uintptr_t)up | (uintptr_t)y) & 15)) {
+        const int64_t n8 = n / 8;
+        int g = (int)((n8 + 255) / 256); if (g > sm_count() * 8) g = sm_count() * 8;
+        if (in_dtype == DT_BF16) act_mul_vec_kernel<true><<<g, 256, 0, st>>>((const uint4*)gate, (const uint4*)up, (uint4*)y, n8, act);
+        else act_mul_vec_kernel<false><<<g, 256, 0, st>>>((const uint4*)gate, (const uint4*)up, (uint4*)y, n8, act);
+        note_launch();
+        return check_launch();
+    }
     int g = (int)((n + 255) / 256); if (g > sm_count() * 8) g = sm_count() * 8;
-    act_mul_kernel<<<g, 256, 0, st>>>(gate, up, y, y_dtype, n, act);
+    act_mul_kernel<<<g, 256, 0, st>>>(gate, up, in_dtype, y, y_dtype, n, act);
     note_launch();
     return check_launch();
 }

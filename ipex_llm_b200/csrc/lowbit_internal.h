@@ -52,7 +52,7 @@ int gemv_launch_ex(const void* w, const void* w2, int act, int qt, int64_t n_row
                    int64_t m, void* y, int y_dtype, const void* bias, int accumulate, void* workspace,
                    size_t workspace_bytes, cudaStream_t st);
 bool gemv_mlp_fused_supported(int qt, int64_t n_rows, int64_t k, int64_t m, int x_dtype);
-int act_mul_launch(const float* gate, const float* up, void* y, int y_dtype, int64_t n, int act, cudaStream_t st);
+int act_mul_launch(const void* gate, const void* up, int in_dtype, void* y, int y_dtype, int64_t n, int act, cudaStream_t st);
 
 // one-token mixture-of-experts (reference xe_linear.moe_forward_vec)
 struct MoeParams {

@@ -102,7 +102,15 @@ def test_mlp_shapes_and_fallbacks(lbl, cuda_device, shape, M):
     assert float((out.double() - want).abs().max()) <= 2e-6 * scale + 1e-6 * float(u.abs().max())
     # default output dtype = activation dtype, same values rounded once
     out16 = lbl.mlp_forward(x_t, tg, tu, M, K, N, lbl.SILU, qid(qtype))
-    assert out16.dtype == torch.float16 and torch.equal(out16, out.half())
+    assert out16.dtype == torch.float16
+    if lbl.takes_tensor_core_path(M, N, K, torch.float16):
+        # behind the tensor-core kernels the two intermediates are kept in the output's half precision (their contract
+        # rounds the weights to it anyway): each of gate and up carries one more rounding of 2^-11
+        g16, u16 = g.half().double(), u.half().double()
+        want16 = torch.nn.functional.silu(g16) * u16
+        assert float((out16.double() - want16).abs().max()) <= 2e-3 * scale
+    else:
+        assert torch.equal(out16, out.half())
 
 
 def test_mlp_deterministic_and_single_launch(lbl, cuda_device):
