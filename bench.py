@@ -305,6 +305,8 @@ def prefill_numbers(model, dev, peaks):
         tf = flops / (ms * 1e-3) / 1e12
         out[f"M{M}"] = {"ms_per_layer": ms / 8, "tflops": tf, "frac_of_peak": tf / burst,
                         "tok_per_s_linears_only": M / (ms / 8 * LAYERS * 1e-3)}
+        if peaks.get("bf16_tflops_sustained"):          # the loop is 120 GEMMs back to back: also against the sustained figure
+            out[f"M{M}"]["frac_of_sustained_peak"] = tf / float(peaks["bf16_tflops_sustained"])
     ids = torch.randint(0, VOCAB, (1, PROMPT_LEN), device=dev)
     with torch.no_grad():
         for _ in range(2):
