@@ -72,6 +72,42 @@ def test_quantize_bit_exact_device_abi(lbl, cuda_device, qtype):
     np.testing.assert_array_equal(got, oracle.quantize(w, qtype))
 
 
+@pytest.mark.parametrize("qtype", ["sym_int4", "asym_int4", "nf4"])
+@pytest.mark.parametrize("rows", [1, 7, 9, 33])
+def test_quantize_four_lanes_per_block_edge_cases(lbl, cuda_device, qtype, rows):
+    """the device path of the 4-bit formats (four lanes per block, eight blocks per warp instruction): ragged block counts
+    (tail groups), all-zero and -0 blocks, the extremum in every lane position and half, equal |x| of both signs (the first
+    one decides the scale), exact .5 ties, a constant block, one huge element; and an unaligned source (the one-warp-per-block
+    kernel takes over) -- bytes equal to the oracle's"""
+    rng = np.random.default_rng(250 + rows)
+    k = 192
+    w = rand_w(rng, rows, k, "wide")
+    blocks = w.reshape(-1, 64)
+    nb = blocks.shape[0]
+    blocks[0 % nb] = 0.0
+    blocks[1 % nb] = -0.0
+    for j in range(2, nb):                                   # the maximum walks over all 64 positions, both signs
+        pos = (5 * j) % 64
+        blocks[j, pos] = 4.0 * (-1.0) ** j
+        if j % 3 == 0:                                       # ... with an equal magnitude of the other sign later or earlier
+            blocks[j, (pos + 17) % 64] = -blocks[j, pos]
+        if j % 4 == 1:
+            blocks[j, (pos + 32) % 64] = blocks[j, pos]
+    if nb > 5:
+        blocks[5] = np.linspace(-1, 1, 64)                   # exact ties at .5 steps for some formats
+    if nb > 6:
+        blocks[6] = 0.25
+    w = blocks.reshape(rows, k).copy()
+    want = oracle.quantize(w, qtype)
+    got = as_np_u8(lbl.ggml_convert_qtype(torch.from_numpy(w).to(cuda_device), qid(qtype)))
+    np.testing.assert_array_equal(got, want)
+    # source not 16-byte aligned
+    pad = torch.zeros(rows * k + 1, device=cuda_device)
+    pad[1:] = torch.from_numpy(w).to(cuda_device).flatten()
+    got2 = as_np_u8(lbl.ggml_convert_qtype(pad[1:].view(rows, k), qid(qtype)))
+    np.testing.assert_array_equal(got2, want)
+
+
 @pytest.mark.parametrize("qtype", ["fp8_e4m3", "fp8_e5m2", "fp6"])
 def test_quantize_scale_search_bit_exact(lbl, cuda_device, qtype):
     rng = np.random.default_rng(300)
