@@ -190,6 +190,12 @@ int lowbit_sdp_fp8_prefill_cuda(const void* d_q, int q_dtype, const int64_t* q_s
                                 const int64_t* k_strides, const void* d_v, const int64_t* v_strides, const void* d_mask,
                                 int mask_dtype, const int64_t* mask_strides, int causal, float scale, int B, int Hq, int Hkv,
                                 int S, int L, int D, void* d_out, int out_dtype, void* stream);
+/* ... with the output's element strides {batch, head, token} (rows of D contiguous, multiples of 8): writing [B][S][Hq][D]
+ * directly saves the transpose copy that follows attention in the model forwards (models/llama.py:198). */
+int lowbit_sdp_fp8_prefill_strided_cuda(const void* d_q, int q_dtype, const int64_t* q_strides, const void* d_k,
+                                const int64_t* k_strides, const void* d_v, const int64_t* v_strides, const void* d_mask,
+                                int mask_dtype, const int64_t* mask_strides, int causal, float scale, int B, int Hq, int Hkv,
+                                int S, int L, int D, void* d_out, int out_dtype, const int64_t* out_strides, void* stream);
 
 /* lowbit_sdp_fp8_cuda for a decode step that is replayed from a CUDA graph: the key count is read on the device,
  * L = min(*d_len + len_add, L_max), so one recorded launch serves every step.  L_max (the cache capacity the step

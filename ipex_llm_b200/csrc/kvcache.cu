@@ -129,6 +129,7 @@ struct SdpArgs {
     int rt;                                                        // query rows per CTA (1, 2 or 4)
     float* part;                                                   // [B][Hkv][row tiles][n_split][RT * (D + 2)]
     void* out; int out_dtype;                                      // [B][Hq][S][D] contiguous
+    int64_t o_sb, o_sh, o_ss;                                      // prefill kernel only: element strides of out (rows of D contiguous)
 };
 
 // key count and keys per split of this launch: the host's values, or -- when the cache length lives in device memory
@@ -624,12 +625,27 @@ extern "C" int lowbit_sdp_fp8_prefill_supported(int Hq, int Hkv, int D, int q_dt
     return Hq > 0 && Hkv > 0 && Hq % Hkv == 0 && D == 128 && (q_dtype == DT_F16 || q_dtype == DT_BF16);
 }
 
+extern "C" int lowbit_sdp_fp8_prefill_strided_cuda(const void* d_q, int q_dtype, const int64_t* q_strides, const void* d_k,
+                                                   const int64_t* k_strides, const void* d_v, const int64_t* v_strides, const void* d_mask,
+                                                   int mask_dtype, const int64_t* mask_strides, int causal, float scale, int B, int Hq,
+                                                   int Hkv, int S, int L, int D, void* d_out, int out_dtype, const int64_t* out_strides,
+                                                   void* stream);
 extern "C" int lowbit_sdp_fp8_prefill_cuda(const void* d_q, int q_dtype, const int64_t* q_strides, const void* d_k,
                                            const int64_t* k_strides, const void* d_v, const int64_t* v_strides, const void* d_mask,
                                            int mask_dtype, const int64_t* mask_strides, int causal, float scale, int B, int Hq,
                                            int Hkv, int S, int L, int D, void* d_out, int out_dtype, void* stream) {
+    const int64_t os[3] = {(int64_t)Hq * S * D, (int64_t)S * D, (int64_t)D};
+    return lowbit_sdp_fp8_prefill_strided_cuda(d_q, q_dtype, q_strides, d_k, k_strides, d_v, v_strides, d_mask, mask_dtype, mask_strides,
+                                               causal, scale, B, Hq, Hkv, S, L, D, d_out, out_dtype, os, stream);
+}
+
+extern "C" int lowbit_sdp_fp8_prefill_strided_cuda(const void* d_q, int q_dtype, const int64_t* q_strides, const void* d_k,
+                                                   const int64_t* k_strides, const void* d_v, const int64_t* v_strides, const void* d_mask,
+                                                   int mask_dtype, const int64_t* mask_strides, int causal, float scale, int B, int Hq,
+                                                   int Hkv, int S, int L, int D, void* d_out, int out_dtype, const int64_t* out_strides,
+                                                   void* stream) {
     reset_launch_count();
-    if (!d_q || !d_k || !d_v || !d_out || !q_strides || !k_strides || !v_strides || (d_mask && !mask_strides) || out_dtype < 0 ||
+    if (!d_q || !d_k || !d_v || !d_out || !q_strides || !k_strides || !v_strides || !out_strides || (d_mask && !mask_strides) || out_dtype < 0 ||
         out_dtype > 2 || (d_mask && (mask_dtype < 0 || mask_dtype > 2)) || B <= 0 || S <= 0 || L < S || !(scale > 0.0f) ||
         !lowbit_sdp_fp8_prefill_supported(Hq, Hkv, D, q_dtype)) {
         set_error(LB_ERR_ARG, "lowbit_sdp_fp8_prefill_cuda: bad argument (B %d, Hq %d, Hkv %d, S %d, L %d, D %d, q_dtype %d)", B, Hq, Hkv, S, L, D, q_dtype);
@@ -637,7 +653,7 @@ extern "C" int lowbit_sdp_fp8_prefill_cuda(const void* d_q, int q_dtype, const i
     }
     if ((((uintptr_t)d_k | (uintptr_t)d_v | (uintptr_t)d_q | (uintptr_t)d_out) & 15) ||
         ((k_strides[0] | k_strides[1] | k_strides[2] | v_strides[0] | v_strides[1] | v_strides[2]) & 15) ||
-        ((q_strides[0] | q_strides[1] | q_strides[2]) & 7)) {
+        ((q_strides[0] | q_strides[1] | q_strides[2]) & 7) || ((out_strides[0] | out_strides[1] | out_strides[2]) & 7)) {
         set_error(LB_ERR_ARG, "lowbit_sdp_fp8_prefill_cuda: caches, query rows and output must be 16-byte aligned (pointers and strides)");
         return LB_ERR_ARG;
     }
@@ -649,7 +665,7 @@ extern "C" int lowbit_sdp_fp8_prefill_cuda(const void* d_q, int q_dtype, const i
     A.m_sb = d_mask ? mask_strides[0] : 0; A.m_sh = d_mask ? mask_strides[1] : 0; A.m_ss = d_mask ? mask_strides[2] : 0;
     A.causal = causal; A.scale_log2e = scale * 1.4426950408889634f;
     A.B = B; A.Hq = Hq; A.Hkv = Hkv; A.S = S; A.L = L; A.D = D;
-    A.out = d_out; A.out_dtype = out_dtype;
+    A.out = d_out; A.out_dtype = out_dtype; A.o_sb = out_strides[0]; A.o_sh = out_strides[1]; A.o_ss = out_strides[2];
     const dim3 grid((unsigned)((S + PF_ROWS - 1) / PF_ROWS), (unsigned)(B * Hq), 1);
     sdp_fp8_prefill_kernel<<<grid, PF_WARPS * 32, 0, (cudaStream_t)stream>>>(A);
     note_launch();

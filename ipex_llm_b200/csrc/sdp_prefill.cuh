@@ -191,7 +191,7 @@ sdp_fp8_prefill_kernel(const SdpArgs A) {
     auto store_row = [&](int row, int base, float denom) {
         if (row >= S) return;
         const float inv = denom > 0.0f ? 1.0f / denom : 0.0f;         // a row with every key masked gives zeros
-        const int64_t oi = (((int64_t)b * A.Hq + hq) * S + row) * D + 32 * t;
+        const int64_t oi = (int64_t)b * A.o_sb + (int64_t)hq * A.o_sh + (int64_t)row * A.o_ss + 32 * t;
 #pragma unroll
         for (int i = 0; i < 2; i++) {
             if (A.out_dtype == DT_F32) {

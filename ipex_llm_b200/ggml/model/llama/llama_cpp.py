@@ -547,6 +547,10 @@ _lib.lowbit_sdp_fp8_prefill_cuda.argtypes = [ctypes.c_void_p, ctypes.c_int, _I64
                                              ctypes.c_void_p, ctypes.c_int, _I64P, ctypes.c_int, ctypes.c_float] + [ctypes.c_int] * 6 + \
                                             [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p]
 _lib.lowbit_sdp_fp8_prefill_cuda.restype = ctypes.c_int
+_lib.lowbit_sdp_fp8_prefill_strided_cuda.argtypes = [ctypes.c_void_p, ctypes.c_int, _I64P, ctypes.c_void_p, _I64P, ctypes.c_void_p, _I64P,
+                                                     ctypes.c_void_p, ctypes.c_int, _I64P, ctypes.c_int, ctypes.c_float] + [ctypes.c_int] * 6 + \
+                                                    [ctypes.c_void_p, ctypes.c_int, _I64P, ctypes.c_void_p]
+_lib.lowbit_sdp_fp8_prefill_strided_cuda.restype = ctypes.c_int
 
 
 def lowbit_sdp_fp8_prefill_supported(hq, hkv, d, dtype):
@@ -554,11 +558,13 @@ def lowbit_sdp_fp8_prefill_supported(hq, hkv, d, dtype):
 
 
 def lowbit_sdp_fp8_prefill(q, k, v, mask, causal, scale, out, stream):
-    """q [B,Hq,S,D] view, k / v uint8 [B,Hkv,L,D] views, mask additive [B,1|Hq,S,L] or None, out [B,Hq,S,D] contiguous"""
+    """q [B,Hq,S,D] view, k / v uint8 [B,Hkv,L,D] views, mask additive [B,1|Hq,S,L] or None, out [B,Hq,S,D] with contiguous
+    rows (any batch / head / token strides: a transposed view of a [B,S,Hq,D] buffer is written in place)"""
     B, Hq, S, D = q.shape
     Hkv, L = k.shape[1], k.shape[2]
-    _check(_lib.lowbit_sdp_fp8_prefill_cuda(q.data_ptr(), _DT_OF[str(q.dtype)], _strides3(q), k.data_ptr(), _strides3(k), v.data_ptr(),
-                                            _strides3(v), mask.data_ptr() if mask is not None else None,
-                                            _DT_OF[str(mask.dtype)] if mask is not None else 0,
-                                            _strides3(mask) if mask is not None else None, int(bool(causal)), float(scale),
-                                            B, Hq, Hkv, S, L, D, out.data_ptr(), _DT_OF[str(out.dtype)], stream), "lowbit_sdp_fp8_prefill_cuda")
+    _check(_lib.lowbit_sdp_fp8_prefill_strided_cuda(q.data_ptr(), _DT_OF[str(q.dtype)], _strides3(q), k.data_ptr(), _strides3(k), v.data_ptr(),
+                                                    _strides3(v), mask.data_ptr() if mask is not None else None,
+                                                    _DT_OF[str(mask.dtype)] if mask is not None else 0,
+                                                    _strides3(mask) if mask is not None else None, int(bool(causal)), float(scale),
+                                                    B, Hq, Hkv, S, L, D, out.data_ptr(), _DT_OF[str(out.dtype)], _strides3(out), stream),
+           "lowbit_sdp_fp8_prefill_cuda")

@@ -103,6 +103,29 @@ class Fp8KVLayer(DynamicLayer):
         self.keys, self.values = append_fp8_kv_cache(self.keys, self.values, key_states, value_states)
         return self.keys, self.values
 
+    def rope_append(self, qkv, n_heads, n_kv_heads, head_dim, cos, sin):
+        """The first call of a sequence: rotary on the q / k heads of the merged projection's output ``qkv`` [B, S, (Hq + 2 Hkv) D]
+        (in place) and the e5m2 cache write of its S tokens in ONE launch -- rotary_half_with_cache_inplaced + update()
+        (= quantize_key_value twice) are three.  cos / sin: [S, D] tables of positions 0..S-1.  Returns the layer's
+        (keys, values) views, or None when the layer already holds tokens (the separate ops then do the work)."""
+        B, S = qkv.shape[0], qkv.shape[1]
+        if self.is_initialized and self.keys.shape[2] != 0:
+            return None
+        if not self.is_initialized:
+            k_view = qkv.view(B, S, n_heads + 2 * n_kv_heads, head_dim).transpose(1, 2)[:, n_heads:n_heads + n_kv_heads]
+            self.lazy_initialization(k_view, k_view)
+        if self.keys.stride(1) < S * head_dim:                    # storage shorter than the prompt (no reserve given)
+            if self.storage is not None:
+                return None
+            self.keys, self.values = init_fp8_kv_cache(B, n_kv_heads, S, head_dim, qkv.device)
+        cap = self.keys.stride(1) // head_dim
+        k_full = self.keys.as_strided((B, n_kv_heads, cap, head_dim), self.keys.stride(), storage_offset=0)
+        v_full = self.values.as_strided((B, n_kv_heads, cap, head_dim), self.values.stride(), storage_offset=0)
+        with torch.cuda.device(qkv.device):
+            ggml.lowbit_rope_kv_append(qkv, n_heads, n_kv_heads, head_dim, cos, sin, None, 0, k_full, v_full, _stream(qkv.device))
+        self.set_length(S)
+        return self.keys, self.values
+
     def set_length(self, length: int):
         """the views after ``length`` positions were written behind the host's back (the recorded decode step)"""
         b, h, _, d = self.keys.shape
@@ -156,6 +179,12 @@ class _LayeredCache(Cache):
 class DynamicFp8Cache(_LayeredCache):
     """kv.py:33-77: K and V as e5m2 bytes; ``update`` returns the uint8 views of the layer."""
     LAYER = Fp8KVLayer
+
+    def rope_append(self, layer_idx, qkv, n_heads, n_kv_heads, head_dim, cos, sin):
+        """see Fp8KVLayer.rope_append"""
+        while len(self.layers) <= layer_idx:
+            self.layers.append(self.new_layer())
+        return self.layers[layer_idx].rope_append(qkv, n_heads, n_kv_heads, head_dim, cos, sin)
 
 
 class NormalKVLayer(DynamicLayer):
@@ -245,7 +274,9 @@ def sdp_fp8_prefill(query, key, value, mask, scale, is_causal):
         if mask.stride(-1) != 1:
             mask = mask.contiguous()
         mask = mask.expand(B, Hq, S, key.shape[2])
-    out = torch.empty((B, Hq, S, D), dtype=query.dtype, device=query.device)
+    # [B, Hq, S, D] as a view of a [B, S, Hq, D] buffer: the transpose(1, 2).contiguous() that follows attention in the model
+    # forwards (models/llama.py:198) finds its layout already there
+    out = torch.empty((B, S, Hq, D), dtype=query.dtype, device=query.device).transpose(1, 2)
     with torch.cuda.device(query.device):
         ggml.lowbit_sdp_fp8_prefill(query, key, value, mask, is_causal, scale, out, _stream(query.device))
     return out

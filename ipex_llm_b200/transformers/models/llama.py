@@ -56,18 +56,27 @@ def decoder_attention_forward(apply_rotary_pos_emb):
         bsz, q_len, _ = hidden_states.size()
         n_heads, n_kv_heads, head_dim = self.config.num_attention_heads, self.config.num_key_value_heads, self.head_dim
 
-        qkv = self.qkv_proj(hidden_states)
-        qkv = qkv.view(bsz, q_len, n_heads + 2 * n_kv_heads, head_dim).transpose(1, 2)
+        qkv_flat = self.qkv_proj(hidden_states)
+        qkv = qkv_flat.view(bsz, q_len, n_heads + 2 * n_kv_heads, head_dim).transpose(1, 2)
         query_states, key_states, value_states = qkv.split([n_heads, n_kv_heads, n_kv_heads], dim=1)
 
         cos, sin = position_embeddings
-        if query_states.device.type == "cuda" and cos.shape[-1] == head_dim:
-            rotary_half_with_cache_inplaced(query_states, key_states, cos, sin)     # in place, on the views of qkv
+        cached = None
+        if (q_len > 1 and qkv_flat.device.type == "cuda" and cos.shape[-1] == head_dim and cos.shape[0] == 1 and cos.shape[1] == q_len
+                and qkv_flat.dtype in (torch.float16, torch.bfloat16) and cos.dtype == qkv_flat.dtype and qkv_flat.is_contiguous()
+                and cos.stride(-1) == 1 and sin.stride(-1) == 1 and hasattr(past_key_values, "rope_append")):
+            # prompt into an empty FP8 cache: rotary + the cache write of all its tokens in one launch (the bytes of the two
+            # separate operators below: tests/test_decode_ops.py)
+            cached = past_key_values.rope_append(self.layer_idx, qkv_flat, n_heads, n_kv_heads, head_dim, cos[0], sin[0])
+        if cached is not None:
+            key_states, value_states = cached
         else:
-            query_states, key_states = apply_rotary_pos_emb(query_states, key_states, cos, sin)
-
-        if past_key_values is not None:
-            key_states, value_states = past_key_values.update(key_states, value_states, self.layer_idx)
+            if query_states.device.type == "cuda" and cos.shape[-1] == head_dim:
+                rotary_half_with_cache_inplaced(query_states, key_states, cos, sin)     # in place, on the views of qkv
+            else:
+                query_states, key_states = apply_rotary_pos_emb(query_states, key_states, cos, sin)
+            if past_key_values is not None:
+                key_states, value_states = past_key_values.update(key_states, value_states, self.layer_idx)
 
         attn_output = scaled_dot_product_attention(query_states, key_states, value_states, attention_mask,
                                                    q_len == key_states.size(2), self.scaling)
