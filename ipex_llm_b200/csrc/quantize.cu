@@ -388,6 +388,63 @@ quantize4_kernel(const float* __restrict__ src, uint8_t* __restrict__ dst, size_
     }
 }
 
+// fp8 (e4m3 / e5m2) without scale search: the same four-lanes-per-block mapping; lane l owns elements 16l..16l+15 = bytes
+// 16l..16l+15 of the record (one code per byte), four float4 loads, d = absmax / MAX.
+template <int QT>
+__global__ void __launch_bounds__(QUANT_WARPS * 32)
+quantize8_kernel(const float* __restrict__ src, uint8_t* __restrict__ dst, size_t nblk) {
+    static_assert(QT == QT_FP8_E4M3 || QT == QT_FP8_E5M2, "fp8 formats");
+    constexpr int LPB = 4, BPP = 32 / LPB, QG = 8, BS = 66;
+    __shared__ __align__(16) uint8_t s_rec[QUANT_WARPS][QG * BS];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int sub = lane / LPB, ls = lane % LPB;
+    const size_t ngroups = (nblk + QG - 1) / QG;
+    const size_t wstride = (size_t)gridDim.x * QUANT_WARPS;
+    for (size_t grp = (size_t)blockIdx.x * QUANT_WARPS + warp; grp < ngroups; grp += wstride) {
+        const size_t b_first = grp * QG;
+        const int nb = (int)((nblk - b_first) < (size_t)QG ? (nblk - b_first) : (size_t)QG);
+        const int j = sub;                             // one pass: eight blocks, one per sub-group
+        float4 raw[4];
+#pragma unroll
+        for (int v = 0; v < 4; v++) raw[v] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        if (j < nb) {
+            const float4* bp = reinterpret_cast<const float4*>(src + (b_first + j) * 64);
+#pragma unroll
+            for (int v = 0; v < 4; v++) raw[v] = __ldcs(bp + ls * 4 + v);
+        }
+        float x[16];
+#pragma unroll
+        for (int v = 0; v < 4; v++) { x[4 * v] = raw[v].x; x[4 * v + 1] = raw[v].y; x[4 * v + 2] = raw[v].z; x[4 * v + 3] = raw[v].w; }
+        uint32_t amax = 0u;
+#pragma unroll
+        for (int i = 0; i < 16; i++) amax = max(amax, __float_as_uint(x[i]) & 0x7fffffffu);
+#pragma unroll
+        for (int o = 1; o < LPB; o <<= 1) amax = max(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+        const float d = __fdiv_rn(__uint_as_float(amax), fmt_max<QT>());
+        const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
+        if (j < nb) {
+            uint8_t* out = s_rec[warp] + j * BS;
+            uint8_t* o16 = out + 2 + 16 * ls;          // 66 j + 2 + 16 l: 2-byte aligned
+#pragma unroll
+            for (int i = 0; i < 16; i += 2) {
+                const uint32_t c0 = mini_encode<QT>(__fmul_rn(x[i], id)), c1 = mini_encode<QT>(__fmul_rn(x[i + 1], id));
+                *reinterpret_cast<unsigned short*>(o16 + i) = (unsigned short)(c0 | (c1 << 8));
+            }
+            if (ls == 0) store_half_bits(out, d);
+        }
+        __syncwarp();
+        uint8_t* gdst = dst + b_first * BS;
+        if (nb == QG && !((uintptr_t)gdst & 15)) {
+            constexpr int NV = QG * BS / 16;
+            for (int v = lane; v < NV; v += 32)
+                __stcs(reinterpret_cast<uint4*>(gdst) + v, reinterpret_cast<const uint4*>(s_rec[warp])[v]);
+        } else {
+            for (int v = lane; v < nb * BS; v += 32) gdst[v] = s_rec[warp][v];
+        }
+        __syncwarp();
+    }
+}
+
 template <typename K>
 static int resident_ctas(K kernel, int& cache) {
     if (!cache) {
@@ -409,6 +466,16 @@ int quantize_launch(const float* src, void* dst, int qt, size_t n, int k, int64_
     }
     size_t blocks = ((nblk + QUANT_GROUP - 1) / QUANT_GROUP + QUANT_WARPS - 1) / QUANT_WARPS;
     const size_t blocks4 = ((nblk + QUANT4_GROUP - 1) / QUANT4_GROUP + QUANT_WARPS - 1) / QUANT_WARPS;
+    if (!scale_search && !((uintptr_t)src & 15) && (qt == QT_FP8_E4M3 || qt == QT_FP8_E5M2)) {
+        static int c8[2] = {0, 0};
+        const int per = qt == QT_FP8_E4M3 ? resident_ctas(quantize8_kernel<QT_FP8_E4M3>, c8[0]) : resident_ctas(quantize8_kernel<QT_FP8_E5M2>, c8[1]);
+        const size_t cap8 = (size_t)sm_count() * per;
+        const int grid8 = (int)(blocks > cap8 ? cap8 : blocks);
+        if (qt == QT_FP8_E4M3) quantize8_kernel<QT_FP8_E4M3><<<grid8, QUANT_WARPS * 32, 0, st>>>(src, (uint8_t*)dst, nblk);
+        else quantize8_kernel<QT_FP8_E5M2><<<grid8, QUANT_WARPS * 32, 0, st>>>(src, (uint8_t*)dst, nblk);
+        note_launch();
+        return check_launch();
+    }
     if (!hist && !((uintptr_t)src & 15) && (qt == QT_SYM_INT4 || qt == QT_ASYM_INT4 || qt == QT_NF4)) {
         // eight lanes per block (see quantize4_kernel); one resident wave of CTAs, each looping over its groups
         static int c4[3] = {0, 0, 0};
