@@ -227,7 +227,9 @@ int lowbit_matmul_cuda(const void* d_w, int qtype, int64_t n_rows, int64_t k, co
 
 size_t lowbit_mlp_workspace_size(int64_t n_rows, int64_t k, int64_t m, int x_dtype) {
     const size_t base = (lowbit_matmul_workspace_size(n_rows, k, m, x_dtype) + 255) / 256 * 256;
-    return base + 2 * (size_t)m * n_rows * sizeof(float);
+    const size_t two = base + 2 * (size_t)m * n_rows * sizeof(float);
+    const size_t sk = use_skinny(B200_QT_SYM_INT4, n_rows, k, m, x_dtype) ? gemm_skinny_mlp_workspace_size(n_rows, k, m) : 0;
+    return two > sk ? two : sk;
 }
 
 int lowbit_mlp_cuda(const void* d_w_gate, const void* d_w_up, int qtype, int64_t n_rows, int64_t k, const void* d_x,
@@ -239,7 +241,7 @@ int lowbit_mlp_cuda(const void* d_w_gate, const void* d_w_up, int qtype, int64_t
     if (!d_w_gate || !d_w_up || !d_x || !d_y || m < 0 || n_rows < 0) { set_error(LB_ERR_ARG, "lowbit_mlp_cuda: null pointer or negative size"); return LB_ERR_ARG; }
     const bool fused = gemv_mlp_fused_supported(qtype, n_rows, k, m, x_dtype);
     const size_t base = (lowbit_matmul_workspace_size(n_rows, k, m, x_dtype) + 255) / 256 * 256;
-    const size_t need = base + (fused ? 0 : 2 * (size_t)m * n_rows * sizeof(float));
+    const size_t need = fused ? base : lowbit_mlp_workspace_size(n_rows, k, m, x_dtype);
     std::unique_lock<std::mutex> lk(g_mu, std::defer_lock);
     if (!workspace) {
         lk.lock();
@@ -260,6 +262,10 @@ int lowbit_mlp_cuda(const void* d_w_gate, const void* d_w_up, int qtype, int64_t
     if (fused) {
         rc = gemv_launch_ex(d_w_gate, d_w_up, act + 1, qtype, n_rows, k, d_x, x_dtype, m, d_y, y_dtype, nullptr, 0, workspace,
                             workspace_bytes, st);
+    } else if (use_skinny(qtype, n_rows, k, m, x_dtype) && workspace_bytes >= gemm_skinny_mlp_workspace_size(n_rows, k, m)) {
+        // 17..64 half-precision rows: both matrices in one pass of the skinny tensor-core kernel, act * up in its reduction launch
+        rc = gemm_skinny_mlp_launch(d_w_gate, d_w_up, act + 1, qtype, n_rows, k, d_x, x_dtype, m, d_y, y_dtype, workspace, workspace_bytes,
+                                    st, gemv_get_pdl());
     } else {
         // the two intermediates: fp32 behind the exact GEMV; behind the tensor-core kernels (whose contract rounds the weights to
         // the activation dtype anyway) in y's half-precision dtype -- half the bytes through the GEMM epilogue and the activation

@@ -27,6 +27,7 @@
 #include <mutex>
 #include "lowbit_common.cuh"
 #include "lowbit_internal.h"
+#include "gemv_args.h"       // apply_act
 
 namespace lowbit {
 
@@ -652,6 +653,7 @@ __device__ unsigned long long g_sk_ts[6][64];
 
 struct SkinnyArgs {
     const uint8_t* w;
+    const uint8_t* w2;       // fused MLP: a second matrix of the same shape; its feature tiles follow w's in the item sequence
     TiledGeom G;
     int M;
     float* part;             // [gridDim.x * max_seg][NTOK][128] fp32 partial tiles
@@ -712,7 +714,8 @@ skinny_kernel(const __grid_constant__ CUtensorMap xmap, const SkinnyArgs A) {
     const uint32_t lut = bars + 512 + 4 * lane;
     if constexpr (E::kLutBytes > 0) E::fill_lut(smem_raw + (bars + 512 - smem_u32(smem_raw)), threadIdx.x, kSkThreads);
     const int nb = (int)A.G.nb, np = nb >> 1;                // k-blocks / pairs of k-blocks per tile (nb is even)
-    const int64_t total = (A.G.rows / kTileN) * (int64_t)np;
+    const int n_ft1 = (int)(A.G.rows / kTileN);                    // feature tiles of one matrix
+    const int64_t total = (int64_t)(A.w2 ? 2 * n_ft1 : n_ft1) * np;
     const int64_t i_begin = (int64_t)blockIdx.x * total / gridDim.x, i_end = (int64_t)(blockIdx.x + 1) * total / gridDim.x;
     const int n_items = (int)(i_end - i_begin);
     const int ft0 = (int)(i_begin / np), p_first = (int)(i_begin - (int64_t)ft0 * np);
@@ -751,11 +754,12 @@ skinny_kernel(const __grid_constant__ CUtensorMap xmap, const SkinnyArgs A) {
                 mbar_expect_tx_w(full_bar(s), ((A.dbg & 4) ? 0 : SM::kX) + 2 * SM::kGroup, leader);
 #pragma unroll
                 for (int gi = 0; gi < 2; gi++) {
-                    const int64_t u = ((int64_t)ft * 2 + gi) * nb + kb;          // units kb and kb + 1 are adjacent in memory
+                    const uint8_t* wb = ft < n_ft1 ? A.w : A.w2;
+                    const int64_t u = ((int64_t)(ft < n_ft1 ? ft : ft - n_ft1) * 2 + gi) * nb + kb;   // units kb and kb + 1 are adjacent in memory
                     const uint32_t dst = pk + gi * SM::kGroup;
-                    bulk_g2s_w(dst, A.w + u * SM::kSuper, 2 * SM::kSuper, full_bar(s), leader);
-                    bulk_g2s_w(dst + 2 * SM::kSuper, A.w + A.G.off_s + u * 128, 256, full_bar(s), leader);
-                    if (E::kHasMin) bulk_g2s_w(dst + 2 * SM::kSuper + 256, A.w + A.G.off_m + u * 128, 256, full_bar(s), leader);
+                    bulk_g2s_w(dst, wb + u * SM::kSuper, 2 * SM::kSuper, full_bar(s), leader);
+                    bulk_g2s_w(dst + 2 * SM::kSuper, wb + A.G.off_s + u * 128, 256, full_bar(s), leader);
+                    if (E::kHasMin) bulk_g2s_w(dst + 2 * SM::kSuper + 256, wb + A.G.off_m + u * 128, 256, full_bar(s), leader);
                 }
             };
             auto acts = [&](int it) {                  // the k-slices of the activations: 2 x [NTOK tokens] x [64]
@@ -904,6 +908,7 @@ struct SkReduceArgs {
     const float* part; int max_seg, grid, np, ntok, M;
     int64_t total, n_cols;
     void* y; int y_dtype; const void* bias; int accumulate; int pdl;
+    int mlp_act, n_ft1;      // mlp_act != 0: y = act(tile ft) * (tile ft + n_ft1), the fused MLP's two matrices (1 SiLU, 2 GELU)
 };
 __global__ void __launch_bounds__(128) skinny_reduce_kernel(const SkReduceArgs A) {
     if (A.pdl) {
@@ -913,17 +918,26 @@ __global__ void __launch_bounds__(128) skinny_reduce_kernel(const SkReduceArgs A
     const int ft = blockIdx.x, f = threadIdx.x;
     // CTA of item i = the largest c with c * total / grid <= i
     auto cta_of = [&](int64_t i) { return (int)(((i + 1) * A.grid + A.total - 1) / A.total - 1); };
-    const int c_lo = cta_of((int64_t)ft * A.np), c_hi = cta_of((int64_t)(ft + 1) * A.np - 1);
     const int t0 = blockIdx.y * 8;
+    auto tile_sum = [&](int tile, float (&v)[8]) {       // the partial tiles of `tile`, in CTA order
+        const int c_lo = cta_of((int64_t)tile * A.np), c_hi = cta_of((int64_t)(tile + 1) * A.np - 1);
+#pragma unroll
+        for (int j = 0; j < 8; j++) v[j] = 0.0f;
+        for (int c = c_lo; c <= c_hi; c++) {
+            const int seg = tile - (int)(((int64_t)c * A.total / A.grid) / A.np);
+            const float* src = A.part + ((int64_t)c * A.max_seg + seg) * (A.ntok * 128) + f;
+#pragma unroll
+            for (int j = 0; j < 8; j++)
+                if (t0 + j < A.M) v[j] += src[(t0 + j) * 128];
+        }
+    };
     float v[8];
+    tile_sum(ft, v);
+    if (A.mlp_act) {                                     // fused MLP: act(gate) * up
+        float u[8];
+        tile_sum(ft + A.n_ft1, u);
 #pragma unroll
-    for (int j = 0; j < 8; j++) v[j] = 0.0f;
-    for (int c = c_lo; c <= c_hi; c++) {
-        const int seg = ft - (int)(((int64_t)c * A.total / A.grid) / A.np);
-        const float* src = A.part + ((int64_t)c * A.max_seg + seg) * (A.ntok * 128) + f;
-#pragma unroll
-        for (int j = 0; j < 8; j++)
-            if (t0 + j < A.M) v[j] += src[(t0 + j) * 128];
+        for (int j = 0; j < 8; j++) v[j] = apply_act(v[j], A.mlp_act) * u[j];
     }
     const int64_t col = (int64_t)ft * kTileN + f;
     float b = 0.0f;
@@ -1098,15 +1112,36 @@ size_t gemm_skinny_workspace_size(int64_t n_rows, int64_t k, int64_t m) {
     const int grid = sk_grid(total);
     return (size_t)grid * sk_max_seg(total, grid, np) * sk_ntok(m) * 128 * sizeof(float);
 }
+static int skinny_launch_impl(const void* w, const void* w2, int mlp_act, int qt, int64_t n_rows, int64_t k, const void* x, int x_dtype,
+                              int64_t m, void* y, int y_dtype, const void* bias, int accumulate, void* workspace, size_t workspace_bytes,
+                              cudaStream_t st, int pdl);
 int gemm_skinny_launch(const void* w, int qt, int64_t n_rows, int64_t k, const void* x, int x_dtype, int64_t m, void* y, int y_dtype,
                        const void* bias, int accumulate, void* workspace, size_t workspace_bytes, cudaStream_t st, int pdl) {
+    return skinny_launch_impl(w, nullptr, 0, qt, n_rows, k, x, x_dtype, m, y, y_dtype, bias, accumulate, workspace, workspace_bytes, st, pdl);
+}
+// fused MLP front half for 17..64 rows: y = act(x . Wgate^T) * (x . Wup^T); both matrices in ONE stream-K pass (their feature
+// tiles follow each other in the item sequence), the activation and the product in the reduction launch.  act: 1 SiLU, 2 GELU
+size_t gemm_skinny_mlp_workspace_size(int64_t n_rows, int64_t k, int64_t m) {
+    using namespace gemmtc;
+    const int64_t np = k / 128, total = 2 * (n_rows / 128) * np;
+    const int grid = sk_grid(total);
+    return (size_t)grid * sk_max_seg(total, grid, np) * sk_ntok(m) * 128 * sizeof(float);
+}
+int gemm_skinny_mlp_launch(const void* w_gate, const void* w_up, int act, int qt, int64_t n_rows, int64_t k, const void* x, int x_dtype,
+                           int64_t m, void* y, int y_dtype, void* workspace, size_t workspace_bytes, cudaStream_t st, int pdl) {
+    if (!w_up || act < 1 || act > 2 || ((uintptr_t)w_up & 15)) return LB_ERR_ARG;
+    return skinny_launch_impl(w_gate, w_up, act, qt, n_rows, k, x, x_dtype, m, y, y_dtype, nullptr, 0, workspace, workspace_bytes, st, pdl);
+}
+static int skinny_launch_impl(const void* w, const void* w2, int mlp_act, int qt, int64_t n_rows, int64_t k, const void* x, int x_dtype,
+                              int64_t m, void* y, int y_dtype, const void* bias, int accumulate, void* workspace, size_t workspace_bytes,
+                              cudaStream_t st, int pdl) {
     using namespace gemmtc;
     qt = canon_qtype(qt);
     if (!gemm_skinny_supported(qt, n_rows, k, m, x_dtype)) return LB_ERR_ARG;
     EncodeTiledFn enc = encode_fn();
     if (!enc) { set_error(LB_ERR_CUDA, "cuTensorMapEncodeTiled is not available from this driver"); return LB_ERR_CUDA; }
     if (((uintptr_t)x & 15) || ((uintptr_t)w & 15)) return LB_ERR_ARG;
-    if (!workspace || workspace_bytes < gemm_skinny_workspace_size(n_rows, k, m)) return LB_ERR_WORKSPACE;
+    if (!workspace || workspace_bytes < (w2 ? gemm_skinny_mlp_workspace_size(n_rows, k, m) : gemm_skinny_workspace_size(n_rows, k, m))) return LB_ERR_WORKSPACE;
     const bool bf = x_dtype == DT_BF16;
     const int ntok = sk_ntok(m);
     CUtensorMap map;
@@ -1119,8 +1154,8 @@ int gemm_skinny_launch(const void* w, int qt, int64_t n_rows, int64_t k, const v
                      CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) { set_error(LB_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d)", (int)r); return LB_ERR_CUDA; }
     SkinnyArgs A;
-    A.w = (const uint8_t*)w; A.G = make_geom(n_rows, k, qt); A.M = (int)m;
-    const int64_t np = k / 128, total = (n_rows / 128) * np;
+    A.w = (const uint8_t*)w; A.w2 = (const uint8_t*)w2; A.G = make_geom(n_rows, k, qt); A.M = (int)m;
+    const int64_t np = k / 128, total = (w2 ? 2 : 1) * (n_rows / 128) * np;
     const int grid = sk_grid(total);
     A.part = (float*)workspace; A.max_seg = sk_max_seg(total, grid, np); A.pdl = pdl;
     { static const int dbg = [] { const char* e = getenv("LOWBIT_SK_DBG"); return e ? atoi(e) : 0; }(); A.dbg = dbg; }
@@ -1139,6 +1174,7 @@ int gemm_skinny_launch(const void* w, int qt, int64_t n_rows, int64_t k, const v
     SkReduceArgs R;
     R.part = A.part; R.max_seg = A.max_seg; R.grid = grid; R.np = (int)np; R.ntok = ntok; R.M = (int)m;
     R.total = total; R.n_cols = n_rows; R.y = y; R.y_dtype = y_dtype; R.bias = bias; R.accumulate = accumulate; R.pdl = pdl;
+    R.mlp_act = w2 ? mlp_act : 0; R.n_ft1 = (int)(n_rows / 128);
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)(n_rows / 128), (unsigned)((m + 7) / 8)); cfg.blockDim = dim3(128); cfg.stream = st;
     cudaLaunchAttribute at[1];

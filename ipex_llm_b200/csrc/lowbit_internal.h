@@ -85,6 +85,9 @@ constexpr int64_t kGemvMaxM = 32;
 // the tensor-core GEMM with the operands swapped (weights = the 128-row operand, tokens = N): 9 <= m <= 128
 bool gemm_skinny_supported(int qt, int64_t n_rows, int64_t k, int64_t m, int x_dtype);
 size_t gemm_skinny_workspace_size(int64_t n_rows, int64_t k, int64_t m);
+size_t gemm_skinny_mlp_workspace_size(int64_t n_rows, int64_t k, int64_t m);
+int gemm_skinny_mlp_launch(const void* w_gate, const void* w_up, int act, int qt, int64_t n_rows, int64_t k, const void* x, int x_dtype,
+                           int64_t m, void* y, int y_dtype, void* workspace, size_t workspace_bytes, cudaStream_t st, int pdl);
 int gemm_skinny_launch(const void* w, int qt, int64_t n_rows, int64_t k, const void* x, int x_dtype, int64_t m, void* y, int y_dtype,
                        const void* bias, int accumulate, void* workspace, size_t workspace_bytes, cudaStream_t st, int pdl);
 

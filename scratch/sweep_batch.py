@@ -22,7 +22,7 @@ for qt in (sys.argv[1:] or ["fp8_e4m3", "fp6", "sym_int4"]):
     q = lbl.ggml_tensor_qtype[qt]
     ws = [dict(qkv=tiled(QKV, H, q), o=tiled(H, H, q), gate=tiled(I, H, q), up=tiled(I, H, q), down=tiled(H, I, q)) for _ in range(LAYERS)]
     nbytes = sum(t.numel() * t.element_size() for t in ws[0].values())
-    for M in (1, 2, 4, 8, 12, 16, 17, 24, 32):
+    for M in (1, 2, 4, 8, 9, 12, 16, 17, 24, 32):
         x = torch.randn(M, H, device=dev, generator=gen).half()
         qkv = torch.empty(M, QKV, device=dev, dtype=torch.float16)
         h = torch.zeros(M, H, device=dev, dtype=torch.float16)
