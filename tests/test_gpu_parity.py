@@ -439,6 +439,37 @@ def test_gemm_skinny_matches_oracle(lbl, cuda_device, qtype, xdt, tol, shape, M)
     assert (np.abs(y - y64) <= bound).all(), float((np.abs(y - y64) / bound).max())
 
 
+@pytest.mark.timeout(300)
+def test_gemm_skinny_random_shapes(lbl, cuda_device):
+    """forty seeded draws of (format, N, K, rows, dtype): N a multiple of 128, K of 128, 17..64 rows -- fewer items than SMs, one
+    pair of k-blocks per tile, ranges that span many tiles, bias / accumulate on some -- against float64 on the dequantised weights"""
+    rng = np.random.default_rng(1280)
+    qtypes = ["sym_int4", "asym_int4", "nf4", "fp8_e4m3", "fp8_e5m2", "fp6"]
+    for trial in range(40):
+        qtype = qtypes[trial % 6]
+        N = 128 * int(rng.integers(1, 20))
+        K = 128 * int(rng.integers(1, 24))
+        M = int(rng.integers(17, 65))
+        xdt = torch.float16 if trial % 2 == 0 else torch.bfloat16
+        w = torch.from_numpy(rand_w(rng, N, K)).to(cuda_device)
+        tiled = lbl.FP4Params(w, qtype=qid(qtype)).to(cuda_device).data
+        wd = lbl.dequantize_device_layout(tiled, (N, K), qid(qtype)).double()
+        x_t = torch.from_numpy(rng.standard_normal((M, K)).astype(np.float32)).to(xdt).to(cuda_device)
+        want = x_t.double() @ wd.T
+        bound = (1e-3 if xdt == torch.float16 else 8e-3) * (x_t.double().abs() @ wd.abs().T) + 1e-30
+        if trial % 3 == 0:
+            bias = torch.from_numpy(rng.standard_normal(N).astype(np.float32)).to(cuda_device)
+            out = torch.from_numpy(rng.standard_normal((M, N)).astype(np.float32)).to(cuda_device)
+            want = want + bias.double() + out.double()
+            lbl.lowbit_matmul(x_t, tiled, (N, K), qid(qtype), out=out, bias=bias, accumulate=True)
+            y = out
+        else:
+            y = lbl.lowbit_matmul(x_t, tiled, (N, K), qid(qtype), out_dtype=torch.float32)
+        assert lbl.ggml.last_launch_count() == 2, (trial, qtype, N, K, M)
+        err = (y.double() - want).abs()
+        assert bool((err <= bound + 1e-6 * want.abs()).all()), (trial, qtype, N, K, M, float((err / bound).max()))
+
+
 def test_gemm_skinny_epilogue_window_and_determinism(lbl, cuda_device):
     rng = np.random.default_rng(1260)
     N, K, M = 1024, 2048, 40
