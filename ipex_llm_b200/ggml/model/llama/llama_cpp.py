@@ -231,13 +231,13 @@ def _strides3(t):
 def lowbit_kv_quantize(src, dst, stream):
     """src float [B,H,S,D] -> dst uint8 view of the same shape (both with D contiguous)"""
     B, H, S, D = src.shape
-    _check(_lib.lowbit_kv_quantize_cuda(src.data_ptr(), _DT_OF[str(src.dtype)], _strides3(src), dst.data_ptr(), _strides3(dst),
+    _check(_lib.lowbit_kv_quantize_cuda(src.data_ptr(), _DT_OF[src.dtype], _strides3(src), dst.data_ptr(), _strides3(dst),
                                         B, H, S, D, stream), "lowbit_kv_quantize_cuda")
 
 
 def lowbit_kv_dequantize(src, dst, stream):
     B, H, S, D = src.shape
-    _check(_lib.lowbit_kv_dequantize_cuda(src.data_ptr(), _strides3(src), dst.data_ptr(), _DT_OF[str(dst.dtype)], _strides3(dst),
+    _check(_lib.lowbit_kv_dequantize_cuda(src.data_ptr(), _strides3(src), dst.data_ptr(), _DT_OF[dst.dtype], _strides3(dst),
                                           B, H, S, D, stream), "lowbit_kv_dequantize_cuda")
 
 
@@ -252,15 +252,25 @@ def lowbit_sdp_fp8_workspace_size(b, hq, hkv, s, l, d):
 def lowbit_sdp_fp8(q, k, v, mask, causal, scale, out, workspace, stream):
     B, Hq, S, D = q.shape
     Hkv, L = k.shape[1], k.shape[2]
-    _check(_lib.lowbit_sdp_fp8_cuda(q.data_ptr(), _DT_OF[str(q.dtype)], _strides3(q), k.data_ptr(), _strides3(k), v.data_ptr(),
+    _check(_lib.lowbit_sdp_fp8_cuda(q.data_ptr(), _DT_OF[q.dtype], _strides3(q), k.data_ptr(), _strides3(k), v.data_ptr(),
                                     _strides3(v), mask.data_ptr() if mask is not None else None,
-                                    _DT_OF[str(mask.dtype)] if mask is not None else 0,
+                                    _DT_OF[mask.dtype] if mask is not None else 0,
                                     _strides3(mask) if mask is not None else None, int(bool(causal)), float(scale),
-                                    B, Hq, Hkv, S, L, D, out.data_ptr(), _DT_OF[str(out.dtype)], workspace.data_ptr(),
+                                    B, Hq, Hkv, S, L, D, out.data_ptr(), _DT_OF[out.dtype], workspace.data_ptr(),
                                     workspace.numel() * workspace.element_size(), stream), "lowbit_sdp_fp8_cuda")
 
 
-_DT_OF = {"torch.float32": 0, "torch.float16": 1, "torch.bfloat16": 2}
+class _DtypeIds(dict):
+    """str(torch dtype) -> DT_* id; a dtype OBJECT is looked up once through its name and remembered (str() of a dtype costs
+    about as much as the rest of a binding's argument marshalling)"""
+
+    def __missing__(self, key):
+        val = dict.__getitem__(self, str(key))
+        self[key] = val
+        return val
+
+
+_DT_OF = _DtypeIds({"torch.float32": 0, "torch.float16": 1, "torch.bfloat16": 2})
 
 _lib.lowbit_mlp_workspace_size.argtypes = [ctypes.c_int64, ctypes.c_int64, ctypes.c_int64, ctypes.c_int]
 _lib.lowbit_mlp_workspace_size.restype = ctypes.c_size_t
@@ -379,11 +389,11 @@ def lowbit_rotary_inplaced(q, k, rotary_dim, two, inv_freq, position_ids, cos, s
         cs_strides = (ctypes.c_int64 * 2)(cos.stride(0) if cos.shape[0] > 1 else 0, cos.stride(1))
     _check(_lib.lowbit_rotary_inplaced_cuda(q.data_ptr(), _strides3(q), Hq, k.data_ptr() if k is not None else None,
                                             _strides3(k) if k is not None else None, k.shape[1] if k is not None else 0,
-                                            _DT_OF[str(q.dtype)], B, S, D, rotary_dim, int(bool(two)),
+                                            _DT_OF[q.dtype], B, S, D, rotary_dim, int(bool(two)),
                                             inv_freq.data_ptr() if inv_freq is not None else None,
                                             position_ids.data_ptr() if inv_freq is not None else None, pos_strides,
                                             cos.data_ptr() if cos is not None else None, sin.data_ptr() if sin is not None else None,
-                                            _DT_OF[str(cos.dtype)] if cos is not None else 0, cs_strides, int(bool(cs_interleaved)),
+                                            _DT_OF[cos.dtype] if cos is not None else 0, cs_strides, int(bool(cs_interleaved)),
                                             stream), "lowbit_rotary_inplaced_cuda")
 
 
@@ -440,7 +450,7 @@ def lowbit_comm_status(ptr):
 def lowbit_allreduce_sum(peer_ptrs, rank, max_bytes, src, dst, stream):
     arr = (ctypes.c_void_p * len(peer_ptrs))(*peer_ptrs)
     _check(_lib.lowbit_allreduce_sum_cuda(arr, rank, len(peer_ptrs), max_bytes, src.data_ptr(), dst.data_ptr(), src.numel(),
-                                          _DT_OF[str(src.dtype)], stream), "lowbit_allreduce_sum_cuda")
+                                          _DT_OF[src.dtype], stream), "lowbit_allreduce_sum_cuda")
 
 
 _lib.lowbit_matmul_allreduce_cuda.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_int64, ctypes.c_void_p, ctypes.c_int,
@@ -452,8 +462,8 @@ _lib.lowbit_matmul_allreduce_cuda.restype = ctypes.c_int
 
 def lowbit_matmul_allreduce(w, qtype, n_rows, k, x, y, bias, accumulate, peer_ptrs, rank, max_bytes, workspace, stream):
     arr = (ctypes.c_void_p * len(peer_ptrs))(*peer_ptrs)
-    _check(_lib.lowbit_matmul_allreduce_cuda(w.data_ptr(), qtype, n_rows, k, x.data_ptr(), _DT_OF[str(x.dtype)], x.shape[0],
-                                             y.data_ptr(), _DT_OF[str(y.dtype)], bias.data_ptr() if bias is not None else None,
+    _check(_lib.lowbit_matmul_allreduce_cuda(w.data_ptr(), qtype, n_rows, k, x.data_ptr(), _DT_OF[x.dtype], x.shape[0],
+                                             y.data_ptr(), _DT_OF[y.dtype], bias.data_ptr() if bias is not None else None,
                                              int(bool(accumulate)), arr, rank, len(peer_ptrs), max_bytes,
                                              workspace.data_ptr() if workspace is not None else None,
                                              workspace.numel() if workspace is not None else 0, stream), "lowbit_matmul_allreduce_cuda")
@@ -480,8 +490,8 @@ _lib.lowbit_greedy_advance_cuda.restype = ctypes.c_int
 def lowbit_rms_norm(x_2d, weight, eps, out, stream):
     """x_2d [rows, hidden] (last dim contiguous), weight [hidden] -> out [rows, hidden]"""
     rows, hidden = x_2d.shape
-    _check(_lib.lowbit_rms_norm_cuda(x_2d.data_ptr(), _DT_OF[str(x_2d.dtype)], x_2d.stride(0), weight.data_ptr(),
-                                     _DT_OF[str(weight.dtype)], float(eps), rows, hidden, out.data_ptr(), _DT_OF[str(out.dtype)],
+    _check(_lib.lowbit_rms_norm_cuda(x_2d.data_ptr(), _DT_OF[x_2d.dtype], x_2d.stride(0), weight.data_ptr(),
+                                     _DT_OF[weight.dtype], float(eps), rows, hidden, out.data_ptr(), _DT_OF[out.dtype],
                                      out.stride(0), stream), "lowbit_rms_norm_cuda")
 
 
@@ -489,8 +499,8 @@ def lowbit_rope_kv_append(qkv, n_heads, n_kv_heads, head_dim, cos, sin, pos, pos
     """qkv [B, S, (Hq + 2 Hkv) * D]; cos / sin [positions, >= D/2] tables; pos: int32 device scalar or None;
     k_cache / v_cache uint8 [B, Hkv, capacity, D]"""
     B, S = qkv.shape[0], qkv.shape[1]
-    _check(_lib.lowbit_rope_kv_append_cuda(qkv.data_ptr(), _DT_OF[str(qkv.dtype)], qkv.stride(0), qkv.stride(1), B, S, n_heads,
-                                           n_kv_heads, head_dim, cos.data_ptr(), sin.data_ptr(), _DT_OF[str(cos.dtype)],
+    _check(_lib.lowbit_rope_kv_append_cuda(qkv.data_ptr(), _DT_OF[qkv.dtype], qkv.stride(0), qkv.stride(1), B, S, n_heads,
+                                           n_kv_heads, head_dim, cos.data_ptr(), sin.data_ptr(), _DT_OF[cos.dtype],
                                            cos.stride(0), cos.shape[0], pos.data_ptr() if pos is not None else None, int(pos_add),
                                            k_cache.data_ptr(), _strides3(k_cache), v_cache.data_ptr(), _strides3(v_cache),
                                            k_cache.shape[2], stream), "lowbit_rope_kv_append_cuda")
@@ -500,16 +510,16 @@ def lowbit_sdp_fp8_devlen(q, k, v, causal, scale, kv_len, len_add, out, workspac
     """q [B, Hq, S, D] view; k / v uint8 [B, Hkv, capacity, D]; kv_len: int32 device scalar (keys = kv_len + len_add)"""
     B, Hq, S, D = q.shape
     Hkv, L_max = k.shape[1], k.shape[2]
-    _check(_lib.lowbit_sdp_fp8_devlen_cuda(q.data_ptr(), _DT_OF[str(q.dtype)], _strides3(q), k.data_ptr(), _strides3(k), v.data_ptr(),
+    _check(_lib.lowbit_sdp_fp8_devlen_cuda(q.data_ptr(), _DT_OF[q.dtype], _strides3(q), k.data_ptr(), _strides3(k), v.data_ptr(),
                                            _strides3(v), int(bool(causal)), float(scale), B, Hq, Hkv, S, L_max, kv_len.data_ptr(),
-                                           int(len_add), D, out.data_ptr(), _DT_OF[str(out.dtype)], workspace.data_ptr(),
+                                           int(len_add), D, out.data_ptr(), _DT_OF[out.dtype], workspace.data_ptr(),
                                            workspace.numel() * workspace.element_size(), stream), "lowbit_sdp_fp8_devlen_cuda")
 
 
 def lowbit_greedy_advance(logits, next_ids, tokens, state, stream, suppress_ids=None):
     """logits [B, V]; next_ids int64 [B]; tokens int64 [B, capacity]; state int32 [8]; suppress_ids int64 [8] or None"""
     B, V = logits.shape
-    _check(_lib.lowbit_greedy_advance_cuda(logits.data_ptr(), _DT_OF[str(logits.dtype)], logits.stride(0), B, V, next_ids.data_ptr(),
+    _check(_lib.lowbit_greedy_advance_cuda(logits.data_ptr(), _DT_OF[logits.dtype], logits.stride(0), B, V, next_ids.data_ptr(),
                                            tokens.data_ptr(), tokens.stride(0), tokens.shape[1], state.data_ptr(),
                                            suppress_ids.data_ptr() if suppress_ids is not None else None, stream),
            "lowbit_greedy_advance_cuda")
@@ -533,11 +543,11 @@ def lowbit_decode_attention(qkv, n_heads, n_kv_heads, head_dim, cos, sin, cache_
     """qkv [B, (Hq + 2 Hkv) * D] (or [B, 1, ...]); cos / sin [positions, >= D/2]; cache_len: int32 device scalar = tokens
     already cached; k_cache / v_cache uint8 [B, Hkv, capacity, D]; out [B, Hq, 1, D] contiguous"""
     B = qkv.shape[0]
-    _check(_lib.lowbit_decode_attention_cuda(qkv.data_ptr(), _DT_OF[str(qkv.dtype)], qkv.stride(0), B, n_heads, n_kv_heads, head_dim,
-                                             cos.data_ptr(), sin.data_ptr(), _DT_OF[str(cos.dtype)], cos.stride(0), cos.shape[0],
+    _check(_lib.lowbit_decode_attention_cuda(qkv.data_ptr(), _DT_OF[qkv.dtype], qkv.stride(0), B, n_heads, n_kv_heads, head_dim,
+                                             cos.data_ptr(), sin.data_ptr(), _DT_OF[cos.dtype], cos.stride(0), cos.shape[0],
                                              cache_len.data_ptr(), k_cache.data_ptr(), _strides3(k_cache), v_cache.data_ptr(),
                                              _strides3(v_cache), k_cache.shape[2], float(scale), out.data_ptr(),
-                                             _DT_OF[str(out.dtype)], int(bool(cache_complete)), workspace.data_ptr(),
+                                             _DT_OF[out.dtype], int(bool(cache_complete)), workspace.data_ptr(),
                                              workspace.numel() * workspace.element_size(), stream), "lowbit_decode_attention_cuda")
 
 
@@ -562,9 +572,9 @@ def lowbit_sdp_fp8_prefill(q, k, v, mask, causal, scale, out, stream):
     rows (any batch / head / token strides: a transposed view of a [B,S,Hq,D] buffer is written in place)"""
     B, Hq, S, D = q.shape
     Hkv, L = k.shape[1], k.shape[2]
-    _check(_lib.lowbit_sdp_fp8_prefill_strided_cuda(q.data_ptr(), _DT_OF[str(q.dtype)], _strides3(q), k.data_ptr(), _strides3(k), v.data_ptr(),
+    _check(_lib.lowbit_sdp_fp8_prefill_strided_cuda(q.data_ptr(), _DT_OF[q.dtype], _strides3(q), k.data_ptr(), _strides3(k), v.data_ptr(),
                                                     _strides3(v), mask.data_ptr() if mask is not None else None,
-                                                    _DT_OF[str(mask.dtype)] if mask is not None else 0,
+                                                    _DT_OF[mask.dtype] if mask is not None else 0,
                                                     _strides3(mask) if mask is not None else None, int(bool(causal)), float(scale),
-                                                    B, Hq, Hkv, S, L, D, out.data_ptr(), _DT_OF[str(out.dtype)], _strides3(out), stream),
+                                                    B, Hq, Hkv, S, L, D, out.data_ptr(), _DT_OF[out.dtype], _strides3(out), stream),
            "lowbit_sdp_fp8_prefill_cuda")

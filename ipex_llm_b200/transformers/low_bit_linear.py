@@ -14,6 +14,7 @@ Differences that are the point of this build:
     nf4 buffer is bf16-typed (LBL:139-145) and ``model.to(torch.float16)`` must not touch it.
 """
 import ctypes
+import functools
 import os
 from functools import reduce
 from operator import mul
@@ -46,6 +47,30 @@ def _check_qtype(qtype):
 
 def _stream_ptr(device):
     return ctypes.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+def _raw_stream(device):
+    """the current stream's handle as an int (the wrappers below run a few hundred times per prefill: every microsecond of
+    host time between two GEMMs is a microsecond the GPU may idle)"""
+    return torch._C._cuda_getCurrentRawStream(device.index if device.index is not None else torch.cuda.current_device())
+
+
+class _on_device:
+    """``with torch.cuda.device(dev)`` only when dev is not the current device already"""
+    __slots__ = ("ctx",)
+
+    def __init__(self, device):
+        idx = device.index
+        self.ctx = None if (idx is None or idx == torch.cuda.current_device()) else torch.cuda.device(device)
+
+    def __enter__(self):
+        if self.ctx is not None:
+            self.ctx.__enter__()
+
+    def __exit__(self, *exc):
+        if self.ctx is not None:
+            self.ctx.__exit__(*exc)
+        return False
 
 
 def get_block_size(qtype: str):
@@ -238,33 +263,37 @@ def lowbit_matmul(x_2d: torch.Tensor, weight: torch.Tensor, weight_shape, qtype:
     """
     N, K = weight_shape
     M = x_2d.shape[0]
-    invalidInputError(x_2d.dtype in _TORCH_TO_DT, f"unsupported activation dtype {x_2d.dtype}")
-    invalidInputError(x_2d.shape[1] == K, f"activation last dim {x_2d.shape[1]} != in_features {K}")
-    x_2d = x_2d.contiguous()
+    x_dt = _TORCH_TO_DT.get(x_2d.dtype)
+    if x_dt is None:
+        invalidInputError(False, f"unsupported activation dtype {x_2d.dtype}")
+    if x_2d.shape[1] != K:
+        invalidInputError(False, f"activation last dim {x_2d.shape[1]} != in_features {K}")
+    if not x_2d.is_contiguous():
+        x_2d = x_2d.contiguous()
     out_dtype = out_dtype or (out.dtype if out is not None else x_2d.dtype)
     if out is None:
         invalidInputError(not accumulate, "accumulate needs an output tensor")
         out = torch.empty((M, N), dtype=out_dtype, device=x_2d.device)
-    else:
-        invalidInputError(out.is_contiguous() and out.shape == (M, N) and out.dtype == out_dtype,
-                          "out must be a contiguous [M, N] tensor of out_dtype")
+    elif not (out.is_contiguous() and out.shape == (M, N) and out.dtype == out_dtype):
+        invalidInputError(False, "out must be a contiguous [M, N] tensor of out_dtype")
     if bias is not None and bias.dtype != out_dtype:
         bias = bias.to(out_dtype)
     if M == 0:
         return out
     w = weight.view(torch.uint8) if weight.dtype != torch.uint8 else weight
     dev = x_2d.device
-    need = ggml.lowbit_matmul_workspace_size(N, K, M, _TORCH_TO_DT[x_2d.dtype])
-    ws = _get_workspace(dev, need)
+    ws = _get_workspace(dev, _matmul_workspace_size(N, K, M, x_dt))
     if next_weight is not None:      # L2 prefetch hint: the weights the following matmul on this stream reads
         ggml.lowbit_hint_next_weights(ctypes.c_void_p(next_weight.data_ptr()), next_weight.numel() * next_weight.element_size())
-    with torch.cuda.device(dev):
-        ggml.lowbit_matmul_cuda(ctypes.c_void_p(w.data_ptr()), qtype, N, K,
-                                ctypes.c_void_p(x_2d.data_ptr()), _TORCH_TO_DT[x_2d.dtype], M,
-                                ctypes.c_void_p(out.data_ptr()), _TORCH_TO_DT[out_dtype],
-                                ctypes.c_void_p(bias.data_ptr()) if bias is not None else None,
-                                accumulate, ctypes.c_void_p(ws.data_ptr()), ws.numel(), _stream_ptr(dev))
+    with _on_device(dev):
+        ggml.lowbit_matmul_cuda(w.data_ptr(), qtype, N, K, x_2d.data_ptr(), x_dt, M, out.data_ptr(), _TORCH_TO_DT[out_dtype],
+                                bias.data_ptr() if bias is not None else None, accumulate, ws.data_ptr(), ws.numel(), _raw_stream(dev))
     return out
+
+
+@functools.lru_cache(maxsize=4096)
+def _matmul_workspace_size(N, K, M, x_dt):
+    return ggml.lowbit_matmul_workspace_size(N, K, M, x_dt)
 
 
 SILU = 0     # activation ids of the reference (transformers/models/utils.py: SILU / GELU)
@@ -529,13 +558,14 @@ class LowBitLinear(nn.Linear):
             return torch.empty(new_shape, dtype=x.dtype, device=x.device)   # LBL:668-670
         if self.act_order:
             x = x[..., self.g_idx_map]
-        x_2d = x.contiguous().view(-1, x.shape[-1])
+        x_2d = (x if x.is_contiguous() else x.contiguous()).view(-1, x.shape[-1])
         invalidInputError(self.weight.quantized, "LowBitLinear weight is not quantised yet: move the module "
                           "to a device first (FP4Params quantises in .to())")
+        wdata = self.weight.data
 
-        if self.weight.data.device.type == "cuda":
-            invalidInputError(x_2d.device == self.weight.data.device,
-                              f"activation on {x_2d.device}, weight on {self.weight.data.device}")
+        if wdata.device.type == "cuda":
+            if x_2d.device != wdata.device:
+                invalidInputError(False, f"activation on {x_2d.device}, weight on {wdata.device}")
             if x_2d.dtype not in _TORCH_TO_DT:
                 x_2d = x_2d.float()
             g = self.mp_group
@@ -543,7 +573,7 @@ class LowBitLinear(nn.Linear):
                     g.fused_supported(x_2d.shape[0], self.out_len, self.qtype):
                 # row-parallel decode: the GEMV pushes its partial sums to the peers itself; the bias is added once,
                 # after the sum (LBL:715-725)
-                result = g.matmul_all_reduce(x_2d, self.weight.data, self.weight_shape, self.qtype, bias=self.bias)
+                result = g.matmul_all_reduce(x_2d, wdata, self.weight_shape, self.qtype, bias=self.bias)
                 return result.view(new_shape).to(x.dtype)
             if x_2d.dtype == torch.float32 and self.conver_to_half and x_2d.shape[0] > GEMV_MAX_M:
                 # LBL:700-705: a prefill-sized fp32 batch is computed in half precision (tensor-core GEMM);
@@ -551,7 +581,7 @@ class LowBitLinear(nn.Linear):
                 x_2d = x_2d.half()
             fuse_bias = self.bias is not None and self.mp_group is None
             nxt = self.next_linear.weight.data if (self.next_linear is not None and x_2d.shape[0] <= GEMV_MAX_M) else None
-            result = lowbit_matmul(x_2d, self.weight.data, self.weight_shape, self.qtype,
+            result = lowbit_matmul(x_2d, wdata, self.weight_shape, self.qtype,
                                    bias=self.bias if fuse_bias else None, next_weight=nxt)
             result = result.view(new_shape)
             if self.mp_group is not None:
@@ -561,13 +591,13 @@ class LowBitLinear(nn.Linear):
         else:
             # weight on the CPU (canonical layout): the reference's CPU call path (LBL:726-754),
             # one call across the reference C ABI per forward; the arithmetic still runs on the GPU
-            result = ggml_matmul_src1_x_src0_t(self.weight.data, x_2d.cpu(), self.weight_shape, self.qtype)
+            result = ggml_matmul_src1_x_src0_t(wdata, x_2d.cpu(), self.weight_shape, self.qtype)
             result = result.view(new_shape).to(x.device)
             if self.mp_group is not None:
                 result = self._all_reduce(result)
             if self.bias is not None:
                 result += self.bias
-        return result.to(x.dtype)
+        return result if result.dtype == x.dtype else result.to(x.dtype)
 
 
 class vLLMLowBitLinear(LowBitLinear):

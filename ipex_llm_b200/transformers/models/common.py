@@ -11,10 +11,11 @@ import torch
 
 import ipex_llm_b200.ggml.model.llama.llama_cpp as ggml
 from ipex_llm_b200.utils.common import invalidInputError
+from ipex_llm_b200.transformers.low_bit_linear import _on_device
 
 
 def _stream(device):
-    return torch.cuda.current_stream(device).cuda_stream
+    return torch._C._cuda_getCurrentRawStream(device.index if device.index is not None else torch.cuda.current_device())
 
 
 def _check_qk(query_states, key_states):
@@ -165,6 +166,9 @@ def mlp_gelu_forward(self, x: torch.Tensor):
     return fuse_mlp_base(self, GELU, x)
 
 
+_RMS_DTYPES = (torch.float, torch.half, torch.bfloat16)
+
+
 def rms_norm_forward(self, hidden_states: torch.Tensor):
     """:187-205: xe_addons.rms_norm -> lowbit_rms_norm_cuda on the GPU, the torch statement elsewhere"""
     weight = self.weight
@@ -173,13 +177,13 @@ def rms_norm_forward(self, hidden_states: torch.Tensor):
         eps = getattr(self, "epsilon", None)
     if eps is None:
         eps = self.eps
-    if hidden_states.device.type == "cuda" and hidden_states.dtype in (torch.float, torch.half, torch.bfloat16) \
-            and weight.dtype in (torch.float, torch.half, torch.bfloat16):
+    if hidden_states.device.type == "cuda" and hidden_states.dtype in _RMS_DTYPES and weight.dtype in _RMS_DTYPES:
         x_2d = hidden_states.reshape(-1, hidden_states.size(-1))
         if x_2d.stride(-1) != 1:
             x_2d = x_2d.contiguous()
-        out = torch.empty(x_2d.shape, dtype=torch.promote_types(weight.dtype, x_2d.dtype), device=x_2d.device)
-        with torch.cuda.device(x_2d.device):
+        out_dtype = x_2d.dtype if weight.dtype == x_2d.dtype else torch.promote_types(weight.dtype, x_2d.dtype)
+        out = torch.empty(x_2d.shape, dtype=out_dtype, device=x_2d.device)
+        with _on_device(x_2d.device):
             ggml.lowbit_rms_norm(x_2d, weight, eps, out, _stream(x_2d.device))
         return out.reshape(hidden_states.shape)
     input_dtype = hidden_states.dtype
