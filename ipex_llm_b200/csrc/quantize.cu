@@ -309,47 +309,66 @@ quantize4_kernel(const float* __restrict__ src, uint8_t* __restrict__ dst, size_
                 const int srcl = LPB * sub + (bl ? (__ffs(bl) - 1) : bh ? (__ffs(bh) - 1) : 0);
                 return __shfl_sync(0xffffffffu, bl ? vl : vh, srcl);
             };
-            if (QT == QT_SYM_INT4 || QT == QT_NF4) {
-                uint32_t a[2 * EL];
-                uint32_t amax = 0u;
+            if (QT == QT_SYM_INT4) {
+                // the signed value of the first element with the largest |x|.  Largest positive and largest negated value
+                // (two FMNMX chains, NaNs drop out as in the serial `amax < fabsf(v)` scan): when they differ the winner's
+                // sign is known; only a block whose extremes are +a and -a needs the scan for the first of them (rare)
+                float pm = x[0], nm = -x[0];
 #pragma unroll
-                for (int i = 0; i < 2 * EL; i++) { a[i] = __float_as_uint(x[i]) & 0x7fffffffu; amax = max(amax, a[i]); }
-#pragma unroll
-                for (int o = 1; o < LPB; o <<= 1) amax = max(amax, __shfl_xor_sync(0xffffffffu, amax, o));
-                if (QT == QT_SYM_INT4) {
-                    bool hit[2 * EL];
-#pragma unroll
-                    for (int i = 0; i < 2 * EL; i++) hit[i] = a[i] == amax;
-                    const float val = first_hit(hit);                                      // the first element with |x| == max
-                    d = (amax != 0u) ? __fmul_rn(val, -0.125f) : -0.0f;                    // x / -8: exact as a product
-                    const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
-#pragma unroll
-                    for (int i = 0; i < 2 * EL; i++) q[i] = (uint32_t)min(15, (int)(signed char)(int)__fadd_rn(__fmul_rn(x[i], id), 8.5f));
-                } else {
-                    d = __uint_as_float(amax);
-                    const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
-#pragma unroll
-                    for (int i = 0; i < 2 * EL; i++) q[i] = nf4_encode(__fmul_rn(x[i], id));
-                }
-            } else {
-                uint32_t klo = 0xffffffffu, khi = 0u;
-#pragma unroll
-                for (int i = 0; i < 2 * EL; i++) { const uint32_t kk = ordered_key(x[i]); klo = min(klo, kk); khi = max(khi, kk); }
+                for (int i = 1; i < 2 * EL; i++) { pm = fmaxf(pm, x[i]); nm = fmaxf(nm, -x[i]); }
 #pragma unroll
                 for (int o = 1; o < LPB; o <<= 1) {
-                    klo = min(klo, __shfl_xor_sync(0xffffffffu, klo, o));
-                    khi = max(khi, __shfl_xor_sync(0xffffffffu, khi, o));
+                    pm = fmaxf(pm, __shfl_xor_sync(0xffffffffu, pm, o));
+                    nm = fmaxf(nm, __shfl_xor_sync(0xffffffffu, nm, o));
                 }
-                // back to floats; the serial scan keeps the FIRST element that compares equal to the extremum (-0 == +0)
-                const float lo_f = __uint_as_float((klo & 0x80000000u) ? (klo & 0x7fffffffu) : ~klo);
-                const float hi_f = __uint_as_float((khi & 0x80000000u) ? (khi & 0x7fffffffu) : ~khi);
-                bool hit[2 * EL];
+                const float am = fmaxf(pm, nm);
+                float val = pm > nm ? pm : -nm;
+                if (__any_sync(0xffffffffu, pm == nm && am > 0.0f)) {
+                    bool hit[2 * EL];
 #pragma unroll
-                for (int i = 0; i < 2 * EL; i++) hit[i] = x[i] == lo_f;
-                mn = first_hit(hit);
+                    for (int i = 0; i < 2 * EL; i++) hit[i] = fabsf(x[i]) == am;
+                    const float first = first_hit(hit);
+                    if (pm == nm) val = first;
+                }
+                d = (am > 0.0f) ? __fmul_rn(val, -0.125f) : -0.0f;                         // x / -8: exact as a product
+                const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
 #pragma unroll
-                for (int i = 0; i < 2 * EL; i++) hit[i] = x[i] == hi_f;
-                const float mx = first_hit(hit);
+                for (int i = 0; i < 2 * EL; i++) q[i] = (uint32_t)min(15, (int)(signed char)(int)__fadd_rn(__fmul_rn(x[i], id), 8.5f));
+            } else if (QT == QT_NF4) {
+                uint32_t amax = 0u;
+#pragma unroll
+                for (int i = 0; i < 2 * EL; i++) amax = max(amax, __float_as_uint(x[i]) & 0x7fffffffu);
+#pragma unroll
+                for (int o = 1; o < LPB; o <<= 1) amax = max(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+                d = __uint_as_float(amax);
+                const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
+#pragma unroll
+                for (int i = 0; i < 2 * EL; i++) q[i] = nf4_encode(__fmul_rn(x[i], id));
+            } else {
+                // min and max by value (FMNMX chains; NaNs drop out as in the serial `v < min` / `v > max` scans).  The serial
+                // scan keeps the FIRST element that compares equal to the extremum, which only matters for a zero extremum
+                // (-0 == +0, and the record stores min's sign bit): those blocks take the scan
+                float lo_f = x[0], hi_f = x[0];
+#pragma unroll
+                for (int i = 1; i < 2 * EL; i++) { lo_f = fminf(lo_f, x[i]); hi_f = fmaxf(hi_f, x[i]); }
+#pragma unroll
+                for (int o = 1; o < LPB; o <<= 1) {
+                    lo_f = fminf(lo_f, __shfl_xor_sync(0xffffffffu, lo_f, o));
+                    hi_f = fmaxf(hi_f, __shfl_xor_sync(0xffffffffu, hi_f, o));
+                }
+                mn = lo_f;
+                float mx = hi_f;
+                if (__any_sync(0xffffffffu, lo_f == 0.0f || hi_f == 0.0f)) {
+                    bool hit[2 * EL];
+#pragma unroll
+                    for (int i = 0; i < 2 * EL; i++) hit[i] = x[i] == lo_f;
+                    const float first_lo = first_hit(hit);
+#pragma unroll
+                    for (int i = 0; i < 2 * EL; i++) hit[i] = x[i] == hi_f;
+                    const float first_hi = first_hit(hit);
+                    if (lo_f == 0.0f) mn = first_lo;
+                    if (hi_f == 0.0f) mx = first_hi;
+                }
                 d = __fdiv_rn(__fsub_rn(mx, mn), 15.0f);
                 const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
 #pragma unroll

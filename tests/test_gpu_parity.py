@@ -97,6 +97,11 @@ def test_quantize_four_lanes_per_block_edge_cases(lbl, cuda_device, qtype, rows)
         blocks[5] = np.linspace(-1, 1, 64)                   # exact ties at .5 steps for some formats
     if nb > 6:
         blocks[6] = 0.25
+    if nb > 12:                                              # a zero extremum: the first of -0 / +0 in element order is kept
+        blocks[9] = np.abs(blocks[9]) + 0.1; blocks[9, 3] = 0.0; blocks[9, 40] = -0.0
+        blocks[10] = np.abs(blocks[10]) + 0.1; blocks[10, 35] = -0.0; blocks[10, 50] = 0.0
+        blocks[11] = -np.abs(blocks[11]) - 0.1; blocks[11, 7] = -0.0; blocks[11, 8] = 0.0
+        blocks[12] = -np.abs(blocks[12]) - 0.1; blocks[12, 60] = 0.0; blocks[12, 61] = -0.0
     w = blocks.reshape(rows, k).copy()
     want = oracle.quantize(w, qtype)
     got = as_np_u8(lbl.ggml_convert_qtype(torch.from_numpy(w).to(cuda_device), qid(qtype)))
