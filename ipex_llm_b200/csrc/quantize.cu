@@ -74,10 +74,39 @@ __device__ __forceinline__ uint32_t nf4_encode(float v) {
     return c;
 }
 
+// nf4_encode through a table of 32 bins of width 1/16 over [-1, 1): the 15 midpoints are more than 0.08 apart, so a bin holds
+// at most one.  Entry b = { 16 * (the midpoint inside [b/16 - 1, (b+1)/16 - 1), or +inf), number of midpoints below the
+// bin }.  v16 = 16 * v (exact: the caller multiplies by 16 / d's reciprocal, a power-of-two scaling of the same rounded
+// product), bin = floor(v16) clamped (NaN -> bin 0 -> code 0, like fifteen false compares), code = below + (v16 > mid16):
+// one exact compare decides, the same one the chain makes.  8 instructions per element instead of 31.
+__device__ __forceinline__ void nf4_bins_init(float2* bins, int b) {           // b = 0..31
+    const float lo = (float)(b - 16), hi = (float)(b - 15);
+    float m16 = __int_as_float(0x7f800000);
+    uint32_t below = 0;
+#pragma unroll
+    for (int i = 0; i < 15; i++) {
+        const float mid16 = __fmul_rn(__fmul_rn(__fadd_rn(kNF4Table[i], kNF4Table[i + 1]), 0.5f), 16.0f);
+        below += (mid16 < lo) ? 1u : 0u;
+        if (mid16 >= lo && mid16 < hi) m16 = mid16;
+    }
+    bins[b] = make_float2(m16, __uint_as_float(below));
+}
+__device__ __forceinline__ uint32_t nf4_encode_bins(float v16, const float2* bins) {
+    const float t = fminf(fmaxf(v16, -16.0f), 15.5f);                          // fmaxf drops a NaN
+    const float2 e = bins[__float2int_rd(t) + 16];
+    return __float_as_uint(e.y) + ((v16 > e.x) ? 1u : 0u);
+}
+
 static __device__ __constant__ float kSearchFactors[9] = {1.0f, 0.95f, 1.05f, 0.9f, 1.1f, 0.85f, 1.15f, 0.8f, 1.2f};
 
 constexpr int QUANT_WARPS = 8;
 constexpr int QUANT_GROUP = 8;      // consecutive blocks a warp takes at once: 8 records are a multiple of 16 bytes
+
+// |v| as bits (ordered like |v|); a NaN counts as 0: the serial scans' `amax < fabsf(v)` never takes one
+__device__ __forceinline__ uint32_t abs_bits(float v) {
+    const uint32_t u = __float_as_uint(v) & 0x7fffffffu;
+    return u > 0x7f800000u ? 0u : u;
+}
 
 // monotonic unsigned key of a float (a < b  <=>  key(a) < key(b); -0 < +0)
 __device__ __forceinline__ uint32_t ordered_key(float v) {
@@ -133,7 +162,7 @@ quantize_kernel(const float* __restrict__ src, uint8_t* __restrict__ dst, size_t
         uint8_t* out = s_rec[warp] + j * BS;
         uint32_t q0 = 0, q1 = 0;
         if (QT == QT_SYM_INT4) {
-            const uint32_t a0 = __float_as_uint(x0) & 0x7fffffffu, a1 = __float_as_uint(x1) & 0x7fffffffu;
+            const uint32_t a0 = abs_bits(x0), a1 = abs_bits(x1);
             const uint32_t amax = __reduce_max_sync(0xffffffffu, max(a0, a1));        // |x| bits order like |x|
             const float val = first_hit_value(a0 == amax, a1 == amax, x0, x1);        // the first element with |x| == max
             const float d = (amax != 0u) ? __fmul_rn(val, -0.125f) : -0.0f;      // x / -8: exact as a product
@@ -161,14 +190,14 @@ quantize_kernel(const float* __restrict__ src, uint8_t* __restrict__ dst, size_t
             }
             out[4 + lane] = (uint8_t)(q0 | (q1 << 4));
         } else if (QT == QT_NF4) {
-            const uint32_t a0 = __float_as_uint(x0) & 0x7fffffffu, a1 = __float_as_uint(x1) & 0x7fffffffu;
+            const uint32_t a0 = abs_bits(x0), a1 = abs_bits(x1);
             const float d = __uint_as_float(__reduce_max_sync(0xffffffffu, max(a0, a1)));
             const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
             q0 = nf4_encode(__fmul_rn(x0, id)); q1 = nf4_encode(__fmul_rn(x1, id));
             if (lane == 0) store_half_bits(out, d);
             out[2 + lane] = (uint8_t)(q0 | (q1 << 4));
         } else {
-            const uint32_t a0 = __float_as_uint(x0) & 0x7fffffffu, a1 = __float_as_uint(x1) & 0x7fffffffu;
+            const uint32_t a0 = abs_bits(x0), a1 = abs_bits(x1);
             const float amax = __uint_as_float(__reduce_max_sync(0xffffffffu, max(a0, a1)));
             const float d0 = __fdiv_rn(amax, fmt_max<QT>());
             float d = d0;
@@ -264,8 +293,13 @@ quantize4_kernel(const float* __restrict__ src, uint8_t* __restrict__ dst, size_
     constexpr int HDR = (QT == QT_ASYM_INT4) ? 4 : 2;
     static_assert(QT == QT_SYM_INT4 || QT == QT_ASYM_INT4 || QT == QT_NF4, "4-bit formats");
     __shared__ __align__(16) uint8_t s_rec[QUANT_WARPS][QG * BS];
+    __shared__ float2 s_bins[QT == QT_NF4 ? 32 : 1];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int sub = lane / LPB, ls = lane % LPB;
+    if (QT == QT_NF4) {
+        if (threadIdx.x < 32) nf4_bins_init(s_bins, threadIdx.x);
+        __syncthreads();
+    }
     const size_t ngroups = (nblk + QG - 1) / QG;
     const size_t wstride = (size_t)gridDim.x * QUANT_WARPS;
     for (size_t grp = (size_t)blockIdx.x * QUANT_WARPS + warp; grp < ngroups; grp += wstride) {
@@ -335,15 +369,22 @@ quantize4_kernel(const float* __restrict__ src, uint8_t* __restrict__ dst, size_
 #pragma unroll
                 for (int i = 0; i < 2 * EL; i++) q[i] = (uint32_t)min(15, (int)(signed char)(int)__fadd_rn(__fmul_rn(x[i], id), 8.5f));
             } else if (QT == QT_NF4) {
-                uint32_t amax = 0u;
+                d = 0.0f;                                                                  // fmaxf drops NaNs like `a > amax`
 #pragma unroll
-                for (int i = 0; i < 2 * EL; i++) amax = max(amax, __float_as_uint(x[i]) & 0x7fffffffu);
+                for (int i = 0; i < 2 * EL; i++) d = fmaxf(d, fabsf(x[i]));
 #pragma unroll
-                for (int o = 1; o < LPB; o <<= 1) amax = max(amax, __shfl_xor_sync(0xffffffffu, amax, o));
-                d = __uint_as_float(amax);
+                for (int o = 1; o < LPB; o <<= 1) d = fmaxf(d, __shfl_xor_sync(0xffffffffu, d, o));
                 const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
+                // 16 * (x * id) == x * (16 * id) bit for bit unless x * id is subnormal (both products then lie deep inside
+                // the bin around zero: same code) or 16 * id overflows (d below 2^-124: those warps take two products)
+                const float id16 = __fmul_rn(id, 16.0f);
+                if (__all_sync(0xffffffffu, id16 < 3.0e38f)) {
 #pragma unroll
-                for (int i = 0; i < 2 * EL; i++) q[i] = nf4_encode(__fmul_rn(x[i], id));
+                    for (int i = 0; i < 2 * EL; i++) q[i] = nf4_encode_bins(__fmul_rn(x[i], id16), s_bins);
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 2 * EL; i++) q[i] = nf4_encode_bins(__fmul_rn(__fmul_rn(x[i], id), 16.0f), s_bins);
+                }
             } else {
                 // min and max by value (FMNMX chains; NaNs drop out as in the serial `v < min` / `v > max` scans).  The serial
                 // scan keeps the FIRST element that compares equal to the extremum, which only matters for a zero extremum
@@ -434,12 +475,12 @@ quantize8_kernel(const float* __restrict__ src, uint8_t* __restrict__ dst, size_
         float x[16];
 #pragma unroll
         for (int v = 0; v < 4; v++) { x[4 * v] = raw[v].x; x[4 * v + 1] = raw[v].y; x[4 * v + 2] = raw[v].z; x[4 * v + 3] = raw[v].w; }
-        uint32_t amax = 0u;
+        float amax = 0.0f;                                                                 // fmaxf drops NaNs like `a > amax`
 #pragma unroll
-        for (int i = 0; i < 16; i++) amax = max(amax, __float_as_uint(x[i]) & 0x7fffffffu);
+        for (int i = 0; i < 16; i++) amax = fmaxf(amax, fabsf(x[i]));
 #pragma unroll
-        for (int o = 1; o < LPB; o <<= 1) amax = max(amax, __shfl_xor_sync(0xffffffffu, amax, o));
-        const float d = __fdiv_rn(__uint_as_float(amax), fmt_max<QT>());
+        for (int o = 1; o < LPB; o <<= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+        const float d = __fdiv_rn(amax, fmt_max<QT>());
         const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
         if (j < nb) {
             uint8_t* out = s_rec[warp] + j * BS;

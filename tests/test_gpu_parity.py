@@ -113,6 +113,44 @@ def test_quantize_four_lanes_per_block_edge_cases(lbl, cuda_device, qtype, rows)
     np.testing.assert_array_equal(got2, want)
 
 
+@pytest.mark.parametrize("amax", [1.0, 3.0, 0.7, 2.0 ** -100, 2.0 ** -125, 1e-40, 2.0 ** 100, 3.0e38])
+def test_quantize_nf4_thresholds(lbl, cuda_device, amax):
+    """nf4 codes come from a 32-bin table on the device and from fifteen compares in the oracle: values at, one ulp below
+    and one ulp above every midpoint between table entries and every bin edge (k/16), scaled by block maxima over the
+    whole exponent range (subnormal scale, overflowing reciprocal), plus NaN / inf elements -- same bytes"""
+    tab = np.array([-1.0, -0.6961928009986877, -0.5250730514526367, -0.39491748809814453, -0.28444138169288635,
+                    -0.18477343022823334, -0.09105003625154495, 0.0, 0.07958029955625534, 0.16093020141124725,
+                    0.24611230194568634, 0.33791524171829224, 0.44070982933044434, 0.5626170039176941,
+                    0.7229568362236023, 1.0], dtype=np.float32)
+    mids = ((tab[:-1] + tab[1:]).astype(np.float32) * np.float32(0.5)).astype(np.float32)
+    pts = np.concatenate([mids, np.arange(-16, 17, dtype=np.float32) / np.float32(16)])
+    pts = np.concatenate([pts, np.nextafter(pts, np.float32(-2)), np.nextafter(pts, np.float32(2)),
+                          np.nextafter(np.nextafter(pts, np.float32(2)), np.float32(2))]).astype(np.float32)
+    rng = np.random.default_rng(77)
+    with np.errstate(over="ignore", under="ignore"):
+        vals = (pts.astype(np.float64) * amax).astype(np.float32)
+        vals = np.concatenate([vals, (rng.uniform(-1, 1, 4096) * amax).astype(np.float32)])
+    vals = np.clip(vals, -np.float32(amax), np.float32(amax))
+    nb = (vals.size + 61) // 62
+    blocks = np.zeros((nb + 3, 64), dtype=np.float32)
+    flat = np.resize(vals, nb * 62).reshape(nb, 62)
+    blocks[:nb, 1:63] = flat
+    blocks[:nb, 0] = np.float32(amax)                        # the block maximum, first and last so that both halves hold one
+    blocks[:nb, 63] = -np.float32(amax)
+    blocks[nb, :] = flat[0, 0]; blocks[nb, 5] = np.nan       # a NaN element, an inf element, an all-inf block
+    blocks[nb + 1, :] = flat[0, 1]; blocks[nb + 1, 40] = np.inf
+    blocks[nb + 2, :] = -np.inf
+    rows = blocks.shape[0]
+    w = blocks.reshape(rows, 64).copy()
+    want = oracle.quantize(w, "nf4")
+    got = as_np_u8(lbl.ggml_convert_qtype(torch.from_numpy(w).to(cuda_device), qid("nf4")))
+    np.testing.assert_array_equal(got, want)
+    pad = torch.zeros(rows * 64 + 1, device=cuda_device)      # unaligned source: the one-warp-per-block kernel (compare chain)
+    pad[1:] = torch.from_numpy(w).to(cuda_device).flatten()
+    got2 = as_np_u8(lbl.ggml_convert_qtype(pad[1:].view(rows, 64), qid("nf4")))
+    np.testing.assert_array_equal(got2, want)
+
+
 @pytest.mark.parametrize("qtype", ["fp8_e4m3", "fp8_e5m2", "fp6"])
 def test_quantize_scale_search_bit_exact(lbl, cuda_device, qtype):
     rng = np.random.default_rng(300)
