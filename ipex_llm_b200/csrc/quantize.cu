@@ -448,13 +448,13 @@ quantize4_kernel(const float* __restrict__ src, uint8_t* __restrict__ dst, size_
     }
 }
 
-// fp8 (e4m3 / e5m2) without scale search: the same four-lanes-per-block mapping; lane l owns elements 16l..16l+15 = bytes
-// 16l..16l+15 of the record (one code per byte), four float4 loads, d = absmax / MAX.
+// fp8 (e4m3 / e5m2) and fp6 without scale search: the same four-lanes-per-block mapping; lane l owns elements 16l..16l+15 =
+// bytes 16l..16l+15 of the record (fp8: one code per byte) or 12l..12l+11 (fp6), four float4 loads, d = absmax / MAX.
 template <int QT>
 __global__ void __launch_bounds__(QUANT_WARPS * 32)
 quantize8_kernel(const float* __restrict__ src, uint8_t* __restrict__ dst, size_t nblk) {
-    static_assert(QT == QT_FP8_E4M3 || QT == QT_FP8_E5M2, "fp8 formats");
-    constexpr int LPB = 4, BPP = 32 / LPB, QG = 8, BS = 66;
+    static_assert(QT == QT_FP8_E4M3 || QT == QT_FP8_E5M2 || QT == QT_FP6, "fp8 / fp6 formats");
+    constexpr int LPB = 4, BPP = 32 / LPB, QG = 8, BS = (QT == QT_FP6) ? 50 : 66;
     __shared__ __align__(16) uint8_t s_rec[QUANT_WARPS][QG * BS];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int sub = lane / LPB, ls = lane % LPB;
@@ -484,11 +484,29 @@ quantize8_kernel(const float* __restrict__ src, uint8_t* __restrict__ dst, size_
         const float id = d != 0.0f ? __fdiv_rn(1.0f, d) : 0.0f;
         if (j < nb) {
             uint8_t* out = s_rec[warp] + j * BS;
-            uint8_t* o16 = out + 2 + 16 * ls;          // 66 j + 2 + 16 l: 2-byte aligned
+            if (QT == QT_FP6) {
+                // elements 16l..16l+15 = code groups 4l..4l+3 (4 codes -> 3 bytes, c0 | c1<<6 | c2<<12 | c3<<18) = bytes
+                // 12l..12l+11 of the payload; 50 j + 2 + 12 l is even: six 2-byte stores
+                uint8_t* o12 = out + 2 + 12 * ls;
+                uint32_t g[4];
 #pragma unroll
-            for (int i = 0; i < 16; i += 2) {
-                const uint32_t c0 = mini_encode<QT>(__fmul_rn(x[i], id)), c1 = mini_encode<QT>(__fmul_rn(x[i + 1], id));
-                *reinterpret_cast<unsigned short*>(o16 + i) = (unsigned short)(c0 | (c1 << 8));
+                for (int v = 0; v < 4; v++) {
+                    g[v] = 0;
+#pragma unroll
+                    for (int i = 0; i < 4; i++) g[v] |= (mini_encode<QT>(__fmul_rn(x[4 * v + i], id)) & 0x3f) << (6 * i);
+                }
+                const uint32_t w0 = g[0] | (g[1] << 24), w1 = (g[1] >> 8) | (g[2] << 16), w2 = (g[2] >> 16) | (g[3] << 8);
+                unsigned short* o = reinterpret_cast<unsigned short*>(o12);
+                o[0] = (unsigned short)w0; o[1] = (unsigned short)(w0 >> 16);
+                o[2] = (unsigned short)w1; o[3] = (unsigned short)(w1 >> 16);
+                o[4] = (unsigned short)w2; o[5] = (unsigned short)(w2 >> 16);
+            } else {
+                uint8_t* o16 = out + 2 + 16 * ls;      // 66 j + 2 + 16 l: 2-byte aligned
+#pragma unroll
+                for (int i = 0; i < 16; i += 2) {
+                    const uint32_t c0 = mini_encode<QT>(__fmul_rn(x[i], id)), c1 = mini_encode<QT>(__fmul_rn(x[i + 1], id));
+                    *reinterpret_cast<unsigned short*>(o16 + i) = (unsigned short)(c0 | (c1 << 8));
+                }
             }
             if (ls == 0) store_half_bits(out, d);
         }
@@ -526,13 +544,15 @@ int quantize_launch(const float* src, void* dst, int qt, size_t n, int k, int64_
     }
     size_t blocks = ((nblk + QUANT_GROUP - 1) / QUANT_GROUP + QUANT_WARPS - 1) / QUANT_WARPS;
     const size_t blocks4 = ((nblk + QUANT4_GROUP - 1) / QUANT4_GROUP + QUANT_WARPS - 1) / QUANT_WARPS;
-    if (!scale_search && !((uintptr_t)src & 15) && (qt == QT_FP8_E4M3 || qt == QT_FP8_E5M2)) {
-        static int c8[2] = {0, 0};
-        const int per = qt == QT_FP8_E4M3 ? resident_ctas(quantize8_kernel<QT_FP8_E4M3>, c8[0]) : resident_ctas(quantize8_kernel<QT_FP8_E5M2>, c8[1]);
+    if (!scale_search && !((uintptr_t)src & 15) && (qt == QT_FP8_E4M3 || qt == QT_FP8_E5M2 || qt == QT_FP6)) {
+        static int c8[3] = {0, 0, 0};
+        const int per = qt == QT_FP8_E4M3 ? resident_ctas(quantize8_kernel<QT_FP8_E4M3>, c8[0])
+                      : qt == QT_FP8_E5M2 ? resident_ctas(quantize8_kernel<QT_FP8_E5M2>, c8[1]) : resident_ctas(quantize8_kernel<QT_FP6>, c8[2]);
         const size_t cap8 = (size_t)sm_count() * per;
         const int grid8 = (int)(blocks > cap8 ? cap8 : blocks);
         if (qt == QT_FP8_E4M3) quantize8_kernel<QT_FP8_E4M3><<<grid8, QUANT_WARPS * 32, 0, st>>>(src, (uint8_t*)dst, nblk);
-        else quantize8_kernel<QT_FP8_E5M2><<<grid8, QUANT_WARPS * 32, 0, st>>>(src, (uint8_t*)dst, nblk);
+        else if (qt == QT_FP8_E5M2) quantize8_kernel<QT_FP8_E5M2><<<grid8, QUANT_WARPS * 32, 0, st>>>(src, (uint8_t*)dst, nblk);
+        else quantize8_kernel<QT_FP6><<<grid8, QUANT_WARPS * 32, 0, st>>>(src, (uint8_t*)dst, nblk);
         note_launch();
         return check_launch();
     }

@@ -72,7 +72,7 @@ def test_quantize_bit_exact_device_abi(lbl, cuda_device, qtype):
     np.testing.assert_array_equal(got, oracle.quantize(w, qtype))
 
 
-@pytest.mark.parametrize("qtype", ["sym_int4", "asym_int4", "nf4", "fp8_e4m3", "fp8_e5m2"])
+@pytest.mark.parametrize("qtype", ["sym_int4", "asym_int4", "nf4", "fp8_e4m3", "fp8_e5m2", "fp6"])
 @pytest.mark.parametrize("rows", [1, 7, 9, 33])
 def test_quantize_four_lanes_per_block_edge_cases(lbl, cuda_device, qtype, rows):
     """the device path of the 4-bit formats and of fp8 without scale search (four lanes per block, eight blocks per warp instruction): ragged block counts
