@@ -230,6 +230,37 @@ def test_relayout_roundtrip_and_device_dequant(lbl, cuda_device, qtype, rows):
     np.testing.assert_array_equal(deq, oracle.dequantize(as_np_u8(packed), (rows, k), qtype))
 
 
+@pytest.mark.parametrize("qtype", QTYPES)
+@pytest.mark.parametrize("rows,k", [(200, 1024), (64, 512), (136, 256), (320, 128), (192, 192), (128, 2048 + 1024)])
+def test_relayout_staged_equals_general(lbl, cuda_device, monkeypatch, qtype, rows, k):
+    """whole 64-row groups with an even block count go through the shared-memory staged relayout kernels (16 / 8 / 4 / 2
+    k-blocks per CTA by divisibility), tail rows and odd block counts through the byte-per-thread kernels: both give the
+    same tiled bytes, the way back restores the records, and the 8-elements-per-thread dequantise of either layout
+    equals the oracle"""
+    rng = np.random.default_rng(rows + k)
+    w = rand_w(rng, rows, k, "wide")
+    packed_np = oracle.quantize(w, qtype)
+    packed = torch.from_numpy(packed_np).to(cuda_device)
+    if qtype == "nf4":
+        packed = packed.view(torch.bfloat16)
+    n = rows * k
+    tiled = lbl.ggml_q_format_convet_cpu2xpu(packed, n, qid(qtype), shape=(rows, k))
+    back = lbl.ggml_q_format_convet_xpu2cpu(tiled, n, qid(qtype), shape=(rows, k))
+    monkeypatch.setenv("LOWBIT_RELAYOUT_GENERAL", "1")
+    tiled_g = lbl.ggml_q_format_convet_cpu2xpu(packed, n, qid(qtype), shape=(rows, k))
+    back_g = lbl.ggml_q_format_convet_xpu2cpu(tiled_g, n, qid(qtype), shape=(rows, k))
+    monkeypatch.delenv("LOWBIT_RELAYOUT_GENERAL")
+    np.testing.assert_array_equal(as_np_u8(tiled), as_np_u8(tiled_g))
+    np.testing.assert_array_equal(as_np_u8(back), packed_np.reshape(-1))
+    np.testing.assert_array_equal(as_np_u8(back_g), packed_np.reshape(-1))
+    want = oracle.dequantize(packed_np, (rows, k), qtype)
+    for dt in (torch.float32, torch.float16, torch.bfloat16):
+        deq = lbl.dequantize_device_layout(tiled, (rows, k), qid(qtype), dtype=dt)
+        assert torch.equal(deq.cpu(), torch.from_numpy(want).to(dt))
+    got = lbl.ggml_convert_fp32(packed, w.shape, w.size, qid(qtype)).cpu().numpy()
+    np.testing.assert_array_equal(got, want)
+
+
 def test_relayout_needs_row_length(native_lib):
     src = np.zeros(34 * 16, np.uint8); dst = np.zeros_like(src)
     native_lib._lib.b200_lowbit_set_row_length(0)
