@@ -150,58 +150,46 @@ template <int QT> struct RlFmt {
 // index of (row of the group, kb) in a super-tile's [g][r][h] scale block
 __device__ __forceinline__ int rl_scale_slot(int row) { return (row & 7) * 8 + (row >> 4) * 2 + ((row >> 3) & 1); }
 
+__device__ __forceinline__ void rl_cp_async4(uint32_t smem_dst, const void* gsrc) {      // LDGSTS.32: no register staging
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_dst), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void rl_cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
+// canonical -> tiled.  The 64 row segments go to shared memory AS THEY ARE with 4-byte asynchronous copies (every word of
+// the CTA in flight at once, any 4-byte alignment: k = 11008 gives 5848-byte rows); a lane's 16 code bytes start 2 bytes
+// off a word boundary in every other record, so they are read as five words and funnel-shifted.  Row stride = 8 words
+// (mod 32): the eight rows a warp reads fall into different banks (2-way conflicts at most).
 template <int QT>
-__global__ void __launch_bounds__(RL_THREADS)
-relayout_to_tiled_staged_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, TiledGeom G, int KB) {
+__global__ void __launch_bounds__(RL_THREADS, 4)
+relayout_to_tiled_staged_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, TiledGeom G, int KB, int RSW) {
     using F = RlFmt<QT>;
     extern __shared__ __align__(16) uint8_t rl_smem[];
-    const int RS = KB * F::CB + 32;
-    uint8_t* s_codes = rl_smem;                                                     // [64][RS]
-    unsigned short* s_hdr = reinterpret_cast<unsigned short*>(rl_smem + 64 * RS);   // [64][KB][HH]
+    uint32_t* raw = reinterpret_cast<uint32_t*>(rl_smem);                           // [64][RSW] words
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int64_t rg = blockIdx.x;
     const int kb0 = blockIdx.y * KB;
     const int SW = KB * F::BLK / 4;                                                 // words per row segment
-    // all loads of four row segments first (up to 20 words per thread in flight), then the split into code bytes / headers
-    constexpr int SWI = (F::KB_MAX * F::BLK / 4 + 31) / 32;                         // words per lane and row segment, at most
-    for (int rb = warp; rb < RG_ROWS; rb += 4 * (RL_THREADS / 32)) {
-        uint32_t v[4][SWI];
-#pragma unroll
-        for (int i = 0; i < 4; i++) {
-            const int row = rb + i * (RL_THREADS / 32);
-            const uint32_t* seg = reinterpret_cast<const uint32_t*>(src + ((rg * RG_ROWS + row) * G.nb + kb0) * F::BLK);
-#pragma unroll
-            for (int j = 0; j < SWI; j++) {
-                const int w = lane + 32 * j;
-                v[i][j] = w < SW ? __ldcs(seg + w) : 0u;
-            }
-        }
-#pragma unroll
-        for (int i = 0; i < 4; i++) {
-            const int row = rb + i * (RL_THREADS / 32);
-#pragma unroll
-            for (int j = 0; j < SWI; j++) {
-                const int w = lane + 32 * j;
-                if (w < SW) {
-#pragma unroll
-                    for (int part = 0; part < 2; part++) {
-                        const int u = 2 * w + part, kb = u / (F::BLK / 2), r = u % (F::BLK / 2);
-                        const unsigned short hv = (unsigned short)(v[i][j] >> (16 * part));
-                        if (r < F::HH) s_hdr[(row * KB + kb) * F::HH + r] = hv;
-                        else *reinterpret_cast<unsigned short*>(s_codes + row * RS + kb * F::CB + 2 * (r - F::HH)) = hv;
-                    }
-                }
-            }
-        }
+    const uint32_t raw_s = (uint32_t)__cvta_generic_to_shared(raw);
+    for (int row = warp; row < RG_ROWS; row += RL_THREADS / 32) {
+        const uint32_t* seg = reinterpret_cast<const uint32_t*>(src + ((rg * RG_ROWS + row) * G.nb + kb0) * F::BLK);
+        for (int w = lane; w < SW; w += 32) rl_cp_async4(raw_s + 4 * (row * RSW + w), seg + w);
     }
+    rl_cp_async_wait_all();
     __syncthreads();
     const int64_t u0 = rg * G.nb + kb0;
     uint8_t* q_out = dst + u0 * (int64_t)F::SCB;
+    // 16 code bytes at byte `byte` of row `row`'s segment
+    auto codes16 = [&](int row, int byte) -> uint4 {
+        const uint32_t* p = raw + row * RSW + (byte >> 2);
+        const uint32_t fs = (byte & 3) * 8;
+        const uint32_t w0 = p[0], w1 = p[1], w2 = p[2], w3 = p[3], w4 = p[4];       // p[4]: at worst the stride's padding
+        return make_uint4(__funnelshift_r(w0, w1, fs), __funnelshift_r(w1, w2, fs), __funnelshift_r(w2, w3, fs), __funnelshift_r(w3, w4, fs));
+    };
     if (F::IS4) {
         for (int item = tid; item < KB * 128; item += RL_THREADS) {                 // item = (kb, tile, lane): 16 output bytes
             const int kb = item >> 7, tr = (item >> 5) & 3, l = item & 31, g = l >> 2, t = l & 3;
-            const uint8_t* pa = s_codes + (tr * 16 + g) * RS + kb * 32 + (t & 1) * 16;
-            const uint4 a = *reinterpret_cast<const uint4*>(pa), b = *reinterpret_cast<const uint4*>(pa + 8 * RS);
+            const int byte = kb * F::BLK + F::HDR + (t & 1) * 16;
+            const uint4 a = codes16(tr * 16 + g, byte), b = codes16(tr * 16 + g + 8, byte);
             const int sh = (t >> 1) * 4;                                            // elements 32.. are the high nibbles
             auto word = [&](uint32_t wa, uint32_t wb) -> uint32_t {
                 const uint32_t x = (wa >> sh) & 0x0f0f0f0fu, y = (wb >> sh) & 0x0f0f0f0fu;   // codes of rows g / g+8, one per byte
@@ -215,31 +203,33 @@ relayout_to_tiled_staged_kernel(const uint8_t* __restrict__ src, uint8_t* __rest
     } else if (F::IS8) {
         for (int item = tid; item < KB * 256; item += RL_THREADS) {                 // item = (kb, tile, half, lane)
             const int kb = item >> 8, tr = (item >> 6) & 3, h = (item >> 5) & 1, l = item & 31, g = l >> 2, t = l & 3;
-            const uint4 v = *reinterpret_cast<const uint4*>(s_codes + (tr * 16 + g + 8 * h) * RS + kb * 64 + 16 * t);
-            __stcs(reinterpret_cast<uint4*>(q_out) + item, v);
+            __stcs(reinterpret_cast<uint4*>(q_out) + item, codes16(tr * 16 + g + 8 * h, kb * F::BLK + F::HDR + 16 * t));
         }
     } else {
+        const uint8_t* raw8 = rl_smem;
         for (int item = tid; item < KB * F::SCB / 4; item += RL_THREADS) {          // one output word
             const int o = item * 4, kb = o / F::SCB, rem = o % F::SCB, tr = rem / F::TCB, off = rem % F::TCB;
-            auto rec = [&](int r) { return s_codes + (tr * 16 + r) * RS + kb * F::CB; };
+            auto rec = [&](int r) { return raw8 + (tr * 16 + r) * RSW * 4 + kb * F::BLK + F::HDR; };
             uint32_t w = 0;
 #pragma unroll
             for (int i = 0; i < 4; i++) w |= tiled_q_byte(QT, off + i, rec) << (8 * i);
             __stcs(reinterpret_cast<uint32_t*>(q_out) + item, w);
         }
     }
+    const unsigned short* raw16 = reinterpret_cast<const unsigned short*>(rl_smem);
     unsigned short* s_out = reinterpret_cast<unsigned short*>(dst + G.off_s) + u0 * 64;
     unsigned short* m_out = reinterpret_cast<unsigned short*>(dst + G.off_m) + u0 * 64;
     for (int item = tid; item < KB * 64; item += RL_THREADS) {
         const int kb = item >> 6, e = item & 63, g = e >> 3, r = (e & 7) >> 1, h = e & 1;
         const int row = r * 16 + g + 8 * h;
-        s_out[item] = s_hdr[(row * KB + kb) * F::HH];
-        if (F::HH == 2) m_out[item] = s_hdr[(row * KB + kb) * F::HH + 1];
+        const unsigned short* hp = raw16 + row * RSW * 2 + kb * (F::BLK / 2);
+        s_out[item] = hp[0];
+        if (F::HH == 2) m_out[item] = hp[1];
     }
 }
 
 template <int QT>
-__global__ void __launch_bounds__(RL_THREADS)
+__global__ void __launch_bounds__(RL_THREADS, 3)
 relayout_to_canonical_staged_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, TiledGeom G, int KB) {
     using F = RlFmt<QT>;
     extern __shared__ __align__(16) uint8_t rl_smem[];
@@ -341,8 +331,10 @@ static bool relayout_staged_launch(const uint8_t* src, uint8_t* dst, const Tiled
     const dim3 grid((unsigned)(G.r64 / RG_ROWS), (unsigned)(G.nb / KB));
     const int RS = KB * F::CB + 32;
     if (to_device) {
-        const int smem = 64 * RS + 64 * KB * F::HDR;
-        relayout_to_tiled_staged_kernel<QT><<<grid, RL_THREADS, smem, st>>>(src, dst, G, KB);
+        const int SW = KB * F::BLK / 4;
+        const int RSW = SW + ((8 - SW % 32) + 32) % 32;                              // row stride = 8 words (mod 32)
+        const int smem = 64 * RSW * 4 + 16;
+        relayout_to_tiled_staged_kernel<QT><<<grid, RL_THREADS, smem, st>>>(src, dst, G, KB, RSW);
     } else {
         const int smem = 64 * RS + KB * F::SCB + KB * 128 * F::HH;
         // per device, and this is a load / save-time path: set on every call
