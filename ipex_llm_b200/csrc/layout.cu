@@ -160,7 +160,7 @@ __device__ __forceinline__ void rl_cp_async_wait_all() { asm volatile("cp.async.
 // off a word boundary in every other record, so they are read as five words and funnel-shifted.  Row stride = 8 words
 // (mod 32): the eight rows a warp reads fall into different banks (2-way conflicts at most).
 template <int QT>
-__global__ void __launch_bounds__(RL_THREADS, 4)
+__global__ void __launch_bounds__(RL_THREADS, 6)
 relayout_to_tiled_staged_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, TiledGeom G, int KB, int RSW) {
     using F = RlFmt<QT>;
     extern __shared__ __align__(16) uint8_t rl_smem[];
@@ -228,29 +228,25 @@ relayout_to_tiled_staged_kernel(const uint8_t* __restrict__ src, uint8_t* __rest
     }
 }
 
+// tiled -> canonical.  4-bit and 8-bit codes go from global memory through registers (16-byte loads, four items in
+// flight per thread) into canonical code bytes in shared memory; fp6 stages the super-tiles first and uses the general
+// position functions.  The rows then leave as coalesced 4-byte words put together from header and code halves.
 template <int QT>
-__global__ void __launch_bounds__(RL_THREADS, 3)
+__global__ void __launch_bounds__(RL_THREADS, RlFmt<QT>::IS4 || RlFmt<QT>::IS8 ? 4 : 3)
 relayout_to_canonical_staged_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, TiledGeom G, int KB) {
     using F = RlFmt<QT>;
+    constexpr bool DIRECT = F::IS4 || F::IS8;
     extern __shared__ __align__(16) uint8_t rl_smem[];
     const int RS = KB * F::CB + 32;
     uint8_t* s_codes = rl_smem;                                                     // [64][RS] canonical code bytes
-    uint8_t* s_til = rl_smem + 64 * RS;                                             // KB super-tiles as stored
-    unsigned short* s_sc = reinterpret_cast<unsigned short*>(s_til + KB * F::SCB);  // [HH][KB][64] scale blocks as stored
+    unsigned short* s_sc = reinterpret_cast<unsigned short*>(rl_smem + 64 * RS);    // [HH][KB][64] scale blocks as stored
+    uint8_t* s_til = rl_smem + 64 * RS + KB * 128 * F::HH;                          // fp6: KB super-tiles as stored
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int64_t rg = blockIdx.x;
     const int kb0 = blockIdx.y * KB;
     const int64_t u0 = rg * G.nb + kb0;
+    const uint8_t* q_in = src + u0 * (int64_t)F::SCB;
     {
-        const uint4* q_in = reinterpret_cast<const uint4*>(src + u0 * (int64_t)F::SCB);
-        const int n16 = KB * F::SCB / 16;
-        for (int i0 = tid; i0 < n16; i0 += 4 * RL_THREADS) {                        // four loads in flight per thread
-            uint4 v[4];
-#pragma unroll
-            for (int j = 0; j < 4; j++) { const int i = i0 + j * RL_THREADS; v[j] = i < n16 ? __ldcs(q_in + i) : make_uint4(0, 0, 0, 0); }
-#pragma unroll
-            for (int j = 0; j < 4; j++) { const int i = i0 + j * RL_THREADS; if (i < n16) reinterpret_cast<uint4*>(s_til)[i] = v[j]; }
-        }
         const uint4* s_in = reinterpret_cast<const uint4*>(src + G.off_s + u0 * 128);
         const uint4* m_in = reinterpret_cast<const uint4*>(src + G.off_m + u0 * 128);
         for (int i = tid; i < KB * 8; i += RL_THREADS) {
@@ -258,36 +254,71 @@ relayout_to_canonical_staged_kernel(const uint8_t* __restrict__ src, uint8_t* __
             if (F::HH == 2) reinterpret_cast<uint4*>(s_sc + KB * 64)[i] = __ldcs(m_in + i);
         }
     }
-    __syncthreads();
     if (F::IS4) {
-        for (int item = tid; item < KB * 64; item += RL_THREADS) {                  // item = (kb, tile, g, c): lanes (g, c) and (g, c + 2)
-            const int kb = item >> 6, tr = (item >> 4) & 3, g = (item >> 1) & 7, c = item & 1;
-            const uint8_t* tile = s_til + kb * F::SCB + tr * F::TCB;
-            const uint4 lo = *reinterpret_cast<const uint4*>(tile + 16 * (4 * g + c));
-            const uint4 hi = *reinterpret_cast<const uint4*>(tile + 16 * (4 * g + c + 2));
-            // per-byte codes of row g (rowsel 0) / g + 8 (rowsel 1) held by one word of the tiled layout
-            auto codes = [&](uint32_t w, int rowsel) -> uint32_t {
-                if (QT == QT_NF4) {
-                    const uint32_t t1 = __byte_perm(w, 0, rowsel ? 0x4341 : 0x4240);
-                    return (t1 | (t1 << 4)) & 0x0f0f0f0fu;
+        const int n_items = KB * 64;                                                // item = (kb, tile, g, c): lanes (g, c) and (g, c + 2)
+        for (int i0 = tid; i0 < n_items; i0 += 4 * RL_THREADS) {
+            uint4 lo[4], hi[4];
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const int item = i0 + j * RL_THREADS;
+                lo[j] = hi[j] = make_uint4(0, 0, 0, 0);
+                if (item < n_items) {
+                    const int kb = item >> 6, tr = (item >> 4) & 3, g = (item >> 1) & 7, c = item & 1;
+                    const uint8_t* tile = q_in + kb * F::SCB + tr * F::TCB;
+                    lo[j] = __ldcs(reinterpret_cast<const uint4*>(tile + 16 * (4 * g + c)));
+                    hi[j] = __ldcs(reinterpret_cast<const uint4*>(tile + 16 * (4 * g + c + 2)));
                 }
-                return __byte_perm((w >> (4 * rowsel)) & 0x0f0f0f0fu, 0, 0x3120);
-            };
-            uint4 ra, rb;
-            ra.x = codes(lo.x, 0) | (codes(hi.x, 0) << 4); rb.x = codes(lo.x, 1) | (codes(hi.x, 1) << 4);
-            ra.y = codes(lo.y, 0) | (codes(hi.y, 0) << 4); rb.y = codes(lo.y, 1) | (codes(hi.y, 1) << 4);
-            ra.z = codes(lo.z, 0) | (codes(hi.z, 0) << 4); rb.z = codes(lo.z, 1) | (codes(hi.z, 1) << 4);
-            ra.w = codes(lo.w, 0) | (codes(hi.w, 0) << 4); rb.w = codes(lo.w, 1) | (codes(hi.w, 1) << 4);
-            uint8_t* pa = s_codes + (tr * 16 + g) * RS + kb * 32 + 16 * c;
-            *reinterpret_cast<uint4*>(pa) = ra;
-            *reinterpret_cast<uint4*>(pa + 8 * RS) = rb;
+            }
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const int item = i0 + j * RL_THREADS;
+                if (item >= n_items) break;
+                const int kb = item >> 6, tr = (item >> 4) & 3, g = (item >> 1) & 7, c = item & 1;
+                // per-byte codes of row g (rowsel 0) / g + 8 (rowsel 1) held by one word of the tiled layout
+                auto codes = [&](uint32_t w, int rowsel) -> uint32_t {
+                    if (QT == QT_NF4) {
+                        const uint32_t t1 = __byte_perm(w, 0, rowsel ? 0x4341 : 0x4240);
+                        return (t1 | (t1 << 4)) & 0x0f0f0f0fu;
+                    }
+                    return __byte_perm((w >> (4 * rowsel)) & 0x0f0f0f0fu, 0, 0x3120);
+                };
+                uint4 ra, rb;
+                ra.x = codes(lo[j].x, 0) | (codes(hi[j].x, 0) << 4); rb.x = codes(lo[j].x, 1) | (codes(hi[j].x, 1) << 4);
+                ra.y = codes(lo[j].y, 0) | (codes(hi[j].y, 0) << 4); rb.y = codes(lo[j].y, 1) | (codes(hi[j].y, 1) << 4);
+                ra.z = codes(lo[j].z, 0) | (codes(hi[j].z, 0) << 4); rb.z = codes(lo[j].z, 1) | (codes(hi[j].z, 1) << 4);
+                ra.w = codes(lo[j].w, 0) | (codes(hi[j].w, 0) << 4); rb.w = codes(lo[j].w, 1) | (codes(hi[j].w, 1) << 4);
+                uint8_t* pa = s_codes + (tr * 16 + g) * RS + kb * 32 + 16 * c;
+                *reinterpret_cast<uint4*>(pa) = ra;
+                *reinterpret_cast<uint4*>(pa + 8 * RS) = rb;
+            }
         }
     } else if (F::IS8) {
-        for (int item = tid; item < KB * 256; item += RL_THREADS) {
-            const int kb = item >> 8, tr = (item >> 6) & 3, h = (item >> 5) & 1, l = item & 31, g = l >> 2, t = l & 3;
-            *reinterpret_cast<uint4*>(s_codes + (tr * 16 + g + 8 * h) * RS + kb * 64 + 16 * t) = reinterpret_cast<const uint4*>(s_til)[item];
+        const int n_items = KB * 256;                                               // item = (kb, tile, half, lane)
+        for (int i0 = tid; i0 < n_items; i0 += 4 * RL_THREADS) {
+            uint4 v[4];
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const int item = i0 + j * RL_THREADS;
+                v[j] = item < n_items ? __ldcs(reinterpret_cast<const uint4*>(q_in) + item) : make_uint4(0, 0, 0, 0);
+            }
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const int item = i0 + j * RL_THREADS;
+                if (item >= n_items) break;
+                const int kb = item >> 8, tr = (item >> 6) & 3, h = (item >> 5) & 1, l = item & 31, g = l >> 2, t = l & 3;
+                *reinterpret_cast<uint4*>(s_codes + (tr * 16 + g + 8 * h) * RS + kb * 64 + 16 * t) = v[j];
+            }
         }
     } else {
+        const int n16 = KB * F::SCB / 16;
+        for (int i0 = tid; i0 < n16; i0 += 4 * RL_THREADS) {                        // four loads in flight per thread
+            uint4 v[4];
+#pragma unroll
+            for (int j = 0; j < 4; j++) { const int i = i0 + j * RL_THREADS; v[j] = i < n16 ? __ldcs(reinterpret_cast<const uint4*>(q_in) + i) : make_uint4(0, 0, 0, 0); }
+#pragma unroll
+            for (int j = 0; j < 4; j++) { const int i = i0 + j * RL_THREADS; if (i < n16) reinterpret_cast<uint4*>(s_til)[i] = v[j]; }
+        }
+        __syncthreads();
         for (int item = tid; item < RG_ROWS * KB * (F::CB / 4); item += RL_THREADS) {   // one canonical code word (fp6: 4 bytes = part of 3-byte groups)
             const int wi = item % (F::CB / 4), kb = (item / (F::CB / 4)) % KB, row = item / (F::CB / 4) / KB;
             const uint8_t* tile = s_til + kb * F::SCB + (row >> 4) * F::TCB;
@@ -319,6 +350,7 @@ relayout_to_canonical_staged_kernel(const uint8_t* __restrict__ src, uint8_t* __
             __stcs(seg + w, v);
         }
     }
+    (void)DIRECT;
 }
 
 // the staged kernels take: whole 64-row groups, an even number of blocks per row, 16-byte aligned buffers
@@ -336,7 +368,7 @@ static bool relayout_staged_launch(const uint8_t* src, uint8_t* dst, const Tiled
         const int smem = 64 * RSW * 4 + 16;
         relayout_to_tiled_staged_kernel<QT><<<grid, RL_THREADS, smem, st>>>(src, dst, G, KB, RSW);
     } else {
-        const int smem = 64 * RS + KB * F::SCB + KB * 128 * F::HH;
+        const int smem = 64 * RS + KB * 128 * F::HH + ((F::IS4 || F::IS8) ? 0 : KB * F::SCB);
         // per device, and this is a load / save-time path: set on every call
         if (cudaFuncSetAttribute(relayout_to_canonical_staged_kernel<QT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024) != cudaSuccess) {
             cudaGetLastError();
