@@ -347,7 +347,42 @@ def quantize_numbers(dev, peaks):
     us = e0.elapsed_time(e1) * 1e3 / 20
     gbs = n_rows * k * (4 + BLK / 64) / (us * 1e-6) / 1e9
     peak = float(peaks.get("hbm_gbs", 6650.0))
-    return {"shape": [n_rows, k], "us": us, "GBps": gbs, "frac_of_hbm_peak": gbs / peak}
+    out = {"shape": [n_rows, k], "us": us, "GBps": gbs, "frac_of_hbm_peak": gbs / peak}
+
+    # the other load-time kernels of row (a): canonical records -> tiled device layout (2 x packed bytes) and the tiled
+    # layout -> fp16 (packed bytes + 2 B per element); four buffers in turn (107 MB of records, 403 MB of fp16)
+    packed = [torch.empty_like(dst) for _ in range(4)]
+    for src, p_ in zip(srcs, packed):
+        ggml.ggml_quantize_tensor_cuda(ctypes.c_void_p(src.data_ptr()), ctypes.c_void_p(p_.data_ptr()), 2, n_rows * k, k, None, False, st)
+    del srcs
+    tiled = [torch.empty_like(dst) for _ in range(4)]
+    dense = [torch.empty(n_rows, k, dtype=torch.float16, device=dev) for _ in range(4)]
+
+    def timed(fn):
+        fn()
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(5):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) * 1e3 / 20
+
+    def relayout():
+        for p_, t_ in zip(packed, tiled):
+            ggml.lowbit_relayout_cuda(ctypes.c_void_p(p_.data_ptr()), ctypes.c_void_p(t_.data_ptr()), n_rows, k, 2, True, st)
+
+    def dequant():
+        for t_, d_ in zip(tiled, dense):
+            ggml.lowbit_dequantize_device_layout_cuda(ctypes.c_void_p(t_.data_ptr()), ctypes.c_void_p(d_.data_ptr()), n_rows, k, 2, 1, st)
+
+    us_r = timed(relayout)
+    us_d = timed(dequant)
+    nbytes = dst.numel()
+    out["relayout_to_tiled"] = {"us": us_r, "GBps": 2 * nbytes / (us_r * 1e-6) / 1e9, "frac_of_hbm_peak": 2 * nbytes / (us_r * 1e-6) / 1e9 / peak}
+    out["dequantize_tiled_f16"] = {"us": us_d, "GBps": (nbytes + 2 * n_rows * k) / (us_d * 1e-6) / 1e9,
+                                   "frac_of_hbm_peak": (nbytes + 2 * n_rows * k) / (us_d * 1e-6) / 1e9 / peak}
+    return out
 
 
 def tp_numbers(args, dev, world, rank):

@@ -418,8 +418,8 @@ __global__ void dequant_kernel(const uint8_t* __restrict__ src, OutT* __restrict
 // once, 32-bit index arithmetic when the block count allows: the whole-matrix dequantise of both layouts.  The kernel above
 // (one element per thread, two 64-bit divisions each) stays for destinations that are not 16-byte aligned.
 template <int qt, typename OutT, bool TILED>
-__global__ void __launch_bounds__(256) dequant8_kernel(const uint8_t* __restrict__ src, OutT* __restrict__ dst, int64_t n_chunks,
-                                                       TiledGeom G) {
+__global__ void __launch_bounds__(256) dequant8_kernel(const uint8_t* __restrict__ src, OutT* __restrict__ dst, int64_t chunk0,
+                                                       int64_t n_chunks, TiledGeom G) {
     const int hdr = header_bytes(qt);
     __shared__ float s_nf4[16];                    // the constant-memory table serialises on divergent codes
     if (qt == QT_NF4) {
@@ -427,7 +427,7 @@ __global__ void __launch_bounds__(256) dequant8_kernel(const uint8_t* __restrict
         __syncthreads();
     }
     const bool small = G.rows * G.nb < (int64_t)0x7fffffff;
-    for (int64_t chunk = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; chunk < n_chunks;
+    for (int64_t chunk = chunk0 + blockIdx.x * (int64_t)blockDim.x + threadIdx.x; chunk < n_chunks;
          chunk += (int64_t)gridDim.x * blockDim.x) {
         const int64_t blk = chunk >> 3;
         const int j0 = (int)(chunk & 7) * 8;
@@ -467,6 +467,59 @@ __global__ void __launch_bounds__(256) dequant8_kernel(const uint8_t* __restrict
         uint4* o = reinterpret_cast<uint4*>(dst + chunk * 8);
 #pragma unroll
         for (int i = 0; i < (int)(8 * sizeof(OutT) / 16); i++) __stcs(o + i, reinterpret_cast<const uint4*>(out)[i]);
+    }
+}
+
+// The tiled layout of the 4-bit and 8-bit formats, whole 64-row groups: one thread per (16-row tile, lane) = the 16 code
+// bytes that lane owns in the GEMV (4-bit: 16 elements of rows g and g + 8; 8-bit: 16 elements of one row), one 16-byte
+// load, the two scales of the lane's rows from one 4-byte load, 32-byte (fp16) / 64-byte (fp32) runs per row that four
+// neighbouring lanes complete to 128 / 256 contiguous bytes.
+template <int QT, typename OutT>
+__global__ void __launch_bounds__(256) dequant_tiled_frag_kernel(const uint8_t* __restrict__ src, OutT* __restrict__ dst, TiledGeom G) {
+    using F = RlFmt<QT>;
+    __shared__ float s_nf4[16];
+    if (QT == QT_NF4) {
+        if (threadIdx.x < 16) s_nf4[threadIdx.x] = kNF4Table[threadIdx.x];
+        __syncthreads();
+    }
+    constexpr int PER_TILE = F::IS8 ? 64 : 32;                 // threads per tile
+    const int64_t n_items = G.nsuper * 4 * PER_TILE;
+    for (int64_t item = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; item < n_items; item += (int64_t)gridDim.x * blockDim.x) {
+        const int l = (int)(item & 31), g = l >> 2, t = l & 3;
+        const int h8 = F::IS8 ? (int)((item >> 5) & 1) : 0;
+        const int64_t tile_idx = item / PER_TILE;              // u * 4 + tr
+        const int tr = (int)(tile_idx & 3);
+        const int64_t u = tile_idx >> 2;
+        int64_t rg, kb;
+        if (G.nsuper < (int64_t)0x7fffffff) { const uint32_t q = (uint32_t)u / (uint32_t)G.nb; rg = q; kb = (uint32_t)u - q * (uint32_t)G.nb; }
+        else { rg = u / G.nb; kb = u % G.nb; }
+        const uint4 c = __ldcs(reinterpret_cast<const uint4*>(src + tile_idx * F::TCB + (F::IS8 ? 512 * h8 : 0) + 16 * l));
+        const uint32_t dd = *reinterpret_cast<const uint32_t*>(src + G.off_s + u * 128 + g * 16 + tr * 4);   // d of rows g, g + 8
+        uint32_t mm = 0;
+        if (F::HH == 2) mm = *reinterpret_cast<const uint32_t*>(src + G.off_m + u * 128 + g * 16 + tr * 4);
+        const uint32_t cw[4] = {c.x, c.y, c.z, c.w};
+        constexpr int NR = F::IS8 ? 1 : 2;                     // rows this thread writes
+#pragma unroll
+        for (int rr = 0; rr < NR; rr++) {
+            const int hsel = F::IS8 ? h8 : rr;
+            const float d = half_bits_to_float((uint16_t)(dd >> (16 * hsel)));
+            const float m = half_bits_to_float((uint16_t)(mm >> (16 * hsel)));
+            OutT out[16];
+#pragma unroll
+            for (int e = 0; e < 16; e++) {
+                uint32_t code;
+                if (F::IS8) code = (cw[e >> 2] >> (8 * (e & 3))) & 0xffu;
+                else if (QT == QT_NF4) code = (cw[e >> 2] >> (8 * (rr + 2 * ((e & 3) >> 1)) + 4 * (e & 1))) & 0x0fu;
+                else { const int i = e & 3, p = ((i >> 1) << 1) + rr + ((i & 1) << 2); code = (cw[e >> 2] >> (4 * p)) & 0x0fu; }
+                float v = __fmul_rn(QT == QT_NF4 ? s_nf4[code] : code_value(QT, code), d);
+                if (F::HH == 2) v = __fadd_rn(v, m);
+                out[e] = from_float<OutT>(v);
+            }
+            const int64_t row = rg * RG_ROWS + tr * 16 + g + 8 * hsel;
+            uint4* o = reinterpret_cast<uint4*>(dst + row * G.k + kb * QK + 16 * t);
+#pragma unroll
+            for (int i = 0; i < (int)(16 * sizeof(OutT) / 16); i++) __stcs(o + i, reinterpret_cast<const uint4*>(out)[i]);
+        }
     }
 }
 
@@ -540,13 +593,33 @@ int relayout_launch(const void* src, void* dst, int64_t rows, int64_t k, int qt,
 template <bool TILED>
 static int dequant_dispatch(const void* src, void* dst, int64_t n, TiledGeom G, int qt, int dt, cudaStream_t st) {
     if (!((uintptr_t)dst & 15)) {                          // n is a multiple of 64
-        const int grid = grid_for(n / 8, 256);
         if (dt != DT_F32 && dt != DT_F16 && dt != DT_BF16) return LB_ERR_ARG;
+        // the tiled layout of 4-bit / 8-bit codes: whole row groups by the fragment kernel, tail rows by the chunk kernel
+        int64_t chunk0 = 0;
+        if (TILED && qt != QT_FP6 && G.nsuper > 0 && !((uintptr_t)src & 15)) {
+            const int per_tile = (qt == QT_FP8_E4M3 || qt == QT_FP8_E5M2) ? 64 : 32;
+            const int grid = grid_for(G.nsuper * 4 * per_tile, 256);
+#define LOWBIT_DEQF(QT)                                                                                                          \
+    case QT:                                                                                                                     \
+        if (dt == DT_F32) dequant_tiled_frag_kernel<QT, float><<<grid, 256, 0, st>>>((const uint8_t*)src, (float*)dst, G);         \
+        else if (dt == DT_F16) dequant_tiled_frag_kernel<QT, __half><<<grid, 256, 0, st>>>((const uint8_t*)src, (__half*)dst, G);  \
+        else dequant_tiled_frag_kernel<QT, __nv_bfloat16><<<grid, 256, 0, st>>>((const uint8_t*)src, (__nv_bfloat16*)dst, G);      \
+        break;
+            switch (qt) {
+                LOWBIT_DEQF(QT_SYM_INT4) LOWBIT_DEQF(QT_ASYM_INT4) LOWBIT_DEQF(QT_NF4) LOWBIT_DEQF(QT_FP8_E4M3) LOWBIT_DEQF(QT_FP8_E5M2)
+                default: return LB_ERR_ARG;
+            }
+#undef LOWBIT_DEQF
+            note_launch();
+            chunk0 = G.r64 * G.k / 8;
+            if (chunk0 >= n / 8) return check_launch();
+        }
+        const int grid = grid_for(n / 8 - chunk0, 256);
 #define LOWBIT_DEQ8(QT)                                                                                                          \
     case QT:                                                                                                                     \
-        if (dt == DT_F32) dequant8_kernel<QT, float, TILED><<<grid, 256, 0, st>>>((const uint8_t*)src, (float*)dst, n / 8, G);    \
-        else if (dt == DT_F16) dequant8_kernel<QT, __half, TILED><<<grid, 256, 0, st>>>((const uint8_t*)src, (__half*)dst, n / 8, G); \
-        else dequant8_kernel<QT, __nv_bfloat16, TILED><<<grid, 256, 0, st>>>((const uint8_t*)src, (__nv_bfloat16*)dst, n / 8, G);  \
+        if (dt == DT_F32) dequant8_kernel<QT, float, TILED><<<grid, 256, 0, st>>>((const uint8_t*)src, (float*)dst, chunk0, n / 8, G);    \
+        else if (dt == DT_F16) dequant8_kernel<QT, __half, TILED><<<grid, 256, 0, st>>>((const uint8_t*)src, (__half*)dst, chunk0, n / 8, G); \
+        else dequant8_kernel<QT, __nv_bfloat16, TILED><<<grid, 256, 0, st>>>((const uint8_t*)src, (__nv_bfloat16*)dst, chunk0, n / 8, G);  \
         break;
         switch (qt) {
             LOWBIT_DEQ8(QT_SYM_INT4) LOWBIT_DEQ8(QT_ASYM_INT4) LOWBIT_DEQ8(QT_NF4)
