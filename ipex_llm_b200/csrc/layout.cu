@@ -527,33 +527,56 @@ __global__ void __launch_bounds__(256) dequant_tiled_frag_kernel(const uint8_t* 
 // xe_linear.dequantize_rows): out[t][:] = dequant(W[ids[t]][:]); an index outside [0, rows) gives a zero row.
 template <typename OutT>
 __global__ void dequant_rows_kernel(const uint8_t* __restrict__ src, OutT* __restrict__ dst, const void* __restrict__ ids,
-                                    int ids_i64, int64_t n_ids, TiledGeom G, int qt) {
+                                    int ids_i64, int64_t n_ids, TiledGeom G, int qt, int vec) {
+    // eight consecutive elements of one block per thread (16-byte stores when `vec`: the destination is 16-byte aligned)
     const int hdr = header_bytes(qt);
-    const int64_t n_elems = n_ids * G.k;
-    for (int64_t idx = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; idx < n_elems;
-         idx += (int64_t)gridDim.x * blockDim.x) {
-        const int64_t t = idx / G.k, col = idx % G.k;
+    const int64_t cpr = G.k / 8;                                   // chunks per row
+    const int64_t n_chunks = n_ids * cpr;
+    for (int64_t chunk = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; chunk < n_chunks;
+         chunk += (int64_t)gridDim.x * blockDim.x) {
+        int64_t t, c;
+        if (n_chunks < (int64_t)0x7fffffff) { const uint32_t q = (uint32_t)chunk / (uint32_t)cpr; t = q; c = (uint32_t)chunk - q * (uint32_t)cpr; }
+        else { t = chunk / cpr; c = chunk % cpr; }
         const int64_t row = ids_i64 ? ((const long long*)ids)[t] : (long long)((const int*)ids)[t];
-        if (row < 0 || row >= G.rows) { dst[idx] = from_float<OutT>(0.0f); continue; }
-        const int64_t kb = col / QK;
-        const int j = (int)(col % QK);
-        uint32_t code; uint16_t dh, mh = 0;
-        if (row < G.r64) {
-            code = tiled_code(qt, src + tile_code_offset(G, row, kb), (int)(row % 16), j);
-            dh = *(const uint16_t*)(src + G.off_s + scale_offset(G, row, kb));
-            if (G.has_m) mh = *(const uint16_t*)(src + G.off_m + scale_offset(G, row, kb));
+        OutT out[8];
+        if (row < 0 || row >= G.rows) {
+#pragma unroll
+            for (int i = 0; i < 8; i++) out[i] = from_float<OutT>(0.0f);
         } else {
-            const uint8_t* rec = src + G.off_tail + ((row - G.r64) * G.nb + kb) * G.blk_bytes;
-            dh = (uint16_t)rec[0] | ((uint16_t)rec[1] << 8);
-            if (G.has_m) mh = (uint16_t)rec[2] | ((uint16_t)rec[3] << 8);
-            code = canonical_code(qt, rec + hdr, j);
+            const int64_t kb = c >> 3;
+            const int j0 = (int)(c & 7) * 8;
+            const uint8_t* rec = nullptr;
+            const uint8_t* tile = nullptr;
+            uint16_t dh, mh = 0;
+            if (row < G.r64) {
+                tile = src + tile_code_offset(G, row, kb);
+                const int64_t so = scale_offset(G, row, kb);
+                dh = *(const uint16_t*)(src + G.off_s + so);
+                if (G.has_m) mh = *(const uint16_t*)(src + G.off_m + so);
+            } else {
+                rec = src + G.off_tail + ((row - G.r64) * G.nb + kb) * G.blk_bytes;
+                dh = (uint16_t)rec[0] | ((uint16_t)rec[1] << 8);
+                if (G.has_m) mh = (uint16_t)rec[2] | ((uint16_t)rec[3] << 8);
+            }
+            const float d = half_bits_to_float(dh), m = half_bits_to_float(mh);
+#pragma unroll
+            for (int i = 0; i < 8; i++) {
+                const uint32_t code = rec ? canonical_code(qt, rec + hdr, j0 + i) : tiled_code(qt, tile, (int)(row & 15), j0 + i);
+                float v = __fmul_rn(code_value(qt, code), d);
+                if (G.has_m) v = __fadd_rn(v, m);
+                out[i] = from_float<OutT>(v);
+            }
         }
-        float v = __fmul_rn(code_value(qt, code), half_bits_to_float(dh));
-        if (G.has_m) v = __fadd_rn(v, half_bits_to_float(mh));
-        dst[idx] = from_float<OutT>(v);
+        OutT* o = dst + chunk * 8;
+        if (vec) {
+#pragma unroll
+            for (int i = 0; i < (int)(8 * sizeof(OutT) / 16); i++) reinterpret_cast<uint4*>(o)[i] = reinterpret_cast<const uint4*>(out)[i];
+        } else {
+#pragma unroll
+            for (int i = 0; i < 8; i++) o[i] = out[i];
+        }
     }
 }
-
 
 int relayout_launch(const void* src, void* dst, int64_t rows, int64_t k, int qt, bool to_device,
                     cudaStream_t st) {
@@ -662,11 +685,12 @@ int dequant_rows_launch(const void* src, void* dst, const void* ids, int ids_i64
     if (!supported(qt) || k <= 0 || k % QK || rows <= 0 || n_ids < 0) return LB_ERR_ARG;
     if (n_ids == 0) return LB_OK;
     const TiledGeom G = make_geom(rows, k, qt);
-    const int grid = grid_for(n_ids * k, 256);
+    const int grid = grid_for(n_ids * (k / 8), 256);
+    const int vec = ((uintptr_t)dst & 15) ? 0 : 1;
     switch (out_dtype) {
-        case DT_F32: dequant_rows_kernel<float><<<grid, 256, 0, st>>>((const uint8_t*)src, (float*)dst, ids, ids_i64, n_ids, G, qt); break;
-        case DT_F16: dequant_rows_kernel<__half><<<grid, 256, 0, st>>>((const uint8_t*)src, (__half*)dst, ids, ids_i64, n_ids, G, qt); break;
-        case DT_BF16: dequant_rows_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>((const uint8_t*)src, (__nv_bfloat16*)dst, ids, ids_i64, n_ids, G, qt); break;
+        case DT_F32: dequant_rows_kernel<float><<<grid, 256, 0, st>>>((const uint8_t*)src, (float*)dst, ids, ids_i64, n_ids, G, qt, vec); break;
+        case DT_F16: dequant_rows_kernel<__half><<<grid, 256, 0, st>>>((const uint8_t*)src, (__half*)dst, ids, ids_i64, n_ids, G, qt, vec); break;
+        case DT_BF16: dequant_rows_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>((const uint8_t*)src, (__nv_bfloat16*)dst, ids, ids_i64, n_ids, G, qt, vec); break;
         default: return LB_ERR_ARG;
     }
     note_launch();
