@@ -273,8 +273,13 @@ int lowbit_mlp_cuda(const void* d_w_gate, const void* d_w_up, int qtype, int64_t
         const int t_dtype = (tc && y_dtype != DT_F32) ? y_dtype : DT_F32;
         char* tg = (char*)workspace + base;
         char* tu = tg + (size_t)m * n_rows * (t_dtype == DT_F32 ? 4 : 2);
-        rc = matmul_dispatch(d_w_gate, qtype, n_rows, k, d_x, x_dtype, m, tg, t_dtype, nullptr, 0, workspace, base, st);
-        if (!rc) rc = matmul_dispatch(d_w_up, qtype, n_rows, k, d_x, x_dtype, m, tu, t_dtype, nullptr, 0, workspace, base, st);
+        if (m > 128 && (n_rows % 128) == 0 && use_gemm(qtype, n_rows, k, m, x_dtype)) {
+            // prefill sizes: gate and up from one grid of the tensor-core kernel (one set of rounds over the SMs instead of two)
+            rc = gemm_tc_pair_launch(d_w_gate, d_w_up, qtype, n_rows, k, d_x, x_dtype, m, tg, tu, t_dtype, workspace, base, st);
+        } else {
+            rc = matmul_dispatch(d_w_gate, qtype, n_rows, k, d_x, x_dtype, m, tg, t_dtype, nullptr, 0, workspace, base, st);
+            if (!rc) rc = matmul_dispatch(d_w_up, qtype, n_rows, k, d_x, x_dtype, m, tu, t_dtype, nullptr, 0, workspace, base, st);
+        }
         if (!rc) rc = act_mul_launch(tg, tu, t_dtype, d_y, y_dtype, m * n_rows, act + 1, st);
     }
     if (rc == LB_ERR_ARG) set_error(rc, "lowbit_mlp_cuda: bad argument (qtype %d, N %lld, K %lld, M %lld)", qtype, (long long)n_rows, (long long)k, (long long)m);

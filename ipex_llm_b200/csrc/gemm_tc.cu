@@ -284,6 +284,8 @@ template <> struct Expand<QT_NF4> {
 
 struct GemmArgs {
     const uint8_t* w;
+    const uint8_t* w2;       // a second matrix of the same shape / qtype (gate and up of an MLP) or NULL: its feature tiles
+    void* y2;                // follow w's in the tile order and go to y2 -- one grid, one set of rounds over the SMs
     TiledGeom G;
     int M;
     void* y; int y_dtype;
@@ -310,11 +312,11 @@ template <int QT> struct Smem {
 // 32 consecutive features of one token: 64 bytes (fp16 / bf16) or 128 bytes (fp32), written with
 // 16-byte stores (n0 is a multiple of 32 and N of 128, so the run is 64-byte aligned).  Scalar
 // 2-byte stores cost one 32-byte sector transaction each: 16x the traffic.
-__device__ __forceinline__ void store_vals(const GemmArgs& A, int64_t token, int64_t n0, float (&v)[32]) {
+__device__ __forceinline__ void store_vals(const GemmArgs& A, void* ybase, int64_t token, int64_t n0, float (&v)[32]) {
     const int64_t N = A.G.rows;
     const int64_t idx = token * N + n0;
     if (A.y_dtype == DT_F32) {
-        float4* p = reinterpret_cast<float4*>((float*)A.y + idx);
+        float4* p = reinterpret_cast<float4*>((float*)ybase + idx);
         const float4* bp = reinterpret_cast<const float4*>((const float*)A.bias + n0);
 #pragma unroll
         for (int i = 0; i < 8; i++) {
@@ -335,7 +337,7 @@ __device__ __forceinline__ void store_vals(const GemmArgs& A, int64_t token, int
         __nv_bfloat162 b = __floats2bfloat162_rn(lo, hi);
         return *reinterpret_cast<uint32_t*>(&b);
     };
-    uint4* p = reinterpret_cast<uint4*>((uint16_t*)A.y + idx);
+    uint4* p = reinterpret_cast<uint4*>((uint16_t*)ybase + idx);
     const uint4* bp = reinterpret_cast<const uint4*>((const uint16_t*)A.bias + n0);
 #pragma unroll
     for (int i = 0; i < 4; i++) {
@@ -384,7 +386,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap xmap, const GemmArgs A) {
     const uint32_t lut = bars + 256 + 4 * lane;
     if constexpr (E::kLutBytes > 0) E::fill_lut(smem_raw + (bars + 256 - smem_u32(smem_raw)), threadIdx.x, kThreads);   // visible after the __syncthreads below
     const int nb = (int)A.G.nb;
-    const int n_ftiles = (int)(A.G.rows / kTileN);
+    const int n_ft1 = (int)(A.G.rows / kTileN);
+    const int n_ftiles = A.w2 ? 2 * n_ft1 : n_ft1;         // the second matrix's feature tiles follow the first's
     const int n_tiles = n_ftiles * ((A.M + 128 * MT - 1) / (128 * MT));
     // work units = tiles x K splits (A.ksplit > 1 when the tiles alone would leave most SMs idle); split ks covers the
     // k-blocks [kb_begin(ks), kb_begin(ks + 1))
@@ -416,7 +419,8 @@ gemm_kernel(const __grid_constant__ CUtensorMap xmap, const GemmArgs A) {
             for (int unit = blockIdx.x; unit < n_units; unit += gridDim.x) {
                 const int tile = unit % n_tiles, ks = unit / n_tiles;
                 const int ftile = tile % n_ftiles, m0 = (tile / n_ftiles) * (128 * MT);
-                const int64_t rg0 = (int64_t)ftile * 2;
+                const uint8_t* wb = ftile < n_ft1 ? A.w : A.w2;
+                const int64_t rg0 = (int64_t)(ftile < n_ft1 ? ftile : ftile - n_ft1) * 2;
                 const int kb1 = kb_begin(ks + 1);
                 for (int kb = kb_begin(ks); kb < kb1; kb++, it++) {
                     const int s = it % kStages, round = it / kStages;
@@ -430,9 +434,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap xmap, const GemmArgs A) {
                     for (int gi = 0; gi < 2; gi++) {
                         const int64_t u = (rg0 + gi) * nb + kb;
                         const uint32_t dst = pk + gi * SM::kPackedGroup;
-                        bulk_g2s_w(dst, A.w + u * SM::kSuper, SM::kSuper, full_bar(s), leader);
-                        bulk_g2s_w(dst + SM::kSuper, A.w + A.G.off_s + u * 128, 128, full_bar(s), leader);
-                        if (E::kHasMin) bulk_g2s_w(dst + SM::kSuper + 128, A.w + A.G.off_m + u * 128, 128, full_bar(s), leader);
+                        bulk_g2s_w(dst, wb + u * SM::kSuper, SM::kSuper, full_bar(s), leader);
+                        bulk_g2s_w(dst + SM::kSuper, wb + A.G.off_s + u * 128, 128, full_bar(s), leader);
+                        if (E::kHasMin) bulk_g2s_w(dst + SM::kSuper + 128, wb + A.G.off_m + u * 128, 128, full_bar(s), leader);
                     }
                 }
             }
@@ -525,7 +529,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap xmap, const GemmArgs A) {
         int ti = 0;
         for (int unit = blockIdx.x; unit < n_units; unit += gridDim.x, ti++) {
             const int tile = unit % n_tiles, ks = unit / n_tiles;
-            const int ftile = tile % n_ftiles, m0 = (tile / n_ftiles) * (128 * MT);
+            const int ftile_all = tile % n_ftiles, m0 = (tile / n_ftiles) * (128 * MT);
+            const int ftile = ftile_all < n_ft1 ? ftile_all : ftile_all - n_ft1;
+            void* ybase = ftile_all < n_ft1 ? A.y : A.y2;
             const int buf = ti & 1;
             mbar_wait(tmem_full(buf), (uint32_t)((ti >> 1) & 1));
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
@@ -541,7 +547,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap xmap, const GemmArgs A) {
                             float4* pp = reinterpret_cast<float4*>(A.part + ((int64_t)ks * A.M + token) * A.G.rows + (int64_t)ftile * kTileN + c);
 #pragma unroll
                             for (int i = 0; i < 8; i++) pp[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
-                        } else store_vals(A, token, (int64_t)ftile * kTileN + c, v);
+                        } else store_vals(A, ybase, token, (int64_t)ftile * kTileN + c, v);
                     }
                 }
             }
@@ -1020,14 +1026,16 @@ size_t gemm_tc_workspace_size(int64_t n_rows, int64_t k, int64_t m, int x_dtype)
     return x_convert_bytes(k, m, x_dtype) + (ks > 1 ? (size_t)ks * m * n_main * sizeof(float) : 0);
 }
 
-// rows [0, n_main) with n_main = n_rows & ~127 are computed here; the caller handles the rest
-int gemm_tc_launch(const void* w, int qt, int64_t n_rows, int64_t k, const void* x, int x_dtype, int64_t m, void* y,
-                   int y_dtype, const void* bias, int accumulate, void* workspace, size_t workspace_bytes, cudaStream_t st,
-                   int64_t* n_done) {
+// rows [0, n_main) with n_main = n_rows & ~127 are computed here; the caller handles the rest.  w2 / y2 (or NULL): a second
+// matrix of the same shape and qtype over the same activations in the same grid (m > 128, no bias, no accumulate).
+static int gemm_tc_launch_impl(const void* w, const void* w2, int qt, int64_t n_rows, int64_t k, const void* x, int x_dtype, int64_t m,
+                               void* y, void* y2, int y_dtype, const void* bias, int accumulate, void* workspace,
+                               size_t workspace_bytes, cudaStream_t st, int64_t* n_done) {
     using namespace gemmtc;
     qt = canon_qtype(qt);
     *n_done = 0;
     if (!gemm_tc_supported(qt, n_rows, k)) return LB_ERR_ARG;
+    if (w2 && (!y2 || m <= 128 || bias || accumulate || ((uintptr_t)w2 & 15))) return LB_ERR_ARG;
     EncodeTiledFn enc = encode_fn();
     if (!enc) { set_error(LB_ERR_CUDA, "cuTensorMapEncodeTiled is not available from this driver"); return LB_ERR_CUDA; }
     const int64_t n_main = n_rows & ~int64_t(127);
@@ -1053,20 +1061,21 @@ int gemm_tc_launch(const void* w, int qt, int64_t n_rows, int64_t k, const void*
                      CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) { set_error(LB_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d)", (int)r); return LB_ERR_CUDA; }
     GemmArgs A;
-    A.w = (const uint8_t*)w; A.G = make_geom(n_rows, k, qt); A.M = (int)m;
+    A.w = (const uint8_t*)w; A.w2 = (const uint8_t*)w2; A.y2 = y2; A.G = make_geom(n_rows, k, qt); A.M = (int)m;
     A.y = y; A.y_dtype = y_dtype; A.bias = bias; A.accumulate = accumulate;
+    const int64_t n_mats = w2 ? 2 : 1;
     // token tile: 256 (two accumulator tiles per CTA, half the weight traffic) unless 128 gives fewer
     // rounds of the 1-CTA-per-SM grid over the SMs
     int mt = 1;
     if (m > 128) {
         const int64_t sms = sm_count();
-        const int64_t c2 = (n_main / 128) * ((m + 255) / 256), c1 = (n_main / 128) * ((m + 127) / 128);
+        const int64_t c2 = n_mats * (n_main / 128) * ((m + 255) / 256), c1 = n_mats * (n_main / 128) * ((m + 127) / 128);
         // rounds of the grid x time per k-block of a unit: measured 0.46 us for a 256-token unit (one expansion serves two
         // token sub-tiles) against 0.33 us for a 128-token one
         const int64_t t2 = (c2 + sms - 1) / sms * 14, t1 = (c1 + sms - 1) / sms * 10;
         mt = t2 <= t1 ? 2 : 1;
     }
-    const int64_t n_tiles = (n_main / 128) * ((m + 128 * mt - 1) / (128 * mt));
+    const int64_t n_tiles = n_mats * (n_main / 128) * ((m + 128 * mt - 1) / (128 * mt));
     A.ksplit = m <= 128 ? pick_ksplit(n_tiles, k / 64, m, n_main) : 1;      // one token tile: few output tiles
     A.part = nullptr;
     if (A.ksplit > 1) {
@@ -1094,6 +1103,22 @@ int gemm_tc_launch(const void* w, int qt, int64_t n_rows, int64_t k, const void*
     }
     *n_done = n_main;
     return check_launch();
+}
+
+int gemm_tc_launch(const void* w, int qt, int64_t n_rows, int64_t k, const void* x, int x_dtype, int64_t m, void* y,
+                   int y_dtype, const void* bias, int accumulate, void* workspace, size_t workspace_bytes, cudaStream_t st,
+                   int64_t* n_done) {
+    return gemm_tc_launch_impl(w, nullptr, qt, n_rows, k, x, x_dtype, m, y, nullptr, y_dtype, bias, accumulate, workspace,
+                               workspace_bytes, st, n_done);
+}
+
+// gate and up of an MLP at prefill sizes: y = x W^T and y2 = x W2^T from ONE grid.  Two launches of 172 tiles each
+// (11008 x 4096 at 512 tokens) are two rounds over 148 SMs EACH; 344 tiles are three rounds together.
+int gemm_tc_pair_launch(const void* w, const void* w2, int qt, int64_t n_rows, int64_t k, const void* x, int x_dtype, int64_t m,
+                        void* y, void* y2, int y_dtype, void* workspace, size_t workspace_bytes, cudaStream_t st) {
+    int64_t done = 0;
+    if (!w2 || !y2 || (n_rows % 128)) return LB_ERR_ARG;
+    return gemm_tc_launch_impl(w, w2, qt, n_rows, k, x, x_dtype, m, y, y2, y_dtype, nullptr, 0, workspace, workspace_bytes, st, &done);
 }
 
 #ifdef LOWBIT_SK_TIMESTAMPS

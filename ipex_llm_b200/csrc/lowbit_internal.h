@@ -79,6 +79,9 @@ size_t gemm_tc_workspace_size(int64_t n_rows, int64_t k, int64_t m, int x_dtype)
 int gemm_tc_launch(const void* w, int qt, int64_t n_rows, int64_t k, const void* x, int x_dtype, int64_t m, void* y,
                    int y_dtype, const void* bias, int accumulate, void* workspace, size_t workspace_bytes, cudaStream_t st,
                    int64_t* n_done);
+// gate and up of an MLP in one grid (m > 128, n_rows % 128 == 0)
+int gemm_tc_pair_launch(const void* w, const void* w2, int qt, int64_t n_rows, int64_t k, const void* x, int x_dtype, int64_t m,
+                        void* y, void* y2, int y_dtype, void* workspace, size_t workspace_bytes, cudaStream_t st);
 
 // M above this goes to the tensor-core GEMM when the shape allows, else to chunks of the GEMV
 constexpr int64_t kGemvMaxM = 32;

@@ -82,7 +82,8 @@ def test_mlp_fused_matches_oracle(lbl, cuda_device, qtype, xdt, M, act):
 
 
 @pytest.mark.parametrize("shape,M", [((11008, 4096), 1), ((14336, 4096), 2), ((1000, 704), 3), ((256, 2048), 12),
-                                     ((256, 2048), 48), ((64, 64), 1), ((11008, 4096), 24), ((1280, 640), 33), ((512, 1024), 100)])
+                                     ((256, 2048), 48), ((64, 64), 1), ((11008, 4096), 24), ((1280, 640), 33), ((512, 1024), 100),
+                                     ((1280, 640), 200), ((11008, 4096), 512), ((2816, 1024), 300)])
 def test_mlp_shapes_and_fallbacks(lbl, cuda_device, shape, M):
     """Llama-2-7B / Llama-3-8B MLP shapes (fused), ragged rows / M > 8 / M > 32 (unfused fallbacks):
     all must agree with two separate matmuls followed by silu * up computed in fp32."""
