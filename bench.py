@@ -279,16 +279,22 @@ def prefill_numbers(model, dev, peaks):
     burst = float(peaks.get("bf16_tflops", 1644.0))
     out = {"peak_tflops": burst, "peak_source": "MEASURED_PEAKS.json bf16_tflops (burst: kernels timed alone)" if peaks else "fallback"}
     for M in (512, 2048):
-        lins = []
+        lins, mlps = [], []
         for layer in core.layers[:8]:                            # rotate over 8 layers' weights: each launch reads cold weights
             a, m = layer.self_attn, layer.mlp
             lins += [a.qkv_proj, a.o_proj, m.gate_proj, m.up_proj, m.down_proj]
+            mlps.append((a.qkv_proj, a.o_proj, m.gate_proj, m.up_proj, m.down_proj))
         xs = {HIDDEN: torch.randn(M, HIDDEN, device=dev).half(), INTER: torch.randn(M, INTER, device=dev).half()}
         ys = {n: torch.empty(M, n, device=dev, dtype=torch.float16) for n in {l.out_len for l in lins}}
 
         def run():
-            for lin in lins:
-                lbl.lowbit_matmul(xs[lin.in_len], lin.weight.data, lin.weight_shape, lin.qtype, out=ys[lin.out_len])
+            # the linears as the model's forward issues them: qkv, o, gate + up through mlp_forward (ONE grid of the
+            # tensor-core kernel for both matrices, then the activation kernel -- its time is inside the figure), down
+            for qkv, o, gate, up, down in mlps:
+                lbl.lowbit_matmul(xs[HIDDEN], qkv.weight.data, qkv.weight_shape, qkv.qtype, out=ys[qkv.out_len])
+                lbl.lowbit_matmul(xs[HIDDEN], o.weight.data, o.weight_shape, o.qtype, out=ys[o.out_len])
+                lbl.mlp_forward(xs[HIDDEN], gate.weight.data, up.weight.data, M, HIDDEN, INTER, lbl.SILU, gate.qtype, out=ys[INTER])
+                lbl.lowbit_matmul(xs[INTER], down.weight.data, down.weight_shape, down.qtype, out=ys[down.out_len])
 
         for _ in range(2):
             run()
