@@ -291,6 +291,8 @@ struct GemmArgs {
     void* y; int y_dtype;
     const void* bias;
     int accumulate;
+    int half0;               // 256-token tiles only: tiles from this index on (the grid's last, partial round) run as two
+                             // 128-token units each on twice as many SMs; >= the tile count: none
     int ksplit;              // K splits per output tile (1: the epilogue writes y)
     float* part;             // ksplit > 1: fp32 partial sums [ksplit][M][N]
 };
@@ -391,8 +393,14 @@ gemm_kernel(const __grid_constant__ CUtensorMap xmap, const GemmArgs A) {
     const int n_tiles = n_ftiles * ((A.M + 128 * MT - 1) / (128 * MT));
     // work units = tiles x K splits (A.ksplit > 1 when the tiles alone would leave most SMs idle); split ks covers the
     // k-blocks [kb_begin(ks), kb_begin(ks + 1))
-    const int n_units = n_tiles * A.ksplit;
+    const bool halves = MT == 2 && A.half0 < n_tiles;     // (host: only with ksplit == 1)
+    const int n_units = halves ? A.half0 + 2 * (n_tiles - A.half0) : n_tiles * A.ksplit;
     auto kb_begin = [&](int ks) { return A.ksplit == 1 ? ks * nb : (ks * nb) / A.ksplit; };      // ks * nb < 2^31
+    // unit -> output tile, K split, first 128-token sub-tile and the number of sub-tiles it covers
+    auto decode_unit = [&](int unit, int& tile, int& ks, int& mt0, int& mt_n) {
+        if (halves && unit >= A.half0) { const int hu = unit - A.half0; tile = A.half0 + (hu >> 1); ks = 0; mt0 = hu & 1; mt_n = 1; }
+        else { tile = unit % n_tiles; ks = unit / n_tiles; mt0 = 0; mt_n = MT; }
+    };
     constexpr uint32_t ACC_COLS = 128 * MT;            // one accumulator buffer
     constexpr uint32_t TMEM_COLS = 2 * ACC_COLS;       // 256 or 512 (powers of two)
 
@@ -417,8 +425,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap xmap, const GemmArgs A) {
             const uint32_t leader = elect_leader();
             int it = 0;                                              // k-iterations issued so far (all tiles)
             for (int unit = blockIdx.x; unit < n_units; unit += gridDim.x) {
-                const int tile = unit % n_tiles, ks = unit / n_tiles;
-                const int ftile = tile % n_ftiles, m0 = (tile / n_ftiles) * (128 * MT);
+                int tile, ks, mt0, mt_n;
+                decode_unit(unit, tile, ks, mt0, mt_n);
+                const int ftile = tile % n_ftiles, m0 = (tile / n_ftiles) * (128 * MT) + mt0 * 128;
                 const uint8_t* wb = ftile < n_ft1 ? A.w : A.w2;
                 const int64_t rg0 = (int64_t)(ftile < n_ft1 ? ftile : ftile - n_ft1) * 2;
                 const int kb1 = kb_begin(ks + 1);
@@ -426,9 +435,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap xmap, const GemmArgs A) {
                     const int s = it % kStages, round = it / kStages;
                     mbar_wait(empty_bar(s), (uint32_t)((round & 1) ^ 1));
                     const uint32_t st = base + s * STAGE;
-                    mbar_expect_tx_w(full_bar(s), MT * kTileBytesAB + 2 * SM::kPackedGroup, leader);
+                    mbar_expect_tx_w(full_bar(s), mt_n * kTileBytesAB + 2 * SM::kPackedGroup, leader);
 #pragma unroll
-                    for (int mt = 0; mt < MT; mt++) tma_load_2d_w(st + mt * kTileBytesAB, &xmap, kb * 64, m0 + mt * 128, full_bar(s), leader);
+                    for (int mt = 0; mt < MT; mt++)
+                        if (mt < mt_n) tma_load_2d_w(st + mt * kTileBytesAB, &xmap, kb * 64, m0 + mt * 128, full_bar(s), leader);
                     const uint32_t pk = st + (MT + 1) * kTileBytesAB;
 #pragma unroll
                     for (int gi = 0; gi < 2; gi++) {
@@ -453,7 +463,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap xmap, const GemmArgs A) {
                 mbar_wait(tmem_empty(buf), (uint32_t)(((ti >> 1) & 1) ^ 1));      // the epilogue has drained this buffer
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 const uint32_t acc = tmem_base + buf * ACC_COLS;
-                const int kb0 = kb_begin(unit / n_tiles), kb1 = kb_begin(unit / n_tiles + 1);
+                int tile_, ks, mt0_, mt_n;
+                decode_unit(unit, tile_, ks, mt0_, mt_n);
+                const int kb0 = kb_begin(ks), kb1 = kb_begin(ks + 1);
                 for (int kb = kb0; kb < kb1; kb++, it++) {
                     const int s = it % kStages, round = it / kStages;
                     mbar_wait(full_bar(s), (uint32_t)(round & 1));
@@ -463,6 +475,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap xmap, const GemmArgs A) {
                     const uint64_t ad0 = make_desc(st), bd0 = make_desc(st + MT * kTileBytesAB);
 #pragma unroll
                     for (int mt = 0; mt < MT; mt++) {
+                        if (mt >= mt_n) break;
 #pragma unroll
                         for (int k4 = 0; k4 < 4; k4++)       // the address field counts 16-byte units
                             umma_f16_w(acc + mt * 128, ad0 + (uint64_t)((mt * kTileBytesAB + k4 * 32) >> 4), bd0 + (uint64_t)((k4 * 32) >> 4), idesc,
@@ -481,7 +494,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap xmap, const GemmArgs A) {
         const int g = lane >> 2, t = lane & 3;
         int it = 0;
         for (int unit = blockIdx.x; unit < n_units; unit += gridDim.x) {
-            const int kb0 = kb_begin(unit / n_tiles), kb1 = kb_begin(unit / n_tiles + 1);
+            int tile_, ks, mt0_, mt_n_;
+            decode_unit(unit, tile_, ks, mt0_, mt_n_);
+            const int kb0 = kb_begin(ks), kb1 = kb_begin(ks + 1);
             for (int kb = kb0; kb < kb1; kb++, it++) {
                 const int s = it % kStages, round = it / kStages;
                 // both groups wait for every stage, also the other group's: with an odd ring depth a stage alternates
@@ -528,8 +543,9 @@ gemm_kernel(const __grid_constant__ CUtensorMap xmap, const GemmArgs A) {
         const int quarter = warp & 3;
         int ti = 0;
         for (int unit = blockIdx.x; unit < n_units; unit += gridDim.x, ti++) {
-            const int tile = unit % n_tiles, ks = unit / n_tiles;
-            const int ftile_all = tile % n_ftiles, m0 = (tile / n_ftiles) * (128 * MT);
+            int tile, ks, mt0, mt_n;
+            decode_unit(unit, tile, ks, mt0, mt_n);
+            const int ftile_all = tile % n_ftiles, m0 = (tile / n_ftiles) * (128 * MT) + mt0 * 128;
             const int ftile = ftile_all < n_ft1 ? ftile_all : ftile_all - n_ft1;
             void* ybase = ftile_all < n_ft1 ? A.y : A.y2;
             const int buf = ti & 1;
@@ -537,6 +553,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap xmap, const GemmArgs A) {
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 #pragma unroll
             for (int mt = 0; mt < MT; mt++) {
+                if (mt >= mt_n) break;
                 const int64_t token = (int64_t)m0 + mt * 128 + quarter * 32 + lane;
 #pragma unroll 1
                 for (int c = 0; c < 128; c += 32) {
@@ -1072,7 +1089,10 @@ static int gemm_tc_launch_impl(const void* w, const void* w2, int qt, int64_t n_
         const int64_t c2 = n_mats * (n_main / 128) * ((m + 255) / 256), c1 = n_mats * (n_main / 128) * ((m + 127) / 128);
         // rounds of the grid x time per k-block of a unit: measured 0.46 us for a 256-token unit (one expansion serves two
         // token sub-tiles) against 0.33 us for a 128-token one
-        const int64_t t2 = (c2 + sms - 1) / sms * 14, t1 = (c1 + sms - 1) / sms * 10;
+        // a partial last round of 256-token tiles that covers at most half the SMs runs as 128-token units (half0 below)
+        const int64_t rem2 = c2 > sms ? c2 % sms : 0;
+        const int64_t t2 = (rem2 > 0 && 2 * rem2 <= sms) ? (c2 / sms) * 14 + 10 : (c2 + sms - 1) / sms * 14;
+        const int64_t t1 = (c1 + sms - 1) / sms * 10;
         mt = t2 <= t1 ? 2 : 1;
     }
     const int64_t n_tiles = n_mats * (n_main / 128) * ((m + 128 * mt - 1) / (128 * mt));
@@ -1083,7 +1103,13 @@ static int gemm_tc_launch_impl(const void* w, const void* w2, int qt, int64_t n_
         if (!workspace || workspace_bytes < off + (size_t)A.ksplit * m * n_main * sizeof(float)) return LB_ERR_WORKSPACE;
         A.part = reinterpret_cast<float*>((uint8_t*)workspace + off);
     }
-    const int64_t n_units = n_tiles * A.ksplit;
+    int64_t n_units = n_tiles * A.ksplit;
+    A.half0 = 0x7fffffff;
+    static const bool no_halves = getenv("LOWBIT_GEMM_NO_HALVES") && atoi(getenv("LOWBIT_GEMM_NO_HALVES")) != 0;   // development
+    if (mt == 2 && A.ksplit == 1 && n_tiles > sm_count() && !no_halves) {
+        const int64_t rem = n_tiles % sm_count();
+        if (rem > 0 && 2 * rem <= sm_count()) { A.half0 = (int)(n_tiles - rem); n_units = n_tiles + rem; }
+    }
     const dim3 grid((unsigned)(n_units < sm_count() ? n_units : sm_count()), 1, 1);       // persistent CTAs
     switch (qt) {
         case QT_SYM_INT4:  launch_qt<QT_SYM_INT4>(bf, mt, map, A, grid, st); break;
