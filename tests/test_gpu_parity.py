@@ -596,6 +596,31 @@ def test_gemm_prefill_repeatable_with_odd_ring_depth(lbl, cuda_device, qtype, M)
         assert torch.equal(first, again)
 
 
+@pytest.mark.parametrize("qtype,N,M", [("sym_int4", 19200, 300), ("sym_int4", 9600, 512), ("asym_int4", 9472, 700),
+                                        ("fp8_e4m3", 19456, 258), ("nf4", 9600, 385)])
+def test_gemm_prefill_last_round_in_halves(lbl, cuda_device, qtype, N, M):
+    """more 256-token tiles than SMs with a partial last round: those tiles run as two 128-token units each (a half that lies
+    wholly beyond M included), with bias and accumulate in the epilogue -- the same bits as the products of whole tiles
+    (the halves do the same MMAs on the same operands), checked against float64 on the dequantised weights.  Shapes (148 SMs,
+    the host picks 256-token tiles for all of them): 300 tiles + 4 left over, one of whose halves starts at token 384 > M;
+    150 + 2; 222 = 148 + 74 (exactly 148 half units); 304 + 8 with two valid tokens in the second tile; token 384 alone in a half"""
+    rng = np.random.default_rng(N + M)
+    K = 256
+    tiled = lbl.FP4Params(torch.from_numpy(rand_w(rng, N, K)).to(cuda_device), qtype=qid(qtype)).to(cuda_device).data
+    x_t = torch.from_numpy(rng.standard_normal((M, K)).astype(np.float32)).half().to(cuda_device)
+    bias = torch.from_numpy(rng.standard_normal(N).astype(np.float32)).to(cuda_device)
+    res = torch.from_numpy(rng.standard_normal((M, N)).astype(np.float32)).to(cuda_device)
+    out = res.clone()
+    lbl.lowbit_matmul(x_t, tiled, (N, K), qid(qtype), out=out, bias=bias, accumulate=True)
+    wd = lbl.dequantize_device_layout(tiled, (N, K), qid(qtype)).double()
+    want = x_t.double() @ wd.T + bias.double() + res.double()
+    bound = 1e-3 * (x_t.double().abs() @ wd.abs().T) + 1e-5 * (bias.double().abs() + res.double().abs()) + 1e-30
+    assert bool(((out.double() - want).abs() <= bound).all())
+    plain = lbl.lowbit_matmul(x_t, tiled, (N, K), qid(qtype), out_dtype=torch.float32)
+    half_out = lbl.lowbit_matmul(x_t, tiled, (N, K), qid(qtype))
+    assert half_out.dtype == torch.float16 and torch.equal(half_out, plain.half())
+
+
 def test_gemm_prefill_epilogue_and_module(lbl, cuda_device):
     rng = np.random.default_rng(1300)
     N, K, M = 256, 512, 96
