@@ -300,8 +300,10 @@ int lowbit_matmul_cuda(const void* d_w, int qtype, int64_t n_rows, int64_t k,
  * (transformers/models/common.py:146-161; act ids from models/utils.py: SILU 0, GELU 1).
  * d_w_gate / d_w_up: two [N][K] weights of the SAME qtype in the device layout.  For M <= 8 (M <= 16 with fp16 /
  * bf16 activations), N a multiple of 64 and a tensor-core qtype this is ONE kernel launch that streams both matrices once
- * and never writes the two intermediate vectors; otherwise it runs the two matmuls into fp32
- * scratch and one elementwise kernel (same result up to fp32 rounding of the intermediates).
+ * and never writes the two intermediate vectors.  17 <= M <= 64 half-precision rows: both matrices in one pass of the skinny
+ * tensor-core kernel, act * up in its reduction launch.  M > 128 half-precision rows (prefill): gate and up as two outputs of
+ * ONE grid of the tensor-core GEMM (half-precision scratch) + one elementwise kernel.  Otherwise two matmuls into scratch
+ * (fp32 behind the exact GEMV) and the elementwise kernel.  Same result in every case up to the rounding of the intermediates.
  * workspace: NULL (library-owned) or lowbit_mlp_workspace_size() bytes. */
 size_t lowbit_mlp_workspace_size(int64_t n_rows, int64_t k, int64_t m, int x_dtype);
 int lowbit_mlp_cuda(const void* d_w_gate, const void* d_w_up, int qtype, int64_t n_rows, int64_t k,
