@@ -157,8 +157,8 @@ __device__ __forceinline__ void rl_cp_async_wait_all() { asm volatile("cp.async.
 
 // canonical -> tiled.  The 64 row segments go to shared memory AS THEY ARE with 4-byte asynchronous copies (every word of
 // the CTA in flight at once, any 4-byte alignment: k = 11008 gives 5848-byte rows); a lane's 16 code bytes start 2 bytes
-// off a word boundary in every other record, so they are read as five words and funnel-shifted.  Row stride = 8 words
-// (mod 32): the eight rows a warp reads fall into different banks (2-way conflicts at most).
+// off a word boundary in every other record, so they are read as five words and funnel-shifted.  Row stride = 3 words
+// (mod 32): the 16 (row, half) pairs a warp reads per instruction fall into 16 different banks.
 template <int QT>
 __global__ void __launch_bounds__(RL_THREADS, 6)
 relayout_to_tiled_staged_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst, TiledGeom G, int KB, int RSW) {
@@ -364,7 +364,9 @@ static bool relayout_staged_launch(const uint8_t* src, uint8_t* dst, const Tiled
     const int RS = KB * F::CB + 32;
     if (to_device) {
         const int SW = KB * F::BLK / 4;
-        const int RSW = SW + ((8 - SW % 32) + 32) % 32;                              // row stride = 8 words (mod 32)
+        // row stride = 3 words (mod 32): the banks 3 g + 4 c of the 16 (row, 16-byte half) pairs a warp reads per LDS.32 are
+        // all different (stride 8 left rows g and g + 4 on the same bank: 43 % of the wavefronts were conflicts)
+        const int RSW = SW + ((3 - SW % 32) + 32) % 32;
         const int smem = 64 * RSW * 4 + 16;
         relayout_to_tiled_staged_kernel<QT><<<grid, RL_THREADS, smem, st>>>(src, dst, G, KB, RSW);
     } else {
